@@ -1,0 +1,178 @@
+"""Synthetic uint8 I/Q capture generator (RTL-SDR "UC8" format) for the 1090 MHz path.
+
+The reference vendors no raw captures (its test inputs are downloaded at CMake
+configure time, CMakeLists.txt:141; tests/test_1090.cpp:127-146), so every
+input used by tests/ and bench.py is produced here from a fixed seed
+(SURVEY.md section 8d, configs 2 and 3).
+
+Signal model: Mode S pulse-position modulation sampled at 2.4 MS/s.  A frame is
+an 8 us preamble (0.5 us pulses at 0, 1.0, 3.5, 4.5 us) followed by 56 or 112
+data bits of 1 us each (bit 1 = pulse in the first half, bit 0 = pulse in the
+second half).  Each sample integrates the pulse envelope over its 416.7 ns
+window; the carrier has a random phase; additive white Gaussian noise with
+standard deviation `sigma` LSB is added to I and Q around the RTL-SDR DC point
+127.4; the result is rounded and clipped to [0, 255].
+"""
+from __future__ import annotations
+
+import numpy as np
+
+FS_1090 = 2_400_000
+SAMPLES_PER_US = 2.4
+_POLY = 0xFFF409
+
+
+def _crc_table():
+    t = np.zeros(256, dtype=np.uint32)
+    for i in range(256):
+        c = i << 16
+        for _ in range(8):
+            c = ((c << 1) ^ _POLY) if (c & 0x800000) else (c << 1)
+        t[i] = c & 0xFFFFFF
+    return t
+
+
+_CRC_TABLE = _crc_table()
+
+
+def modes_crc(data: bytes) -> int:
+    """CRC-24 remainder of `data` (generator 0xFFF409), MSB first."""
+    rem = 0
+    for b in data:
+        rem = ((rem << 8) & 0xFFFFFF) ^ int(_CRC_TABLE[b ^ ((rem >> 16) & 0xFF)])
+    return rem
+
+
+def make_frame(df: int, icao: int, rng: np.random.Generator, iid: int = 0) -> bytes:
+    """Build one valid Mode S frame (bytes) for the given downlink format.
+
+    DF11/17/18 carry the address in bytes 1..3 and parity (xor IID for DF11)
+    in the last three bytes; the Address/Parity formats DF0/4/5/16/20/21
+    overlay the address on the parity field.
+    """
+    n = 14 if (df & 16) else 7
+    body = bytearray(rng.integers(0, 256, size=n - 3, dtype=np.uint8).tobytes())
+    body[0] = ((df & 31) << 3) | (body[0] & 7)
+    if df in (11, 17, 18):
+        body[1] = (icao >> 16) & 0xFF
+        body[2] = (icao >> 8) & 0xFF
+        body[3] = icao & 0xFF
+        par = modes_crc(bytes(body))
+        if df == 11:
+            par ^= iid & 0x7F
+    else:
+        par = modes_crc(bytes(body)) ^ (icao & 0xFFFFFF)
+    return bytes(body) + bytes([(par >> 16) & 0xFF, (par >> 8) & 0xFF, par & 0xFF])
+
+
+def flip_bits(frame: bytes, bits) -> bytes:
+    b = bytearray(frame)
+    for k in bits:
+        b[k >> 3] ^= 0x80 >> (k & 7)
+    return bytes(b)
+
+
+def _pulse_starts_us(frame: bytes) -> np.ndarray:
+    bits = np.unpackbits(np.frombuffer(frame, dtype=np.uint8))
+    data = 8.0 + np.arange(bits.size) + np.where(bits == 1, 0.0, 0.5)
+    return np.concatenate([np.array([0.0, 1.0, 3.5, 4.5]), data])
+
+
+def synth_capture(n_samples: int,
+                  frames,
+                  starts,
+                  amps,
+                  carrier_phase,
+                  sigma: float,
+                  rng: np.random.Generator,
+                  dc: float = 127.4) -> np.ndarray:
+    """Render `frames` (list of bytes) into an interleaved uint8 I/Q array.
+
+    starts: message start times in (fractional) samples; amps: peak amplitude
+    in LSB; carrier_phase: radians.  Returns uint8[2*n_samples].
+    """
+    sig = np.zeros(n_samples + 8, dtype=np.complex64)
+    if len(frames):
+        idx_all, val_all = [], []
+        for f, t0, a, th in zip(frames, starts, amps, carrier_phase):
+            ps = t0 + _pulse_starts_us(f) * SAMPLES_PER_US          # pulse start, samples
+            pe = ps + 0.5 * SAMPLES_PER_US
+            base = np.floor(ps).astype(np.int64)
+            c = a * np.exp(1j * th)
+            for k in range(3):                                       # a 1.2-sample pulse spans <= 3 samples
+                lo = np.maximum(ps, base + k)
+                hi = np.minimum(pe, base + k + 1)
+                ov = np.clip(hi - lo, 0.0, None)
+                idx_all.append(base + k)
+                val_all.append(ov * c)
+        idx = np.concatenate(idx_all)
+        val = np.concatenate(val_all)
+        ok = (idx >= 0) & (idx < n_samples)
+        idx, val = idx[ok], val[ok]
+        sig[:n_samples] += (np.bincount(idx, weights=val.real, minlength=n_samples)[:n_samples]
+                            + 1j * np.bincount(idx, weights=val.imag, minlength=n_samples)[:n_samples]
+                            ).astype(np.complex64)
+    out = np.empty(2 * n_samples, dtype=np.uint8)
+    chunk = 1 << 22
+    for s in range(0, n_samples, chunk):
+        e = min(n_samples, s + chunk)
+        nz = rng.standard_normal((e - s, 2), dtype=np.float32) * np.float32(sigma)
+        nz[:, 0] += sig[s:e].real + np.float32(dc)
+        nz[:, 1] += sig[s:e].imag + np.float32(dc)
+        np.rint(nz, out=nz)
+        np.clip(nz, 0, 255, out=nz)
+        out[2 * s:2 * e] = nz.astype(np.uint8).reshape(-1)
+    return out
+
+
+def config2(seconds: float = 60.0, seed: int = 0x10900002, msgs_per_s: float = 1000.0,
+            sigma: float = 2.0, pool: int = 512, snr_db=(6.0, 30.0)):
+    """non-overlapping DF17 (70 %) / DF11 IID0 (30 %)
+    frames at 6..30 dB SNR over sigma=2 LSB noise.  Returns (iq uint8, frames, starts)."""
+    rng = np.random.default_rng(seed)
+    n = int(round(seconds * FS_1090))
+    m = int(round(seconds * msgs_per_s))
+    icaos = rng.integers(1, 1 << 24, size=pool)
+    slot = n / max(m, 1)
+    frames, starts = [], []
+    for k in range(m):
+        df = 17 if rng.random() < 0.7 else 11
+        frames.append(make_frame(df, int(icaos[rng.integers(0, pool)]), rng))
+        # one frame per slot, uniformly placed so that frames never overlap
+        room = slot - 300.0
+        starts.append(k * slot + (rng.random() * room if room > 0 else 0.0))
+    starts = np.array(starts)
+    snr = rng.uniform(snr_db[0], snr_db[1], size=m)
+    amps = np.minimum(sigma * np.sqrt(2.0) * 10.0 ** (snr / 20.0), 90.0)
+    ph = rng.uniform(0, 2 * np.pi, size=m)
+    iq = synth_capture(n, frames, starts, amps, ph, sigma, rng)
+    return iq, frames, starts
+
+
+def config3(seconds: float = 1.0, seed: int = 0x10900003, msgs_per_s: float = 2000.0,
+            sigma: float = 2.0, pool: int = 2000):
+    """Poisson arrivals (overlaps allowed), mixed DFs,
+    10 % frames with one flipped bit and 5 % with two."""
+    rng = np.random.default_rng(seed)
+    n = int(round(seconds * FS_1090))
+    m = int(rng.poisson(seconds * msgs_per_s))
+    icaos = rng.integers(1, 1 << 24, size=pool)
+    dfs = rng.choice([17, 11, 4, 5, 20, 21, 18, 0, 16], size=m,
+                     p=[0.40, 0.15, 0.10, 0.08, 0.08, 0.07, 0.06, 0.03, 0.03])
+    frames = []
+    for k in range(m):
+        f = make_frame(int(dfs[k]), int(icaos[rng.integers(0, pool)]), rng,
+                       iid=int(rng.integers(0, 16)) if rng.random() < 0.2 else 0)
+        u = rng.random()
+        nb = len(f) * 8
+        if u < 0.10:
+            f = flip_bits(f, [int(rng.integers(0, nb))])
+        elif u < 0.15:
+            f = flip_bits(f, [int(x) for x in rng.choice(nb, size=2, replace=False)])
+        frames.append(f)
+    starts = np.sort(rng.uniform(0, max(n - 400, 1), size=m))
+    snr = rng.uniform(6.0, 30.0, size=m)
+    amps = np.minimum(sigma * np.sqrt(2.0) * 10.0 ** (snr / 20.0), 90.0)
+    ph = rng.uniform(0, 2 * np.pi, size=m)
+    iq = synth_capture(n, frames, starts, amps, ph, sigma, rng)
+    return iq, frames, starts
