@@ -1,0 +1,545 @@
+/*
+ * TEST INFRASTRUCTURE ONLY -- see oracle1090.h.  CPU restatement of the
+ * reference's 1090 MHz path; every function cites the reference lines it
+ * follows (paths relative to /root/reference).  Written from the behaviour of
+ * that code, not copied from it.
+ */
+#include "oracle1090.h"
+
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define OVERLAP        326u      /* dump1090/dump1090.c:159 (8+112+16 us at 2.4 MS/s) */
+#define DEFAULT_BLOCK  131072u   /* dump1090/dump1090.h:92-94 */
+#define FILTER_SLOTS   4096u     /* dump1090/icao_filter.c:23 */
+#define FILTER_EMPTY   0xFFFFFFFFu
+#define NT_FLAG        (1u << 25) /* dump1090/icao_filter.h:24 */
+#define NON_ICAO       (1u << 24) /* dump1090/dump1090.h:262 */
+#define UNCHECKED      0xFFFFFFFFu
+
+/* score ranks, dump1090/mode_s.h:32-80 */
+enum {
+    R_NOT_SET = 0, R_ALL_ZEROS, R_UNKNOWN_DF, R_UNCORRECTABLE, R_UNKNOWN_THRESHOLD,
+    R_UNRELIABLE_UNKNOWN, R_DF11_IID_1ERR_UNK, R_DF11_ACQ_1ERR_UNK, R_DF11_IID_UNK,
+    R_DF18_2ERR_UNK, R_DF17_2ERR_UNK, R_ACCEPT_THRESHOLD, R_UNRELIABLE_KNOWN,
+    R_DF18_2ERR_KNOWN, R_DF17_2ERR_KNOWN, R_DF18_1ERR_UNK, R_DF17_1ERR_UNK,
+    R_DF11_ACQ_UNK, R_DF11_IID_1ERR_KNOWN, R_DF11_ACQ_1ERR_KNOWN, R_DF11_IID_KNOWN,
+    R_DF18_1ERR_KNOWN, R_DF17_1ERR_KNOWN, R_DF11_ACQ_KNOWN, R_DF18_UNK, R_DF17_UNK,
+    R_DF18_KNOWN, R_DF17_KNOWN
+};
+
+typedef struct {
+    uint32_t syndrome;
+    int      nerr;       /* 1 or 2; -1 while flagged for removal */
+    int8_t   bit[2];
+} synd_entry;
+
+struct oracle1090 {
+    int nfix, fix_df;
+    unsigned block;
+    uint32_t crc_tab[256];
+    uint32_t bit_synd[112];
+    synd_entry *tab_short, *tab_long;
+    int n_short, n_long;
+    uint32_t valid_short, valid_long;   /* DF pre-filter bitsets */
+    uint32_t filter[FILTER_SLOTS];      /* file mode: the active table never flips (dump1090.c:469-472) */
+    uint16_t lut[65536];
+    uint16_t *mag;                      /* OVERLAP + block */
+    uint16_t tail[OVERLAP];             /* fifo.c overlap_buffer */
+    unsigned last_message_end;
+    uint64_t sample_counter;
+    uint8_t  scratch[2][14];            /* msg1/msg2 of demod_2400.c:103 (stale bytes persist) */
+    int      scratch_sel;
+};
+
+/* ---- magnitude table: dump1090/dsp/helpers/tables.c:9-41 ---------------------------- */
+void oracle1090_mag_table(uint16_t out[65536])
+{
+    for (int i = 0; i < 256; i++) {
+        for (int q = 0; q < 256; q++) {
+            volatile float fi = (float) ((i - 127.4) / 128);   /* double expression narrowed to float */
+            volatile float fq = (float) ((q - 127.4) / 128);
+            volatile float ii = fi * fi;                       /* volatile: no FMA contraction */
+            volatile float qq = fq * fq;
+            volatile float sq = ii + qq;
+            float mag = (float) round((double) (sqrtf(sq) * 65536.0f));
+            if (mag > 65535) mag = 65535;
+            out[(unsigned) i | ((unsigned) q << 8)] = (uint16_t) mag;  /* little-endian {I,Q}: dsp-types.h:6-14 */
+        }
+    }
+}
+
+/* ---- CRC-24: dump1090/crc.c:28-81 ---------------------------------------------------- */
+static void crc_init(oracle1090 *o)
+{
+    for (unsigned v = 0; v < 256; v++) {
+        uint32_t c = v << 16;
+        for (int k = 0; k < 8; k++)
+            c = (c & 0x800000) ? ((c << 1) ^ 0xFFF409u) : (c << 1);
+        o->crc_tab[v] = c & 0xFFFFFF;
+    }
+}
+
+static uint32_t crc24(const oracle1090 *o, const uint8_t *m, int bits)
+{
+    int n = bits / 8;
+    uint32_t rem = 0;
+    for (int i = 0; i < n - 3; i++)
+        rem = ((rem << 8) ^ o->crc_tab[m[i] ^ ((rem >> 16) & 0xFF)]) & 0xFFFFFF;
+    return rem ^ ((uint32_t) m[n - 3] << 16) ^ ((uint32_t) m[n - 2] << 8) ^ m[n - 1];
+}
+
+/* ---- syndrome tables: dump1090/crc.c:182-381 ----------------------------------------- */
+static int cmp_synd(const void *a, const void *b)
+{
+    uint32_t x = ((const synd_entry *) a)->syndrome, y = ((const synd_entry *) b)->syndrome;
+    return (x > y) - (x < y);
+}
+
+static synd_entry *find_synd(synd_entry *t, int n, uint32_t s)
+{
+    int lo = 0, hi = n - 1;
+    while (lo <= hi) {
+        int mid = (lo + hi) / 2;
+        if (t[mid].syndrome == s) return &t[mid];
+        if (t[mid].syndrome < s) lo = mid + 1; else hi = mid - 1;
+    }
+    return NULL;
+}
+
+/* flag entries whose syndrome is also produced by a (weight)-bit error: crc.c:152-177 */
+static void flag_aliases(const oracle1090 *o, synd_entry *t, int n, int off, int bits,
+                         int start, uint32_t acc, int depth, int lo_w, int hi_w)
+{
+    if (depth > hi_w) return;
+    for (int i = start; i < bits; i++) {
+        uint32_t s = acc ^ o->bit_synd[i + off];
+        if (depth >= lo_w) {
+            synd_entry *e = find_synd(t, n, s);
+            if (e) e->nerr = -1;
+        }
+        flag_aliases(o, t, n, off, bits, i + 1, s, depth + 1, lo_w, hi_w);
+    }
+}
+
+static synd_entry *build_table(const oracle1090 *o, int bits, int max_correct, int max_detect, int *n_out)
+{
+    *n_out = 0;
+    if (max_correct <= 0) return NULL;
+    int off = 112 - bits;
+    int cap = bits + (max_correct >= 2 ? bits * (bits - 1) / 2 : 0);
+    synd_entry *t = malloc((size_t) cap * sizeof(*t));
+    int n = 0;
+    for (int a = 0; a < bits; a++) {
+        t[n++] = (synd_entry) { o->bit_synd[a + off], 1, { (int8_t) a, -1 } };
+        if (max_correct >= 2)
+            for (int b = a + 1; b < bits; b++)
+                t[n++] = (synd_entry) { o->bit_synd[a + off] ^ o->bit_synd[b + off], 2, { (int8_t) a, (int8_t) b } };
+    }
+    qsort(t, (size_t) n, sizeof(*t), cmp_synd);
+    /* drop every member of a group sharing one syndrome (crc.c:245-262) */
+    int w = 0;
+    for (int i = 0; i < n;) {
+        int k = i + 1;
+        while (k < n && t[k].syndrome == t[i].syndrome) k++;
+        if (k == i + 1) t[w++] = t[i];
+        i = k;
+    }
+    n = w;
+    if (max_detect > max_correct) {           /* crc.c:265-292 */
+        flag_aliases(o, t, n, off, bits, 0, 0, 1, max_correct + 1, max_detect);
+        w = 0;
+        for (int i = 0; i < n; i++)
+            if (t[i].nerr != -1) t[w++] = t[i];
+        n = w;
+    }
+    *n_out = n;
+    return t;
+}
+
+/* ---- ICAO filter: dump1090/icao_filter.c:40-109 (single active table, no expiry) ----- */
+static uint32_t filter_hash(uint32_t a)
+{
+    uint32_t h = 0;
+    for (int k = 0; k < 3; k++) {       /* Jenkins one-at-a-time over the low three bytes */
+        h += (a >> (8 * k)) & 0xFF;
+        h += h << 10;
+        h ^= h >> 6;
+    }
+    h += h << 3;
+    h ^= h >> 11;
+    h += h << 15;
+    return h & (FILTER_SLOTS - 1);
+}
+
+void oracle1090_filter_add(oracle1090 *o, uint32_t addr)
+{
+    uint32_t h0 = filter_hash(addr), h = h0;
+    while (o->filter[h] != FILTER_EMPTY && o->filter[h] != addr) {
+        h = (h + 1) & (FILTER_SLOTS - 1);
+        if (h == h0) return;            /* table full: silently dropped */
+    }
+    if (o->filter[h] == FILTER_EMPTY) o->filter[h] = addr;
+}
+
+int oracle1090_filter_test(oracle1090 *o, uint32_t addr)
+{
+    uint32_t h0 = filter_hash(addr), h = h0;
+    while (o->filter[h] != FILTER_EMPTY && o->filter[h] != addr) {
+        h = (h + 1) & (FILTER_SLOTS - 1);
+        if (h == h0) break;
+    }
+    return o->filter[h] == addr;
+}
+
+/* ---- message correction: dump1090/mode_s.c:252-346 ----------------------------------- */
+static const uint32_t k_fixable_short[3] = { 0x00000800u, 0x08008e08u, 0x08008e08u }; /* mode_s.c:260-262 */
+static const uint32_t k_fixable_long[3]  = { 0x00060000u, 0x066f0006u, 0x6fff066fu }; /* mode_s.c:263-265 */
+
+static unsigned df_of(const uint8_t *m) { return m[0] >> 3; }
+
+static const synd_entry k_no_errors = { 0, 0, { -1, -1 } };
+
+static const synd_entry *diagnose(const oracle1090 *o, uint32_t s, int bits)   /* crc.c:386-405 */
+{
+    if (s == 0) return &k_no_errors;
+    synd_entry *t = bits == 56 ? o->tab_short : o->tab_long;
+    int n = bits == 56 ? o->n_short : o->n_long;
+    return t ? find_synd(t, n, s) : NULL;
+}
+
+static void apply_fix(uint8_t *m, const synd_entry *e)                        /* crc.c:409-418 */
+{
+    for (int i = 0; i < e->nerr; i++)
+        m[e->bit[i] >> 3] ^= (uint8_t) (0x80 >> (e->bit[i] & 7));
+}
+
+static int correct_message(const oracle1090 *o, const uint8_t *in, uint8_t *out,
+                           uint32_t *ss, uint32_t *ls)
+{
+    *ss = *ls = UNCHECKED;
+    uint32_t dfbit = 1u << df_of(in);
+    int sel = o->fix_df ? o->nfix : 0;
+    const synd_entry *le = NULL, *se = NULL;
+
+    if (k_fixable_long[sel] & dfbit) {
+        *ls = crc24(o, in, 112);
+        if ((df_of(in) == 17 || df_of(in) == 18) && *ls == 0) { memcpy(out, in, 14); return 0; }
+        le = diagnose(o, *ls, 112);
+    }
+    if (k_fixable_short[sel] & dfbit) {
+        *ss = crc24(o, in, 56);
+        if (df_of(in) == 11 && (*ss & 0xFFFF80u) == 0) { memcpy(out, in, 7); return 0; }
+        se = diagnose(o, *ss, 56);
+    }
+    unsigned lerr = le ? (unsigned) le->nerr : 999, serr = se ? (unsigned) se->nerr : 999;
+
+    if (le && lerr <= serr) {                      /* fewer errors first; tie -> long first */
+        memcpy(out, in, 14); apply_fix(out, le);
+        if (df_of(out) == 17 || df_of(out) == 18) return (int) lerr;
+    }
+    if (se && serr == 1) {                         /* DF11: never more than one bit */
+        memcpy(out, in, 7); apply_fix(out, se);
+        if (df_of(out) == 11) return (int) serr;
+    }
+    if (le && lerr > serr) {
+        memcpy(out, in, 14); apply_fix(out, le);
+        if (df_of(out) == 17 || df_of(out) == 18) return (int) lerr;
+    }
+    memcpy(out, in, 14);
+    return -1;
+}
+
+/* ---- scoring: dump1090/mode_s.c:350-466 ---------------------------------------------- */
+static int score_message(oracle1090 *o, const uint8_t *raw)
+{
+    static const uint8_t zeros[7] = { 0 };
+    if (!memcmp(raw, zeros, 7)) return R_ALL_ZEROS;
+
+    uint8_t fixed[14];
+    uint32_t ss, ls;
+    int nc = correct_message(o, raw, fixed, &ss, &ls);
+    uint32_t addr = ((uint32_t) fixed[1] << 16) | ((uint32_t) fixed[2] << 8) | fixed[3];
+    int known;
+
+    switch (df_of(fixed)) {
+    case 0: case 4: case 5:
+        if (ss == UNCHECKED) ss = crc24(o, fixed, 56);
+        return oracle1090_filter_test(o, ss) ? R_UNRELIABLE_KNOWN : R_UNRELIABLE_UNKNOWN;
+    case 16: case 20: case 21:
+        if (ls == UNCHECKED) ls = crc24(o, fixed, 112);
+        return oracle1090_filter_test(o, ls) ? R_UNRELIABLE_KNOWN : R_UNRELIABLE_UNKNOWN;
+    case 24: case 25: case 26: case 27: case 28: case 29: case 30: case 31:
+        return R_UNCORRECTABLE;                    /* enable_df24 is off */
+    case 11: {
+        if (ss == UNCHECKED) ss = crc24(o, fixed, 56);
+        int acq = (ss & 0x7F) == 0;                /* IID taken from the syndrome of the *uncorrected* bytes */
+        known = oracle1090_filter_test(o, addr);
+        if (nc == 0) return acq ? (known ? R_DF11_ACQ_KNOWN : R_DF11_ACQ_UNK) : (known ? R_DF11_IID_KNOWN : R_DF11_IID_UNK);
+        if (nc == 1) return acq ? (known ? R_DF11_ACQ_1ERR_KNOWN : R_DF11_ACQ_1ERR_UNK) : (known ? R_DF11_IID_1ERR_KNOWN : R_DF11_IID_1ERR_UNK);
+        return R_UNCORRECTABLE;
+    }
+    case 17:
+        known = oracle1090_filter_test(o, addr);
+        if (nc == 0) return known ? R_DF17_KNOWN : R_DF17_UNK;
+        if (nc == 1) return known ? R_DF17_1ERR_KNOWN : R_DF17_1ERR_UNK;
+        if (nc == 2) return known ? R_DF17_2ERR_KNOWN : R_DF17_2ERR_UNK;
+        return R_UNCORRECTABLE;
+    case 18:
+        known = oracle1090_filter_test(o, addr | NT_FLAG);
+        if (nc == 0) return known ? R_DF18_KNOWN : R_DF18_UNK;
+        if (nc == 1) return known ? R_DF18_1ERR_KNOWN : R_DF18_1ERR_UNK;
+        if (nc == 2) return known ? R_DF18_2ERR_KNOWN : R_DF18_2ERR_UNK;
+        return R_UNCORRECTABLE;
+    default:
+        return R_UNKNOWN_DF;
+    }
+}
+
+int oracle1090_score(oracle1090 *o, const uint8_t msg[14]) { return score_message(o, msg); }
+uint32_t oracle1090_crc(const uint8_t *msg, int bits)
+{
+    static oracle1090 tmp; static int init;
+    if (!init) { crc_init(&tmp); init = 1; }
+    return crc24(&tmp, msg, bits);
+}
+
+/* 1-based big-endian bit / field access, as util getbit/getbits in the reference */
+static unsigned mbit(const uint8_t *d, unsigned n) { return (d[(n - 1) >> 3] >> (7 - ((n - 1) & 7))) & 1; }
+static unsigned mbits(const uint8_t *d, unsigned a, unsigned b)
+{
+    unsigned v = 0;
+    for (unsigned k = a; k <= b; k++) v = (v << 1) | mbit(d, k);
+    return v;
+}
+
+/* Does decodeExtendedSquitter flag a DF18 address as non-ICAO?  Only this side effect
+ * matters here because the flag ends up in the key handed to icaoFilterAdd
+ * (mode_s.c:786-788).  Follows mode_s.c:1447-1548 with the IMF bit positions at
+ * :869, :991, :1031-1033, :1126, :1137, :1333. */
+static int df18_non_icao(const uint8_t *msg)
+{
+    const uint8_t *me = msg + 4;
+    unsigned cf = msg[0] & 7, metype = me[0] >> 3, imf = 0;
+    switch (cf) {
+    case 0: break;
+    case 1: case 5: return 1;   /* flag set, decoding continues but nothing clears it */
+    case 2: case 6: imf = 1; break;
+    case 3: return (int) mbit(me, 1);
+    default: return 1;
+    }
+    if (!imf) return 0;
+    switch (metype) {
+    case 19: { unsigned sub = mbits(me, 6, 8); return (sub >= 1 && sub <= 4) ? (int) mbit(me, 9) : 0; }
+    case 5: case 6: case 7: case 8: return (int) mbit(me, 21);
+    case 0: case 9: case 10: case 11: case 12: case 13: case 14: case 15: case 16: case 17: case 18:
+    case 20: case 21: case 22: return (int) mbit(me, 8);
+    case 28: return (mbits(me, 6, 8) == 1) ? (int) mbit(me, 56) : 0;
+    case 29: return (int) mbit(me, 51);
+    case 31: return (int) mbit(me, 56);
+    default: return 0;
+    }
+}
+
+/* ---- preamble detector: dump1090/demod_2400.c:155-218 -------------------------------- */
+int oracle1090_preamble(const uint16_t *p)
+{
+    if (!(p[0] < p[1] && p[12] > p[13])) return 0;
+    unsigned hi, sig, noise;
+    int up12 = p[11] < p[12];
+    if (p[1] > p[2] && p[2] < p[3] && p[3] > p[4] && p[8] < p[9] && p[9] > p[10] && p[10] < p[11]) {
+        hi = (p[1] + p[3] + p[9] + p[11] + p[12]) / 4;  sig = p[1] + p[3] + p[9];  noise = p[5] + p[6] + p[7];
+    } else if (p[1] > p[2] && p[2] < p[3] && p[3] > p[4] && p[8] < p[9] && p[9] > p[10] && up12) {
+        hi = (p[1] + p[3] + p[9] + p[12]) / 4;  sig = p[1] + p[3] + p[9] + p[12];  noise = p[5] + p[6] + p[7] + p[8];
+    } else if (p[1] > p[2] && p[2] < p[3] && p[4] > p[5] && p[8] < p[9] && p[10] > p[11] && up12) {
+        hi = (p[1] + p[3] + p[4] + p[9] + p[10] + p[12]) / 4;  sig = p[1] + p[12];  noise = p[6] + p[7];
+    } else if (p[1] > p[2] && p[3] < p[4] && p[4] > p[5] && p[9] < p[10] && p[10] > p[11] && up12) {
+        hi = (p[1] + p[4] + p[10] + p[12]) / 4;  sig = p[1] + p[4] + p[10] + p[12];  noise = p[5] + p[6] + p[7] + p[8];
+    } else if (p[2] > p[3] && p[3] < p[4] && p[4] > p[5] && p[9] < p[10] && p[10] > p[11] && up12) {
+        hi = (p[1] + p[2] + p[4] + p[10] + p[12]) / 4;  sig = p[4] + p[10] + p[12];  noise = p[6] + p[7] + p[8];
+    } else {
+        return 0;
+    }
+    if (sig * 2 < 3 * noise) return 0;
+    static const int quiet[9] = { 5, 6, 7, 8, 14, 15, 16, 17, 18 };
+    for (int k = 0; k < 9; k++)
+        if (p[quiet[k]] >= hi) return 0;
+    return 1;
+}
+
+/* ---- bit slicer: dump1090/demod_2400.c:45-59 and :223-313 in closed form --------------
+ * Symbol k of try_phase p sits u = p + 12k fifths-of-a-sample after m[j+19]; the
+ * correlator used is the one for sub-phase u mod 5 applied at sample floor(u/5). */
+static int slice_bit(const uint16_t *s, int sub)
+{
+    switch (sub) {
+    case 0: return 5 * s[0] - 3 * s[1] - 2 * s[2];
+    case 1: return 4 * s[0] - s[1] - 3 * s[2];
+    case 2: return 3 * s[0] + s[1] - 4 * s[2];
+    case 3: return 2 * s[0] + 3 * s[1] - 5 * s[2];
+    default: return s[0] + 5 * s[1] - 5 * s[2] - s[3];
+    }
+}
+
+static void slice_bytes(const uint16_t *m, int try_phase, uint8_t *out, int first, int count)
+{
+    for (int b = first; b < first + count; b++) {
+        unsigned v = 0;
+        for (int k = 8 * b; k < 8 * b + 8; k++) {
+            int u = try_phase + 12 * k;
+            v = (v << 1) | (slice_bit(m + 19 + u / 5, u % 5) > 0);
+        }
+        out[b] = (uint8_t) v;
+    }
+}
+
+void oracle1090_slice(const uint16_t *m, int try_phase, uint8_t out[14]) { slice_bytes(m, try_phase, out, 0, 14); }
+
+static uint32_t damage_set(unsigned df, int dist)                   /* demod_2400.c:64-78 */
+{
+    uint32_t s = 1u << df;
+    if (dist > 0)
+        for (int b = 0; b < 5; b++) s |= damage_set(df ^ (1u << b), dist - 1);
+    return s;
+}
+
+/* ---- one mag_buf: dump1090/demod_2400.c:99-444 ---------------------------------------- */
+static size_t demod_block(oracle1090 *o, unsigned mlen, uint64_t block_ts,
+                          oracle1090_msg *out, size_t cap, size_t have)
+{
+    const uint16_t *m = o->mag;
+    size_t n = 0;
+    if (o->last_message_end > mlen) o->last_message_end = mlen;
+
+    for (unsigned j = o->last_message_end; j < mlen; j++) {
+        if (!oracle1090_preamble(m + j)) continue;
+
+        int best_score = R_NOT_SET, best_phase = -1;
+        uint8_t *best = NULL;
+        for (int ph = 4; ph <= 8; ph++) {
+            uint8_t *buf = o->scratch[o->scratch_sel];
+            slice_bytes(m + j, ph, buf, 0, 1);
+            uint32_t dfbit = 1u << (buf[0] >> 3);
+            int nbytes = (o->valid_long & dfbit) ? 14 : (o->valid_short & dfbit) ? 7 : 0;   /* :317-325 */
+            if (!nbytes) continue;
+            slice_bytes(m + j, ph, buf, 1, nbytes - 1);
+            int sc = score_message(o, buf);
+            if (sc > best_score) {            /* strict: lowest phase wins ties (:336) */
+                best = buf; best_score = sc; best_phase = ph;
+                o->scratch_sel ^= 1;
+            }
+        }
+        if (best_score < R_ACCEPT_THRESHOLD) continue;
+
+        int msglen = (best[0] & 0x80) ? 112 : 56;          /* from the *uncorrected* DF (:357) */
+        oracle1090_msg mm;
+        memset(&mm, 0, sizeof(mm));
+        mm.timestamp = block_ts + (uint64_t) j * 5 + (8 + 56) * 12 + (uint64_t) best_phase;   /* :366 */
+        mm.score = (uint8_t) best_score;
+
+        /* decodeModesMessage prefix: mode_s.c:520-626 */
+        memcpy(mm.verbatim, best, 14);
+        uint32_t ss, ls;
+        int nc = correct_message(o, best, mm.msg, &ss, &ls);
+        mm.msgtype = (uint8_t) df_of(mm.msg);
+        mm.msgbits = (mm.msgtype & 16) ? 112 : 56;
+        if (mm.msgtype & 16) { if (ls == UNCHECKED) ls = crc24(o, mm.msg, 112); mm.crc = ls; }
+        else                 { if (ss == UNCHECKED) ss = crc24(o, mm.msg, 56);  mm.crc = ss; }
+        mm.correctedbits = (uint8_t) (nc > 0 ? nc : 0);
+        uint32_t aa = ((uint32_t) mm.msg[1] << 16) | ((uint32_t) mm.msg[2] << 8) | mm.msg[3];
+        switch (mm.msgtype) {
+        case 11: case 17: mm.addr = aa; break;
+        case 18: mm.addr = aa | (df18_non_icao(mm.msg) ? NON_ICAO : 0); break;
+        default: mm.addr = mm.crc; break;                  /* Address/Parity formats */
+        }
+        /* filter insertions: mode_s.c:781-788 */
+        if (!mm.correctedbits && (mm.msgtype == 17 || (mm.msgtype == 11 && (mm.crc & 0x7F) == 0)))
+            oracle1090_filter_add(o, mm.addr);
+        if (!mm.correctedbits && mm.msgtype == 18)
+            oracle1090_filter_add(o, mm.addr | NT_FLAG);
+
+        /* signal power: demod_2400.c:382-393 */
+        int siglen = msglen * 12 / 5;
+        uint64_t acc = 0;
+        for (int k = 0; k < siglen; k++) { uint32_t v = m[j + 19 + k]; acc += (uint64_t) (v * v); }
+        mm.signal_level = (acc / 65535.0 / 65535.0) / siglen;
+
+        if (have + n < cap) out[have + n] = mm;
+        n++;
+
+        o->last_message_end = j + (unsigned) ((msglen + 8) * 12 / 5);    /* :410 */
+        j = o->last_message_end - 8 * 12 / 5;                            /* :418; loop then adds 1 */
+    }
+    if (o->last_message_end < mlen) o->last_message_end = 0;            /* :432-443 */
+    else o->last_message_end -= mlen;
+    return n;
+}
+
+size_t oracle1090_feed(oracle1090 *o, const uint8_t *iq, size_t nsamples, oracle1090_msg *out, size_t cap)
+{
+    size_t total = 0, pos = 0;
+    while (pos < nsamples) {
+        size_t take = nsamples - pos < o->block ? nsamples - pos : o->block;
+        memcpy(o->mag, o->tail, sizeof(o->tail));                                   /* fifo.c:187-193 */
+        for (size_t k = 0; k < take; k++)                                           /* magnitude_uc8.c:30-63 */
+            o->mag[OVERLAP + k] = o->lut[(unsigned) iq[2 * (pos + k)] | ((unsigned) iq[2 * (pos + k) + 1] << 8)];
+        memcpy(o->tail, o->mag + take, sizeof(o->tail));                            /* fifo.c:196 */
+        uint64_t ts = (uint64_t) ((double) o->sample_counter * 12e6 / 2400000.0);   /* sdr_ifile.c:202 */
+        total += demod_block(o, (unsigned) take, ts, out, cap, total);
+        o->sample_counter += take;
+        pos += take;
+    }
+    return total;
+}
+
+size_t oracle1090_syndrome_table(oracle1090 *o, int bits, uint32_t *out, size_t cap)
+{
+    synd_entry *t = bits == 56 ? o->tab_short : o->tab_long;
+    size_t n = (size_t) (bits == 56 ? o->n_short : o->n_long);
+    for (size_t i = 0; i < n && i < cap; i++) {
+        out[4 * i] = t[i].syndrome; out[4 * i + 1] = (uint32_t) t[i].nerr;
+        out[4 * i + 2] = (uint32_t) (int32_t) t[i].bit[0]; out[4 * i + 3] = (uint32_t) (int32_t) t[i].bit[1];
+    }
+    return n;
+}
+
+oracle1090 *oracle1090_create(int nfix_crc, int fix_df, unsigned block_samples)
+{
+    oracle1090 *o = calloc(1, sizeof(*o));
+    if (!o) return NULL;
+    o->nfix = nfix_crc < 0 ? 0 : nfix_crc > 2 ? 2 : nfix_crc;
+    o->fix_df = fix_df != 0;
+    o->block = block_samples ? block_samples : DEFAULT_BLOCK;
+    crc_init(o);
+    uint8_t z[14];
+    for (int i = 0; i < 112; i++) {                     /* crc.c:57-62 */
+        memset(z, 0, sizeof(z));
+        z[i >> 3] = (uint8_t) (0x80 >> (i & 7));
+        o->bit_synd[i] = crc24(o, z, 112);
+    }
+    if (o->nfix == 1) {                                 /* crc.c:355-381 */
+        o->tab_short = build_table(o, 56, 1, 1, &o->n_short);
+        o->tab_long = build_table(o, 112, 1, 1, &o->n_long);
+    } else if (o->nfix == 2) {
+        o->tab_short = build_table(o, 56, 2, 4, &o->n_short);
+        o->tab_long = build_table(o, 112, 2, 4, &o->n_long);
+    }
+    o->valid_short = (1u << 0) | (1u << 4) | (1u << 5) | (1u << 11);           /* demod_2400.c:80-93 */
+    o->valid_long = (1u << 16) | (1u << 17) | (1u << 18) | (1u << 20) | (1u << 21);
+    if (o->fix_df && o->nfix) {
+        o->valid_short |= damage_set(11, 1);
+        o->valid_long |= damage_set(17, o->nfix) | damage_set(18, o->nfix);
+    }
+    memset(o->filter, 0xFF, sizeof(o->filter));
+    oracle1090_mag_table(o->lut);
+    o->mag = calloc(OVERLAP + o->block, sizeof(uint16_t));
+    if (!o->mag) { oracle1090_destroy(o); return NULL; }
+    return o;
+}
+
+void oracle1090_destroy(oracle1090 *o)
+{
+    if (!o) return;
+    free(o->tab_short); free(o->tab_long); free(o->mag); free(o);
+}

@@ -1,0 +1,140 @@
+"""TEST INFRASTRUCTURE ONLY: ctypes binding of oracle/liboracle1090.so (the CPU
+restatement) and a runner for oracle/_ref/dump1090_ref (the reference's own code).
+Imported only by tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+import tempfile
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "liboracle1090.so")
+REF_BIN = os.path.join(HERE, "_ref", "dump1090_ref")
+
+MSG_DTYPE = np.dtype([
+    ("timestamp", "<u8"), ("msg", "u1", 14), ("verbatim", "u1", 14), ("msgbits", "u1"),
+    ("correctedbits", "u1"), ("msgtype", "u1"), ("score", "u1"), ("crc", "<u4"), ("addr", "<u4"),
+    ("signal_level", "<f8")])
+assert MSG_DTYPE.itemsize == 56
+
+_lib = None
+
+
+def build():
+    subprocess.run(["make", "-s", "-C", HERE, "all"], check=True)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            build()
+        L = C.CDLL(LIB_PATH)
+        L.oracle1090_create.restype = C.c_void_p
+        L.oracle1090_create.argtypes = [C.c_int, C.c_int, C.c_uint]
+        L.oracle1090_destroy.argtypes = [C.c_void_p]
+        L.oracle1090_feed.restype = C.c_size_t
+        L.oracle1090_feed.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
+        L.oracle1090_mag_table.argtypes = [C.c_void_p]
+        L.oracle1090_crc.restype = C.c_uint32
+        L.oracle1090_crc.argtypes = [C.c_void_p, C.c_int]
+        L.oracle1090_score.argtypes = [C.c_void_p, C.c_void_p]
+        L.oracle1090_syndrome_table.restype = C.c_size_t
+        L.oracle1090_syndrome_table.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]
+        L.oracle1090_filter_add.argtypes = [C.c_void_p, C.c_uint32]
+        L.oracle1090_filter_test.argtypes = [C.c_void_p, C.c_uint32]
+        L.oracle1090_preamble.argtypes = [C.c_void_p]
+        L.oracle1090_slice.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        _lib = L
+    return _lib
+
+
+class Oracle1090:
+    def __init__(self, nfix_crc=0, fix_df=1, block_samples=0):
+        self.h = lib().oracle1090_create(nfix_crc, fix_df, block_samples)
+        if not self.h:
+            raise MemoryError("oracle1090_create failed")
+
+    def close(self):
+        if self.h:
+            lib().oracle1090_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def feed(self, iq: np.ndarray, cap: int | None = None) -> np.ndarray:
+        iq = np.ascontiguousarray(iq, dtype=np.uint8)
+        n = iq.size // 2
+        cap = cap if cap is not None else max(1024, n // 100)
+        out = np.zeros(cap, dtype=MSG_DTYPE)
+        got = lib().oracle1090_feed(self.h, iq.ctypes.data, n, out.ctypes.data, cap)
+        if got > cap:
+            raise OverflowError(f"oracle produced {got} messages, cap {cap}")
+        return out[:got]
+
+    def score(self, msg: bytes) -> int:
+        b = (C.c_uint8 * 14)(*bytes(msg).ljust(14, b"\0"))
+        return lib().oracle1090_score(self.h, b)
+
+    def syndrome_table(self, bits: int) -> np.ndarray:
+        out = np.zeros((8192, 4), dtype=np.uint32)
+        n = lib().oracle1090_syndrome_table(self.h, bits, out.ctypes.data, 8192)
+        return out[:n]
+
+    def filter_add(self, a): lib().oracle1090_filter_add(self.h, a)
+    def filter_test(self, a): return bool(lib().oracle1090_filter_test(self.h, a))
+
+
+def mag_table() -> np.ndarray:
+    t = np.zeros(65536, dtype=np.uint16)
+    lib().oracle1090_mag_table(t.ctypes.data)
+    return t
+
+
+def crc(msg: bytes, bits: int) -> int:
+    b = (C.c_uint8 * 14)(*bytes(msg).ljust(14, b"\0"))
+    return lib().oracle1090_crc(b, bits)
+
+
+def have_ref() -> bool:
+    return os.path.exists(REF_BIN) and os.access(REF_BIN, os.X_OK)
+
+
+def run_ref(iq: np.ndarray, nfix_crc=0, fix_df=1, extra=()) -> np.ndarray:
+    """Run the reference's own dump1090 (--ifile) on `iq`; returns its accepted messages."""
+    flags = {0: [], 1: ["--fix"], 2: ["--fix-2bit"]}[nfix_crc] + ([] if fix_df else ["--no-fix-df"])
+    tmpdir = "/dev/shm" if os.path.isdir("/dev/shm") else None
+    with tempfile.TemporaryDirectory(dir=tmpdir) as d:
+        cap, rec = os.path.join(d, "cap.uc8"), os.path.join(d, "out.rec")
+        np.ascontiguousarray(iq, dtype=np.uint8).tofile(cap)
+        env = dict(os.environ, REF1090_OUT=rec)
+        subprocess.run([REF_BIN, "--ifile", cap, "--quiet", *flags, *extra], env=env,
+                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, check=False)
+        if not os.path.exists(rec):
+            return np.zeros(0, dtype=MSG_DTYPE)
+        return np.fromfile(rec, dtype=MSG_DTYPE)
+
+
+def same_messages(a: np.ndarray, b: np.ndarray, check_signal=True) -> list[str]:
+    """Compare two message arrays on the parity tuple; returns a list of differences."""
+    diffs = []
+    if len(a) != len(b):
+        diffs.append(f"count {len(a)} != {len(b)}")
+    for k in range(min(len(a), len(b))):
+        x, y = a[k], b[k]
+        nb = int(x["msgbits"]) // 8
+        for f in ("timestamp", "msgbits", "correctedbits", "msgtype", "score", "crc", "addr"):
+            if x[f] != y[f]:
+                diffs.append(f"#{k} {f}: {x[f]} != {y[f]}")
+        if bytes(x["msg"][:nb]) != bytes(y["msg"][:nb]):
+            diffs.append(f"#{k} msg differs")
+        if bytes(x["verbatim"][:nb]) != bytes(y["verbatim"][:nb]):
+            diffs.append(f"#{k} verbatim differs")
+        if check_signal and x["signal_level"] != y["signal_level"]:
+            diffs.append(f"#{k} signal_level {x['signal_level']} != {y['signal_level']}")
+        if len(diffs) > 20:
+            break
+    return diffs
