@@ -1,0 +1,130 @@
+/*
+ * adsbcu.h -- C ABI of the B200 (sm_100a) Mode S demodulation engine.
+ *
+ * This is the thin extern "C" layer the reference's host C++ would call from
+ * below its RTLSDR::IDataHandler::HandleData(span<uint8_t const>) entry
+ * (reference RTLSDR.hpp:39-49; caller RTLSDR.hpp:518-539).  It replaces, for
+ * the 1090 MHz band, the work the reference does between "raw uint8 I/Q
+ * buffer" and "accepted Mode S message":
+ *
+ *   dump1090/convert.c:22-44 + dsp/impl/magnitude_uc8.c:30-63   (I/Q -> uint16 magnitude)
+ *   dump1090/fifo.c:173-210                                      (326-sample overlap carry)
+ *   dump1090/demod_2400.c:99-444  demodulate2400()               (preamble, 5-phase slicer)
+ *   dump1090/mode_s.c:252-466     correctMessage/scoreModesMessage
+ *   dump1090/crc.c:65-418         modesChecksum / syndrome tables
+ *   dump1090/icao_filter.c:40-109 recently-seen address filter
+ *   dump1090/mode_s.c:520-626,781-788  decodeModesMessage prefix + filter insertions
+ *
+ * and hands back what demodulate2400() passes to useModesMessage()
+ * (mode_s.c:2274): message bytes, CRC, corrected-bit count, 12 MHz timestamp,
+ * score and RSSI.  Plain pointers and sizes only; no exceptions cross it; every
+ * function returns 0 on success or a negative adsbcu_status.
+ *
+ * Threading: one host thread per handle at a time (the reference's consumer
+ * thread model).  Each handle owns one CUDA stream.
+ */
+#ifndef ADSBCU_H
+#define ADSBCU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ADSBCU_ABI_VERSION 1
+
+typedef enum adsbcu_status {
+    ADSBCU_OK            = 0,
+    ADSBCU_ERR_ARG       = -1,   /* null pointer, bad size, misaligned device pointer */
+    ADSBCU_ERR_CUDA      = -2,   /* a CUDA runtime call failed; see adsbcu_last_error() */
+    ADSBCU_ERR_NO_DEVICE = -3,   /* no usable sm_100 device */
+    ADSBCU_ERR_OVERFLOW  = -4,   /* out[] too small, or an internal candidate list overflowed */
+    ADSBCU_ERR_NOMEM     = -5
+} adsbcu_status;
+
+/* Mirrors the parity-relevant knobs of the reference's global `Modes`
+ * (dump1090/dump1090.c:108-150, :624-633). */
+typedef struct adsbcu_config {
+    uint32_t struct_size;      /* sizeof(adsbcu_config), for ABI evolution */
+    int32_t  device;           /* CUDA device ordinal */
+    int32_t  nfix_crc;         /* 0 = none (reference default), 1 = --fix, 2 = --fix-2bit */
+    int32_t  fix_df;           /* 1 (default) = also repair the DF field; 0 = --no-fix-df */
+    uint32_t block_samples;    /* samples per reference mag_buf; 0 -> 131072 (dump1090.h:92-94).
+                                  Only the skip rule at block boundaries depends on it
+                                  (demod_2400.c:432-443). */
+    uint32_t max_feed_samples; /* largest nsamples accepted by one feed call; 0 -> 1<<24 */
+} adsbcu_config;
+
+#pragma pack(push, 1)
+/* One accepted message == one useModesMessage() call of the reference. */
+typedef struct adsbcu_msg {
+    uint64_t timestamp;        /* 12 MHz: 5*sample + 768 + phase (demod_2400.c:366) */
+    uint8_t  msg[14];          /* corrected bytes; only msgbits/8 are meaningful */
+    uint8_t  verbatim[14];     /* bytes as sliced, before correction */
+    uint8_t  msgbits;          /* 56 or 112 */
+    uint8_t  correctedbits;    /* 0..2 */
+    uint8_t  msgtype;          /* downlink format */
+    uint8_t  score;            /* score_rank (mode_s.h:32-80) */
+    uint32_t crc;              /* mm.crc (mode_s.c:541-549) */
+    uint32_t addr;             /* mm.addr incl. MODES_NON_ICAO_ADDRESS flag (bit 24) */
+    double   signal_level;     /* mean squared magnitude, full scale = 1.0 */
+} adsbcu_msg;
+#pragma pack(pop)
+
+/* Counters and device timings of the most recent feed call. */
+typedef struct adsbcu_stats {
+    uint64_t samples;          /* samples in the feed */
+    uint64_t preambles;        /* positions that passed the preamble detector */
+    uint64_t phase_records;    /* (position, phase) records kept by the scan kernel */
+    uint64_t resolved_records; /* records that survived the known-address filter */
+    uint64_t messages;         /* accepted messages */
+    float    ms_h2d;           /* host->device copy (0 for device feeds) */
+    float    ms_scan;          /* scan kernel (magnitude+preamble+slice+CRC+compaction) */
+    float    ms_finalize;      /* filter/finalize kernel */
+    float    ms_d2h;           /* record download */
+    float    ms_resolve;       /* sequential host pass (wall clock) */
+    uint32_t scan_launches;    /* kernels launched by the feed */
+    uint32_t reserved;
+} adsbcu_stats;
+
+typedef struct adsbcu_handle adsbcu_handle;
+
+int         adsbcu_abi_version(void);
+const char *adsbcu_last_error(const adsbcu_handle *h);   /* h may be NULL: last create() error */
+
+int  adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out);
+void adsbcu_destroy(adsbcu_handle *h);
+
+/* Forget stream state: overlap carry, last_message_end and sample clock, as a
+ * MAGBUF_DISCONTINUOUS buffer does (demod_2400.c:112-115, fifo.c:187-190); if
+ * clear_filter != 0 also icaoFilterInit() (icao_filter.c:64-69). */
+int adsbcu_1090_reset(adsbcu_handle *h, int clear_filter);
+
+/* Demodulate `nsamples` interleaved uint8 I/Q pairs that continue the stream.
+ * iq is HOST memory; the copy to the device is part of the call.  Accepted
+ * messages are appended to out[0..cap) in stream order, *n_out receives their
+ * number.  Equivalent to the reference consuming the same bytes through
+ * sdr_ifile.c:178-245 -> demodulate2400(). */
+int adsbcu_1090_feed(adsbcu_handle *h, const uint8_t *iq, size_t nsamples,
+                     adsbcu_msg *out, size_t cap, size_t *n_out);
+
+/* Same, for I/Q already resident in device memory (16-byte aligned). */
+int adsbcu_1090_feed_device(adsbcu_handle *h, const uint8_t *iq_dev, size_t nsamples,
+                            adsbcu_msg *out, size_t cap, size_t *n_out);
+
+/* Stage-level entry (replaces starch_magnitude_uc8, magnitude_uc8.c:30-63):
+ * mag_out[k] = LUT[I,Q] for k < nsamples, both HOST pointers. */
+int adsbcu_1090_magnitude(adsbcu_handle *h, const uint8_t *iq, size_t nsamples, uint16_t *mag_out);
+
+/* Filter access for host code that shares the reference's icaoFilterAdd/Test view. */
+int adsbcu_1090_filter_add(adsbcu_handle *h, uint32_t addr);
+int adsbcu_1090_filter_test(adsbcu_handle *h, uint32_t addr);   /* 1 = present, 0 = absent */
+
+int adsbcu_get_stats(const adsbcu_handle *h, adsbcu_stats *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,126 @@
+"""ctypes binding of the C ABI in include/adsbcu.h.
+
+This is plumbing for tests and bench.py; the product is libadsbcu.so.  There is no CPU
+fallback: if the library or a B200 is missing, construction raises."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libadsbcu.so")
+
+MSG_DTYPE = np.dtype([
+    ("timestamp", "<u8"), ("msg", "u1", 14), ("verbatim", "u1", 14), ("msgbits", "u1"),
+    ("correctedbits", "u1"), ("msgtype", "u1"), ("score", "u1"), ("crc", "<u4"), ("addr", "<u4"),
+    ("signal_level", "<f8")])
+assert MSG_DTYPE.itemsize == 56
+
+EXPORTS = ["adsbcu_abi_version", "adsbcu_last_error", "adsbcu_create", "adsbcu_destroy", "adsbcu_1090_reset",
+           "adsbcu_1090_feed", "adsbcu_1090_feed_device", "adsbcu_1090_magnitude", "adsbcu_1090_filter_add",
+           "adsbcu_1090_filter_test", "adsbcu_get_stats"]
+
+
+class Config(C.Structure):
+    _fields_ = [("struct_size", C.c_uint32), ("device", C.c_int32), ("nfix_crc", C.c_int32), ("fix_df", C.c_int32),
+                ("block_samples", C.c_uint32), ("max_feed_samples", C.c_uint32)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("samples", C.c_uint64), ("preambles", C.c_uint64), ("phase_records", C.c_uint64),
+                ("resolved_records", C.c_uint64), ("messages", C.c_uint64), ("ms_h2d", C.c_float),
+                ("ms_scan", C.c_float), ("ms_finalize", C.c_float), ("ms_d2h", C.c_float), ("ms_resolve", C.c_float),
+                ("scan_launches", C.c_uint32), ("reserved", C.c_uint32)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved"}
+
+
+_lib = None
+
+
+def load():
+    """dlopen libadsbcu.so (loudly failing if it has not been built)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} missing: run `python -m libadsb_b200.build` (nvcc, sm_100a)")
+        L = C.CDLL(LIB_PATH)
+        L.adsbcu_abi_version.restype = C.c_int
+        L.adsbcu_last_error.restype = C.c_char_p
+        L.adsbcu_last_error.argtypes = [C.c_void_p]
+        L.adsbcu_create.argtypes = [C.POINTER(Config), C.POINTER(C.c_void_p)]
+        L.adsbcu_destroy.argtypes = [C.c_void_p]
+        L.adsbcu_1090_reset.argtypes = [C.c_void_p, C.c_int]
+        L.adsbcu_1090_feed.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.adsbcu_1090_feed_device.argtypes = L.adsbcu_1090_feed.argtypes
+        L.adsbcu_1090_magnitude.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.adsbcu_1090_filter_add.argtypes = [C.c_void_p, C.c_uint32]
+        L.adsbcu_1090_filter_test.argtypes = [C.c_void_p, C.c_uint32]
+        L.adsbcu_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
+        _lib = L
+    return _lib
+
+
+class AdsbcuError(RuntimeError):
+    pass
+
+
+class Demod1090:
+    """One demodulator stream (one `adsbcu_handle`)."""
+
+    def __init__(self, nfix_crc=0, fix_df=1, block_samples=0, max_feed_samples=0, device=0):
+        L = load()
+        cfg = Config(C.sizeof(Config), device, nfix_crc, fix_df, block_samples, max_feed_samples)
+        self.h = C.c_void_p()
+        rc = L.adsbcu_create(C.byref(cfg), C.byref(self.h))
+        if rc != 0:
+            msg = L.adsbcu_last_error(None)
+            self.h = None
+            raise AdsbcuError(f"adsbcu_create failed ({rc}): {msg.decode() if msg else ''}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            load().adsbcu_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def _check(self, rc):
+        if rc != 0:
+            raise AdsbcuError(f"adsbcu error {rc}: {load().adsbcu_last_error(self.h).decode()}")
+
+    def reset(self, clear_filter=True):
+        self._check(load().adsbcu_1090_reset(self.h, int(clear_filter)))
+
+    def feed(self, iq: np.ndarray, cap: int | None = None, out: np.ndarray | None = None) -> np.ndarray:
+        iq = np.ascontiguousarray(iq, dtype=np.uint8)
+        n = iq.size // 2
+        if out is None:
+            out = np.zeros(cap if cap is not None else max(1024, n // 100), dtype=MSG_DTYPE)
+        got = C.c_size_t(0)
+        self._check(load().adsbcu_1090_feed(self.h, iq.ctypes.data, n, out.ctypes.data, len(out), C.byref(got)))
+        return out[:got.value]
+
+    def feed_device(self, dev_ptr: int, nsamples: int, out: np.ndarray) -> np.ndarray:
+        got = C.c_size_t(0)
+        self._check(load().adsbcu_1090_feed_device(self.h, C.c_void_p(dev_ptr), nsamples, out.ctypes.data, len(out),
+                                                   C.byref(got)))
+        return out[:got.value]
+
+    def magnitude(self, iq: np.ndarray) -> np.ndarray:
+        iq = np.ascontiguousarray(iq, dtype=np.uint8)
+        n = iq.size // 2
+        out = np.zeros(n, dtype=np.uint16)
+        self._check(load().adsbcu_1090_magnitude(self.h, iq.ctypes.data, n, out.ctypes.data))
+        return out
+
+    def filter_add(self, addr): self._check(load().adsbcu_1090_filter_add(self.h, addr))
+    def filter_test(self, addr): return bool(load().adsbcu_1090_filter_test(self.h, addr))
+
+    def stats(self) -> dict:
+        s = Stats()
+        self._check(load().adsbcu_get_stats(self.h, C.byref(s)))
+        return s.as_dict()

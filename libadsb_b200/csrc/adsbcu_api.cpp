@@ -1,0 +1,458 @@
+// C ABI (include/adsbcu.h) and the ordered host pass.
+//
+// The GPU evaluates every start position and every phase without any stream state.  What is
+// left for the host is exactly the part of demodulate2400() that is sequential by definition
+// (demod_2400.c:222,336,349-355,410-419,432-443 and mode_s.c:781-788): pick the best-scoring
+// phase per position given the *current* ICAO filter, accept, skip over the message, add the
+// address to the filter, carry last_message_end across mag_buf boundaries.
+#include "../../include/adsbcu.h"
+#include "adsbcu_internal.h"
+
+#include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+using namespace adsbcu;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+// Reference ICAO filter (icao_filter.c:23-109): two 4096-slot open-addressed tables, one
+// active; the flip (icaoFilterExpire) only happens for live SDR input (dump1090.c:469-472).
+struct IcaoFilter {
+    static constexpr uint32_t kSlots = 4096, kEmpty = 0xFFFFFFFFu;
+    uint32_t a[kSlots], b[kSlots];
+    uint32_t *active;
+    IcaoFilter() { clear(); }
+    void clear()
+    {
+        std::memset(a, 0xFF, sizeof(a));
+        std::memset(b, 0xFF, sizeof(b));
+        active = a;
+    }
+    static uint32_t hash(uint32_t v)
+    {
+        uint32_t h = 0;
+        for (int k = 0; k < 3; ++k) {
+            h += (v >> (8 * k)) & 0xFF;
+            h += h << 10;
+            h ^= h >> 6;
+        }
+        h += h << 3;
+        h ^= h >> 11;
+        h += h << 15;
+        return h & (kSlots - 1);
+    }
+    void add(uint32_t v)
+    {
+        const uint32_t h0 = hash(v);
+        uint32_t h = h0;
+        while (active[h] != kEmpty && active[h] != v) {
+            h = (h + 1) & (kSlots - 1);
+            if (h == h0) return;
+        }
+        if (active[h] == kEmpty) active[h] = v;
+    }
+    static bool probe(const uint32_t *t, uint32_t v)
+    {
+        const uint32_t h0 = hash(v);
+        uint32_t h = h0;
+        while (t[h] != kEmpty && t[h] != v) {
+            h = (h + 1) & (kSlots - 1);
+            if (h == h0) break;
+        }
+        return t[h] == v;
+    }
+    bool test(uint32_t v) const { return probe(a, v) || probe(b, v); }
+};
+
+}  // namespace
+
+struct adsbcu_handle {
+    adsbcu_config cfg{};
+    int device = 0, sm_count = 148;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[6]{};
+    std::string error;
+
+    DevTables *d_tab = nullptr;
+    uint32_t *d_bitmap = nullptr;
+    uint16_t *d_carry = nullptr;
+    uint8_t *d_iq = nullptr;          // staging for host feeds
+    PhaseRec *d_phase = nullptr;
+    FullRec *d_full = nullptr;
+    ScanCounters *d_ctr = nullptr;
+    uint32_t phase_cap = 0, full_cap = 0;
+    ScanCounters *h_ctr = nullptr;    // pinned
+    FullRec *h_full = nullptr;        // pinned
+    uint16_t *d_mag = nullptr;        // stage-level magnitude output
+    size_t d_mag_cap = 0;
+
+    // stream state
+    uint64_t stream_pos = 0;          // samples consumed so far == padded coordinate of the next feed's first start
+    bool has_last = false;            // last accepted message: its start and last_message_end, both in
+    uint64_t last_a = 0, last_lme = 0; // stream coordinates counted from the first (zero) overlap sample
+    IcaoFilter filter;
+    adsbcu_stats stats{};
+};
+
+namespace {
+
+bool cuda_ok(adsbcu_handle *h, cudaError_t e, const char *what)
+{
+    if (e == cudaSuccess) return true;
+    char buf[256];
+    std::snprintf(buf, sizeof(buf), "%s: %s", what, cudaGetErrorString(e));
+    if (h) h->error = buf; else g_create_error = buf;
+    return false;
+}
+#define CK(call) do { if (!cuda_ok(h, (call), #call)) return ADSBCU_ERR_CUDA; } while (0)
+
+void free_all(adsbcu_handle *h)
+{
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    cudaFree(h->d_tab); cudaFree(h->d_bitmap); cudaFree(h->d_carry); cudaFree(h->d_iq);
+    cudaFree(h->d_phase); cudaFree(h->d_full); cudaFree(h->d_ctr); cudaFree(h->d_mag);
+    if (h->h_ctr) cudaFreeHost(h->h_ctr);
+    if (h->h_full) cudaFreeHost(h->h_full);
+    for (auto &e : h->ev) if (e) cudaEventDestroy(e);
+    if (h->stream) cudaStreamDestroy(h->stream);
+}
+
+// ---- ordered host pass ------------------------------------------------------------------
+// recs: all surviving (position, phase) records of one feed, sorted by (pos, phase).
+// feed_base: padded-stream coordinate of the feed's first start position.
+int resolve(adsbcu_handle *h, const FullRec *recs, size_t nrec, uint64_t feed_base,
+            adsbcu_msg *out, size_t cap, size_t *n_out)
+{
+    const uint64_t block = h->cfg.block_samples;
+    size_t nmsg = 0;
+    int rc = ADSBCU_OK;
+    size_t i = 0;
+    while (i < nrec) {
+        const uint64_t a = feed_base + recs[i].pos;
+        size_t e = i;
+        while (e < nrec && recs[e].pos == recs[i].pos) ++e;
+        if (h->has_last) {
+            // inside the mag_buf of the last accepted message scanning resumes 18 samples before its
+            // end (j = last_message_end - 19, then ++j); a later mag_buf starts exactly at its end
+            const bool same_block = (a / block) == (h->last_a / block);
+            if (a < (same_block ? h->last_lme - 18 : h->last_lme)) { i = e; continue; }
+        }
+
+        int best = 0;                       // SR_NOT_SET
+        const FullRec *bp = nullptr;
+        for (size_t k = i; k < e; ++k) {    // phases ascending; strict > keeps the lowest phase on ties
+            const int sc = rank_of(recs[k].kind, h->filter.test(recs[k].test_key));
+            if (sc > best) { best = sc; bp = &recs[k]; }
+        }
+        i = e;
+        if (best < kAcceptThreshold) continue;
+
+        const FullRec &r = *bp;
+        if (nmsg < cap) {
+            adsbcu_msg &m = out[nmsg];
+            std::memset(&m, 0, sizeof(m));
+            // sampleTimestamp of the block (sdr_ifile.c:202) + 5*j + 768 + phase: with 12e6/2.4e6 == 5 this
+            // is 5*a + 768 + phase where a counts from the first overlap sample of the stream
+            const uint64_t bstart = (a / block) * block;
+            const uint64_t ts_block = uint64_t(double(bstart) * 12e6 / 2400000.0);
+            m.timestamp = ts_block + (a - bstart) * 5 + (8 + 56) * 12 + r.phase;
+            std::memcpy(m.msg, r.msg, 14);
+            std::memcpy(m.verbatim, r.verbatim, 14);
+            m.msgtype = r.msgtype;
+            m.msgbits = (r.msgtype & 16) ? 112 : 56;
+            m.correctedbits = uint8_t(r.corrections);
+            m.score = uint8_t(best);
+            m.crc = r.crc;
+            m.addr = r.addr;
+            const int msglen = (r.verbatim[0] & 0x80) ? 112 : 56;
+            const int siglen = msglen * 12 / 5;
+            m.signal_level = (double(r.sum_sq) / 65535.0 / 65535.0) / siglen;
+        } else {
+            rc = ADSBCU_ERR_OVERFLOW;
+        }
+        ++nmsg;
+        if (r.add_key != kUnchecked) h->filter.add(r.add_key);
+
+        // skip rule (demod_2400.c:410-419, :432-443): remember where this message ends
+        h->has_last = true;
+        h->last_a = a;
+        h->last_lme = a + uint64_t((((r.verbatim[0] & 0x80) ? 112 : 56) + 8) * 12 / 5);
+    }
+    *n_out = nmsg;
+    return rc;
+}
+
+}  // namespace
+
+// ---- one feed: scan -> finalize -> download -> ordered host pass ---------------------------
+namespace {
+
+int run_feed(adsbcu_handle *h, const uint8_t *d_iq, uint32_t n, bool timed_h2d, adsbcu_msg *out, size_t cap,
+             size_t *n_out)
+{
+    ScanArgs a{};
+    a.iq = d_iq;
+    a.carry_mag = h->d_carry;
+    a.nsamples = n;
+    a.tab = h->d_tab;
+    a.bitmap = h->d_bitmap;
+    a.phase = h->d_phase; a.phase_cap = h->phase_cap;
+    a.full = h->d_full;   a.full_cap = h->full_cap;
+    a.ctr = h->d_ctr;
+
+    CK(cudaMemsetAsync(h->d_ctr, 0, sizeof(ScanCounters), h->stream));
+    CK(cudaEventRecord(h->ev[1], h->stream));
+    CK(launch_scan(a, h->sm_count, h->stream));
+    CK(cudaEventRecord(h->ev[2], h->stream));
+    CK(launch_finalize(a, h->sm_count, h->stream));
+    CK(launch_carry(d_iq, n, h->d_carry, h->d_tab, h->stream));
+    CK(cudaEventRecord(h->ev[3], h->stream));
+    CK(cudaMemcpyAsync(h->h_ctr, h->d_ctr, sizeof(ScanCounters), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    const ScanCounters c = *h->h_ctr;
+    if (c.overflow || c.n_phase > h->phase_cap || c.n_full > h->full_cap) {
+        h->error = "internal candidate list overflow (feed smaller chunks)";
+        return ADSBCU_ERR_OVERFLOW;
+    }
+    if (c.n_full)
+        CK(cudaMemcpyAsync(h->h_full, h->d_full, size_t(c.n_full) * sizeof(FullRec), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaEventRecord(h->ev[4], h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+
+    const auto t0 = std::chrono::steady_clock::now();
+    std::sort(h->h_full, h->h_full + c.n_full, [](const FullRec &x, const FullRec &y) {
+        return x.pos != y.pos ? x.pos < y.pos : x.phase < y.phase;
+    });
+    size_t nmsg = 0;
+    const int rc = resolve(h, h->h_full, c.n_full, h->stream_pos, out, cap, &nmsg);
+    const auto t1 = std::chrono::steady_clock::now();
+    h->stream_pos += n;
+    if (n_out) *n_out = nmsg;
+
+    adsbcu_stats &s = h->stats;
+    s = adsbcu_stats{};
+    s.samples = n; s.preambles = c.preambles; s.phase_records = c.n_phase; s.resolved_records = c.n_full;
+    s.messages = nmsg;
+    if (timed_h2d) cudaEventElapsedTime(&s.ms_h2d, h->ev[0], h->ev[1]);
+    cudaEventElapsedTime(&s.ms_scan, h->ev[1], h->ev[2]);
+    cudaEventElapsedTime(&s.ms_finalize, h->ev[2], h->ev[3]);
+    cudaEventElapsedTime(&s.ms_d2h, h->ev[3], h->ev[4]);
+    s.ms_resolve = std::chrono::duration<float, std::milli>(t1 - t0).count();
+    s.scan_launches = 3;
+    return rc;
+}
+
+}  // namespace
+
+extern "C" {
+
+int adsbcu_abi_version(void) { return ADSBCU_ABI_VERSION; }
+
+const char *adsbcu_last_error(const adsbcu_handle *h) { return h ? h->error.c_str() : g_create_error.c_str(); }
+
+int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
+{
+    if (!out) return ADSBCU_ERR_ARG;
+    *out = nullptr;
+    adsbcu_config c{};
+    c.struct_size = sizeof(c); c.fix_df = 1;
+    if (cfg) {
+        if (cfg->struct_size < sizeof(uint32_t) * 2 || cfg->struct_size > sizeof(c)) { g_create_error = "bad struct_size"; return ADSBCU_ERR_ARG; }
+        std::memcpy(&c, cfg, cfg->struct_size);
+    }
+    if (c.nfix_crc < 0 || c.nfix_crc > 2) { g_create_error = "nfix_crc must be 0..2"; return ADSBCU_ERR_ARG; }
+    if (!c.block_samples) c.block_samples = 131072;
+    if (!c.max_feed_samples) c.max_feed_samples = 1u << 24;
+    if (c.block_samples < 1024) { g_create_error = "block_samples too small"; return ADSBCU_ERR_ARG; }
+
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || c.device < 0 || c.device >= ndev) {
+        cudaGetLastError();
+        g_create_error = "no usable CUDA device (this library has no CPU fallback)";
+        return ADSBCU_ERR_NO_DEVICE;
+    }
+    adsbcu_handle *h = new (std::nothrow) adsbcu_handle;
+    if (!h) return ADSBCU_ERR_NOMEM;
+    h->cfg = c;
+    h->device = c.device;
+    auto fail = [&](int code) { g_create_error = h->error; free_all(h); delete h; return code; };
+#define CKC(call) do { if (!cuda_ok(h, (call), #call)) return fail(ADSBCU_ERR_CUDA); } while (0)
+    CKC(cudaSetDevice(h->device));
+    cudaDeviceProp prop{};
+    CKC(cudaGetDeviceProperties(&prop, h->device));
+    if (prop.major < 10) { h->error = "device is not sm_100 class"; return fail(ADSBCU_ERR_NO_DEVICE); }
+    h->sm_count = prop.multiProcessorCount;
+    CKC(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    for (auto &e : h->ev) CKC(cudaEventCreate(&e));
+
+    DevTables *tab = new (std::nothrow) DevTables;
+    if (!tab) return fail(ADSBCU_ERR_NOMEM);
+    build_tables(*tab, c.nfix_crc, c.fix_df);
+    CKC(cudaMalloc(&h->d_tab, sizeof(DevTables)));
+    cudaError_t e = cudaMemcpy(h->d_tab, tab, sizeof(DevTables), cudaMemcpyHostToDevice);
+    delete tab;
+    CKC(e);
+
+    const size_t nmax = c.max_feed_samples;
+    h->phase_cap = uint32_t(std::max<size_t>(1u << 16, nmax / 16));
+    h->full_cap = uint32_t(std::max<size_t>(1u << 14, nmax / 64));
+    CKC(cudaMalloc(&h->d_bitmap, (size_t(1) << 25) / 8));
+    CKC(cudaMemset(h->d_bitmap, 0, (size_t(1) << 25) / 8));
+    CKC(cudaMalloc(&h->d_carry, kOverlap * sizeof(uint16_t) + 32));
+    CKC(cudaMemset(h->d_carry, 0, kOverlap * sizeof(uint16_t) + 32));
+    CKC(cudaMalloc(&h->d_iq, nmax * 2 + 64));
+    CKC(cudaMalloc(&h->d_phase, size_t(h->phase_cap) * sizeof(PhaseRec)));
+    CKC(cudaMalloc(&h->d_full, size_t(h->full_cap) * sizeof(FullRec)));
+    CKC(cudaMalloc(&h->d_ctr, sizeof(ScanCounters)));
+    CKC(cudaMallocHost(&h->h_ctr, sizeof(ScanCounters)));
+    CKC(cudaMallocHost(&h->h_full, size_t(h->full_cap) * sizeof(FullRec)));
+#undef CKC
+    *out = h;
+    return ADSBCU_OK;
+}
+
+void adsbcu_destroy(adsbcu_handle *h)
+{
+    if (!h) return;
+    free_all(h);
+    delete h;
+}
+
+int adsbcu_1090_reset(adsbcu_handle *h, int clear_filter)
+{
+    if (!h) return ADSBCU_ERR_ARG;
+    CK(cudaSetDevice(h->device));
+    CK(cudaMemsetAsync(h->d_carry, 0, kOverlap * sizeof(uint16_t), h->stream));
+    if (clear_filter) {
+        h->filter.clear();
+        CK(cudaMemsetAsync(h->d_bitmap, 0, (size_t(1) << 25) / 8, h->stream));
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    h->stream_pos = 0;
+    h->has_last = false;
+    h->last_a = h->last_lme = 0;
+    return ADSBCU_OK;
+}
+
+int adsbcu_1090_feed_device(adsbcu_handle *h, const uint8_t *iq_dev, size_t nsamples, adsbcu_msg *out, size_t cap,
+                            size_t *n_out)
+{
+    if (!h) return ADSBCU_ERR_ARG;
+    if (n_out) *n_out = 0;
+    if ((!iq_dev && nsamples) || (!out && cap) || (reinterpret_cast<uintptr_t>(iq_dev) & 15u)) {
+        h->error = "bad argument (null or misaligned pointer)";
+        return ADSBCU_ERR_ARG;
+    }
+    CK(cudaSetDevice(h->device));
+    size_t done = 0, total = 0;
+    int rc = ADSBCU_OK;
+    adsbcu_stats acc{};
+    while (done < nsamples) {
+        // chunk size keeps 16-byte alignment of every chunk start (multiple of 8 samples)
+        const size_t take = std::min<size_t>(nsamples - done, h->cfg.max_feed_samples & ~size_t(7));
+        size_t got = 0;
+        CK(cudaEventRecord(h->ev[0], h->stream));
+        const int r = run_feed(h, iq_dev + 2 * done, uint32_t(take), false, out ? out + std::min(total, cap) : nullptr,
+                               cap > total ? cap - total : 0, &got);
+        if (r != ADSBCU_OK && r != ADSBCU_ERR_OVERFLOW) return r;
+        if (r == ADSBCU_ERR_OVERFLOW) { if (!h->h_ctr->overflow && h->h_ctr->n_phase <= h->phase_cap && h->h_ctr->n_full <= h->full_cap) rc = r; else return r; }
+        total += got; done += take;
+        const adsbcu_stats &s = h->stats;
+        acc.samples += s.samples; acc.preambles += s.preambles; acc.phase_records += s.phase_records;
+        acc.resolved_records += s.resolved_records; acc.messages += s.messages; acc.ms_scan += s.ms_scan;
+        acc.ms_finalize += s.ms_finalize; acc.ms_d2h += s.ms_d2h; acc.ms_resolve += s.ms_resolve;
+        acc.scan_launches += s.scan_launches;
+    }
+    h->stats = acc;
+    if (n_out) *n_out = total;
+    if (rc == ADSBCU_ERR_OVERFLOW) h->error = "out[] too small for the accepted messages";
+    return rc;
+}
+
+int adsbcu_1090_feed(adsbcu_handle *h, const uint8_t *iq, size_t nsamples, adsbcu_msg *out, size_t cap, size_t *n_out)
+{
+    if (!h) return ADSBCU_ERR_ARG;
+    if (n_out) *n_out = 0;
+    if ((!iq && nsamples) || (!out && cap)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
+    CK(cudaSetDevice(h->device));
+    size_t done = 0, total = 0;
+    int rc = ADSBCU_OK;
+    adsbcu_stats acc{};
+    while (done < nsamples) {
+        const size_t take = std::min<size_t>(nsamples - done, h->cfg.max_feed_samples);
+        size_t got = 0;
+        CK(cudaEventRecord(h->ev[0], h->stream));
+        CK(cudaMemcpyAsync(h->d_iq, iq + 2 * done, take * 2, cudaMemcpyHostToDevice, h->stream));
+        const int r = run_feed(h, h->d_iq, uint32_t(take), true, out ? out + std::min(total, cap) : nullptr,
+                               cap > total ? cap - total : 0, &got);
+        if (r != ADSBCU_OK && r != ADSBCU_ERR_OVERFLOW) return r;
+        if (r == ADSBCU_ERR_OVERFLOW) { if (!h->h_ctr->overflow && h->h_ctr->n_phase <= h->phase_cap && h->h_ctr->n_full <= h->full_cap) rc = r; else return r; }
+        total += got; done += take;
+        const adsbcu_stats &s = h->stats;
+        acc.samples += s.samples; acc.preambles += s.preambles; acc.phase_records += s.phase_records;
+        acc.resolved_records += s.resolved_records; acc.messages += s.messages; acc.ms_h2d += s.ms_h2d;
+        acc.ms_scan += s.ms_scan; acc.ms_finalize += s.ms_finalize; acc.ms_d2h += s.ms_d2h; acc.ms_resolve += s.ms_resolve;
+        acc.scan_launches += s.scan_launches;
+    }
+    h->stats = acc;
+    if (n_out) *n_out = total;
+    if (rc == ADSBCU_ERR_OVERFLOW) h->error = "out[] too small for the accepted messages";
+    return rc;
+}
+
+int adsbcu_1090_magnitude(adsbcu_handle *h, const uint8_t *iq, size_t nsamples, uint16_t *mag_out)
+{
+    if (!h || (!iq && nsamples) || (!mag_out && nsamples)) return ADSBCU_ERR_ARG;
+    if (nsamples > h->cfg.max_feed_samples) { h->error = "nsamples exceeds max_feed_samples"; return ADSBCU_ERR_ARG; }
+    if (!nsamples) return ADSBCU_OK;
+    CK(cudaSetDevice(h->device));
+    if (h->d_mag_cap < nsamples) {
+        cudaFree(h->d_mag); h->d_mag = nullptr; h->d_mag_cap = 0;
+        CK(cudaMalloc(&h->d_mag, nsamples * sizeof(uint16_t) + 64));
+        h->d_mag_cap = nsamples;
+    }
+    CK(cudaMemcpyAsync(h->d_iq, iq, nsamples * 2, cudaMemcpyHostToDevice, h->stream));
+    CK(launch_magnitude(h->d_iq, uint32_t(nsamples), h->d_mag, h->d_tab, h->stream));
+    CK(cudaMemcpyAsync(mag_out, h->d_mag, nsamples * sizeof(uint16_t), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return ADSBCU_OK;
+}
+
+int adsbcu_1090_filter_add(adsbcu_handle *h, uint32_t addr)
+{
+    if (!h) return ADSBCU_ERR_ARG;
+    h->filter.add(addr);
+    // keep the device-side superset consistent: queries use the 24-bit address (+ NT table bit)
+    if (!(addr & kNonIcao)) {
+        const uint32_t bi = (addr & 0xFFFFFFu) | ((addr & kNtFlag) ? (1u << 24) : 0u);
+        uint32_t word = 0;
+        CK(cudaSetDevice(h->device));
+        CK(cudaMemcpy(&word, h->d_bitmap + (bi >> 5), 4, cudaMemcpyDeviceToHost));
+        word |= 1u << (bi & 31);
+        CK(cudaMemcpy(h->d_bitmap + (bi >> 5), &word, 4, cudaMemcpyHostToDevice));
+    }
+    return ADSBCU_OK;
+}
+
+int adsbcu_1090_filter_test(adsbcu_handle *h, uint32_t addr)
+{
+    if (!h) return ADSBCU_ERR_ARG;
+    return h->filter.test(addr) ? 1 : 0;
+}
+
+int adsbcu_get_stats(const adsbcu_handle *h, adsbcu_stats *out)
+{
+    if (!h || !out) return ADSBCU_ERR_ARG;
+    *out = h->stats;
+    return ADSBCU_OK;
+}
+
+}  // extern "C"

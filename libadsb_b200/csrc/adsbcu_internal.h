@@ -1,0 +1,128 @@
+// Shared between the host side (adsbcu_api.cpp, adsbcu_tables.cpp) and the
+// kernels (adsbcu_kernels.cu).  Domain vocabulary follows the reference:
+// samples, magnitudes, preambles, phases, syndromes, the ICAO filter.
+#pragma once
+
+#include <cstddef>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace adsbcu {
+
+constexpr int      kOverlap       = 326;      // dump1090.c:159 trailing_samples
+constexpr int      kLookahead     = 290;      // samples read past a start position (demod_2400.c:121, +1 pad)
+constexpr uint32_t kNtFlag        = 1u << 25; // icao_filter.h:24
+constexpr uint32_t kNonIcao       = 1u << 24; // dump1090.h:262
+constexpr uint32_t kUnchecked     = 0xFFFFFFFFu;
+
+// ---- scan kernel tiling --------------------------------------------------------------
+constexpr int kTile        = 8192;            // start positions per tile
+constexpr int kTileLead    = 2;               // smem index of the tile's first start position (16 B alignment of x0)
+constexpr int kTileSamples = kTile + 296;     // magnitudes staged per tile (lead + tile + lookahead, multiple of 8)
+constexpr int kScanThreads = 256;
+
+// State-independent classification of one sliced phase.  The host combines it
+// with the filter state to get the reference's score_rank (mode_s.h:32-80).
+enum Kind : uint32_t {
+    K_AP = 0,          // DF0/4/5/16/20/21: address = syndrome; accepted only if known
+    K_DF11_ACQ_0,      // DF11, IID 0, clean
+    K_DF11_IID_0,      // DF11, IID != 0, clean
+    K_DF11_ACQ_1,      // DF11, IID 0, one bit repaired
+    K_DF11_IID_1,
+    K_DF17_0, K_DF17_1, K_DF17_2,
+    K_DF18_0, K_DF18_1, K_DF18_2,
+    K_COUNT
+};
+
+// rank when the address is unknown / known
+__host__ __device__ inline int rank_of(uint32_t kind, bool known)
+{
+    switch (kind) {
+    case K_AP:         return known ? 12 : 5;
+    case K_DF11_ACQ_0: return known ? 23 : 17;
+    case K_DF11_IID_0: return known ? 20 : 8;
+    case K_DF11_ACQ_1: return known ? 19 : 7;
+    case K_DF11_IID_1: return known ? 18 : 6;
+    case K_DF17_0:     return known ? 27 : 25;
+    case K_DF17_1:     return known ? 22 : 16;
+    case K_DF17_2:     return known ? 14 : 10;
+    case K_DF18_0:     return known ? 26 : 24;
+    case K_DF18_1:     return known ? 21 : 15;
+    case K_DF18_2:     return known ? 13 : 9;
+    default:           return 0;
+    }
+}
+constexpr int kAcceptThreshold = 11;          // SR_ACCEPT_THRESHOLD
+
+// (position, phase) record kept by the scan kernel: 8 bytes.
+//   pos  : start position relative to the feed (padded-stream coordinate minus feed base)
+//   info : bits 0..24 filter key (24-bit address, bit 24 = DF18 "NT" table), 25..27 phase-4,
+//          bit 28 = needs a known address to reach the accept threshold
+struct PhaseRec {
+    uint32_t pos;
+    uint32_t info;
+};
+
+// Fully evaluated record produced by the finalize kernel for the host pass.
+struct alignas(8) FullRec {
+    uint32_t pos;          // as PhaseRec.pos
+    uint8_t  phase;        // try_phase 4..8
+    uint8_t  kind;         // Kind
+    int8_t   corrections;  // 0..2
+    uint8_t  msgtype;      // DF after correction
+    uint8_t  verbatim[14];
+    uint8_t  msg[14];
+    uint32_t crc;          // mm.crc
+    uint32_t addr;         // mm.addr (with non-ICAO flag for DF18)
+    uint32_t test_key;     // key for icaoFilterTest
+    uint32_t add_key;      // key for icaoFilterAdd, kUnchecked if the message is not added
+    uint64_t sum_sq;       // sum of squared magnitudes over the signal window
+};
+static_assert(sizeof(FullRec) == 64, "FullRec layout");
+
+// Syndrome hash tables (open addressing, linear probe, power-of-two slots).
+// entry: bits 0..23 syndrome, 24..25 nerr, 26..32 bit0, 33..39 bit1; all-ones = empty.
+constexpr int      kSyndSlotsLong  = 8192;
+constexpr int      kSyndSlotsShort = 4096;
+constexpr uint64_t kSyndEmpty      = ~0ull;
+__host__ __device__ inline uint32_t synd_hash(uint32_t s, uint32_t slots) { return (s * 2654435761u) >> 8 & (slots - 1); }
+
+struct DevTables {
+    float    sq[256];            // ((i-127.4)/128)^2 as float, scaled by 2^34 (tables.c:24-29)
+    uint32_t bit_synd[112];      // CRC-24 syndrome of each single bit of a 112-bit frame (crc.c:57-62)
+    uint32_t valid_short, valid_long;       // DF pre-filter (demod_2400.c:80-93)
+    uint32_t fixable_short, fixable_long;   // df_correctable_* for the active setting (mode_s.c:260-265)
+    int32_t  nfix;
+    int32_t  pad;
+    uint64_t synd_long[kSyndSlotsLong];
+    uint64_t synd_short[kSyndSlotsShort];
+};
+
+struct ScanCounters {
+    unsigned long long preambles;
+    unsigned int n_phase;        // PhaseRec written (may exceed capacity -> overflow)
+    unsigned int n_full;         // FullRec written
+    unsigned int overflow;
+    unsigned int pad;
+};
+
+struct ScanArgs {
+    const uint8_t  *iq;          // feed samples (device), 16 B aligned
+    const uint16_t *carry_mag;   // kOverlap magnitudes preceding the feed (zeros at stream start)
+    uint32_t        nsamples;    // samples in the feed == start positions in the feed
+    const DevTables *tab;
+    uint32_t       *bitmap;      // 2 x 2^24 bits: [plain | NT] addresses that may enter the filter
+    PhaseRec       *phase;       uint32_t phase_cap;
+    FullRec        *full;        uint32_t full_cap;
+    ScanCounters   *ctr;
+};
+
+void build_tables(DevTables &t, int nfix_crc, int fix_df);
+
+// launchers (adsbcu_kernels.cu)
+cudaError_t launch_scan(const ScanArgs &a, int sm_count, cudaStream_t s);
+cudaError_t launch_finalize(const ScanArgs &a, int sm_count, cudaStream_t s);
+cudaError_t launch_carry(const uint8_t *iq, uint32_t nsamples, uint16_t *carry_mag, const DevTables *tab, cudaStream_t s);
+cudaError_t launch_magnitude(const uint8_t *iq, uint32_t nsamples, uint16_t *mag, const DevTables *tab, cudaStream_t s);
+
+}  // namespace adsbcu

@@ -1,0 +1,310 @@
+// sm_100a kernels of the 1090 MHz path.
+//
+//   scan_kernel      fused: uint8 I/Q -> magnitudes (registers -> shared tile with a
+//                    290-sample lookahead halo) -> preamble detector over every start
+//                    position (warp ballots build rising/falling-edge bit masks, the five
+//                    preamble patterns are evaluated 32 positions at a time) -> five-phase
+//                    bit slicer + CRC-24 syndromes + syndrome-table repair -> compaction
+//                    of (position, phase) records that can still reach the accept
+//                    threshold.  Replaces magnitude_uc8.c:30-63 + demod_2400.c:134-347 +
+//                    mode_s.c:252-466 (state-independent part).
+//   finalize_kernel  drops records whose address can never be in the ICAO filter, re-slices
+//                    the survivors and emits fully evaluated records for the ordered host
+//                    pass (demod_2400.c:349-423 is sequential by definition).
+//   carry_kernel     keeps the last 326 magnitudes for the next feed (fifo.c:187-196).
+//   magnitude_kernel stage-level I/Q -> magnitude (starch_magnitude_uc8).
+#include "adsbcu_device.cuh"
+
+namespace adsbcu {
+
+namespace {
+
+constexpr int kWarps = kScanThreads / 32;
+static_assert(kTile == kWarps * 1024, "each warp owns 1024 start positions of a tile");
+
+__device__ __forceinline__ uint32_t funnel_r(uint32_t lo, uint32_t hi, int sh) { return __funnelshift_r(lo, hi, sh); }
+
+// Reference preamble test at p[0..18] (demod_2400.c:155-218).  `p` points into shared memory.
+__device__ __forceinline__ bool preamble_ok(const uint16_t *p)
+{
+    const int p1 = p[1], p2 = p[2], p3 = p[3], p4 = p[4], p5 = p[5], p6 = p[6], p7 = p[7], p8 = p[8], p9 = p[9],
+              p10 = p[10], p11 = p[11], p12 = p[12];
+    int high;
+    unsigned sig, noise;
+    const bool up12 = p11 < p12;
+    if (p1 > p2 && p2 < p3 && p3 > p4 && p8 < p9 && p9 > p10 && p10 < p11) {
+        high = (p1 + p3 + p9 + p11 + p12) / 4; sig = p1 + p3 + p9; noise = p5 + p6 + p7;
+    } else if (p1 > p2 && p2 < p3 && p3 > p4 && p8 < p9 && p9 > p10 && up12) {
+        high = (p1 + p3 + p9 + p12) / 4; sig = p1 + p3 + p9 + p12; noise = p5 + p6 + p7 + p8;
+    } else if (p1 > p2 && p2 < p3 && p4 > p5 && p8 < p9 && p10 > p11 && up12) {
+        high = (p1 + p3 + p4 + p9 + p10 + p12) / 4; sig = p1 + p12; noise = p6 + p7;
+    } else if (p1 > p2 && p3 < p4 && p4 > p5 && p9 < p10 && p10 > p11 && up12) {
+        high = (p1 + p4 + p10 + p12) / 4; sig = p1 + p4 + p10 + p12; noise = p5 + p6 + p7 + p8;
+    } else if (p2 > p3 && p3 < p4 && p4 > p5 && p9 < p10 && p10 > p11 && up12) {
+        high = (p1 + p2 + p4 + p10 + p12) / 4; sig = p4 + p10 + p12; noise = p6 + p7 + p8;
+    } else {
+        return false;
+    }
+    if (sig * 2 < 3 * noise) return false;
+    if (p5 >= high || p6 >= high || p7 >= high || p8 >= high) return false;
+    if (p[14] >= high || p[15] >= high || p[16] >= high || p[17] >= high || p[18] >= high) return false;
+    return true;
+}
+
+__global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanArgs a)
+{
+    __shared__ __align__(16) uint16_t s_mag[kTileSamples];
+    __shared__ float s_sq[256];
+    __shared__ uint32_t s_bitsynd[112];
+    __shared__ uint16_t s_cand[kTile];
+    __shared__ uint32_t s_ncand;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < 256; i += kScanThreads) s_sq[i] = a.tab->sq[i];
+    for (int i = tid; i < 112; i += kScanThreads) s_bitsynd[i] = a.tab->bit_synd[i];
+
+    const int64_t n = a.nsamples;
+    const uint32_t ntiles = uint32_t((n + kTile - 1) / kTile);
+    unsigned long long my_preambles = 0;
+
+    for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        __syncthreads();   // previous tile fully consumed (also covers the table loads above)
+        const int64_t tile_base = int64_t(tile) * kTile;
+        // shared index i <-> feed sample x = x0 + i ; start position s (tile-local) sits at i = s + kTileLead
+        const int64_t x0 = tile_base - kOverlap - kTileLead;
+
+        // ---- phase A: magnitudes --------------------------------------------------------
+        for (int v = tid; v < kTileSamples / 8; v += kScanThreads) {
+            const int64_t x = x0 + 8 * v;
+            uint32_t m[8];
+            if (x >= 0 && x + 8 <= n) {
+                const uint4 d = __ldg(reinterpret_cast<const uint4 *>(a.iq + 2 * x));
+                const uint32_t w[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    m[2 * e] = mag_iq(s_sq, w[e] & 0xFF, (w[e] >> 8) & 0xFF);
+                    m[2 * e + 1] = mag_iq(s_sq, (w[e] >> 16) & 0xFF, w[e] >> 24);
+                }
+            } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    const int64_t xe = x + e;
+                    if (xe < 0) m[e] = (xe + kOverlap >= 0) ? a.carry_mag[xe + kOverlap] : 0u;
+                    else if (xe < n) m[e] = mag_iq(s_sq, a.iq[2 * xe], a.iq[2 * xe + 1]);
+                    else m[e] = 0u;
+                }
+            }
+            uint4 o;
+            o.x = m[0] | (m[1] << 16); o.y = m[2] | (m[3] << 16); o.z = m[4] | (m[5] << 16); o.w = m[6] | (m[7] << 16);
+            *reinterpret_cast<uint4 *>(&s_mag[8 * v]) = o;
+        }
+        if (tid == 0) s_ncand = 0;
+        __syncthreads();
+
+        // ---- phase B: preamble detector ---------------------------------------------------
+        // L bit k: m[k] < m[k+1]; G bit k: m[k] > m[k+1].  Iteration `it` ballots 32 consecutive
+        // positions; lane `it` keeps that word, lane `it-1` keeps it as its lookahead word.
+        {
+            const int wbase = warp * 1024;
+            uint32_t myL = 0, myG = 0, nxL = 0, nxG = 0;
+            for (int it = 0; it <= 32; ++it) {
+                const int idx = wbase + it * 32 + lane + kTileLead;
+                const uint32_t m0 = s_mag[idx], m1 = s_mag[idx + 1];
+                const uint32_t L = __ballot_sync(0xFFFFFFFFu, m0 < m1);
+                const uint32_t G = __ballot_sync(0xFFFFFFFFu, m0 > m1);
+                if (it == lane) { myL = L; myG = G; }
+                if (it == lane + 1) { nxL = L; nxG = G; }
+            }
+            // positions lane*32 + b, b = 0..31; shifted views of the 64-bit windows
+            const uint32_t L0 = myL, L2 = funnel_r(myL, nxL, 2), L3 = funnel_r(myL, nxL, 3), L8 = funnel_r(myL, nxL, 8),
+                           L9 = funnel_r(myL, nxL, 9), L10 = funnel_r(myL, nxL, 10), L11 = funnel_r(myL, nxL, 11);
+            const uint32_t G1 = funnel_r(myG, nxG, 1), G2 = funnel_r(myG, nxG, 2), G3 = funnel_r(myG, nxG, 3),
+                           G4 = funnel_r(myG, nxG, 4), G9 = funnel_r(myG, nxG, 9), G10 = funnel_r(myG, nxG, 10),
+                           G12 = funnel_r(myG, nxG, 12);
+            const uint32_t early = G1 & L2, late = G10 & L11 & L9 & G4;
+            const uint32_t pat = (early & G3 & L8 & G9 & (L10 | L11))          // phase 3, 4
+                               | (early & G4 & L8 & G10 & L11)                 // phase 5
+                               | (late & L3 & (G1 | G2));                      // phase 6, 7
+            uint32_t cand = pat & L0 & G12;
+            const int64_t first = tile_base + wbase + lane * 32;               // feed position of bit 0
+            if (first + 32 > n) cand = first >= n ? 0u : cand & (0xFFFFFFFFu >> (32 - int(n - first)));
+            while (cand) {
+                const int b = __ffs(cand) - 1;
+                cand &= cand - 1;
+                const int pos = wbase + lane * 32 + b;
+                if (preamble_ok(&s_mag[pos + kTileLead])) {
+                    const uint32_t slot = atomicAdd(&s_ncand, 1u);
+                    s_cand[slot] = uint16_t(pos);
+                    ++my_preambles;
+                }
+            }
+        }
+        __syncthreads();
+
+        // ---- phase C: five-phase slicer + CRC + classification ---------------------------
+        const uint32_t nitems = s_ncand * 5u;
+        for (uint32_t it = tid; it < nitems; it += kScanThreads) {
+            const uint32_t pos = s_cand[it / 5u];
+            const int ph = 4 + int(it % 5u);
+            const uint16_t *d = &s_mag[pos + kTileLead + 19];
+            auto mag = [d](int i) { return int(d[i]); };
+            Frame f{0, 0};
+            uint32_t xs = 0, xl = 0;
+            slice_bits(mag, ph, 0, 8, s_bitsynd, f, xs, xl);
+            const uint32_t dfbit = 1u << frame_df(f);
+            const int nbits = (a.tab->valid_long & dfbit) ? 112 : (a.tab->valid_short & dfbit) ? 56 : 0;
+            if (!nbits) continue;
+            slice_bits(mag, ph, 8, nbits, s_bitsynd, f, xs, xl);
+            const Classified c = classify(f, xs, xl, a.tab);
+            if (!c.keep) continue;
+            const uint32_t bi = bitmap_index(c.test_key);
+            if (c.kind == K_DF17_0 || c.kind == K_DF11_ACQ_0 || (c.kind == K_DF18_0 && !df18_non_icao(c.fixed)))
+                atomicOr(&a.bitmap[bi >> 5], 1u << (bi & 31));
+            const uint32_t slot = atomicAdd(&a.ctr->n_phase, 1u);
+            if (slot < a.phase_cap) {
+                PhaseRec r;
+                r.pos = uint32_t(tile_base) + pos;
+                r.info = bi | (uint32_t(ph - 4) << 25) | (c.needs_known ? (1u << 28) : 0u);
+                a.phase[slot] = r;
+            } else {
+                a.ctr->overflow = 1u;
+            }
+        }
+    }
+    if (my_preambles) atomicAdd(&a.ctr->preambles, my_preambles);
+}
+
+// One thread per (position, phase) record.
+__global__ void __launch_bounds__(128) finalize_kernel(ScanArgs a)
+{
+    const uint32_t nrec = min(a.ctr->n_phase, a.phase_cap);
+    const int64_t n = a.nsamples;
+    const float *sq = a.tab->sq;
+    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < nrec; r += gridDim.x * blockDim.x) {
+        const PhaseRec pr = a.phase[r];
+        const uint32_t bi = pr.info & 0x1FFFFFFu;
+        if ((pr.info >> 28) & 1u) {
+            if (!((a.bitmap[bi >> 5] >> (bi & 31)) & 1u)) continue;   // address can never be known
+        }
+        const int ph = 4 + int((pr.info >> 25) & 7u);
+        const int64_t xb = int64_t(pr.pos) - kOverlap + 19;           // feed sample of m[j+19]
+        const uint8_t *iq = a.iq;
+        const uint16_t *carry = a.carry_mag;
+        auto mag = [=](int i) -> int {
+            const int64_t x = xb + i;
+            if (x < 0) return (x + kOverlap >= 0) ? int(carry[x + kOverlap]) : 0;
+            if (x >= n) return 0;
+            return int(mag_iq(sq, iq[2 * x], iq[2 * x + 1]));
+        };
+        Frame f{0, 0};
+        uint32_t xs = 0, xl = 0;
+        slice_bits(mag, ph, 0, 8, a.tab->bit_synd, f, xs, xl);
+        const uint32_t dfbit = 1u << frame_df(f);
+        const int nbits = (a.tab->valid_long & dfbit) ? 112 : (a.tab->valid_short & dfbit) ? 56 : 0;
+        if (!nbits) continue;
+        slice_bits(mag, ph, 8, nbits, a.tab->bit_synd, f, xs, xl);
+        const Classified c = classify(f, xs, xl, a.tab);
+        if (!c.keep) continue;
+
+        FullRec o;
+        o.pos = pr.pos;
+        o.phase = uint8_t(ph);
+        o.kind = uint8_t(c.kind);
+        o.corrections = int8_t(c.corrections < 0 ? 0 : c.corrections);
+        o.msgtype = uint8_t(frame_df(c.fixed));
+#pragma unroll
+        for (int b = 0; b < 14; ++b) {
+            o.verbatim[b] = uint8_t(frame_byte(f, b));
+            o.msg[b] = uint8_t(frame_byte(c.fixed, b));
+        }
+        o.crc = c.crc;
+        o.test_key = c.test_key;
+        o.add_key = kUnchecked;
+        const uint32_t aa = frame_aa(c.fixed);
+        switch (o.msgtype) {
+        case 11: o.addr = aa; if (c.kind == K_DF11_ACQ_0) o.add_key = aa; break;
+        case 17: o.addr = aa; if (c.kind == K_DF17_0) o.add_key = aa; break;
+        case 18:
+            o.addr = aa | (df18_non_icao(c.fixed) ? kNonIcao : 0u);
+            if (c.kind == K_DF18_0) o.add_key = o.addr | kNtFlag;
+            break;
+        default: o.addr = c.crc; break;
+        }
+        // signal power window (demod_2400.c:382-389): length from the *uncorrected* DF
+        const int siglen = (frame_df(f) & 16u) ? 268 : 134;
+        uint64_t acc = 0;
+        for (int k = 0; k < siglen; ++k) {
+            const uint32_t v = uint32_t(mag(k));
+            acc += uint64_t(v * v);
+        }
+        o.sum_sq = acc;
+        const uint32_t slot = atomicAdd(&a.ctr->n_full, 1u);
+        if (slot < a.full_cap) a.full[slot] = o; else a.ctr->overflow = 1u;
+    }
+}
+
+__global__ void carry_kernel(const uint8_t *iq, uint32_t nsamples, uint16_t *carry_mag, const DevTables *tab)
+{
+    // new_carry[i] = magnitude of stream sample (end - 326 + i); samples before this feed come from the old carry
+    const int i = threadIdx.x;
+    uint32_t v = 0;
+    if (i < kOverlap) {
+        const int64_t x = int64_t(nsamples) - kOverlap + i;
+        if (x >= 0) v = mag_iq(tab->sq, iq[2 * x], iq[2 * x + 1]);
+        else v = carry_mag[x + kOverlap];
+    }
+    __syncthreads();
+    if (i < kOverlap) carry_mag[i] = uint16_t(v);
+}
+
+__global__ void __launch_bounds__(256) magnitude_kernel(const uint8_t *iq, uint32_t nsamples, uint16_t *mag, const DevTables *tab)
+{
+    __shared__ float s_sq[256];
+    s_sq[threadIdx.x] = tab->sq[threadIdx.x];
+    __syncthreads();
+    const uint32_t nvec = nsamples / 8;
+    for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += gridDim.x * blockDim.x) {
+        const uint4 d = __ldg(reinterpret_cast<const uint4 *>(iq) + v);
+        const uint32_t w[4] = {d.x, d.y, d.z, d.w};
+        uint32_t o[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+            o[e] = mag_iq(s_sq, w[e] & 0xFF, (w[e] >> 8) & 0xFF) | (mag_iq(s_sq, (w[e] >> 16) & 0xFF, w[e] >> 24) << 16);
+        reinterpret_cast<uint4 *>(mag)[v] = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+    if (blockIdx.x == 0)
+        for (uint32_t k = nvec * 8 + threadIdx.x; k < nsamples; k += blockDim.x)
+            mag[k] = uint16_t(mag_iq(s_sq, iq[2 * k], iq[2 * k + 1]));
+}
+
+}  // namespace
+
+cudaError_t launch_scan(const ScanArgs &a, int sm_count, cudaStream_t s)
+{
+    const uint32_t ntiles = (a.nsamples + kTile - 1) / kTile;
+    if (!ntiles) return cudaSuccess;
+    const uint32_t grid = ntiles < uint32_t(sm_count) * 4u ? ntiles : uint32_t(sm_count) * 4u;
+    scan_kernel<<<grid, kScanThreads, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_finalize(const ScanArgs &a, int sm_count, cudaStream_t s)
+{
+    finalize_kernel<<<sm_count * 8, 128, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_carry(const uint8_t *iq, uint32_t nsamples, uint16_t *carry_mag, const DevTables *tab, cudaStream_t s)
+{
+    carry_kernel<<<1, 352, 0, s>>>(iq, nsamples, carry_mag, tab);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_magnitude(const uint8_t *iq, uint32_t nsamples, uint16_t *mag, const DevTables *tab, cudaStream_t s)
+{
+    if (!nsamples) return cudaSuccess;
+    magnitude_kernel<<<148 * 8, 256, 0, s>>>(iq, nsamples, mag, tab);
+    return cudaGetLastError();
+}
+
+}  // namespace adsbcu
