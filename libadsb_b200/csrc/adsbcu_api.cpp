@@ -303,7 +303,7 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
 
     const size_t nmax = c.max_feed_samples;
     h->phase_cap = uint32_t(std::max<size_t>(1u << 16, nmax / 16));
-    h->full_cap = uint32_t(std::max<size_t>(1u << 14, nmax / 64));
+    h->full_cap = uint32_t(std::max<size_t>(1u << 14, nmax / 128));
     CKC(cudaMalloc(&h->d_bitmap, (size_t(1) << 25) / 8));
     CKC(cudaMemset(h->d_bitmap, 0, (size_t(1) << 25) / 8));
     CKC(cudaMalloc(&h->d_carry, kOverlap * sizeof(uint16_t) + 32));
