@@ -69,6 +69,116 @@ __device__ __forceinline__ void slice_bits(MagFn mag, int ph, int first, int las
     }
 }
 
+// ---- fast slicer: uniform code for every phase ---------------------------------------------
+// Symbol k of try_phase p starts u = p + 12k fifths-of-a-sample after m[j+19].  Re-index with a
+// "virtual" symbol v = k + v0 where v0 = 3p mod 5: then u = 5c + 12v with c = (p - 12 v0)/5, so the
+// correlator sub-phase is 2v mod 5 for EVERY phase and the pattern repeats every 5 symbols / 12
+// samples:  v mod 5 = 0..4 -> sample offset 0,2,4,7,9 with sub-phase 0,2,4,1,3.  One "period" is
+// therefore 12 consecutive samples -> 5 symbols with fixed weights (demod_2400.c:45-59):
+//     r0 = 5m0-3m1-2m2   r1 = 3m2+m3-4m4   r2 = m4+5m5-5m6-m7   r3 = 4m7-m8-3m9   r4 = 2m9+3m10-5m11
+// A lane only differs in where its sample 0 is (c) and in how many leading virtual symbols are
+// garbage (v0).  Samples are consumed as packed uint16 pairs straight from the shared-memory tile
+// with IDP.2A (u16 x s8 dot products); the two possible alignments of sample 0 inside a 32-bit
+// word are folded into per-lane weight registers, so there is no divergence on parity either.
+__device__ __forceinline__ int dp2a_lo(uint32_t a, uint32_t b, int c)
+{
+    int d;
+    asm("dp2a.lo.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int dp2a_hi(uint32_t a, uint32_t b, int c)
+{
+    int d;
+    asm("dp2a.hi.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+// weights are stored NEGATED so that (corr > 0) is the sign bit of the accumulated value
+__host__ __device__ constexpr uint32_t wpair(int lo, int hi) { return uint32_t(uint8_t(-lo)) | (uint32_t(uint8_t(-hi)) << 8); }
+__host__ __device__ constexpr uint32_t wreg(uint32_t pa, uint32_t pb) { return pa | (pb << 16); }
+// 13 (word, weight-pair) terms per period; register k holds terms 2k (dp2a.lo) and 2k+1 (dp2a.hi)
+//   term: 0:r0/W0 1:r0/W1 2:r1/W1 3:r1/W2 4:r2/W2 5:r2/W3 6:r2/W4 7:r3/W3 8:r3/W4 9:r3/W5 10:r4/W4 11:r4/W5 12:r4/W6
+__device__ __forceinline__ void slicer_weights(bool odd, uint32_t (&w)[7])
+{
+    // sample 0 in the low half of word 0 (even) or in the high half (odd)
+    constexpr uint32_t E[7] = {wreg(wpair(5, -3), wpair(-2, 0)), wreg(wpair(3, 1), wpair(-4, 0)), wreg(wpair(1, 5), wpair(-5, -1)),
+                               wreg(wpair(0, 0), wpair(0, 4)), wreg(wpair(-1, -3), wpair(0, 0)), wreg(wpair(0, 2), wpair(3, -5)),
+                               wreg(wpair(0, 0), 0)};
+    constexpr uint32_t O[7] = {wreg(wpair(0, 5), wpair(-3, -2)), wreg(wpair(0, 3), wpair(1, -4)), wreg(wpair(0, 1), wpair(5, -5)),
+                               wreg(wpair(-1, 0), wpair(0, 0)), wreg(wpair(4, -1), wpair(-3, 0)), wreg(wpair(0, 0), wpair(2, 3)),
+                               wreg(wpair(-5, 0), 0)};
+#pragma unroll
+    for (int k = 0; k < 7; ++k) w[k] = odd ? O[k] : E[k];
+}
+
+// Slice NPER periods (5*NPER virtual symbols) starting at 32-bit word pointer wp (shared memory).
+// acc[i] receives virtual symbols 32i..32i+31, first symbol in the MSB once the word is full.
+template <int NPER>
+__device__ __forceinline__ void slice_periods(const uint32_t *wp, const uint32_t (&w)[7], uint32_t (&acc)[4])
+{
+    uint32_t W0 = wp[0];
+#pragma unroll
+    for (int q = 0; q < NPER; ++q) {
+        const uint32_t W1 = wp[6 * q + 1], W2 = wp[6 * q + 2], W3 = wp[6 * q + 3], W4 = wp[6 * q + 4],
+                       W5 = wp[6 * q + 5], W6 = wp[6 * q + 6];
+        int c[5];
+        c[0] = dp2a_hi(W1, w[0], dp2a_lo(W0, w[0], 0));
+        c[1] = dp2a_hi(W2, w[1], dp2a_lo(W1, w[1], 0));
+        c[2] = dp2a_lo(W4, w[3], dp2a_hi(W3, w[2], dp2a_lo(W2, w[2], 0)));
+        c[3] = dp2a_hi(W5, w[4], dp2a_lo(W4, w[4], dp2a_hi(W3, w[3], 0)));
+        c[4] = dp2a_lo(W6, w[6], dp2a_hi(W5, w[5], dp2a_lo(W4, w[5], 0)));
+#pragma unroll
+        for (int r = 0; r < 5; ++r) {
+            const int v = 5 * q + r;
+            acc[v >> 5] = __funnelshift_l(uint32_t(c[r]), acc[v >> 5], 1);   // (acc << 1) | (corr > 0)
+        }
+        W0 = W6;
+    }
+}
+
+// per-phase constants of the re-indexing above
+__device__ __forceinline__ int phase_v0(int ph) { return (3 * ph) % 5; }
+__device__ __forceinline__ int phase_c(int ph) { return (ph - 12 * phase_v0(ph)) / 5; }
+
+// Align the virtual-symbol accumulators to message bits: returns M[0..3], bit 0 of the message in the
+// MSB of M[0].  NBITS = number of virtual symbols accumulated (5*NPER).
+template <int NBITS>
+__device__ __forceinline__ void align_message(const uint32_t (&acc)[4], int v0, uint32_t (&M)[4])
+{
+    uint32_t a[5] = {acc[0], acc[1], acc[2], acc[3], 0u};
+    constexpr int last = (NBITS - 1) >> 5, rem = NBITS & 31;
+    if (rem) a[last] <<= (32 - rem);                    // left-align the partially filled word
+#pragma unroll
+    for (int i = last + 1; i < 5; ++i) a[i] = 0u;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) M[i] = __funnelshift_l(a[i + 1], a[i], v0);
+}
+
+// CRC-24 syndromes of the sliced bytes via per-byte contribution tables (linear code):
+// long: bytes 0..10 through tables 0..10, xor bytes 11..13; short: bytes 0..3 through tables 7..10, xor bytes 4..6
+__device__ __forceinline__ uint32_t msg_byte(const uint32_t (&M)[4], int b) { return (M[b >> 2] >> (24 - 8 * (b & 3))) & 0xFFu; }
+__device__ __forceinline__ uint32_t crc_long(const uint32_t (&M)[4], const uint32_t *crc_byte)
+{
+    uint32_t x = (M[2] & 0xFFu) << 16 | (M[3] >> 16);
+#pragma unroll
+    for (int b = 0; b < 11; ++b) x ^= crc_byte[b * 256 + msg_byte(M, b)];
+    return x;
+}
+__device__ __forceinline__ uint32_t crc_short(const uint32_t (&M)[4], const uint32_t *crc_byte)
+{
+    uint32_t x = M[1] >> 8;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) x ^= crc_byte[(7 + b) * 256 + msg_byte(M, b)];
+    return x;
+}
+__device__ __forceinline__ Frame frame_from_words(const uint32_t (&M)[4], bool is_long)
+{
+    Frame f;
+    f.h0 = (uint64_t(M[0]) << 24) | (M[1] >> 8);
+    f.h1 = is_long ? (uint64_t(M[1] & 0xFFu) << 48) | (uint64_t(M[2]) << 16) | (M[3] >> 16) : 0ull;
+    return f;
+}
+
 // ---- syndrome lookup (crc.c:386-405 as a hash probe) -----------------------------------
 struct Diag {
     int nerr;       // -1: not correctable

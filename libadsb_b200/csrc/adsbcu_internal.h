@@ -19,6 +19,7 @@ constexpr uint32_t kUnchecked     = 0xFFFFFFFFu;
 constexpr int kTile        = 8192;            // start positions per tile
 constexpr int kTileLead    = 2;               // smem index of the tile's first start position (16 B alignment of x0)
 constexpr int kTileSamples = kTile + 296;     // magnitudes staged per tile (lead + tile + lookahead, multiple of 8)
+constexpr int kTilePad     = 32;              // slack read (never used) by the unrolled slicer's last period
 constexpr int kScanThreads = 256;
 
 // State-independent classification of one sliced phase.  The host combines it
@@ -96,6 +97,7 @@ struct DevTables {
     int32_t  pad;
     uint64_t synd_long[kSyndSlotsLong];
     uint64_t synd_short[kSyndSlotsShort];
+    uint32_t crc_byte[11][256];  // syndrome contribution of byte b (0..10) of a 112-bit frame having value v
 };
 
 struct ScanCounters {

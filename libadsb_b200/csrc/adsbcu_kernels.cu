@@ -20,6 +20,9 @@ namespace adsbcu {
 namespace {
 
 constexpr int kWarps = kScanThreads / 32;
+constexpr int kCandCap = 4096;                 // preambles kept per tile (overflow -> error, never silently dropped)
+constexpr int kCandChunk = 256;                // preambles per slicer round
+constexpr int kQueueCap = 5 * kCandChunk;      // (preamble, phase) items per round
 static_assert(kTile == kWarps * 1024, "each warp owns 1024 start positions of a tile");
 
 __device__ __forceinline__ uint32_t funnel_r(uint32_t lo, uint32_t hi, int sh) { return __funnelshift_r(lo, hi, sh); }
@@ -53,15 +56,18 @@ __device__ __forceinline__ bool preamble_ok(const uint16_t *p)
 
 __global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanArgs a)
 {
-    __shared__ __align__(16) uint16_t s_mag[kTileSamples];
+    __shared__ __align__(16) uint16_t s_mag[kTileSamples + kTilePad];
     __shared__ float s_sq[256];
-    __shared__ uint32_t s_bitsynd[112];
-    __shared__ uint16_t s_cand[kTile];
-    __shared__ uint32_t s_ncand;
+    __shared__ uint32_t s_crcb[11 * 256];
+    __shared__ uint16_t s_cand[kCandCap];
+    __shared__ uint32_t s_queue[2][kQueueCap];     // [0] 112-bit items, [1] 56-bit items: pos | (phase-4) << 16
+    __shared__ uint32_t s_ncand, s_nq[2];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int i = tid; i < 256; i += kScanThreads) s_sq[i] = a.tab->sq[i];
-    for (int i = tid; i < 112; i += kScanThreads) s_bitsynd[i] = a.tab->bit_synd[i];
+    for (int i = tid; i < 11 * 256; i += kScanThreads) s_crcb[i] = (&a.tab->crc_byte[0][0])[i];
+    const uint32_t valid_long = a.tab->valid_long, valid_short = a.tab->valid_short, fixable_short = a.tab->fixable_short;
+    const uint32_t *s_magw = reinterpret_cast<const uint32_t *>(s_mag);
 
     const int64_t n = a.nsamples;
     const uint32_t ntiles = uint32_t((n + kTile - 1) / kTile);
@@ -134,7 +140,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanArgs a)
                 const int pos = wbase + lane * 32 + b;
                 if (preamble_ok(&s_mag[pos + kTileLead])) {
                     const uint32_t slot = atomicAdd(&s_ncand, 1u);
-                    s_cand[slot] = uint16_t(pos);
+                    if (slot < kCandCap) s_cand[slot] = uint16_t(pos); else a.ctr->overflow = 1u;
                     ++my_preambles;
                 }
             }
@@ -142,32 +148,66 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanArgs a)
         __syncthreads();
 
         // ---- phase C: five-phase slicer + CRC + classification ---------------------------
-        const uint32_t nitems = s_ncand * 5u;
-        for (uint32_t it = tid; it < nitems; it += kScanThreads) {
-            const uint32_t pos = s_cand[it / 5u];
-            const int ph = 4 + int(it % 5u);
-            const uint16_t *d = &s_mag[pos + kTileLead + 19];
-            auto mag = [d](int i) { return int(d[i]); };
-            Frame f{0, 0};
-            uint32_t xs = 0, xl = 0;
-            slice_bits(mag, ph, 0, 8, s_bitsynd, f, xs, xl);
-            const uint32_t dfbit = 1u << frame_df(f);
-            const int nbits = (a.tab->valid_long & dfbit) ? 112 : (a.tab->valid_short & dfbit) ? 56 : 0;
-            if (!nbits) continue;
-            slice_bits(mag, ph, 8, nbits, s_bitsynd, f, xs, xl);
-            const Classified c = classify(f, xs, xl, a.tab);
-            if (!c.keep) continue;
-            const uint32_t bi = bitmap_index(c.test_key);
-            if (c.kind == K_DF17_0 || c.kind == K_DF11_ACQ_0 || (c.kind == K_DF18_0 && !df18_non_icao(c.fixed)))
-                atomicOr(&a.bitmap[bi >> 5], 1u << (bi & 31));
-            const uint32_t slot = atomicAdd(&a.ctr->n_phase, 1u);
-            if (slot < a.phase_cap) {
-                PhaseRec r;
-                r.pos = uint32_t(tile_base) + pos;
-                r.info = bi | (uint32_t(ph - 4) << 25) | (c.needs_known ? (1u << 28) : 0u);
-                a.phase[slot] = r;
-            } else {
-                a.ctr->overflow = 1u;
+        // C1 slices two periods of every (preamble, phase) to read the DF field and queues the items the
+        // DF pre-filter keeps (demod_2400.c:317-331); C2 slices the queued items completely, one item per
+        // lane, all lanes running the same unrolled code (see slice_periods).
+        const uint32_t ncand = min(s_ncand, uint32_t(kCandCap));
+        for (uint32_t c0 = 0; c0 < ncand; c0 += kCandChunk) {
+            if (tid < 2) s_nq[tid] = 0;
+            __syncthreads();
+            const uint32_t nitems = min(uint32_t(kCandChunk), ncand - c0) * 5u;
+            for (uint32_t it = tid; it < nitems; it += kScanThreads) {
+                const uint32_t pos = s_cand[c0 + it / 5u];
+                const int ph = 4 + int(it % 5u);
+                const int b = int(pos) + kTileLead + 19 + phase_c(ph);
+                uint32_t w[7], acc[4] = {0u, 0u, 0u, 0u}, M[4];
+                slicer_weights(b & 1, w);
+                slice_periods<2>(s_magw + (b >> 1), w, acc);
+                align_message<10>(acc, phase_v0(ph), M);
+                const uint32_t dfbit = 1u << (M[0] >> 27);
+                const uint32_t item = pos | (uint32_t(ph - 4) << 16);
+                if (valid_long & dfbit) s_queue[0][atomicAdd(&s_nq[0], 1u)] = item;
+                else if (valid_short & dfbit) s_queue[1][atomicAdd(&s_nq[1], 1u)] = item;
+            }
+            __syncthreads();
+            const uint32_t nlong = s_nq[0], nshort = s_nq[1];
+            for (uint32_t it = tid; it < nlong + nshort; it += kScanThreads) {
+                const bool is_long = it < nlong;
+                const uint32_t item = is_long ? s_queue[0][it] : s_queue[1][it - nlong];
+                const uint32_t pos = item & 0xFFFFu;
+                const int ph = 4 + int(item >> 16);
+                const int b = int(pos) + kTileLead + 19 + phase_c(ph);
+                uint32_t w[7], acc[4] = {0u, 0u, 0u, 0u}, M[4];
+                slicer_weights(b & 1, w);
+                uint32_t xs = 0, xl = 0;
+                if (is_long) {
+                    slice_periods<24>(s_magw + (b >> 1), w, acc);
+                    align_message<120>(acc, phase_v0(ph), M);
+                    M[3] &= 0xFFFF0000u;
+                    xl = crc_long(M, s_crcb);
+                    // the 56-bit syndrome is also needed when a short DF was sliced long (DF0/DF5 are within two
+                    // bit flips of DF17/18, so --fix-2bit slices them to 14 bytes but scores them as 56-bit A/P)
+                    if (!(M[0] >> 31) || (fixable_short & (1u << (M[0] >> 27)))) xs = crc_short(M, s_crcb);
+                } else {
+                    slice_periods<12>(s_magw + (b >> 1), w, acc);
+                    align_message<60>(acc, phase_v0(ph), M);
+                    M[1] &= 0xFFFFFF00u; M[2] = 0u; M[3] = 0u;
+                    xs = crc_short(M, s_crcb);
+                }
+                const Classified c = classify(frame_from_words(M, is_long), xs, xl, a.tab);
+                if (!c.keep) continue;
+                const uint32_t bi = bitmap_index(c.test_key);
+                if (c.kind == K_DF17_0 || c.kind == K_DF11_ACQ_0 || (c.kind == K_DF18_0 && !df18_non_icao(c.fixed)))
+                    atomicOr(&a.bitmap[bi >> 5], 1u << (bi & 31));
+                const uint32_t slot = atomicAdd(&a.ctr->n_phase, 1u);
+                if (slot < a.phase_cap) {
+                    PhaseRec r;
+                    r.pos = uint32_t(tile_base) + pos;
+                    r.info = bi | (uint32_t(ph - 4) << 25) | (c.needs_known ? (1u << 28) : 0u);
+                    a.phase[slot] = r;
+                } else {
+                    a.ctr->overflow = 1u;
+                }
             }
         }
     }

@@ -108,6 +108,13 @@ void build_tables(DevTables &t, int nfix_crc, int fix_df)
         z[k >> 3] = uint8_t(0x80 >> (k & 7));
         t.bit_synd[k] = crc_bitwise(z, 14);
     }
+    for (int b = 0; b < 11; ++b)
+        for (int v = 0; v < 256; ++v) {
+            uint32_t x = 0;
+            for (int k = 0; k < 8; ++k)
+                if (v & (0x80 >> k)) x ^= t.bit_synd[8 * b + k];
+            t.crc_byte[b][v] = x;
+        }
     static const uint32_t fix_short[3] = {0x00000800u, 0x08008e08u, 0x08008e08u};
     static const uint32_t fix_long[3] = {0x00060000u, 0x066f0006u, 0x6fff066fu};
     const int nfix = nfix_crc < 0 ? 0 : nfix_crc > 2 ? 2 : nfix_crc;
