@@ -73,23 +73,34 @@ struct IcaoFilter {
 
 }  // namespace
 
+constexpr int kSlots = 3;            // chunks in flight: GPU works on chunk c+1, c+2 while the host pass replays chunk c
+
+// Everything one in-flight chunk owns.
+struct Slot {
+    PhaseRec *d_seg = nullptr;        // nseg segments of seg_cap records
+    uint32_t *d_seg_count = nullptr;
+    ChunkCounters *d_ctr = nullptr;
+    ChunkCounters *h_ctr = nullptr;   // pinned
+    FullRec *h_full = nullptr;        // pinned + mapped: the evaluate kernel writes it directly
+    FullRec *d_full = nullptr;        // device alias of h_full
+    cudaEvent_t ev[4]{};              // scan begin, scan end, evaluate end, done (counters on the host)
+};
+
 struct adsbcu_handle {
     adsbcu_config cfg{};
     int device = 0, sm_count = 148;
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev[6]{};
+    cudaStream_t stream = nullptr;    // kernels + counter downloads
+    cudaStream_t copy_stream = nullptr;   // host->device uploads of the feed, chunk by chunk
+    cudaEvent_t ev_h2d[2]{};
+    cudaEvent_t ev_up[kSlots]{};      // upload of the chunk using that slot has finished
     std::string error;
 
     DevTables *d_tab = nullptr;
     uint32_t *d_bitmap = nullptr;
     uint16_t *d_carry = nullptr;
     uint8_t *d_iq = nullptr;          // staging for host feeds
-    PhaseRec *d_phase = nullptr;
-    FullRec *d_full = nullptr;
-    ScanCounters *d_ctr = nullptr;
-    uint32_t phase_cap = 0, full_cap = 0;
-    ScanCounters *h_ctr = nullptr;    // pinned
-    FullRec *h_full = nullptr;        // pinned
+    uint32_t nseg = 0, seg_cap = 0, full_cap = 0, chunk_positions = 0;
+    Slot slot[kSlots];
     uint16_t *d_mag = nullptr;        // stage-level magnitude output
     size_t d_mag_cap = 0;
 
@@ -117,28 +128,38 @@ void free_all(adsbcu_handle *h)
 {
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
-    cudaFree(h->d_tab); cudaFree(h->d_bitmap); cudaFree(h->d_carry); cudaFree(h->d_iq);
-    cudaFree(h->d_phase); cudaFree(h->d_full); cudaFree(h->d_ctr); cudaFree(h->d_mag);
-    if (h->h_ctr) cudaFreeHost(h->h_ctr);
-    if (h->h_full) cudaFreeHost(h->h_full);
-    for (auto &e : h->ev) if (e) cudaEventDestroy(e);
+    if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
+    cudaFree(h->d_tab); cudaFree(h->d_bitmap); cudaFree(h->d_carry); cudaFree(h->d_iq); cudaFree(h->d_mag);
+    for (Slot &s : h->slot) {
+        cudaFree(s.d_seg); cudaFree(s.d_seg_count); cudaFree(s.d_ctr);
+        if (s.h_ctr) cudaFreeHost(s.h_ctr);
+        if (s.h_full) cudaFreeHost(s.h_full);
+        for (auto &e : s.ev) if (e) cudaEventDestroy(e);
+    }
+    for (auto &e : h->ev_h2d) if (e) cudaEventDestroy(e);
+    for (auto &e : h->ev_up) if (e) cudaEventDestroy(e);
     if (h->stream) cudaStreamDestroy(h->stream);
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
 }
 
 // ---- ordered host pass ------------------------------------------------------------------
-// recs: all surviving (position, phase) records of one feed, sorted by (pos, phase).
+// recs: the surviving (position, phase) records of one chunk in (pos, phase) order.
 // feed_base: padded-stream coordinate of the feed's first start position.
-int resolve(adsbcu_handle *h, const FullRec *recs, size_t nrec, uint64_t feed_base,
-            adsbcu_msg *out, size_t cap, size_t *n_out)
+struct Sink {
+    adsbcu_msg *out;
+    size_t cap, n;
+    bool overflow;
+};
+
+void resolve(adsbcu_handle *h, const FullRec *recs, size_t nrec, uint64_t feed_base, Sink &sink)
 {
     const uint64_t block = h->cfg.block_samples;
-    size_t nmsg = 0;
-    int rc = ADSBCU_OK;
     size_t i = 0;
     while (i < nrec) {
-        const uint64_t a = feed_base + recs[i].pos;
-        size_t e = i;
-        while (e < nrec && recs[e].pos == recs[i].pos) ++e;
+        const uint32_t pos = recs[i].pos;
+        const uint64_t a = feed_base + pos;
+        size_t e = i + 1;
+        while (e < nrec && recs[e].pos == pos) ++e;
         if (h->has_last) {
             // inside the mag_buf of the last accepted message scanning resumes 18 samples before its
             // end (j = last_message_end - 19, then ++j); a later mag_buf starts exactly at its end
@@ -156,8 +177,8 @@ int resolve(adsbcu_handle *h, const FullRec *recs, size_t nrec, uint64_t feed_ba
         if (best < kAcceptThreshold) continue;
 
         const FullRec &r = *bp;
-        if (nmsg < cap) {
-            adsbcu_msg &m = out[nmsg];
+        if (sink.n < sink.cap) {
+            adsbcu_msg &m = sink.out[sink.n];
             std::memset(&m, 0, sizeof(m));
             // sampleTimestamp of the block (sdr_ifile.c:202) + 5*j + 768 + phase: with 12e6/2.4e6 == 5 this
             // is 5*a + 768 + phase where a counts from the first overlap sample of the stream
@@ -176,9 +197,9 @@ int resolve(adsbcu_handle *h, const FullRec *recs, size_t nrec, uint64_t feed_ba
             const int siglen = msglen * 12 / 5;
             m.signal_level = (double(r.sum_sq) / 65535.0 / 65535.0) / siglen;
         } else {
-            rc = ADSBCU_ERR_OVERFLOW;
+            sink.overflow = true;
         }
-        ++nmsg;
+        ++sink.n;
         if (r.add_key != kUnchecked) h->filter.add(r.add_key);
 
         // skip rule (demod_2400.c:410-419, :432-443): remember where this message ends
@@ -186,68 +207,116 @@ int resolve(adsbcu_handle *h, const FullRec *recs, size_t nrec, uint64_t feed_ba
         h->last_a = a;
         h->last_lme = a + uint64_t((((r.verbatim[0] & 0x80) ? 112 : 56) + 8) * 12 / 5);
     }
-    *n_out = nmsg;
-    return rc;
 }
 
-}  // namespace
-
-// ---- one feed: scan -> finalize -> download -> ordered host pass ---------------------------
-namespace {
-
-int run_feed(adsbcu_handle *h, const uint8_t *d_iq, uint32_t n, bool timed_h2d, adsbcu_msg *out, size_t cap,
-             size_t *n_out)
+// ---- one feed of at most max_feed_samples: a pipeline of chunks ---------------------------------
+// For every chunk: [upload its samples] -> scan -> filter -> evaluate -> counters to the host.
+// Everything is queued without host synchronisation; the host pass of chunk c runs while the GPU
+// works on the following chunks.  iq_host != nullptr: the samples are uploaded into d_iq chunk by
+// chunk on copy_stream (a chunk only looks at samples at or before its own end, see ScanArgs).
+int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint32_t n, Sink &sink)
 {
-    ScanArgs a{};
-    a.iq = d_iq;
-    a.carry_mag = h->d_carry;
-    a.nsamples = n;
-    a.tab = h->d_tab;
-    a.bitmap = h->d_bitmap;
-    a.phase = h->d_phase; a.phase_cap = h->phase_cap;
-    a.full = h->d_full;   a.full_cap = h->full_cap;
-    a.ctr = h->d_ctr;
+    adsbcu_stats &st = h->stats;
+    const uint32_t cp = h->chunk_positions;
+    const uint32_t nchunks = (n + cp - 1) / cp;
+    float ms_h2d = 0.f;
+    if (iq_host) CK(cudaEventRecord(h->ev_h2d[0], h->copy_stream));
 
-    CK(cudaMemsetAsync(h->d_ctr, 0, sizeof(ScanCounters), h->stream));
-    CK(cudaEventRecord(h->ev[1], h->stream));
-    CK(launch_scan(a, h->sm_count, h->stream));
-    CK(cudaEventRecord(h->ev[2], h->stream));
-    CK(launch_finalize(a, h->sm_count, h->stream));
-    CK(launch_carry(d_iq, n, h->d_carry, h->d_tab, h->stream));
-    CK(cudaEventRecord(h->ev[3], h->stream));
-    CK(cudaMemcpyAsync(h->h_ctr, h->d_ctr, sizeof(ScanCounters), cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaStreamSynchronize(h->stream));
-    const ScanCounters c = *h->h_ctr;
-    if (c.overflow || c.n_phase > h->phase_cap || c.n_full > h->full_cap) {
-        h->error = "internal candidate list overflow (feed smaller chunks)";
-        return ADSBCU_ERR_OVERFLOW;
+    auto submit = [&](uint32_t c) -> int {
+        Slot &s = h->slot[c % kSlots];
+        ScanArgs a{};
+        a.iq = d_iq;
+        a.carry_mag = h->d_carry;
+        a.nsamples = n;
+        a.pos_begin = c * cp;
+        a.pos_end = std::min<uint64_t>(uint64_t(c + 1) * cp, n);
+        a.tab = h->d_tab;
+        a.bitmap = h->d_bitmap;
+        a.seg = s.d_seg; a.seg_cap = h->seg_cap; a.nseg = h->nseg;
+        a.seg_count = s.d_seg_count;
+        a.full = s.d_full; a.full_cap = h->full_cap;
+        a.ctr = s.d_ctr;
+        if (iq_host) {
+            CK(cudaMemcpyAsync(h->d_iq + 2 * size_t(a.pos_begin), iq_host + 2 * size_t(a.pos_begin),
+                               2 * size_t(a.pos_end - a.pos_begin), cudaMemcpyHostToDevice, h->copy_stream));
+            CK(cudaEventRecord(h->ev_up[c % kSlots], h->copy_stream));
+            if (c + 1 == nchunks) CK(cudaEventRecord(h->ev_h2d[1], h->copy_stream));
+            CK(cudaStreamWaitEvent(h->stream, h->ev_up[c % kSlots], 0));
+        }
+        CK(cudaMemsetAsync(s.d_ctr, 0, sizeof(ChunkCounters), h->stream));
+        CK(cudaEventRecord(s.ev[0], h->stream));
+        CK(launch_scan(a, h->stream));
+        CK(cudaEventRecord(s.ev[1], h->stream));
+        CK(launch_filter(a, h->stream));
+        CK(launch_evaluate(a, h->stream));
+        CK(cudaEventRecord(s.ev[2], h->stream));
+        CK(cudaMemcpyAsync(s.h_ctr, s.d_ctr, sizeof(ChunkCounters), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaEventRecord(s.ev[3], h->stream));
+        return ADSBCU_OK;
+    };
+    auto retire = [&](uint32_t c) -> int {
+        Slot &s = h->slot[c % kSlots];
+        CK(cudaEventSynchronize(s.ev[3]));
+        const ChunkCounters k = *s.h_ctr;
+        if (k.overflow || k.n_full > h->full_cap) {
+            h->error = "internal candidate list overflow (traffic denser than the lists are sized for)";
+            return ADSBCU_ERR_OVERFLOW;
+        }
+        const auto t0 = std::chrono::steady_clock::now();
+        resolve(h, s.h_full, k.n_full, h->stream_pos, sink);
+        const auto t1 = std::chrono::steady_clock::now();
+        float ms = 0.f;
+        st.preambles += k.preambles; st.phase_records += k.n_cand; st.resolved_records += k.n_full;
+        cudaEventElapsedTime(&ms, s.ev[0], s.ev[1]); st.ms_scan += ms;
+        cudaEventElapsedTime(&ms, s.ev[1], s.ev[2]); st.ms_finalize += ms;
+        st.ms_resolve += std::chrono::duration<float, std::milli>(t1 - t0).count();
+        st.scan_launches += 3;
+        return ADSBCU_OK;
+    };
+
+    int rc = ADSBCU_OK;
+    uint32_t submitted = 0, retired = 0;
+    while (retired < nchunks) {
+        while (submitted < nchunks && submitted < retired + kSlots) {
+            rc = submit(submitted);
+            if (rc != ADSBCU_OK) break;
+            ++submitted;
+        }
+        if (rc != ADSBCU_OK) break;
+        rc = retire(retired);
+        if (rc != ADSBCU_OK) break;
+        ++retired;
     }
-    if (c.n_full)
-        CK(cudaMemcpyAsync(h->h_full, h->d_full, size_t(c.n_full) * sizeof(FullRec), cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaEventRecord(h->ev[4], h->stream));
+    if (rc != ADSBCU_OK) { cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->copy_stream); return rc; }
+    CK(launch_carry(d_iq, n, h->d_carry, h->d_tab, h->stream));
+    st.scan_launches += 1;
     CK(cudaStreamSynchronize(h->stream));
-
-    const auto t0 = std::chrono::steady_clock::now();
-    std::sort(h->h_full, h->h_full + c.n_full, [](const FullRec &x, const FullRec &y) {
-        return x.pos != y.pos ? x.pos < y.pos : x.phase < y.phase;
-    });
-    size_t nmsg = 0;
-    const int rc = resolve(h, h->h_full, c.n_full, h->stream_pos, out, cap, &nmsg);
-    const auto t1 = std::chrono::steady_clock::now();
+    if (iq_host && nchunks) { cudaEventElapsedTime(&ms_h2d, h->ev_h2d[0], h->ev_h2d[1]); st.ms_h2d += ms_h2d; }
+    st.samples += n;
     h->stream_pos += n;
-    if (n_out) *n_out = nmsg;
+    return ADSBCU_OK;
+}
 
-    adsbcu_stats &s = h->stats;
-    s = adsbcu_stats{};
-    s.samples = n; s.preambles = c.preambles; s.phase_records = c.n_phase; s.resolved_records = c.n_full;
-    s.messages = nmsg;
-    if (timed_h2d) cudaEventElapsedTime(&s.ms_h2d, h->ev[0], h->ev[1]);
-    cudaEventElapsedTime(&s.ms_scan, h->ev[1], h->ev[2]);
-    cudaEventElapsedTime(&s.ms_finalize, h->ev[2], h->ev[3]);
-    cudaEventElapsedTime(&s.ms_d2h, h->ev[3], h->ev[4]);
-    s.ms_resolve = std::chrono::duration<float, std::milli>(t1 - t0).count();
-    s.scan_launches = 3;
-    return rc;
+int feed_common(adsbcu_handle *h, const uint8_t *iq, bool on_device, size_t nsamples, adsbcu_msg *out, size_t cap,
+                size_t *n_out)
+{
+    CK(cudaSetDevice(h->device));
+    h->stats = adsbcu_stats{};
+    Sink sink{out, cap, 0, false};
+    size_t done = 0;
+    // a feed larger than max_feed_samples is cut into takes (multiples of 8 samples keep device pointers 16 B aligned)
+    const size_t max_take = h->cfg.max_feed_samples & ~size_t(7);
+    while (done < nsamples) {
+        const size_t take = std::min<size_t>(nsamples - done, max_take);
+        const int r = on_device ? run_feed(h, iq + 2 * done, nullptr, uint32_t(take), sink)
+                                : run_feed(h, h->d_iq, iq + 2 * done, uint32_t(take), sink);
+        if (r != ADSBCU_OK) return r;
+        done += take;
+    }
+    h->stats.messages = sink.n;
+    if (n_out) *n_out = sink.n;
+    if (sink.overflow) { h->error = "out[] too small for the accepted messages"; return ADSBCU_ERR_OVERFLOW; }
+    return ADSBCU_OK;
 }
 
 }  // namespace
@@ -291,7 +360,10 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
     if (prop.major < 10) { h->error = "device is not sm_100 class"; return fail(ADSBCU_ERR_NO_DEVICE); }
     h->sm_count = prop.multiProcessorCount;
     CKC(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-    for (auto &e : h->ev) CKC(cudaEventCreate(&e));
+    CKC(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    for (auto &e : h->ev_h2d) CKC(cudaEventCreate(&e));
+    for (auto &e : h->ev_up) CKC(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CKC(init_kernels());
 
     DevTables *tab = new (std::nothrow) DevTables;
     if (!tab) return fail(ADSBCU_ERR_NOMEM);
@@ -301,19 +373,30 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
     delete tab;
     CKC(e);
 
+    // chunk geometry: every scan CTA (4 per SM) owns kTilesPerSeg consecutive tiles of a chunk
+    constexpr uint32_t kTilesPerSeg = 2;
     const size_t nmax = c.max_feed_samples;
-    h->phase_cap = uint32_t(std::max<size_t>(1u << 16, nmax / 16));
-    h->full_cap = uint32_t(std::max<size_t>(1u << 14, nmax / 128));
+    h->nseg = uint32_t(h->sm_count) * 4u;
+    h->chunk_positions = h->nseg * uint32_t(kTile) * kTilesPerSeg;
+    const size_t chunk = std::min<size_t>(h->chunk_positions, (nmax + kTile - 1) / kTile * kTile);
+    // list sizes: 1 (position, phase) record per 8 positions, 1 evaluated record per 32 positions, per chunk
+    // (Gaussian noise needs 1 per 230 / real traffic 1 per ~800); overflow is reported, never silent
+    h->seg_cap = uint32_t(std::max<size_t>(2048, chunk / 8 / h->nseg * 4));   // >= one full tile list per tile of the segment
+    h->full_cap = uint32_t(std::max<size_t>(1u << 12, chunk / 32));
     CKC(cudaMalloc(&h->d_bitmap, (size_t(1) << 25) / 8));
     CKC(cudaMemset(h->d_bitmap, 0, (size_t(1) << 25) / 8));
     CKC(cudaMalloc(&h->d_carry, kOverlap * sizeof(uint16_t) + 32));
     CKC(cudaMemset(h->d_carry, 0, kOverlap * sizeof(uint16_t) + 32));
     CKC(cudaMalloc(&h->d_iq, nmax * 2 + 64));
-    CKC(cudaMalloc(&h->d_phase, size_t(h->phase_cap) * sizeof(PhaseRec)));
-    CKC(cudaMalloc(&h->d_full, size_t(h->full_cap) * sizeof(FullRec)));
-    CKC(cudaMalloc(&h->d_ctr, sizeof(ScanCounters)));
-    CKC(cudaMallocHost(&h->h_ctr, sizeof(ScanCounters)));
-    CKC(cudaMallocHost(&h->h_full, size_t(h->full_cap) * sizeof(FullRec)));
+    for (Slot &s : h->slot) {
+        CKC(cudaMalloc(&s.d_seg, size_t(h->nseg) * h->seg_cap * sizeof(PhaseRec)));
+        CKC(cudaMalloc(&s.d_seg_count, size_t(h->nseg) * sizeof(uint32_t)));
+        CKC(cudaMalloc(&s.d_ctr, sizeof(ChunkCounters)));
+        CKC(cudaHostAlloc(&s.h_ctr, sizeof(ChunkCounters), cudaHostAllocDefault));
+        CKC(cudaHostAlloc(&s.h_full, size_t(h->full_cap) * sizeof(FullRec), cudaHostAllocMapped));
+        CKC(cudaHostGetDevicePointer(&s.d_full, s.h_full, 0));
+        for (int k = 0; k < 4; ++k) CKC(cudaEventCreate(&s.ev[k]));
+    }
 #undef CKC
     *out = h;
     return ADSBCU_OK;
@@ -351,30 +434,7 @@ int adsbcu_1090_feed_device(adsbcu_handle *h, const uint8_t *iq_dev, size_t nsam
         h->error = "bad argument (null or misaligned pointer)";
         return ADSBCU_ERR_ARG;
     }
-    CK(cudaSetDevice(h->device));
-    size_t done = 0, total = 0;
-    int rc = ADSBCU_OK;
-    adsbcu_stats acc{};
-    while (done < nsamples) {
-        // chunk size keeps 16-byte alignment of every chunk start (multiple of 8 samples)
-        const size_t take = std::min<size_t>(nsamples - done, h->cfg.max_feed_samples & ~size_t(7));
-        size_t got = 0;
-        CK(cudaEventRecord(h->ev[0], h->stream));
-        const int r = run_feed(h, iq_dev + 2 * done, uint32_t(take), false, out ? out + std::min(total, cap) : nullptr,
-                               cap > total ? cap - total : 0, &got);
-        if (r != ADSBCU_OK && r != ADSBCU_ERR_OVERFLOW) return r;
-        if (r == ADSBCU_ERR_OVERFLOW) { if (!h->h_ctr->overflow && h->h_ctr->n_phase <= h->phase_cap && h->h_ctr->n_full <= h->full_cap) rc = r; else return r; }
-        total += got; done += take;
-        const adsbcu_stats &s = h->stats;
-        acc.samples += s.samples; acc.preambles += s.preambles; acc.phase_records += s.phase_records;
-        acc.resolved_records += s.resolved_records; acc.messages += s.messages; acc.ms_scan += s.ms_scan;
-        acc.ms_finalize += s.ms_finalize; acc.ms_d2h += s.ms_d2h; acc.ms_resolve += s.ms_resolve;
-        acc.scan_launches += s.scan_launches;
-    }
-    h->stats = acc;
-    if (n_out) *n_out = total;
-    if (rc == ADSBCU_ERR_OVERFLOW) h->error = "out[] too small for the accepted messages";
-    return rc;
+    return feed_common(h, iq_dev, true, nsamples, out, cap, n_out);
 }
 
 int adsbcu_1090_feed(adsbcu_handle *h, const uint8_t *iq, size_t nsamples, adsbcu_msg *out, size_t cap, size_t *n_out)
@@ -382,30 +442,7 @@ int adsbcu_1090_feed(adsbcu_handle *h, const uint8_t *iq, size_t nsamples, adsbc
     if (!h) return ADSBCU_ERR_ARG;
     if (n_out) *n_out = 0;
     if ((!iq && nsamples) || (!out && cap)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
-    CK(cudaSetDevice(h->device));
-    size_t done = 0, total = 0;
-    int rc = ADSBCU_OK;
-    adsbcu_stats acc{};
-    while (done < nsamples) {
-        const size_t take = std::min<size_t>(nsamples - done, h->cfg.max_feed_samples);
-        size_t got = 0;
-        CK(cudaEventRecord(h->ev[0], h->stream));
-        CK(cudaMemcpyAsync(h->d_iq, iq + 2 * done, take * 2, cudaMemcpyHostToDevice, h->stream));
-        const int r = run_feed(h, h->d_iq, uint32_t(take), true, out ? out + std::min(total, cap) : nullptr,
-                               cap > total ? cap - total : 0, &got);
-        if (r != ADSBCU_OK && r != ADSBCU_ERR_OVERFLOW) return r;
-        if (r == ADSBCU_ERR_OVERFLOW) { if (!h->h_ctr->overflow && h->h_ctr->n_phase <= h->phase_cap && h->h_ctr->n_full <= h->full_cap) rc = r; else return r; }
-        total += got; done += take;
-        const adsbcu_stats &s = h->stats;
-        acc.samples += s.samples; acc.preambles += s.preambles; acc.phase_records += s.phase_records;
-        acc.resolved_records += s.resolved_records; acc.messages += s.messages; acc.ms_h2d += s.ms_h2d;
-        acc.ms_scan += s.ms_scan; acc.ms_finalize += s.ms_finalize; acc.ms_d2h += s.ms_d2h; acc.ms_resolve += s.ms_resolve;
-        acc.scan_launches += s.scan_launches;
-    }
-    h->stats = acc;
-    if (n_out) *n_out = total;
-    if (rc == ADSBCU_ERR_OVERFLOW) h->error = "out[] too small for the accepted messages";
-    return rc;
+    return feed_common(h, iq, false, nsamples, out, cap, n_out);
 }
 
 int adsbcu_1090_magnitude(adsbcu_handle *h, const uint8_t *iq, size_t nsamples, uint16_t *mag_out)

@@ -100,30 +100,42 @@ struct DevTables {
     uint32_t crc_byte[11][256];  // syndrome contribution of byte b (0..10) of a 112-bit frame having value v
 };
 
-struct ScanCounters {
+// Per-chunk counters (device; copied to pinned host memory after the chunk's kernels).
+struct ChunkCounters {
     unsigned long long preambles;
-    unsigned int n_phase;        // PhaseRec written (may exceed capacity -> overflow)
-    unsigned int n_full;         // FullRec written
-    unsigned int overflow;
+    unsigned int n_cand;         // (position, phase) records written by the scan kernel (all segments)
+    unsigned int n_full;         // FullRec written by the evaluate kernel
+    unsigned int overflow;       // a tile list, a segment or full[] overflowed: results are incomplete
     unsigned int pad;
 };
 
+// One chunk = a contiguous range of start positions of the current feed.  Position p (feed-relative,
+// in the reference's padded mag_buf coordinate) looks at feed samples p-326 .. p-326+289; samples
+// before the feed come from carry_mag (fifo.c:187-196), so a chunk never reads past the feed end.
+//
+// Ordered emission: segment g of `nseg` owns a contiguous run of the chunk's tiles and writes its
+// records in (position, phase) order into seg[g*seg_cap ..]; segments in index order are therefore
+// the whole chunk in stream order and the host pass never sorts.
 struct ScanArgs {
     const uint8_t  *iq;          // feed samples (device), 16 B aligned
     const uint16_t *carry_mag;   // kOverlap magnitudes preceding the feed (zeros at stream start)
-    uint32_t        nsamples;    // samples in the feed == start positions in the feed
+    uint32_t        nsamples;    // samples in the feed
+    uint32_t        pos_begin, pos_end;   // this chunk's start positions
     const DevTables *tab;
     uint32_t       *bitmap;      // 2 x 2^24 bits: [plain | NT] addresses that may enter the filter
-    PhaseRec       *phase;       uint32_t phase_cap;
-    FullRec        *full;        uint32_t full_cap;
-    ScanCounters   *ctr;
+    PhaseRec       *seg;         uint32_t seg_cap;  uint32_t nseg;
+    uint32_t       *seg_count;   // [nseg] records per segment (scan: kept; filter: survivors)
+    FullRec        *full;        uint32_t full_cap; // mapped pinned host memory
+    ChunkCounters  *ctr;
 };
 
 void build_tables(DevTables &t, int nfix_crc, int fix_df);
 
 // launchers (adsbcu_kernels.cu)
-cudaError_t launch_scan(const ScanArgs &a, int sm_count, cudaStream_t s);
-cudaError_t launch_finalize(const ScanArgs &a, int sm_count, cudaStream_t s);
+cudaError_t init_kernels();                                        // per device, once (opt-in shared memory size)
+cudaError_t launch_scan(const ScanArgs &a, cudaStream_t s);       // grid = a.nseg
+cudaError_t launch_filter(const ScanArgs &a, cudaStream_t s);     // drop A/P records whose address can never be known
+cudaError_t launch_evaluate(const ScanArgs &a, cudaStream_t s);   // survivors -> FullRec, stream order
 cudaError_t launch_carry(const uint8_t *iq, uint32_t nsamples, uint16_t *carry_mag, const DevTables *tab, cudaStream_t s);
 cudaError_t launch_magnitude(const uint8_t *iq, uint32_t nsamples, uint16_t *mag, const DevTables *tab, cudaStream_t s);
 

@@ -8,9 +8,14 @@
 //                    of (position, phase) records that can still reach the accept
 //                    threshold.  Replaces magnitude_uc8.c:30-63 + demod_2400.c:134-347 +
 //                    mode_s.c:252-466 (state-independent part).
-//   finalize_kernel  drops records whose address can never be in the ICAO filter, re-slices
-//                    the survivors and emits fully evaluated records for the ordered host
-//                    pass (demod_2400.c:349-423 is sequential by definition).
+//                    Each CTA owns a contiguous run of tiles (one "segment") and writes its records
+//                    in (position, phase) order, so the chunk comes out in stream order.
+//   filter_kernel    per segment, in place and order preserving: drops Address/Parity records
+//                    whose address can never be in the ICAO filter (bitmap built by the scan).
+//   evaluate_kernel  one warp per surviving record: re-slices it from the I/Q samples and
+//                    writes the fully evaluated record, in stream order, straight into mapped
+//                    host memory for the ordered host pass (demod_2400.c:349-423 is
+//                    sequential by definition).
 //   carry_kernel     keeps the last 326 magnitudes for the next feed (fifo.c:187-196).
 //   magnitude_kernel stage-level I/Q -> magnitude (starch_magnitude_uc8).
 #include "adsbcu_device.cuh"
@@ -23,6 +28,17 @@ constexpr int kWarps = kScanThreads / 32;
 constexpr int kCandCap = 4096;                 // preambles kept per tile (overflow -> error, never silently dropped)
 constexpr int kCandChunk = 256;                // preambles per slicer round
 constexpr int kQueueCap = 5 * kCandChunk;      // (preamble, phase) items per round
+constexpr int kKeepCap = 1024;                 // kept (position, phase) records per tile
+
+struct ScanSmem {
+    __align__(16) uint16_t mag[kTileSamples + kTilePad];
+    float    sq[256];
+    uint32_t crcb[11 * 256];
+    uint16_t cand[kCandCap];
+    uint32_t queue[2][kQueueCap];              // [0] 112-bit items, [1] 56-bit items: pos | (phase-4) << 16
+    uint2    keep[kKeepCap];                   // x: pos << 3 | phase-4 (sort key), y: PhaseRec.info
+    uint32_t ncand, nq[2], nkeep;
+};
 static_assert(kTile == kWarps * 1024, "each warp owns 1024 start positions of a tile");
 
 __device__ __forceinline__ uint32_t funnel_r(uint32_t lo, uint32_t hi, int sh) { return __funnelshift_r(lo, hi, sh); }
@@ -56,12 +72,15 @@ __device__ __forceinline__ bool preamble_ok(const uint16_t *p)
 
 __global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanArgs a)
 {
-    __shared__ __align__(16) uint16_t s_mag[kTileSamples + kTilePad];
-    __shared__ float s_sq[256];
-    __shared__ uint32_t s_crcb[11 * 256];
-    __shared__ uint16_t s_cand[kCandCap];
-    __shared__ uint32_t s_queue[2][kQueueCap];     // [0] 112-bit items, [1] 56-bit items: pos | (phase-4) << 16
-    __shared__ uint32_t s_ncand, s_nq[2];
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    ScanSmem &sm = *reinterpret_cast<ScanSmem *>(smem_raw);
+    uint16_t *s_mag = sm.mag;
+    float *s_sq = sm.sq;
+    uint32_t *s_crcb = sm.crcb;
+    uint16_t *s_cand = sm.cand;
+    uint32_t (*s_queue)[kQueueCap] = sm.queue;
+    uint32_t &s_ncand = sm.ncand;
+    uint32_t *s_nq = sm.nq;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int i = tid; i < 256; i += kScanThreads) s_sq[i] = a.tab->sq[i];
@@ -70,12 +89,18 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanArgs a)
     const uint32_t *s_magw = reinterpret_cast<const uint32_t *>(s_mag);
 
     const int64_t n = a.nsamples;
-    const uint32_t ntiles = uint32_t((n + kTile - 1) / kTile);
+    const int64_t pos_end = a.pos_end;
+    const uint32_t ntiles = (a.pos_end - a.pos_begin + kTile - 1) / kTile;
+    // this CTA's segment: a contiguous run of the chunk's tiles
+    const uint32_t tile_first = uint32_t(uint64_t(blockIdx.x) * ntiles / gridDim.x);
+    const uint32_t tile_last = uint32_t(uint64_t(blockIdx.x + 1) * ntiles / gridDim.x);
+    PhaseRec *seg = a.seg + size_t(blockIdx.x) * a.seg_cap;
+    uint32_t seg_n = 0;                            // uniform across the CTA
     unsigned long long my_preambles = 0;
 
-    for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    for (uint32_t tile = tile_first; tile < tile_last; ++tile) {
         __syncthreads();   // previous tile fully consumed (also covers the table loads above)
-        const int64_t tile_base = int64_t(tile) * kTile;
+        const int64_t tile_base = int64_t(a.pos_begin) + int64_t(tile) * kTile;
         // shared index i <-> feed sample x = x0 + i ; start position s (tile-local) sits at i = s + kTileLead
         const int64_t x0 = tile_base - kOverlap - kTileLead;
 
@@ -104,7 +129,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanArgs a)
             o.x = m[0] | (m[1] << 16); o.y = m[2] | (m[3] << 16); o.z = m[4] | (m[5] << 16); o.w = m[6] | (m[7] << 16);
             *reinterpret_cast<uint4 *>(&s_mag[8 * v]) = o;
         }
-        if (tid == 0) s_ncand = 0;
+        if (tid == 0) { s_ncand = 0; sm.nkeep = 0; }
         __syncthreads();
 
         // ---- phase B: preamble detector ---------------------------------------------------
@@ -133,7 +158,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanArgs a)
                                | (late & L3 & (G1 | G2));                      // phase 6, 7
             uint32_t cand = pat & L0 & G12;
             const int64_t first = tile_base + wbase + lane * 32;               // feed position of bit 0
-            if (first + 32 > n) cand = first >= n ? 0u : cand & (0xFFFFFFFFu >> (32 - int(n - first)));
+            if (first + 32 > pos_end) cand = first >= pos_end ? 0u : cand & (0xFFFFFFFFu >> (32 - int(pos_end - first)));
             while (cand) {
                 const int b = __ffs(cand) - 1;
                 cand &= cand - 1;
@@ -199,87 +224,174 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanArgs a)
                 const uint32_t bi = bitmap_index(c.test_key);
                 if (c.kind == K_DF17_0 || c.kind == K_DF11_ACQ_0 || (c.kind == K_DF18_0 && !df18_non_icao(c.fixed)))
                     atomicOr(&a.bitmap[bi >> 5], 1u << (bi & 31));
-                const uint32_t slot = atomicAdd(&a.ctr->n_phase, 1u);
-                if (slot < a.phase_cap) {
-                    PhaseRec r;
-                    r.pos = uint32_t(tile_base) + pos;
-                    r.info = bi | (uint32_t(ph - 4) << 25) | (c.needs_known ? (1u << 28) : 0u);
-                    a.phase[slot] = r;
-                } else {
+                const uint32_t slot = atomicAdd(&sm.nkeep, 1u);
+                if (slot < kKeepCap)
+                    sm.keep[slot] = make_uint2((pos << 3) | uint32_t(ph - 4),
+                                               bi | (uint32_t(ph - 4) << 25) | (c.needs_known ? (1u << 28) : 0u));
+                else
                     a.ctr->overflow = 1u;
-                }
             }
         }
+
+        // ---- phase D: ordered emission of this tile's records into the segment ----------------
+        __syncthreads();
+        const uint32_t nkeep = min(sm.nkeep, uint32_t(kKeepCap));
+        if (seg_n + nkeep > a.seg_cap) {
+            if (tid == 0) a.ctr->overflow = 1u;
+        } else {
+            for (uint32_t i = tid; i < nkeep; i += kScanThreads) {
+                const uint2 me = sm.keep[i];
+                uint32_t rank = 0;
+                for (uint32_t j = 0; j < nkeep; ++j) rank += sm.keep[j].x < me.x;   // keys are unique
+                PhaseRec r;
+                r.pos = uint32_t(tile_base) + (me.x >> 3);
+                r.info = me.y;
+                seg[seg_n + rank] = r;
+            }
+            seg_n += nkeep;
+        }
+    }
+    if (tid == 0) {
+        a.seg_count[blockIdx.x] = seg_n;
+        if (seg_n) atomicAdd(&a.ctr->n_cand, seg_n);
     }
     if (my_preambles) atomicAdd(&a.ctr->preambles, my_preambles);
 }
 
-// One thread per (position, phase) record.
-__global__ void __launch_bounds__(128) finalize_kernel(ScanArgs a)
+// Per segment, in place, order preserving: keep a record unless it needs a known address that is
+// not in the bitmap of addresses that may ever enter the ICAO filter (mode_s.c:781-788).
+__global__ void __launch_bounds__(256) filter_kernel(ScanArgs a)
 {
-    const uint32_t nrec = min(a.ctr->n_phase, a.phase_cap);
+    __shared__ uint32_t s_warp[8];
+    PhaseRec *seg = a.seg + size_t(blockIdx.x) * a.seg_cap;
+    const uint32_t n = min(a.seg_count[blockIdx.x], a.seg_cap);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint32_t w = 0;                                                  // uniform
+    for (uint32_t base = 0; base < n; base += 256) {
+        const uint32_t i = base + tid;
+        PhaseRec r{0, 0};
+        bool keep = false;
+        if (i < n) {
+            r = seg[i];
+            const uint32_t bi = r.info & 0x1FFFFFFu;
+            keep = !((r.info >> 28) & 1u) || ((a.bitmap[bi >> 5] >> (bi & 31)) & 1u);
+        }
+        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, keep);
+        if (lane == 0) s_warp[warp] = __popc(bal);
+        __syncthreads();                                             // all reads of this batch are done
+        uint32_t before = 0, total = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { const uint32_t c = s_warp[k]; if (k < warp) before += c; total += c; }
+        if (keep) seg[w + before + __popc(bal & ((1u << lane) - 1u))] = r;   // index <= i: never ahead of the reads
+        w += total;
+        __syncthreads();
+    }
+    if (tid == 0) a.seg_count[blockIdx.x] = w;
+}
+
+// One warp per surviving record, one CTA per segment.  The record's 290 samples are converted
+// to magnitudes into a per-warp shared buffer, lane l slices message bits l, l+32, l+64, l+96,
+// ballots assemble the frame, the CRC-24 syndromes are an XOR reduction of per-bit syndromes.
+__global__ void __launch_bounds__(256) evaluate_kernel(ScanArgs a)
+{
+    __shared__ uint16_t s_m[8][320];
+    __shared__ __align__(16) FullRec s_rec[8];
+    __shared__ uint32_t s_part[8];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // exclusive prefix of the survivor counts of the segments before this one
+    uint32_t part = 0;
+    for (uint32_t g = tid; g < blockIdx.x; g += 256) part += a.seg_count[g];
+    part = __reduce_add_sync(0xFFFFFFFFu, part);
+    if (lane == 0) s_part[warp] = part;
+    __syncthreads();
+    uint32_t offset = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) offset += s_part[k];
+    const uint32_t nrec = min(a.seg_count[blockIdx.x], a.seg_cap);
+    if (blockIdx.x == gridDim.x - 1 && tid == 0) {
+        a.ctr->n_full = offset + nrec;
+        if (offset + nrec > a.full_cap) a.ctr->overflow = 1u;
+    }
+    const PhaseRec *seg = a.seg + size_t(blockIdx.x) * a.seg_cap;
     const int64_t n = a.nsamples;
     const float *sq = a.tab->sq;
-    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < nrec; r += gridDim.x * blockDim.x) {
-        const PhaseRec pr = a.phase[r];
-        const uint32_t bi = pr.info & 0x1FFFFFFu;
-        if ((pr.info >> 28) & 1u) {
-            if (!((a.bitmap[bi >> 5] >> (bi & 31)) & 1u)) continue;   // address can never be known
-        }
+    const uint32_t *bit_synd = a.tab->bit_synd;
+    uint16_t *m = s_m[warp];
+
+    for (uint32_t r = warp; r < nrec; r += 8) {
+        const uint32_t o = offset + r;
+        if (o >= a.full_cap) break;
+        const PhaseRec pr = seg[r];
         const int ph = 4 + int((pr.info >> 25) & 7u);
         const int64_t xb = int64_t(pr.pos) - kOverlap + 19;           // feed sample of m[j+19]
-        const uint8_t *iq = a.iq;
-        const uint16_t *carry = a.carry_mag;
-        auto mag = [=](int i) -> int {
+        __syncwarp();
+        for (int i = lane; i < 320; i += 32) {
             const int64_t x = xb + i;
-            if (x < 0) return (x + kOverlap >= 0) ? int(carry[x + kOverlap]) : 0;
-            if (x >= n) return 0;
-            return int(mag_iq(sq, iq[2 * x], iq[2 * x + 1]));
-        };
-        Frame f{0, 0};
-        uint32_t xs = 0, xl = 0;
-        slice_bits(mag, ph, 0, 8, a.tab->bit_synd, f, xs, xl);
-        const uint32_t dfbit = 1u << frame_df(f);
-        const int nbits = (a.tab->valid_long & dfbit) ? 112 : (a.tab->valid_short & dfbit) ? 56 : 0;
-        if (!nbits) continue;
-        slice_bits(mag, ph, 8, nbits, a.tab->bit_synd, f, xs, xl);
-        const Classified c = classify(f, xs, xl, a.tab);
-        if (!c.keep) continue;
-
-        FullRec o;
-        o.pos = pr.pos;
-        o.phase = uint8_t(ph);
-        o.kind = uint8_t(c.kind);
-        o.corrections = int8_t(c.corrections < 0 ? 0 : c.corrections);
-        o.msgtype = uint8_t(frame_df(c.fixed));
+            uint32_t v = 0;
+            if (x < 0) v = (x + kOverlap >= 0) ? a.carry_mag[x + kOverlap] : 0u;
+            else if (x < n) v = mag_iq(sq, a.iq[2 * x], a.iq[2 * x + 1]);
+            m[i] = uint16_t(v);
+        }
+        __syncwarp();
+        uint32_t M[4], xs = 0, xl = 0;
 #pragma unroll
-        for (int b = 0; b < 14; ++b) {
-            o.verbatim[b] = uint8_t(frame_byte(f, b));
-            o.msg[b] = uint8_t(frame_byte(c.fixed, b));
+        for (int w = 0; w < 4; ++w) {
+            const int k = 32 * w + lane;
+            const int u = ph + 12 * k, s = u / 5, sub = u - 5 * s;
+            const bool bit = k < 112 && slice_corr(m[s], m[s + 1], m[s + 2], m[s + 3], sub) > 0;
+            M[w] = __brev(__ballot_sync(0xFFFFFFFFu, bit));
         }
-        o.crc = c.crc;
-        o.test_key = c.test_key;
-        o.add_key = kUnchecked;
-        const uint32_t aa = frame_aa(c.fixed);
-        switch (o.msgtype) {
-        case 11: o.addr = aa; if (c.kind == K_DF11_ACQ_0) o.add_key = aa; break;
-        case 17: o.addr = aa; if (c.kind == K_DF17_0) o.add_key = aa; break;
-        case 18:
-            o.addr = aa | (df18_non_icao(c.fixed) ? kNonIcao : 0u);
-            if (c.kind == K_DF18_0) o.add_key = o.addr | kNtFlag;
-            break;
-        default: o.addr = c.crc; break;
+        const uint32_t dfbit = 1u << (M[0] >> 27);
+        const bool is_long = (a.tab->valid_long & dfbit) != 0;
+        if (!is_long && !(a.tab->valid_short & dfbit)) continue;      // cannot happen for a record the scan kept
+        if (is_long) { M[3] &= 0xFFFF0000u; } else { M[1] &= 0xFFFFFF00u; M[2] = 0u; M[3] = 0u; }
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            const int k = 32 * w + lane;
+            if ((M[w] >> (31 - lane)) & 1u) {
+                xl ^= bit_synd[k < 112 ? k : 0];
+                if (k < 56) xs ^= bit_synd[k + 56];
+            }
         }
+        xl = __reduce_xor_sync(0xFFFFFFFFu, xl);
+        xs = __reduce_xor_sync(0xFFFFFFFFu, xs);
+        const Frame f = frame_from_words(M, is_long);
+        const Classified c = classify(f, xs, xl, a.tab);              // uniform across the warp
         // signal power window (demod_2400.c:382-389): length from the *uncorrected* DF
         const int siglen = (frame_df(f) & 16u) ? 268 : 134;
-        uint64_t acc = 0;
-        for (int k = 0; k < siglen; ++k) {
-            const uint32_t v = uint32_t(mag(k));
-            acc += uint64_t(v * v);
+        unsigned long long acc = 0;
+        for (int i = lane; i < siglen; i += 32) { const uint32_t v = m[i]; acc += uint64_t(v * v); }
+#pragma unroll
+        for (int d = 16; d; d >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, d);
+        if (lane == 0) {
+            FullRec &q = s_rec[warp];
+            q.pos = pr.pos;
+            q.phase = uint8_t(ph);
+            q.kind = uint8_t(c.keep ? c.kind : K_COUNT);
+            q.corrections = int8_t(c.corrections < 0 ? 0 : c.corrections);
+            q.msgtype = uint8_t(frame_df(c.fixed));
+#pragma unroll
+            for (int b = 0; b < 14; ++b) {
+                q.verbatim[b] = uint8_t(frame_byte(f, b));
+                q.msg[b] = uint8_t(frame_byte(c.fixed, b));
+            }
+            q.crc = c.crc;
+            q.test_key = c.test_key;
+            q.add_key = kUnchecked;
+            const uint32_t aa = frame_aa(c.fixed);
+            switch (q.msgtype) {
+            case 11: q.addr = aa; if (c.kind == K_DF11_ACQ_0) q.add_key = aa; break;
+            case 17: q.addr = aa; if (c.kind == K_DF17_0) q.add_key = aa; break;
+            case 18:
+                q.addr = aa | (df18_non_icao(c.fixed) ? kNonIcao : 0u);
+                if (c.kind == K_DF18_0) q.add_key = q.addr | kNtFlag;
+                break;
+            default: q.addr = c.crc; break;
+            }
+            q.sum_sq = acc;
         }
-        o.sum_sq = acc;
-        const uint32_t slot = atomicAdd(&a.ctr->n_full, 1u);
-        if (slot < a.full_cap) a.full[slot] = o; else a.ctr->overflow = 1u;
+        __syncwarp();
+        if (lane < 4) reinterpret_cast<uint4 *>(&a.full[o])[lane] = reinterpret_cast<const uint4 *>(&s_rec[warp])[lane];
     }
 }
 
@@ -319,18 +431,29 @@ __global__ void __launch_bounds__(256) magnitude_kernel(const uint8_t *iq, uint3
 
 }  // namespace
 
-cudaError_t launch_scan(const ScanArgs &a, int sm_count, cudaStream_t s)
+cudaError_t init_kernels()
 {
-    const uint32_t ntiles = (a.nsamples + kTile - 1) / kTile;
-    if (!ntiles) return cudaSuccess;
-    const uint32_t grid = ntiles < uint32_t(sm_count) * 4u ? ntiles : uint32_t(sm_count) * 4u;
-    scan_kernel<<<grid, kScanThreads, 0, s>>>(a);
+    return cudaFuncSetAttribute(scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(ScanSmem)));
+}
+
+cudaError_t launch_scan(const ScanArgs &a, cudaStream_t s)
+{
+    if (a.pos_end <= a.pos_begin || !a.nseg) return cudaSuccess;
+    scan_kernel<<<a.nseg, kScanThreads, sizeof(ScanSmem), s>>>(a);
     return cudaGetLastError();
 }
 
-cudaError_t launch_finalize(const ScanArgs &a, int sm_count, cudaStream_t s)
+cudaError_t launch_filter(const ScanArgs &a, cudaStream_t s)
 {
-    finalize_kernel<<<sm_count * 8, 128, 0, s>>>(a);
+    if (a.pos_end <= a.pos_begin || !a.nseg) return cudaSuccess;
+    filter_kernel<<<a.nseg, 256, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_evaluate(const ScanArgs &a, cudaStream_t s)
+{
+    if (a.pos_end <= a.pos_begin || !a.nseg) return cudaSuccess;
+    evaluate_kernel<<<a.nseg, 256, 0, s>>>(a);
     return cudaGetLastError();
 }
 
