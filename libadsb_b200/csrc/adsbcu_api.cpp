@@ -372,17 +372,18 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
     cudaError_t e = cudaMemcpy(h->d_tab, tab, sizeof(DevTables), cudaMemcpyHostToDevice);
     delete tab;
     CKC(e);
+    CKC(launch_build_lut(h->d_tab, h->stream));
 
-    // chunk geometry: every scan CTA (4 per SM) owns kTilesPerSeg consecutive tiles of a chunk
-    constexpr uint32_t kTilesPerSeg = 2;
+    // chunk geometry: every scan group (kGroups per SM) owns kTilesPerSeg consecutive tiles of a chunk
+    constexpr uint32_t kTilesPerSeg = 6;
     const size_t nmax = c.max_feed_samples;
-    h->nseg = uint32_t(h->sm_count) * 4u;
+    h->nseg = uint32_t(h->sm_count) * uint32_t(kGroups);
     h->chunk_positions = h->nseg * uint32_t(kTile) * kTilesPerSeg;
     const size_t chunk = std::min<size_t>(h->chunk_positions, (nmax + kTile - 1) / kTile * kTile);
-    // list sizes: 1 (position, phase) record per 8 positions, 1 evaluated record per 32 positions, per chunk
+    // list sizes: 1 (position, phase) record per 4 positions of a segment, 1 evaluated record per 48 positions of a chunk
     // (Gaussian noise needs 1 per 230 / real traffic 1 per ~800); overflow is reported, never silent
-    h->seg_cap = uint32_t(std::max<size_t>(2048, chunk / 8 / h->nseg * 4));   // >= one full tile list per tile of the segment
-    h->full_cap = uint32_t(std::max<size_t>(1u << 12, chunk / 32));
+    h->seg_cap = uint32_t(std::max<size_t>(2048, chunk / h->nseg / 4));   // >= one full tile list per tile of the segment
+    h->full_cap = uint32_t(std::max<size_t>(1u << 12, chunk / 48));
     CKC(cudaMalloc(&h->d_bitmap, (size_t(1) << 25) / 8));
     CKC(cudaMemset(h->d_bitmap, 0, (size_t(1) << 25) / 8));
     CKC(cudaMalloc(&h->d_carry, kOverlap * sizeof(uint16_t) + 32));

@@ -16,11 +16,16 @@ constexpr uint32_t kNonIcao       = 1u << 24; // dump1090.h:262
 constexpr uint32_t kUnchecked     = 0xFFFFFFFFu;
 
 // ---- scan kernel tiling --------------------------------------------------------------
-constexpr int kTile        = 8192;            // start positions per tile
+// One CTA per SM; a CTA is kGroups independent groups of kGroupThreads threads that share the
+// 128 KiB magnitude LUT in shared memory.  A group stages kTileSamples magnitudes per tile and
+// scans the kTile start positions whose 290-sample lookahead fits in them.
+constexpr int kTileSamples = 8192;            // magnitudes staged per tile (2 x 16 B vectors per thread)
 constexpr int kTileLead    = 2;               // smem index of the tile's first start position (16 B alignment of x0)
-constexpr int kTileSamples = kTile + 296;     // magnitudes staged per tile (lead + tile + lookahead, multiple of 8)
+constexpr int kTile        = kTileSamples - 296;   // start positions per tile (lead + lookahead + pad to a multiple of 8)
 constexpr int kTilePad     = 32;              // slack read (never used) by the unrolled slicer's last period
-constexpr int kScanThreads = 256;
+constexpr int kGroups      = 2;
+constexpr int kGroupThreads = 512;
+static_assert(kTile % 8 == 0, "tile starts must keep 16-byte alignment of the I/Q vectors");
 
 // State-independent classification of one sliced phase.  The host combines it
 // with the filter state to get the reference's score_rank (mode_s.h:32-80).
@@ -98,7 +103,18 @@ struct DevTables {
     uint64_t synd_long[kSyndSlotsLong];
     uint64_t synd_short[kSyndSlotsShort];
     uint32_t crc_byte[11][256];  // syndrome contribution of byte b (0..10) of a 112-bit frame having value v
+    alignas(16) uint16_t mag_lut[65536];   // the reference's uc8 magnitude table (tables.c:9-41) in the bank-swizzled
+                                 // layout of lut_offset(); filled on the device by build_lut at create time
 };
+
+// Byte offset of magnitude(I, Q) inside mag_lut.  idx2 = 2 * (I | Q << 8); five low bits of Q are
+// xor-ed into the 32-bit-word index so that the 32 lanes of a gather spread over the shared-memory
+// banks even when every sample sits within a few LSB of the DC point (bank = (I>>1 ^ Q) & 31).
+__host__ __device__ inline uint32_t lut_offset(uint32_t i, uint32_t q)
+{
+    const uint32_t idx2 = (q << 9) | (i << 1);
+    return idx2 ^ ((idx2 >> 7) & 0x7Cu);
+}
 
 // Per-chunk counters (device; copied to pinned host memory after the chunk's kernels).
 struct ChunkCounters {
@@ -136,6 +152,7 @@ cudaError_t init_kernels();                                        // per device
 cudaError_t launch_scan(const ScanArgs &a, cudaStream_t s);       // grid = a.nseg
 cudaError_t launch_filter(const ScanArgs &a, cudaStream_t s);     // drop A/P records whose address can never be known
 cudaError_t launch_evaluate(const ScanArgs &a, cudaStream_t s);   // survivors -> FullRec, stream order
+cudaError_t launch_build_lut(DevTables *tab, cudaStream_t s);     // fills tab->mag_lut with the register-computed magnitudes
 cudaError_t launch_carry(const uint8_t *iq, uint32_t nsamples, uint16_t *carry_mag, const DevTables *tab, cudaStream_t s);
 cudaError_t launch_magnitude(const uint8_t *iq, uint32_t nsamples, uint16_t *mag, const DevTables *tab, cudaStream_t s);
 

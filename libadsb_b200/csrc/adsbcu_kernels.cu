@@ -24,24 +24,46 @@ namespace adsbcu {
 
 namespace {
 
-constexpr int kWarps = kScanThreads / 32;
-constexpr int kCandCap = 4096;                 // preambles kept per tile (overflow -> error, never silently dropped)
+constexpr int kPreCap = 2048;                  // positions passing the edge masks, per tile
+constexpr int kCandCap = 1024;                 // preambles kept per tile (overflow -> error, never silently dropped)
 constexpr int kCandChunk = 256;                // preambles per slicer round
 constexpr int kQueueCap = 5 * kCandChunk;      // (preamble, phase) items per round
 constexpr int kKeepCap = 1024;                 // kept (position, phase) records per tile
+constexpr int kPosWords = (kTile + 31) / 32;   // 32-position words per tile
 
-struct ScanSmem {
+struct GroupSmem {
     __align__(16) uint16_t mag[kTileSamples + kTilePad];
-    float    sq[256];
-    uint32_t crcb[11 * 256];
+    __align__(16) uint8_t lbits[kTileSamples / 8 + 16];   // bit i: mag[i] < mag[i+1]
+    __align__(16) uint8_t gbits[kTileSamples / 8 + 16];   // bit i: mag[i] > mag[i+1]
+    uint16_t pre[kPreCap];
     uint16_t cand[kCandCap];
     uint32_t queue[2][kQueueCap];              // [0] 112-bit items, [1] 56-bit items: pos | (phase-4) << 16
     uint2    keep[kKeepCap];                   // x: pos << 3 | phase-4 (sort key), y: PhaseRec.info
-    uint32_t ncand, nq[2], nkeep;
+    uint32_t npre, ncand, nq[2], nkeep;
 };
-static_assert(kTile == kWarps * 1024, "each warp owns 1024 start positions of a tile");
+struct ScanSmem {
+    __align__(16) uint16_t lut[65536];         // DevTables::mag_lut
+    uint32_t  crcb[11 * 256];
+    GroupSmem grp[kGroups];
+};
+static_assert(sizeof(ScanSmem) <= 227 * 1024, "scan kernel shared memory exceeds the sm_100 per-CTA limit");
 
 __device__ __forceinline__ uint32_t funnel_r(uint32_t lo, uint32_t hi, int sh) { return __funnelshift_r(lo, hi, sh); }
+__device__ __forceinline__ void group_sync(int g)
+{
+    asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "n"(kGroupThreads) : "memory");
+}
+// magnitude of the sample in the low / high half of a 32-bit word {I0,Q0,I1,Q1} (see lut_offset)
+__device__ __forceinline__ uint32_t lut_lo(const unsigned char *lut, uint32_t w)
+{
+    const uint32_t off = ((w << 1) & 0x1FFFEu) ^ ((w >> 6) & 0x7Cu);
+    return *reinterpret_cast<const uint16_t *>(lut + off);
+}
+__device__ __forceinline__ uint32_t lut_hi(const unsigned char *lut, uint32_t w)
+{
+    const uint32_t off = ((w >> 15) & 0x1FFFEu) ^ ((w >> 22) & 0x7Cu);
+    return *reinterpret_cast<const uint16_t *>(lut + off);
+}
 
 // Reference preamble test at p[0..18] (demod_2400.c:155-218).  `p` points into shared memory.
 __device__ __forceinline__ bool preamble_ok(const uint16_t *p)
@@ -70,83 +92,94 @@ __device__ __forceinline__ bool preamble_ok(const uint16_t *p)
     return true;
 }
 
-__global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanArgs a)
+__global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanArgs a)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     ScanSmem &sm = *reinterpret_cast<ScanSmem *>(smem_raw);
-    uint16_t *s_mag = sm.mag;
-    float *s_sq = sm.sq;
-    uint32_t *s_crcb = sm.crcb;
-    uint16_t *s_cand = sm.cand;
-    uint32_t (*s_queue)[kQueueCap] = sm.queue;
-    uint32_t &s_ncand = sm.ncand;
-    uint32_t *s_nq = sm.nq;
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < 256; i += kScanThreads) s_sq[i] = a.tab->sq[i];
-    for (int i = tid; i < 11 * 256; i += kScanThreads) s_crcb[i] = (&a.tab->crc_byte[0][0])[i];
+    // ---- CTA prologue: magnitude LUT and CRC byte tables into shared memory ------------------
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(a.tab->mag_lut);
+        uint4 *dst = reinterpret_cast<uint4 *>(sm.lut);
+        for (int i = threadIdx.x; i < 65536 * 2 / 16; i += kGroups * kGroupThreads) dst[i] = __ldg(src + i);
+        for (int i = threadIdx.x; i < 11 * 256; i += kGroups * kGroupThreads) sm.crcb[i] = (&a.tab->crc_byte[0][0])[i];
+    }
+    __syncthreads();
+
+    const int grp = threadIdx.x / kGroupThreads, tid = threadIdx.x % kGroupThreads, lane = tid & 31;
+    GroupSmem &gs = sm.grp[grp];
+    uint16_t *s_mag = gs.mag;
+    const uint32_t *s_magw = reinterpret_cast<const uint32_t *>(gs.mag);
+    const unsigned char *lut = reinterpret_cast<const unsigned char *>(sm.lut);
+    const uint32_t *s_crcb = sm.crcb;
     const uint32_t valid_long = a.tab->valid_long, valid_short = a.tab->valid_short, fixable_short = a.tab->fixable_short;
-    const uint32_t *s_magw = reinterpret_cast<const uint32_t *>(s_mag);
 
     const int64_t n = a.nsamples;
-    const int64_t pos_end = a.pos_end;
     const uint32_t ntiles = (a.pos_end - a.pos_begin + kTile - 1) / kTile;
-    // this CTA's segment: a contiguous run of the chunk's tiles
-    const uint32_t tile_first = uint32_t(uint64_t(blockIdx.x) * ntiles / gridDim.x);
-    const uint32_t tile_last = uint32_t(uint64_t(blockIdx.x + 1) * ntiles / gridDim.x);
-    PhaseRec *seg = a.seg + size_t(blockIdx.x) * a.seg_cap;
-    uint32_t seg_n = 0;                            // uniform across the CTA
+    // this group's segment: a contiguous run of the chunk's tiles
+    const uint32_t segi = blockIdx.x * kGroups + grp, nseg = gridDim.x * kGroups;
+    const uint32_t tile_first = uint32_t(uint64_t(segi) * ntiles / nseg);
+    const uint32_t tile_last = uint32_t(uint64_t(segi + 1) * ntiles / nseg);
+    PhaseRec *seg = a.seg + size_t(segi) * a.seg_cap;
+    uint32_t seg_n = 0;                            // uniform across the group
     unsigned long long my_preambles = 0;
 
     for (uint32_t tile = tile_first; tile < tile_last; ++tile) {
-        __syncthreads();   // previous tile fully consumed (also covers the table loads above)
+        group_sync(grp);   // previous tile fully consumed
         const int64_t tile_base = int64_t(a.pos_begin) + int64_t(tile) * kTile;
+        const int npos = int(min(int64_t(kTile), int64_t(a.pos_end) - tile_base));   // start positions in this tile
         // shared index i <-> feed sample x = x0 + i ; start position s (tile-local) sits at i = s + kTileLead
         const int64_t x0 = tile_base - kOverlap - kTileLead;
 
-        // ---- phase A: magnitudes --------------------------------------------------------
-        for (int v = tid; v < kTileSamples / 8; v += kScanThreads) {
+        // ---- phase A: magnitudes (LUT gather) + rising/falling edge bits -----------------------
+        for (int v = tid; v < kTileSamples / 8; v += kGroupThreads) {
             const int64_t x = x0 + 8 * v;
             uint32_t m[8];
             if (x >= 0 && x + 8 <= n) {
                 const uint4 d = __ldg(reinterpret_cast<const uint4 *>(a.iq + 2 * x));
-                const uint32_t w[4] = {d.x, d.y, d.z, d.w};
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    m[2 * e] = mag_iq(s_sq, w[e] & 0xFF, (w[e] >> 8) & 0xFF);
-                    m[2 * e + 1] = mag_iq(s_sq, (w[e] >> 16) & 0xFF, w[e] >> 24);
-                }
+                m[0] = lut_lo(lut, d.x); m[1] = lut_hi(lut, d.x);
+                m[2] = lut_lo(lut, d.y); m[3] = lut_hi(lut, d.y);
+                m[4] = lut_lo(lut, d.z); m[5] = lut_hi(lut, d.z);
+                m[6] = lut_lo(lut, d.w); m[7] = lut_hi(lut, d.w);
             } else {
 #pragma unroll
                 for (int e = 0; e < 8; ++e) {
                     const int64_t xe = x + e;
                     if (xe < 0) m[e] = (xe + kOverlap >= 0) ? a.carry_mag[xe + kOverlap] : 0u;
-                    else if (xe < n) m[e] = mag_iq(s_sq, a.iq[2 * xe], a.iq[2 * xe + 1]);
+                    else if (xe < n) m[e] = lut_lo(lut, uint32_t(a.iq[2 * xe]) | (uint32_t(a.iq[2 * xe + 1]) << 8));
                     else m[e] = 0u;
                 }
             }
             uint4 o;
             o.x = m[0] | (m[1] << 16); o.y = m[2] | (m[3] << 16); o.z = m[4] | (m[5] << 16); o.w = m[6] | (m[7] << 16);
             *reinterpret_cast<uint4 *>(&s_mag[8 * v]) = o;
-        }
-        if (tid == 0) { s_ncand = 0; sm.nkeep = 0; }
-        __syncthreads();
-
-        // ---- phase B: preamble detector ---------------------------------------------------
-        // L bit k: m[k] < m[k+1]; G bit k: m[k] > m[k+1].  Iteration `it` ballots 32 consecutive
-        // positions; lane `it` keeps that word, lane `it-1` keeps it as its lookahead word.
-        {
-            const int wbase = warp * 1024;
-            uint32_t myL = 0, myG = 0, nxL = 0, nxG = 0;
-            for (int it = 0; it <= 32; ++it) {
-                const int idx = wbase + it * 32 + lane + kTileLead;
-                const uint32_t m0 = s_mag[idx], m1 = s_mag[idx + 1];
-                const uint32_t L = __ballot_sync(0xFFFFFFFFu, m0 < m1);
-                const uint32_t G = __ballot_sync(0xFFFFFFFFu, m0 > m1);
-                if (it == lane) { myL = L; myG = G; }
-                if (it == lane + 1) { nxL = L; nxG = G; }
+            // bit k of the byte: m[k] <,> m[k+1]; lane 31 has no right neighbour here, its bit 7 is repaired in phase B
+            const uint32_t m8 = __shfl_down_sync(0xFFFFFFFFu, m[0], 1);
+            uint32_t L = __funnelshift_l(m[7] - m8, 0u, 1), G = __funnelshift_l(m8 - m[7], 0u, 1);
+#pragma unroll
+            for (int k = 6; k >= 0; --k) {
+                L = __funnelshift_l(m[k] - m[k + 1], L, 1);
+                G = __funnelshift_l(m[k + 1] - m[k], G, 1);
             }
-            // positions lane*32 + b, b = 0..31; shifted views of the 64-bit windows
+            gs.lbits[v] = uint8_t(L);
+            gs.gbits[v] = uint8_t(G);
+        }
+        if (tid == 0) { gs.npre = 0; gs.ncand = 0; gs.nkeep = 0; }
+        group_sync(grp);
+
+        // ---- phase B: preamble edge patterns, 32 start positions per thread ----------------------
+        if (tid < kPosWords) {
+            const uint32_t *Lw = reinterpret_cast<const uint32_t *>(gs.lbits), *Gw = reinterpret_cast<const uint32_t *>(gs.gbits);
+            uint32_t l0 = Lw[tid], g0 = Gw[tid];
+            const uint32_t l1 = Lw[tid + 1], l2 = Lw[tid + 2], g1 = Gw[tid + 1], g2 = Gw[tid + 2];
+            if ((tid & 7) == 7) {                   // bit 31 of this word came from a lane 31 (see phase A)
+                const uint32_t ma = s_mag[32 * tid + 31], mb = s_mag[32 * tid + 32];
+                l0 = (l0 & 0x7FFFFFFFu) | (ma < mb ? 0x80000000u : 0u);
+                g0 = (g0 & 0x7FFFFFFFu) | (ma > mb ? 0x80000000u : 0u);
+            }
+            // bit b of myL/myG <-> start position 32*tid + b (smem index + kTileLead)
+            const uint32_t myL = funnel_r(l0, l1, kTileLead), nxL = funnel_r(l1, l2, kTileLead);
+            const uint32_t myG = funnel_r(g0, g1, kTileLead), nxG = funnel_r(g1, g2, kTileLead);
             const uint32_t L0 = myL, L2 = funnel_r(myL, nxL, 2), L3 = funnel_r(myL, nxL, 3), L8 = funnel_r(myL, nxL, 8),
                            L9 = funnel_r(myL, nxL, 9), L10 = funnel_r(myL, nxL, 10), L11 = funnel_r(myL, nxL, 11);
             const uint32_t G1 = funnel_r(myG, nxG, 1), G2 = funnel_r(myG, nxG, 2), G3 = funnel_r(myG, nxG, 3),
@@ -157,32 +190,40 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanArgs a)
                                | (early & G4 & L8 & G10 & L11)                 // phase 5
                                | (late & L3 & (G1 | G2));                      // phase 6, 7
             uint32_t cand = pat & L0 & G12;
-            const int64_t first = tile_base + wbase + lane * 32;               // feed position of bit 0
-            if (first + 32 > pos_end) cand = first >= pos_end ? 0u : cand & (0xFFFFFFFFu >> (32 - int(pos_end - first)));
+            const int first = 32 * tid;
+            if (first + 32 > npos) cand = first >= npos ? 0u : cand & (0xFFFFFFFFu >> (32 - (npos - first)));
             while (cand) {
                 const int b = __ffs(cand) - 1;
                 cand &= cand - 1;
-                const int pos = wbase + lane * 32 + b;
+                const uint32_t slot = atomicAdd(&gs.npre, 1u);
+                if (slot < kPreCap) gs.pre[slot] = uint16_t(first + b); else a.ctr->overflow = 1u;
+            }
+        }
+        group_sync(grp);
+        {   // full preamble test (signal/noise ratio, quiet zones) on the compacted list
+            const uint32_t npre = min(gs.npre, uint32_t(kPreCap));
+            for (uint32_t i = tid; i < npre; i += kGroupThreads) {
+                const uint32_t pos = gs.pre[i];
                 if (preamble_ok(&s_mag[pos + kTileLead])) {
-                    const uint32_t slot = atomicAdd(&s_ncand, 1u);
-                    if (slot < kCandCap) s_cand[slot] = uint16_t(pos); else a.ctr->overflow = 1u;
+                    const uint32_t slot = atomicAdd(&gs.ncand, 1u);
+                    if (slot < kCandCap) gs.cand[slot] = uint16_t(pos); else a.ctr->overflow = 1u;
                     ++my_preambles;
                 }
             }
         }
-        __syncthreads();
+        group_sync(grp);
 
         // ---- phase C: five-phase slicer + CRC + classification ---------------------------
         // C1 slices two periods of every (preamble, phase) to read the DF field and queues the items the
         // DF pre-filter keeps (demod_2400.c:317-331); C2 slices the queued items completely, one item per
         // lane, all lanes running the same unrolled code (see slice_periods).
-        const uint32_t ncand = min(s_ncand, uint32_t(kCandCap));
+        const uint32_t ncand = min(gs.ncand, uint32_t(kCandCap));
         for (uint32_t c0 = 0; c0 < ncand; c0 += kCandChunk) {
-            if (tid < 2) s_nq[tid] = 0;
-            __syncthreads();
+            if (tid < 2) gs.nq[tid] = 0;
+            group_sync(grp);
             const uint32_t nitems = min(uint32_t(kCandChunk), ncand - c0) * 5u;
-            for (uint32_t it = tid; it < nitems; it += kScanThreads) {
-                const uint32_t pos = s_cand[c0 + it / 5u];
+            for (uint32_t it = tid; it < nitems; it += kGroupThreads) {
+                const uint32_t pos = gs.cand[c0 + it / 5u];
                 const int ph = 4 + int(it % 5u);
                 const int b = int(pos) + kTileLead + 19 + phase_c(ph);
                 uint32_t w[7], acc[4] = {0u, 0u, 0u, 0u}, M[4];
@@ -191,14 +232,14 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanArgs a)
                 align_message<10>(acc, phase_v0(ph), M);
                 const uint32_t dfbit = 1u << (M[0] >> 27);
                 const uint32_t item = pos | (uint32_t(ph - 4) << 16);
-                if (valid_long & dfbit) s_queue[0][atomicAdd(&s_nq[0], 1u)] = item;
-                else if (valid_short & dfbit) s_queue[1][atomicAdd(&s_nq[1], 1u)] = item;
+                if (valid_long & dfbit) gs.queue[0][atomicAdd(&gs.nq[0], 1u)] = item;
+                else if (valid_short & dfbit) gs.queue[1][atomicAdd(&gs.nq[1], 1u)] = item;
             }
-            __syncthreads();
-            const uint32_t nlong = s_nq[0], nshort = s_nq[1];
-            for (uint32_t it = tid; it < nlong + nshort; it += kScanThreads) {
+            group_sync(grp);
+            const uint32_t nlong = gs.nq[0], nshort = gs.nq[1];
+            for (uint32_t it = tid; it < nlong + nshort; it += kGroupThreads) {
                 const bool is_long = it < nlong;
-                const uint32_t item = is_long ? s_queue[0][it] : s_queue[1][it - nlong];
+                const uint32_t item = is_long ? gs.queue[0][it] : gs.queue[1][it - nlong];
                 const uint32_t pos = item & 0xFFFFu;
                 const int ph = 4 + int(item >> 16);
                 const int b = int(pos) + kTileLead + 19 + phase_c(ph);
@@ -224,9 +265,9 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanArgs a)
                 const uint32_t bi = bitmap_index(c.test_key);
                 if (c.kind == K_DF17_0 || c.kind == K_DF11_ACQ_0 || (c.kind == K_DF18_0 && !df18_non_icao(c.fixed)))
                     atomicOr(&a.bitmap[bi >> 5], 1u << (bi & 31));
-                const uint32_t slot = atomicAdd(&sm.nkeep, 1u);
+                const uint32_t slot = atomicAdd(&gs.nkeep, 1u);
                 if (slot < kKeepCap)
-                    sm.keep[slot] = make_uint2((pos << 3) | uint32_t(ph - 4),
+                    gs.keep[slot] = make_uint2((pos << 3) | uint32_t(ph - 4),
                                                bi | (uint32_t(ph - 4) << 25) | (c.needs_known ? (1u << 28) : 0u));
                 else
                     a.ctr->overflow = 1u;
@@ -234,15 +275,15 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanArgs a)
         }
 
         // ---- phase D: ordered emission of this tile's records into the segment ----------------
-        __syncthreads();
-        const uint32_t nkeep = min(sm.nkeep, uint32_t(kKeepCap));
+        group_sync(grp);
+        const uint32_t nkeep = min(gs.nkeep, uint32_t(kKeepCap));
         if (seg_n + nkeep > a.seg_cap) {
             if (tid == 0) a.ctr->overflow = 1u;
         } else {
-            for (uint32_t i = tid; i < nkeep; i += kScanThreads) {
-                const uint2 me = sm.keep[i];
+            for (uint32_t i = tid; i < nkeep; i += kGroupThreads) {
+                const uint2 me = gs.keep[i];
                 uint32_t rank = 0;
-                for (uint32_t j = 0; j < nkeep; ++j) rank += sm.keep[j].x < me.x;   // keys are unique
+                for (uint32_t j = 0; j < nkeep; ++j) rank += gs.keep[j].x < me.x;   // keys are unique
                 PhaseRec r;
                 r.pos = uint32_t(tile_base) + (me.x >> 3);
                 r.info = me.y;
@@ -252,10 +293,11 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanArgs a)
         }
     }
     if (tid == 0) {
-        a.seg_count[blockIdx.x] = seg_n;
+        a.seg_count[segi] = seg_n;
         if (seg_n) atomicAdd(&a.ctr->n_cand, seg_n);
     }
-    if (my_preambles) atomicAdd(&a.ctr->preambles, my_preambles);
+    my_preambles = __reduce_add_sync(0xFFFFFFFFu, uint32_t(my_preambles));
+    if (lane == 0 && my_preambles) atomicAdd(&a.ctr->preambles, my_preambles);
 }
 
 // Per segment, in place, order preserving: keep a record unless it needs a known address that is
@@ -395,6 +437,13 @@ __global__ void __launch_bounds__(256) evaluate_kernel(ScanArgs a)
     }
 }
 
+// mag_lut[lut_offset(I, Q) / 2] = magnitude(I, Q), computed exactly as magnitude_kernel does
+__global__ void build_lut_kernel(DevTables *tab)
+{
+    const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;    // I | Q << 8
+    if (idx < 65536u) tab->mag_lut[lut_offset(idx & 255u, idx >> 8) >> 1] = uint16_t(mag_iq(tab->sq, idx & 255u, idx >> 8));
+}
+
 __global__ void carry_kernel(const uint8_t *iq, uint32_t nsamples, uint16_t *carry_mag, const DevTables *tab)
 {
     // new_carry[i] = magnitude of stream sample (end - 326 + i); samples before this feed come from the old carry
@@ -439,7 +488,13 @@ cudaError_t init_kernels()
 cudaError_t launch_scan(const ScanArgs &a, cudaStream_t s)
 {
     if (a.pos_end <= a.pos_begin || !a.nseg) return cudaSuccess;
-    scan_kernel<<<a.nseg, kScanThreads, sizeof(ScanSmem), s>>>(a);
+    scan_kernel<<<a.nseg / kGroups, kGroups * kGroupThreads, sizeof(ScanSmem), s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_build_lut(DevTables *tab, cudaStream_t s)
+{
+    build_lut_kernel<<<256, 256, 0, s>>>(tab);
     return cudaGetLastError();
 }
 
