@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -68,7 +69,8 @@ struct IcaoFilter {
         }
         return t[h] == v;
     }
-    bool test(uint32_t v) const { return probe(a, v) || probe(b, v); }
+    // table b only fills after an expiry flip (live SDR input, dump1090.c:469-472), which this engine never does
+    bool test(uint32_t v) const { return probe(a, v); }
 };
 
 }  // namespace
@@ -99,7 +101,8 @@ struct adsbcu_handle {
     uint32_t *d_bitmap = nullptr;
     uint16_t *d_carry = nullptr;
     uint8_t *d_iq = nullptr;          // staging for host feeds
-    uint32_t nseg = 0, seg_cap = 0, full_cap = 0, chunk_positions = 0;
+    uint32_t nseg = 0, seg_cap = 0, full_cap = 0;
+    uint32_t unit_positions = 0, max_tps = 1;   // chunk = unit_positions * (tiles per segment), at most max_tps
     Slot slot[kSlots];
     uint16_t *d_mag = nullptr;        // stage-level magnitude output
     size_t d_mag_cap = 0;
@@ -169,8 +172,11 @@ void resolve(adsbcu_handle *h, const FullRec *recs, size_t nrec, uint64_t feed_b
 
         int best = 0;                       // SR_NOT_SET
         const FullRec *bp = nullptr;
+        uint32_t last_key = kUnchecked;
+        bool last_known = false;
         for (size_t k = i; k < e; ++k) {    // phases ascending; strict > keeps the lowest phase on ties
-            const int sc = rank_of(recs[k].kind, h->filter.test(recs[k].test_key));
+            if (recs[k].test_key != last_key) { last_key = recs[k].test_key; last_known = h->filter.test(last_key); }
+            const int sc = rank_of(recs[k].kind, last_known);
             if (sc > best) { best = sc; bp = &recs[k]; }
         }
         i = e;
@@ -217,8 +223,12 @@ void resolve(adsbcu_handle *h, const FullRec *recs, size_t nrec, uint64_t feed_b
 int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint32_t n, Sink &sink)
 {
     adsbcu_stats &st = h->stats;
-    const uint32_t cp = h->chunk_positions;
-    const uint32_t nchunks = (n + cp - 1) / cp;
+    // chunk boundaries: the first chunks are short so that the pipeline (upload -> kernels -> host pass)
+    // fills quickly, later ones long so that per-launch costs (LUT load, tail) are amortised
+    std::vector<uint32_t> bounds{0};
+    for (uint32_t tps = std::min(4u, h->max_tps); bounds.back() < n; tps = std::min(2 * tps, h->max_tps))
+        bounds.push_back(uint32_t(std::min<uint64_t>(n, uint64_t(bounds.back()) + uint64_t(h->unit_positions) * tps)));
+    const uint32_t nchunks = uint32_t(bounds.size() - 1);
     float ms_h2d = 0.f;
     if (iq_host) CK(cudaEventRecord(h->ev_h2d[0], h->copy_stream));
 
@@ -228,8 +238,8 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
         a.iq = d_iq;
         a.carry_mag = h->d_carry;
         a.nsamples = n;
-        a.pos_begin = c * cp;
-        a.pos_end = std::min<uint64_t>(uint64_t(c + 1) * cp, n);
+        a.pos_begin = bounds[c];
+        a.pos_end = bounds[c + 1];
         a.tab = h->d_tab;
         a.bitmap = h->d_bitmap;
         a.seg = s.d_seg; a.seg_cap = h->seg_cap; a.nseg = h->nseg;
@@ -374,16 +384,18 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
     CKC(e);
     CKC(launch_build_lut(h->d_tab, h->stream));
 
-    // chunk geometry: every scan group (kGroups per SM) owns kTilesPerSeg consecutive tiles of a chunk
-    constexpr uint32_t kTilesPerSeg = 6;
+    // chunk geometry: every scan group (kGroups per SM) owns up to max_tps consecutive tiles of a chunk
+    uint32_t tps = 16;
+    if (const char *e = std::getenv("ADSBCU_TILES_PER_SEG")) tps = uint32_t(std::max(1, std::atoi(e)));
     const size_t nmax = c.max_feed_samples;
     h->nseg = uint32_t(h->sm_count) * uint32_t(kGroups);
-    h->chunk_positions = h->nseg * uint32_t(kTile) * kTilesPerSeg;
-    const size_t chunk = std::min<size_t>(h->chunk_positions, (nmax + kTile - 1) / kTile * kTile);
-    // list sizes: 1 (position, phase) record per 4 positions of a segment, 1 evaluated record per 48 positions of a chunk
-    // (Gaussian noise needs 1 per 230 / real traffic 1 per ~800); overflow is reported, never silent
-    h->seg_cap = uint32_t(std::max<size_t>(2048, chunk / h->nseg / 4));   // >= one full tile list per tile of the segment
-    h->full_cap = uint32_t(std::max<size_t>(1u << 12, chunk / 48));
+    h->unit_positions = h->nseg * uint32_t(kTile);
+    h->max_tps = uint32_t(std::max<size_t>(1, std::min<size_t>(tps, (nmax + h->unit_positions - 1) / h->unit_positions)));
+    const size_t chunk = size_t(h->unit_positions) * h->max_tps;
+    // list sizes: 1 (position, phase) record per 8 positions of a segment (Gaussian noise keeps 1 per 90),
+    // 1 evaluated record per 96 positions of a chunk (real traffic needs 1 per ~800); overflow is reported, never silent
+    h->seg_cap = uint32_t(std::max<size_t>(2048, chunk / h->nseg / 8));
+    h->full_cap = uint32_t(std::max<size_t>(1u << 13, chunk / 96));
     CKC(cudaMalloc(&h->d_bitmap, (size_t(1) << 25) / 8));
     CKC(cudaMemset(h->d_bitmap, 0, (size_t(1) << 25) / 8));
     CKC(cudaMalloc(&h->d_carry, kOverlap * sizeof(uint16_t) + 32));

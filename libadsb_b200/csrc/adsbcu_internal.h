@@ -19,12 +19,18 @@ constexpr uint32_t kUnchecked     = 0xFFFFFFFFu;
 // One CTA per SM; a CTA is kGroups independent groups of kGroupThreads threads that share the
 // 128 KiB magnitude LUT in shared memory.  A group stages kTileSamples magnitudes per tile and
 // scans the kTile start positions whose 290-sample lookahead fits in them.
-constexpr int kTileSamples = 8192;            // magnitudes staged per tile (2 x 16 B vectors per thread)
+#ifndef ADSBCU_TILE_SAMPLES
+#define ADSBCU_TILE_SAMPLES 8192
+#define ADSBCU_GROUPS 2
+#define ADSBCU_GROUP_THREADS 512
+#endif
+constexpr int kTileSamples = ADSBCU_TILE_SAMPLES;   // magnitudes staged per tile (2 x 16 B vectors per thread)
 constexpr int kTileLead    = 2;               // smem index of the tile's first start position (16 B alignment of x0)
 constexpr int kTile        = kTileSamples - 296;   // start positions per tile (lead + lookahead + pad to a multiple of 8)
 constexpr int kTilePad     = 32;              // slack read (never used) by the unrolled slicer's last period
-constexpr int kGroups      = 2;
-constexpr int kGroupThreads = 512;
+constexpr int kGroups      = ADSBCU_GROUPS;
+constexpr int kGroupThreads = ADSBCU_GROUP_THREADS;
+static_assert(kTileSamples % (8 * kGroupThreads) == 0, "whole 16-byte vectors per thread");
 static_assert(kTile % 8 == 0, "tile starts must keep 16-byte alignment of the I/Q vectors");
 
 // State-independent classification of one sliced phase.  The host combines it
@@ -62,8 +68,7 @@ constexpr int kAcceptThreshold = 11;          // SR_ACCEPT_THRESHOLD
 
 // (position, phase) record kept by the scan kernel: 8 bytes.
 //   pos  : start position relative to the feed (padded-stream coordinate minus feed base)
-//   info : bits 0..24 filter key (24-bit address, bit 24 = DF18 "NT" table), 25..27 phase-4,
-//          bit 28 = needs a known address to reach the accept threshold
+//   info : bits 0..24 filter key (24-bit address, bit 24 = DF18 "NT" table), 25..27 phase-4, 28..31 Kind
 struct PhaseRec {
     uint32_t pos;
     uint32_t info;
@@ -102,7 +107,7 @@ struct DevTables {
     int32_t  pad;
     uint64_t synd_long[kSyndSlotsLong];
     uint64_t synd_short[kSyndSlotsShort];
-    uint32_t crc_byte[11][256];  // syndrome contribution of byte b (0..10) of a 112-bit frame having value v
+    alignas(16) uint32_t crc_byte[11][256];  // syndrome contribution of byte b (0..10) of a 112-bit frame having value v
     alignas(16) uint16_t mag_lut[65536];   // the reference's uc8 magnitude table (tables.c:9-41) in the bank-swizzled
                                  // layout of lut_offset(); filled on the device by build_lut at create time
 };

@@ -24,20 +24,46 @@ namespace adsbcu {
 
 namespace {
 
-constexpr int kPreCap = 2048;                  // positions passing the edge masks, per tile
-constexpr int kCandCap = 1024;                 // preambles kept per tile (overflow -> error, never silently dropped)
-constexpr int kCandChunk = 256;                // preambles per slicer round
+#ifdef ADSBCU_EXPERIMENT_NOCONFLICT   // timing experiment only (wrong results): C2 lanes read distinct banks
+#define C2BASE(b) ((((b) >> 1) & ~31) | lane)
+#else
+#define C2BASE(b) ((b) >> 1)
+#endif
+#ifdef ADSBCU_PHASE_TIMING           // debug: cycles between group barriers, summed over all groups (thread 0 of each)
+__device__ unsigned long long g_phase_cycles[8];
+#define PHASE_MARK(k) PHASE_SLOT(((k) + 4) % 5)
+#define PHASE_SLOT(k) do { if (tid == 0) { const long long t_now = clock64(); if (t_prev) atomicAdd(&g_phase_cycles[k], (unsigned long long)(t_now - t_prev)); t_prev = t_now; } } while (0)
+#else
+#define PHASE_MARK(k) do { } while (0)
+#define PHASE_SLOT(k) do { } while (0)
+#endif
+constexpr int kPreCap = kTileSamples / 4;      // positions passing the edge masks, per tile
+constexpr int kCandCap = kTileSamples / 8;     // preambles kept per tile (overflow -> error, never silently dropped)
+constexpr int kCandChunk = kGroupThreads * 3 / 10;   // preambles per slicer round
 constexpr int kQueueCap = 5 * kCandChunk;      // (preamble, phase) items per round
-constexpr int kKeepCap = 1024;                 // kept (position, phase) records per tile
+constexpr int kKeepCap = kTileSamples / 8;     // kept (position, phase) records per tile
+constexpr int kBuckets = 128, kBucketShift = 9; // phase D counting sort: 64 positions x 8 phase slots per bucket
 constexpr int kPosWords = (kTile + 31) / 32;   // 32-position words per tile
+constexpr int kUnitPeriods = 6;                // slicer work unit: 6 periods = 30 symbols = 72 samples
 
+// Scratch that is live in different phases of a tile shares storage.
+union GroupScratch {
+    struct {                                   // phases A..B2
+        __align__(16) uint8_t lbits[kTileSamples / 8 + 16];   // bit i: mag[i] < mag[i+1]
+        __align__(16) uint8_t gbits[kTileSamples / 8 + 16];   // bit i: mag[i] > mag[i+1]
+        uint16_t pre[kPreCap];
+    } edge;
+    __align__(16) uint32_t pieces[kQueueCap][4];   // phase C: the 30-symbol pieces of every queued item
+    uint2 sorted[kKeepCap];                        // phase D
+};
 struct GroupSmem {
     __align__(16) uint16_t mag[kTileSamples + kTilePad];
-    __align__(16) uint8_t lbits[kTileSamples / 8 + 16];   // bit i: mag[i] < mag[i+1]
-    __align__(16) uint8_t gbits[kTileSamples / 8 + 16];   // bit i: mag[i] > mag[i+1]
-    uint16_t pre[kPreCap];
-    uint16_t cand[kCandCap];
-    uint32_t queue[2][kQueueCap];              // [0] 112-bit items, [1] 56-bit items: pos | (phase-4) << 16
+    GroupScratch u;
+    union {
+        uint16_t cand[kCandCap];               // phases B2..C
+        uint32_t hist[3 * kBuckets];           // phase D
+    };
+    uint32_t queue[kQueueCap];                 // 112-bit items from the front, 56-bit items from the back: pos | (phase-4) << 16
     uint2    keep[kKeepCap];                   // x: pos << 3 | phase-4 (sort key), y: PhaseRec.info
     uint32_t npre, ncand, nq[2], nkeep;
 };
@@ -97,14 +123,31 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
     extern __shared__ __align__(16) unsigned char smem_raw[];
     ScanSmem &sm = *reinterpret_cast<ScanSmem *>(smem_raw);
 
-    // ---- CTA prologue: magnitude LUT and CRC byte tables into shared memory ------------------
+    // ---- CTA prologue: magnitude LUT and CRC byte tables into shared memory (TMA bulk copies) ------
     {
-        const uint4 *src = reinterpret_cast<const uint4 *>(a.tab->mag_lut);
-        uint4 *dst = reinterpret_cast<uint4 *>(sm.lut);
-        for (int i = threadIdx.x; i < 65536 * 2 / 16; i += kGroups * kGroupThreads) dst[i] = __ldg(src + i);
-        for (int i = threadIdx.x; i < 11 * 256; i += kGroups * kGroupThreads) sm.crcb[i] = (&a.tab->crc_byte[0][0])[i];
+        __shared__ __align__(8) unsigned long long s_bar;
+        const uint32_t bar = uint32_t(__cvta_generic_to_shared(&s_bar));
+        if (threadIdx.x == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            constexpr uint32_t kLutBytes = 65536 * 2, kCrcBytes = 11 * 256 * 4, kPiece = 32768;
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(kLutBytes + kCrcBytes) : "memory");
+            const unsigned char *src = reinterpret_cast<const unsigned char *>(a.tab->mag_lut);
+            const uint32_t dst = uint32_t(__cvta_generic_to_shared(sm.lut));
+            for (uint32_t o = 0; o < kLutBytes; o += kPiece)
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                             ::"r"(dst + o), "l"(src + o), "r"(kPiece), "r"(bar) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(uint32_t(__cvta_generic_to_shared(sm.crcb))), "l"(&a.tab->crc_byte[0][0]), "r"(kCrcBytes), "r"(bar) : "memory");
+        }
+        uint32_t done = 0;
+        while (!done)
+            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }"
+                         : "=r"(done) : "r"(bar) : "memory");
     }
-    __syncthreads();
 
     const int grp = threadIdx.x / kGroupThreads, tid = threadIdx.x % kGroupThreads, lane = tid & 31;
     GroupSmem &gs = sm.grp[grp];
@@ -120,23 +163,47 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
     const uint32_t segi = blockIdx.x * kGroups + grp, nseg = gridDim.x * kGroups;
     const uint32_t tile_first = uint32_t(uint64_t(segi) * ntiles / nseg);
     const uint32_t tile_last = uint32_t(uint64_t(segi + 1) * ntiles / nseg);
+    const int64_t seg_begin = int64_t(a.pos_begin) + int64_t(tile_first) * kTile;
+    const int64_t seg_end = min(int64_t(a.pos_end), int64_t(a.pos_begin) + int64_t(tile_last) * kTile);
     PhaseRec *seg = a.seg + size_t(segi) * a.seg_cap;
     uint32_t seg_n = 0;                            // uniform across the group
     unsigned long long my_preambles = 0;
 
-    for (uint32_t tile = tile_first; tile < tile_last; ++tile) {
+    // The groups of a CTA start together; a shorter first tile for every group but the first puts them
+    // out of step so that one group's load-latency phase overlaps another's slicing phase.
+    int64_t tile_base = seg_begin;
+#ifdef ADSBCU_PHASE_TIMING
+    long long t_prev = 0;
+#endif
+    int first_len = kTile - ((kTile / kGroups * grp) & ~7);
+    constexpr int kVec = kTileSamples / 8 / kGroupThreads;          // 16-byte vectors per thread
+    uint4 raw[kVec];
+    auto load_raw = [&](int64_t base) {                             // the tile whose first start position is `base`
+#pragma unroll
+        for (int r = 0; r < kVec; ++r) {
+            const int64_t x = base - kOverlap - kTileLead + 8 * (tid + r * kGroupThreads);
+            if (x >= 0 && x + 8 <= n) raw[r] = __ldg(reinterpret_cast<const uint4 *>(a.iq + 2 * x));
+        }
+    };
+    if (tile_base < seg_end) load_raw(tile_base);
+    while (tile_base < seg_end) {
         group_sync(grp);   // previous tile fully consumed
-        const int64_t tile_base = int64_t(a.pos_begin) + int64_t(tile) * kTile;
-        const int npos = int(min(int64_t(kTile), int64_t(a.pos_end) - tile_base));   // start positions in this tile
+        PHASE_MARK(0);
+        const int npos = int(min(int64_t(first_len), seg_end - tile_base));   // start positions in this tile
+        first_len = kTile;
+        const int64_t next_base = tile_base + npos;
         // shared index i <-> feed sample x = x0 + i ; start position s (tile-local) sits at i = s + kTileLead
         const int64_t x0 = tile_base - kOverlap - kTileLead;
 
         // ---- phase A: magnitudes (LUT gather) + rising/falling edge bits -----------------------
-        for (int v = tid; v < kTileSamples / 8; v += kGroupThreads) {
+        // raw[] was loaded while the previous tile was being sliced (or just before the loop)
+#pragma unroll
+        for (int r = 0; r < kVec; ++r) {
+            const int v = tid + r * kGroupThreads;
             const int64_t x = x0 + 8 * v;
             uint32_t m[8];
             if (x >= 0 && x + 8 <= n) {
-                const uint4 d = __ldg(reinterpret_cast<const uint4 *>(a.iq + 2 * x));
+                const uint4 d = raw[r];
                 m[0] = lut_lo(lut, d.x); m[1] = lut_hi(lut, d.x);
                 m[2] = lut_lo(lut, d.y); m[3] = lut_hi(lut, d.y);
                 m[4] = lut_lo(lut, d.z); m[5] = lut_hi(lut, d.z);
@@ -161,15 +228,17 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
                 L = __funnelshift_l(m[k] - m[k + 1], L, 1);
                 G = __funnelshift_l(m[k + 1] - m[k], G, 1);
             }
-            gs.lbits[v] = uint8_t(L);
-            gs.gbits[v] = uint8_t(G);
+            gs.u.edge.lbits[v] = uint8_t(L);
+            gs.u.edge.gbits[v] = uint8_t(G);
         }
         if (tid == 0) { gs.npre = 0; gs.ncand = 0; gs.nkeep = 0; }
+        if (next_base < seg_end) load_raw(next_base);                   // in flight during phases B..D
         group_sync(grp);
+        PHASE_MARK(1);
 
         // ---- phase B: preamble edge patterns, 32 start positions per thread ----------------------
         if (tid < kPosWords) {
-            const uint32_t *Lw = reinterpret_cast<const uint32_t *>(gs.lbits), *Gw = reinterpret_cast<const uint32_t *>(gs.gbits);
+            const uint32_t *Lw = reinterpret_cast<const uint32_t *>(gs.u.edge.lbits), *Gw = reinterpret_cast<const uint32_t *>(gs.u.edge.gbits);
             uint32_t l0 = Lw[tid], g0 = Gw[tid];
             const uint32_t l1 = Lw[tid + 1], l2 = Lw[tid + 2], g1 = Gw[tid + 1], g2 = Gw[tid + 2];
             if ((tid & 7) == 7) {                   // bit 31 of this word came from a lane 31 (see phase A)
@@ -196,14 +265,15 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
                 const int b = __ffs(cand) - 1;
                 cand &= cand - 1;
                 const uint32_t slot = atomicAdd(&gs.npre, 1u);
-                if (slot < kPreCap) gs.pre[slot] = uint16_t(first + b); else a.ctr->overflow = 1u;
+                if (slot < kPreCap) gs.u.edge.pre[slot] = uint16_t(first + b); else a.ctr->overflow = 1u;
             }
         }
         group_sync(grp);
+        PHASE_MARK(2);
         {   // full preamble test (signal/noise ratio, quiet zones) on the compacted list
             const uint32_t npre = min(gs.npre, uint32_t(kPreCap));
             for (uint32_t i = tid; i < npre; i += kGroupThreads) {
-                const uint32_t pos = gs.pre[i];
+                const uint32_t pos = gs.u.edge.pre[i];
                 if (preamble_ok(&s_mag[pos + kTileLead])) {
                     const uint32_t slot = atomicAdd(&gs.ncand, 1u);
                     if (slot < kCandCap) gs.cand[slot] = uint16_t(pos); else a.ctr->overflow = 1u;
@@ -212,11 +282,14 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
             }
         }
         group_sync(grp);
+        PHASE_MARK(3);
 
         // ---- phase C: five-phase slicer + CRC + classification ---------------------------
-        // C1 slices two periods of every (preamble, phase) to read the DF field and queues the items the
-        // DF pre-filter keeps (demod_2400.c:317-331); C2 slices the queued items completely, one item per
-        // lane, all lanes running the same unrolled code (see slice_periods).
+        // C1 slices two periods of every (preamble, phase) to read the DF field and queues the items the DF
+        //    pre-filter keeps (demod_2400.c:317-331);
+        // C2 slices the queued items in units of 6 periods (30 symbols), one unit per lane, every lane running
+        //    the same unrolled code: a 112-bit item is 4 units, a 56-bit item 2;
+        // C3 reassembles each item from its pieces, one item per lane: CRC-24 syndromes, repair, classification.
         const uint32_t ncand = min(gs.ncand, uint32_t(kCandCap));
         for (uint32_t c0 = 0; c0 < ncand; c0 += kCandChunk) {
             if (tid < 2) gs.nq[tid] = 0;
@@ -232,31 +305,48 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
                 align_message<10>(acc, phase_v0(ph), M);
                 const uint32_t dfbit = 1u << (M[0] >> 27);
                 const uint32_t item = pos | (uint32_t(ph - 4) << 16);
-                if (valid_long & dfbit) gs.queue[0][atomicAdd(&gs.nq[0], 1u)] = item;
-                else if (valid_short & dfbit) gs.queue[1][atomicAdd(&gs.nq[1], 1u)] = item;
+                if (valid_long & dfbit) gs.queue[atomicAdd(&gs.nq[0], 1u)] = item;
+                else if (valid_short & dfbit) gs.queue[kQueueCap - 1 - atomicAdd(&gs.nq[1], 1u)] = item;
             }
             group_sync(grp);
+            PHASE_SLOT(5);
             const uint32_t nlong = gs.nq[0], nshort = gs.nq[1];
-            for (uint32_t it = tid; it < nlong + nshort; it += kGroupThreads) {
-                const bool is_long = it < nlong;
-                const uint32_t item = is_long ? gs.queue[0][it] : gs.queue[1][it - nlong];
+            const uint32_t nunits = 4u * nlong + 2u * nshort;
+            for (uint32_t u = tid; u < nunits; u += kGroupThreads) {
+                const bool is_long = u < 4u * nlong;
+                const uint32_t idx = is_long ? u >> 2 : nlong + ((u - 4u * nlong) >> 1);      // item index of this round
+                const uint32_t blk = is_long ? u & 3u : (u - 4u * nlong) & 1u;
+                const uint32_t item = is_long ? gs.queue[idx] : gs.queue[kQueueCap - 1 - (idx - nlong)];
                 const uint32_t pos = item & 0xFFFFu;
                 const int ph = 4 + int(item >> 16);
-                const int b = int(pos) + kTileLead + 19 + phase_c(ph);
-                uint32_t w[7], acc[4] = {0u, 0u, 0u, 0u}, M[4];
+                const int b = int(pos) + kTileLead + 19 + phase_c(ph) + 12 * kUnitPeriods * int(blk);
+                uint32_t w[7], acc[4] = {0u, 0u, 0u, 0u};
                 slicer_weights(b & 1, w);
+                slice_periods<kUnitPeriods>(s_magw + (b >> 1), w, acc);
+                gs.u.pieces[idx][blk] = acc[0];                                               // 30 symbols, first in bit 29
+            }
+            group_sync(grp);
+            PHASE_SLOT(6);
+            for (uint32_t it = tid; it < nlong + nshort; it += kGroupThreads) {
+                const bool is_long = it < nlong;
+                const uint32_t item = is_long ? gs.queue[it] : gs.queue[kQueueCap - 1 - (it - nlong)];
+                const uint32_t pos = item & 0xFFFFu;
+                const int ph = 4 + int(item >> 16);
+                const uint4 pc = *reinterpret_cast<const uint4 *>(gs.u.pieces[it]);
+                // symbol stream, first symbol in the MSB of W0; then shift out the v0 leading virtual symbols
+                const uint32_t W0 = (pc.x << 2) | ((pc.y >> 28) & 3u);
+                uint32_t W1 = pc.y << 4, W2 = 0u, W3 = 0u;
+                if (is_long) { W1 |= (pc.z >> 26) & 15u; W2 = (pc.z << 6) | ((pc.w >> 24) & 63u); W3 = pc.w << 8; }
+                const int v0 = phase_v0(ph);
+                uint32_t M[4] = {__funnelshift_l(W1, W0, v0), __funnelshift_l(W2, W1, v0), __funnelshift_l(W3, W2, v0), W3 << v0};
                 uint32_t xs = 0, xl = 0;
                 if (is_long) {
-                    slice_periods<24>(s_magw + (b >> 1), w, acc);
-                    align_message<120>(acc, phase_v0(ph), M);
                     M[3] &= 0xFFFF0000u;
                     xl = crc_long(M, s_crcb);
                     // the 56-bit syndrome is also needed when a short DF was sliced long (DF0/DF5 are within two
                     // bit flips of DF17/18, so --fix-2bit slices them to 14 bytes but scores them as 56-bit A/P)
                     if (!(M[0] >> 31) || (fixable_short & (1u << (M[0] >> 27)))) xs = crc_short(M, s_crcb);
                 } else {
-                    slice_periods<12>(s_magw + (b >> 1), w, acc);
-                    align_message<60>(acc, phase_v0(ph), M);
                     M[1] &= 0xFFFFFF00u; M[2] = 0u; M[3] = 0u;
                     xs = crc_short(M, s_crcb);
                 }
@@ -268,22 +358,50 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
                 const uint32_t slot = atomicAdd(&gs.nkeep, 1u);
                 if (slot < kKeepCap)
                     gs.keep[slot] = make_uint2((pos << 3) | uint32_t(ph - 4),
-                                               bi | (uint32_t(ph - 4) << 25) | (c.needs_known ? (1u << 28) : 0u));
+                                               bi | (uint32_t(ph - 4) << 25) | (c.kind << 28));
                 else
                     a.ctr->overflow = 1u;
             }
         }
 
         // ---- phase D: ordered emission of this tile's records into the segment ----------------
+        // counting sort by 64-position bucket, then rank inside the (tiny) bucket
         group_sync(grp);
+        PHASE_MARK(4);
         const uint32_t nkeep = min(gs.nkeep, uint32_t(kKeepCap));
+        uint32_t *hist = gs.hist, *start = hist + kBuckets, *fill = hist + 2 * kBuckets;
+        uint2 *sorted = gs.u.sorted;
+        static_assert((kTileSamples << 3) <= (kBuckets << kBucketShift), "phase D buckets");
         if (seg_n + nkeep > a.seg_cap) {
             if (tid == 0) a.ctr->overflow = 1u;
-        } else {
+        } else if (nkeep) {
+            for (int i = tid; i < kBuckets; i += kGroupThreads) { hist[i] = 0; fill[i] = 0; }
+            group_sync(grp);
+            for (uint32_t i = tid; i < nkeep; i += kGroupThreads) atomicAdd(&hist[gs.keep[i].x >> kBucketShift], 1u);
+            group_sync(grp);
+            if (tid < 32) {
+                constexpr int kPer = kBuckets / 32;
+                uint32_t c[kPer], sum = 0;
+#pragma unroll
+                for (int k = 0; k < kPer; ++k) { c[k] = hist[kPer * tid + k]; sum += c[k]; }
+                uint32_t incl = sum;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (tid >= d) incl += t; }
+                uint32_t run = incl - sum;
+#pragma unroll
+                for (int k = 0; k < kPer; ++k) { start[kPer * tid + k] = run; run += c[k]; }
+            }
+            group_sync(grp);
             for (uint32_t i = tid; i < nkeep; i += kGroupThreads) {
                 const uint2 me = gs.keep[i];
-                uint32_t rank = 0;
-                for (uint32_t j = 0; j < nkeep; ++j) rank += gs.keep[j].x < me.x;   // keys are unique
+                sorted[start[me.x >> kBucketShift] + atomicAdd(&fill[me.x >> kBucketShift], 1u)] = me;
+            }
+            group_sync(grp);
+            for (uint32_t i = tid; i < nkeep; i += kGroupThreads) {
+                const uint2 me = sorted[i];
+                const uint32_t lo = start[me.x >> kBucketShift], hi = lo + hist[me.x >> kBucketShift];
+                uint32_t rank = lo;
+                for (uint32_t j = lo; j < hi; ++j) rank += sorted[j].x < me.x;       // keys are unique
                 PhaseRec r;
                 r.pos = uint32_t(tile_base) + (me.x >> 3);
                 r.info = me.y;
@@ -291,6 +409,7 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
             }
             seg_n += nkeep;
         }
+        tile_base = next_base;
     }
     if (tid == 0) {
         a.seg_count[segi] = seg_n;
@@ -300,32 +419,56 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
     if (lane == 0 && my_preambles) atomicAdd(&a.ctr->preambles, my_preambles);
 }
 
-// Per segment, in place, order preserving: keep a record unless it needs a known address that is
-// not in the bitmap of addresses that may ever enter the ICAO filter (mode_s.c:781-788).
+// Per segment, in place, order preserving.  A record is dropped when it can never be the accepted phase
+// of its position:
+//  * its score needs a known address (mode_s.c:370-446) and the address is not in the bitmap of addresses
+//    that may ever enter the ICAO filter (mode_s.c:781-788);
+//  * another phase of the same position with the SAME filter key beats it whether or not that key is known
+//    (higher score_rank, or equal rank and lower phase: demod_2400.c:336 keeps the first best).
+__device__ __forceinline__ bool kind_needs_known(uint32_t kind)
+{
+    return rank_of(kind, false) < kAcceptThreshold;
+}
 __global__ void __launch_bounds__(256) filter_kernel(ScanArgs a)
 {
     __shared__ uint32_t s_warp[8];
+    __shared__ PhaseRec s_r[4 + 256 + 4];
     PhaseRec *seg = a.seg + size_t(blockIdx.x) * a.seg_cap;
     const uint32_t n = min(a.seg_count[blockIdx.x], a.seg_cap);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const PhaseRec none{0xFFFFFFFFu, 0u};
+    if (tid < 4) s_r[tid] = none;
     uint32_t w = 0;                                                  // uniform
     for (uint32_t base = 0; base < n; base += 256) {
         const uint32_t i = base + tid;
-        PhaseRec r{0, 0};
+        s_r[4 + tid] = i < n ? seg[i] : none;
+        if (tid < 4) s_r[260 + tid] = base + 256 + tid < n ? seg[base + 256 + tid] : none;
+        __syncthreads();                                             // all reads of this batch are done
+        const PhaseRec r = s_r[4 + tid];
         bool keep = false;
         if (i < n) {
-            r = seg[i];
-            const uint32_t bi = r.info & 0x1FFFFFFu;
-            keep = !((r.info >> 28) & 1u) || ((a.bitmap[bi >> 5] >> (bi & 31)) & 1u);
+            const uint32_t key = r.info & 0x1FFFFFFu, kind = r.info >> 28, ph = (r.info >> 25) & 7u;
+            keep = !kind_needs_known(kind) || ((a.bitmap[key >> 5] >> (key & 31)) & 1u);
+            const int r0 = rank_of(kind, false), r1 = rank_of(kind, true);
+#pragma unroll
+            for (int d = -4; d <= 4; ++d) {
+                if (d == 0) continue;
+                const PhaseRec q = s_r[4 + tid + d];
+                if (q.pos != r.pos || (q.info & 0x1FFFFFFu) != key) continue;
+                const uint32_t qk = q.info >> 28, qp = (q.info >> 25) & 7u;
+                const int q0 = rank_of(qk, false), q1 = rank_of(qk, true);
+                if ((q0 > r0 || (q0 == r0 && qp < ph)) && (q1 > r1 || (q1 == r1 && qp < ph))) keep = false;
+            }
         }
         const uint32_t bal = __ballot_sync(0xFFFFFFFFu, keep);
         if (lane == 0) s_warp[warp] = __popc(bal);
-        __syncthreads();                                             // all reads of this batch are done
+        __syncthreads();
         uint32_t before = 0, total = 0;
 #pragma unroll
         for (int k = 0; k < 8; ++k) { const uint32_t c = s_warp[k]; if (k < warp) before += c; total += c; }
         if (keep) seg[w + before + __popc(bal & ((1u << lane) - 1u))] = r;   // index <= i: never ahead of the reads
         w += total;
+        if (tid < 4) s_r[tid] = s_r[256 + tid];                      // look-back for the next batch
         __syncthreads();
     }
     if (tid == 0) a.seg_count[blockIdx.x] = w;
@@ -479,6 +622,15 @@ __global__ void __launch_bounds__(256) magnitude_kernel(const uint8_t *iq, uint3
 }
 
 }  // namespace
+
+#ifdef ADSBCU_PHASE_TIMING
+extern "C" void adsbcu_debug_phase_cycles(unsigned long long *out, int reset)
+{
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, g_phase_cycles, sizeof(g_phase_cycles));
+    if (reset) { unsigned long long z[8] = {}; cudaMemcpyToSymbol(g_phase_cycles, z, sizeof(z)); }
+}
+#endif
 
 cudaError_t init_kernels()
 {
