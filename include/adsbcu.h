@@ -124,6 +124,36 @@ int adsbcu_1090_filter_test(adsbcu_handle *h, uint32_t addr);   /* 1 = present, 
 
 int adsbcu_get_stats(const adsbcu_handle *h, adsbcu_stats *out);
 
+/* ---- Path B: the 1090 MHz demodulator libadsb itself compiles (2.0 MS/s) --------------------
+ * Replaces the body of ADSB1090Handler::HandleData (reference ADSB1090.cpp:158-175) down to the
+ * point where the reference calls UseModesMessage() with mm.crcok set (ADSB1090.cpp:741-959,
+ * 491-596, 266-435): LUT magnitude, preamble test, plain and phase-corrected decode attempts, mean
+ * delta filter, CRC-24 check, single-bit repair of DF11/DF17, Address/Parity recovery against the
+ * 60 s cache of recently seen ICAO addresses.  Field decoding, CPR and the IListener callback
+ * (ADSB1090.cpp:597-672, 1079-1175) stay in the caller.  Fixed reference configuration
+ * (ADSB1090.cpp:111-122): fixErrors, checkCRC, not aggressive. */
+#pragma pack(push, 1)
+typedef struct adsbcu_msg_b {
+    uint32_t pos;              /* j: sample index of the preamble inside this buffer */
+    uint32_t crc;              /* mm.crc */
+    uint32_t addr;             /* aa1<<16 | aa2<<8 | aa3 (recovered address for Address/Parity formats) */
+    uint8_t  msg[14];          /* mm.msg, after single-bit repair */
+    uint8_t  msgbits;          /* 56 or 112 */
+    uint8_t  msgtype;          /* DF as sliced (a repair does not update it, ADSB1090.cpp:501,513-519) */
+    int8_t   errorbit;         /* repaired bit, or -1 */
+    uint8_t  corrected;        /* 1: decoded on the phase-correction retry (ADSB1090.cpp:817-826) */
+    uint16_t reserved;
+} adsbcu_msg_b;
+#pragma pack(pop)
+
+/* One call == one HandleData(span) call: `iq` is nbytes of interleaved uint8 I/Q (HOST memory);
+ * no sample state is carried between calls (the reference drops messages straddling buffers,
+ * ADSB1090.cpp:772); only the ICAO cache persists.  Messages come back in buffer order. */
+int adsbcu_1090b_feed(adsbcu_handle *h, const uint8_t *iq, size_t nbytes,
+                      adsbcu_msg_b *out, size_t cap, size_t *n_out);
+/* Forget the recently-seen ICAO cache (a fresh ADSB1090Handler). */
+int adsbcu_1090b_reset(adsbcu_handle *h);
+
 #ifdef __cplusplus
 }
 #endif

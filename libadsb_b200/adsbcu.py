@@ -17,10 +17,13 @@ MSG_DTYPE = np.dtype([
     ("correctedbits", "u1"), ("msgtype", "u1"), ("score", "u1"), ("crc", "<u4"), ("addr", "<u4"),
     ("signal_level", "<f8")])
 assert MSG_DTYPE.itemsize == 56
+MSG_B_DTYPE = np.dtype([("pos", "<u4"), ("crc", "<u4"), ("addr", "<u4"), ("msg", "u1", 14), ("msgbits", "u1"),
+                        ("msgtype", "u1"), ("errorbit", "i1"), ("corrected", "u1"), ("reserved", "<u2")])
+assert MSG_B_DTYPE.itemsize == 32
 
 EXPORTS = ["adsbcu_abi_version", "adsbcu_last_error", "adsbcu_create", "adsbcu_destroy", "adsbcu_1090_reset",
            "adsbcu_1090_feed", "adsbcu_1090_feed_device", "adsbcu_1090_magnitude", "adsbcu_1090_filter_add",
-           "adsbcu_1090_filter_test", "adsbcu_get_stats"]
+           "adsbcu_1090_filter_test", "adsbcu_get_stats", "adsbcu_1090b_feed", "adsbcu_1090b_reset"]
 
 
 class Config(C.Structure):
@@ -60,6 +63,8 @@ def load():
         L.adsbcu_1090_filter_add.argtypes = [C.c_void_p, C.c_uint32]
         L.adsbcu_1090_filter_test.argtypes = [C.c_void_p, C.c_uint32]
         L.adsbcu_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
+        L.adsbcu_1090b_feed.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.adsbcu_1090b_reset.argtypes = [C.c_void_p]
         _lib = L
     return _lib
 
@@ -116,6 +121,17 @@ class Demod1090:
         out = np.zeros(n, dtype=np.uint16)
         self._check(load().adsbcu_1090_magnitude(self.h, iq.ctypes.data, n, out.ctypes.data))
         return out
+
+    def handle_data_b(self, iq: np.ndarray, cap: int = 1 << 16) -> np.ndarray:
+        """Path B: one ADSB1090Handler::HandleData(span) call (libadsb's own 2.0 MS/s demodulator)."""
+        iq = np.ascontiguousarray(iq, dtype=np.uint8)
+        out = np.zeros(cap, dtype=MSG_B_DTYPE)
+        got = C.c_size_t(0)
+        self._check(load().adsbcu_1090b_feed(self.h, iq.ctypes.data, iq.size, out.ctypes.data, cap, C.byref(got)))
+        return out[:got.value]
+
+    def reset_b(self):
+        self._check(load().adsbcu_1090b_reset(self.h))
 
     def filter_add(self, addr): self._check(load().adsbcu_1090_filter_add(self.h, addr))
     def filter_test(self, addr): return bool(load().adsbcu_1090_filter_test(self.h, addr))

@@ -113,6 +113,7 @@ struct adsbcu_handle {
     uint64_t last_a = 0, last_lme = 0; // stream coordinates counted from the first (zero) overlap sample
     IcaoFilter filter;
     adsbcu_stats stats{};
+    PathB *pathb = nullptr;
 };
 
 namespace {
@@ -131,6 +132,8 @@ void free_all(adsbcu_handle *h)
 {
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
+    pathb_free(h->pathb);
+    h->pathb = nullptr;
     if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
     cudaFree(h->d_tab); cudaFree(h->d_bitmap); cudaFree(h->d_carry); cudaFree(h->d_iq); cudaFree(h->d_mag);
     for (Slot &s : h->slot) {
@@ -496,6 +499,22 @@ int adsbcu_1090_filter_test(adsbcu_handle *h, uint32_t addr)
 {
     if (!h) return ADSBCU_ERR_ARG;
     return h->filter.test(addr) ? 1 : 0;
+}
+
+int adsbcu_1090b_feed(adsbcu_handle *h, const uint8_t *iq, size_t nbytes, adsbcu_msg_b *out, size_t cap, size_t *n_out)
+{
+    if (!h) return ADSBCU_ERR_ARG;
+    if (n_out) *n_out = 0;
+    if ((!iq && nbytes) || (!out && cap)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
+    CK(cudaSetDevice(h->device));
+    return pathb_feed(h->pathb, h->d_tab, h->sm_count, h->stream, iq, nbytes, out, cap, n_out, h->error);
+}
+
+int adsbcu_1090b_reset(adsbcu_handle *h)
+{
+    if (!h) return ADSBCU_ERR_ARG;
+    pathb_reset(h->pathb);
+    return ADSBCU_OK;
 }
 
 int adsbcu_get_stats(const adsbcu_handle *h, adsbcu_stats *out)

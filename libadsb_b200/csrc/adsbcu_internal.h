@@ -161,4 +161,16 @@ cudaError_t launch_build_lut(DevTables *tab, cudaStream_t s);     // fills tab->
 cudaError_t launch_carry(const uint8_t *iq, uint32_t nsamples, uint16_t *carry_mag, const DevTables *tab, cudaStream_t s);
 cudaError_t launch_magnitude(const uint8_t *iq, uint32_t nsamples, uint16_t *mag, const DevTables *tab, cudaStream_t s);
 
+
+// Path B (adsbcu_pathb.cu): libadsb's own 2.0 MS/s demodulator
+struct PathB;
+}  // namespace adsbcu
+#include <string>
+struct adsbcu_msg_b;
+namespace adsbcu {
+int  pathb_feed(PathB *&b, const DevTables *d_tab, int sm_count, cudaStream_t s, const uint8_t *iq, size_t nbytes,
+                adsbcu_msg_b *out, size_t cap, size_t *n_out, std::string &err);
+void pathb_reset(PathB *b);
+void pathb_free(PathB *b);
+
 }  // namespace adsbcu

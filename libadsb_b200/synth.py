@@ -85,7 +85,8 @@ def synth_capture(n_samples: int,
                   carrier_phase,
                   sigma: float,
                   rng: np.random.Generator,
-                  dc: float = 127.4) -> np.ndarray:
+                  dc: float = 127.4,
+                  samples_per_us: float = SAMPLES_PER_US) -> np.ndarray:
     """Render `frames` (list of bytes) into an interleaved uint8 I/Q array.
 
     starts: message start times in (fractional) samples; amps: peak amplitude
@@ -95,8 +96,8 @@ def synth_capture(n_samples: int,
     if len(frames):
         idx_all, val_all = [], []
         for f, t0, a, th in zip(frames, starts, amps, carrier_phase):
-            ps = t0 + _pulse_starts_us(f) * SAMPLES_PER_US          # pulse start, samples
-            pe = ps + 0.5 * SAMPLES_PER_US
+            ps = t0 + _pulse_starts_us(f) * samples_per_us          # pulse start, samples
+            pe = ps + 0.5 * samples_per_us
             base = np.floor(ps).astype(np.int64)
             c = a * np.exp(1j * th)
             for k in range(3):                                       # a 1.2-sample pulse spans <= 3 samples
@@ -175,4 +176,40 @@ def config3(seconds: float = 1.0, seed: int = 0x10900003, msgs_per_s: float = 20
     amps = np.minimum(sigma * np.sqrt(2.0) * 10.0 ** (snr / 20.0), 90.0)
     ph = rng.uniform(0, 2 * np.pi, size=m)
     iq = synth_capture(n, frames, starts, amps, ph, sigma, rng)
+    return iq, frames, starts
+
+
+FS_1090B = 2_000_000
+
+
+def config_b(seconds: float = 1.0, seed: int = 0x1090B002, msgs_per_s: float = 1000.0, sigma: float = 1.5,
+             pool: int = 300, flip_frac: float = 0.15, ap_frac: float = 0.25):
+    """Capture for the 2.0 MS/s path libadsb compiles (ADSB1090.cpp): sample-aligned and
+    half-sample-offset DF17/DF11 frames (the latter exercise the phase-correction retry), a
+    share of single-bit errors (FixSingleBitErrors) and Address/Parity replies (BruteForceAp)
+    from aircraft of the same pool.  DC point 127 as the handler assumes (ADSB1090.cpp:165-166)."""
+    rng = np.random.default_rng(seed)
+    n = int(round(seconds * FS_1090B))
+    m = int(round(seconds * msgs_per_s))
+    icaos = rng.integers(1, 1 << 24, size=pool)
+    slot = n / max(m, 1)
+    frames, starts = [], []
+    for k in range(m):
+        u = rng.random()
+        if u < ap_frac:
+            df = int(rng.choice([0, 4, 5, 16, 20, 21]))
+        else:
+            df = 17 if rng.random() < 0.7 else 11
+        f = make_frame(df, int(icaos[rng.integers(0, pool)]), rng)
+        if rng.random() < flip_frac:
+            f = flip_bits(f, [int(rng.integers(0, len(f) * 8))])
+        frames.append(f)
+        room = slot - 260.0
+        t0 = k * slot + (rng.random() * room if room > 0 else 0.0)
+        frac = rng.choice([0.0, 0.0, 0.5, rng.random()])           # aligned, half-sample, arbitrary
+        starts.append(np.floor(t0) + frac)
+    starts = np.array(starts)
+    amps = rng.uniform(25.0, 100.0, size=m)
+    ph = rng.uniform(0, 2 * np.pi, size=m)
+    iq = synth_capture(n, frames, starts, amps, ph, sigma, rng, dc=127.0, samples_per_us=2.0)
     return iq, frames, starts
