@@ -154,6 +154,35 @@ int adsbcu_1090b_feed(adsbcu_handle *h, const uint8_t *iq, size_t nbytes,
 /* Forget the recently-seen ICAO cache (a fresh ADSB1090Handler). */
 int adsbcu_1090b_reset(adsbcu_handle *h);
 
+
+/* ---- Path C: 978 MHz UAT -----------------------------------------------------------------------
+ * Replaces the body of UAT978Handler::HandleData (reference UAT978.cpp:43-60): the phase-table
+ * mapping (UAT978.cpp:52,76-100), the 65536-sample staging buffer with carry-over (:48-59) and the
+ * dump978 entry points it calls through its extern "C" FFI, `int process_buffer(uint16_t const*,
+ * int len, uint64_t offset)` and `void init_fec()` (UAT978.cpp:9-10).  Every frame the reference
+ * would pass to `dump_raw_message(char updown, uint8_t *data, int len, int rs_errors)`
+ * (uat2json-wrapper.cpp:14) comes back as one adsbcu_uat_frame, in stream order.  dump978 itself
+ * is an absent submodule of the reference: parity for this path is unpinned. */
+#pragma pack(push, 1)
+typedef struct adsbcu_uat_frame {
+    uint64_t offset;           /* stream index of the sample holding the first sync bit */
+    int16_t  rs_errors;        /* Reed-Solomon symbols corrected (sum over the six blocks for uplink) */
+    uint16_t len;              /* 18 (basic ADS-B), 34 (long ADS-B) or 432 (ground uplink) payload bytes */
+    uint8_t  updown;           /* '-' ADS-B downlink, '+' ground uplink */
+    uint8_t  reserved[3];
+    uint8_t  data[432];
+} adsbcu_uat_frame;
+#pragma pack(pop)
+
+/* One call == one UAT978Handler::HandleData(span) call on `nbytes` of interleaved uint8 I/Q
+ * sampled at 2.083334 MS/s (HOST memory).  The stream continues across calls. */
+int adsbcu_978_feed(adsbcu_handle *h, const uint8_t *iq, size_t nbytes,
+                    adsbcu_uat_frame *out, size_t cap, size_t *n_out);
+/* A fresh UAT978Handler: forget the staged samples and the stream offset. */
+int adsbcu_978_reset(adsbcu_handle *h);
+/* Stage-level entry: phi_out[k] = iqphase[{I,Q}] (UAT978.cpp:52) for k < nsamples, HOST pointers. */
+int adsbcu_978_phase(adsbcu_handle *h, const uint8_t *iq, size_t nsamples, uint16_t *phi_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -20,10 +20,14 @@ assert MSG_DTYPE.itemsize == 56
 MSG_B_DTYPE = np.dtype([("pos", "<u4"), ("crc", "<u4"), ("addr", "<u4"), ("msg", "u1", 14), ("msgbits", "u1"),
                         ("msgtype", "u1"), ("errorbit", "i1"), ("corrected", "u1"), ("reserved", "<u2")])
 assert MSG_B_DTYPE.itemsize == 32
+UAT_DTYPE = np.dtype([("offset", "<u8"), ("rs_errors", "<i2"), ("len", "<u2"), ("updown", "u1"), ("reserved", "u1", 3),
+                      ("data", "u1", 432)])
+assert UAT_DTYPE.itemsize == 448
 
 EXPORTS = ["adsbcu_abi_version", "adsbcu_last_error", "adsbcu_create", "adsbcu_destroy", "adsbcu_1090_reset",
            "adsbcu_1090_feed", "adsbcu_1090_feed_device", "adsbcu_1090_magnitude", "adsbcu_1090_filter_add",
-           "adsbcu_1090_filter_test", "adsbcu_get_stats", "adsbcu_1090b_feed", "adsbcu_1090b_reset"]
+           "adsbcu_1090_filter_test", "adsbcu_get_stats", "adsbcu_1090b_feed", "adsbcu_1090b_reset",
+           "adsbcu_978_feed", "adsbcu_978_reset", "adsbcu_978_phase"]
 
 
 class Config(C.Structure):
@@ -65,6 +69,9 @@ def load():
         L.adsbcu_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
         L.adsbcu_1090b_feed.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.adsbcu_1090b_reset.argtypes = [C.c_void_p]
+        L.adsbcu_978_feed.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.adsbcu_978_reset.argtypes = [C.c_void_p]
+        L.adsbcu_978_phase.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         _lib = L
     return _lib
 
@@ -132,6 +139,23 @@ class Demod1090:
 
     def reset_b(self):
         self._check(load().adsbcu_1090b_reset(self.h))
+
+    def handle_data_uat(self, iq: np.ndarray, cap: int = 1 << 14) -> np.ndarray:
+        """Path C: one UAT978Handler::HandleData(span) call (978 MHz UAT, 2.083334 MS/s)."""
+        iq = np.ascontiguousarray(iq, dtype=np.uint8)
+        out = np.zeros(cap, dtype=UAT_DTYPE)
+        got = C.c_size_t(0)
+        self._check(load().adsbcu_978_feed(self.h, iq.ctypes.data, iq.size, out.ctypes.data, cap, C.byref(got)))
+        return out[:got.value]
+
+    def reset_uat(self):
+        self._check(load().adsbcu_978_reset(self.h))
+
+    def uat_phase(self, iq: np.ndarray) -> np.ndarray:
+        iq = np.ascontiguousarray(iq, dtype=np.uint8)
+        out = np.zeros(iq.size // 2, dtype=np.uint16)
+        self._check(load().adsbcu_978_phase(self.h, iq.ctypes.data, iq.size // 2, out.ctypes.data))
+        return out
 
     def filter_add(self, addr): self._check(load().adsbcu_1090_filter_add(self.h, addr))
     def filter_test(self, addr): return bool(load().adsbcu_1090_filter_test(self.h, addr))

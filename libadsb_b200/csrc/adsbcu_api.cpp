@@ -114,6 +114,7 @@ struct adsbcu_handle {
     IcaoFilter filter;
     adsbcu_stats stats{};
     PathB *pathb = nullptr;
+    PathC *pathc = nullptr;
 };
 
 namespace {
@@ -134,6 +135,8 @@ void free_all(adsbcu_handle *h)
     if (h->stream) cudaStreamSynchronize(h->stream);
     pathb_free(h->pathb);
     h->pathb = nullptr;
+    pathc_free(h->pathc);
+    h->pathc = nullptr;
     if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
     cudaFree(h->d_tab); cudaFree(h->d_bitmap); cudaFree(h->d_carry); cudaFree(h->d_iq); cudaFree(h->d_mag);
     for (Slot &s : h->slot) {
@@ -515,6 +518,29 @@ int adsbcu_1090b_reset(adsbcu_handle *h)
     if (!h) return ADSBCU_ERR_ARG;
     pathb_reset(h->pathb);
     return ADSBCU_OK;
+}
+
+int adsbcu_978_feed(adsbcu_handle *h, const uint8_t *iq, size_t nbytes, adsbcu_uat_frame *out, size_t cap, size_t *n_out)
+{
+    if (!h) return ADSBCU_ERR_ARG;
+    if (n_out) *n_out = 0;
+    if ((!iq && nbytes) || (!out && cap)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
+    CK(cudaSetDevice(h->device));
+    return pathc_feed(h->pathc, h->sm_count, h->stream, iq, nbytes, out, cap, n_out, h->error);
+}
+
+int adsbcu_978_reset(adsbcu_handle *h)
+{
+    if (!h) return ADSBCU_ERR_ARG;
+    pathc_reset(h->pathc);
+    return ADSBCU_OK;
+}
+
+int adsbcu_978_phase(adsbcu_handle *h, const uint8_t *iq, size_t nsamples, uint16_t *phi_out)
+{
+    if (!h || (!iq && nsamples) || (!phi_out && nsamples)) return ADSBCU_ERR_ARG;
+    CK(cudaSetDevice(h->device));
+    return pathc_phase(h->pathc, h->sm_count, h->stream, iq, nsamples, phi_out, h->error);
 }
 
 int adsbcu_get_stats(const adsbcu_handle *h, adsbcu_stats *out)

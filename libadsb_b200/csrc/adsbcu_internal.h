@@ -172,5 +172,15 @@ int  pathb_feed(PathB *&b, const DevTables *d_tab, int sm_count, cudaStream_t s,
                 adsbcu_msg_b *out, size_t cap, size_t *n_out, std::string &err);
 void pathb_reset(PathB *b);
 void pathb_free(PathB *b);
+}  // namespace adsbcu
+struct adsbcu_uat_frame;
+namespace adsbcu {
+// Path C (adsbcu_uat.cu): 978 MHz UAT
+struct PathC;
+int  pathc_feed(PathC *&c, int sm_count, cudaStream_t s, const uint8_t *iq, size_t nbytes, adsbcu_uat_frame *out, size_t cap,
+                size_t *n_out, std::string &err);
+int  pathc_phase(PathC *&c, int sm_count, cudaStream_t s, const uint8_t *iq, size_t n, uint16_t *phi_out, std::string &err);
+void pathc_reset(PathC *c);
+void pathc_free(PathC *c);
 
 }  // namespace adsbcu

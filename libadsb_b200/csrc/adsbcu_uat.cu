@@ -1,0 +1,518 @@
+// Path C: 978 MHz UAT behind UAT978Handler::HandleData (reference UAT978.cpp:43-60).
+//
+// The reference maps every I/Q byte pair through a 64 Ki phase table (UAT978.cpp:52,76-100), stages the
+// phases in a 65536-entry buffer and calls the dump978 C function process_buffer() (UAT978.cpp:9-10,54),
+// which scans two bit alignments for the ADS-B / uplink sync words, slices frames around a per-frame
+// centre frequency, Reed-Solomon-corrects them and hands them to dump_raw_message()
+// (uat2json-wrapper.cpp:14).  dump978 itself is an absent submodule (github.com/ankurvdev/dump978 @
+// a461b30): PARITY UNPINNED, the algorithm is restated from the published dump978 legacy demodulator
+// and libfec (see oracle/oracle978.c for the same statement on the checker side).
+//
+//   uat_phase_kernel   I/Q -> phase (table gather), appended after the carried tail of the stream
+//   uat_sync_kernel    every sample position: check_sync_word() for both sync words (mean dphi of the
+//                      one / zero bits -> slicing centre -> at most 4 sync errors); candidates compacted
+//   uat_decode_kernel  one thread per candidate: slice the frame, RS(48,34) / RS(30,18) or de-interleave
+//                      + 6 x RS(92,72) (Berlekamp-Massey, Chien, Forney over GF(256)/0x187)
+//   host pass          the order-dependent rest of process_buffer(): which alignment the scan tries,
+//                      fewer-corrections-wins between index and index+1, skipping over a decoded frame,
+//                      sync shift registers that keep stale bits across a skip, 65536-sample staging with
+//                      carry-over exactly as UAT978.cpp:48-59 does it.
+#include "../../include/adsbcu.h"
+#include "adsbcu_internal.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+namespace adsbcu {
+
+namespace {
+
+constexpr int kSyncBits = 36;
+constexpr unsigned long long kAdsbSync = 0xEACDDA4E2ull, kUplinkSync = 0x153225B1Dull;
+constexpr int kLongBytes = 48, kShortBytes = 30, kLongData = 34, kShortData = 18;
+constexpr int kUpBlocks = 6, kUpBlockBytes = 92, kUpBlockData = 72, kUpBytes = 552, kUpData = 432;
+constexpr int kUpBits = kUpBytes * 8;
+constexpr int kNeed = 2 * (kSyncBits + kUpBits) + 2;          // samples a candidate position may look at
+constexpr int kTail = 9216;                                   // >= kNeed + sigma window lead, multiple of 8
+constexpr int kSigmaLead = 8;                                 // sigma window of a record starts 8 samples before it
+
+struct CandC { uint32_t x; int16_t center; uint16_t uplink; };   // x: index into the device phase buffer
+
+struct RecC {                 // 480 bytes
+    uint64_t s;               // absolute stream sample of the first sync bit
+    uint32_t sigma[3];        // bit i: phi_difference(phi[s-8+i], phi[s-7+i]) > 0
+    int16_t  rs_errors;
+    uint8_t  uplink;          // 0 ADS-B, 1 ground uplink
+    uint8_t  type;            // ADS-B: 1 basic, 2 long
+    uint8_t  data[kUpData];
+    uint8_t  pad[24];
+};
+static_assert(sizeof(RecC) == 480, "RecC layout");
+
+struct CountersC { unsigned int n_cand, n_rec, overflow, pad; };
+
+__device__ __forceinline__ int phi_diff(uint32_t from, uint32_t to)
+{
+    return int(int16_t(uint16_t(to - from)));                 // wrap to [-32768, 32767]
+}
+
+__global__ void __launch_bounds__(256) uat_phase_kernel(const uint8_t *iq, uint32_t n, const uint16_t *lut, uint16_t *phi)
+{
+    const uint16_t *iq16 = reinterpret_cast<const uint16_t *>(iq);   // {I,Q} little endian == table index (UAT978.cpp:88-96)
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) phi[i] = __ldg(&lut[iq16[i]]);
+}
+
+// positions [first, last) of the phase buffer; every position reads phi[x .. x+72)
+__global__ void __launch_bounds__(256) uat_sync_kernel(const uint16_t *phi, uint32_t first, uint32_t last, CandC *cand, uint32_t cand_cap,
+                                                       CountersC *ctr)
+{
+    __shared__ int16_t s_d[256 + 72];
+    const uint32_t base = first + blockIdx.x * 256u;
+    for (int i = threadIdx.x; i < 256 + 72; i += 256) {
+        const uint32_t x = base + i;
+        s_d[i] = x < last + 72 ? int16_t(phi_diff(phi[x], phi[x + 1])) : int16_t(0);
+    }
+    __syncthreads();
+    const uint32_t x = base + threadIdx.x;
+    if (x >= last) return;
+    const int16_t *d = &s_d[threadIdx.x];
+    int one_a = 0, zero_a = 0, one_u = 0, zero_u = 0;
+#pragma unroll
+    for (int i = 0; i < kSyncBits; ++i) {
+        const int v = d[2 * i];
+        if ((kAdsbSync >> (35 - i)) & 1ull) one_a += v; else zero_a += v;
+        if ((kUplinkSync >> (35 - i)) & 1ull) one_u += v; else zero_u += v;
+    }
+    constexpr int kOnesA = __builtin_popcountll(kAdsbSync), kOnesU = __builtin_popcountll(kUplinkSync);
+    const int ca = int(int16_t((one_a / kOnesA + zero_a / (kSyncBits - kOnesA)) / 2));
+    const int cu = int(int16_t((one_u / kOnesU + zero_u / (kSyncBits - kOnesU)) / 2));
+    int err_a = 0, err_u = 0;
+#pragma unroll
+    for (int i = 0; i < kSyncBits; ++i) {
+        const int v = d[2 * i];
+        err_a += ((kAdsbSync >> (35 - i)) & 1ull) ? (v < ca) : (v >= ca);
+        err_u += ((kUplinkSync >> (35 - i)) & 1ull) ? (v < cu) : (v >= cu);
+    }
+    if (err_a <= 4) {
+        const uint32_t slot = atomicAdd(&ctr->n_cand, 1u);
+        if (slot < cand_cap) cand[slot] = CandC{x, int16_t(ca), 0}; else ctr->overflow = 1u;
+    }
+    if (err_u <= 4) {
+        const uint32_t slot = atomicAdd(&ctr->n_cand, 1u);
+        if (slot < cand_cap) cand[slot] = CandC{x, int16_t(cu), 1}; else ctr->overflow = 1u;
+    }
+}
+
+// ---- GF(256) / Reed-Solomon (field polynomial 0x187, first root alpha^120, libfec char-codec behaviour) ----
+struct Gf { uint8_t exp[256], log[256]; };                    // log[0] = 255 ("A0"), exp[255] = 0
+
+__device__ __forceinline__ int mod255(int x) { while (x >= 255) { x -= 255; x = (x >> 8) + (x & 255); } return x; }
+
+// In-place decode of a shortened code word of n = 255 - pad symbols with `nroots` parity symbols.
+// Returns the number of error locations found, or -1 (block untouched) if the locator has fewer roots than
+// its degree.  A location inside the virtual padding is counted but not applied, as libfec does.
+__device__ int rs_correct(const Gf &gf, uint8_t *blk, int nroots, int pad)
+{
+    constexpr int kA0 = 255, kFcr = 120, kMax = 20;
+    uint8_t syn[kMax], lam[kMax + 1], bb[kMax + 1], tt[kMax + 1], omg[kMax + 1], reg[kMax + 1], root[kMax], loc[kMax];
+    const int n = 255 - pad;
+    for (int i = 0; i < nroots; ++i) syn[i] = blk[0];
+    for (int j = 1; j < n; ++j)
+        for (int i = 0; i < nroots; ++i)
+            syn[i] = syn[i] == 0 ? blk[j] : blk[j] ^ gf.exp[mod255(gf.log[syn[i]] + kFcr + i)];
+    int any = 0;
+    for (int i = 0; i < nroots; ++i) { any |= syn[i]; syn[i] = gf.log[syn[i]]; }
+    if (!any) return 0;
+    // Berlekamp-Massey: error locator lam (polynomial form), bb in log form
+    for (int i = 1; i <= nroots; ++i) { lam[i] = 0; bb[i] = kA0; }
+    lam[0] = 1; bb[0] = 0;
+    int el = 0;
+    for (int r = 1; r <= nroots; ++r) {
+        int disc = 0;
+        for (int i = 0; i < r; ++i)
+            if (lam[i] != 0 && syn[r - i - 1] != kA0) disc ^= gf.exp[mod255(gf.log[lam[i]] + syn[r - i - 1])];
+        disc = gf.log[disc];
+        if (disc == kA0) {
+            for (int i = nroots; i > 0; --i) bb[i] = bb[i - 1];
+            bb[0] = kA0;
+        } else {
+            tt[0] = lam[0];
+            for (int i = 0; i < nroots; ++i) tt[i + 1] = bb[i] != kA0 ? lam[i + 1] ^ gf.exp[mod255(disc + bb[i])] : lam[i + 1];
+            if (2 * el <= r - 1) {
+                el = r - el;
+                for (int i = 0; i <= nroots; ++i) bb[i] = lam[i] == 0 ? kA0 : uint8_t(mod255(gf.log[lam[i]] - disc + 255));
+            } else {
+                for (int i = nroots; i > 0; --i) bb[i] = bb[i - 1];
+                bb[0] = kA0;
+            }
+            for (int i = 0; i <= nroots; ++i) lam[i] = tt[i];
+        }
+    }
+    int deg = 0;
+    for (int i = 0; i <= nroots; ++i) { lam[i] = gf.log[lam[i]]; if (lam[i] != kA0) deg = i; }
+    // Chien search
+    for (int i = 1; i <= nroots; ++i) reg[i] = lam[i];
+    int count = 0;
+    for (int i = 1, k = 0; i <= 255; ++i, k = mod255(k + 1)) {
+        int q = 1;
+        for (int j = deg; j > 0; --j)
+            if (reg[j] != kA0) { reg[j] = uint8_t(mod255(reg[j] + j)); q ^= gf.exp[reg[j]]; }
+        if (q != 0) continue;
+        root[count] = uint8_t(i); loc[count] = uint8_t(k);
+        if (++count == deg) break;
+    }
+    if (deg != count) return -1;
+    // error evaluator and Forney
+    const int dego = deg - 1;
+    for (int i = 0; i <= dego; ++i) {
+        int t = 0;
+        for (int j = i; j >= 0; --j)
+            if (syn[i - j] != kA0 && lam[j] != kA0) t ^= gf.exp[mod255(syn[i - j] + lam[j])];
+        omg[i] = gf.log[t];
+    }
+    for (int j = count - 1; j >= 0; --j) {
+        int num1 = 0, den = 0;
+        for (int i = dego; i >= 0; --i)
+            if (omg[i] != kA0) num1 ^= gf.exp[mod255(omg[i] + i * root[j])];
+        const int num2 = gf.exp[mod255(root[j] * (kFcr - 1) + 255)];
+        for (int i = min(deg, nroots - 1) & ~1; i >= 0; i -= 2)
+            if (lam[i + 1] != kA0) den ^= gf.exp[mod255(lam[i + 1] + i * root[j])];
+        if (num1 != 0 && loc[j] >= pad) blk[loc[j] - pad] ^= gf.exp[mod255(gf.log[num1] + gf.log[num2] + 255 - gf.log[den])];
+    }
+    return count;
+}
+
+__device__ __forceinline__ uint8_t slice_byte(const uint16_t *p, int center)
+{
+    uint32_t b = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) b = (b << 1) | uint32_t(phi_diff(p[2 * k], p[2 * k + 1]) > center);
+    return uint8_t(b);
+}
+
+__global__ void __launch_bounds__(64) uat_decode_kernel(const uint16_t *phi, uint64_t abs_of_index0, const CandC *cand, RecC *rec,
+                                                        uint32_t rec_cap, CountersC *ctr, const Gf *gf_g)
+{
+    __shared__ Gf gf;
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) { gf.exp[i] = gf_g->exp[i]; gf.log[i] = gf_g->log[i]; }
+    __syncthreads();
+    const uint32_t ncand = min(ctr->n_cand, 0xFFFFFFFFu);
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncand) return;
+    const CandC cd = cand[c];
+    const uint16_t *p = phi + cd.x + 2 * kSyncBits;
+    uint8_t out[kUpData + 20];
+    int rs = 0, type = 0;
+    if (!cd.uplink) {
+        for (int b = 0; b < kLongBytes; ++b) out[b] = slice_byte(p + 16 * b, cd.center);
+        int nfix = rs_correct(gf, out, 14, 207);                          // long: RS(48,34)
+        if (nfix >= 0 && nfix <= 7 && (out[0] >> 3) != 0) { type = 2; rs = nfix; }
+        else {
+            nfix = rs_correct(gf, out, 12, 225);                          // basic: RS(30,18)
+            if (nfix >= 0 && nfix <= 6 && (out[0] >> 3) == 0) { type = 1; rs = nfix; }
+            else return;
+        }
+    } else {
+        for (int blk = 0; blk < kUpBlocks; ++blk) {                       // de-interleave: byte i of block b is frame byte 6i+b
+            uint8_t *bd = &out[blk * kUpBlockData];
+            for (int i = 0; i < kUpBlockBytes; ++i) bd[i] = slice_byte(p + 16 * (i * kUpBlocks + blk), cd.center);
+            const int nfix = rs_correct(gf, bd, 20, 163);                 // RS(92,72); the next block overwrites the parity
+            if (nfix < 0 || nfix > 10) return;
+            rs += nfix;
+        }
+    }
+    const uint32_t slot = atomicAdd(&ctr->n_rec, 1u);
+    if (slot >= rec_cap) { ctr->overflow = 1u; return; }
+    RecC &r = rec[slot];
+    r.s = abs_of_index0 + cd.x;
+    for (int w = 0; w < 3; ++w) {
+        uint32_t bits = 0;
+        for (int i = 0; i < 32; ++i) {
+            const int64_t x = int64_t(cd.x) - kSigmaLead + 32 * w + i;
+            if (x >= 0) bits |= uint32_t(phi_diff(phi[x], phi[x + 1]) > 0) << i;
+        }
+        r.sigma[w] = bits;
+    }
+    r.rs_errors = int16_t(rs); r.uplink = uint8_t(cd.uplink); r.type = uint8_t(type);
+    const int len = cd.uplink ? kUpData : (type == 2 ? kLongData : kShortData);
+    for (int i = 0; i < len; ++i) r.data[i] = out[i];
+}
+
+}  // namespace
+
+struct PathC {
+    uint16_t *d_lut = nullptr;
+    Gf *d_gf = nullptr;
+    uint8_t *d_iq = nullptr;      size_t iq_cap = 0;
+    uint16_t *d_phi = nullptr;    size_t phi_cap = 0;     // [tail of the stream | new samples]
+    uint16_t *d_phi_out = nullptr; size_t phi_out_cap = 0;
+    CandC *d_cand = nullptr;      uint32_t cand_cap = 0;
+    RecC *d_rec = nullptr, *h_rec = nullptr; uint32_t rec_cap = 0;
+    CountersC *d_ctr = nullptr, *h_ctr = nullptr;
+    uint64_t abs_end = 0;         // samples received so far
+    uint32_t held = 0;            // samples kept in d_phi from earlier calls (the last `held` of the stream)
+    uint64_t eval_next = 0;       // first absolute position not yet evaluated on the device
+    // UAT978Handler state (UAT978.cpp:106-107)
+    uint64_t offset = 0;          // absolute sample of buffer[0]
+    uint64_t used = 0;            // samples in the staging buffer
+    std::vector<RecC> pending;    // decoded candidates not yet passed by the emulated scan, sorted by s
+};
+
+void pathc_free(PathC *c)
+{
+    if (!c) return;
+    cudaFree(c->d_lut); cudaFree(c->d_gf); cudaFree(c->d_iq); cudaFree(c->d_phi); cudaFree(c->d_phi_out); cudaFree(c->d_cand); cudaFree(c->d_rec);
+    cudaFree(c->d_ctr);
+    if (c->h_rec) cudaFreeHost(c->h_rec);
+    if (c->h_ctr) cudaFreeHost(c->h_ctr);
+    delete c;
+}
+
+#define CKC_(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { err = std::string(#call ": ") + cudaGetErrorString(e_); return ADSBCU_ERR_CUDA; } } while (0)
+
+static int pathc_init(PathC *&c, std::string &err)
+{
+    if (c) return ADSBCU_OK;
+    c = new PathC;
+    std::vector<uint16_t> lut(65536);
+    for (unsigned i = 0; i < 256; ++i) {                   // UAT978.cpp:76-100
+        const double dI = i - 127.5;
+        for (unsigned q = 0; q < 256; ++q) {
+            const double dQ = q - 127.5;
+            const double ang = std::atan2(dQ, dI) + 3.14159265358979323846;
+            const double scaled = std::round(32768 * ang / 3.14159265358979323846);
+            lut[i | (q << 8)] = uint16_t(scaled < 0 ? 0 : scaled > 65535 ? 65535 : scaled);
+        }
+    }
+    Gf gf;
+    int sr = 1;
+    gf.log[0] = 255; gf.exp[255] = 0;
+    for (int i = 0; i < 255; ++i) { gf.log[sr] = uint8_t(i); gf.exp[i] = uint8_t(sr); sr <<= 1; if (sr & 256) sr ^= 0x187; sr &= 255; }
+    CKC_(cudaMalloc(&c->d_lut, 65536 * 2));
+    CKC_(cudaMemcpy(c->d_lut, lut.data(), 65536 * 2, cudaMemcpyHostToDevice));
+    CKC_(cudaMalloc(&c->d_gf, sizeof(Gf)));
+    CKC_(cudaMemcpy(c->d_gf, &gf, sizeof(Gf), cudaMemcpyHostToDevice));
+    CKC_(cudaMalloc(&c->d_ctr, sizeof(CountersC)));
+    CKC_(cudaHostAlloc(&c->h_ctr, sizeof(CountersC), cudaHostAllocDefault));
+    return ADSBCU_OK;
+}
+
+void pathc_reset(PathC *c)
+{
+    if (!c) return;
+    c->abs_end = 0; c->held = 0; c->eval_next = 0; c->offset = 0; c->used = 0; c->pending.clear();
+}
+
+namespace {
+
+inline bool fuzzy(uint64_t word, uint64_t expected) { return __builtin_popcountll(word ^ expected) <= 4; }
+
+// 36-bit sync register as the reference's scan would hold it at scan bit `b` of a process_buffer() call on
+// the buffer starting at absolute sample B: the last (up to 36) bits shifted in since `fresh_from` are true
+// stream bits, older ones are whatever the register held when the scan jumped over a decoded frame.
+struct Regs { uint64_t stale0 = 0, stale1 = 0; int64_t fresh_from = 0; };
+
+inline uint32_t sigma_at(const RecC &r, int64_t x)           // x: absolute sample; must lie in the record's window
+{
+    const int64_t i = x - (int64_t(r.s) - kSigmaLead);
+    return (r.sigma[i >> 5] >> (i & 31)) & 1u;
+}
+
+}  // namespace
+
+int pathc_feed(PathC *&c, int sm_count, cudaStream_t st, const uint8_t *iq, size_t nbytes, adsbcu_uat_frame *out, size_t cap,
+               size_t *n_out, std::string &err)
+{
+    if (n_out) *n_out = 0;
+    const int rc0 = pathc_init(c, err);
+    if (rc0 != ADSBCU_OK) return rc0;
+    const size_t n = nbytes / 2;
+    if (!n) return ADSBCU_OK;
+    if (n > 0x7FFF0000ull) { err = "buffer too large"; return ADSBCU_ERR_ARG; }
+
+    // ---- device: phases of the new samples behind the carried tail, sync search, frame decode ----------
+    if (c->iq_cap < n * 2) { cudaFree(c->d_iq); c->d_iq = nullptr; c->iq_cap = 0; CKC_(cudaMalloc(&c->d_iq, n * 2 + 64)); c->iq_cap = n * 2; }
+    if (c->phi_cap < c->held + n + 128) {
+        uint16_t *np = nullptr;
+        CKC_(cudaMalloc(&np, (kTail + n + 128) * sizeof(uint16_t)));
+        if (c->held) CKC_(cudaMemcpyAsync(np, c->d_phi, c->held * sizeof(uint16_t), cudaMemcpyDeviceToDevice, st));
+        CKC_(cudaStreamSynchronize(st));
+        cudaFree(c->d_phi);
+        c->d_phi = np; c->phi_cap = kTail + n + 128;
+    }
+    const uint32_t want_cand = uint32_t(std::max<size_t>(4096, n / 256));
+    if (c->cand_cap < want_cand) {
+        cudaFree(c->d_cand); cudaFree(c->d_rec); if (c->h_rec) cudaFreeHost(c->h_rec);
+        c->d_cand = nullptr; c->d_rec = nullptr; c->h_rec = nullptr; c->cand_cap = c->rec_cap = 0;
+        CKC_(cudaMalloc(&c->d_cand, size_t(want_cand) * sizeof(CandC)));
+        CKC_(cudaMalloc(&c->d_rec, size_t(want_cand) * sizeof(RecC)));
+        CKC_(cudaHostAlloc(&c->h_rec, size_t(want_cand) * sizeof(RecC), cudaHostAllocDefault));
+        c->cand_cap = c->rec_cap = want_cand;
+    }
+    CKC_(cudaMemcpyAsync(c->d_iq, iq, n * 2, cudaMemcpyHostToDevice, st));
+    CKC_(cudaMemsetAsync(c->d_ctr, 0, sizeof(CountersC), st));
+    uat_phase_kernel<<<sm_count * 8, 256, 0, st>>>(c->d_iq, uint32_t(n), c->d_lut, c->d_phi + c->held);
+    CKC_(cudaGetLastError());
+    CKC_(cudaMemsetAsync(c->d_phi + c->held + n, 0, 128 * sizeof(uint16_t), st));
+    const uint64_t new_end = c->abs_end + n;
+    const uint64_t abs_of_index0 = c->abs_end - c->held;                   // absolute sample of d_phi[0]
+    const uint64_t eval_end = new_end >= uint64_t(kNeed) ? new_end - kNeed + 1 : 0;   // positions s with s + kNeed <= new_end
+    uint32_t nrec = 0;
+    if (eval_end > c->eval_next) {
+        const uint32_t first = uint32_t(c->eval_next - abs_of_index0), last = uint32_t(eval_end - abs_of_index0);
+        uat_sync_kernel<<<(last - first + 255) / 256, 256, 0, st>>>(c->d_phi, first, last, c->d_cand, c->cand_cap, c->d_ctr);
+        CKC_(cudaGetLastError());
+        CKC_(cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(CountersC), cudaMemcpyDeviceToHost, st));
+        CKC_(cudaStreamSynchronize(st));
+        if (c->h_ctr->overflow || c->h_ctr->n_cand > c->cand_cap) { err = "internal candidate list overflow"; return ADSBCU_ERR_OVERFLOW; }
+        const uint32_t ncand = c->h_ctr->n_cand;
+        if (ncand) {
+            uat_decode_kernel<<<(ncand + 63) / 64, 64, 0, st>>>(c->d_phi, abs_of_index0, c->d_cand, c->d_rec, c->rec_cap, c->d_ctr, c->d_gf);
+            CKC_(cudaGetLastError());
+            CKC_(cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(CountersC), cudaMemcpyDeviceToHost, st));
+            CKC_(cudaStreamSynchronize(st));
+            if (c->h_ctr->overflow) { err = "internal record list overflow"; return ADSBCU_ERR_OVERFLOW; }
+            nrec = c->h_ctr->n_rec;
+            if (nrec) {
+                CKC_(cudaMemcpyAsync(c->h_rec, c->d_rec, size_t(nrec) * sizeof(RecC), cudaMemcpyDeviceToHost, st));
+                CKC_(cudaStreamSynchronize(st));
+            }
+        }
+        c->eval_next = eval_end;
+    }
+    // keep the tail of the stream for the next call
+    {
+        const uint64_t total = c->held + n;
+        const uint32_t keep = uint32_t(std::min<uint64_t>(total, kTail));
+        if (total > keep) {
+            // ranges may overlap when n < kTail: stage through the (now free) candidate-independent iq buffer is not
+            // large enough in general, so copy in two steps via d_phi's own slack only when disjoint
+            if (total - keep >= keep) {
+                CKC_(cudaMemcpyAsync(c->d_phi, c->d_phi + (total - keep), keep * sizeof(uint16_t), cudaMemcpyDeviceToDevice, st));
+            } else {
+                uint16_t *tmp = nullptr;
+                CKC_(cudaMalloc(&tmp, keep * sizeof(uint16_t)));
+                CKC_(cudaMemcpyAsync(tmp, c->d_phi + (total - keep), keep * sizeof(uint16_t), cudaMemcpyDeviceToDevice, st));
+                CKC_(cudaMemcpyAsync(c->d_phi, tmp, keep * sizeof(uint16_t), cudaMemcpyDeviceToDevice, st));
+                CKC_(cudaStreamSynchronize(st));
+                cudaFree(tmp);
+            }
+        }
+        CKC_(cudaStreamSynchronize(st));
+        c->held = keep;
+        c->abs_end = new_end;
+    }
+    std::sort(c->h_rec, c->h_rec + nrec, [](const RecC &a, const RecC &b) { return a.s != b.s ? a.s < b.s : a.uplink < b.uplink; });
+    c->pending.insert(c->pending.end(), c->h_rec, c->h_rec + nrec);
+
+    // ---- host: replay UAT978Handler::HandleData's staging and process_buffer()'s scan ----------------------
+    size_t nout = 0;
+    bool overflow = false;
+    auto find = [&](uint64_t s, int uplink) -> const RecC * {
+        auto it = std::lower_bound(c->pending.begin(), c->pending.end(), s, [](const RecC &r, uint64_t v) { return r.s < v; });
+        for (; it != c->pending.end() && it->s == s; ++it)
+            if (it->uplink == uplink) return &*it;
+        return nullptr;
+    };
+    auto emit = [&](const RecC &r) {
+        if (nout < cap) {
+            adsbcu_uat_frame &f = out[nout];
+            std::memset(&f, 0, sizeof(f));
+            f.offset = r.s; f.rs_errors = r.rs_errors; f.updown = r.uplink ? '+' : '-';
+            f.len = uint16_t(r.uplink ? kUpData : (r.type == 2 ? kLongData : kShortData));
+            std::memcpy(f.data, r.data, f.len);
+        } else {
+            overflow = true;
+        }
+        ++nout;
+    };
+    uint64_t fed = new_end - n;                              // absolute index of the next sample HandleData copies in
+    while (fed < new_end) {
+        const uint64_t i = std::min<uint64_t>(65536, c->used + (new_end - fed));   // UAT978.cpp:52
+        fed += i - c->used;
+        const int64_t len = int64_t(i), lenbits = len / 2 - (kSyncBits + kUpBits);
+        if (lenbits <= 0) { c->used = i; continue; }          // never happens with the reference's 262144-byte buffers
+        const uint64_t B = c->offset;
+        int64_t bit = 0;                                      // the scan's loop variable
+        Regs regs;
+        // scan bits worth looking at: those from which a decoded candidate could be tried
+        auto lo = std::lower_bound(c->pending.begin(), c->pending.end(), B, [](const RecC &r, uint64_t v) { return r.s < v; });
+        std::vector<int64_t> sbs;
+        for (auto it = lo; it != c->pending.end() && it->s < B + uint64_t(2 * lenbits + 4); ++it) {
+            const int64_t rel = int64_t(it->s - B);
+            sbs.push_back(rel >> 1);
+            if ((rel >> 1) >= 1) sbs.push_back((rel >> 1) - 1);
+        }
+        std::sort(sbs.begin(), sbs.end());
+        sbs.erase(std::unique(sbs.begin(), sbs.end()), sbs.end());
+        for (const int64_t sb : sbs) {
+            const int64_t b = sb + kSyncBits - 1;             // scan bit at which startbit == sb
+            if (b < bit || b < kSyncBits || b >= lenbits) continue;
+            // any decoded candidate near 2*sb carries the sign bits the registers are made of
+            const RecC *win = nullptr;
+            for (int e = 0; e <= 3 && !win; ++e)
+                for (int up = 0; up < 2 && !win; ++up) win = find(B + uint64_t(2 * sb + e), up);
+            if (!win) continue;
+            uint64_t r0 = 0, r1 = 0;
+            const int64_t nfresh = b - regs.fresh_from + 1;
+            const int64_t ntrue = std::min<int64_t>(kSyncBits, nfresh);
+            for (int64_t k = b - ntrue + 1; k <= b; ++k) {
+                r0 = (r0 << 1) | sigma_at(*win, int64_t(B) + 2 * k);
+                r1 = (r1 << 1) | sigma_at(*win, int64_t(B) + 2 * k + 1);
+            }
+            if (ntrue < kSyncBits) {
+                const uint64_t mask = (1ull << kSyncBits) - 1;
+                r0 |= (regs.stale0 << ntrue) & mask;
+                r1 |= (regs.stale1 << ntrue) & mask;
+            }
+            bool taken = false;
+            for (int up = 0; up < 2 && !taken; ++up) {        // the ADS-B sync word is tried first, then the uplink one
+                const uint64_t word = up ? kUplinkSync : kAdsbSync;
+                const bool m0 = fuzzy(r0, word), m1 = fuzzy(r1, word);
+                if (!m0 && !m1) continue;
+                const uint64_t index = B + uint64_t(2 * sb + (m0 ? 0 : 1));
+                const RecC *f0 = find(index, up), *f1 = find(index + 1, up);
+                const int rs0 = f0 ? f0->rs_errors : 9999, rs1 = f1 ? f1->rs_errors : 9999;
+                const RecC *pick = (f0 && rs0 <= rs1) ? f0 : (f1 && rs1 <= rs0) ? f1 : nullptr;
+                if (!pick) continue;
+                emit(*pick);
+                const int skip = kSyncBits + (up ? kUpBits : (pick->type == 2 ? kLongBytes * 8 : kShortBytes * 8));
+                bit = sb + skip + 1;                          // bit = startbit + skip; continue -> ++bit
+                regs.stale0 = r0; regs.stale1 = r1; regs.fresh_from = bit;
+                taken = true;
+            }
+        }
+        if (bit < lenbits) bit = lenbits;                     // the loop runs to lenbits unless a skip carried it past
+        const int64_t done = (bit - kSyncBits) * 2;
+        c->offset += uint64_t(done);
+        c->used = uint64_t(len - done);
+        // records before the new buffer start can never be tried again
+        auto cut = std::lower_bound(c->pending.begin(), c->pending.end(), c->offset, [](const RecC &r, uint64_t v) { return r.s < v; });
+        c->pending.erase(c->pending.begin(), cut);
+    }
+    if (n_out) *n_out = nout;
+    if (overflow) { err = "out[] too small for the decoded frames"; return ADSBCU_ERR_OVERFLOW; }
+    return ADSBCU_OK;
+}
+
+// stage-level: the phase table mapping of UAT978.cpp:52 on `n` samples
+int pathc_phase(PathC *&c, int sm_count, cudaStream_t st, const uint8_t *iq, size_t n, uint16_t *phi_out, std::string &err)
+{
+    const int rc0 = pathc_init(c, err);
+    if (rc0 != ADSBCU_OK) return rc0;
+    if (!n) return ADSBCU_OK;
+    if (c->iq_cap < n * 2) { cudaFree(c->d_iq); c->d_iq = nullptr; c->iq_cap = 0; CKC_(cudaMalloc(&c->d_iq, n * 2 + 64)); c->iq_cap = n * 2; }
+    if (c->phi_out_cap < n) { cudaFree(c->d_phi_out); c->d_phi_out = nullptr; c->phi_out_cap = 0; CKC_(cudaMalloc(&c->d_phi_out, n * 2 + 64)); c->phi_out_cap = n; }
+    CKC_(cudaMemcpyAsync(c->d_iq, iq, n * 2, cudaMemcpyHostToDevice, st));
+    uat_phase_kernel<<<sm_count * 8, 256, 0, st>>>(c->d_iq, uint32_t(n), c->d_lut, c->d_phi_out);
+    CKC_(cudaGetLastError());
+    CKC_(cudaMemcpyAsync(phi_out, c->d_phi_out, n * 2, cudaMemcpyDeviceToHost, st));
+    CKC_(cudaStreamSynchronize(st));
+    return ADSBCU_OK;
+}
+
+}  // namespace adsbcu
