@@ -1,0 +1,159 @@
+// Host-side mirror of the reference's handler interface for the three hot paths.
+//
+// The reference's capture thread hands every ring-buffer slot to
+//     RTLSDR::IDataHandler::HandleData(std::span<uint8_t const> const&)        (RTLSDR.hpp:39-49, :518-539)
+// and the handlers (ADSB1090Handler, UAT978Handler) demodulate on the calling thread and push each
+// frame to the next layer.  The classes below keep that shape -- same method names, same argument
+// meaning, one consumer thread per handler, sink called synchronously in stream order -- and do
+// the demodulation through the C ABI of include/adsbcu.h instead of the CPU loops:
+//
+//   ModeS2400Handler   flightaware demodulate2400 at 2.4 MS/s (dump1090/demod_2400.c:99-444); the
+//                      sink sees what useModesMessage() sees (mode_s.c:2274)
+//   ADSB1090Handler    libadsb's own 2.0 MS/s demodulator (ADSB1090.cpp:158-175, :741-959); the sink
+//                      sees what UseModesMessage(mm) sees with mm.crcok set (ADSB1090.cpp:937,968-971)
+//   UAT978Handler      UAT978.cpp:43-60 + dump978 process_buffer; the sink has the signature of
+//                      dump_raw_message(char updown, uint8_t* data, int len, int rs_errors)
+//                      (uat2json-wrapper.cpp:14)
+//
+// Inside libadsb, define ADSBCU_WITH_LIBADSB before including this file (after RTLSDR.hpp): the
+// classes then derive from RTLSDR::IDataHandler itself and can be passed to RTLSDR::Start().
+// Errors: HandleData is void in the reference and only throws (RTLSDR.hpp:495); a failing ABI call
+// throws std::runtime_error carrying adsbcu_last_error().  There is no CPU fallback.
+#pragma once
+
+#include "../../include/adsbcu.h"
+
+#include <cstdint>
+#include <functional>
+#include <span>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace adsbcu_host {
+
+#ifdef ADSBCU_WITH_LIBADSB
+using IDataHandler = RTLSDR::IDataHandler;
+#else
+struct IDataHandler {
+    virtual ~IDataHandler() = default;
+    virtual void HandleData(std::span<uint8_t const> const &data) = 0;
+    virtual void OnDeviceStatusChanged(bool available) = 0;
+};
+#endif
+
+class Engine {
+public:
+    explicit Engine(adsbcu_config cfg)
+    {
+        cfg.struct_size = sizeof(cfg);
+        const int rc = adsbcu_create(&cfg, &h_);
+        if (rc != ADSBCU_OK) throw std::runtime_error(std::string("adsbcu_create: ") + adsbcu_last_error(nullptr));
+    }
+    ~Engine() { adsbcu_destroy(h_); }
+    Engine(Engine const &) = delete;
+    Engine &operator=(Engine const &) = delete;
+    adsbcu_handle *get() const { return h_; }
+    void check(int rc, char const *what) const
+    {
+        if (rc != ADSBCU_OK) throw std::runtime_error(std::string(what) + ": " + adsbcu_last_error(h_));
+    }
+
+private:
+    adsbcu_handle *h_ = nullptr;
+};
+
+inline adsbcu_config make_config(int device, int nfix_crc, int fix_df, uint32_t max_feed_samples)
+{
+    adsbcu_config c{};
+    c.struct_size = sizeof(c);
+    c.device = device;
+    c.nfix_crc = nfix_crc;
+    c.fix_df = fix_df;
+    c.max_feed_samples = max_feed_samples;
+    return c;
+}
+
+// ---- Path A -------------------------------------------------------------------------------------
+class ModeS2400Handler : public IDataHandler {
+public:
+    using Sink = std::function<void(adsbcu_msg const &)>;   // == useModesMessage(struct modesMessage*)
+    ModeS2400Handler(Sink sink, int nfix_crc = 0, int fix_df = 1, int device = 0, uint32_t max_feed_samples = 1u << 24)
+        : eng_(make_config(device, nfix_crc, fix_df, max_feed_samples)), sink_(std::move(sink)), out_(1u << 16)
+    {
+    }
+    void HandleData(std::span<uint8_t const> const &data) override
+    {
+        size_t n = 0;
+        const size_t cap = out_.size();
+        int rc = adsbcu_1090_feed(eng_.get(), data.data(), data.size() / 2, out_.data(), cap, &n);
+        if (rc == ADSBCU_ERR_OVERFLOW && n > cap) {
+            // the stream state already advanced past this buffer: the messages beyond cap are lost, like a
+            // dropped mag_buf in the reference (fifo.c:148-152); grow so that it cannot happen twice
+            out_.resize(n + n / 2);
+            rc = ADSBCU_OK;
+            n = cap;
+        }
+        eng_.check(rc, "adsbcu_1090_feed");
+        for (size_t k = 0; k < n; ++k) sink_(out_[k]);
+    }
+    void OnDeviceStatusChanged(bool) override {}
+    void Reset(bool clear_filter) { eng_.check(adsbcu_1090_reset(eng_.get(), clear_filter ? 1 : 0), "adsbcu_1090_reset"); }
+    adsbcu_stats Stats() const
+    {
+        adsbcu_stats s{};
+        adsbcu_get_stats(eng_.get(), &s);
+        return s;
+    }
+
+private:
+    Engine eng_;
+    Sink sink_;
+    std::vector<adsbcu_msg> out_;
+};
+
+// ---- Path B -------------------------------------------------------------------------------------
+class ADSB1090Handler : public IDataHandler {
+public:
+    using Sink = std::function<void(adsbcu_msg_b const &)>;   // == UseModesMessage(Message const&), crcok only
+    explicit ADSB1090Handler(Sink sink, int device = 0)
+        : eng_(make_config(device, 0, 1, 1u << 22)), sink_(std::move(sink)), out_(1u << 16)
+    {
+    }
+    void HandleData(std::span<uint8_t const> const &data) override
+    {
+        size_t n = 0;
+        eng_.check(adsbcu_1090b_feed(eng_.get(), data.data(), data.size(), out_.data(), out_.size(), &n), "adsbcu_1090b_feed");
+        for (size_t k = 0; k < n; ++k) sink_(out_[k]);
+    }
+    void OnDeviceStatusChanged(bool) override {}
+
+private:
+    Engine eng_;
+    Sink sink_;
+    std::vector<adsbcu_msg_b> out_;
+};
+
+// ---- Path C -------------------------------------------------------------------------------------
+class UAT978Handler : public IDataHandler {
+public:
+    using Sink = std::function<void(char updown, uint8_t *data, int len, int rs_errors)>;   // == dump_raw_message
+    explicit UAT978Handler(Sink sink, int device = 0)
+        : eng_(make_config(device, 0, 1, 1u << 22)), sink_(std::move(sink)), out_(1u << 12)
+    {
+    }
+    void HandleData(std::span<uint8_t const> const &data) override
+    {
+        size_t n = 0;
+        eng_.check(adsbcu_978_feed(eng_.get(), data.data(), data.size(), out_.data(), out_.size(), &n), "adsbcu_978_feed");
+        for (size_t k = 0; k < n; ++k) sink_(char(out_[k].updown), out_[k].data, int(out_[k].len), int(out_[k].rs_errors));
+    }
+    void OnDeviceStatusChanged(bool) override {}
+
+private:
+    Engine eng_;
+    Sink sink_;
+    std::vector<adsbcu_uat_frame> out_;
+};
+
+}  // namespace adsbcu_host

@@ -1,0 +1,104 @@
+// File replay through the handler shim: the analogue of `dump1090 --ifile X --raw --mlat`
+// (sdr_ifile.c:178-245 -> demodulate2400 -> displayModesMessage, mode_s.c:1897-1903), of
+// tests/test_1090.cpp's TestEmbedded loop for libadsb's own handler, and of UAT978Handler fed from
+// a file.  Output formats:
+//   path a : "@<12 hex 12 MHz timestamp><hex msg>;"  one line per message (net_io.c:529-545), and with
+//            --beast FILE the Beast binary stream of writeBeastMessage (net_io.c:440-487) on the verbatim bytes
+//   path b : "*<hex msg>;"
+//   path uat: "<updown><hex payload>;rs=<n>;"  (dump978 raw line format)
+// usage: adsbcu_replay --path a|b|uat [--fix|--fix-2bit] [--no-fix-df] [--block BYTES] [--beast FILE] capture.bin
+#include "adsbcu_handlers.hpp"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+
+using namespace adsbcu_host;
+
+static void beast_put(std::vector<uint8_t> &o, uint8_t ch)
+{
+    o.push_back(ch);
+    if (ch == 0x1A) o.push_back(ch);
+}
+
+// writeBeastMessage (net_io.c:440-487)
+static void beast_message(std::vector<uint8_t> &o, uint64_t ts, double signal, const uint8_t *msg, int len)
+{
+    o.push_back(0x1A);
+    o.push_back(len == 7 ? '2' : '3');
+    for (int s = 40; s >= 0; s -= 8) beast_put(o, uint8_t(ts >> s));
+    int sig = int(std::round(std::sqrt(signal) * 255));
+    if (signal > 0 && sig < 1) sig = 1;
+    if (sig > 255) sig = 255;
+    beast_put(o, uint8_t(sig));
+    for (int j = 0; j < len; ++j) beast_put(o, msg[j]);
+}
+
+int main(int argc, char **argv)
+{
+    std::string path = "a", file, beast_file;
+    int nfix = 0, fix_df = 1;
+    size_t block = 262144;   // RTLSDR::BufferLength (RTLSDR.hpp:55)
+    for (int i = 1; i < argc; ++i) {
+        const std::string a = argv[i];
+        if (a == "--path" && i + 1 < argc) path = argv[++i];
+        else if (a == "--fix") nfix = 1;
+        else if (a == "--fix-2bit") nfix = 2;
+        else if (a == "--no-fix-df") fix_df = 0;
+        else if (a == "--block" && i + 1 < argc) block = std::strtoull(argv[++i], nullptr, 0);
+        else if (a == "--beast" && i + 1 < argc) beast_file = argv[++i];
+        else file = a;
+    }
+    if (file.empty() || block < 2) { std::fprintf(stderr, "usage: adsbcu_replay --path a|b|uat [options] capture.bin\n"); return 2; }
+    std::FILE *fp = std::fopen(file.c_str(), "rb");
+    if (!fp) { std::perror(file.c_str()); return 2; }
+    std::vector<uint8_t> beast;
+    size_t count = 0;
+    try {
+        std::unique_ptr<IDataHandler> h;
+        if (path == "a") {
+            h = std::make_unique<ModeS2400Handler>([&](adsbcu_msg const &m) {
+                std::printf("@%012llX", (unsigned long long) m.timestamp);
+                for (int j = 0; j < m.msgbits / 8; ++j) std::printf("%02x", m.msg[j]);
+                std::printf(";\n");
+                if (!beast_file.empty()) beast_message(beast, m.timestamp, m.signal_level, m.verbatim, m.msgbits / 8);
+                ++count;
+            }, nfix, fix_df, 0, uint32_t(std::max<size_t>(block / 2, 1u << 20)));
+        } else if (path == "b") {
+            h = std::make_unique<ADSB1090Handler>([&](adsbcu_msg_b const &m) {
+                std::printf("*");
+                for (int j = 0; j < m.msgbits / 8; ++j) std::printf("%02x", m.msg[j]);
+                std::printf(";\n");
+                ++count;
+            });
+        } else {
+            h = std::make_unique<UAT978Handler>([&](char updown, uint8_t *d, int len, int rs) {
+                std::printf("%c", updown);
+                for (int j = 0; j < len; ++j) std::printf("%02x", d[j]);
+                std::printf(";rs=%d;\n", rs);
+                ++count;
+            });
+        }
+        std::vector<uint8_t> buf(block & ~size_t(1));
+        for (;;) {
+            const size_t got = std::fread(buf.data(), 1, buf.size(), fp);
+            if (got < 2) break;
+            h->HandleData(std::span<uint8_t const>(buf.data(), got & ~size_t(1)));
+            if (got < buf.size()) break;
+        }
+    } catch (std::exception const &e) {
+        std::fprintf(stderr, "adsbcu_replay: %s\n", e.what());
+        std::fclose(fp);
+        return 3;
+    }
+    std::fclose(fp);
+    if (!beast_file.empty()) {
+        std::FILE *bf = std::fopen(beast_file.c_str(), "wb");
+        if (!bf) { std::perror(beast_file.c_str()); return 2; }
+        std::fwrite(beast.data(), 1, beast.size(), bf);
+        std::fclose(bf);
+    }
+    std::fprintf(stderr, "%zu frames\n", count);
+    return 0;
+}
