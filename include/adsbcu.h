@@ -124,6 +124,56 @@ int adsbcu_1090_filter_test(adsbcu_handle *h, uint32_t addr);   /* 1 = present, 
 
 int adsbcu_get_stats(const adsbcu_handle *h, adsbcu_stats *out);
 
+/* ---- Path A on a capture sharded over several GPUs -------------------------------------------------
+ * demodulate2400() is sequential in three places only: the skip after an accepted message
+ * (demod_2400.c:410-419,432-443), the ICAO filter (mode_s.c:370-446,781-788) and best-of-five-phases
+ * (demod_2400.c:336).  The entry points below split the path there: every shard produces state-free
+ * candidates on its own GPU, one handle replays the sequential rules over the merged candidates, so
+ * the message set does not depend on the number of shards.  Per window of the capture:
+ *
+ *   every shard:  adsbcu_1090_seek -> adsbcu_1090_scan_candidates -> adsbcu_1090_known_export
+ *   exchange   :  OR of the exported sets (host; a few MiB)   -> adsbcu_1090_known_import on every shard
+ *   every shard:  adsbcu_1090_revive          (candidates that only became possible through another shard's addresses)
+ *   one handle :  adsbcu_1090_resolve(candidates of all shards, ascending (pos, phase))
+ */
+#pragma pack(push, 1)
+typedef struct adsbcu_cand {
+    uint64_t pos;              /* start position: sample index in the capture (the padded mag_buf coordinate) */
+    uint8_t  phase;            /* try_phase 4..8 */
+    uint8_t  kind;             /* state-independent class; with the filter state it gives score_rank */
+    int8_t   corrections;
+    uint8_t  msgtype;
+    uint8_t  verbatim[14];
+    uint8_t  msg[14];
+    uint32_t crc;
+    uint32_t addr;
+    uint32_t test_key;         /* argument of icaoFilterTest for this candidate */
+    uint32_t add_key;          /* argument of icaoFilterAdd if accepted, 0xFFFFFFFF: none */
+    uint64_t sum_sq;           /* sum of squared magnitudes over the signal window */
+} adsbcu_cand;
+#pragma pack(pop)
+#define ADSBCU_KNOWN_WORDS (1u << 20)   /* 2 x 2^24 bits: addresses that may enter the filter [ICAO | DF18 NT] */
+
+/* Position the stream: the next sample fed is sample `stream_pos` of the capture.  prev_iq (HOST)
+ * holds the nprev <= 326 samples just before it (fewer only at the capture start, where the
+ * reference's first overlap is zeros, fifo.c:45). */
+int adsbcu_1090_seek(adsbcu_handle *h, uint64_t stream_pos, const uint8_t *prev_iq, size_t nprev);
+/* Scan nsamples <= max_feed_samples (HOST memory, or device memory if on_device != 0) and return the
+ * candidates in ascending (pos, phase) order.  Touches neither the ICAO filter nor the skip state.
+ * A device buffer must stay valid until adsbcu_1090_revive has returned. */
+int adsbcu_1090_scan_candidates(adsbcu_handle *h, const uint8_t *iq, size_t nsamples, int on_device,
+                                adsbcu_cand *out, size_t cap, size_t *n_out);
+int adsbcu_1090_known_export(adsbcu_handle *h, uint32_t *words /* [ADSBCU_KNOWN_WORDS] */);
+int adsbcu_1090_known_import(adsbcu_handle *h, const uint32_t *words);   /* OR into this handle's set */
+/* Candidates of the last scan that were dropped only because their address was not in the local set
+ * and is in the set now; ascending (pos, phase).  The list is consumed. */
+int adsbcu_1090_revive(adsbcu_handle *h, adsbcu_cand *out, size_t cap, size_t *n_out);
+/* The ordered pass of demodulate2400 over candidates in ascending (pos, phase) order: continues this
+ * handle's ICAO filter and skip state.  Works on a handle created with cfg.device = -1 (a merge-only
+ * handle: no GPU needed, every scan/feed entry point then returns ADSBCU_ERR_NO_DEVICE). */
+int adsbcu_1090_resolve(adsbcu_handle *h, const adsbcu_cand *cands, size_t n,
+                        adsbcu_msg *out, size_t cap, size_t *n_out);
+
 /* ---- Path B: the 1090 MHz demodulator libadsb itself compiles (2.0 MS/s) --------------------
  * Replaces the body of ADSB1090Handler::HandleData (reference ADSB1090.cpp:158-175) down to the
  * point where the reference calls UseModesMessage() with mm.crcok set (ADSB1090.cpp:741-959,

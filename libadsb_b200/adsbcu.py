@@ -24,10 +24,17 @@ UAT_DTYPE = np.dtype([("offset", "<u8"), ("rs_errors", "<i2"), ("len", "<u2"), (
                       ("data", "u1", 432)])
 assert UAT_DTYPE.itemsize == 448
 
+CAND_DTYPE = np.dtype([("pos", "<u8"), ("phase", "u1"), ("kind", "u1"), ("corrections", "i1"), ("msgtype", "u1"),
+                       ("verbatim", "u1", 14), ("msg", "u1", 14), ("crc", "<u4"), ("addr", "<u4"), ("test_key", "<u4"),
+                       ("add_key", "<u4"), ("sum_sq", "<u8")])
+assert CAND_DTYPE.itemsize == 64
+KNOWN_WORDS = 1 << 20
+
 EXPORTS = ["adsbcu_abi_version", "adsbcu_last_error", "adsbcu_create", "adsbcu_destroy", "adsbcu_1090_reset",
            "adsbcu_1090_feed", "adsbcu_1090_feed_device", "adsbcu_1090_magnitude", "adsbcu_1090_filter_add",
            "adsbcu_1090_filter_test", "adsbcu_get_stats", "adsbcu_1090b_feed", "adsbcu_1090b_reset",
-           "adsbcu_978_feed", "adsbcu_978_reset", "adsbcu_978_phase"]
+           "adsbcu_978_feed", "adsbcu_978_reset", "adsbcu_978_phase", "adsbcu_1090_seek", "adsbcu_1090_scan_candidates",
+           "adsbcu_1090_known_export", "adsbcu_1090_known_import", "adsbcu_1090_revive", "adsbcu_1090_resolve"]
 
 
 class Config(C.Structure):
@@ -72,6 +79,13 @@ def load():
         L.adsbcu_978_feed.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.adsbcu_978_reset.argtypes = [C.c_void_p]
         L.adsbcu_978_phase.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.adsbcu_1090_seek.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_size_t]
+        L.adsbcu_1090_scan_candidates.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t,
+                                                  C.POINTER(C.c_size_t)]
+        L.adsbcu_1090_known_export.argtypes = [C.c_void_p, C.c_void_p]
+        L.adsbcu_1090_known_import.argtypes = [C.c_void_p, C.c_void_p]
+        L.adsbcu_1090_revive.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.adsbcu_1090_resolve.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         _lib = L
     return _lib
 
@@ -156,6 +170,46 @@ class Demod1090:
         out = np.zeros(iq.size // 2, dtype=np.uint16)
         self._check(load().adsbcu_978_phase(self.h, iq.ctypes.data, iq.size // 2, out.ctypes.data))
         return out
+
+    # ---- sharded captures (include/adsbcu.h, "Path A on a capture sharded over several GPUs") ----
+    def seek(self, stream_pos: int, prev_iq: np.ndarray | None = None):
+        prev = np.ascontiguousarray(prev_iq if prev_iq is not None else np.zeros(0, np.uint8), dtype=np.uint8)
+        self._check(load().adsbcu_1090_seek(self.h, stream_pos, prev.ctypes.data if prev.size else None, prev.size // 2))
+
+    def scan_candidates(self, iq, nsamples: int | None = None, cap: int | None = None) -> np.ndarray:
+        """iq: host uint8 array, or an int device pointer (then nsamples is required)."""
+        if isinstance(iq, int):
+            ptr, n, on_dev = iq, int(nsamples), 1
+        else:
+            iq = np.ascontiguousarray(iq, dtype=np.uint8)
+            ptr, n, on_dev = iq.ctypes.data, iq.size // 2, 0
+        out = np.zeros(cap if cap is not None else max(4096, n // 64), dtype=CAND_DTYPE)
+        got = C.c_size_t(0)
+        self._check(load().adsbcu_1090_scan_candidates(self.h, C.c_void_p(ptr), n, on_dev, out.ctypes.data, len(out), C.byref(got)))
+        return out[:got.value]
+
+    def known_export(self) -> np.ndarray:
+        w = np.zeros(KNOWN_WORDS, dtype=np.uint32)
+        self._check(load().adsbcu_1090_known_export(self.h, w.ctypes.data))
+        return w
+
+    def known_import(self, words: np.ndarray):
+        w = np.ascontiguousarray(words, dtype=np.uint32)
+        assert w.size == KNOWN_WORDS
+        self._check(load().adsbcu_1090_known_import(self.h, w.ctypes.data))
+
+    def revive(self, cap: int = 1 << 16) -> np.ndarray:
+        out = np.zeros(cap, dtype=CAND_DTYPE)
+        got = C.c_size_t(0)
+        self._check(load().adsbcu_1090_revive(self.h, out.ctypes.data, cap, C.byref(got)))
+        return out[:got.value]
+
+    def resolve(self, cands: np.ndarray, cap: int | None = None) -> np.ndarray:
+        cands = np.ascontiguousarray(cands, dtype=CAND_DTYPE)
+        out = np.zeros(cap if cap is not None else max(16, len(cands)), dtype=MSG_DTYPE)
+        got = C.c_size_t(0)
+        self._check(load().adsbcu_1090_resolve(self.h, cands.ctypes.data, len(cands), out.ctypes.data, len(out), C.byref(got)))
+        return out[:got.value]
 
     def filter_add(self, addr): self._check(load().adsbcu_1090_filter_add(self.h, addr))
     def filter_test(self, addr): return bool(load().adsbcu_1090_filter_test(self.h, addr))

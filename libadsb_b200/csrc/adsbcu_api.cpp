@@ -115,6 +115,16 @@ struct adsbcu_handle {
     adsbcu_stats stats{};
     PathB *pathb = nullptr;
     PathC *pathc = nullptr;
+
+    // sharded captures (adsbcu_1090_scan_candidates / _revive)
+    bool host_only = false;           // cfg.device == -1: merge-only handle, no CUDA at all
+    uint16_t *d_carry_prev = nullptr; // the carry the last scan started from (revive re-slices with it)
+    PhaseRec *d_deferred = nullptr;
+    uint32_t *d_n_deferred = nullptr, *d_known_tmp = nullptr;
+    uint32_t deferred_cap = 0;
+    const uint8_t *last_iq = nullptr; // device samples of the last candidate scan
+    uint32_t last_n = 0;
+    uint64_t last_base = 0;
 };
 
 namespace {
@@ -131,7 +141,9 @@ bool cuda_ok(adsbcu_handle *h, cudaError_t e, const char *what)
 
 void free_all(adsbcu_handle *h)
 {
+    if (h->host_only) return;
     cudaSetDevice(h->device);
+    cudaFree(h->d_carry_prev); cudaFree(h->d_deferred); cudaFree(h->d_n_deferred); cudaFree(h->d_known_tmp);
     if (h->stream) cudaStreamSynchronize(h->stream);
     pathb_free(h->pathb);
     h->pathb = nullptr;
@@ -158,14 +170,32 @@ struct Sink {
     adsbcu_msg *out;
     size_t cap, n;
     bool overflow;
+    adsbcu_cand *cands = nullptr;     // candidate mode: records are copied out instead of resolved
 };
 
-void resolve(adsbcu_handle *h, const FullRec *recs, size_t nrec, uint64_t feed_base, Sink &sink)
+static_assert(sizeof(adsbcu_cand) == 64, "adsbcu_cand layout");
+
+void copy_candidates(const FullRec *recs, size_t nrec, uint64_t feed_base, Sink &sink)
+{
+    for (size_t i = 0; i < nrec; ++i, ++sink.n) {
+        if (sink.n >= sink.cap) { sink.overflow = true; continue; }
+        const FullRec &r = recs[i];
+        adsbcu_cand &c = sink.cands[sink.n];
+        c.pos = feed_base + r.pos;
+        c.phase = r.phase; c.kind = r.kind; c.corrections = r.corrections; c.msgtype = r.msgtype;
+        std::memcpy(c.verbatim, r.verbatim, 14);
+        std::memcpy(c.msg, r.msg, 14);
+        c.crc = r.crc; c.addr = r.addr; c.test_key = r.test_key; c.add_key = r.add_key; c.sum_sq = r.sum_sq;
+    }
+}
+
+template <class Rec>
+void resolve(adsbcu_handle *h, const Rec *recs, size_t nrec, uint64_t feed_base, Sink &sink)
 {
     const uint64_t block = h->cfg.block_samples;
     size_t i = 0;
     while (i < nrec) {
-        const uint32_t pos = recs[i].pos;
+        const auto pos = recs[i].pos;
         const uint64_t a = feed_base + pos;
         size_t e = i + 1;
         while (e < nrec && recs[e].pos == pos) ++e;
@@ -177,18 +207,18 @@ void resolve(adsbcu_handle *h, const FullRec *recs, size_t nrec, uint64_t feed_b
         }
 
         int best = 0;                       // SR_NOT_SET
-        const FullRec *bp = nullptr;
+        const Rec *bp = nullptr;
         uint32_t last_key = kUnchecked;
         bool last_known = false;
         for (size_t k = i; k < e; ++k) {    // phases ascending; strict > keeps the lowest phase on ties
-            if (recs[k].test_key != last_key) { last_key = recs[k].test_key; last_known = h->filter.test(last_key); }
+            if (const uint32_t key = recs[k].test_key; key != last_key) { last_key = key; last_known = h->filter.test(key); }
             const int sc = rank_of(recs[k].kind, last_known);
             if (sc > best) { best = sc; bp = &recs[k]; }
         }
         i = e;
         if (best < kAcceptThreshold) continue;
 
-        const FullRec &r = *bp;
+        const Rec &r = *bp;
         if (sink.n < sink.cap) {
             adsbcu_msg &m = sink.out[sink.n];
             std::memset(&m, 0, sizeof(m));
@@ -205,14 +235,15 @@ void resolve(adsbcu_handle *h, const FullRec *recs, size_t nrec, uint64_t feed_b
             m.score = uint8_t(best);
             m.crc = r.crc;
             m.addr = r.addr;
+            const uint64_t sum_sq = r.sum_sq;      // (packed field: copy before use)
             const int msglen = (r.verbatim[0] & 0x80) ? 112 : 56;
             const int siglen = msglen * 12 / 5;
-            m.signal_level = (double(r.sum_sq) / 65535.0 / 65535.0) / siglen;
+            m.signal_level = (double(sum_sq) / 65535.0 / 65535.0) / siglen;
         } else {
             sink.overflow = true;
         }
         ++sink.n;
-        if (r.add_key != kUnchecked) h->filter.add(r.add_key);
+        if (const uint32_t add_key = r.add_key; add_key != kUnchecked) h->filter.add(add_key);
 
         // skip rule (demod_2400.c:410-419, :432-443): remember where this message ends
         h->has_last = true;
@@ -252,6 +283,7 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
         a.seg_count = s.d_seg_count;
         a.full = s.d_full; a.full_cap = h->full_cap;
         a.ctr = s.d_ctr;
+        if (sink.cands) { a.deferred = h->d_deferred; a.deferred_cap = h->deferred_cap; a.n_deferred = h->d_n_deferred; }
         if (iq_host) {
             CK(cudaMemcpyAsync(h->d_iq + 2 * size_t(a.pos_begin), iq_host + 2 * size_t(a.pos_begin),
                                2 * size_t(a.pos_end - a.pos_begin), cudaMemcpyHostToDevice, h->copy_stream));
@@ -279,7 +311,8 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
             return ADSBCU_ERR_OVERFLOW;
         }
         const auto t0 = std::chrono::steady_clock::now();
-        resolve(h, s.h_full, k.n_full, h->stream_pos, sink);
+        if (sink.cands) copy_candidates(s.h_full, k.n_full, h->stream_pos, sink);
+        else resolve(h, s.h_full, k.n_full, h->stream_pos, sink);
         const auto t1 = std::chrono::steady_clock::now();
         float ms = 0.f;
         st.preambles += k.preambles; st.phase_records += k.n_cand; st.resolved_records += k.n_full;
@@ -304,6 +337,7 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
         ++retired;
     }
     if (rc != ADSBCU_OK) { cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->copy_stream); return rc; }
+    if (sink.cands) CK(cudaMemcpyAsync(h->d_carry_prev, h->d_carry, kOverlap * sizeof(uint16_t), cudaMemcpyDeviceToDevice, h->stream));
     CK(launch_carry(d_iq, n, h->d_carry, h->d_tab, h->stream));
     st.scan_launches += 1;
     CK(cudaStreamSynchronize(h->stream));
@@ -358,6 +392,13 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
     if (!c.max_feed_samples) c.max_feed_samples = 1u << 24;
     if (c.block_samples < 1024) { g_create_error = "block_samples too small"; return ADSBCU_ERR_ARG; }
 
+    if (c.device == -1) {              // merge-only handle: ICAO filter + skip state for adsbcu_1090_resolve, no CUDA
+        adsbcu_handle *m = new (std::nothrow) adsbcu_handle;
+        if (!m) return ADSBCU_ERR_NOMEM;
+        m->cfg = c; m->device = -1; m->host_only = true;
+        *out = m;
+        return ADSBCU_OK;
+    }
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || c.device < 0 || c.device >= ndev) {
         cudaGetLastError();
@@ -428,9 +469,16 @@ void adsbcu_destroy(adsbcu_handle *h)
     delete h;
 }
 
+#define NEED_DEVICE(h) do { if ((h)->host_only) { (h)->error = "merge-only handle (device = -1): no GPU work possible"; return ADSBCU_ERR_NO_DEVICE; } } while (0)
+
 int adsbcu_1090_reset(adsbcu_handle *h, int clear_filter)
 {
     if (!h) return ADSBCU_ERR_ARG;
+    if (h->host_only) {
+        if (clear_filter) h->filter.clear();
+        h->stream_pos = 0; h->has_last = false; h->last_a = h->last_lme = 0;
+        return ADSBCU_OK;
+    }
     CK(cudaSetDevice(h->device));
     CK(cudaMemsetAsync(h->d_carry, 0, kOverlap * sizeof(uint16_t), h->stream));
     if (clear_filter) {
@@ -449,6 +497,7 @@ int adsbcu_1090_feed_device(adsbcu_handle *h, const uint8_t *iq_dev, size_t nsam
 {
     if (!h) return ADSBCU_ERR_ARG;
     if (n_out) *n_out = 0;
+    NEED_DEVICE(h);
     if ((!iq_dev && nsamples) || (!out && cap) || (reinterpret_cast<uintptr_t>(iq_dev) & 15u)) {
         h->error = "bad argument (null or misaligned pointer)";
         return ADSBCU_ERR_ARG;
@@ -460,6 +509,7 @@ int adsbcu_1090_feed(adsbcu_handle *h, const uint8_t *iq, size_t nsamples, adsbc
 {
     if (!h) return ADSBCU_ERR_ARG;
     if (n_out) *n_out = 0;
+    NEED_DEVICE(h);
     if ((!iq && nsamples) || (!out && cap)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
     return feed_common(h, iq, false, nsamples, out, cap, n_out);
 }
@@ -467,6 +517,7 @@ int adsbcu_1090_feed(adsbcu_handle *h, const uint8_t *iq, size_t nsamples, adsbc
 int adsbcu_1090_magnitude(adsbcu_handle *h, const uint8_t *iq, size_t nsamples, uint16_t *mag_out)
 {
     if (!h || (!iq && nsamples) || (!mag_out && nsamples)) return ADSBCU_ERR_ARG;
+    NEED_DEVICE(h);
     if (nsamples > h->cfg.max_feed_samples) { h->error = "nsamples exceeds max_feed_samples"; return ADSBCU_ERR_ARG; }
     if (!nsamples) return ADSBCU_OK;
     CK(cudaSetDevice(h->device));
@@ -486,6 +537,7 @@ int adsbcu_1090_filter_add(adsbcu_handle *h, uint32_t addr)
 {
     if (!h) return ADSBCU_ERR_ARG;
     h->filter.add(addr);
+    if (h->host_only) return ADSBCU_OK;
     // keep the device-side superset consistent: queries use the 24-bit address (+ NT table bit)
     if (!(addr & kNonIcao)) {
         const uint32_t bi = (addr & 0xFFFFFFu) | ((addr & kNtFlag) ? (1u << 24) : 0u);
@@ -508,6 +560,7 @@ int adsbcu_1090b_feed(adsbcu_handle *h, const uint8_t *iq, size_t nbytes, adsbcu
 {
     if (!h) return ADSBCU_ERR_ARG;
     if (n_out) *n_out = 0;
+    NEED_DEVICE(h);
     if ((!iq && nbytes) || (!out && cap)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
     CK(cudaSetDevice(h->device));
     return pathb_feed(h->pathb, h->d_tab, h->sm_count, h->stream, iq, nbytes, out, cap, n_out, h->error);
@@ -516,6 +569,7 @@ int adsbcu_1090b_feed(adsbcu_handle *h, const uint8_t *iq, size_t nbytes, adsbcu
 int adsbcu_1090b_reset(adsbcu_handle *h)
 {
     if (!h) return ADSBCU_ERR_ARG;
+    NEED_DEVICE(h);
     pathb_reset(h->pathb);
     return ADSBCU_OK;
 }
@@ -524,6 +578,7 @@ int adsbcu_978_feed(adsbcu_handle *h, const uint8_t *iq, size_t nbytes, adsbcu_u
 {
     if (!h) return ADSBCU_ERR_ARG;
     if (n_out) *n_out = 0;
+    NEED_DEVICE(h);
     if ((!iq && nbytes) || (!out && cap)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
     CK(cudaSetDevice(h->device));
     return pathc_feed(h->pathc, h->sm_count, h->stream, iq, nbytes, out, cap, n_out, h->error);
@@ -532,6 +587,7 @@ int adsbcu_978_feed(adsbcu_handle *h, const uint8_t *iq, size_t nbytes, adsbcu_u
 int adsbcu_978_reset(adsbcu_handle *h)
 {
     if (!h) return ADSBCU_ERR_ARG;
+    NEED_DEVICE(h);
     pathc_reset(h->pathc);
     return ADSBCU_OK;
 }
@@ -539,8 +595,124 @@ int adsbcu_978_reset(adsbcu_handle *h)
 int adsbcu_978_phase(adsbcu_handle *h, const uint8_t *iq, size_t nsamples, uint16_t *phi_out)
 {
     if (!h || (!iq && nsamples) || (!phi_out && nsamples)) return ADSBCU_ERR_ARG;
+    NEED_DEVICE(h);
     CK(cudaSetDevice(h->device));
     return pathc_phase(h->pathc, h->sm_count, h->stream, iq, nsamples, phi_out, h->error);
+}
+
+// ---- sharded captures ---------------------------------------------------------------------------
+
+int adsbcu_1090_seek(adsbcu_handle *h, uint64_t stream_pos, const uint8_t *prev_iq, size_t nprev)
+{
+    if (!h || (nprev && !prev_iq) || nprev > size_t(kOverlap)) return ADSBCU_ERR_ARG;
+    if (h->host_only) { h->stream_pos = stream_pos; return ADSBCU_OK; }
+    CK(cudaSetDevice(h->device));
+    CK(cudaMemsetAsync(h->d_carry, 0, kOverlap * sizeof(uint16_t), h->stream));
+    if (nprev) {
+        CK(cudaMemcpyAsync(h->d_iq, prev_iq, 2 * nprev, cudaMemcpyHostToDevice, h->stream));
+        CK(launch_carry(h->d_iq, uint32_t(nprev), h->d_carry, h->d_tab, h->stream));
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    h->stream_pos = stream_pos;
+    return ADSBCU_OK;
+}
+
+int adsbcu_1090_scan_candidates(adsbcu_handle *h, const uint8_t *iq, size_t nsamples, int on_device, adsbcu_cand *out,
+                                size_t cap, size_t *n_out)
+{
+    if (!h) return ADSBCU_ERR_ARG;
+    if (n_out) *n_out = 0;
+    NEED_DEVICE(h);
+    if ((!iq && nsamples) || (!out && cap) || (on_device && (reinterpret_cast<uintptr_t>(iq) & 15u)) ||
+        nsamples > h->cfg.max_feed_samples) {
+        h->error = "bad argument (null or misaligned pointer, or nsamples > max_feed_samples)";
+        return ADSBCU_ERR_ARG;
+    }
+    CK(cudaSetDevice(h->device));
+    if (!h->d_deferred) {
+        // noise leaves ~1 unknown-address record per 100 positions with --fix; dense traffic more
+        h->deferred_cap = uint32_t(std::max<size_t>(1u << 16, size_t(h->cfg.max_feed_samples) / 12));
+        CK(cudaMalloc(&h->d_deferred, size_t(h->deferred_cap) * sizeof(PhaseRec)));
+        CK(cudaMalloc(&h->d_n_deferred, sizeof(uint32_t)));
+        CK(cudaMalloc(&h->d_carry_prev, kOverlap * sizeof(uint16_t) + 32));
+        CK(cudaMalloc(&h->d_known_tmp, size_t(ADSBCU_KNOWN_WORDS) * sizeof(uint32_t)));
+    }
+    CK(cudaMemsetAsync(h->d_n_deferred, 0, sizeof(uint32_t), h->stream));
+    h->stats = adsbcu_stats{};
+    Sink sink{nullptr, cap, 0, false, out};
+    h->last_base = h->stream_pos;
+    h->last_n = uint32_t(nsamples);
+    h->last_iq = on_device ? iq : h->d_iq;
+    if (nsamples) {
+        const int r = on_device ? run_feed(h, iq, nullptr, uint32_t(nsamples), sink) : run_feed(h, h->d_iq, iq, uint32_t(nsamples), sink);
+        if (r != ADSBCU_OK) return r;
+    }
+    if (n_out) *n_out = sink.n;
+    if (sink.overflow) { h->error = "out[] too small for the candidates"; return ADSBCU_ERR_OVERFLOW; }
+    return ADSBCU_OK;
+}
+
+int adsbcu_1090_known_export(adsbcu_handle *h, uint32_t *words)
+{
+    if (!h || !words) return ADSBCU_ERR_ARG;
+    NEED_DEVICE(h);
+    CK(cudaSetDevice(h->device));
+    CK(cudaMemcpyAsync(words, h->d_bitmap, size_t(ADSBCU_KNOWN_WORDS) * 4, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return ADSBCU_OK;
+}
+
+int adsbcu_1090_known_import(adsbcu_handle *h, const uint32_t *words)
+{
+    if (!h || !words) return ADSBCU_ERR_ARG;
+    NEED_DEVICE(h);
+    CK(cudaSetDevice(h->device));
+    if (!h->d_known_tmp) CK(cudaMalloc(&h->d_known_tmp, size_t(ADSBCU_KNOWN_WORDS) * sizeof(uint32_t)));
+    CK(cudaMemcpyAsync(h->d_known_tmp, words, size_t(ADSBCU_KNOWN_WORDS) * 4, cudaMemcpyHostToDevice, h->stream));
+    CK(launch_or_words(h->d_bitmap, h->d_known_tmp, ADSBCU_KNOWN_WORDS, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return ADSBCU_OK;
+}
+
+int adsbcu_1090_revive(adsbcu_handle *h, adsbcu_cand *out, size_t cap, size_t *n_out)
+{
+    if (!h || (!out && cap)) return ADSBCU_ERR_ARG;
+    if (n_out) *n_out = 0;
+    NEED_DEVICE(h);
+    if (!h->d_deferred || !h->last_n) return ADSBCU_OK;
+    CK(cudaSetDevice(h->device));
+    Slot &s = h->slot[0];
+    ScanArgs a{};
+    a.iq = h->last_iq; a.carry_mag = h->d_carry_prev; a.nsamples = h->last_n;
+    a.pos_begin = 0; a.pos_end = h->last_n;
+    a.tab = h->d_tab; a.bitmap = h->d_bitmap;
+    a.seg = s.d_seg; a.seg_cap = h->seg_cap; a.nseg = h->nseg; a.seg_count = s.d_seg_count;
+    a.full = s.d_full; a.full_cap = h->full_cap; a.ctr = s.d_ctr;
+    a.deferred = h->d_deferred; a.deferred_cap = h->deferred_cap; a.n_deferred = h->d_n_deferred;
+    CK(cudaMemsetAsync(s.d_ctr, 0, sizeof(ChunkCounters), h->stream));
+    CK(launch_revive(a, h->stream));
+    CK(cudaMemcpyAsync(s.h_ctr, s.d_ctr, sizeof(ChunkCounters), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemsetAsync(h->d_n_deferred, 0, sizeof(uint32_t), h->stream));   // consumed
+    CK(cudaStreamSynchronize(h->stream));
+    const ChunkCounters k = *s.h_ctr;
+    if (k.overflow || k.n_full > h->full_cap) { h->error = "revive: candidate list overflow"; return ADSBCU_ERR_OVERFLOW; }
+    std::vector<FullRec> v(s.h_full, s.h_full + k.n_full);
+    std::sort(v.begin(), v.end(), [](const FullRec &x, const FullRec &y) { return x.pos != y.pos ? x.pos < y.pos : x.phase < y.phase; });
+    Sink sink{nullptr, cap, 0, false, out};
+    copy_candidates(v.data(), v.size(), h->last_base, sink);
+    if (n_out) *n_out = sink.n;
+    if (sink.overflow) { h->error = "out[] too small for the revived candidates"; return ADSBCU_ERR_OVERFLOW; }
+    return ADSBCU_OK;
+}
+
+int adsbcu_1090_resolve(adsbcu_handle *h, const adsbcu_cand *cands, size_t n, adsbcu_msg *out, size_t cap, size_t *n_out)
+{
+    if (!h || (!cands && n) || (!out && cap)) return ADSBCU_ERR_ARG;
+    Sink sink{out, cap, 0, false};
+    resolve(h, cands, n, 0, sink);
+    if (n_out) *n_out = sink.n;
+    if (sink.overflow) { h->error = "out[] too small for the accepted messages"; return ADSBCU_ERR_OVERFLOW; }
+    return ADSBCU_OK;
 }
 
 int adsbcu_get_stats(const adsbcu_handle *h, adsbcu_stats *out)

@@ -148,6 +148,10 @@ struct ScanArgs {
     uint32_t       *seg_count;   // [nseg] records per segment (scan: kept; filter: survivors)
     FullRec        *full;        uint32_t full_cap; // mapped pinned host memory
     ChunkCounters  *ctr;
+    // sharded captures only (else null): records the filter drops ONLY for an address missing from the
+    // bitmap are appended here (unordered); another shard's addresses may revive them later
+    PhaseRec       *deferred;    uint32_t deferred_cap;
+    uint32_t       *n_deferred;
 };
 
 void build_tables(DevTables &t, int nfix_crc, int fix_df);
@@ -157,6 +161,9 @@ cudaError_t init_kernels();                                        // per device
 cudaError_t launch_scan(const ScanArgs &a, cudaStream_t s);       // grid = a.nseg
 cudaError_t launch_filter(const ScanArgs &a, cudaStream_t s);     // drop A/P records whose address can never be known
 cudaError_t launch_evaluate(const ScanArgs &a, cudaStream_t s);   // survivors -> FullRec, stream order
+// deferred records whose address is in the bitmap now -> flat into a.seg (seg_count set per segment)
+cudaError_t launch_revive(const ScanArgs &a, cudaStream_t s);
+cudaError_t launch_or_words(uint32_t *dst, const uint32_t *src, uint32_t nwords, cudaStream_t s);
 cudaError_t launch_build_lut(DevTables *tab, cudaStream_t s);     // fills tab->mag_lut with the register-computed magnitudes
 cudaError_t launch_carry(const uint8_t *iq, uint32_t nsamples, uint16_t *carry_mag, const DevTables *tab, cudaStream_t s);
 cudaError_t launch_magnitude(const uint8_t *iq, uint32_t nsamples, uint16_t *mag, const DevTables *tab, cudaStream_t s);

@@ -448,7 +448,8 @@ __global__ void __launch_bounds__(256) filter_kernel(ScanArgs a)
         bool keep = false;
         if (i < n) {
             const uint32_t key = r.info & 0x1FFFFFFu, kind = r.info >> 28, ph = (r.info >> 25) & 7u;
-            keep = !kind_needs_known(kind) || ((a.bitmap[key >> 5] >> (key & 31)) & 1u);
+            const bool unknown = kind_needs_known(kind) && !((a.bitmap[key >> 5] >> (key & 31)) & 1u);
+            keep = true;
             const int r0 = rank_of(kind, false), r1 = rank_of(kind, true);
 #pragma unroll
             for (int d = -4; d <= 4; ++d) {
@@ -458,6 +459,13 @@ __global__ void __launch_bounds__(256) filter_kernel(ScanArgs a)
                 const uint32_t qk = q.info >> 28, qp = (q.info >> 25) & 7u;
                 const int q0 = rank_of(qk, false), q1 = rank_of(qk, true);
                 if ((q0 > r0 || (q0 == r0 && qp < ph)) && (q1 > r1 || (q1 == r1 && qp < ph))) keep = false;
+            }
+            if (keep && unknown) {
+                keep = false;
+                if (a.deferred) {
+                    const uint32_t slot = atomicAdd(a.n_deferred, 1u);
+                    if (slot < a.deferred_cap) a.deferred[slot] = r; else a.ctr->overflow = 1u;
+                }
             }
         }
         const uint32_t bal = __ballot_sync(0xFFFFFFFFu, keep);
@@ -472,6 +480,31 @@ __global__ void __launch_bounds__(256) filter_kernel(ScanArgs a)
         __syncthreads();
     }
     if (tid == 0) a.seg_count[blockIdx.x] = w;
+}
+
+// Sharded captures: after the address sets of the other shards were OR-ed into the bitmap, the deferred
+// records whose address is in it now are laid out flat over the segments for evaluate_kernel.
+__global__ void __launch_bounds__(256) revive_kernel(ScanArgs a)
+{
+    const uint32_t n = min(*a.n_deferred, a.deferred_cap);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const PhaseRec r = a.deferred[i];
+        const uint32_t key = r.info & 0x1FFFFFFu;
+        if (!((a.bitmap[key >> 5] >> (key & 31)) & 1u)) continue;
+        const uint32_t slot = atomicAdd(&a.ctr->n_cand, 1u);
+        if (slot < a.nseg * a.seg_cap) a.seg[slot] = r; else a.ctr->overflow = 1u;
+    }
+}
+__global__ void revive_counts_kernel(ScanArgs a)
+{
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= a.nseg) return;
+    const uint64_t total = min(uint64_t(a.ctr->n_cand), uint64_t(a.nseg) * a.seg_cap), lo = uint64_t(g) * a.seg_cap;
+    a.seg_count[g] = total > lo ? uint32_t(min(uint64_t(a.seg_cap), total - lo)) : 0u;
+}
+__global__ void or_words_kernel(uint32_t *dst, const uint32_t *src, uint32_t n)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) dst[i] |= src[i];
 }
 
 // One warp per surviving record, one CTA per segment.  The record's 290 samples are converted
@@ -661,6 +694,20 @@ cudaError_t launch_evaluate(const ScanArgs &a, cudaStream_t s)
 {
     if (a.pos_end <= a.pos_begin || !a.nseg) return cudaSuccess;
     evaluate_kernel<<<a.nseg, 256, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_revive(const ScanArgs &a, cudaStream_t s)
+{
+    revive_kernel<<<296, 256, 0, s>>>(a);
+    revive_counts_kernel<<<(a.nseg + 255) / 256, 256, 0, s>>>(a);
+    evaluate_kernel<<<a.nseg, 256, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_or_words(uint32_t *dst, const uint32_t *src, uint32_t nwords, cudaStream_t s)
+{
+    or_words_kernel<<<296, 256, 0, s>>>(dst, src, nwords);
     return cudaGetLastError();
 }
 
