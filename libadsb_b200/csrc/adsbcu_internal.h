@@ -17,20 +17,17 @@ constexpr uint32_t kUnchecked     = 0xFFFFFFFFu;
 
 // ---- scan kernel tiling --------------------------------------------------------------
 // One CTA per SM; a CTA is kGroups independent groups of kGroupThreads threads that share the
-// 128 KiB magnitude LUT in shared memory.  A group stages kTileSamples magnitudes per tile and
-// scans the kTile start positions whose 290-sample lookahead fits in them.
-#ifndef ADSBCU_TILE_SAMPLES
-#define ADSBCU_TILE_SAMPLES 8192
-#define ADSBCU_GROUPS 2
-#define ADSBCU_GROUP_THREADS 512
-#endif
-constexpr int kTileSamples = ADSBCU_TILE_SAMPLES;   // magnitudes staged per tile (2 x 16 B vectors per thread)
+// 32 KiB central magnitude LUT in shared memory.  Every thread of a group owns kRun consecutive
+// samples of a tile (kRun = 24 samples = 120 fifths of a sample = 10 symbols on each of the 12
+// sampling grids of the 2.4 MS/s slicer); a tile scans the kTile start positions whose 290-sample
+// lookahead fits in it.
+constexpr int kRun         = 24;              // samples per thread and tile
+constexpr int kGroups      = 4;
+constexpr int kGroupThreads = 256;
+constexpr int kTileSamples = kRun * kGroupThreads;   // 6144 magnitudes staged per tile
 constexpr int kTileLead    = 2;               // smem index of the tile's first start position (16 B alignment of x0)
 constexpr int kTile        = kTileSamples - 296;   // start positions per tile (lead + lookahead + pad to a multiple of 8)
-constexpr int kTilePad     = 32;              // slack read (never used) by the unrolled slicer's last period
-constexpr int kGroups      = ADSBCU_GROUPS;
-constexpr int kGroupThreads = ADSBCU_GROUP_THREADS;
-static_assert(kTileSamples % (8 * kGroupThreads) == 0, "whole 16-byte vectors per thread");
+constexpr int kTilePad     = 32;
 static_assert(kTile % 8 == 0, "tile starts must keep 16-byte alignment of the I/Q vectors");
 
 // State-independent classification of one sliced phase.  The host combines it
@@ -108,18 +105,20 @@ struct DevTables {
     uint64_t synd_long[kSyndSlotsLong];
     uint64_t synd_short[kSyndSlotsShort];
     alignas(16) uint32_t crc_byte[11][256];  // syndrome contribution of byte b (0..10) of a 112-bit frame having value v
-    alignas(16) uint16_t mag_lut[65536];   // the reference's uc8 magnitude table (tables.c:9-41) in the bank-swizzled
-                                 // layout of lut_offset(); filled on the device by build_lut at create time
+    alignas(16) uint16_t mag_lut[16384];   // central 128 x 128 part (I, Q in [64, 192)) of the reference's uc8 magnitude
+                                 // table (tables.c:9-41) in the bank-swizzled layout of lut_offset(); filled on the
+                                 // device by build_lut at create time.  Samples outside it (|I-128| > 64: strong
+                                 // signals only) take the register path mag_iq().
 };
 
-// Byte offset of magnitude(I, Q) inside mag_lut.  idx2 = 2 * (I | Q << 8); five low bits of Q are
-// xor-ed into the 32-bit-word index so that the 32 lanes of a gather spread over the shared-memory
-// banks even when every sample sits within a few LSB of the DC point (bank = (I>>1 ^ Q) & 31).
+// Byte offset of magnitude(I, Q) inside mag_lut, for I, Q in [64, 192): [64,192) -> (x & 127) is a bijection
+// onto [0,128).  Five low bits of Q are xor-ed into the 32-bit-word index so that the 32 lanes of a gather
+// spread over the shared-memory banks even when every sample sits within a few LSB of the DC point.
 __host__ __device__ inline uint32_t lut_offset(uint32_t i, uint32_t q)
 {
-    const uint32_t idx2 = (q << 9) | (i << 1);
-    return idx2 ^ ((idx2 >> 7) & 0x7Cu);
+    return (((i & 127u) << 1) | ((q & 127u) << 8)) ^ ((q & 31u) << 2);
 }
+__host__ __device__ inline bool lut_covers(uint32_t x) { return x >= 64u && x < 192u; }
 
 // Per-chunk counters (device; copied to pinned host memory after the chunk's kernels).
 struct ChunkCounters {

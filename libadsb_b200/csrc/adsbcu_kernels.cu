@@ -24,27 +24,15 @@ namespace adsbcu {
 
 namespace {
 
-#ifdef ADSBCU_EXPERIMENT_NOCONFLICT   // timing experiment only (wrong results): C2 lanes read distinct banks
-#define C2BASE(b) ((((b) >> 1) & ~31) | lane)
-#else
-#define C2BASE(b) ((b) >> 1)
-#endif
-#ifdef ADSBCU_PHASE_TIMING           // debug: cycles between group barriers, summed over all groups (thread 0 of each)
-__device__ unsigned long long g_phase_cycles[8];
-#define PHASE_MARK(k) PHASE_SLOT(((k) + 4) % 5)
-#define PHASE_SLOT(k) do { if (tid == 0) { const long long t_now = clock64(); if (t_prev) atomicAdd(&g_phase_cycles[k], (unsigned long long)(t_now - t_prev)); t_prev = t_now; } } while (0)
-#else
-#define PHASE_MARK(k) do { } while (0)
-#define PHASE_SLOT(k) do { } while (0)
-#endif
 constexpr int kPreCap = kTileSamples / 4;      // positions passing the edge masks, per tile
 constexpr int kCandCap = kTileSamples / 8;     // preambles kept per tile (overflow -> error, never silently dropped)
-constexpr int kCandChunk = kGroupThreads * 3 / 10;   // preambles per slicer round
+constexpr int kCandChunk = kGroupThreads;      // preambles per slicer round
 constexpr int kQueueCap = 5 * kCandChunk;      // (preamble, phase) items per round
 constexpr int kKeepCap = kTileSamples / 8;     // kept (position, phase) records per tile
 constexpr int kBuckets = 128, kBucketShift = 9; // phase D counting sort: 64 positions x 8 phase slots per bucket
 constexpr int kPosWords = (kTile + 31) / 32;   // 32-position words per tile
-constexpr int kUnitPeriods = 6;                // slicer work unit: 6 periods = 30 symbols = 72 samples
+constexpr int kPlaneStride = kGroupThreads + 16;   // symbol-plane fields per plane (+ zeroed slack for the 128-bit reads)
+static_assert(kPosWords + 2 <= kGroupThreads, "phase B: one thread per 32 start positions");
 
 // Scratch that is live in different phases of a tile shares storage.
 union GroupScratch {
@@ -53,11 +41,15 @@ union GroupScratch {
         __align__(16) uint8_t gbits[kTileSamples / 8 + 16];   // bit i: mag[i] > mag[i+1]
         uint16_t pre[kPreCap];
     } edge;
-    __align__(16) uint32_t pieces[kQueueCap][4];   // phase C: the 30-symbol pieces of every queued item
     uint2 sorted[kKeepCap];                        // phase D
 };
 struct GroupSmem {
     __align__(16) uint16_t mag[kTileSamples + kTilePad];
+    // Symbol planes.  The slicer decision at "time" t = 5 * sample + sub (sub = correlator phase 0..4) only
+    // depends on t, and symbol k of a message starting at time t0 sits at t0 + 12 k: a message is therefore
+    // 56 / 112 CONSECUTIVE bits of the plane t0 mod 12.  plane[c][v] holds, MSB first in its low 10 bits, the
+    // 10 decisions of plane c inside the 24 samples (120 fifths) of thread v.
+    uint16_t plane[12][kPlaneStride];
     GroupScratch u;
     union {
         uint16_t cand[kCandCap];               // phases B2..C
@@ -68,8 +60,9 @@ struct GroupSmem {
     uint32_t npre, ncand, nq[2], nkeep;
 };
 struct ScanSmem {
-    __align__(16) uint16_t lut[65536];         // DevTables::mag_lut
+    __align__(16) uint16_t lut[16384];         // DevTables::mag_lut
     uint32_t  crcb[11 * 256];
+    float     sq[256];                         // DevTables::sq, for samples outside the central LUT
     GroupSmem grp[kGroups];
 };
 static_assert(sizeof(ScanSmem) <= 227 * 1024, "scan kernel shared memory exceeds the sm_100 per-CTA limit");
@@ -79,16 +72,30 @@ __device__ __forceinline__ void group_sync(int g)
 {
     asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "n"(kGroupThreads) : "memory");
 }
-// magnitude of the sample in the low / high half of a 32-bit word {I0,Q0,I1,Q1} (see lut_offset)
-__device__ __forceinline__ uint32_t lut_lo(const unsigned char *lut, uint32_t w)
+// packed magnitudes {m(I0,Q0), m(I1,Q1)} of the two samples in a 32-bit word {I0,Q0,I1,Q1}; both must be
+// inside the central LUT (see lut_offset)
+__device__ __forceinline__ uint32_t lut_pair(const unsigned char *lut, uint32_t w)
 {
-    const uint32_t off = ((w << 1) & 0x1FFFEu) ^ ((w >> 6) & 0x7Cu);
-    return *reinterpret_cast<const uint16_t *>(lut + off);
+    const uint32_t h = w >> 16;
+    const uint32_t a0 = (((w << 1) & 0xFEu) | (w & 0x7F00u)) ^ ((w >> 6) & 0x7Cu);
+    const uint32_t a1 = (((h << 1) & 0xFEu) | (h & 0x7F00u)) ^ ((h >> 6) & 0x7Cu);
+    return uint32_t(*reinterpret_cast<const uint16_t *>(lut + a0)) | (uint32_t(*reinterpret_cast<const uint16_t *>(lut + a1)) << 16);
 }
-__device__ __forceinline__ uint32_t lut_hi(const unsigned char *lut, uint32_t w)
+// every byte of w in [64, 192)  <=>  bit7 != bit6 in every byte
+__device__ __forceinline__ uint32_t central_bits(uint32_t w) { return w ^ (w << 1); }
+__device__ __forceinline__ uint32_t mag_pair_any(const float *sq, uint32_t w)
 {
-    const uint32_t off = ((w >> 15) & 0x1FFFEu) ^ ((w >> 22) & 0x7Cu);
-    return *reinterpret_cast<const uint16_t *>(lut + off);
+    return mag_iq(sq, w & 0xFFu, (w >> 8) & 0xFFu) | (mag_iq(sq, (w >> 16) & 0xFFu, w >> 24) << 16);
+}
+__host__ __device__ constexpr uint32_t w2(int lo, int hi) { return uint32_t(uint8_t(lo)) | (uint32_t(uint8_t(hi)) << 8); }
+
+// 32 consecutive decisions of one symbol plane starting at stream bit n, first one in the MSB
+__device__ __forceinline__ uint32_t plane_bits32(const uint16_t *pl, uint32_t n)
+{
+    const uint32_t f = n / 10u, r = n - 10u * f;
+    const uint64_t W = (uint64_t(pl[f]) << 40) | (uint64_t(pl[f + 1]) << 30) | (uint64_t(pl[f + 2]) << 20) |
+                       (uint64_t(pl[f + 3]) << 10) | uint64_t(pl[f + 4]);
+    return uint32_t(W >> (18u - r));
 }
 
 // Reference preamble test at p[0..18] (demod_2400.c:155-218).  `p` points into shared memory.
@@ -133,15 +140,14 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
         }
         __syncthreads();
         if (threadIdx.x == 0) {
-            constexpr uint32_t kLutBytes = 65536 * 2, kCrcBytes = 11 * 256 * 4, kPiece = 32768;
-            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(kLutBytes + kCrcBytes) : "memory");
-            const unsigned char *src = reinterpret_cast<const unsigned char *>(a.tab->mag_lut);
-            const uint32_t dst = uint32_t(__cvta_generic_to_shared(sm.lut));
-            for (uint32_t o = 0; o < kLutBytes; o += kPiece)
-                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                             ::"r"(dst + o), "l"(src + o), "r"(kPiece), "r"(bar) : "memory");
+            constexpr uint32_t kLutBytes = 16384 * 2, kCrcBytes = 11 * 256 * 4, kSqBytes = 256 * 4;
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(kLutBytes + kCrcBytes + kSqBytes) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(uint32_t(__cvta_generic_to_shared(sm.lut))), "l"(a.tab->mag_lut), "r"(kLutBytes), "r"(bar) : "memory");
             asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                          ::"r"(uint32_t(__cvta_generic_to_shared(sm.crcb))), "l"(&a.tab->crc_byte[0][0]), "r"(kCrcBytes), "r"(bar) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(uint32_t(__cvta_generic_to_shared(sm.sq))), "l"(a.tab->sq), "r"(kSqBytes), "r"(bar) : "memory");
         }
         uint32_t done = 0;
         while (!done)
@@ -152,10 +158,12 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
     const int grp = threadIdx.x / kGroupThreads, tid = threadIdx.x % kGroupThreads, lane = tid & 31;
     GroupSmem &gs = sm.grp[grp];
     uint16_t *s_mag = gs.mag;
-    const uint32_t *s_magw = reinterpret_cast<const uint32_t *>(gs.mag);
     const unsigned char *lut = reinterpret_cast<const unsigned char *>(sm.lut);
+    const float *s_sq = sm.sq;
     const uint32_t *s_crcb = sm.crcb;
     const uint32_t valid_long = a.tab->valid_long, valid_short = a.tab->valid_short, fixable_short = a.tab->fixable_short;
+    for (int i = tid; i < 12 * (kPlaneStride - kGroupThreads); i += kGroupThreads)     // slack fields stay zero
+        gs.plane[i / (kPlaneStride - kGroupThreads)][kGroupThreads + i % (kPlaneStride - kGroupThreads)] = 0;
 
     const int64_t n = a.nsamples;
     const uint32_t ntiles = (a.pos_end - a.pos_begin + kTile - 1) / kTile;
@@ -170,82 +178,112 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
     unsigned long long my_preambles = 0;
 
     // The groups of a CTA start together; a shorter first tile for every group but the first puts them
-    // out of step so that one group's load-latency phase overlaps another's slicing phase.
+    // out of step so that one group's dense phase A overlaps the sparse phases B..D of the others.
     int64_t tile_base = seg_begin;
-#ifdef ADSBCU_PHASE_TIMING
-    long long t_prev = 0;
-#endif
     int first_len = kTile - ((kTile / kGroups * grp) & ~7);
-    constexpr int kVec = kTileSamples / 8 / kGroupThreads;          // 16-byte vectors per thread
-    uint4 raw[kVec];
-    auto load_raw = [&](int64_t base) {                             // the tile whose first start position is `base`
+    // a thread's 24 samples + the 4 samples of lookahead its correlators need: 3 x 16 B + 8 B of I/Q
+    uint4 raw[3];
+    uint2 rawx;
+    auto load_raw = [&](int64_t base) {             // the tile whose first start position is `base`
+        const int64_t x = base - kOverlap - kTileLead + kRun * tid;
 #pragma unroll
-        for (int r = 0; r < kVec; ++r) {
-            const int64_t x = base - kOverlap - kTileLead + 8 * (tid + r * kGroupThreads);
-            if (x >= 0 && x + 8 <= n) raw[r] = __ldg(reinterpret_cast<const uint4 *>(a.iq + 2 * x));
-        }
+        for (int r = 0; r < 3; ++r)
+            if (x + 8 * r >= 0 && x + 8 * r + 8 <= n) raw[r] = __ldg(reinterpret_cast<const uint4 *>(a.iq + 2 * (x + 8 * r)));
+        if (x + 24 >= 0 && x + 28 <= n) rawx = __ldg(reinterpret_cast<const uint2 *>(a.iq + 2 * (x + 24)));
+    };
+    // magnitude of feed sample xe on the slow path (stream edges): carry, scalar I/Q, or zero padding
+    auto mag_edge = [&](int64_t xe) -> uint32_t {
+        if (xe < 0) return (xe + kOverlap >= 0) ? uint32_t(a.carry_mag[xe + kOverlap]) : 0u;
+        if (xe < n) return mag_iq(s_sq, a.iq[2 * xe], a.iq[2 * xe + 1]);
+        return 0u;
     };
     if (tile_base < seg_end) load_raw(tile_base);
     while (tile_base < seg_end) {
         group_sync(grp);   // previous tile fully consumed
-        PHASE_MARK(0);
         const int npos = int(min(int64_t(first_len), seg_end - tile_base));   // start positions in this tile
         first_len = kTile;
         const int64_t next_base = tile_base + npos;
         // shared index i <-> feed sample x = x0 + i ; start position s (tile-local) sits at i = s + kTileLead
         const int64_t x0 = tile_base - kOverlap - kTileLead;
 
-        // ---- phase A: magnitudes (LUT gather) + rising/falling edge bits -----------------------
-        // raw[] was loaded while the previous tile was being sliced (or just before the loop)
+        // ---- phase A: magnitudes, rising/falling edge bits and all slicer decisions of 24 samples -------
+        {
+            const int64_t x = x0 + kRun * tid;
+            uint32_t P[14];                          // P[k] = {mag[2k], mag[2k+1]} of this thread's run, k = 12, 13: lookahead
 #pragma unroll
-        for (int r = 0; r < kVec; ++r) {
-            const int v = tid + r * kGroupThreads;
-            const int64_t x = x0 + 8 * v;
-            uint32_t m[8];
-            if (x >= 0 && x + 8 <= n) {
-                const uint4 d = raw[r];
-                m[0] = lut_lo(lut, d.x); m[1] = lut_hi(lut, d.x);
-                m[2] = lut_lo(lut, d.y); m[3] = lut_hi(lut, d.y);
-                m[4] = lut_lo(lut, d.z); m[5] = lut_hi(lut, d.z);
-                m[6] = lut_lo(lut, d.w); m[7] = lut_hi(lut, d.w);
-            } else {
+            for (int r = 0; r < 3; ++r) {
+                const int64_t xv = x + 8 * r;
+                if (xv >= 0 && xv + 8 <= n) {
+                    const uint4 d = raw[r];
+                    const uint32_t c = central_bits(d.x) & central_bits(d.y) & central_bits(d.z) & central_bits(d.w);
+                    if ((c & 0x80808080u) == 0x80808080u) {
+                        P[4 * r] = lut_pair(lut, d.x); P[4 * r + 1] = lut_pair(lut, d.y);
+                        P[4 * r + 2] = lut_pair(lut, d.z); P[4 * r + 3] = lut_pair(lut, d.w);
+                    } else {
+                        P[4 * r] = mag_pair_any(s_sq, d.x); P[4 * r + 1] = mag_pair_any(s_sq, d.y);
+                        P[4 * r + 2] = mag_pair_any(s_sq, d.z); P[4 * r + 3] = mag_pair_any(s_sq, d.w);
+                    }
+                } else {
 #pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                    const int64_t xe = x + e;
-                    if (xe < 0) m[e] = (xe + kOverlap >= 0) ? a.carry_mag[xe + kOverlap] : 0u;
-                    else if (xe < n) m[e] = lut_lo(lut, uint32_t(a.iq[2 * xe]) | (uint32_t(a.iq[2 * xe + 1]) << 8));
-                    else m[e] = 0u;
+                    for (int e = 0; e < 4; ++e) P[4 * r + e] = mag_edge(xv + 2 * e) | (mag_edge(xv + 2 * e + 1) << 16);
                 }
+                *reinterpret_cast<uint4 *>(&s_mag[kRun * tid + 8 * r]) = make_uint4(P[4 * r], P[4 * r + 1], P[4 * r + 2], P[4 * r + 3]);
             }
-            uint4 o;
-            o.x = m[0] | (m[1] << 16); o.y = m[2] | (m[3] << 16); o.z = m[4] | (m[5] << 16); o.w = m[6] | (m[7] << 16);
-            *reinterpret_cast<uint4 *>(&s_mag[8 * v]) = o;
-            // bit k of the byte: m[k] <,> m[k+1]; lane 31 has no right neighbour here, its bit 7 is repaired in phase B
-            const uint32_t m8 = __shfl_down_sync(0xFFFFFFFFu, m[0], 1);
-            uint32_t L = __funnelshift_l(m[7] - m8, 0u, 1), G = __funnelshift_l(m8 - m[7], 0u, 1);
+            if (x + 24 >= 0 && x + 28 <= n) {
+                const uint32_t c = central_bits(rawx.x) & central_bits(rawx.y);
+                if ((c & 0x80808080u) == 0x80808080u) { P[12] = lut_pair(lut, rawx.x); P[13] = lut_pair(lut, rawx.y); }
+                else { P[12] = mag_pair_any(s_sq, rawx.x); P[13] = mag_pair_any(s_sq, rawx.y); }
+            } else {
+                P[12] = mag_edge(x + 24) | (mag_edge(x + 25) << 16);
+                P[13] = mag_edge(x + 26) | (mag_edge(x + 27) << 16);
+            }
+            // first differences nd[e] = mag[e+1] - mag[e] give everything else:
+            //   edge bits      mag[e] < mag[e+1]  <=>  -nd[e] < 0 ;  mag[e] > mag[e+1]  <=>  nd[e] < 0
+            //   correlators    slice_sub(&m[e]) = (5-sub) d0 + (2+sub) d1 (+ d2 for sub 4), d = -nd  (demod_2400.c:45-59);
+            //                  their NEGATION is accumulated so that "correlation > 0" is the sign bit
+            constexpr uint32_t kUp = w2(-1, 1);
+            auto nd_at = [&](int e) -> int {         // e: compile-time after unrolling
+                const uint32_t X = (e & 1) ? __funnelshift_r(P[e >> 1], P[(e >> 1) + 1], 16) : P[e >> 1];
+                return dp2a_lo(X, kUp, 0);
+            };
+            uint32_t acc[12], L = 0, G = 0;
 #pragma unroll
-            for (int k = 6; k >= 0; --k) {
-                L = __funnelshift_l(m[k] - m[k + 1], L, 1);
-                G = __funnelshift_l(m[k + 1] - m[k], G, 1);
+            for (int c = 0; c < 12; ++c) acc[c] = 0;
+            int nd0 = nd_at(0), nd1 = nd_at(1);
+#pragma unroll
+            for (int e = 0; e < kRun; ++e) {
+                const int nd2 = nd_at(e + 2);
+                G = __funnelshift_l(uint32_t(nd0), G, 1);
+                L = __funnelshift_l(uint32_t(-nd0), L, 1);
+                const int step = nd1 - nd0;
+                int v = 5 * nd0 + 2 * nd1;           // -(5 d0 + 2 d1)
+#pragma unroll
+                for (int sub = 0; sub < 5; ++sub) {
+                    if (sub == 4) v += nd2;
+                    const int c = (5 * e + sub) % 12;
+                    acc[c] = __funnelshift_l(uint32_t(v), acc[c], 1);
+                    v += step;
+                }
+                nd0 = nd1; nd1 = nd2;
             }
-            gs.u.edge.lbits[v] = uint8_t(L);
-            gs.u.edge.gbits[v] = uint8_t(G);
+#pragma unroll
+            for (int c = 0; c < 12; ++c) gs.plane[c][tid] = uint16_t(acc[c]);
+            L = __brev(L) >> 8; G = __brev(G) >> 8;   // bit e <-> sample e of the run
+#pragma unroll
+            for (int r = 0; r < 3; ++r) {
+                gs.u.edge.lbits[3 * tid + r] = uint8_t(L >> (8 * r));
+                gs.u.edge.gbits[3 * tid + r] = uint8_t(G >> (8 * r));
+            }
         }
         if (tid == 0) { gs.npre = 0; gs.ncand = 0; gs.nkeep = 0; }
         if (next_base < seg_end) load_raw(next_base);                   // in flight during phases B..D
         group_sync(grp);
-        PHASE_MARK(1);
 
         // ---- phase B: preamble edge patterns, 32 start positions per thread ----------------------
         if (tid < kPosWords) {
             const uint32_t *Lw = reinterpret_cast<const uint32_t *>(gs.u.edge.lbits), *Gw = reinterpret_cast<const uint32_t *>(gs.u.edge.gbits);
-            uint32_t l0 = Lw[tid], g0 = Gw[tid];
+            const uint32_t l0 = Lw[tid], g0 = Gw[tid];
             const uint32_t l1 = Lw[tid + 1], l2 = Lw[tid + 2], g1 = Gw[tid + 1], g2 = Gw[tid + 2];
-            if ((tid & 7) == 7) {                   // bit 31 of this word came from a lane 31 (see phase A)
-                const uint32_t ma = s_mag[32 * tid + 31], mb = s_mag[32 * tid + 32];
-                l0 = (l0 & 0x7FFFFFFFu) | (ma < mb ? 0x80000000u : 0u);
-                g0 = (g0 & 0x7FFFFFFFu) | (ma > mb ? 0x80000000u : 0u);
-            }
             // bit b of myL/myG <-> start position 32*tid + b (smem index + kTileLead)
             const uint32_t myL = funnel_r(l0, l1, kTileLead), nxL = funnel_r(l1, l2, kTileLead);
             const uint32_t myG = funnel_r(g0, g1, kTileLead), nxG = funnel_r(g1, g2, kTileLead);
@@ -269,7 +307,6 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
             }
         }
         group_sync(grp);
-        PHASE_MARK(2);
         {   // full preamble test (signal/noise ratio, quiet zones) on the compacted list
             const uint32_t npre = min(gs.npre, uint32_t(kPreCap));
             for (uint32_t i = tid; i < npre; i += kGroupThreads) {
@@ -282,14 +319,11 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
             }
         }
         group_sync(grp);
-        PHASE_MARK(3);
 
-        // ---- phase C: five-phase slicer + CRC + classification ---------------------------
-        // C1 slices two periods of every (preamble, phase) to read the DF field and queues the items the DF
-        //    pre-filter keeps (demod_2400.c:317-331);
-        // C2 slices the queued items in units of 6 periods (30 symbols), one unit per lane, every lane running
-        //    the same unrolled code: a 112-bit item is 4 units, a 56-bit item 2;
-        // C3 reassembles each item from its pieces, one item per lane: CRC-24 syndromes, repair, classification.
+        // ---- phase C: messages are bit strings of the symbol planes ----------------------------------
+        // C1 reads the DF field (5 bits) of every (preamble, phase) and queues the items the DF pre-filter
+        //    keeps (demod_2400.c:317-331);
+        // C2 one item per thread: 56 / 112 plane bits, CRC-24 syndromes, repair, classification.
         const uint32_t ncand = min(gs.ncand, uint32_t(kCandCap));
         for (uint32_t c0 = 0; c0 < ncand; c0 += kCandChunk) {
             if (tid < 2) gs.nq[tid] = 0;
@@ -297,68 +331,45 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
             const uint32_t nitems = min(uint32_t(kCandChunk), ncand - c0) * 5u;
             for (uint32_t it = tid; it < nitems; it += kGroupThreads) {
                 const uint32_t pos = gs.cand[c0 + it / 5u];
-                const int ph = 4 + int(it % 5u);
-                const int b = int(pos) + kTileLead + 19 + phase_c(ph);
-                uint32_t w[7], acc[4] = {0u, 0u, 0u, 0u}, M[4];
-                slicer_weights(b & 1, w);
-                slice_periods<2>(s_magw + (b >> 1), w, acc);
-                align_message<10>(acc, phase_v0(ph), M);
-                const uint32_t dfbit = 1u << (M[0] >> 27);
-                const uint32_t item = pos | (uint32_t(ph - 4) << 16);
+                const uint32_t ph = 4u + it % 5u;
+                const uint32_t t0 = 5u * (pos + kTileLead + 19u) + ph;
+                const uint32_t c = t0 % 12u, n0 = t0 / 12u, f = n0 / 10u, r = n0 - 10u * f;
+                const uint32_t w20 = (uint32_t(gs.plane[c][f]) << 10) | gs.plane[c][f + 1];
+                const uint32_t dfbit = 1u << ((w20 >> (15u - r)) & 31u);
+                const uint32_t item = pos | ((ph - 4u) << 16);
                 if (valid_long & dfbit) gs.queue[atomicAdd(&gs.nq[0], 1u)] = item;
                 else if (valid_short & dfbit) gs.queue[kQueueCap - 1 - atomicAdd(&gs.nq[1], 1u)] = item;
             }
             group_sync(grp);
-            PHASE_SLOT(5);
             const uint32_t nlong = gs.nq[0], nshort = gs.nq[1];
-            const uint32_t nunits = 4u * nlong + 2u * nshort;
-            for (uint32_t u = tid; u < nunits; u += kGroupThreads) {
-                const bool is_long = u < 4u * nlong;
-                const uint32_t idx = is_long ? u >> 2 : nlong + ((u - 4u * nlong) >> 1);      // item index of this round
-                const uint32_t blk = is_long ? u & 3u : (u - 4u * nlong) & 1u;
-                const uint32_t item = is_long ? gs.queue[idx] : gs.queue[kQueueCap - 1 - (idx - nlong)];
-                const uint32_t pos = item & 0xFFFFu;
-                const int ph = 4 + int(item >> 16);
-                const int b = int(pos) + kTileLead + 19 + phase_c(ph) + 12 * kUnitPeriods * int(blk);
-                uint32_t w[7], acc[4] = {0u, 0u, 0u, 0u};
-                slicer_weights(b & 1, w);
-                slice_periods<kUnitPeriods>(s_magw + (b >> 1), w, acc);
-                gs.u.pieces[idx][blk] = acc[0];                                               // 30 symbols, first in bit 29
-            }
-            group_sync(grp);
-            PHASE_SLOT(6);
             for (uint32_t it = tid; it < nlong + nshort; it += kGroupThreads) {
                 const bool is_long = it < nlong;
                 const uint32_t item = is_long ? gs.queue[it] : gs.queue[kQueueCap - 1 - (it - nlong)];
-                const uint32_t pos = item & 0xFFFFu;
-                const int ph = 4 + int(item >> 16);
-                const uint4 pc = *reinterpret_cast<const uint4 *>(gs.u.pieces[it]);
-                // symbol stream, first symbol in the MSB of W0; then shift out the v0 leading virtual symbols
-                const uint32_t W0 = (pc.x << 2) | ((pc.y >> 28) & 3u);
-                uint32_t W1 = pc.y << 4, W2 = 0u, W3 = 0u;
-                if (is_long) { W1 |= (pc.z >> 26) & 15u; W2 = (pc.z << 6) | ((pc.w >> 24) & 63u); W3 = pc.w << 8; }
-                const int v0 = phase_v0(ph);
-                uint32_t M[4] = {__funnelshift_l(W1, W0, v0), __funnelshift_l(W2, W1, v0), __funnelshift_l(W3, W2, v0), W3 << v0};
+                const uint32_t pos = item & 0xFFFFu, ph = 4u + (item >> 16);
+                const uint32_t t0 = 5u * (pos + kTileLead + 19u) + ph;
+                const uint32_t c = t0 % 12u, n0 = t0 / 12u;
+                const uint16_t *pl = gs.plane[c];
+                uint32_t M[4] = {plane_bits32(pl, n0), plane_bits32(pl, n0 + 32u), 0u, 0u};
                 uint32_t xs = 0, xl = 0;
                 if (is_long) {
-                    M[3] &= 0xFFFF0000u;
+                    M[2] = plane_bits32(pl, n0 + 64u);
+                    M[3] = plane_bits32(pl, n0 + 96u) & 0xFFFF0000u;
                     xl = crc_long(M, s_crcb);
                     // the 56-bit syndrome is also needed when a short DF was sliced long (DF0/DF5 are within two
                     // bit flips of DF17/18, so --fix-2bit slices them to 14 bytes but scores them as 56-bit A/P)
                     if (!(M[0] >> 31) || (fixable_short & (1u << (M[0] >> 27)))) xs = crc_short(M, s_crcb);
                 } else {
-                    M[1] &= 0xFFFFFF00u; M[2] = 0u; M[3] = 0u;
+                    M[1] &= 0xFFFFFF00u;
                     xs = crc_short(M, s_crcb);
                 }
-                const Classified c = classify(frame_from_words(M, is_long), xs, xl, a.tab);
-                if (!c.keep) continue;
-                const uint32_t bi = bitmap_index(c.test_key);
-                if (c.kind == K_DF17_0 || c.kind == K_DF11_ACQ_0 || (c.kind == K_DF18_0 && !df18_non_icao(c.fixed)))
+                const Classified cl = classify(frame_from_words(M, is_long), xs, xl, a.tab);
+                if (!cl.keep) continue;
+                const uint32_t bi = bitmap_index(cl.test_key);
+                if (cl.kind == K_DF17_0 || cl.kind == K_DF11_ACQ_0 || (cl.kind == K_DF18_0 && !df18_non_icao(cl.fixed)))
                     atomicOr(&a.bitmap[bi >> 5], 1u << (bi & 31));
                 const uint32_t slot = atomicAdd(&gs.nkeep, 1u);
                 if (slot < kKeepCap)
-                    gs.keep[slot] = make_uint2((pos << 3) | uint32_t(ph - 4),
-                                               bi | (uint32_t(ph - 4) << 25) | (c.kind << 28));
+                    gs.keep[slot] = make_uint2((pos << 3) | (ph - 4u), bi | ((ph - 4u) << 25) | (cl.kind << 28));
                 else
                     a.ctr->overflow = 1u;
             }
@@ -367,7 +378,6 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
         // ---- phase D: ordered emission of this tile's records into the segment ----------------
         // counting sort by 64-position bucket, then rank inside the (tiny) bucket
         group_sync(grp);
-        PHASE_MARK(4);
         const uint32_t nkeep = min(gs.nkeep, uint32_t(kKeepCap));
         uint32_t *hist = gs.hist, *start = hist + kBuckets, *fill = hist + 2 * kBuckets;
         uint2 *sorted = gs.u.sorted;
@@ -617,7 +627,8 @@ __global__ void __launch_bounds__(256) evaluate_kernel(ScanArgs a)
 __global__ void build_lut_kernel(DevTables *tab)
 {
     const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;    // I | Q << 8
-    if (idx < 65536u) tab->mag_lut[lut_offset(idx & 255u, idx >> 8) >> 1] = uint16_t(mag_iq(tab->sq, idx & 255u, idx >> 8));
+    const uint32_t i = idx & 255u, q = idx >> 8;
+    if (idx < 65536u && lut_covers(i) && lut_covers(q)) tab->mag_lut[lut_offset(i, q) >> 1] = uint16_t(mag_iq(tab->sq, i, q));
 }
 
 __global__ void carry_kernel(const uint8_t *iq, uint32_t nsamples, uint16_t *carry_mag, const DevTables *tab)
@@ -655,15 +666,6 @@ __global__ void __launch_bounds__(256) magnitude_kernel(const uint8_t *iq, uint3
 }
 
 }  // namespace
-
-#ifdef ADSBCU_PHASE_TIMING
-extern "C" void adsbcu_debug_phase_cycles(unsigned long long *out, int reset)
-{
-    cudaDeviceSynchronize();
-    cudaMemcpyFromSymbol(out, g_phase_cycles, sizeof(g_phase_cycles));
-    if (reset) { unsigned long long z[8] = {}; cudaMemcpyToSymbol(g_phase_cycles, z, sizeof(z)); }
-}
-#endif
 
 cudaError_t init_kernels()
 {
