@@ -102,6 +102,7 @@ struct adsbcu_handle {
     uint16_t *d_carry = nullptr;
     uint8_t *d_iq = nullptr;          // staging for host feeds
     uint32_t nseg = 0, seg_cap = 0, full_cap = 0;
+    uint32_t skew = 0, skew_ns = 2500;   // measured on B200: no skew 0.5065 ms, sleep skew 0.506-0.516, short first tile 0.529 (profiles/sweep_skew.sh)
     uint32_t unit_positions = 0, max_tps = 1;   // chunk = unit_positions * (tiles per segment), at most max_tps
     Slot slot[kSlots];
     uint16_t *d_mag = nullptr;        // stage-level magnitude output
@@ -283,6 +284,7 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
         a.seg_count = s.d_seg_count;
         a.full = s.d_full; a.full_cap = h->full_cap;
         a.ctr = s.d_ctr;
+        a.skew = h->skew; a.skew_ns = h->skew_ns;
         if (sink.cands) { a.deferred = h->d_deferred; a.deferred_cap = h->deferred_cap; a.n_deferred = h->d_n_deferred; }
         if (iq_host) {
             CK(cudaMemcpyAsync(h->d_iq + 2 * size_t(a.pos_begin), iq_host + 2 * size_t(a.pos_begin),
@@ -434,6 +436,8 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
     // chunk geometry: every scan group (kGroups per SM) owns up to max_tps consecutive tiles of a chunk
     uint32_t tps = 16;
     if (const char *e = std::getenv("ADSBCU_TILES_PER_SEG")) tps = uint32_t(std::max(1, std::atoi(e)));
+    if (const char *e = std::getenv("ADSBCU_SKEW")) h->skew = uint32_t(std::atoi(e));
+    if (const char *e = std::getenv("ADSBCU_SKEW_NS")) h->skew_ns = uint32_t(std::max(0, std::atoi(e)));
     const size_t nmax = c.max_feed_samples;
     h->nseg = uint32_t(h->sm_count) * uint32_t(kGroups);
     h->unit_positions = h->nseg * uint32_t(kTile);

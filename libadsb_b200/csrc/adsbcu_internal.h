@@ -105,18 +105,21 @@ struct DevTables {
     uint64_t synd_long[kSyndSlotsLong];
     uint64_t synd_short[kSyndSlotsShort];
     alignas(16) uint32_t crc_byte[11][256];  // syndrome contribution of byte b (0..10) of a 112-bit frame having value v
-    alignas(16) uint16_t mag_lut[16384];   // central 128 x 128 part (I, Q in [64, 192)) of the reference's uc8 magnitude
+    alignas(16) uint16_t mag_lut[32768];   // central 128 x 128 part (I, Q in [64, 192)) of the reference's uc8 magnitude
                                  // table (tables.c:9-41) in the bank-swizzled layout of lut_offset(); filled on the
                                  // device by build_lut at create time.  Samples outside it (|I-128| > 64: strong
                                  // signals only) take the register path mag_iq().
 };
 
 // Byte offset of magnitude(I, Q) inside mag_lut, for I, Q in [64, 192): [64,192) -> (x & 127) is a bijection
-// onto [0,128).  Five low bits of Q are xor-ed into the 32-bit-word index so that the 32 lanes of a gather
-// spread over the shared-memory banks even when every sample sits within a few LSB of the DC point.
+// onto [0,128).  Element index = (Q & 127) << 8 | (I & 127): the two 7-bit fields stay where they are in the
+// 16-bit sample word, so one AND addresses both samples of a 32-bit word at once (bit 7 of the index is a hole:
+// rows are 256 elements of which 128 are used).  Five low bits of Q are xor-ed into index bits 1..5 (= the
+// shared-memory bank) so that the 32 lanes of a gather spread over the banks even when every sample sits
+// within a few LSB of the DC point.
 __host__ __device__ inline uint32_t lut_offset(uint32_t i, uint32_t q)
 {
-    return (((i & 127u) << 1) | ((q & 127u) << 8)) ^ ((q & 31u) << 2);
+    return 2u * ((((q & 127u) << 8) | (i & 127u)) ^ ((q & 31u) << 1));
 }
 __host__ __device__ inline bool lut_covers(uint32_t x) { return x >= 64u && x < 192u; }
 
@@ -151,6 +154,7 @@ struct ScanArgs {
     // bitmap are appended here (unordered); another shard's addresses may revive them later
     PhaseRec       *deferred;    uint32_t deferred_cap;
     uint32_t       *n_deferred;
+    uint32_t        skew, skew_ns;   // how the groups of a CTA are put out of step (scan_kernel)
 };
 
 void build_tables(DevTables &t, int nfix_crc, int fix_df);

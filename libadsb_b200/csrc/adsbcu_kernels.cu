@@ -60,7 +60,7 @@ struct GroupSmem {
     uint32_t npre, ncand, nq[2], nkeep;
 };
 struct ScanSmem {
-    __align__(16) uint16_t lut[16384];         // DevTables::mag_lut
+    __align__(16) uint16_t lut[32768];         // DevTables::mag_lut
     uint32_t  crcb[11 * 256];
     float     sq[256];                         // DevTables::sq, for samples outside the central LUT
     GroupSmem grp[kGroups];
@@ -74,12 +74,10 @@ __device__ __forceinline__ void group_sync(int g)
 }
 // packed magnitudes {m(I0,Q0), m(I1,Q1)} of the two samples in a 32-bit word {I0,Q0,I1,Q1}; both must be
 // inside the central LUT (see lut_offset)
-__device__ __forceinline__ uint32_t lut_pair(const unsigned char *lut, uint32_t w)
+__device__ __forceinline__ uint32_t lut_pair(const uint16_t *lut, uint32_t w)
 {
-    const uint32_t h = w >> 16;
-    const uint32_t a0 = (((w << 1) & 0xFEu) | (w & 0x7F00u)) ^ ((w >> 6) & 0x7Cu);
-    const uint32_t a1 = (((h << 1) & 0xFEu) | (h & 0x7F00u)) ^ ((h >> 6) & 0x7Cu);
-    return uint32_t(*reinterpret_cast<const uint16_t *>(lut + a0)) | (uint32_t(*reinterpret_cast<const uint16_t *>(lut + a1)) << 16);
+    const uint32_t u = (w ^ ((w >> 7) & 0x003E003Eu)) & 0x7F7F7F7Fu;   // both element indices at once
+    return uint32_t(lut[u & 0xFFFFu]) | (uint32_t(lut[u >> 16]) << 16);
 }
 // every byte of w in [64, 192)  <=>  bit7 != bit6 in every byte
 __device__ __forceinline__ uint32_t central_bits(uint32_t w) { return w ^ (w << 1); }
@@ -140,10 +138,11 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
         }
         __syncthreads();
         if (threadIdx.x == 0) {
-            constexpr uint32_t kLutBytes = 16384 * 2, kCrcBytes = 11 * 256 * 4, kSqBytes = 256 * 4;
+            constexpr uint32_t kLutBytes = 32768 * 2, kCrcBytes = 11 * 256 * 4, kSqBytes = 256 * 4;
             asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(kLutBytes + kCrcBytes + kSqBytes) : "memory");
-            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                         ::"r"(uint32_t(__cvta_generic_to_shared(sm.lut))), "l"(a.tab->mag_lut), "r"(kLutBytes), "r"(bar) : "memory");
+            for (uint32_t o = 0; o < kLutBytes; o += 32768u)
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                             ::"r"(uint32_t(__cvta_generic_to_shared(sm.lut)) + o), "l"(reinterpret_cast<const unsigned char *>(a.tab->mag_lut) + o), "r"(32768u), "r"(bar) : "memory");
             asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                          ::"r"(uint32_t(__cvta_generic_to_shared(sm.crcb))), "l"(&a.tab->crc_byte[0][0]), "r"(kCrcBytes), "r"(bar) : "memory");
             asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -158,7 +157,7 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
     const int grp = threadIdx.x / kGroupThreads, tid = threadIdx.x % kGroupThreads, lane = tid & 31;
     GroupSmem &gs = sm.grp[grp];
     uint16_t *s_mag = gs.mag;
-    const unsigned char *lut = reinterpret_cast<const unsigned char *>(sm.lut);
+    const uint16_t *lut = sm.lut;
     const float *s_sq = sm.sq;
     const uint32_t *s_crcb = sm.crcb;
     const uint32_t valid_long = a.tab->valid_long, valid_short = a.tab->valid_short, fixable_short = a.tab->fixable_short;
@@ -177,19 +176,30 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
     uint32_t seg_n = 0;                            // uniform across the group
     unsigned long long my_preambles = 0;
 
-    // The groups of a CTA start together; a shorter first tile for every group but the first puts them
-    // out of step so that one group's dense phase A overlaps the sparse phases B..D of the others.
+    // The groups of a CTA start together; a.skew puts them out of step so that one group's dense phase A overlaps
+    // the sparse phases B..D of the others: 1 = groups 1.. start a fraction of a tile time late (costs no issue
+    // slots), 2 = a shorter first tile for every group but the first (one extra tile per group), 0 = nothing.
     int64_t tile_base = seg_begin;
-    int first_len = kTile - ((kTile / kGroups * grp) & ~7);
+    int first_len = a.skew == 2 ? kTile - ((kTile / kGroups * grp) & ~7) : kTile;
+    if (a.skew == 1 && grp) __nanosleep(a.skew_ns * grp);
     // a thread's 24 samples + the 4 samples of lookahead its correlators need: 3 x 16 B + 8 B of I/Q
     uint4 raw[3];
     uint2 rawx;
+    // tile-local sample indices [lo, hi) that exist in the feed: everything else comes from the carry / zero padding
+    auto valid_range = [&](int64_t x0t, int &lo, int &hi) {
+        lo = int(max(int64_t(0), -x0t));
+        hi = int(min(int64_t(kTileSamples + 8), n - x0t));
+    };
     auto load_raw = [&](int64_t base) {             // the tile whose first start position is `base`
-        const int64_t x = base - kOverlap - kTileLead + kRun * tid;
+        const int64_t x0t = base - kOverlap - kTileLead;
+        int lo, hi;
+        valid_range(x0t, lo, hi);
+        const int i = kRun * tid;
+        const uint8_t *p = a.iq + 2 * (x0t + i);
 #pragma unroll
         for (int r = 0; r < 3; ++r)
-            if (x + 8 * r >= 0 && x + 8 * r + 8 <= n) raw[r] = __ldg(reinterpret_cast<const uint4 *>(a.iq + 2 * (x + 8 * r)));
-        if (x + 24 >= 0 && x + 28 <= n) rawx = __ldg(reinterpret_cast<const uint2 *>(a.iq + 2 * (x + 24)));
+            if (i + 8 * r >= lo && i + 8 * r + 8 <= hi) raw[r] = __ldg(reinterpret_cast<const uint4 *>(p + 16 * r));
+        if (i + 24 >= lo && i + 28 <= hi) rawx = __ldg(reinterpret_cast<const uint2 *>(p + 48));
     };
     // magnitude of feed sample xe on the slow path (stream edges): carry, scalar I/Q, or zero padding
     auto mag_edge = [&](int64_t xe) -> uint32_t {
@@ -209,11 +219,14 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
         // ---- phase A: magnitudes, rising/falling edge bits and all slicer decisions of 24 samples -------
         {
             const int64_t x = x0 + kRun * tid;
+            const int i0 = kRun * tid;
+            int v_lo, v_hi;
+            valid_range(x0, v_lo, v_hi);
             uint32_t P[14];                          // P[k] = {mag[2k], mag[2k+1]} of this thread's run, k = 12, 13: lookahead
 #pragma unroll
             for (int r = 0; r < 3; ++r) {
                 const int64_t xv = x + 8 * r;
-                if (xv >= 0 && xv + 8 <= n) {
+                if (i0 + 8 * r >= v_lo && i0 + 8 * r + 8 <= v_hi) {
                     const uint4 d = raw[r];
                     const uint32_t c = central_bits(d.x) & central_bits(d.y) & central_bits(d.z) & central_bits(d.w);
                     if ((c & 0x80808080u) == 0x80808080u) {
@@ -229,7 +242,7 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
                 }
                 *reinterpret_cast<uint4 *>(&s_mag[kRun * tid + 8 * r]) = make_uint4(P[4 * r], P[4 * r + 1], P[4 * r + 2], P[4 * r + 3]);
             }
-            if (x + 24 >= 0 && x + 28 <= n) {
+            if (i0 + 24 >= v_lo && i0 + 28 <= v_hi) {
                 const uint32_t c = central_bits(rawx.x) & central_bits(rawx.y);
                 if ((c & 0x80808080u) == 0x80808080u) { P[12] = lut_pair(lut, rawx.x); P[13] = lut_pair(lut, rawx.y); }
                 else { P[12] = mag_pair_any(s_sq, rawx.x); P[13] = mag_pair_any(s_sq, rawx.y); }
