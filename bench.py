@@ -221,6 +221,17 @@ def main():
             step_resident()
     clocks = sampler.stop()
 
+    # host->device ceiling for the e2e arm: one plain pinned-memory copy of the same capture, CUDA events
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    h2d_ms = []
+    for _ in range(4):
+        ev0.record()
+        dev.copy_(host, non_blocking=True)
+        ev1.record()
+        torch.cuda.synchronize()
+        h2d_ms.append(ev0.elapsed_time(ev1))
+    h2d_gbs = 2.0 * n / (min(h2d_ms[1:]) * 1e-3) / 1e9
+
     for _ in range(2):
         step_e2e()
     barrier()
@@ -252,6 +263,8 @@ def main():
             "roofline": {"bound": "hbm", "kernel": "scan_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "peak_source": peak_src, "traffic": None,
                          "algorithmic_bytes_per_launch": 2 * n, "kernel_ms": k_ms},
+            "pcie": {"h2d_gbs": h2d_gbs, "h2d_ceiling_msamples_s": h2d_gbs * 1e3 / 2.0,
+                     "note": "plain pinned cudaMemcpy of the capture on this box; e2e cannot exceed world * this"},
             "breakdown_ms": {"scan": k_ms, "finalize": float(np.mean(fin_ms)), "host_resolve": float(np.mean(res_ms))},
             "messages_per_step": nmsg,
         }

@@ -149,7 +149,7 @@ typedef struct adsbcu_cand {
     uint32_t addr;
     uint32_t test_key;         /* argument of icaoFilterTest for this candidate */
     uint32_t add_key;          /* argument of icaoFilterAdd if accepted, 0xFFFFFFFF: none */
-    uint64_t sum_sq;           /* sum of squared magnitudes over the signal window */
+    double   signal_level;     /* mean squared magnitude over the signal window, full scale = 1.0 */
 } adsbcu_cand;
 #pragma pack(pop)
 #define ADSBCU_KNOWN_WORDS (1u << 20)   /* 2 x 2^24 bits: addresses that may enter the filter [ICAO | DF18 NT] */

@@ -26,7 +26,7 @@ assert UAT_DTYPE.itemsize == 448
 
 CAND_DTYPE = np.dtype([("pos", "<u8"), ("phase", "u1"), ("kind", "u1"), ("corrections", "i1"), ("msgtype", "u1"),
                        ("verbatim", "u1", 14), ("msg", "u1", 14), ("crc", "<u4"), ("addr", "<u4"), ("test_key", "<u4"),
-                       ("add_key", "<u4"), ("sum_sq", "<u8")])
+                       ("add_key", "<u4"), ("signal_level", "<f8")])
 assert CAND_DTYPE.itemsize == 64
 KNOWN_WORDS = 1 << 20
 

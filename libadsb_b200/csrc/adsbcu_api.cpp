@@ -103,7 +103,7 @@ struct adsbcu_handle {
     uint8_t *d_iq = nullptr;          // staging for host feeds
     uint32_t nseg = 0, seg_cap = 0, full_cap = 0;
     uint32_t skew = 0, skew_ns = 2500;   // measured on B200: no skew 0.5065 ms, sleep skew 0.506-0.516, short first tile 0.529 (profiles/sweep_skew.sh)
-    uint32_t unit_positions = 0, max_tps = 1;   // chunk = unit_positions * (tiles per segment), at most max_tps
+    uint32_t unit_positions = 0, max_tps = 1, host_tps = 4;   // chunk = unit_positions * (tiles per segment), at most max_tps
     Slot slot[kSlots];
     uint16_t *d_mag = nullptr;        // stage-level magnitude output
     size_t d_mag_cap = 0;
@@ -186,7 +186,7 @@ void copy_candidates(const FullRec *recs, size_t nrec, uint64_t feed_base, Sink 
         c.phase = r.phase; c.kind = r.kind; c.corrections = r.corrections; c.msgtype = r.msgtype;
         std::memcpy(c.verbatim, r.verbatim, 14);
         std::memcpy(c.msg, r.msg, 14);
-        c.crc = r.crc; c.addr = r.addr; c.test_key = r.test_key; c.add_key = r.add_key; c.sum_sq = r.sum_sq;
+        c.crc = r.crc; c.addr = r.addr; c.test_key = r.test_key; c.add_key = r.add_key; c.signal_level = r.signal_level;
     }
 }
 
@@ -194,6 +194,7 @@ template <class Rec>
 void resolve(adsbcu_handle *h, const Rec *recs, size_t nrec, uint64_t feed_base, Sink &sink)
 {
     const uint64_t block = h->cfg.block_samples;
+    uint64_t ts_blk = ~0ull, ts_bstart = 0, ts_base = 0;     // timestamp base of the mag_buf being replayed
     size_t i = 0;
     while (i < nrec) {
         const auto pos = recs[i].pos;
@@ -222,24 +223,20 @@ void resolve(adsbcu_handle *h, const Rec *recs, size_t nrec, uint64_t feed_base,
         const Rec &r = *bp;
         if (sink.n < sink.cap) {
             adsbcu_msg &m = sink.out[sink.n];
-            std::memset(&m, 0, sizeof(m));
             // sampleTimestamp of the block (sdr_ifile.c:202) + 5*j + 768 + phase: with 12e6/2.4e6 == 5 this
             // is 5*a + 768 + phase where a counts from the first overlap sample of the stream
-            const uint64_t bstart = (a / block) * block;
-            const uint64_t ts_block = uint64_t(double(bstart) * 12e6 / 2400000.0);
-            m.timestamp = ts_block + (a - bstart) * 5 + (8 + 56) * 12 + r.phase;
+            const uint64_t blk = a / block;
+            if (blk != ts_blk) { ts_blk = blk; ts_bstart = blk * block; ts_base = uint64_t(double(ts_bstart) * 12e6 / 2400000.0); }
+            m.timestamp = ts_base + (a - ts_bstart) * 5 + (8 + 56) * 12 + r.phase;
             std::memcpy(m.msg, r.msg, 14);
             std::memcpy(m.verbatim, r.verbatim, 14);
-            m.msgtype = r.msgtype;
             m.msgbits = (r.msgtype & 16) ? 112 : 56;
             m.correctedbits = uint8_t(r.corrections);
+            m.msgtype = r.msgtype;
             m.score = uint8_t(best);
             m.crc = r.crc;
             m.addr = r.addr;
-            const uint64_t sum_sq = r.sum_sq;      // (packed field: copy before use)
-            const int msglen = (r.verbatim[0] & 0x80) ? 112 : 56;
-            const int siglen = msglen * 12 / 5;
-            m.signal_level = (double(sum_sq) / 65535.0 / 65535.0) / siglen;
+            m.signal_level = r.signal_level;
         } else {
             sink.overflow = true;
         }
@@ -264,7 +261,9 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
     // chunk boundaries: the first chunks are short so that the pipeline (upload -> kernels -> host pass)
     // fills quickly, later ones long so that per-launch costs (LUT load, tail) are amortised
     std::vector<uint32_t> bounds{0};
-    for (uint32_t tps = std::min(4u, h->max_tps); bounds.back() < n; tps = std::min(2 * tps, h->max_tps))
+    // host feeds are bound by the upload: short chunks throughout keep the work left after the last byte arrived small
+    const uint32_t tps_cap = iq_host ? std::min(h->host_tps, h->max_tps) : h->max_tps;
+    for (uint32_t tps = std::min(4u, tps_cap); bounds.back() < n; tps = std::min(2 * tps, tps_cap))
         bounds.push_back(uint32_t(std::min<uint64_t>(n, uint64_t(bounds.back()) + uint64_t(h->unit_positions) * tps)));
     const uint32_t nchunks = uint32_t(bounds.size() - 1);
     float ms_h2d = 0.f;
@@ -437,6 +436,7 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
     uint32_t tps = 16;
     if (const char *e = std::getenv("ADSBCU_TILES_PER_SEG")) tps = uint32_t(std::max(1, std::atoi(e)));
     if (const char *e = std::getenv("ADSBCU_SKEW")) h->skew = uint32_t(std::atoi(e));
+    if (const char *e = std::getenv("ADSBCU_HOST_TPS")) h->host_tps = uint32_t(std::max(1, std::atoi(e)));
     if (const char *e = std::getenv("ADSBCU_SKEW_NS")) h->skew_ns = uint32_t(std::max(0, std::atoi(e)));
     const size_t nmax = c.max_feed_samples;
     h->nseg = uint32_t(h->sm_count) * uint32_t(kGroups);

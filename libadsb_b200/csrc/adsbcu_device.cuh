@@ -184,12 +184,13 @@ struct Diag {
     int nerr;       // -1: not correctable
     int b0, b1;
 };
-__device__ __forceinline__ Diag diagnose(uint32_t syn, const uint64_t *slots, uint32_t nslots)
+__device__ __forceinline__ Diag diagnose(uint32_t syn, const uint64_t *slots, uint32_t nslots, const uint32_t *occ)
 {
     Diag d{-1, 0, 0};
     if (syn == 0) { d.nerr = 0; return d; }
     uint32_t h = synd_hash(syn, nslots);
     for (;;) {
+        if (occ && !((occ[h >> 5] >> (h & 31)) & 1u)) return d;    // empty slot, known without touching the table
         const uint64_t e = slots[h];
         if (e == kSyndEmpty) return d;
         if (uint32_t(e & 0xFFFFFF) == syn) {
@@ -247,7 +248,9 @@ struct Classified {
     uint32_t test_key;     // argument of icaoFilterTest
 };
 
-__device__ __forceinline__ Classified classify(const Frame &in, uint32_t xs, uint32_t xl, const DevTables *t)
+// occ_long / occ_short: shared-memory copies of DevTables::occ_* (or nullptr)
+__device__ __forceinline__ Classified classify(const Frame &in, uint32_t xs, uint32_t xl, const DevTables *t,
+                                               const uint32_t *occ_long = nullptr, const uint32_t *occ_short = nullptr)
 {
     Classified r;
     r.keep = false; r.needs_known = true; r.kind = K_AP; r.corrections = -1; r.fixed = in; r.crc = 0; r.test_key = 0;
@@ -263,12 +266,12 @@ __device__ __forceinline__ Classified classify(const Frame &in, uint32_t xs, uin
     if (t->fixable_long & dfbit) {
         ls = xl;
         if ((df == 17 || df == 18) && ls == 0) { nc = 0; done = true; }
-        else le = diagnose(ls, t->synd_long, kSyndSlotsLong);
+        else le = diagnose(ls, t->synd_long, kSyndSlotsLong, occ_long);
     }
     if (!done && (t->fixable_short & dfbit)) {
         ss = xs;
         if (df == 11 && (ss & 0xFFFF80u) == 0) { nc = 0; done = true; }
-        else se = diagnose(ss, t->synd_short, kSyndSlotsShort);
+        else se = diagnose(ss, t->synd_short, kSyndSlotsShort, occ_short);
     }
     if (!done) {
         const unsigned lerr = le.nerr >= 0 ? unsigned(le.nerr) : 999u;

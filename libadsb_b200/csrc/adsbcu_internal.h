@@ -84,7 +84,7 @@ struct alignas(8) FullRec {
     uint32_t addr;         // mm.addr (with non-ICAO flag for DF18)
     uint32_t test_key;     // key for icaoFilterTest
     uint32_t add_key;      // key for icaoFilterAdd, kUnchecked if the message is not added
-    uint64_t sum_sq;       // sum of squared magnitudes over the signal window
+    double   signal_level; // mean squared magnitude over the signal window, full scale = 1.0
 };
 static_assert(sizeof(FullRec) == 64, "FullRec layout");
 
@@ -104,6 +104,8 @@ struct DevTables {
     int32_t  pad;
     uint64_t synd_long[kSyndSlotsLong];
     uint64_t synd_short[kSyndSlotsShort];
+    alignas(16) uint32_t occ_long[kSyndSlotsLong / 32];    // bit h: synd_long[h] is occupied (the scan keeps these in shared
+    alignas(16) uint32_t occ_short[kSyndSlotsShort / 32];  // memory: most probes end at an empty slot without a global load)
     alignas(16) uint32_t crc_byte[11][256];  // syndrome contribution of byte b (0..10) of a 112-bit frame having value v
     alignas(16) uint16_t mag_lut[32768];   // central 128 x 128 part (I, Q in [64, 192)) of the reference's uc8 magnitude
                                  // table (tables.c:9-41) in the bank-swizzled layout of lut_offset(); filled on the

@@ -63,6 +63,7 @@ struct ScanSmem {
     __align__(16) uint16_t lut[32768];         // DevTables::mag_lut
     uint32_t  crcb[11 * 256];
     float     sq[256];                         // DevTables::sq, for samples outside the central LUT
+    uint32_t  occ_long[kSyndSlotsLong / 32], occ_short[kSyndSlotsShort / 32];   // DevTables::occ_*
     GroupSmem grp[kGroups];
 };
 static_assert(sizeof(ScanSmem) <= 227 * 1024, "scan kernel shared memory exceeds the sm_100 per-CTA limit");
@@ -138,7 +139,7 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
         }
         __syncthreads();
         if (threadIdx.x == 0) {
-            constexpr uint32_t kLutBytes = 32768 * 2, kCrcBytes = 11 * 256 * 4, kSqBytes = 256 * 4;
+            constexpr uint32_t kLutBytes = 32768 * 2, kCrcBytes = 11 * 256 * 4, kSqBytes = 256 * 4 + kSyndSlotsLong / 8 + kSyndSlotsShort / 8;
             asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(kLutBytes + kCrcBytes + kSqBytes) : "memory");
             for (uint32_t o = 0; o < kLutBytes; o += 32768u)
                 asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -146,7 +147,9 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
             asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                          ::"r"(uint32_t(__cvta_generic_to_shared(sm.crcb))), "l"(&a.tab->crc_byte[0][0]), "r"(kCrcBytes), "r"(bar) : "memory");
             asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                         ::"r"(uint32_t(__cvta_generic_to_shared(sm.sq))), "l"(a.tab->sq), "r"(kSqBytes), "r"(bar) : "memory");
+                         ::"r"(uint32_t(__cvta_generic_to_shared(sm.sq))), "l"(a.tab->sq), "r"(256u * 4u), "r"(bar) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(uint32_t(__cvta_generic_to_shared(sm.occ_long))), "l"(a.tab->occ_long), "r"(uint32_t(kSyndSlotsLong / 8 + kSyndSlotsShort / 8)), "r"(bar) : "memory");
         }
         uint32_t done = 0;
         while (!done)
@@ -268,14 +271,14 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
                 const int nd2 = nd_at(e + 2);
                 G = __funnelshift_l(uint32_t(nd0), G, 1);
                 L = __funnelshift_l(uint32_t(-nd0), L, 1);
+                // the five negated correlators, each at most three operations deep
                 const int step = nd1 - nd0;
-                int v = 5 * nd0 + 2 * nd1;           // -(5 d0 + 2 d1)
+                const int v0 = 5 * nd0 + 2 * nd1;     // -(5 d0 + 2 d1)
+                const int v[5] = {v0, v0 + step, 2 * step + v0, 3 * step + v0, 4 * step + (v0 + nd2)};
 #pragma unroll
                 for (int sub = 0; sub < 5; ++sub) {
-                    if (sub == 4) v += nd2;
                     const int c = (5 * e + sub) % 12;
-                    acc[c] = __funnelshift_l(uint32_t(v), acc[c], 1);
-                    v += step;
+                    acc[c] = __funnelshift_l(uint32_t(v[sub]), acc[c], 1);
                 }
                 nd0 = nd1; nd1 = nd2;
             }
@@ -288,7 +291,7 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
                 gs.u.edge.gbits[3 * tid + r] = uint8_t(G >> (8 * r));
             }
         }
-        if (tid == 0) { gs.npre = 0; gs.ncand = 0; gs.nkeep = 0; }
+        if (tid == 0) { gs.npre = 0; gs.ncand = 0; gs.nkeep = 0; gs.nq[0] = 0; gs.nq[1] = 0; }
         if (next_base < seg_end) load_raw(next_base);                   // in flight during phases B..D
         group_sync(grp);
 
@@ -339,8 +342,10 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
         // C2 one item per thread: 56 / 112 plane bits, CRC-24 syndromes, repair, classification.
         const uint32_t ncand = min(gs.ncand, uint32_t(kCandCap));
         for (uint32_t c0 = 0; c0 < ncand; c0 += kCandChunk) {
-            if (tid < 2) gs.nq[tid] = 0;
-            group_sync(grp);
+            if (c0) {                                // (the first round's counters were cleared before phase B)
+                if (tid < 2) gs.nq[tid] = 0;
+                group_sync(grp);
+            }
             const uint32_t nitems = min(uint32_t(kCandChunk), ncand - c0) * 5u;
             for (uint32_t it = tid; it < nitems; it += kGroupThreads) {
                 const uint32_t pos = gs.cand[c0 + it / 5u];
@@ -375,7 +380,7 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
                     M[1] &= 0xFFFFFF00u;
                     xs = crc_short(M, s_crcb);
                 }
-                const Classified cl = classify(frame_from_words(M, is_long), xs, xl, a.tab);
+                const Classified cl = classify(frame_from_words(M, is_long), xs, xl, a.tab, sm.occ_long, sm.occ_short);
                 if (!cl.keep) continue;
                 const uint32_t bi = bitmap_index(cl.test_key);
                 if (cl.kind == K_DF17_0 || cl.kind == K_DF11_ACQ_0 || (cl.kind == K_DF18_0 && !df18_non_icao(cl.fixed)))
@@ -629,7 +634,8 @@ __global__ void __launch_bounds__(256) evaluate_kernel(ScanArgs a)
                 break;
             default: q.addr = c.crc; break;
             }
-            q.sum_sq = acc;
+            // mm.signalLevel (demod_2400.c:382-403): IEEE double divisions, the same on the device as on the host
+            q.signal_level = double(acc) / 65535.0 / 65535.0 / double(siglen);
         }
         __syncwarp();
         if (lane < 4) reinterpret_cast<uint4 *>(&a.full[o])[lane] = reinterpret_cast<const uint4 *>(&s_rec[warp])[lane];

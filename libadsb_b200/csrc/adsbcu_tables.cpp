@@ -130,6 +130,10 @@ void build_tables(DevTables &t, int nfix_crc, int fix_df)
     }
     build_synd(t.bit_synd, 112, nfix, nfix == 2 ? 4 : nfix, t.synd_long, kSyndSlotsLong);
     build_synd(t.bit_synd, 56, nfix, nfix == 2 ? 4 : nfix, t.synd_short, kSyndSlotsShort);
+    std::memset(t.occ_long, 0, sizeof(t.occ_long));
+    std::memset(t.occ_short, 0, sizeof(t.occ_short));
+    for (int h = 0; h < kSyndSlotsLong; ++h) if (t.synd_long[h] != kSyndEmpty) t.occ_long[h >> 5] |= 1u << (h & 31);
+    for (int h = 0; h < kSyndSlotsShort; ++h) if (t.synd_short[h] != kSyndEmpty) t.occ_short[h >> 5] |= 1u << (h & 31);
 }
 
 }  // namespace adsbcu

@@ -22,6 +22,7 @@ def cands_from_records(recs):
     c["phase"] = ts - 768 - 5 * c["pos"].astype(np.int64)
     c["corrections"], c["msgtype"] = recs["correctedbits"], recs["msgtype"]
     c["verbatim"], c["msg"], c["crc"], c["addr"] = recs["verbatim"], recs["msg"], recs["crc"], recs["addr"]
+    c["signal_level"] = recs["signal_level"]
     for i, r in enumerate(recs):
         df, nc, addr, crc = int(r["msgtype"]), int(r["correctedbits"]), int(r["addr"]), int(r["crc"])
         kind, test, add = 0, crc, NONE                       # K_AP
@@ -36,8 +37,6 @@ def cands_from_records(recs):
             kind, test = (1 if acq else 2) + 2 * nc, addr
             add = addr if (acq and nc == 0) else NONE
         c["kind"][i], c["test_key"][i], c["add_key"][i] = kind, test, add
-        siglen = (112 if r["verbatim"][0] & 0x80 else 56) * 12 // 5
-        c["sum_sq"][i] = int(round(float(r["signal_level"]) * siglen * 65535.0 * 65535.0))
     return c
 
 
