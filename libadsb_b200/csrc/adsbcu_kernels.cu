@@ -24,6 +24,13 @@ namespace adsbcu {
 
 namespace {
 
+#ifdef ADSBCU_PHASE_TIMING           // debug: cycles between group barriers, summed over all groups (thread 0 of each)
+__device__ unsigned long long g_phase_cycles[8];
+// PHASE_MARK(k): the interval that ends here belongs to slot k
+#define PHASE_MARK(k) do { if (tid == 0) { const long long t_now = clock64(); if (t_prev) atomicAdd(&g_phase_cycles[k], (unsigned long long)(t_now - t_prev)); t_prev = t_now; } } while (0)
+#else
+#define PHASE_MARK(k) do { } while (0)
+#endif
 constexpr int kPreCap = kTileSamples / 4;      // positions passing the edge masks, per tile
 constexpr int kCandCap = kTileSamples / 8;     // preambles kept per tile (overflow -> error, never silently dropped)
 constexpr int kCandChunk = kGroupThreads;      // preambles per slicer round
@@ -183,8 +190,12 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
     // the sparse phases B..D of the others: 1 = groups 1.. start a fraction of a tile time late (costs no issue
     // slots), 2 = a shorter first tile for every group but the first (one extra tile per group), 0 = nothing.
     int64_t tile_base = seg_begin;
+#ifdef ADSBCU_PHASE_TIMING
+    long long t_prev = 0;
+#endif
     int first_len = a.skew == 2 ? kTile - ((kTile / kGroups * grp) & ~7) : kTile;
     if (a.skew == 1 && grp) __nanosleep(a.skew_ns * grp);
+    if (a.skew >= 10 && grp >= int(a.skew - 10)) tile_base = seg_end;   // timing experiment only: idle groups
     // a thread's 24 samples + the 4 samples of lookahead its correlators need: 3 x 16 B + 8 B of I/Q
     uint4 raw[3];
     uint2 rawx;
@@ -213,6 +224,7 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
     if (tile_base < seg_end) load_raw(tile_base);
     while (tile_base < seg_end) {
         group_sync(grp);   // previous tile fully consumed
+        PHASE_MARK(1);
         const int npos = int(min(int64_t(first_len), seg_end - tile_base));   // start positions in this tile
         first_len = kTile;
         const int64_t next_base = tile_base + npos;
@@ -294,6 +306,7 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
         if (tid == 0) { gs.npre = 0; gs.ncand = 0; gs.nkeep = 0; gs.nq[0] = 0; gs.nq[1] = 0; }
         if (next_base < seg_end) load_raw(next_base);                   // in flight during phases B..D
         group_sync(grp);
+        PHASE_MARK(2);
 
         // ---- phase B: preamble edge patterns, 32 start positions per thread ----------------------
         if (tid < kPosWords) {
@@ -323,6 +336,7 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
             }
         }
         group_sync(grp);
+        PHASE_MARK(3);
         {   // full preamble test (signal/noise ratio, quiet zones) on the compacted list
             const uint32_t npre = min(gs.npre, uint32_t(kPreCap));
             for (uint32_t i = tid; i < npre; i += kGroupThreads) {
@@ -335,6 +349,7 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
             }
         }
         group_sync(grp);
+        PHASE_MARK(4);
 
         // ---- phase C: messages are bit strings of the symbol planes ----------------------------------
         // C1 reads the DF field (5 bits) of every (preamble, phase) and queues the items the DF pre-filter
@@ -359,6 +374,7 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
                 else if (valid_short & dfbit) gs.queue[kQueueCap - 1 - atomicAdd(&gs.nq[1], 1u)] = item;
             }
             group_sync(grp);
+            PHASE_MARK(5);
             const uint32_t nlong = gs.nq[0], nshort = gs.nq[1];
             for (uint32_t it = tid; it < nlong + nshort; it += kGroupThreads) {
                 const bool is_long = it < nlong;
@@ -396,6 +412,7 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
         // ---- phase D: ordered emission of this tile's records into the segment ----------------
         // counting sort by 64-position bucket, then rank inside the (tiny) bucket
         group_sync(grp);
+        PHASE_MARK(6);
         const uint32_t nkeep = min(gs.nkeep, uint32_t(kKeepCap));
         uint32_t *hist = gs.hist, *start = hist + kBuckets, *fill = hist + 2 * kBuckets;
         uint2 *sorted = gs.u.sorted;
@@ -405,8 +422,10 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
         } else if (nkeep) {
             for (int i = tid; i < kBuckets; i += kGroupThreads) { hist[i] = 0; fill[i] = 0; }
             group_sync(grp);
+            PHASE_MARK(7);
             for (uint32_t i = tid; i < nkeep; i += kGroupThreads) atomicAdd(&hist[gs.keep[i].x >> kBucketShift], 1u);
             group_sync(grp);
+            PHASE_MARK(7);
             if (tid < 32) {
                 constexpr int kPer = kBuckets / 32;
                 uint32_t c[kPer], sum = 0;
@@ -420,11 +439,13 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
                 for (int k = 0; k < kPer; ++k) { start[kPer * tid + k] = run; run += c[k]; }
             }
             group_sync(grp);
+            PHASE_MARK(7);
             for (uint32_t i = tid; i < nkeep; i += kGroupThreads) {
                 const uint2 me = gs.keep[i];
                 sorted[start[me.x >> kBucketShift] + atomicAdd(&fill[me.x >> kBucketShift], 1u)] = me;
             }
             group_sync(grp);
+            PHASE_MARK(7);
             for (uint32_t i = tid; i < nkeep; i += kGroupThreads) {
                 const uint2 me = sorted[i];
                 const uint32_t lo = start[me.x >> kBucketShift], hi = lo + hist[me.x >> kBucketShift];
@@ -685,6 +706,15 @@ __global__ void __launch_bounds__(256) magnitude_kernel(const uint8_t *iq, uint3
 }
 
 }  // namespace
+
+#ifdef ADSBCU_PHASE_TIMING
+extern "C" void adsbcu_debug_phase_cycles(unsigned long long *out, int reset)
+{
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, g_phase_cycles, sizeof(g_phase_cycles));
+    if (reset) { unsigned long long z[8] = {}; cudaMemcpyToSymbol(g_phase_cycles, z, sizeof(z)); }
+}
+#endif
 
 cudaError_t init_kernels()
 {
