@@ -194,9 +194,16 @@ template <class Rec>
 void resolve(adsbcu_handle *h, const Rec *recs, size_t nrec, uint64_t feed_base, Sink &sink)
 {
     const uint64_t block = h->cfg.block_samples;
+    // mag_buf index of a stream coordinate; block_samples is a power of two unless a test shrinks it oddly
+    const int bshift = (block & (block - 1)) == 0 ? __builtin_ctzll(block) : -1;
+    auto blk_of = [&](uint64_t x) { return bshift >= 0 ? x >> bshift : x / block; };
+    uint64_t last_blk = h->has_last ? blk_of(h->last_a) : 0;
     uint64_t ts_blk = ~0ull, ts_bstart = 0, ts_base = 0;     // timestamp base of the mag_buf being replayed
     size_t i = 0;
     while (i < nrec) {
+        // the records were written by the GPU into mapped host memory: keep a few cache lines in flight
+        __builtin_prefetch(reinterpret_cast<const char *>(recs + i) + 1024);
+        __builtin_prefetch(reinterpret_cast<const char *>(recs + i) + 1088);
         const auto pos = recs[i].pos;
         const uint64_t a = feed_base + pos;
         size_t e = i + 1;
@@ -204,18 +211,18 @@ void resolve(adsbcu_handle *h, const Rec *recs, size_t nrec, uint64_t feed_base,
         if (h->has_last) {
             // inside the mag_buf of the last accepted message scanning resumes 18 samples before its
             // end (j = last_message_end - 19, then ++j); a later mag_buf starts exactly at its end
-            const bool same_block = (a / block) == (h->last_a / block);
+            const bool same_block = blk_of(a) == last_blk;
             if (a < (same_block ? h->last_lme - 18 : h->last_lme)) { i = e; continue; }
         }
 
         int best = 0;                       // SR_NOT_SET
         const Rec *bp = nullptr;
-        uint32_t last_key = kUnchecked;
-        bool last_known = false;
+        uint32_t last_key = kUnchecked, best_key = kUnchecked;
+        bool last_known = false, best_known = false;
         for (size_t k = i; k < e; ++k) {    // phases ascending; strict > keeps the lowest phase on ties
             if (const uint32_t key = recs[k].test_key; key != last_key) { last_key = key; last_known = h->filter.test(key); }
             const int sc = rank_of(recs[k].kind, last_known);
-            if (sc > best) { best = sc; bp = &recs[k]; }
+            if (sc > best) { best = sc; bp = &recs[k]; best_key = last_key; best_known = last_known; }
         }
         i = e;
         if (best < kAcceptThreshold) continue;
@@ -225,7 +232,7 @@ void resolve(adsbcu_handle *h, const Rec *recs, size_t nrec, uint64_t feed_base,
             adsbcu_msg &m = sink.out[sink.n];
             // sampleTimestamp of the block (sdr_ifile.c:202) + 5*j + 768 + phase: with 12e6/2.4e6 == 5 this
             // is 5*a + 768 + phase where a counts from the first overlap sample of the stream
-            const uint64_t blk = a / block;
+            const uint64_t blk = blk_of(a);
             if (blk != ts_blk) { ts_blk = blk; ts_bstart = blk * block; ts_base = uint64_t(double(ts_bstart) * 12e6 / 2400000.0); }
             m.timestamp = ts_base + (a - ts_bstart) * 5 + (8 + 56) * 12 + r.phase;
             std::memcpy(m.msg, r.msg, 14);
@@ -241,11 +248,13 @@ void resolve(adsbcu_handle *h, const Rec *recs, size_t nrec, uint64_t feed_base,
             sink.overflow = true;
         }
         ++sink.n;
-        if (const uint32_t add_key = r.add_key; add_key != kUnchecked) h->filter.add(add_key);
+        // icaoFilterAdd of an address the filter just reported as present is a no-op: skip its hash + probe
+        if (const uint32_t add_key = r.add_key; add_key != kUnchecked && !(add_key == best_key && best_known)) h->filter.add(add_key);
 
         // skip rule (demod_2400.c:410-419, :432-443): remember where this message ends
         h->has_last = true;
         h->last_a = a;
+        last_blk = blk_of(a);
         h->last_lme = a + uint64_t((((r.verbatim[0] & 0x80) ? 112 : 56) + 8) * 12 / 5);
     }
 }
