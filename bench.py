@@ -123,7 +123,7 @@ def cpu_baseline(iq: np.ndarray, nfix: int, cores: int, sample_desc: str):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--seconds", type=float, default=60.0, help="capture length per GPU (config 2: 60 s)")
@@ -251,8 +251,14 @@ def main():
 
     if rank == 0:
         peak, peak_src = load_peaks()
-        k_ms = float(np.mean(scan_ms))
+        k_ms = float(np.mean(scan_ms))                    # all scan_kernel launches of one step (one per chunk)
         achieved = 2.0 * n / (k_ms * 1e-3) / 1e9
+        scan_per_step = (launches // args.steps - 2 - 1) // 3    # per chunk: scan, filter, evaluate; + carry + 2 memsets
+        try:
+            with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+                traffic_ratio = float(json.load(f)["traffic_over_algorithmic"])
+        except Exception:
+            traffic_ratio = None
         line = {
             "metric": METRIC, "value": world * n * args.steps / t_res / 1e6, "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_res / args.steps * 1e3,
@@ -261,8 +267,13 @@ def main():
             "e2e": {"value": world * n * args.steps / t_e2e / 1e6, "unit": UNIT, "h2d_bytes_per_step": 2 * n,
                     "d2h_bytes_per_step": d2h // args.steps},
             "roofline": {"bound": "hbm", "kernel": "scan_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "peak_source": peak_src, "traffic": None,
-                         "algorithmic_bytes_per_launch": 2 * n, "kernel_ms": k_ms},
+                         "frac": achieved / peak, "peak_source": peak_src,
+                         "launches_per_step": scan_per_step,
+                         "algorithmic_bytes_per_launch": 2 * n / max(scan_per_step, 1),
+                         "avg_launch_ms": k_ms / max(scan_per_step, 1),
+                         "traffic": None if traffic_ratio is None else traffic_ratio * 2 * n / max(scan_per_step, 1),
+                         "traffic_source": "profiles/ncu_traffic.json: dram read+write of one ncu --set full launch / its algorithmic bytes",
+                         "kernel_ms_per_step": k_ms},
             "pcie": {"h2d_gbs": h2d_gbs, "h2d_ceiling_msamples_s": h2d_gbs * 1e3 / 2.0,
                      "note": "plain pinned cudaMemcpy of the capture on this box; e2e cannot exceed world * this"},
             "breakdown_ms": {"scan": k_ms, "finalize": float(np.mean(fin_ms)), "host_resolve": float(np.mean(res_ms))},

@@ -120,3 +120,39 @@ def demod_sharded(d: adsbcu.Demod1090, group, iq: np.ndarray, resolver: adsbcu.D
     if group.rank != 0:
         return None
     return np.concatenate(msgs) if msgs else np.zeros(0, adsbcu.MSG_DTYPE)
+
+
+def _selftest():
+    """torchrun --nproc-per-node N -m libadsb_b200.shard : one capture over N GPUs == the reference's message set
+    (tests/golden/c3_dense.npz was produced by the reference binary) and == the single-GPU stream."""
+    import os
+    import torch
+    import torch.distributed as dist
+    rank, local = int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    group = TorchGroup(device=torch.device("cuda", local))
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    with np.load(os.path.join(root, "tests", "golden", "c3_dense.npz")) as z:
+        iq, ref = z["iq"], z["ref_fix2_df1"]
+    d = adsbcu.Demod1090(2, 1, device=local)
+    resolver = adsbcu.Demod1090(2, 1, device=-1) if rank == 0 else None
+    ok = True
+    for window in (iq.size // 2, 100_000):
+        if resolver is not None:
+            resolver.reset(True)
+        d.reset(True)
+        got = demod_sharded(d, group, iq, resolver=resolver, window_samples=window)
+        if rank == 0:
+            same = len(got) == len(ref) and all(np.array_equal(got[f], ref[f]) for f in
+                                                ("timestamp", "msg", "verbatim", "correctedbits", "score", "crc", "addr"))
+            print(f"shard selftest: world={group.world} window={window}: {len(got)} messages, "
+                  f"{'bit-identical to the reference' if same else 'MISMATCH'}")
+            ok = ok and same
+    dist.destroy_process_group()
+    if not ok:
+        raise SystemExit(1)
+
+
+if __name__ == "__main__":
+    _selftest()
