@@ -1,0 +1,70 @@
+#!/usr/bin/env python
+"""Secondary timing lines (not the headline metric): Path B (libadsb's own 2.0 MS/s handler) and Path C
+(UAT 978) through their C-ABI entry points with HOST buffers, next to their CPU checkers on one core.
+usage: python profiles/bench_paths.py [seconds]   -> one JSON line per path"""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from libadsb_b200 import adsbcu, synth, synth978   # noqa: E402
+
+seconds = float(sys.argv[1]) if len(sys.argv) > 1 else 10.0
+BUF = 262144   # RTLSDR.hpp:55: bytes per HandleData call in live mode
+
+
+def timed(fn, reps=3):
+    fn()
+    t = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        n = fn()
+        t.append(time.perf_counter() - t0)
+    return min(t), n
+
+
+# ---- Path B: one HandleData call per 262144-byte buffer, and one call per 8 MB (the largest the reference's
+# fixed magnitude vector allows, ADSB1090.cpp:109)
+iq = synth.config_b(seconds=seconds, seed=0x1090B002)[0]
+d = adsbcu.Demod1090()
+for name, step in (("262144-byte buffers", BUF), ("8 MiB buffers", 8 << 20)):
+    def run_b():
+        d.reset_b()
+        return sum(len(d.handle_data_b(iq[k:k + step], cap=1 << 17)) for k in range(0, iq.size, step))
+    dt, n = timed(run_b)
+    line = {"path": "B (ADSB1090Handler, 2.0 MS/s)", "feed": name, "msamples_s": iq.size / 2 / dt / 1e6, "messages": n,
+            "realtime_factor": iq.size / 2 / dt / 2.0e6}
+    print(json.dumps(line))
+try:
+    from oracle import oracle1090b as B
+    part = iq[:min(iq.size, 16 * BUF)]
+    o = B.Oracle1090B()
+    t0 = time.perf_counter()
+    for k in range(0, part.size, BUF):
+        o.handle_data(part[k:k + BUF])
+    print(json.dumps({"path": "B cpu checker (1 core)", "msamples_s": part.size / 2 / (time.perf_counter() - t0) / 1e6}))
+except Exception as e:   # the checker is optional here
+    print(json.dumps({"path": "B cpu checker", "unavailable": repr(e)}))
+
+# ---- Path C
+iq = synth978.config5(seconds=seconds)[0]
+for name, step in (("262144-byte buffers", BUF), ("whole capture", iq.size)):
+    def run_c():
+        d.reset_uat()
+        return sum(len(d.handle_data_uat(iq[k:k + step])) for k in range(0, iq.size, step))
+    dt, n = timed(run_c)
+    print(json.dumps({"path": "C (UAT978Handler, 2.083334 MS/s)", "feed": name, "msamples_s": iq.size / 2 / dt / 1e6,
+                      "frames": n, "realtime_factor": iq.size / 2 / dt / 2083334.0}))
+try:
+    from oracle import oracle978 as O
+    part = iq[:min(iq.size, 16 * BUF)]
+    o = O.Oracle978()
+    t0 = time.perf_counter()
+    for k in range(0, part.size, BUF):
+        o.handle_data(part[k:k + BUF])
+    print(json.dumps({"path": "C cpu checker (1 core)", "msamples_s": part.size / 2 / (time.perf_counter() - t0) / 1e6}))
+except Exception as e:
+    print(json.dumps({"path": "C cpu checker", "unavailable": repr(e)}))
