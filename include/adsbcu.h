@@ -174,6 +174,19 @@ int adsbcu_1090_revive(adsbcu_handle *h, adsbcu_cand *out, size_t cap, size_t *n
 int adsbcu_1090_resolve(adsbcu_handle *h, const adsbcu_cand *cands, size_t n,
                         adsbcu_msg *out, size_t cap, size_t *n_out);
 
+/* ---- Mode A/C on one mag_buf (dump1090 --modeac) ----------------------------------------------------
+ * One call == one demodulate2400AC(struct mag_buf*) call of the reference (demod_2400.c:539-726), which
+ * dump1090's main loop makes right after demodulate2400 on the same buffer (dump1090.c:902-905).  The
+ * detector's noise level is the mean level / power of THIS buffer's new samples (demod_2400.c:550-551,
+ * magnitude_power_uc8.c:48-90), so the unit is the reference's mag_buf: `iq` holds the buffer's nsamples new
+ * samples (131072 in live mode), `overlap_iq` the n_overlap <= 326 samples that preceded it (fewer only at the
+ * start of a stream, where the reference's overlap is zero magnitudes), both HOST memory.  block_timestamp is
+ * mag->sampleTimestamp (12 MHz).  Replies come back as adsbcu_msg with msgtype 32, msgbits 16, msg[0..1] the
+ * Mode A code in the reference's layout and addr = code | MODES_NON_ICAO_ADDRESS (mode_ac.c:123-158). */
+int adsbcu_1090_modeac_block(adsbcu_handle *h, const uint8_t *iq, size_t nsamples,
+                             const uint8_t *overlap_iq, size_t n_overlap, uint64_t block_timestamp,
+                             adsbcu_msg *out, size_t cap, size_t *n_out);
+
 /* ---- Path B: the 1090 MHz demodulator libadsb itself compiles (2.0 MS/s) --------------------
  * Replaces the body of ADSB1090Handler::HandleData (reference ADSB1090.cpp:158-175) down to the
  * point where the reference calls UseModesMessage() with mm.crcok set (ADSB1090.cpp:741-959,

@@ -34,7 +34,7 @@ EXPORTS = ["adsbcu_abi_version", "adsbcu_last_error", "adsbcu_create", "adsbcu_d
            "adsbcu_1090_feed", "adsbcu_1090_feed_device", "adsbcu_1090_magnitude", "adsbcu_1090_filter_add",
            "adsbcu_1090_filter_test", "adsbcu_get_stats", "adsbcu_1090b_feed", "adsbcu_1090b_reset",
            "adsbcu_978_feed", "adsbcu_978_reset", "adsbcu_978_phase", "adsbcu_1090_seek", "adsbcu_1090_scan_candidates",
-           "adsbcu_1090_known_export", "adsbcu_1090_known_import", "adsbcu_1090_revive", "adsbcu_1090_resolve"]
+           "adsbcu_1090_known_export", "adsbcu_1090_known_import", "adsbcu_1090_revive", "adsbcu_1090_resolve", "adsbcu_1090_modeac_block"]
 
 
 class Config(C.Structure):
@@ -86,6 +86,8 @@ def load():
         L.adsbcu_1090_known_import.argtypes = [C.c_void_p, C.c_void_p]
         L.adsbcu_1090_revive.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.adsbcu_1090_resolve.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.adsbcu_1090_modeac_block.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_uint64, C.c_void_p,
+                                               C.c_size_t, C.POINTER(C.c_size_t)]
         _lib = L
     return _lib
 
@@ -209,6 +211,16 @@ class Demod1090:
         out = np.zeros(cap if cap is not None else max(16, len(cands)), dtype=MSG_DTYPE)
         got = C.c_size_t(0)
         self._check(load().adsbcu_1090_resolve(self.h, cands.ctypes.data, len(cands), out.ctypes.data, len(out), C.byref(got)))
+        return out[:got.value]
+
+    def modeac_block(self, iq: np.ndarray, overlap_iq: np.ndarray | None, block_timestamp: int, cap: int = 1 << 15) -> np.ndarray:
+        """One demodulate2400AC(mag_buf) call: `iq` = the buffer's new samples, `overlap_iq` = the <= 326 samples before it."""
+        iq = np.ascontiguousarray(iq, dtype=np.uint8)
+        ov = np.ascontiguousarray(overlap_iq if overlap_iq is not None else np.zeros(0, np.uint8), dtype=np.uint8)
+        out = np.zeros(cap, dtype=MSG_DTYPE)
+        got = C.c_size_t(0)
+        self._check(load().adsbcu_1090_modeac_block(self.h, iq.ctypes.data, iq.size // 2, ov.ctypes.data if ov.size else None,
+                                                    ov.size // 2, block_timestamp, out.ctypes.data, cap, C.byref(got)))
         return out[:got.value]
 
     def filter_add(self, addr): self._check(load().adsbcu_1090_filter_add(self.h, addr))

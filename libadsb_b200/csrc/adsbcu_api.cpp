@@ -123,6 +123,11 @@ struct adsbcu_handle {
     PhaseRec *d_deferred = nullptr;
     uint32_t *d_n_deferred = nullptr, *d_known_tmp = nullptr;
     uint32_t deferred_cap = 0;
+    // Mode A/C (adsbcu_1090_modeac_block)
+    uint8_t *d_ac_ov = nullptr;
+    unsigned long long *d_ac_sums = nullptr;      // [2] sums, then the record counter
+    AcRec *d_ac_rec = nullptr, *h_ac_rec = nullptr;
+    uint32_t ac_cap = 0;
     const uint8_t *last_iq = nullptr; // device samples of the last candidate scan
     uint32_t last_n = 0;
     uint64_t last_base = 0;
@@ -144,6 +149,8 @@ void free_all(adsbcu_handle *h)
 {
     if (h->host_only) return;
     cudaSetDevice(h->device);
+    cudaFree(h->d_ac_ov); cudaFree(h->d_ac_sums); cudaFree(h->d_ac_rec);
+    if (h->h_ac_rec) cudaFreeHost(h->h_ac_rec);
     cudaFree(h->d_carry_prev); cudaFree(h->d_deferred); cudaFree(h->d_n_deferred); cudaFree(h->d_known_tmp);
     if (h->stream) cudaStreamSynchronize(h->stream);
     pathb_free(h->pathb);
@@ -725,6 +732,79 @@ int adsbcu_1090_resolve(adsbcu_handle *h, const adsbcu_cand *cands, size_t n, ad
     resolve(h, cands, n, 0, sink);
     if (n_out) *n_out = sink.n;
     if (sink.overflow) { h->error = "out[] too small for the accepted messages"; return ADSBCU_ERR_OVERFLOW; }
+    return ADSBCU_OK;
+}
+
+int adsbcu_1090_modeac_block(adsbcu_handle *h, const uint8_t *iq, size_t nsamples, const uint8_t *overlap_iq, size_t n_overlap,
+                             uint64_t block_timestamp, adsbcu_msg *out, size_t cap, size_t *n_out)
+{
+    if (!h) return ADSBCU_ERR_ARG;
+    if (n_out) *n_out = 0;
+    NEED_DEVICE(h);
+    if ((!iq && nsamples) || (!out && cap) || (n_overlap && !overlap_iq) || n_overlap > size_t(kOverlap) ||
+        nsamples > h->cfg.max_feed_samples) {
+        h->error = "bad argument (null pointer, more than 326 overlap samples, or nsamples > max_feed_samples)";
+        return ADSBCU_ERR_ARG;
+    }
+    if (nsamples < 2) return ADSBCU_OK;
+    CK(cudaSetDevice(h->device));
+    const uint32_t n = uint32_t(nsamples);
+    const uint32_t want = std::max<uint32_t>(4096u, n / 16);
+    if (h->ac_cap < want) {
+        cudaFree(h->d_ac_rec); h->d_ac_rec = nullptr;
+        if (h->h_ac_rec) { cudaFreeHost(h->h_ac_rec); h->h_ac_rec = nullptr; }
+        h->ac_cap = 0;
+        CK(cudaMalloc(&h->d_ac_rec, size_t(want) * sizeof(AcRec)));
+        CK(cudaHostAlloc(&h->h_ac_rec, size_t(want) * sizeof(AcRec), cudaHostAllocDefault));
+        h->ac_cap = want;
+    }
+    if (!h->d_ac_ov) {
+        CK(cudaMalloc(&h->d_ac_ov, 2 * kOverlap + 64));
+        CK(cudaMalloc(&h->d_ac_sums, 4 * sizeof(unsigned long long)));
+    }
+    const size_t need_mag = nsamples + kOverlap + kAcLead + 64;
+    if (h->d_mag_cap < need_mag) {
+        cudaFree(h->d_mag); h->d_mag = nullptr; h->d_mag_cap = 0;
+        CK(cudaMalloc(&h->d_mag, need_mag * sizeof(uint16_t) + 64));
+        h->d_mag_cap = need_mag;
+    }
+    uint32_t *d_count = reinterpret_cast<uint32_t *>(h->d_ac_sums + 2);
+    if (n_overlap) CK(cudaMemcpyAsync(h->d_ac_ov, overlap_iq, 2 * n_overlap, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(h->d_iq, iq, 2 * nsamples, cudaMemcpyHostToDevice, h->stream));
+    CK(launch_modeac(h->d_tab, h->sm_count, h->stream, h->d_iq, n, h->d_ac_ov, uint32_t(n_overlap), h->d_mag, h->d_ac_sums,
+                     h->d_ac_rec, h->ac_cap, d_count));
+    uint32_t count = 0;
+    CK(cudaMemcpyAsync(&count, d_count, sizeof(count), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    if (count > h->ac_cap) { h->error = "Mode A/C candidate list overflow"; return ADSBCU_ERR_OVERFLOW; }
+    if (count) {
+        CK(cudaMemcpyAsync(h->h_ac_rec, h->d_ac_rec, size_t(count) * sizeof(AcRec), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    std::sort(h->h_ac_rec, h->h_ac_rec + count, [](const AcRec &x, const AcRec &y) { return x.f1 < y.f1; });
+    size_t nmsg = 0;
+    bool overflow = false;
+    uint32_t next_ok = 0;
+    for (uint32_t k = 0; k < count; ++k) {
+        const AcRec &r = h->h_ac_rec[k];
+        if (r.f1 < next_ok) continue;                       // f1_sample += 20*87/25 after a decoded reply (demod_2400.c:722)
+        next_ok = r.f1 + 20 * 87 / 25 + 1;
+        if (nmsg < cap) {
+            adsbcu_msg &m = out[nmsg];                      // decodeModeAMessage (mode_ac.c:123-158)
+            std::memset(&m, 0, sizeof(m));
+            m.timestamp = block_timestamp + r.f2_clock / 5; // 60 MHz -> 12 MHz, reported at F2 (demod_2400.c:712)
+            m.msgtype = 32;
+            m.msgbits = 16;
+            m.msg[0] = m.verbatim[0] = uint8_t(r.modeac >> 8);
+            m.msg[1] = m.verbatim[1] = uint8_t(r.modeac);
+            m.addr = (r.modeac & 0x0000FF7Fu) | kNonIcao;
+        } else {
+            overflow = true;
+        }
+        ++nmsg;
+    }
+    if (n_out) *n_out = nmsg;
+    if (overflow) { h->error = "out[] too small for the Mode A/C replies"; return ADSBCU_ERR_OVERFLOW; }
     return ADSBCU_OK;
 }
 

@@ -174,6 +174,13 @@ cudaError_t launch_carry(const uint8_t *iq, uint32_t nsamples, uint16_t *carry_m
 cudaError_t launch_magnitude(const uint8_t *iq, uint32_t nsamples, uint16_t *mag, const DevTables *tab, cudaStream_t s);
 
 
+// Mode A/C (adsbcu_modeac.cu): demodulate2400AC on one mag_buf
+struct AcRec { uint32_t f1, f2_clock, modeac; };
+constexpr int kAcLead = 2;    // magnitudes buffer: m[0] at base + kAcLead puts the first new sample m[326] on 16 bytes
+cudaError_t launch_modeac(const DevTables *tab, int sm_count, cudaStream_t s, const uint8_t *d_iq_block, uint32_t n,
+                          const uint8_t *d_iq_overlap, uint32_t n_overlap, uint16_t *d_mag_base, unsigned long long *d_sums,
+                          AcRec *d_rec, uint32_t cap, uint32_t *d_count);
+
 // Path B (adsbcu_pathb.cu): libadsb's own 2.0 MS/s demodulator
 struct PathB;
 }  // namespace adsbcu

@@ -78,6 +78,19 @@ def _pulse_starts_us(frame: bytes) -> np.ndarray:
     return np.concatenate([np.array([0.0, 1.0, 3.5, 4.5]), data])
 
 
+AC_BITS = {"F1": 0, "C1": 1, "A1": 2, "C2": 3, "A2": 4, "C4": 5, "A4": 6, "B1": 8, "D1": 9, "B2": 10, "D2": 11, "B4": 12,
+           "D4": 13, "F2": 14, "SPI": 17}   # pulse slots of a Mode A/C reply, 1.45 us apart (demod_2400.c:556-577)
+
+
+def modeac_pulses_us(code: int) -> np.ndarray:
+    """Pulse start times (us) of the Mode A/C reply whose 13 data bits are `code` in the reference's layout
+    00 A4 A2 A1  00 B4 B2 B1  SPI C4 C2 C1  00 D4 D2 D1 (demod_2400.c:690-705)."""
+    m = {"C1": 0x0010, "A1": 0x1000, "C2": 0x0020, "A2": 0x2000, "C4": 0x0040, "A4": 0x4000, "B1": 0x0100, "D1": 0x0001,
+         "B2": 0x0200, "D2": 0x0002, "B4": 0x0400, "D4": 0x0004, "SPI": 0x0080}
+    slots = [0, 14] + [AC_BITS[k] for k, v in m.items() if code & v]
+    return 1.45 * np.array(sorted(slots), dtype=np.float64)
+
+
 def synth_capture(n_samples: int,
                   frames,
                   starts,
@@ -87,7 +100,8 @@ def synth_capture(n_samples: int,
                   rng: np.random.Generator,
                   dc: float = 127.4,
                   samples_per_us: float = SAMPLES_PER_US) -> np.ndarray:
-    """Render `frames` (list of bytes) into an interleaved uint8 I/Q array.
+    """Render `frames` (list of bytes; an int item is a Mode A/C reply code, 0.45 us pulses) into an
+    interleaved uint8 I/Q array.
 
     starts: message start times in (fractional) samples; amps: peak amplitude
     in LSB; carrier_phase: radians.  Returns uint8[2*n_samples].
@@ -96,8 +110,9 @@ def synth_capture(n_samples: int,
     if len(frames):
         idx_all, val_all = [], []
         for f, t0, a, th in zip(frames, starts, amps, carrier_phase):
-            ps = t0 + _pulse_starts_us(f) * samples_per_us          # pulse start, samples
-            pe = ps + 0.5 * samples_per_us
+            is_ac = isinstance(f, (int, np.integer))
+            ps = t0 + (modeac_pulses_us(int(f)) if is_ac else _pulse_starts_us(f)) * samples_per_us   # pulse start, samples
+            pe = ps + (0.45 if is_ac else 0.5) * samples_per_us
             base = np.floor(ps).astype(np.int64)
             c = a * np.exp(1j * th)
             for k in range(3):                                       # a 1.2-sample pulse spans <= 3 samples
@@ -212,4 +227,29 @@ def config_b(seconds: float = 1.0, seed: int = 0x1090B002, msgs_per_s: float = 1
     amps = rng.uniform(25.0, 100.0, size=m)
     ph = rng.uniform(0, 2 * np.pi, size=m)
     iq = synth_capture(n, frames, starts, amps, ph, sigma, rng, dc=127.0, samples_per_us=2.0)
+    return iq, frames, starts
+
+
+def config_ac(seconds: float = 1.0, seed: int = 0x1090AC01, msgs_per_s: float = 1500.0, ac_per_s: float = 3000.0,
+              sigma: float = 2.0, pool: int = 300):
+    """Mode S traffic (as config 2) plus Mode A/C replies (random 12-bit codes, some with SPI), for --modeac
+    (demod_2400.c:539-726).  Returns (iq, frames, starts); a Mode A/C item of `frames` is its int code."""
+    rng = np.random.default_rng(seed)
+    n = int(round(seconds * FS_1090))
+    m, k = int(round(seconds * msgs_per_s)), int(round(seconds * ac_per_s))
+    icaos = rng.integers(1, 1 << 24, size=pool)
+    frames = [make_frame(17 if rng.random() < 0.7 else 11, int(icaos[rng.integers(0, pool)]), rng) for _ in range(m)]
+    for _ in range(k):
+        code = int(rng.integers(0, 1 << 12))
+        code = ((code & 0x007) << 0) | ((code & 0x038) << 1) | ((code & 0x1C0) << 2) | ((code & 0xE00) << 3)   # D, C, B, A octal digits
+        if rng.random() < 0.1:
+            code |= 0x0080
+        frames.append(code)
+    order = rng.permutation(len(frames))
+    frames = [frames[i] for i in order]
+    starts = np.sort(rng.uniform(400.0, n - 400.0, size=len(frames)))
+    snr = rng.uniform(10.0, 30.0, size=len(frames))
+    amps = sigma * np.sqrt(2.0) * 10.0 ** (snr / 20.0)
+    phases = rng.uniform(0, 2 * np.pi, size=len(frames))
+    iq = synth_capture(n, frames, starts, amps, phases, sigma, rng)
     return iq, frames, starts

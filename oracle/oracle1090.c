@@ -4,6 +4,7 @@
  * follows (paths relative to /root/reference).  Written from the behaviour of
  * that code, not copied from it.
  */
+#define _DEFAULT_SOURCE            /* M_SQRT2 under -std=c11 */
 #include "oracle1090.h"
 
 #include <math.h>
@@ -51,6 +52,7 @@ struct oracle1090 {
     uint64_t sample_counter;
     uint8_t  scratch[2][14];            /* msg1/msg2 of demod_2400.c:103 (stale bytes persist) */
     int      scratch_sel;
+    int      mode_ac;                   /* --modeac: demodulate2400AC after demodulate2400 (dump1090.c:902-905) */
 };
 
 /* ---- magnitude table: dump1090/dsp/helpers/tables.c:9-41 ---------------------------- */
@@ -476,6 +478,80 @@ static size_t demod_block(oracle1090 *o, unsigned mlen, uint64_t block_ts,
     return n;
 }
 
+/* ---- Mode A/C on one mag_buf: dump1090/demod_2400.c:539-726 ----------------------------------
+ * mean_level / mean_power are those of the block's NEW samples as magnitude_power_uc8 (lookup_unroll_4, the
+ * generic flavour's first registered implementation; dsp/impl/magnitude_power_uc8.c:48-90) computes them. */
+static size_t modeac_block(oracle1090 *o, unsigned mlen, uint64_t block_ts, double mean_level, double mean_power,
+                           oracle1090_msg *out, size_t cap, size_t have)
+{
+    const uint16_t *m = o->mag;
+    size_t n = 0;
+    double noise_stddev = sqrt(mean_power - mean_level * mean_level);                     /* :550 */
+    unsigned noise_level = (unsigned) ((mean_power + noise_stddev) * 65535 + 0.5);        /* :551 */
+
+    for (unsigned f1_sample = 1; f1_sample < mlen; ++f1_sample) {
+        if (!(m[f1_sample - 1] < m[f1_sample + 0])) continue;                              /* :606 */
+        if (m[f1_sample + 2] > m[f1_sample + 0] || m[f1_sample + 2] > m[f1_sample + 1]) continue;
+        unsigned f1_level = (m[f1_sample + 0] + m[f1_sample + 1]) / 2;
+        if (noise_level * 2 > f1_level) continue;
+
+        volatile float f1a_power = (float) m[f1_sample] * m[f1_sample];                   /* :622-625 */
+        volatile float f1b_power = (float) m[f1_sample + 1] * m[f1_sample + 1];
+        volatile float fsum = f1a_power + f1b_power;
+        volatile float fraction = f1b_power / fsum;
+        volatile float fr2 = fraction * fraction;
+        volatile float fpos = f1_sample + fr2;
+        volatile float f25 = 25 * fpos;
+        unsigned f1_clock = (unsigned) (f25 + 0.5);
+
+        unsigned f2_clock = f1_clock + (87 * 14);
+        unsigned f2_sample = f2_clock / 25;
+        if (!(m[f2_sample - 1] < m[f2_sample + 0])) continue;
+        if (m[f2_sample + 2] > m[f2_sample + 0] || m[f2_sample + 2] > m[f2_sample + 1]) continue;
+        unsigned f2_level = (m[f2_sample + 0] + m[f2_sample + 1]) / 2;
+        if (noise_level * 2 > f2_level) continue;
+
+        unsigned f1f2_level = (f1_level > f2_level ? f1_level : f2_level);
+        float midpoint = sqrtf(noise_level * f1f2_level);                                  /* unsigned product -> float */
+        unsigned signal_threshold = (unsigned) (midpoint * M_SQRT2 + 0.5);
+        unsigned noise_threshold = (unsigned) (midpoint / M_SQRT2 + 0.5);
+
+        unsigned uncertain_bits = 0, noisy_bits = 0, bits = 0, bit, clock;
+        for (bit = 0, clock = f1_clock; bit < 20; ++bit, clock += 87) {
+            unsigned sample = clock / 25;
+            bits <<= 1; noisy_bits <<= 1; uncertain_bits <<= 1;
+            if (m[sample + 2] >= signal_threshold) noisy_bits |= 1;
+            if (m[sample + 0] >= signal_threshold || m[sample + 1] >= signal_threshold) bits |= 1;
+            else if (m[sample + 0] > noise_threshold && m[sample + 1] > noise_threshold) uncertain_bits |= 1;
+        }
+        if ((bits & 0x80020) != 0x80020) continue;
+        if ((bits & 0x0101B) != 0) continue;
+        if (noisy_bits || uncertain_bits) continue;
+
+        unsigned modeac =
+            ((bits & 0x40000) ? 0x0010 : 0) | ((bits & 0x20000) ? 0x1000 : 0) | ((bits & 0x10000) ? 0x0020 : 0) |
+            ((bits & 0x08000) ? 0x2000 : 0) | ((bits & 0x04000) ? 0x0040 : 0) | ((bits & 0x02000) ? 0x4000 : 0) |
+            ((bits & 0x00800) ? 0x0100 : 0) | ((bits & 0x00400) ? 0x0001 : 0) | ((bits & 0x00200) ? 0x0200 : 0) |
+            ((bits & 0x00100) ? 0x0002 : 0) | ((bits & 0x00080) ? 0x0400 : 0) | ((bits & 0x00040) ? 0x0004 : 0) |
+            ((bits & 0x00004) ? 0x0080 : 0);
+
+        oracle1090_msg mm;                                  /* decodeModeAMessage: mode_ac.c:123-158 */
+        memset(&mm, 0, sizeof(mm));
+        mm.timestamp = block_ts + f2_clock / 5;             /* :712 */
+        mm.msgtype = 32;
+        mm.msgbits = 16;
+        mm.msg[0] = mm.verbatim[0] = (uint8_t) (modeac >> 8);
+        mm.msg[1] = mm.verbatim[1] = (uint8_t) modeac;
+        mm.addr = (modeac & 0x0000FF7F) | NON_ICAO;
+        if (have + n < cap) out[have + n] = mm;
+        n++;
+        f1_sample += (20 * 87 / 25);                        /* :722 */
+    }
+    return n;
+}
+
+void oracle1090_set_mode_ac(oracle1090 *o, int on) { o->mode_ac = on; }
+
 size_t oracle1090_feed(oracle1090 *o, const uint8_t *iq, size_t nsamples, oracle1090_msg *out, size_t cap)
 {
     size_t total = 0, pos = 0;
@@ -487,6 +563,12 @@ size_t oracle1090_feed(oracle1090 *o, const uint8_t *iq, size_t nsamples, oracle
         memcpy(o->tail, o->mag + take, sizeof(o->tail));                            /* fifo.c:196 */
         uint64_t ts = (uint64_t) ((double) o->sample_counter * 12e6 / 2400000.0);   /* sdr_ifile.c:202 */
         total += demod_block(o, (unsigned) take, ts, out, cap, total);
+        if (o->mode_ac) {                                                           /* dump1090.c:902-905 */
+            uint64_t sum_level = 0, sum_power = 0;                                  /* magnitude_power_uc8.c:55-89 */
+            for (size_t k = 0; k < take; k++) { uint32_t v = o->mag[OVERLAP + k]; sum_level += v; sum_power += (uint64_t) (v * v); }
+            double level = sum_level / 65536.0 / (unsigned) take, power = sum_power / 65536.0 / 65536.0 / (unsigned) take;
+            total += modeac_block(o, (unsigned) take, ts, level, power, out, cap, total);
+        }
         o->sample_counter += take;
         pos += take;
     }

@@ -46,6 +46,9 @@ typedef struct oracle1090 oracle1090;
 oracle1090 *oracle1090_create(int nfix_crc, int fix_df, unsigned block_samples);
 void oracle1090_destroy(oracle1090 *o);
 
+/* --modeac: also run demodulate2400AC (demod_2400.c:539-726) on every mag_buf, after demodulate2400. */
+void oracle1090_set_mode_ac(oracle1090 *o, int on);
+
 /* Feed `nsamples` I/Q pairs, processed the way sdr_ifile.c:178-245 + fifo.c:173-210
  * + demod_2400.c:99-444 would process a file read: in blocks of block_samples
  * (the last one short).  Returns the number of messages accepted during this

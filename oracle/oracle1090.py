@@ -36,6 +36,7 @@ def lib():
         L.oracle1090_create.restype = C.c_void_p
         L.oracle1090_create.argtypes = [C.c_int, C.c_int, C.c_uint]
         L.oracle1090_destroy.argtypes = [C.c_void_p]
+        L.oracle1090_set_mode_ac.argtypes = [C.c_void_p, C.c_int]
         L.oracle1090_feed.restype = C.c_size_t
         L.oracle1090_feed.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
         L.oracle1090_mag_table.argtypes = [C.c_void_p]
