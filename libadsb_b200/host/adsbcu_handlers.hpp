@@ -78,8 +78,11 @@ inline adsbcu_config make_config(int device, int nfix_crc, int fix_df, uint32_t 
 class ModeS2400Handler : public IDataHandler {
 public:
     using Sink = std::function<void(adsbcu_msg const &)>;   // == useModesMessage(struct modesMessage*)
-    ModeS2400Handler(Sink sink, int nfix_crc = 0, int fix_df = 1, int device = 0, uint32_t max_feed_samples = 1u << 24)
-        : eng_(make_config(device, nfix_crc, fix_df, max_feed_samples)), sink_(std::move(sink)), out_(1u << 16)
+    // mode_ac: also run demodulate2400AC on every buffer, after the Mode S pass (dump1090 --modeac, dump1090.c:902-905);
+    // one HandleData call is then treated as one mag_buf of the reference
+    ModeS2400Handler(Sink sink, int nfix_crc = 0, int fix_df = 1, int device = 0, uint32_t max_feed_samples = 1u << 24,
+                     bool mode_ac = false)
+        : eng_(make_config(device, nfix_crc, fix_df, max_feed_samples)), sink_(std::move(sink)), out_(1u << 16), mode_ac_(mode_ac)
     {
     }
     void HandleData(std::span<uint8_t const> const &data) override
@@ -96,6 +99,21 @@ public:
         }
         eng_.check(rc, "adsbcu_1090_feed");
         for (size_t k = 0; k < n; ++k) sink_(out_[k]);
+        if (mode_ac_) {
+            const size_t ns = data.size() / 2;
+            size_t na = 0;
+            // sampleTimestamp of the buffer (sdr_ifile.c:202): samples so far at 12 MHz / 2.4 MS/s
+            const uint64_t ts = uint64_t(double(samples_seen_) * 12e6 / 2400000.0);
+            eng_.check(adsbcu_1090_modeac_block(eng_.get(), data.data(), ns, tail_.data(), tail_.size() / 2, ts, out_.data(),
+                                                out_.size(), &na), "adsbcu_1090_modeac_block");
+            for (size_t k = 0; k < na; ++k) sink_(out_[k]);
+            // keep the last 326 samples as the next buffer's overlap (fifo.c:187-196)
+            std::vector<uint8_t> t(tail_);
+            t.insert(t.end(), data.begin(), data.begin() + 2 * ns);
+            if (t.size() > 2 * 326) t.erase(t.begin(), t.end() - 2 * 326);
+            tail_.swap(t);
+            samples_seen_ += ns;
+        }
     }
     void OnDeviceStatusChanged(bool) override {}
     void Reset(bool clear_filter) { eng_.check(adsbcu_1090_reset(eng_.get(), clear_filter ? 1 : 0), "adsbcu_1090_reset"); }
@@ -110,6 +128,9 @@ private:
     Engine eng_;
     Sink sink_;
     std::vector<adsbcu_msg> out_;
+    bool mode_ac_ = false;
+    std::vector<uint8_t> tail_;
+    uint64_t samples_seen_ = 0;
 };
 
 // ---- Path B -------------------------------------------------------------------------------------

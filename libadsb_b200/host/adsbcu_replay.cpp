@@ -6,7 +6,8 @@
 //            --beast FILE the Beast binary stream of writeBeastMessage (net_io.c:440-487) on the verbatim bytes
 //   path b : "*<hex msg>;"
 //   path uat: "<updown><hex payload>;rs=<n>;"  (dump978 raw line format)
-// usage: adsbcu_replay --path a|b|uat [--fix|--fix-2bit] [--no-fix-df] [--block BYTES] [--beast FILE] capture.bin
+// usage: adsbcu_replay --path a|b|uat [--fix|--fix-2bit] [--no-fix-df] [--modeac] [--block BYTES] [--beast FILE] capture.bin
+// (--modeac: every block is one mag_buf of the reference; use --block 262144 to mirror dump1090 --ifile)
 #include "adsbcu_handlers.hpp"
 
 #include <cmath>
@@ -39,6 +40,7 @@ int main(int argc, char **argv)
 {
     std::string path = "a", file, beast_file;
     int nfix = 0, fix_df = 1;
+    bool mode_ac = false;
     size_t block = 262144;   // RTLSDR::BufferLength (RTLSDR.hpp:55)
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
@@ -46,6 +48,7 @@ int main(int argc, char **argv)
         else if (a == "--fix") nfix = 1;
         else if (a == "--fix-2bit") nfix = 2;
         else if (a == "--no-fix-df") fix_df = 0;
+        else if (a == "--modeac") mode_ac = true;
         else if (a == "--block" && i + 1 < argc) block = std::strtoull(argv[++i], nullptr, 0);
         else if (a == "--beast" && i + 1 < argc) beast_file = argv[++i];
         else file = a;
@@ -64,7 +67,7 @@ int main(int argc, char **argv)
                 std::printf(";\n");
                 if (!beast_file.empty()) beast_message(beast, m.timestamp, m.signal_level, m.verbatim, m.msgbits / 8);
                 ++count;
-            }, nfix, fix_df, 0, uint32_t(std::max<size_t>(block / 2, 1u << 20)));
+            }, nfix, fix_df, 0, uint32_t(std::max<size_t>(block / 2, 1u << 20)), mode_ac);
         } else if (path == "b") {
             h = std::make_unique<ADSB1090Handler>([&](adsbcu_msg_b const &m) {
                 std::printf("*");

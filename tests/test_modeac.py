@@ -71,3 +71,19 @@ def test_gpu_modeac_edges(adsbcu_mod):
     assert len(d.modeac_block(np.full(2000, 127, np.uint8), np.full(10, 127, np.uint8), 0)) == 0
     with pytest.raises(adsbcu_mod.AdsbcuError):
         d.modeac_block(np.zeros(100, np.uint8), np.zeros(2 * 327, np.uint8), 0)
+
+
+@pytest.mark.gpu
+def test_replay_cli_modeac_matches_reference(tmp_path):
+    """host shim + CLI: `adsbcu_replay --path a --fix --modeac --block 262144` == `dump1090 --ifile X --fix --modeac`."""
+    import subprocess
+    from libadsb_b200 import build
+    build.build()
+    with np.load(GOLD) as z:
+        iq, ref = z["iq"], z["ref_fix1_modeac"]
+    cap = tmp_path / "cap.uc8"
+    iq.tofile(cap)
+    p = subprocess.run([build.REPLAY, "--path", "a", "--fix", "--modeac", "--block", "262144", str(cap)], capture_output=True, text=True)
+    assert p.returncode == 0, p.stderr
+    want = ["@%012X%s;" % (int(r["timestamp"]), bytes(r["msg"][:int(r["msgbits"]) // 8]).hex()) for r in ref]
+    assert p.stdout.split() == want
