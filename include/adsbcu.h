@@ -114,6 +114,13 @@ int adsbcu_1090_feed(adsbcu_handle *h, const uint8_t *iq, size_t nsamples,
 int adsbcu_1090_feed_device(adsbcu_handle *h, const uint8_t *iq_dev, size_t nsamples,
                             adsbcu_msg *out, size_t cap, size_t *n_out);
 
+/* The other two input formats of the reference (convert.c:46-92, --iformat SC16 / SC16Q11): interleaved
+ * little-endian int16 I/Q pairs (HOST memory), q11 != 0 for the 12-bit Q11 scaling.  Magnitudes follow
+ * magnitude_sc16.c:27-45 / magnitude_sc16q11.c:29-47; everything downstream is the same path as
+ * adsbcu_1090_feed and the stream may mix calls of both. */
+int adsbcu_1090_feed_sc16(adsbcu_handle *h, const int16_t *iq, size_t nsamples, int q11,
+                          adsbcu_msg *out, size_t cap, size_t *n_out);
+
 /* Stage-level entry (replaces starch_magnitude_uc8, magnitude_uc8.c:30-63):
  * mag_out[k] = LUT[I,Q] for k < nsamples, both HOST pointers. */
 int adsbcu_1090_magnitude(adsbcu_handle *h, const uint8_t *iq, size_t nsamples, uint16_t *mag_out);

@@ -34,7 +34,7 @@ EXPORTS = ["adsbcu_abi_version", "adsbcu_last_error", "adsbcu_create", "adsbcu_d
            "adsbcu_1090_feed", "adsbcu_1090_feed_device", "adsbcu_1090_magnitude", "adsbcu_1090_filter_add",
            "adsbcu_1090_filter_test", "adsbcu_get_stats", "adsbcu_1090b_feed", "adsbcu_1090b_reset",
            "adsbcu_978_feed", "adsbcu_978_reset", "adsbcu_978_phase", "adsbcu_1090_seek", "adsbcu_1090_scan_candidates",
-           "adsbcu_1090_known_export", "adsbcu_1090_known_import", "adsbcu_1090_revive", "adsbcu_1090_resolve", "adsbcu_1090_modeac_block"]
+           "adsbcu_1090_known_export", "adsbcu_1090_known_import", "adsbcu_1090_revive", "adsbcu_1090_resolve", "adsbcu_1090_modeac_block", "adsbcu_1090_feed_sc16"]
 
 
 class Config(C.Structure):
@@ -88,6 +88,7 @@ def load():
         L.adsbcu_1090_resolve.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.adsbcu_1090_modeac_block.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_uint64, C.c_void_p,
                                                C.c_size_t, C.POINTER(C.c_size_t)]
+        L.adsbcu_1090_feed_sc16.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         _lib = L
     return _lib
 
@@ -130,6 +131,15 @@ class Demod1090:
             out = np.zeros(cap if cap is not None else max(1024, n // 100), dtype=MSG_DTYPE)
         got = C.c_size_t(0)
         self._check(load().adsbcu_1090_feed(self.h, iq.ctypes.data, n, out.ctypes.data, len(out), C.byref(got)))
+        return out[:got.value]
+
+    def feed_sc16(self, iq: np.ndarray, q11: bool = False, cap: int | None = None) -> np.ndarray:
+        """--iformat SC16 / SC16Q11: interleaved int16 I/Q."""
+        iq = np.ascontiguousarray(iq, dtype="<i2")
+        n = iq.size // 2
+        out = np.zeros(cap if cap is not None else max(1024, n // 100), dtype=MSG_DTYPE)
+        got = C.c_size_t(0)
+        self._check(load().adsbcu_1090_feed_sc16(self.h, iq.ctypes.data, n, int(q11), out.ctypes.data, len(out), C.byref(got)))
         return out[:got.value]
 
     def feed_device(self, dev_ptr: int, nsamples: int, out: np.ndarray) -> np.ndarray:

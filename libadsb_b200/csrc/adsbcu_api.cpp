@@ -101,6 +101,7 @@ struct adsbcu_handle {
     uint32_t *d_bitmap = nullptr;
     uint16_t *d_carry = nullptr;
     uint8_t *d_iq = nullptr;          // staging for host feeds
+    int16_t *d_sc16 = nullptr;        // staging for SC16 / SC16Q11 host feeds (allocated on first use)
     uint32_t nseg = 0, seg_cap = 0, full_cap = 0;
     uint32_t skew = 0, skew_ns = 2500;   // measured on B200: no skew 0.5065 ms, sleep skew 0.506-0.516, short first tile 0.529 (profiles/sweep_skew.sh)
     uint32_t unit_positions = 0, max_tps = 1, host_tps = 4;   // chunk = unit_positions * (tiles per segment), at most max_tps
@@ -149,6 +150,7 @@ void free_all(adsbcu_handle *h)
 {
     if (h->host_only) return;
     cudaSetDevice(h->device);
+    cudaFree(h->d_sc16);
     cudaFree(h->d_ac_ov); cudaFree(h->d_ac_sums); cudaFree(h->d_ac_rec);
     if (h->h_ac_rec) cudaFreeHost(h->h_ac_rec);
     cudaFree(h->d_carry_prev); cudaFree(h->d_deferred); cudaFree(h->d_n_deferred); cudaFree(h->d_known_tmp);
@@ -271,19 +273,24 @@ void resolve(adsbcu_handle *h, const Rec *recs, size_t nrec, uint64_t feed_base,
 // Everything is queued without host synchronisation; the host pass of chunk c runs while the GPU
 // works on the following chunks.  iq_host != nullptr: the samples are uploaded into d_iq chunk by
 // chunk on copy_stream (a chunk only looks at samples at or before its own end, see ScanArgs).
-int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint32_t n, Sink &sink)
+// sc16_host != nullptr (then iq_host must be null): SC16 / SC16Q11 samples; they are uploaded chunk by chunk into
+// d_sc16, converted to uint16 magnitudes into d_iq (2 bytes per sample, like uc8 I/Q) and every kernel runs
+// in magnitudes-in mode (convert.c:46-92).
+int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint32_t n, Sink &sink,
+             const int16_t *sc16_host = nullptr, int q11 = 0)
 {
+    const bool from_host = iq_host || sc16_host;
     adsbcu_stats &st = h->stats;
     // chunk boundaries: the first chunks are short so that the pipeline (upload -> kernels -> host pass)
     // fills quickly, later ones long so that per-launch costs (LUT load, tail) are amortised
     std::vector<uint32_t> bounds{0};
     // host feeds are bound by the upload: short chunks throughout keep the work left after the last byte arrived small
-    const uint32_t tps_cap = iq_host ? std::min(h->host_tps, h->max_tps) : h->max_tps;
+    const uint32_t tps_cap = from_host ? std::min(h->host_tps, h->max_tps) : h->max_tps;
     for (uint32_t tps = std::min(4u, tps_cap); bounds.back() < n; tps = std::min(2 * tps, tps_cap))
         bounds.push_back(uint32_t(std::min<uint64_t>(n, uint64_t(bounds.back()) + uint64_t(h->unit_positions) * tps)));
     const uint32_t nchunks = uint32_t(bounds.size() - 1);
     float ms_h2d = 0.f;
-    if (iq_host) CK(cudaEventRecord(h->ev_h2d[0], h->copy_stream));
+    if (from_host) CK(cudaEventRecord(h->ev_h2d[0], h->copy_stream));
 
     auto submit = [&](uint32_t c) -> int {
         Slot &s = h->slot[c % kSlots];
@@ -301,6 +308,17 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
         a.ctr = s.d_ctr;
         a.skew = h->skew; a.skew_ns = h->skew_ns;
         if (sink.cands) { a.deferred = h->d_deferred; a.deferred_cap = h->deferred_cap; a.n_deferred = h->d_n_deferred; }
+        if (sc16_host) {
+            a.iq = nullptr;
+            a.mag_in = reinterpret_cast<const uint16_t *>(h->d_iq);
+            CK(cudaMemcpyAsync(h->d_sc16 + 2 * size_t(a.pos_begin), sc16_host + 2 * size_t(a.pos_begin),
+                               4 * size_t(a.pos_end - a.pos_begin), cudaMemcpyHostToDevice, h->copy_stream));
+            CK(cudaEventRecord(h->ev_up[c % kSlots], h->copy_stream));
+            if (c + 1 == nchunks) CK(cudaEventRecord(h->ev_h2d[1], h->copy_stream));
+            CK(cudaStreamWaitEvent(h->stream, h->ev_up[c % kSlots], 0));
+            CK(launch_convert_sc16(h->d_sc16 + 2 * size_t(a.pos_begin), a.pos_end - a.pos_begin,
+                                   reinterpret_cast<uint16_t *>(h->d_iq) + a.pos_begin, q11, h->stream));
+        }
         if (iq_host) {
             CK(cudaMemcpyAsync(h->d_iq + 2 * size_t(a.pos_begin), iq_host + 2 * size_t(a.pos_begin),
                                2 * size_t(a.pos_end - a.pos_begin), cudaMemcpyHostToDevice, h->copy_stream));
@@ -355,10 +373,11 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
     }
     if (rc != ADSBCU_OK) { cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->copy_stream); return rc; }
     if (sink.cands) CK(cudaMemcpyAsync(h->d_carry_prev, h->d_carry, kOverlap * sizeof(uint16_t), cudaMemcpyDeviceToDevice, h->stream));
-    CK(launch_carry(d_iq, n, h->d_carry, h->d_tab, h->stream));
+    if (sc16_host) CK(launch_carry_mag(reinterpret_cast<const uint16_t *>(h->d_iq), n, h->d_carry, h->stream));
+    else CK(launch_carry(d_iq, n, h->d_carry, h->d_tab, h->stream));
     st.scan_launches += 1;
     CK(cudaStreamSynchronize(h->stream));
-    if (iq_host && nchunks) { cudaEventElapsedTime(&ms_h2d, h->ev_h2d[0], h->ev_h2d[1]); st.ms_h2d += ms_h2d; }
+    if (from_host && nchunks) { cudaEventElapsedTime(&ms_h2d, h->ev_h2d[0], h->ev_h2d[1]); st.ms_h2d += ms_h2d; }
     st.samples += n;
     h->stream_pos += n;
     return ADSBCU_OK;
@@ -730,6 +749,29 @@ int adsbcu_1090_resolve(adsbcu_handle *h, const adsbcu_cand *cands, size_t n, ad
     if (!h || (!cands && n) || (!out && cap)) return ADSBCU_ERR_ARG;
     Sink sink{out, cap, 0, false};
     resolve(h, cands, n, 0, sink);
+    if (n_out) *n_out = sink.n;
+    if (sink.overflow) { h->error = "out[] too small for the accepted messages"; return ADSBCU_ERR_OVERFLOW; }
+    return ADSBCU_OK;
+}
+
+int adsbcu_1090_feed_sc16(adsbcu_handle *h, const int16_t *iq, size_t nsamples, int q11, adsbcu_msg *out, size_t cap, size_t *n_out)
+{
+    if (!h) return ADSBCU_ERR_ARG;
+    if (n_out) *n_out = 0;
+    NEED_DEVICE(h);
+    if ((!iq && nsamples) || (!out && cap)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
+    CK(cudaSetDevice(h->device));
+    if (!h->d_sc16) CK(cudaMalloc(&h->d_sc16, size_t(h->cfg.max_feed_samples) * 4 + 64));
+    h->stats = adsbcu_stats{};
+    Sink sink{out, cap, 0, false};
+    const size_t max_take = h->cfg.max_feed_samples & ~size_t(7);
+    for (size_t done = 0; done < nsamples;) {
+        const size_t take = std::min<size_t>(nsamples - done, max_take);
+        const int r = run_feed(h, h->d_iq, nullptr, uint32_t(take), sink, iq + 2 * done, q11 ? 1 : 0);
+        if (r != ADSBCU_OK) return r;
+        done += take;
+    }
+    h->stats.messages = sink.n;
     if (n_out) *n_out = sink.n;
     if (sink.overflow) { h->error = "out[] too small for the accepted messages"; return ADSBCU_ERR_OVERFLOW; }
     return ADSBCU_OK;

@@ -143,6 +143,7 @@ struct ChunkCounters {
 // the whole chunk in stream order and the host pass never sorts.
 struct ScanArgs {
     const uint8_t  *iq;          // feed samples (device), 16 B aligned
+    const uint16_t *mag_in;      // or, for SC16 / SC16Q11 inputs, their magnitudes (then iq is unused); 16 B aligned
     const uint16_t *carry_mag;   // kOverlap magnitudes preceding the feed (zeros at stream start)
     uint32_t        nsamples;    // samples in the feed
     uint32_t        pos_begin, pos_end;   // this chunk's start positions
@@ -171,6 +172,8 @@ cudaError_t launch_revive(const ScanArgs &a, cudaStream_t s);
 cudaError_t launch_or_words(uint32_t *dst, const uint32_t *src, uint32_t nwords, cudaStream_t s);
 cudaError_t launch_build_lut(DevTables *tab, cudaStream_t s);     // fills tab->mag_lut with the register-computed magnitudes
 cudaError_t launch_carry(const uint8_t *iq, uint32_t nsamples, uint16_t *carry_mag, const DevTables *tab, cudaStream_t s);
+cudaError_t launch_convert_sc16(const int16_t *in, uint32_t nsamples, uint16_t *mag, int q11, cudaStream_t s);
+cudaError_t launch_carry_mag(const uint16_t *mag_in, uint32_t nsamples, uint16_t *carry_mag, cudaStream_t s);
 cudaError_t launch_magnitude(const uint8_t *iq, uint32_t nsamples, uint16_t *mag, const DevTables *tab, cudaStream_t s);
 
 

@@ -209,7 +209,8 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
         int lo, hi;
         valid_range(x0t, lo, hi);
         const int i = kRun * tid;
-        const uint8_t *p = a.iq + 2 * (x0t + i);
+        // magnitudes-in mode (SC16 inputs were converted to uint16 magnitudes): also 2 bytes per sample
+        const uint8_t *p = (a.mag_in ? reinterpret_cast<const uint8_t *>(a.mag_in) : a.iq) + 2 * (x0t + i);
 #pragma unroll
         for (int r = 0; r < 3; ++r)
             if (i + 8 * r >= lo && i + 8 * r + 8 <= hi) raw[r] = __ldg(reinterpret_cast<const uint4 *>(p + 16 * r));
@@ -218,7 +219,7 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
     // magnitude of feed sample xe on the slow path (stream edges): carry, scalar I/Q, or zero padding
     auto mag_edge = [&](int64_t xe) -> uint32_t {
         if (xe < 0) return (xe + kOverlap >= 0) ? uint32_t(a.carry_mag[xe + kOverlap]) : 0u;
-        if (xe < n) return mag_iq(s_sq, a.iq[2 * xe], a.iq[2 * xe + 1]);
+        if (xe < n) return a.mag_in ? uint32_t(a.mag_in[xe]) : mag_iq(s_sq, a.iq[2 * xe], a.iq[2 * xe + 1]);
         return 0u;
     };
     if (tile_base < seg_end) load_raw(tile_base);
@@ -244,7 +245,9 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
                 if (i0 + 8 * r >= v_lo && i0 + 8 * r + 8 <= v_hi) {
                     const uint4 d = raw[r];
                     const uint32_t c = central_bits(d.x) & central_bits(d.y) & central_bits(d.z) & central_bits(d.w);
-                    if ((c & 0x80808080u) == 0x80808080u) {
+                    if (a.mag_in) {
+                        P[4 * r] = d.x; P[4 * r + 1] = d.y; P[4 * r + 2] = d.z; P[4 * r + 3] = d.w;
+                    } else if ((c & 0x80808080u) == 0x80808080u) {
                         P[4 * r] = lut_pair(lut, d.x); P[4 * r + 1] = lut_pair(lut, d.y);
                         P[4 * r + 2] = lut_pair(lut, d.z); P[4 * r + 3] = lut_pair(lut, d.w);
                     } else {
@@ -259,7 +262,8 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
             }
             if (i0 + 24 >= v_lo && i0 + 28 <= v_hi) {
                 const uint32_t c = central_bits(rawx.x) & central_bits(rawx.y);
-                if ((c & 0x80808080u) == 0x80808080u) { P[12] = lut_pair(lut, rawx.x); P[13] = lut_pair(lut, rawx.y); }
+                if (a.mag_in) { P[12] = rawx.x; P[13] = rawx.y; }
+                else if ((c & 0x80808080u) == 0x80808080u) { P[12] = lut_pair(lut, rawx.x); P[13] = lut_pair(lut, rawx.y); }
                 else { P[12] = mag_pair_any(s_sq, rawx.x); P[13] = mag_pair_any(s_sq, rawx.y); }
             } else {
                 P[12] = mag_edge(x + 24) | (mag_edge(x + 25) << 16);
@@ -596,7 +600,7 @@ __global__ void __launch_bounds__(256) evaluate_kernel(ScanArgs a)
             const int64_t x = xb + i;
             uint32_t v = 0;
             if (x < 0) v = (x + kOverlap >= 0) ? a.carry_mag[x + kOverlap] : 0u;
-            else if (x < n) v = mag_iq(sq, a.iq[2 * x], a.iq[2 * x + 1]);
+            else if (x < n) v = a.mag_in ? uint32_t(a.mag_in[x]) : mag_iq(sq, a.iq[2 * x], a.iq[2 * x + 1]);
             m[i] = uint16_t(v);
         }
         __syncwarp();
@@ -669,6 +673,32 @@ __global__ void build_lut_kernel(DevTables *tab)
     const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;    // I | Q << 8
     const uint32_t i = idx & 255u, q = idx >> 8;
     if (idx < 65536u && lut_covers(i) && lut_covers(q)) tab->mag_lut[lut_offset(i, q) >> 1] = uint16_t(mag_iq(tab->sq, i, q));
+}
+
+// SC16 / SC16Q11 input converters (convert.c:46-92 -> dsp/impl/magnitude_sc16.c:27-45, magnitude_sc16q11.c:29-47,
+// the "exact_float" implementations the generic flavour registers first): |I|,|Q| scaled by 2 (or 32), float
+// squares and sum each rounded to nearest (no FMA contraction), sqrtf, clamp, truncate.
+__global__ void __launch_bounds__(256) convert_sc16_kernel(const int16_t *in, uint32_t nsamples, uint16_t *mag, int scale)
+{
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < nsamples; k += gridDim.x * blockDim.x) {
+        const int2 raw = make_int2(in[2 * k], in[2 * k + 1]);
+        const float i = float(abs(raw.x) * scale), q = float(abs(raw.y) * scale);
+        float m = __fsqrt_rn(__fadd_rn(__fmul_rn(i, i), __fmul_rn(q, q)));
+        if (m > 65535.0f) m = 65535.0f;
+        mag[k] = uint16_t(__float2uint_rz(m));
+    }
+}
+
+__global__ void carry_mag_kernel(const uint16_t *mag_in, uint32_t nsamples, uint16_t *carry_mag)
+{
+    const int i = threadIdx.x;
+    uint32_t v = 0;
+    if (i < kOverlap) {
+        const int64_t x = int64_t(nsamples) - kOverlap + i;
+        v = x >= 0 ? mag_in[x] : carry_mag[x + kOverlap];
+    }
+    __syncthreads();
+    if (i < kOverlap) carry_mag[i] = uint16_t(v);
 }
 
 __global__ void carry_kernel(const uint8_t *iq, uint32_t nsamples, uint16_t *carry_mag, const DevTables *tab)
@@ -759,6 +789,19 @@ cudaError_t launch_revive(const ScanArgs &a, cudaStream_t s)
 cudaError_t launch_or_words(uint32_t *dst, const uint32_t *src, uint32_t nwords, cudaStream_t s)
 {
     or_words_kernel<<<296, 256, 0, s>>>(dst, src, nwords);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_convert_sc16(const int16_t *in, uint32_t nsamples, uint16_t *mag, int q11, cudaStream_t s)
+{
+    if (!nsamples) return cudaSuccess;
+    convert_sc16_kernel<<<148 * 8, 256, 0, s>>>(in, nsamples, mag, q11 ? 32 : 2);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_carry_mag(const uint16_t *mag_in, uint32_t nsamples, uint16_t *carry_mag, cudaStream_t s)
+{
+    carry_mag_kernel<<<1, 352, 0, s>>>(mag_in, nsamples, carry_mag);
     return cudaGetLastError();
 }
 

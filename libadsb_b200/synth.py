@@ -253,3 +253,13 @@ def config_ac(seconds: float = 1.0, seed: int = 0x1090AC01, msgs_per_s: float = 
     phases = rng.uniform(0, 2 * np.pi, size=len(frames))
     iq = synth_capture(n, frames, starts, amps, phases, sigma, rng)
     return iq, frames, starts
+
+
+def to_sc16(iq_uc8: np.ndarray, q11: bool = False) -> np.ndarray:
+    """The same capture as interleaved int16 I/Q (dump1090 --iformat SC16 / SC16Q11): 8-bit samples around the
+    127 DC point scaled to the 16-bit (or 12-bit Q11) range, with a little sub-LSB dither so that the converter's
+    float rounding is exercised on more than 256 distinct values per axis."""
+    rng = np.random.default_rng(int(iq_uc8[:64].sum()) + int(q11))
+    x = (iq_uc8.astype(np.int32) - 127) * (16 if q11 else 256) + rng.integers(-7, 8, size=iq_uc8.size)
+    lim = 2047 if q11 else 32767
+    return np.clip(x, -lim - 1, lim).astype("<i2")

@@ -52,6 +52,7 @@ struct oracle1090 {
     uint64_t sample_counter;
     uint8_t  scratch[2][14];            /* msg1/msg2 of demod_2400.c:103 (stale bytes persist) */
     int      scratch_sel;
+    int      iformat;                   /* 0 UC8, 1 SC16, 2 SC16Q11 (convert.c:94-118) */
     int      mode_ac;                   /* --modeac: demodulate2400AC after demodulate2400 (dump1090.c:902-905) */
 };
 
@@ -551,6 +552,7 @@ static size_t modeac_block(oracle1090 *o, unsigned mlen, uint64_t block_ts, doub
 }
 
 void oracle1090_set_mode_ac(oracle1090 *o, int on) { o->mode_ac = on; }
+void oracle1090_set_input_format(oracle1090 *o, int fmt) { o->iformat = fmt; }
 
 size_t oracle1090_feed(oracle1090 *o, const uint8_t *iq, size_t nsamples, oracle1090_msg *out, size_t cap)
 {
@@ -558,6 +560,19 @@ size_t oracle1090_feed(oracle1090 *o, const uint8_t *iq, size_t nsamples, oracle
     while (pos < nsamples) {
         size_t take = nsamples - pos < o->block ? nsamples - pos : o->block;
         memcpy(o->mag, o->tail, sizeof(o->tail));                                   /* fifo.c:187-193 */
+        if (o->iformat) {       /* magnitude_sc16.c:27-45 / magnitude_sc16q11.c:29-47 ("exact_float") */
+            const int16_t *s16 = (const int16_t *) (const void *) iq;
+            const int scale = o->iformat == 2 ? 32 : 2;
+            for (size_t k = 0; k < take; k++) {
+                volatile float I = abs((int16_t) s16[2 * (pos + k)]) * scale;
+                volatile float Q = abs((int16_t) s16[2 * (pos + k) + 1]) * scale;
+                volatile float ii = I * I, qq = Q * Q;                              /* volatile: no FMA contraction */
+                volatile float magsq = ii + qq;
+                float mag = sqrtf(magsq);
+                if (mag > 65535.0) mag = 65535.0;
+                o->mag[OVERLAP + k] = (uint16_t) mag;
+            }
+        } else
         for (size_t k = 0; k < take; k++)                                           /* magnitude_uc8.c:30-63 */
             o->mag[OVERLAP + k] = o->lut[(unsigned) iq[2 * (pos + k)] | ((unsigned) iq[2 * (pos + k) + 1] << 8)];
         memcpy(o->tail, o->mag + take, sizeof(o->tail));                            /* fifo.c:196 */

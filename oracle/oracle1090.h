@@ -49,6 +49,9 @@ void oracle1090_destroy(oracle1090 *o);
 /* --modeac: also run demodulate2400AC (demod_2400.c:539-726) on every mag_buf, after demodulate2400. */
 void oracle1090_set_mode_ac(oracle1090 *o, int on);
 
+/* --iformat: 0 UC8 (default), 1 SC16, 2 SC16Q11; for 1 and 2 `iq` of oracle1090_feed points at int16 pairs. */
+void oracle1090_set_input_format(oracle1090 *o, int fmt);
+
 /* Feed `nsamples` I/Q pairs, processed the way sdr_ifile.c:178-245 + fifo.c:173-210
  * + demod_2400.c:99-444 would process a file read: in blocks of block_samples
  * (the last one short).  Returns the number of messages accepted during this

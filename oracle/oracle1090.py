@@ -37,6 +37,7 @@ def lib():
         L.oracle1090_create.argtypes = [C.c_int, C.c_int, C.c_uint]
         L.oracle1090_destroy.argtypes = [C.c_void_p]
         L.oracle1090_set_mode_ac.argtypes = [C.c_void_p, C.c_int]
+        L.oracle1090_set_input_format.argtypes = [C.c_void_p, C.c_int]
         L.oracle1090_feed.restype = C.c_size_t
         L.oracle1090_feed.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
         L.oracle1090_mag_table.argtypes = [C.c_void_p]
@@ -66,8 +67,13 @@ class Oracle1090:
 
     __del__ = close
 
+    def set_input_format(self, fmt: int):
+        """0 UC8, 1 SC16, 2 SC16Q11; feed() then takes int16 arrays for 1 and 2."""
+        lib().oracle1090_set_input_format(self.h, fmt)
+        self._fmt = fmt
+
     def feed(self, iq: np.ndarray, cap: int | None = None) -> np.ndarray:
-        iq = np.ascontiguousarray(iq, dtype=np.uint8)
+        iq = np.ascontiguousarray(iq, dtype="<i2" if getattr(self, "_fmt", 0) else np.uint8)
         n = iq.size // 2
         cap = cap if cap is not None else max(1024, n // 100)
         out = np.zeros(cap, dtype=MSG_DTYPE)
@@ -110,7 +116,7 @@ def run_ref(iq: np.ndarray, nfix_crc=0, fix_df=1, extra=()) -> np.ndarray:
     tmpdir = "/dev/shm" if os.path.isdir("/dev/shm") else None
     with tempfile.TemporaryDirectory(dir=tmpdir) as d:
         cap, rec = os.path.join(d, "cap.uc8"), os.path.join(d, "out.rec")
-        np.ascontiguousarray(iq, dtype=np.uint8).tofile(cap)
+        np.ascontiguousarray(iq).tofile(cap)     # uint8 (UC8) or int16 (with --iformat SC16 / SC16Q11 in `extra`)
         env = dict(os.environ, REF1090_OUT=rec)
         subprocess.run([REF_BIN, "--ifile", cap, "--quiet", *flags, *extra], env=env,
                        stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, check=False)
