@@ -199,8 +199,8 @@ int adsbcu_1090_modeac_block(adsbcu_handle *h, const uint8_t *iq, size_t nsample
  * point where the reference calls UseModesMessage() with mm.crcok set (ADSB1090.cpp:741-959,
  * 491-596, 266-435): LUT magnitude, preamble test, plain and phase-corrected decode attempts, mean
  * delta filter, CRC-24 check, single-bit repair of DF11/DF17, Address/Parity recovery against the
- * 60 s cache of recently seen ICAO addresses.  Field decoding, CPR and the IListener callback
- * (ADSB1090.cpp:597-672, 1079-1175) stay in the caller.  Fixed reference configuration
+ * 60 s cache of recently seen ICAO addresses.  Field decoding and CPR (ADSB1090.cpp:597-672, 1079-1121) have their
+ * own bulk entry points below; the aircraft table and the IListener callback stay in the caller.  Fixed reference configuration
  * (ADSB1090.cpp:111-122): fixErrors, checkCRC, not aggressive. */
 #pragma pack(push, 1)
 typedef struct adsbcu_msg_b {
@@ -223,6 +223,40 @@ int adsbcu_1090b_feed(adsbcu_handle *h, const uint8_t *iq, size_t nbytes,
                       adsbcu_msg_b *out, size_t cap, size_t *n_out);
 /* Forget the recently-seen ICAO cache (a fresh ADSB1090Handler). */
 int adsbcu_1090b_reset(adsbcu_handle *h);
+
+/* ---- Path B, next layer: bulk field decode and CPR ---------------------------
+ * What DecodeModesMessage does after the CRC stage (ADSB1090.cpp:525-672) and what
+ * InteractiveReceiveData hands to DecodeCpr (ADSB1090.cpp:986-1121), for many frames per call.  Both
+ * are pure functions of their input: no handle state is read or written.  Field names follow
+ * `struct Message` (ADSB1090.cpp:30-107); aa1..aa3 are adsbcu_msg_b::addr already. */
+typedef struct adsbcu_fields_b {
+    int32_t ca, metype, mesub;          /* mm.ca, mm.metype, mm.mesub */
+    int32_t heading;                    /* mm.heading: DF17 type 19, degrees 0..359 */
+    int32_t fflag;                      /* mm.fflag: msg[6] & 4, non-zero = odd CPR frame */
+    int32_t raw_latitude, raw_longitude;/* 17-bit CPR values */
+    char    flight[8];                  /* mm.flight, all zero unless DF17 type 1..4 */
+    int32_t ew_dir, ew_velocity, ns_dir, ns_velocity, velocity;
+    int32_t fs, dr, um, identity, altitude;
+    int32_t unit;                       /* Message::ModeSUnit: 0 feet, 1 metres */
+} adsbcu_fields_b;                      /* 80 bytes */
+
+/* out[k] = the fields of msgs[k].msg (HOST arrays of n records).  The input frames are the ones
+ * adsbcu_1090b_feed returned, i.e. after the CRC stage's repair. */
+int adsbcu_1090b_decode_fields(adsbcu_handle *h, const adsbcu_msg_b *msgs, size_t n, adsbcu_fields_b *out);
+
+typedef struct adsbcu_cpr_pair {
+    int32_t even_lat, even_lon;         /* a.cprEvenLat / a.cprEvenLon */
+    int32_t odd_lat, odd_lon;           /* a.cprOddLat / a.cprOddLon */
+    int32_t even_is_newer;              /* a.cprEvenTime > a.cprOddTime */
+} adsbcu_cpr_pair;
+typedef struct adsbcu_cpr_fix {
+    int32_t lat1e7, lon1e7;             /* a.lat1E7 / a.lon1E7; untouched (0) when !valid */
+    int32_t valid;                      /* 0: the two frames lie in different latitude zones, DecodeCpr returned early */
+} adsbcu_cpr_fix;
+/* out[k] = DecodeCpr on pairs[k] (HOST arrays).  The caller keeps the reference's 10 s pairing rule
+ * (ADSB1090.cpp:1161).  IEEE double arithmetic in the reference's operation order; a latitude outside the
+ * int32 range converts to INT32_MIN like the reference's x86-64 build. */
+int adsbcu_cpr_decode(adsbcu_handle *h, const adsbcu_cpr_pair *pairs, size_t n, adsbcu_cpr_fix *out);
 
 
 /* ---- Path C: 978 MHz UAT -----------------------------------------------------------------------

@@ -23,6 +23,15 @@ assert MSG_B_DTYPE.itemsize == 32
 UAT_DTYPE = np.dtype([("offset", "<u8"), ("rs_errors", "<i2"), ("len", "<u2"), ("updown", "u1"), ("reserved", "u1", 3),
                       ("data", "u1", 432)])
 assert UAT_DTYPE.itemsize == 448
+# adsbcu_fields_b / adsbcu_cpr_pair / adsbcu_cpr_fix
+FIELDS_B_DTYPE = np.dtype([("ca", "<i4"), ("metype", "<i4"), ("mesub", "<i4"), ("heading", "<i4"), ("fflag", "<i4"),
+                           ("raw_latitude", "<i4"), ("raw_longitude", "<i4"), ("flight", "S8"), ("ew_dir", "<i4"),
+                           ("ew_velocity", "<i4"), ("ns_dir", "<i4"), ("ns_velocity", "<i4"), ("velocity", "<i4"),
+                           ("fs", "<i4"), ("dr", "<i4"), ("um", "<i4"), ("identity", "<i4"), ("altitude", "<i4"), ("unit", "<i4")])
+assert FIELDS_B_DTYPE.itemsize == 80
+CPR_PAIR_DTYPE = np.dtype([("even_lat", "<i4"), ("even_lon", "<i4"), ("odd_lat", "<i4"), ("odd_lon", "<i4"),
+                           ("even_is_newer", "<i4")])
+CPR_FIX_DTYPE = np.dtype([("lat1e7", "<i4"), ("lon1e7", "<i4"), ("valid", "<i4")])
 
 CAND_DTYPE = np.dtype([("pos", "<u8"), ("phase", "u1"), ("kind", "u1"), ("corrections", "i1"), ("msgtype", "u1"),
                        ("verbatim", "u1", 14), ("msg", "u1", 14), ("crc", "<u4"), ("addr", "<u4"), ("test_key", "<u4"),
@@ -34,7 +43,8 @@ EXPORTS = ["adsbcu_abi_version", "adsbcu_last_error", "adsbcu_create", "adsbcu_d
            "adsbcu_1090_feed", "adsbcu_1090_feed_device", "adsbcu_1090_magnitude", "adsbcu_1090_filter_add",
            "adsbcu_1090_filter_test", "adsbcu_get_stats", "adsbcu_1090b_feed", "adsbcu_1090b_reset",
            "adsbcu_978_feed", "adsbcu_978_reset", "adsbcu_978_phase", "adsbcu_1090_seek", "adsbcu_1090_scan_candidates",
-           "adsbcu_1090_known_export", "adsbcu_1090_known_import", "adsbcu_1090_revive", "adsbcu_1090_resolve", "adsbcu_1090_modeac_block", "adsbcu_1090_feed_sc16"]
+           "adsbcu_1090_known_export", "adsbcu_1090_known_import", "adsbcu_1090_revive", "adsbcu_1090_resolve", "adsbcu_1090_modeac_block", "adsbcu_1090_feed_sc16",
+           "adsbcu_1090b_decode_fields", "adsbcu_cpr_decode"]
 
 
 class Config(C.Structure):
@@ -76,6 +86,8 @@ def load():
         L.adsbcu_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
         L.adsbcu_1090b_feed.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.adsbcu_1090b_reset.argtypes = [C.c_void_p]
+        L.adsbcu_1090b_decode_fields.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.adsbcu_cpr_decode.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         L.adsbcu_978_feed.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.adsbcu_978_reset.argtypes = [C.c_void_p]
         L.adsbcu_978_phase.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
@@ -162,6 +174,20 @@ class Demod1090:
         got = C.c_size_t(0)
         self._check(load().adsbcu_1090b_feed(self.h, iq.ctypes.data, iq.size, out.ctypes.data, cap, C.byref(got)))
         return out[:got.value]
+
+    def decode_fields_b(self, msgs: np.ndarray) -> np.ndarray:
+        """Path B, next layer: the Message fields DecodeModesMessage fills after the CRC stage, for every record."""
+        msgs = np.ascontiguousarray(msgs, dtype=MSG_B_DTYPE)
+        out = np.zeros(msgs.size, dtype=FIELDS_B_DTYPE)
+        self._check(load().adsbcu_1090b_decode_fields(self.h, msgs.ctypes.data, msgs.size, out.ctypes.data))
+        return out
+
+    def cpr_decode(self, pairs: np.ndarray) -> np.ndarray:
+        """DecodeCpr on every even/odd pair (CPR_PAIR_DTYPE) -> CPR_FIX_DTYPE."""
+        pairs = np.ascontiguousarray(pairs, dtype=CPR_PAIR_DTYPE)
+        out = np.zeros(pairs.size, dtype=CPR_FIX_DTYPE)
+        self._check(load().adsbcu_cpr_decode(self.h, pairs.ctypes.data, pairs.size, out.ctypes.data))
+        return out
 
     def reset_b(self):
         self._check(load().adsbcu_1090b_reset(self.h))

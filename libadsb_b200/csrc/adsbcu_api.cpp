@@ -116,6 +116,7 @@ struct adsbcu_handle {
     IcaoFilter filter;
     adsbcu_stats stats{};
     PathB *pathb = nullptr;
+    Fields *fields = nullptr;
     PathC *pathc = nullptr;
 
     // sharded captures (adsbcu_1090_scan_candidates / _revive)
@@ -157,6 +158,8 @@ void free_all(adsbcu_handle *h)
     if (h->stream) cudaStreamSynchronize(h->stream);
     pathb_free(h->pathb);
     h->pathb = nullptr;
+    fields_free(h->fields);
+    h->fields = nullptr;
     pathc_free(h->pathc);
     h->pathc = nullptr;
     if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
@@ -611,6 +614,26 @@ int adsbcu_1090b_reset(adsbcu_handle *h)
     NEED_DEVICE(h);
     pathb_reset(h->pathb);
     return ADSBCU_OK;
+}
+
+int adsbcu_1090b_decode_fields(adsbcu_handle *h, const adsbcu_msg_b *msgs, size_t n, adsbcu_fields_b *out)
+{
+    if (!h) return ADSBCU_ERR_ARG;
+    NEED_DEVICE(h);
+    if (n && (!msgs || !out)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
+    if (n > (size_t(1) << 28)) { h->error = "bad argument (more than 2^28 records in one call)"; return ADSBCU_ERR_ARG; }
+    CK(cudaSetDevice(h->device));
+    return fields_decode(h->fields, h->stream, msgs, n, out, h->error);
+}
+
+int adsbcu_cpr_decode(adsbcu_handle *h, const adsbcu_cpr_pair *pairs, size_t n, adsbcu_cpr_fix *out)
+{
+    if (!h) return ADSBCU_ERR_ARG;
+    NEED_DEVICE(h);
+    if (n && (!pairs || !out)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
+    if (n > (size_t(1) << 28)) { h->error = "bad argument (more than 2^28 records in one call)"; return ADSBCU_ERR_ARG; }
+    CK(cudaSetDevice(h->device));
+    return cpr_decode(h->fields, h->stream, pairs, n, out, h->error);
 }
 
 int adsbcu_978_feed(adsbcu_handle *h, const uint8_t *iq, size_t nbytes, adsbcu_uat_frame *out, size_t cap, size_t *n_out)

@@ -1,0 +1,247 @@
+// Path B, the layer after the CRC stage: bulk field decode and CPR.
+//
+//   fields_kernel   one thread per frame: everything DecodeModesMessage fills after the CRC stage
+//                   (ADSB1090.cpp:525-672).  32-byte record in, 80-byte record out, no shared state.
+//   cpr_kernel      one thread per even/odd pair: DecodeCpr (ADSB1090.cpp:1079-1121) with the NL table of
+//                   :993-1055, in IEEE doubles with explicit round-to-nearest intrinsics so that the compiler
+//                   cannot contract a*b+c into an FMA the reference's x86-64 build does not have.
+//
+// The one libm call on the path, atan2 in the velocity heading (:649-652), is not reproducible bit for bit with
+// the device's atan2, and the result is truncated to whole degrees.  The heading therefore comes from a table
+// over all 2^22 (ew_dir, ns_dir, ew_velocity, ns_velocity) combinations, filled once per handle by the host's
+// own libm, the one the reference links: exact by construction, 8 MiB of HBM.
+#include "../../include/adsbcu.h"
+#include "adsbcu_internal.h"
+
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+namespace adsbcu {
+
+struct Fields {
+    void *d_in = nullptr, *d_out = nullptr;
+    size_t cap_in = 0, cap_out = 0;         // bytes
+    int16_t *d_heading = nullptr;           // [ew_dir][ns_dir][ew_velocity][ns_velocity]
+};
+
+namespace {
+
+constexpr uint32_t kHeadingEntries = 1u << 22;
+
+__device__ __forceinline__ int32_t to_i32(double v)
+{
+    // static_cast<int32_t>(double) as x86-64 executes it: cvttsd2si, out of range -> INT32_MIN
+    return (v >= 2147483648.0 || v <= -2147483649.0 || v != v) ? INT32_MIN : __double2int_rz(v);
+}
+
+__global__ void __launch_bounds__(256) fields_kernel(const uint4 *in, uint32_t n, uint4 *out, const int16_t *heading_lut)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    // adsbcu_msg_b: pos, crc, addr, msg[14], msgbits, msgtype, errorbit, corrected, reserved
+    const uint4 lo = in[2 * k], hi = in[2 * k + 1];
+    uint8_t m[11];
+    {
+        const uint32_t w[3] = {lo.w, hi.x, hi.y};
+#pragma unroll
+        for (int j = 0; j < 11; ++j) m[j] = uint8_t(w[j >> 2] >> (8 * (j & 3)));
+    }
+    const int df = hi.z >> 24;              // hi.z = msg[12], msg[13], msgbits, msgtype: the DF as sliced
+
+    int32_t f[20];
+#pragma unroll
+    for (int j = 0; j < 20; ++j) f[j] = 0;
+    enum { CA, METYPE, MESUB, HEADING, FFLAG, RAWLAT, RAWLON, FLIGHT0, FLIGHT1, EWDIR, EWVEL, NSDIR, NSVEL, VELOCITY, FS, DR, UM,
+           IDENTITY, ALTITUDE, UNIT };
+    f[CA] = f[FS] = m[0] & 7;
+    f[METYPE] = m[4] >> 3;
+    f[MESUB] = m[4] & 7;
+    f[DR] = m[1] >> 3;
+    f[UM] = ((m[1] & 7) << 3) | (m[2] >> 5);
+    {
+        const int a = ((m[3] & 0x80) >> 5) | (m[2] & 0x02) | ((m[2] & 0x08) >> 3);
+        const int b = ((m[3] & 0x02) << 1) | ((m[3] & 0x08) >> 2) | ((m[3] & 0x20) >> 5);
+        const int c = ((m[2] & 0x01) << 2) | ((m[2] & 0x04) >> 1) | ((m[2] & 0x10) >> 4);
+        const int d = ((m[3] & 0x01) << 2) | ((m[3] & 0x04) >> 1) | ((m[3] & 0x10) >> 4);
+        f[IDENTITY] = a * 1000 + b * 100 + c * 10 + d;
+    }
+    if (df == 0 || df == 4 || df == 16 || df == 20) {       // 13-bit altitude code (:440-466)
+        if (m[3] & 0x40) f[UNIT] = 1;
+        else if (m[3] & 0x10)
+            f[ALTITUDE] = ((((m[2] & 31) << 6) | ((m[3] & 0x80) >> 2) | ((m[3] & 0x20) >> 1) | (m[3] & 15)) * 25) - 1000;
+    }
+    if (df == 17) {
+        const int me = f[METYPE], sub = f[MESUB];
+        if (me >= 1 && me <= 4) {
+            // eight 6-bit characters in msg[5..10]; the reference's charset: 1..26 letters, 32 space, 48..57 digits
+            uint64_t v = 0;
+#pragma unroll
+            for (int j = 5; j <= 10; ++j) v = (v << 8) | m[j];
+            uint32_t pack[2] = {0, 0};
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const uint32_t c = uint32_t(v >> (42 - 6 * j)) & 63;
+                const uint32_t ch = (c >= 1 && c <= 26) ? c + 64 : (c == 32 || (c >= 48 && c <= 57)) ? c : uint32_t('?');
+                pack[j >> 2] |= ch << (8 * (j & 3));
+            }
+            f[FLIGHT0] = int32_t(pack[0]);
+            f[FLIGHT1] = int32_t(pack[1]);
+        } else if (me >= 9 && me <= 18) {
+            f[FFLAG] = m[6] & 4;
+            if (m[5] & 1) f[ALTITUDE] = ((((m[5] >> 1) << 4) | (m[6] >> 4)) * 25) - 1000;   // 12-bit code (:470-486)
+            f[RAWLAT] = ((m[6] & 3) << 15) | (m[7] << 7) | (m[8] >> 1);
+            f[RAWLON] = ((m[8] & 1) << 16) | (m[9] << 8) | m[10];
+        } else if (me == 19 && sub >= 1 && sub <= 4) {
+            if (sub <= 2) {
+                const int ewd = (m[5] >> 2) & 1, ewv = ((m[5] & 3) << 8) | m[6];
+                const int nsd = m[7] >> 7, nsv = ((m[7] & 0x7f) << 3) | (m[8] >> 5);
+                f[EWDIR] = ewd; f[EWVEL] = ewv; f[NSDIR] = nsd; f[NSVEL] = nsv;
+                f[VELOCITY] = __double2int_rz(__dsqrt_rn(double(nsv * nsv + ewv * ewv)));
+                if (f[VELOCITY]) f[HEADING] = heading_lut[(ewd << 21) | (nsd << 20) | (ewv << 10) | nsv];
+            } else {
+                f[HEADING] = __double2int_rz(__dmul_rn(360.0 / 128, double(((m[5] & 3) << 5) | (m[6] >> 3))));
+            }
+        }
+    }
+    uint4 *o = out + 5 * size_t(k);
+#pragma unroll
+    for (int j = 0; j < 5; ++j) o[j] = make_uint4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+}
+
+// NL(lat): the 58 zone edges of 1090-WP-9-14 as the reference lists them (ADSB1090.cpp:993-1055)
+__constant__ double c_nl_edge[58] = {
+    10.47047130, 14.82817437, 18.18626357, 21.02939493, 23.54504487, 25.82924707, 27.93898710, 29.91135686, 31.77209708,
+    33.53993436, 35.22899598, 36.85025108, 38.41241892, 39.92256684, 41.38651832, 42.80914012, 44.19454951, 45.54626723,
+    46.86733252, 48.16039128, 49.42776439, 50.67150166, 51.89342469, 53.09516153, 54.27817472, 55.44378444, 56.59318756,
+    57.72747354, 58.84763776, 59.95459277, 61.04917774, 62.13216659, 63.20427479, 64.26616523, 65.31845310, 66.36171008,
+    67.39646774, 68.42322022, 69.44242631, 70.45451075, 71.45986473, 72.45884545, 73.45177442, 74.43893416, 75.42056257,
+    76.39684391, 77.36789461, 78.33374083, 79.29428225, 80.24923213, 81.19801349, 82.13956981, 83.07199445, 83.99173563,
+    84.89166191, 85.75541621, 86.53536998, 87.00000000};
+
+__device__ __forceinline__ int cpr_nl(double lat)
+{
+    lat = fabs(lat);
+    // number of edges <= lat, by bisection over the sorted table (58 entries, 6 probes)
+    int lo = 0, hi = 58;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (lat < c_nl_edge[mid]) hi = mid; else lo = mid + 1;
+    }
+    return 59 - lo;
+}
+__device__ __forceinline__ int cpr_mod(int a, int b) { const int r = a % b; return r < 0 ? r + b : r; }
+
+__global__ void __launch_bounds__(256) cpr_kernel(const adsbcu_cpr_pair *in, uint32_t n, adsbcu_cpr_fix *out)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const adsbcu_cpr_pair p = in[k];
+    const double lat0 = p.even_lat, lon0 = p.even_lon, lat1 = p.odd_lat, lon1 = p.odd_lon;
+    adsbcu_cpr_fix r{0, 0, 0};
+    // j = floor((59*lat0 - 60*lat1)/131072 + 0.5)
+    const int j = __double2int_rd(__dadd_rn(__ddiv_rn(__dsub_rn(__dmul_rn(59.0, lat0), __dmul_rn(60.0, lat1)), 131072.0), 0.5));
+    double rlat0 = __dmul_rn(360.0 / 60, __dadd_rn(double(cpr_mod(j, 60)), __ddiv_rn(lat0, 131072.0)));
+    double rlat1 = __dmul_rn(360.0 / 59, __dadd_rn(double(cpr_mod(j, 59)), __ddiv_rn(lat1, 131072.0)));
+    if (rlat0 >= 270) rlat0 = __dsub_rn(rlat0, 360.0);
+    if (rlat1 >= 270) rlat1 = __dsub_rn(rlat1, 360.0);
+    const int nl0 = cpr_nl(rlat0), nl1 = cpr_nl(rlat1);
+    if (nl0 == nl1) {
+        const bool even = p.even_is_newer != 0;
+        const double rlat = even ? rlat0 : rlat1;
+        const int nl = even ? nl0 : nl1, ni = max(nl - (even ? 0 : 1), 1);
+        const int m = __double2int_rd(__dadd_rn(
+            __ddiv_rn(__dsub_rn(__dmul_rn(lon0, double(nl - 1)), __dmul_rn(lon1, double(nl))), 131072.0), 0.5));
+        double lon = __dmul_rn(__dmul_rn(__ddiv_rn(360.0, double(ni)),
+                                         __dadd_rn(double(cpr_mod(m, ni)), __ddiv_rn(even ? lon0 : lon1, 131072.0))),
+                               10000000.0);
+        if (lon > 1800000000.0) lon = __dsub_rn(lon, 3600000000.0);
+        r.lat1e7 = to_i32(__dmul_rn(rlat, 10000000.0));
+        r.lon1e7 = to_i32(lon);
+        r.valid = 1;
+    }
+    out[k] = r;
+}
+
+bool grow(void *&p, size_t &cap, size_t need)
+{
+    if (need <= cap) return true;
+    cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    const size_t want = need + need / 2;
+    if (cudaMalloc(&p, want) != cudaSuccess) return false;
+    cap = want;
+    return true;
+}
+
+int fail(std::string &err, const char *what, cudaError_t e)
+{
+    err = std::string(what) + ": " + cudaGetErrorString(e);
+    return ADSBCU_ERR_CUDA;
+}
+
+}  // namespace
+
+int fields_decode(Fields *&f, cudaStream_t s, const adsbcu_msg_b *msgs, size_t n, adsbcu_fields_b *out, std::string &err)
+{
+    static_assert(sizeof(adsbcu_msg_b) == 32 && sizeof(adsbcu_fields_b) == 80, "record layout");
+    if (!f) f = new Fields();
+    if (!n) return ADSBCU_OK;
+    cudaError_t e;
+    if (!f->d_heading) {
+        // heading of every (ew_dir, ns_dir, ew_velocity, ns_velocity): ADSB1090.cpp:640-656 on the host's libm
+        std::vector<int16_t> lut(kHeadingEntries);
+        for (uint32_t i = 0; i < kHeadingEntries; ++i) {
+            int ewv = int((i >> 10) & 1023), nsv = int(i & 1023);
+            if (i >> 21) ewv = -ewv;
+            if ((i >> 20) & 1) nsv = -nsv;
+            int h = int(std::atan2(double(ewv), double(nsv)) * 360 / (M_PI * 2));
+            if (h < 0) h += 360;
+            lut[i] = int16_t(h);
+        }
+        if ((e = cudaMalloc(&f->d_heading, kHeadingEntries * sizeof(int16_t))) != cudaSuccess) return fail(err, "cudaMalloc(heading)", e);
+        if ((e = cudaMemcpy(f->d_heading, lut.data(), kHeadingEntries * sizeof(int16_t), cudaMemcpyHostToDevice)) != cudaSuccess)
+            return fail(err, "cudaMemcpy(heading)", e);
+    }
+    if (!grow(f->d_in, f->cap_in, n * sizeof(adsbcu_msg_b)) || !grow(f->d_out, f->cap_out, n * sizeof(adsbcu_fields_b)))
+        return fail(err, "cudaMalloc(fields)", cudaGetLastError());
+    if ((e = cudaMemcpyAsync(f->d_in, msgs, n * sizeof(adsbcu_msg_b), cudaMemcpyHostToDevice, s)) != cudaSuccess)
+        return fail(err, "H2D(fields)", e);
+    fields_kernel<<<unsigned((n + 255) / 256), 256, 0, s>>>(static_cast<const uint4 *>(f->d_in), uint32_t(n),
+                                                            static_cast<uint4 *>(f->d_out), f->d_heading);
+    if ((e = cudaGetLastError()) != cudaSuccess) return fail(err, "fields_kernel", e);
+    if ((e = cudaMemcpyAsync(out, f->d_out, n * sizeof(adsbcu_fields_b), cudaMemcpyDeviceToHost, s)) != cudaSuccess)
+        return fail(err, "D2H(fields)", e);
+    if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail(err, "fields sync", e);
+    return ADSBCU_OK;
+}
+
+int cpr_decode(Fields *&f, cudaStream_t s, const adsbcu_cpr_pair *pairs, size_t n, adsbcu_cpr_fix *out, std::string &err)
+{
+    if (!f) f = new Fields();
+    if (!n) return ADSBCU_OK;
+    cudaError_t e;
+    if (!grow(f->d_in, f->cap_in, n * sizeof(adsbcu_cpr_pair)) || !grow(f->d_out, f->cap_out, n * sizeof(adsbcu_cpr_fix)))
+        return fail(err, "cudaMalloc(cpr)", cudaGetLastError());
+    if ((e = cudaMemcpyAsync(f->d_in, pairs, n * sizeof(adsbcu_cpr_pair), cudaMemcpyHostToDevice, s)) != cudaSuccess)
+        return fail(err, "H2D(cpr)", e);
+    cpr_kernel<<<unsigned((n + 255) / 256), 256, 0, s>>>(static_cast<const adsbcu_cpr_pair *>(f->d_in), uint32_t(n),
+                                                         static_cast<adsbcu_cpr_fix *>(f->d_out));
+    if ((e = cudaGetLastError()) != cudaSuccess) return fail(err, "cpr_kernel", e);
+    if ((e = cudaMemcpyAsync(out, f->d_out, n * sizeof(adsbcu_cpr_fix), cudaMemcpyDeviceToHost, s)) != cudaSuccess)
+        return fail(err, "D2H(cpr)", e);
+    if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail(err, "cpr sync", e);
+    return ADSBCU_OK;
+}
+
+void fields_free(Fields *f)
+{
+    if (!f) return;
+    cudaFree(f->d_in);
+    cudaFree(f->d_out);
+    cudaFree(f->d_heading);
+    delete f;
+}
+
+}  // namespace adsbcu

@@ -196,7 +196,16 @@ void pathb_reset(PathB *b);
 void pathb_free(PathB *b);
 }  // namespace adsbcu
 struct adsbcu_uat_frame;
+struct adsbcu_fields_b;
+struct adsbcu_cpr_pair;
+struct adsbcu_cpr_fix;
 namespace adsbcu {
+// Path B, next layer (adsbcu_fields.cu): bulk field decode and CPR
+struct Fields;
+int  fields_decode(Fields *&f, cudaStream_t s, const adsbcu_msg_b *msgs, size_t n, adsbcu_fields_b *out, std::string &err);
+int  cpr_decode(Fields *&f, cudaStream_t s, const adsbcu_cpr_pair *pairs, size_t n, adsbcu_cpr_fix *out, std::string &err);
+void fields_free(Fields *f);
+
 // Path C (adsbcu_uat.cu): 978 MHz UAT
 struct PathC;
 int  pathc_feed(PathC *&c, int sm_count, cudaStream_t s, const uint8_t *iq, size_t nbytes, adsbcu_uat_frame *out, size_t cap,

@@ -249,6 +249,115 @@ struct oracle1090b {
     }
 };
 
+/* ---- field decode (ADSB1090.cpp:525-672) and CPR (ADSB1090.cpp:986-1121): SURVEY 8f rank 2 ---- */
+namespace {
+struct Fields {     /* == adsbcu_fields_b */
+    int32_t ca, metype, mesub, heading, fflag, raw_latitude, raw_longitude;
+    char flight[8];
+    int32_t ew_dir, ew_velocity, ns_dir, ns_velocity, velocity, fs, dr, um, identity, altitude, unit;
+};
+static_assert(sizeof(Fields) == 80, "Fields layout");
+
+/* 13-bit altitude code of DF0/4/16/20 (ADSB1090.cpp:440-466), 12-bit of DF17 (:470-486) */
+int altitude13(const uint8_t *m, int32_t &unit)
+{
+    if (m[3] & 0x40) { unit = 1; return 0; }
+    unit = 0;
+    if (!(m[3] & 0x10)) return 0;
+    return ((((m[2] & 31) << 6) | ((m[3] & 0x80) >> 2) | ((m[3] & 0x20) >> 1) | (m[3] & 15)) * 25) - 1000;
+}
+int altitude12(const uint8_t *m, int32_t &unit)
+{
+    if (!(m[5] & 1)) return 0;
+    unit = 0;
+    return ((((m[5] >> 1) << 4) | (m[6] >> 4)) * 25) - 1000;
+}
+
+/* m = the frame after the CRC stage's single-bit repair, df = mm.msgtype, which the repair does not refresh (:501,513-519) */
+Fields fields_of(const uint8_t *m, int df)
+{
+    static const char ais[] = "?ABCDEFGHIJKLMNOPQRSTUVWXYZ????? ???????????????0123456789??????";
+    Fields f{};
+    f.ca = f.fs = m[0] & 7;
+    f.metype = m[4] >> 3;
+    f.mesub = m[4] & 7;
+    f.dr = m[1] >> 3;
+    f.um = ((m[1] & 7) << 3) | (m[2] >> 5);
+    const int a = ((m[3] & 0x80) >> 5) | (m[2] & 0x02) | ((m[2] & 0x08) >> 3);
+    const int b = ((m[3] & 0x02) << 1) | ((m[3] & 0x08) >> 2) | ((m[3] & 0x20) >> 5);
+    const int c = ((m[2] & 0x01) << 2) | ((m[2] & 0x04) >> 1) | ((m[2] & 0x10) >> 4);
+    const int d = ((m[3] & 0x01) << 2) | ((m[3] & 0x04) >> 1) | ((m[3] & 0x10) >> 4);
+    f.identity = a * 1000 + b * 100 + c * 10 + d;
+    if (df == 0 || df == 4 || df == 16 || df == 20) f.altitude = altitude13(m, f.unit);
+    if (df != 17) return f;
+    if (f.metype >= 1 && f.metype <= 4) {
+        uint64_t v = 0;
+        for (int k = 5; k <= 10; ++k) v = (v << 8) | m[k];
+        for (int k = 0; k < 8; ++k) f.flight[k] = ais[(v >> (42 - 6 * k)) & 63];
+    } else if (f.metype >= 9 && f.metype <= 18) {
+        f.fflag = m[6] & 4;
+        f.altitude = altitude12(m, f.unit);
+        f.raw_latitude = ((m[6] & 3) << 15) | (m[7] << 7) | (m[8] >> 1);
+        f.raw_longitude = ((m[8] & 1) << 16) | (m[9] << 8) | m[10];
+    } else if (f.metype == 19 && f.mesub >= 1 && f.mesub <= 4) {
+        if (f.mesub <= 2) {
+            f.ew_dir = (m[5] >> 2) & 1;
+            f.ew_velocity = ((m[5] & 3) << 8) | m[6];
+            f.ns_dir = m[7] >> 7;
+            f.ns_velocity = ((m[7] & 0x7f) << 3) | (m[8] >> 5);
+            f.velocity = int(std::sqrt(double(f.ns_velocity * f.ns_velocity + f.ew_velocity * f.ew_velocity)));
+            if (f.velocity) {
+                const int ewv = f.ew_dir ? -f.ew_velocity : f.ew_velocity, nsv = f.ns_dir ? -f.ns_velocity : f.ns_velocity;
+                f.heading = int(std::atan2(double(ewv), double(nsv)) * 360 / (M_PI * 2));
+                if (f.heading < 0) f.heading += 360;
+            }
+        } else {
+            f.heading = int((360.0 / 128) * (((m[5] & 3) << 5) | (m[6] >> 3)));
+        }
+    }
+    return f;
+}
+
+int cpr_nl(double lat)      /* the table of 1090-WP-9-14 as ADSB1090.cpp:993-1055 holds it */
+{
+    static const double edge[58] = {
+        10.47047130, 14.82817437, 18.18626357, 21.02939493, 23.54504487, 25.82924707, 27.93898710, 29.91135686, 31.77209708,
+        33.53993436, 35.22899598, 36.85025108, 38.41241892, 39.92256684, 41.38651832, 42.80914012, 44.19454951, 45.54626723,
+        46.86733252, 48.16039128, 49.42776439, 50.67150166, 51.89342469, 53.09516153, 54.27817472, 55.44378444, 56.59318756,
+        57.72747354, 58.84763776, 59.95459277, 61.04917774, 62.13216659, 63.20427479, 64.26616523, 65.31845310, 66.36171008,
+        67.39646774, 68.42322022, 69.44242631, 70.45451075, 71.45986473, 72.45884545, 73.45177442, 74.43893416, 75.42056257,
+        76.39684391, 77.36789461, 78.33374083, 79.29428225, 80.24923213, 81.19801349, 82.13956981, 83.07199445, 83.99173563,
+        84.89166191, 85.75541621, 86.53536998, 87.00000000};
+    if (lat < 0) lat = -lat;
+    for (int k = 0; k < 58; ++k)
+        if (lat < edge[k]) return 59 - k;
+    return 1;
+}
+int cpr_mod(int a, int b) { const int r = a % b; return r < 0 ? r + b : r; }
+int32_t to_i32(double v)     /* the reference's static_cast<int32_t> as x86-64 executes it (cvttsd2si: out of range -> INT32_MIN) */
+{
+    return (v >= 2147483648.0 || v <= -2147483649.0 || v != v) ? INT32_MIN : int32_t(v);
+}
+
+int cpr_global(double lat0, double lon0, double lat1, double lon1, bool even_newer, int32_t out[2])   /* DecodeCpr :1079-1121 */
+{
+    const int j = int(std::floor(((59 * lat0 - 60 * lat1) / 131072) + 0.5));
+    double rlat0 = (360.0 / 60) * (cpr_mod(j, 60) + lat0 / 131072);
+    double rlat1 = (360.0 / 59) * (cpr_mod(j, 59) + lat1 / 131072);
+    if (rlat0 >= 270) rlat0 -= 360;
+    if (rlat1 >= 270) rlat1 -= 360;
+    if (cpr_nl(rlat0) != cpr_nl(rlat1)) return 0;
+    const double rlat = even_newer ? rlat0 : rlat1;
+    const int nl = cpr_nl(rlat), ni = std::max(nl - (even_newer ? 0 : 1), 1);
+    const int m = int(std::floor((((lon0 * (nl - 1)) - (lon1 * nl)) / 131072) + 0.5));
+    double lon = (360.0 / ni) * (cpr_mod(m, ni) + (even_newer ? lon0 : lon1) / 131072) * 10000000;
+    if (lon > 180 * 10000000.0) lon -= 3600000000.0;
+    out[0] = to_i32(rlat * 10000000);
+    out[1] = to_i32(lon);
+    return 1;
+}
+}  // namespace
+
 extern "C" {
 
 oracle1090b *oracle1090b_create(void)
@@ -276,6 +385,35 @@ void oracle1090b_decode(oracle1090b *o, uint8_t *msg, int32_t out[6])
     const Decoded d = o->decode(msg);
     std::memcpy(msg, d.msg, 14);
     out[0] = d.msgbits; out[1] = d.msgtype; out[2] = d.crcok; out[3] = d.errorbit; out[4] = int32_t(d.crc); out[5] = int32_t(d.addr);
+}
+/* CRC stage (repairs DF11/17 single-bit errors) then every other Message field; out = adsbcu_fields_b as 20 int32 */
+void oracle1090b_fields(oracle1090b *o, const uint8_t *msg, int32_t out[20])
+{
+    const Decoded d = o->decode(msg);
+    const Fields f = fields_of(d.msg, d.msgtype);
+    std::memcpy(out, &f, sizeof f);
+}
+int oracle1090b_cpr(int even_lat, int even_lon, int odd_lat, int odd_lon, int even_is_newer, int32_t out[2])
+{
+    out[0] = out[1] = INT32_MIN;
+    return cpr_global(even_lat, even_lon, odd_lat, odd_lon, even_is_newer != 0, out);
+}
+/* many frames / pairs per call, for timing the CPU side without per-call binding overhead */
+void oracle1090b_fields_bulk(const uint8_t *msgs14, const uint8_t *msgtype, size_t n, int32_t *out20)
+{
+    for (size_t k = 0; k < n; ++k) {      /* frames already past the CRC stage, like adsbcu_1090b_decode_fields */
+        const Fields f = fields_of(msgs14 + 14 * k, msgtype[k]);
+        std::memcpy(out20 + 20 * k, &f, sizeof f);
+    }
+}
+void oracle1090b_cpr_bulk(const int32_t *pairs5, size_t n, int32_t *out3)
+{
+    for (size_t k = 0; k < n; ++k) {
+        const int32_t *p = pairs5 + 5 * k;
+        int32_t r[2] = {0, 0};
+        out3[3 * k + 2] = cpr_global(p[0], p[1], p[2], p[3], p[4] != 0, r);
+        out3[3 * k] = r[0]; out3[3 * k + 1] = r[1];
+    }
 }
 size_t oracle1090b_cache(const oracle1090b *o, uint32_t *out, size_t cap)
 {

@@ -39,9 +39,18 @@ def _bind(path, prefix):
     f("checksum").argtypes = [C.c_void_p, C.c_int]
     f("fix_single").argtypes = [C.c_void_p, C.c_int]
     f("decode").argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    f("fields").argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    f("cpr").argtypes = [C.c_int] * 5 + [C.c_void_p]
     f("cache").restype = C.c_size_t
     f("cache").argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
     return L
+
+# == adsbcu_fields_b (include/adsbcu.h)
+FIELDS_DTYPE = np.dtype([("ca", "<i4"), ("metype", "<i4"), ("mesub", "<i4"), ("heading", "<i4"), ("fflag", "<i4"),
+                         ("raw_latitude", "<i4"), ("raw_longitude", "<i4"), ("flight", "S8"), ("ew_dir", "<i4"),
+                         ("ew_velocity", "<i4"), ("ns_dir", "<i4"), ("ns_velocity", "<i4"), ("velocity", "<i4"), ("fs", "<i4"),
+                         ("dr", "<i4"), ("um", "<i4"), ("identity", "<i4"), ("altitude", "<i4"), ("unit", "<i4")])
+assert FIELDS_DTYPE.itemsize == 80
 
 
 class _Base:
@@ -87,6 +96,37 @@ class _Base:
         self._f("decode")(self.h, b.ctypes.data, o.ctypes.data)
         return dict(msg=bytes(b), msgbits=int(o[0]), msgtype=int(o[1]), crcok=int(o[2]), errorbit=int(o[3]),
                     crc=int(o[4]) & 0xFFFFFF, addr=int(o[5]) & 0xFFFFFF)
+
+    def fields(self, msg: bytes) -> np.ndarray:
+        """Every Message field DecodeModesMessage fills beyond the CRC stage, as one FIELDS_DTYPE record."""
+        b = np.frombuffer(bytes(msg).ljust(14, b"\0"), dtype=np.uint8).copy()
+        o = np.zeros(1, dtype=FIELDS_DTYPE)
+        self._f("fields")(self.h, b.ctypes.data, o.ctypes.data)
+        return o[0]
+
+    def cpr(self, even_lat, even_lon, odd_lat, odd_lon, even_is_newer):
+        """DecodeCpr on one even/odd pair -> (updated, lat1E7, lon1E7)."""
+        o = np.zeros(2, dtype=np.int32)
+        ok = self._f("cpr")(int(even_lat), int(even_lon), int(odd_lat), int(odd_lon), int(bool(even_is_newer)), o.ctypes.data)
+        return int(ok), int(o[0]), int(o[1])
+
+    def fields_bulk(self, msgs14: np.ndarray, msgtype: np.ndarray) -> np.ndarray:
+        """Fields of frames that are already past the CRC stage (msgtype = the DF as sliced)."""
+        msgs14 = np.ascontiguousarray(msgs14, dtype=np.uint8).reshape(-1, 14)
+        msgtype = np.ascontiguousarray(msgtype, dtype=np.uint8)
+        out = np.zeros(msgs14.shape[0], dtype=FIELDS_DTYPE)
+        f = self.L.oracle1090b_fields_bulk
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        f(msgs14.ctypes.data, msgtype.ctypes.data, msgs14.shape[0], out.ctypes.data)
+        return out
+
+    def cpr_bulk(self, pairs5: np.ndarray) -> np.ndarray:
+        pairs5 = np.ascontiguousarray(pairs5, dtype=np.int32).reshape(-1, 5)
+        out = np.zeros((pairs5.shape[0], 3), dtype=np.int32)
+        f = self.L.oracle1090b_cpr_bulk
+        f.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
+        f(pairs5.ctypes.data, pairs5.shape[0], out.ctypes.data)
+        return out
 
     def cache(self) -> set:
         v = np.zeros(1 << 16, dtype=np.uint32)

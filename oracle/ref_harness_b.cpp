@@ -120,6 +120,34 @@ void ref1090b_decode(void *rp, uint8_t *msg, int32_t out[6])
     out[0] = int32_t(mm.msgbits); out[1] = mm.msgtype; out[2] = mm.crcok; out[3] = mm.errorbit; out[4] = int32_t(mm.crc);
     out[5] = (mm.aa1 << 16) | (mm.aa2 << 8) | mm.aa3;
 }
+/* every field DecodeModesMessage fills after the CRC stage (ADSB1090.cpp:525-672); layout = adsbcu_fields_b */
+void ref1090b_fields(void *rp, const uint8_t *msg, int32_t out[20])
+{
+    std::array<uint8_t, 14> m{};
+    std::memcpy(m.data(), msg, 14);
+    const Message mm = static_cast<Ref *>(rp)->h->DecodeModesMessage(m);
+    out[0] = mm.ca; out[1] = mm.metype; out[2] = mm.mesub; out[3] = mm.heading; out[4] = mm.fflag;
+    out[5] = mm.rawLatitude; out[6] = mm.rawLongitude;
+    std::memcpy(&out[7], mm.flight.data(), 8);
+    out[9] = mm.ewDir; out[10] = mm.ewVelocity; out[11] = mm.nsDir; out[12] = mm.nsVelocity; out[13] = mm.velocity;
+    out[14] = mm.fs; out[15] = mm.dr; out[16] = mm.um; out[17] = mm.identity; out[18] = mm.altitude; out[19] = int32_t(mm.unit);
+}
+/* DecodeCpr (ADSB1090.cpp:1079-1121) on one even/odd pair; returns 1 if the position was updated */
+int ref1090b_cpr(int even_lat, int even_lon, int odd_lat, int odd_lon, int even_is_newer, int32_t out[2])
+{
+    int32_t got[2][2];
+    for (int pass = 0; pass < 2; ++pass) {      /* two sentinels tell "not updated" from a value that equals one of them */
+        ADSB::AirCraftImpl a{};
+        a.cprEvenLat = even_lat; a.cprEvenLon = even_lon; a.cprOddLat = odd_lat; a.cprOddLon = odd_lon;
+        a.cprEvenTime = ADSB::AirCraftImpl::time_point{} + std::chrono::seconds(even_is_newer ? 2 : 1);
+        a.cprOddTime = ADSB::AirCraftImpl::time_point{} + std::chrono::seconds(even_is_newer ? 1 : 2);
+        a.lat1E7 = a.lon1E7 = pass ? 12345 : INT32_MIN;
+        DecodeCpr(a);
+        got[pass][0] = a.lat1E7; got[pass][1] = a.lon1E7;
+    }
+    out[0] = got[0][0]; out[1] = got[0][1];
+    return got[0][0] == got[1][0] && got[0][1] == got[1][1];
+}
 size_t ref1090b_cache(void *rp, uint32_t *out, size_t cap)
 {
     size_t k = 0;

@@ -68,3 +68,33 @@ try:
     print(json.dumps({"path": "C cpu checker (1 core)", "msamples_s": part.size / 2 / (time.perf_counter() - t0) / 1e6}))
 except Exception as e:
     print(json.dumps({"path": "C cpu checker", "unavailable": repr(e)}))
+
+# ---- Path B next layer: bulk field decode and CPR (host buffers in, host buffers out) next to the CPU checker
+rng = np.random.default_rng(3)
+N = 4 << 20
+rec = np.zeros(N, dtype=adsbcu.MSG_B_DTYPE)
+rec["msg"] = rng.integers(0, 256, (N, 14), dtype=np.uint8)
+rec["msg"][::2, 0] = (17 << 3) | 5
+rec["msgtype"] = rec["msg"][:, 0] >> 3
+rec["msgbits"] = 112
+pairs = np.zeros(N, dtype=adsbcu.CPR_PAIR_DTYPE)
+for f in ("even_lat", "even_lon", "odd_lat", "odd_lon"):
+    pairs[f] = rng.integers(0, 131072, N)
+dt, _ = timed(lambda: d.decode_fields_b(rec).size)
+print(json.dumps({"path": "B fields (adsbcu_1090b_decode_fields)", "records": N, "mrecords_s": N / dt / 1e6,
+                  "pcie_bytes_per_record": 112}))
+dt, _ = timed(lambda: d.cpr_decode(pairs).size)
+print(json.dumps({"path": "B cpr (adsbcu_cpr_decode)", "pairs": N, "mpairs_s": N / dt / 1e6, "pcie_bytes_per_pair": 32}))
+try:
+    from oracle import oracle1090b as B
+    o = B.Oracle1090B()
+    raw = np.ascontiguousarray(rec["msg"][:1 << 20])
+    t0 = time.perf_counter()
+    o.fields_bulk(raw, np.ascontiguousarray(rec["msgtype"][:1 << 20]))
+    print(json.dumps({"path": "B fields cpu checker (1 core)", "mrecords_s": raw.shape[0] / (time.perf_counter() - t0) / 1e6}))
+    p5 = np.stack([pairs[f][:1 << 20] for f in pairs.dtype.names], axis=1)
+    t0 = time.perf_counter()
+    o.cpr_bulk(p5)
+    print(json.dumps({"path": "B cpr cpu checker (1 core)", "mpairs_s": p5.shape[0] / (time.perf_counter() - t0) / 1e6}))
+except Exception as e:
+    print(json.dumps({"path": "B fields/cpr cpu checker", "unavailable": repr(e)}))
