@@ -194,6 +194,32 @@ int adsbcu_1090_modeac_block(adsbcu_handle *h, const uint8_t *iq, size_t nsample
                              const uint8_t *overlap_iq, size_t n_overlap, uint64_t block_timestamp,
                              adsbcu_msg *out, size_t cap, size_t *n_out);
 
+/* ---- Path A, next layer: CPR position decode ----------------------------------
+ * The three decoders of the flightaware tree's cpr.c, many records per call, results as the same IEEE
+ * doubles the reference computes (bit for bit; dump1090's own cprtests.c vectors are in tests/golden):
+ *   mode ADSBCU_CPR_AIRBORNE           decodeCPRairborne(even_lat, even_lon, odd_lat, odd_lon, fflag, ...)   cpr.c:162-214
+ *   mode ADSBCU_CPR_SURFACE            decodeCPRsurface(reflat, reflon, even.., odd.., fflag, ...)            cpr.c:216-311
+ *   mode ADSBCU_CPR_RELATIVE_AIRBORNE  decodeCPRrelative(reflat, reflon, cprlat, cprlon, fflag, 0, ...)      cpr.c:325-369
+ *   mode ADSBCU_CPR_RELATIVE_SURFACE   decodeCPRrelative(reflat, reflon, cprlat, cprlon, fflag, 1, ...)
+ * For the relative modes the single frame's raw values travel in even_lat / even_lon whatever its parity.
+ * Which decoder to call, with which reference position and how to vet the answer stays with the tracker
+ * (track.c:doGlobalCPR / doLocalCPR). */
+enum { ADSBCU_CPR_AIRBORNE = 0, ADSBCU_CPR_SURFACE = 1, ADSBCU_CPR_RELATIVE_AIRBORNE = 2, ADSBCU_CPR_RELATIVE_SURFACE = 3 };
+typedef struct adsbcu_cpr_in {
+    double  reflat, reflon;             /* reference position, degrees (unused for ADSBCU_CPR_AIRBORNE) */
+    int32_t even_lat, even_lon;         /* 17-bit raw CPR values of the even frame (or of the only frame) */
+    int32_t odd_lat, odd_lon;           /* ... of the odd frame */
+    int32_t fflag;                      /* non-zero: the odd frame is the latest / the only frame is odd */
+    int32_t mode;                       /* ADSBCU_CPR_* */
+} adsbcu_cpr_in;                        /* 40 bytes */
+typedef struct adsbcu_cpr_out {
+    double  lat, lon;                   /* *out_lat, *out_lon; 0 unless result == 0 */
+    int32_t result;                     /* the reference's return value: 0 ok, -1 zone crossing / ambiguous, -2 bad data */
+    int32_t reserved;
+} adsbcu_cpr_out;                       /* 24 bytes */
+/* out[k] = decoder(in[k]); HOST arrays of n records; an unknown mode is ADSBCU_ERR_ARG for the whole call. */
+int adsbcu_1090_cpr_decode(adsbcu_handle *h, const adsbcu_cpr_in *in, size_t n, adsbcu_cpr_out *out);
+
 /* ---- Path B: the 1090 MHz demodulator libadsb itself compiles (2.0 MS/s) --------------------
  * Replaces the body of ADSB1090Handler::HandleData (reference ADSB1090.cpp:158-175) down to the
  * point where the reference calls UseModesMessage() with mm.crcok set (ADSB1090.cpp:741-959,
@@ -256,7 +282,7 @@ typedef struct adsbcu_cpr_fix {
 /* out[k] = DecodeCpr on pairs[k] (HOST arrays).  The caller keeps the reference's 10 s pairing rule
  * (ADSB1090.cpp:1161).  IEEE double arithmetic in the reference's operation order; a latitude outside the
  * int32 range converts to INT32_MIN like the reference's x86-64 build. */
-int adsbcu_cpr_decode(adsbcu_handle *h, const adsbcu_cpr_pair *pairs, size_t n, adsbcu_cpr_fix *out);
+int adsbcu_1090b_cpr_decode(adsbcu_handle *h, const adsbcu_cpr_pair *pairs, size_t n, adsbcu_cpr_fix *out);
 
 
 /* ---- Path C: 978 MHz UAT -----------------------------------------------------------------------

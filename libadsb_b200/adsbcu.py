@@ -32,6 +32,12 @@ assert FIELDS_B_DTYPE.itemsize == 80
 CPR_PAIR_DTYPE = np.dtype([("even_lat", "<i4"), ("even_lon", "<i4"), ("odd_lat", "<i4"), ("odd_lon", "<i4"),
                            ("even_is_newer", "<i4")])
 CPR_FIX_DTYPE = np.dtype([("lat1e7", "<i4"), ("lon1e7", "<i4"), ("valid", "<i4")])
+# adsbcu_cpr_in / adsbcu_cpr_out (dump1090/cpr.c)
+CPR_IN_DTYPE = np.dtype([("reflat", "<f8"), ("reflon", "<f8"), ("even_lat", "<i4"), ("even_lon", "<i4"), ("odd_lat", "<i4"),
+                         ("odd_lon", "<i4"), ("fflag", "<i4"), ("mode", "<i4")])
+CPR_OUT_DTYPE = np.dtype([("lat", "<f8"), ("lon", "<f8"), ("result", "<i4"), ("reserved", "<i4")])
+assert CPR_IN_DTYPE.itemsize == 40 and CPR_OUT_DTYPE.itemsize == 24
+CPR_AIRBORNE, CPR_SURFACE, CPR_RELATIVE_AIRBORNE, CPR_RELATIVE_SURFACE = 0, 1, 2, 3
 
 CAND_DTYPE = np.dtype([("pos", "<u8"), ("phase", "u1"), ("kind", "u1"), ("corrections", "i1"), ("msgtype", "u1"),
                        ("verbatim", "u1", 14), ("msg", "u1", 14), ("crc", "<u4"), ("addr", "<u4"), ("test_key", "<u4"),
@@ -44,7 +50,7 @@ EXPORTS = ["adsbcu_abi_version", "adsbcu_last_error", "adsbcu_create", "adsbcu_d
            "adsbcu_1090_filter_test", "adsbcu_get_stats", "adsbcu_1090b_feed", "adsbcu_1090b_reset",
            "adsbcu_978_feed", "adsbcu_978_reset", "adsbcu_978_phase", "adsbcu_1090_seek", "adsbcu_1090_scan_candidates",
            "adsbcu_1090_known_export", "adsbcu_1090_known_import", "adsbcu_1090_revive", "adsbcu_1090_resolve", "adsbcu_1090_modeac_block", "adsbcu_1090_feed_sc16",
-           "adsbcu_1090b_decode_fields", "adsbcu_cpr_decode"]
+           "adsbcu_1090b_decode_fields", "adsbcu_1090b_cpr_decode", "adsbcu_1090_cpr_decode"]
 
 
 class Config(C.Structure):
@@ -87,7 +93,8 @@ def load():
         L.adsbcu_1090b_feed.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.adsbcu_1090b_reset.argtypes = [C.c_void_p]
         L.adsbcu_1090b_decode_fields.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
-        L.adsbcu_cpr_decode.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.adsbcu_1090b_cpr_decode.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.adsbcu_1090_cpr_decode.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         L.adsbcu_978_feed.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.adsbcu_978_reset.argtypes = [C.c_void_p]
         L.adsbcu_978_phase.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
@@ -175,6 +182,13 @@ class Demod1090:
         self._check(load().adsbcu_1090b_feed(self.h, iq.ctypes.data, iq.size, out.ctypes.data, cap, C.byref(got)))
         return out[:got.value]
 
+    def cpr_decode_a(self, rec: np.ndarray) -> np.ndarray:
+        """dump1090's decodeCPRairborne / decodeCPRsurface / decodeCPRrelative on every CPR_IN_DTYPE record."""
+        rec = np.ascontiguousarray(rec, dtype=CPR_IN_DTYPE)
+        out = np.zeros(rec.size, dtype=CPR_OUT_DTYPE)
+        self._check(load().adsbcu_1090_cpr_decode(self.h, rec.ctypes.data, rec.size, out.ctypes.data))
+        return out
+
     def decode_fields_b(self, msgs: np.ndarray) -> np.ndarray:
         """Path B, next layer: the Message fields DecodeModesMessage fills after the CRC stage, for every record."""
         msgs = np.ascontiguousarray(msgs, dtype=MSG_B_DTYPE)
@@ -186,7 +200,7 @@ class Demod1090:
         """DecodeCpr on every even/odd pair (CPR_PAIR_DTYPE) -> CPR_FIX_DTYPE."""
         pairs = np.ascontiguousarray(pairs, dtype=CPR_PAIR_DTYPE)
         out = np.zeros(pairs.size, dtype=CPR_FIX_DTYPE)
-        self._check(load().adsbcu_cpr_decode(self.h, pairs.ctypes.data, pairs.size, out.ctypes.data))
+        self._check(load().adsbcu_1090b_cpr_decode(self.h, pairs.ctypes.data, pairs.size, out.ctypes.data))
         return out
 
     def reset_b(self):

@@ -1,7 +1,9 @@
-// Path B, the layer after the CRC stage: bulk field decode and CPR.
+// The layer after the CRC stage: bulk field decode and CPR for libadsb's own handler (Path B),
+// and the CPR decoders of dump1090/cpr.c (Path A).
 //
 //   fields_kernel   one thread per frame: everything DecodeModesMessage fills after the CRC stage
 //                   (ADSB1090.cpp:525-672).  32-byte record in, 80-byte record out, no shared state.
+//   cpr_a_kernel    one thread per record: decodeCPRairborne / decodeCPRsurface / decodeCPRrelative (cpr.c:162-369)
 //   cpr_kernel      one thread per even/odd pair: DecodeCpr (ADSB1090.cpp:1079-1121) with the NL table of
 //                   :993-1055, in IEEE doubles with explicit round-to-nearest intrinsics so that the compiler
 //                   cannot contract a*b+c into an FMA the reference's x86-64 build does not have.
@@ -163,6 +165,81 @@ __global__ void __launch_bounds__(256) cpr_kernel(const adsbcu_cpr_pair *in, uin
     out[k] = r;
 }
 
+// ---- Path A: dump1090/cpr.c.  Every double step goes through an explicit round-to-nearest intrinsic in the
+// reference's operation order; fmod and floor are exact on both sides. ------------------------------------
+__device__ __forceinline__ double dadd(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ double dsub(double a, double b) { return __dsub_rn(a, b); }
+__device__ __forceinline__ double dmul(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ double ddiv(double a, double b) { return __ddiv_rn(a, b); }
+__device__ __forceinline__ int cpr_zones(double lat, int odd) { return max(cpr_nl(lat) - odd, 1); }     // cpr.c:142-146
+__device__ __forceinline__ double pfmod(double a, double b) { const double r = fmod(a, b); return r < 0 ? dadd(r, b) : r; }
+
+__device__ __forceinline__ double surface_quadrant(double rlat, double reflat)     // cpr.c:262-278
+{
+    if (rlat == 0) return reflat < -45 ? -90.0 : reflat > 45 ? 90.0 : rlat;
+    return dsub(rlat, reflat) > 45 ? dsub(rlat, 90.0) : rlat;
+}
+
+__device__ int cpr_global(const adsbcu_cpr_in &in, bool surface, double &out_lat, double &out_lon)   // cpr.c:162-311
+{
+    const double span = surface ? 90.0 : 360.0;
+    const double lat0 = in.even_lat, lat1 = in.odd_lat, lon0 = in.even_lon, lon1 = in.odd_lon;
+    const int j = __double2int_rd(dadd(ddiv(dsub(dmul(59.0, lat0), dmul(60.0, lat1)), 131072.0), 0.5));
+    double rlat0 = dmul(ddiv(span, 60.0), dadd(double(cpr_mod(j, 60)), ddiv(lat0, 131072.0)));
+    double rlat1 = dmul(ddiv(span, 59.0), dadd(double(cpr_mod(j, 59)), ddiv(lat1, 131072.0)));
+    if (surface) {
+        rlat0 = surface_quadrant(rlat0, in.reflat);
+        rlat1 = surface_quadrant(rlat1, in.reflat);
+    } else {
+        if (rlat0 >= 270) rlat0 = dsub(rlat0, 360.0);
+        if (rlat1 >= 270) rlat1 = dsub(rlat1, 360.0);
+    }
+    if (rlat0 < -90 || rlat0 > 90 || rlat1 < -90 || rlat1 > 90) return -2;
+    const int nl0 = cpr_nl(rlat0), nl1 = cpr_nl(rlat1);
+    if (nl0 != nl1) return -1;
+    const bool odd = in.fflag != 0;
+    const double rlat = odd ? rlat1 : rlat0;
+    const int ni = max(nl0 - (odd ? 1 : 0), 1);
+    const int m = __double2int_rd(dadd(ddiv(dsub(dmul(lon0, double(nl0 - 1)), dmul(lon1, double(nl0))), 131072.0), 0.5));
+    double rlon = dmul(ddiv(span, double(ni)), dadd(double(cpr_mod(m, ni)), ddiv(odd ? lon1 : lon0, 131072.0)));
+    if (surface) rlon = dadd(rlon, dmul(floor(ddiv(dadd(dsub(in.reflon, rlon), 45.0), 90.0)), 90.0));
+    rlon = dsub(rlon, dmul(floor(ddiv(dadd(rlon, 180.0), 360.0)), 360.0));
+    out_lat = rlat;
+    out_lon = rlon;
+    return 0;
+}
+
+__device__ int cpr_relative(const adsbcu_cpr_in &in, bool surface, double &out_lat, double &out_lon)   // cpr.c:325-369
+{
+    const bool odd = in.fflag != 0;
+    const double flat = ddiv(double(in.even_lat), 131072.0), flon = ddiv(double(in.even_lon), 131072.0);
+    const double dlat = ddiv(surface ? 90.0 : 360.0, odd ? 59.0 : 60.0);
+    const int j = __double2int_rz(dadd(floor(ddiv(in.reflat, dlat)), floor(dsub(dadd(0.5, ddiv(pfmod(in.reflat, dlat), dlat)), flat))));
+    double rlat = dmul(dlat, dadd(double(j), flat));
+    if (rlat >= 270) rlat = dsub(rlat, 360.0);
+    if (rlat < -90 || rlat > 90) return -1;
+    if (fabs(dsub(rlat, in.reflat)) > ddiv(dlat, 2.0)) return -1;
+    const double dlon = ddiv(surface ? 90.0 : 360.0, double(cpr_zones(rlat, odd ? 1 : 0)));
+    const int m = __double2int_rz(dadd(floor(ddiv(in.reflon, dlon)), floor(dsub(dadd(0.5, ddiv(pfmod(in.reflon, dlon), dlon)), flon))));
+    double rlon = dmul(dlon, dadd(double(m), flon));
+    if (rlon > 180) rlon = dsub(rlon, 360.0);
+    if (fabs(dsub(rlon, in.reflon)) > ddiv(dlon, 2.0)) return -1;
+    out_lat = rlat;
+    out_lon = rlon;
+    return 0;
+}
+
+__global__ void __launch_bounds__(256) cpr_a_kernel(const adsbcu_cpr_in *in, uint32_t n, adsbcu_cpr_out *out)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const adsbcu_cpr_in r = in[k];
+    adsbcu_cpr_out o{0.0, 0.0, 0, 0};
+    o.result = r.mode < ADSBCU_CPR_RELATIVE_AIRBORNE ? cpr_global(r, r.mode == ADSBCU_CPR_SURFACE, o.lat, o.lon)
+                                                     : cpr_relative(r, r.mode == ADSBCU_CPR_RELATIVE_SURFACE, o.lat, o.lon);
+    out[k] = o;
+}
+
 bool grow(void *&p, size_t &cap, size_t need)
 {
     if (need <= cap) return true;
@@ -230,6 +307,27 @@ int cpr_decode(Fields *&f, cudaStream_t s, const adsbcu_cpr_pair *pairs, size_t 
                                                          static_cast<adsbcu_cpr_fix *>(f->d_out));
     if ((e = cudaGetLastError()) != cudaSuccess) return fail(err, "cpr_kernel", e);
     if ((e = cudaMemcpyAsync(out, f->d_out, n * sizeof(adsbcu_cpr_fix), cudaMemcpyDeviceToHost, s)) != cudaSuccess)
+        return fail(err, "D2H(cpr)", e);
+    if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail(err, "cpr sync", e);
+    return ADSBCU_OK;
+}
+
+int cpr_a_decode(Fields *&f, cudaStream_t s, const adsbcu_cpr_in *in, size_t n, adsbcu_cpr_out *out, std::string &err)
+{
+    static_assert(sizeof(adsbcu_cpr_in) == 40 && sizeof(adsbcu_cpr_out) == 24, "record layout");
+    if (!f) f = new Fields();
+    if (!n) return ADSBCU_OK;
+    for (size_t k = 0; k < n; ++k)
+        if (in[k].mode < 0 || in[k].mode > ADSBCU_CPR_RELATIVE_SURFACE) { err = "bad argument (unknown CPR mode)"; return ADSBCU_ERR_ARG; }
+    cudaError_t e;
+    if (!grow(f->d_in, f->cap_in, n * sizeof(adsbcu_cpr_in)) || !grow(f->d_out, f->cap_out, n * sizeof(adsbcu_cpr_out)))
+        return fail(err, "cudaMalloc(cpr)", cudaGetLastError());
+    if ((e = cudaMemcpyAsync(f->d_in, in, n * sizeof(adsbcu_cpr_in), cudaMemcpyHostToDevice, s)) != cudaSuccess)
+        return fail(err, "H2D(cpr)", e);
+    cpr_a_kernel<<<unsigned((n + 255) / 256), 256, 0, s>>>(static_cast<const adsbcu_cpr_in *>(f->d_in), uint32_t(n),
+                                                           static_cast<adsbcu_cpr_out *>(f->d_out));
+    if ((e = cudaGetLastError()) != cudaSuccess) return fail(err, "cpr_a_kernel", e);
+    if ((e = cudaMemcpyAsync(out, f->d_out, n * sizeof(adsbcu_cpr_out), cudaMemcpyDeviceToHost, s)) != cudaSuccess)
         return fail(err, "D2H(cpr)", e);
     if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail(err, "cpr sync", e);
     return ADSBCU_OK;

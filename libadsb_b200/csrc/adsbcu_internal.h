@@ -199,11 +199,14 @@ struct adsbcu_uat_frame;
 struct adsbcu_fields_b;
 struct adsbcu_cpr_pair;
 struct adsbcu_cpr_fix;
+struct adsbcu_cpr_in;
+struct adsbcu_cpr_out;
 namespace adsbcu {
 // Path B, next layer (adsbcu_fields.cu): bulk field decode and CPR
 struct Fields;
 int  fields_decode(Fields *&f, cudaStream_t s, const adsbcu_msg_b *msgs, size_t n, adsbcu_fields_b *out, std::string &err);
 int  cpr_decode(Fields *&f, cudaStream_t s, const adsbcu_cpr_pair *pairs, size_t n, adsbcu_cpr_fix *out, std::string &err);
+int  cpr_a_decode(Fields *&f, cudaStream_t s, const adsbcu_cpr_in *in, size_t n, adsbcu_cpr_out *out, std::string &err);
 void fields_free(Fields *f);
 
 // Path C (adsbcu_uat.cu): 978 MHz UAT

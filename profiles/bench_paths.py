@@ -84,7 +84,7 @@ dt, _ = timed(lambda: d.decode_fields_b(rec).size)
 print(json.dumps({"path": "B fields (adsbcu_1090b_decode_fields)", "records": N, "mrecords_s": N / dt / 1e6,
                   "pcie_bytes_per_record": 112}))
 dt, _ = timed(lambda: d.cpr_decode(pairs).size)
-print(json.dumps({"path": "B cpr (adsbcu_cpr_decode)", "pairs": N, "mpairs_s": N / dt / 1e6, "pcie_bytes_per_pair": 32}))
+print(json.dumps({"path": "B cpr (adsbcu_1090b_cpr_decode)", "pairs": N, "mpairs_s": N / dt / 1e6, "pcie_bytes_per_pair": 32}))
 try:
     from oracle import oracle1090b as B
     o = B.Oracle1090B()
@@ -98,3 +98,17 @@ try:
     print(json.dumps({"path": "B cpr cpu checker (1 core)", "mpairs_s": p5.shape[0] / (time.perf_counter() - t0) / 1e6}))
 except Exception as e:
     print(json.dumps({"path": "B fields/cpr cpu checker", "unavailable": repr(e)}))
+
+# ---- Path A next layer: dump1090's CPR decoders, all four modes mixed
+try:
+    from oracle import oraclecpr as P
+    recs = P.random_records(1 << 20, 5)
+    recs = np.tile(recs, 4)
+    dt, _ = timed(lambda: d.cpr_decode_a(recs).size)
+    print(json.dumps({"path": "A cpr (adsbcu_1090_cpr_decode)", "records": int(recs.size), "mrecords_s": recs.size / dt / 1e6,
+                      "pcie_bytes_per_record": 64}))
+    t0 = time.perf_counter()
+    P.decode(recs[:1 << 20])
+    print(json.dumps({"path": "A cpr cpu checker (1 core)", "mrecords_s": (1 << 20) / (time.perf_counter() - t0) / 1e6}))
+except Exception as e:
+    print(json.dumps({"path": "A cpr", "unavailable": repr(e)}))

@@ -1,6 +1,6 @@
 """bulk field decode and CPR for libadsb's own handler (ADSB1090.cpp:525-672, :986-1121).
 CPU part: the oracle restatement against the reference's own DecodeModesMessage / DecodeCpr (oracle/_ref).
-GPU part: adsbcu_1090b_decode_fields / adsbcu_cpr_decode against the oracle, bit-exact."""
+GPU part: adsbcu_1090b_decode_fields / adsbcu_1090b_cpr_decode against the oracle, bit-exact."""
 import os
 
 import numpy as np
