@@ -22,8 +22,12 @@ constexpr uint32_t kUnchecked     = 0xFFFFFFFFu;
 // sampling grids of the 2.4 MS/s slicer); a tile scans the kTile start positions whose 290-sample
 // lookahead fits in it.
 constexpr int kRun         = 24;              // samples per thread and tile
-constexpr int kGroups      = 4;
-constexpr int kGroupThreads = 256;
+#ifndef ADSBCU_GROUPS               // measurement knobs: -DADSBCU_GROUPS=8 -DADSBCU_GROUP_THREADS=128 (profiles/sweep_groups.sh)
+#define ADSBCU_GROUPS 4
+#define ADSBCU_GROUP_THREADS 256
+#endif
+constexpr int kGroups      = ADSBCU_GROUPS;
+constexpr int kGroupThreads = ADSBCU_GROUP_THREADS;
 constexpr int kTileSamples = kRun * kGroupThreads;   // 6144 magnitudes staged per tile
 constexpr int kTileLead    = 2;               // smem index of the tile's first start position (16 B alignment of x0)
 constexpr int kTile        = kTileSamples - 296;   // start positions per tile (lead + lookahead + pad to a multiple of 8)

@@ -35,8 +35,8 @@ constexpr int kPreCap = kTileSamples / 4;      // positions passing the edge mas
 constexpr int kCandCap = kTileSamples / 8;     // preambles kept per tile (overflow -> error, never silently dropped)
 constexpr int kCandChunk = kGroupThreads;      // preambles per slicer round
 constexpr int kQueueCap = 5 * kCandChunk;      // (preamble, phase) items per round
-constexpr int kKeepCap = kTileSamples / 8;     // kept (position, phase) records per tile
-constexpr int kBuckets = 128, kBucketShift = 9; // phase D counting sort: 64 positions x 8 phase slots per bucket
+constexpr int kKeepCap = kGroups > 4 ? kTileSamples / 10 : kTileSamples / 8;     // kept (position, phase) records per tile
+constexpr int kBuckets = kTileSamples / 48, kBucketShift = 9; // phase D counting sort: 64 positions x 8 phase slots per bucket
 constexpr int kPosWords = (kTile + 31) / 32;   // 32-position words per tile
 constexpr int kPlaneStride = kGroupThreads + 16;   // symbol-plane fields per plane (+ zeroed slack for the 128-bit reads)
 static_assert(kPosWords + 2 <= kGroupThreads, "phase B: one thread per 32 start positions");
