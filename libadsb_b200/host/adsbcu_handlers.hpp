@@ -23,11 +23,13 @@
 
 #include "../../include/adsbcu.h"
 
+#include <chrono>
 #include <cstdint>
 #include <functional>
 #include <span>
 #include <stdexcept>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 namespace adsbcu_host {
@@ -134,25 +136,102 @@ private:
 };
 
 // ---- Path B -------------------------------------------------------------------------------------
+// What IListener::OnChanged(IAirCraft const&) sees after one message (ADSBListener.h, AircraftImpl.h:9-48)
+struct AircraftState {
+    uint32_t addr = 0;
+    char     callsign[8] = {};
+    int32_t  altitude = 0;
+    uint32_t speed = 0, track = 0;
+    int32_t  lat1E7 = 0, lon1E7 = 0;
+};
+
 class ADSB1090Handler : public IDataHandler {
 public:
     using Sink = std::function<void(adsbcu_msg_b const &)>;   // == UseModesMessage(Message const&), crcok only
+    using AircraftSink = std::function<void(AircraftState const &)>;   // == IListener::OnChanged
     explicit ADSB1090Handler(Sink sink, int device = 0)
         : eng_(make_config(device, 0, 1, 1u << 22)), sink_(std::move(sink)), out_(1u << 16)
     {
+    }
+    // With an aircraft sink the handler also does what follows UseModesMessage in the reference: field decode
+    // (ADSB1090.cpp:597-672) and CPR (:1079-1121) in bulk on the device, the aircraft table of
+    // InteractiveReceiveData (:1125-1175) here, one callback per message in stream order.
+    ADSB1090Handler(Sink sink, AircraftSink aircraft, int device = 0) : ADSB1090Handler(std::move(sink), device)
+    {
+        aircraft_ = std::move(aircraft);
     }
     void HandleData(std::span<uint8_t const> const &data) override
     {
         size_t n = 0;
         eng_.check(adsbcu_1090b_feed(eng_.get(), data.data(), data.size(), out_.data(), out_.size(), &n), "adsbcu_1090b_feed");
-        for (size_t k = 0; k < n; ++k) sink_(out_[k]);
+        if (sink_) for (size_t k = 0; k < n; ++k) sink_(out_[k]);
+        if (aircraft_ && n) track(n);
     }
     void OnDeviceStatusChanged(bool) override {}
 
 private:
+    struct Entry {
+        AircraftState st;
+        int32_t evenLat = 0, evenLon = 0, oddLat = 0, oddLon = 0;
+        std::chrono::system_clock::time_point evenTime{}, oddTime{};
+    };
+    void track(size_t n)
+    {
+        fields_.resize(n);
+        eng_.check(adsbcu_1090b_decode_fields(eng_.get(), out_.data(), n, fields_.data()), "adsbcu_1090b_decode_fields");
+        // pass 1: the CPR pairs every position message will hand to DecodeCpr, in stream order
+        pairs_.clear();
+        pair_of_.assign(n, -1);
+        for (size_t k = 0; k < n; ++k) {
+            adsbcu_fields_b const &f = fields_[k];
+            if (out_[k].msgtype != 17 || f.metype < 9 || f.metype > 18) continue;
+            Entry &e = table_[out_[k].addr];
+            const auto now = std::chrono::system_clock::now();
+            if (f.fflag) { e.oddLat = f.raw_latitude; e.oddLon = f.raw_longitude; e.oddTime = now; }
+            else { e.evenLat = f.raw_latitude; e.evenLon = f.raw_longitude; e.evenTime = now; }
+            const auto apart = std::chrono::duration_cast<std::chrono::seconds>(e.evenTime - e.oddTime).count();
+            if ((apart < 0 ? -apart : apart) > 10) continue;                       // ADSB1090.cpp:1161
+            pair_of_[k] = int(pairs_.size());
+            pairs_.push_back(adsbcu_cpr_pair{e.evenLat, e.evenLon, e.oddLat, e.oddLon, e.evenTime > e.oddTime ? 1 : 0});
+        }
+        fixes_.resize(pairs_.size());
+        if (!pairs_.empty())
+            eng_.check(adsbcu_1090b_cpr_decode(eng_.get(), pairs_.data(), pairs_.size(), fixes_.data()), "adsbcu_1090b_cpr_decode");
+        // pass 2: InteractiveReceiveData's updates and the callback, message by message
+        for (size_t k = 0; k < n; ++k) {
+            adsbcu_fields_b const &f = fields_[k];
+            const int df = out_[k].msgtype;
+            Entry &e = table_[out_[k].addr];
+            e.st.addr = out_[k].addr;
+            if (df == 0 || df == 4 || df == 20) {
+                e.st.altitude = f.altitude;
+            } else if (df == 17) {
+                if (f.metype >= 1 && f.metype <= 4) {
+                    for (int j = 0; j < 8; ++j) e.st.callsign[j] = f.flight[j];
+                } else if (f.metype >= 9 && f.metype <= 18) {
+                    e.st.altitude = f.altitude;
+                    if (pair_of_[k] >= 0 && fixes_[size_t(pair_of_[k])].valid) {
+                        e.st.lat1E7 = fixes_[size_t(pair_of_[k])].lat1e7;
+                        e.st.lon1E7 = fixes_[size_t(pair_of_[k])].lon1e7;
+                    }
+                } else if (f.metype == 19 && (f.mesub == 1 || f.mesub == 2)) {
+                    e.st.speed = uint32_t(f.velocity);
+                    e.st.track = uint32_t(f.heading);
+                }
+            }
+            aircraft_(e.st);
+        }
+    }
+
     Engine eng_;
     Sink sink_;
+    AircraftSink aircraft_;
     std::vector<adsbcu_msg_b> out_;
+    std::vector<adsbcu_fields_b> fields_;
+    std::vector<adsbcu_cpr_pair> pairs_;
+    std::vector<adsbcu_cpr_fix> fixes_;
+    std::vector<int> pair_of_;
+    std::unordered_map<uint32_t, Entry> table_;
 };
 
 // ---- Path C -------------------------------------------------------------------------------------

@@ -4,9 +4,10 @@
 // a file.  Output formats:
 //   path a : "@<12 hex 12 MHz timestamp><hex msg>;"  one line per message (net_io.c:529-545), and with
 //            --beast FILE the Beast binary stream of writeBeastMessage (net_io.c:440-487) on the verbatim bytes
-//   path b : "*<hex msg>;"
+//   path b : "*<hex msg>;", or with --aircraft one "addr,altitude,speed,track,lat1E7,lon1E7,callsign" line per
+//            IListener::OnChanged callback of the reference (field decode + CPR on the device, aircraft table on the host)
 //   path uat: "<updown><hex payload>;rs=<n>;"  (dump978 raw line format)
-// usage: adsbcu_replay --path a|b|uat [--fix|--fix-2bit] [--no-fix-df] [--modeac] [--block BYTES] [--beast FILE] capture.bin
+// usage: adsbcu_replay --path a|b|uat [--fix|--fix-2bit] [--no-fix-df] [--modeac] [--aircraft] [--block BYTES] [--beast FILE] capture.bin
 // (--modeac: every block is one mag_buf of the reference; use --block 262144 to mirror dump1090 --ifile)
 #include "adsbcu_handlers.hpp"
 
@@ -40,7 +41,7 @@ int main(int argc, char **argv)
 {
     std::string path = "a", file, beast_file;
     int nfix = 0, fix_df = 1;
-    bool mode_ac = false;
+    bool mode_ac = false, aircraft = false;
     size_t block = 262144;   // RTLSDR::BufferLength (RTLSDR.hpp:55)
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
@@ -49,6 +50,7 @@ int main(int argc, char **argv)
         else if (a == "--fix-2bit") nfix = 2;
         else if (a == "--no-fix-df") fix_df = 0;
         else if (a == "--modeac") mode_ac = true;
+        else if (a == "--aircraft") aircraft = true;
         else if (a == "--block" && i + 1 < argc) block = std::strtoull(argv[++i], nullptr, 0);
         else if (a == "--beast" && i + 1 < argc) beast_file = argv[++i];
         else file = a;
@@ -69,12 +71,20 @@ int main(int argc, char **argv)
                 ++count;
             }, nfix, fix_df, 0, uint32_t(std::max<size_t>(block / 2, 1u << 20)), mode_ac);
         } else if (path == "b") {
-            h = std::make_unique<ADSB1090Handler>([&](adsbcu_msg_b const &m) {
+            auto raw = [&](adsbcu_msg_b const &m) {
                 std::printf("*");
                 for (int j = 0; j < m.msgbits / 8; ++j) std::printf("%02x", m.msg[j]);
                 std::printf(";\n");
                 ++count;
-            });
+            };
+            if (aircraft)   // one line per IListener::OnChanged: addr,altitude,speed,track,lat1E7,lon1E7,callsign
+                h = std::make_unique<ADSB1090Handler>(nullptr, [&](AircraftState const &a) {
+                    std::printf("%06X,%d,%u,%u,%d,%d,%.8s\n", a.addr, a.altitude, a.speed, a.track, a.lat1E7, a.lon1E7,
+                                std::string(a.callsign, 8).c_str());
+                    ++count;
+                });
+            else
+                h = std::make_unique<ADSB1090Handler>(raw);
         } else {
             h = std::make_unique<UAT978Handler>([&](char updown, uint8_t *d, int len, int rs) {
                 std::printf("%c", updown);

@@ -73,3 +73,22 @@ def test_replay_path_b_matches_reference_fixture(tmp_path):
     assert p.returncode == 0, p.stderr
     want = ["*%s;" % bytes(r["msg"][:int(r["msgbits"]) // 8]).hex() for r in msgs]
     assert p.stdout.split() == want
+
+
+@pytest.mark.gpu
+def test_replay_path_b_aircraft_callbacks_match_reference(tmp_path):
+    """The reference's IListener::OnChanged callbacks for the same capture (b_mixed.npz, `ref_callbacks`, recorded from
+    the reference's own ADSB1090Handler + TrafficManager): field decode and CPR run on the device
+    (adsbcu_1090b_decode_fields / adsbcu_1090b_cpr_decode), the aircraft table on the host."""
+    with np.load(os.path.join(os.path.dirname(__file__), "golden", "b_mixed.npz")) as z:
+        iq, calls = z["iq"], z["ref_callbacks"]
+    cap = tmp_path / "b.bin"
+    iq.tofile(cap)
+    p = subprocess.run([_replay(), "--path", "b", "--aircraft", str(cap)], capture_output=True, text=True)
+    assert p.returncode == 0, p.stderr
+    want = ["%06X,%d,%d,%d,%d,%d,%s" % (int(c["addr"]), int(c["altitude"]), int(c["speed"]), int(c["track"]), int(c["lat1e7"]),
+                                        int(c["lon1e7"]), c["callsign"].decode("ascii")) for c in calls]
+    got = p.stdout.splitlines()
+    assert len(got) == len(want)
+    assert got == want
+    assert sum(1 for c in calls if c["lat1e7"] != 0) > 10 and sum(1 for c in calls if c["speed"] != 0) > 10
