@@ -24,7 +24,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-           "-Xcompiler", "-fPIC", "-shared", "-o", LIB] + SOURCES
+           "-Xcompiler", "-fPIC", "-Xcompiler", "-pthread", "-shared", "-o", LIB] + SOURCES
     cmd[1:1] = os.environ.get("ADSBCU_CFLAGS", "").split()
     if verbose:
         cmd.insert(1, "-Xptxas=-v")

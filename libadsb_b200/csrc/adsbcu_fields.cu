@@ -17,6 +17,7 @@
 
 #include <cmath>
 #include <cstring>
+#include <thread>
 #include <vector>
 
 namespace adsbcu {
@@ -268,14 +269,25 @@ int fields_decode(Fields *&f, cudaStream_t s, const adsbcu_msg_b *msgs, size_t n
     cudaError_t e;
     if (!f->d_heading) {
         // heading of every (ew_dir, ns_dir, ew_velocity, ns_velocity): ADSB1090.cpp:640-656 on the host's libm
+        // (four host threads over the eastbound half; atan2 is odd in its first argument and the conversion
+        // truncates towards zero, so the westbound half is 360 - h, or 0 where h is 0)
         std::vector<int16_t> lut(kHeadingEntries);
-        for (uint32_t i = 0; i < kHeadingEntries; ++i) {
-            int ewv = int((i >> 10) & 1023), nsv = int(i & 1023);
-            if (i >> 21) ewv = -ewv;
-            if ((i >> 20) & 1) nsv = -nsv;
-            int h = int(std::atan2(double(ewv), double(nsv)) * 360 / (M_PI * 2));
-            if (h < 0) h += 360;
-            lut[i] = int16_t(h);
+        auto fill = [&lut](uint32_t begin, uint32_t end) {
+            for (uint32_t i = begin; i < end; ++i) {
+                const int ewv = int((i >> 10) & 1023);
+                int nsv = int(i & 1023);
+                if ((i >> 20) & 1) nsv = -nsv;
+                const int h = int(std::atan2(double(ewv), double(nsv)) * 360 / (M_PI * 2));
+                lut[i] = int16_t(h);
+                lut[i | (1u << 21)] = int16_t(h ? 360 - h : 0);
+            }
+        };
+        {
+            constexpr uint32_t kHalf = kHeadingEntries / 2, kThreads = 4;
+            std::vector<std::thread> pool;
+            for (uint32_t t = 1; t < kThreads; ++t) pool.emplace_back(fill, t * (kHalf / kThreads), (t + 1) * (kHalf / kThreads));
+            fill(0, kHalf / kThreads);
+            for (auto &th : pool) th.join();
         }
         if ((e = cudaMalloc(&f->d_heading, kHeadingEntries * sizeof(int16_t))) != cudaSuccess) return fail(err, "cudaMalloc(heading)", e);
         if ((e = cudaMemcpy(f->d_heading, lut.data(), kHeadingEntries * sizeof(int16_t), cudaMemcpyHostToDevice)) != cudaSuccess)
