@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """Secondary timing lines (not the headline metric): Path B (libadsb's own 2.0 MS/s handler) and Path C
-(UAT 978) through their C-ABI entry points with HOST buffers, next to their CPU checkers on one core.
+(UAT 978) through their C-ABI entry points with HOST buffers.  The CPU checkers are timed by
+tests/perf_cpu_checkers.py (only tests/ may execute oracle/).
 usage: python profiles/bench_paths.py [seconds]   -> one JSON line per path"""
 import json
 import os
@@ -38,16 +39,6 @@ for name, step in (("262144-byte buffers", BUF), ("8 MiB buffers", 8 << 20)):
     line = {"path": "B (ADSB1090Handler, 2.0 MS/s)", "feed": name, "msamples_s": iq.size / 2 / dt / 1e6, "messages": n,
             "realtime_factor": iq.size / 2 / dt / 2.0e6}
     print(json.dumps(line))
-try:
-    from oracle import oracle1090b as B
-    part = iq[:min(iq.size, 16 * BUF)]
-    o = B.Oracle1090B()
-    t0 = time.perf_counter()
-    for k in range(0, part.size, BUF):
-        o.handle_data(part[k:k + BUF])
-    print(json.dumps({"path": "B cpu checker (1 core)", "msamples_s": part.size / 2 / (time.perf_counter() - t0) / 1e6}))
-except Exception as e:   # the checker is optional here
-    print(json.dumps({"path": "B cpu checker", "unavailable": repr(e)}))
 
 # ---- Path C
 iq = synth978.config5(seconds=seconds)[0]
@@ -58,16 +49,6 @@ for name, step in (("262144-byte buffers", BUF), ("whole capture", iq.size)):
     dt, n = timed(run_c)
     print(json.dumps({"path": "C (UAT978Handler, 2.083334 MS/s)", "feed": name, "msamples_s": iq.size / 2 / dt / 1e6,
                       "frames": n, "realtime_factor": iq.size / 2 / dt / 2083334.0}))
-try:
-    from oracle import oracle978 as O
-    part = iq[:min(iq.size, 16 * BUF)]
-    o = O.Oracle978()
-    t0 = time.perf_counter()
-    for k in range(0, part.size, BUF):
-        o.handle_data(part[k:k + BUF])
-    print(json.dumps({"path": "C cpu checker (1 core)", "msamples_s": part.size / 2 / (time.perf_counter() - t0) / 1e6}))
-except Exception as e:
-    print(json.dumps({"path": "C cpu checker", "unavailable": repr(e)}))
 
 # ---- Path B next layer: bulk field decode and CPR (host buffers in, host buffers out) next to the CPU checker
 rng = np.random.default_rng(3)
@@ -85,30 +66,16 @@ print(json.dumps({"path": "B fields (adsbcu_1090b_decode_fields)", "records": N,
                   "pcie_bytes_per_record": 112}))
 dt, _ = timed(lambda: d.cpr_decode(pairs).size)
 print(json.dumps({"path": "B cpr (adsbcu_1090b_cpr_decode)", "pairs": N, "mpairs_s": N / dt / 1e6, "pcie_bytes_per_pair": 32}))
-try:
-    from oracle import oracle1090b as B
-    o = B.Oracle1090B()
-    raw = np.ascontiguousarray(rec["msg"][:1 << 20])
-    t0 = time.perf_counter()
-    o.fields_bulk(raw, np.ascontiguousarray(rec["msgtype"][:1 << 20]))
-    print(json.dumps({"path": "B fields cpu checker (1 core)", "mrecords_s": raw.shape[0] / (time.perf_counter() - t0) / 1e6}))
-    p5 = np.stack([pairs[f][:1 << 20] for f in pairs.dtype.names], axis=1)
-    t0 = time.perf_counter()
-    o.cpr_bulk(p5)
-    print(json.dumps({"path": "B cpr cpu checker (1 core)", "mpairs_s": p5.shape[0] / (time.perf_counter() - t0) / 1e6}))
-except Exception as e:
-    print(json.dumps({"path": "B fields/cpr cpu checker", "unavailable": repr(e)}))
 
 # ---- Path A next layer: dump1090's CPR decoders, all four modes mixed
-try:
-    from oracle import oraclecpr as P
-    recs = P.random_records(1 << 20, 5)
-    recs = np.tile(recs, 4)
-    dt, _ = timed(lambda: d.cpr_decode_a(recs).size)
-    print(json.dumps({"path": "A cpr (adsbcu_1090_cpr_decode)", "records": int(recs.size), "mrecords_s": recs.size / dt / 1e6,
-                      "pcie_bytes_per_record": 64}))
-    t0 = time.perf_counter()
-    P.decode(recs[:1 << 20])
-    print(json.dumps({"path": "A cpr cpu checker (1 core)", "mrecords_s": (1 << 20) / (time.perf_counter() - t0) / 1e6}))
-except Exception as e:
-    print(json.dumps({"path": "A cpr", "unavailable": repr(e)}))
+rng5 = np.random.default_rng(5)
+recs = np.zeros(4 << 20, dtype=adsbcu.CPR_IN_DTYPE)
+for f in ("even_lat", "even_lon", "odd_lat", "odd_lon"):
+    recs[f] = rng5.integers(0, 131072, recs.size)
+recs["mode"] = rng5.integers(0, 4, recs.size)
+recs["fflag"] = rng5.integers(0, 2, recs.size)
+recs["reflat"] = rng5.uniform(-90, 90, recs.size)
+recs["reflon"] = rng5.uniform(-180, 180, recs.size)
+dt, _ = timed(lambda: d.cpr_decode_a(recs).size)
+print(json.dumps({"path": "A cpr (adsbcu_1090_cpr_decode)", "records": int(recs.size), "mrecords_s": recs.size / dt / 1e6,
+                  "pcie_bytes_per_record": 64}))
