@@ -281,22 +281,34 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
             uint32_t acc[12], L = 0, G = 0;
 #pragma unroll
             for (int c = 0; c < 12; ++c) acc[c] = 0;
-            int nd0 = nd_at(0), nd1 = nd_at(1);
+            // Two samples per round share the multiples of the middle difference: with a = nd[e], b = nd[e+1],
+            // c = nd[e+2], d = nd[e+3] the negated correlators are
+            //   sample e   : (5-sub) a + (2+sub) b (+ c for sub 4)  = a * (5-sub) + K[2+sub]
+            //   sample e+1 : (5-sub) b + (2+sub) c (+ d for sub 4)  = c * (2+sub) + K[5-sub]        K[k] = k b
+            // i.e. one multiply-add each on top of the five multiples K[2..6]
+            int na = nd_at(0);
 #pragma unroll
-            for (int e = 0; e < kRun; ++e) {
-                const int nd2 = nd_at(e + 2);
-                G = __funnelshift_l(uint32_t(nd0), G, 1);
-                L = __funnelshift_l(uint32_t(-nd0), L, 1);
-                // the five negated correlators, each at most three operations deep
-                const int step = nd1 - nd0;
-                const int v0 = 5 * nd0 + 2 * nd1;     // -(5 d0 + 2 d1)
-                const int v[5] = {v0, v0 + step, 2 * step + v0, 3 * step + v0, 4 * step + (v0 + nd2)};
+            for (int e = 0; e < kRun; e += 2) {
+                const int nb = nd_at(e + 1), nc = nd_at(e + 2), ndd = nd_at(e + 3);
+                G = __funnelshift_l(uint32_t(na), G, 1);
+                L = __funnelshift_l(uint32_t(-na), L, 1);
+                G = __funnelshift_l(uint32_t(nb), G, 1);
+                L = __funnelshift_l(uint32_t(-nb), L, 1);
+                const int K[7] = {0, nb, 2 * nb, 3 * nb, 4 * nb, 5 * nb, 6 * nb};
+                int v[10];
 #pragma unroll
                 for (int sub = 0; sub < 5; ++sub) {
-                    const int c = (5 * e + sub) % 12;
-                    acc[c] = __funnelshift_l(uint32_t(v[sub]), acc[c], 1);
+                    v[sub] = na * (5 - sub) + K[2 + sub];
+                    v[5 + sub] = nc * (2 + sub) + K[5 - sub];
                 }
-                nd0 = nd1; nd1 = nd2;
+                v[4] += nc;
+                v[9] += ndd;
+#pragma unroll
+                for (int q = 0; q < 10; ++q) {
+                    const int c = (5 * e + q) % 12;
+                    acc[c] = __funnelshift_l(uint32_t(v[q]), acc[c], 1);
+                }
+                na = nc;
             }
 #pragma unroll
             for (int c = 0; c < 12; ++c) gs.plane[c][tid] = uint16_t(acc[c]);
