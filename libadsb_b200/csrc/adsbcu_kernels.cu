@@ -131,6 +131,8 @@ __device__ __forceinline__ bool preamble_ok(const uint16_t *p)
     return true;
 }
 
+// kMagIn: the input is uint16 magnitudes (ScanArgs::mag_in, SC16 front end) instead of uint8 I/Q
+template <bool kMagIn>
 __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanArgs a)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -210,7 +212,7 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
         valid_range(x0t, lo, hi);
         const int i = kRun * tid;
         // magnitudes-in mode (SC16 inputs were converted to uint16 magnitudes): also 2 bytes per sample
-        const uint8_t *p = (a.mag_in ? reinterpret_cast<const uint8_t *>(a.mag_in) : a.iq) + 2 * (x0t + i);
+        const uint8_t *p = (kMagIn ? reinterpret_cast<const uint8_t *>(a.mag_in) : a.iq) + 2 * (x0t + i);
 #pragma unroll
         for (int r = 0; r < 3; ++r)
             if (i + 8 * r >= lo && i + 8 * r + 8 <= hi) raw[r] = __ldg(reinterpret_cast<const uint4 *>(p + 16 * r));
@@ -219,7 +221,7 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
     // magnitude of feed sample xe on the slow path (stream edges): carry, scalar I/Q, or zero padding
     auto mag_edge = [&](int64_t xe) -> uint32_t {
         if (xe < 0) return (xe + kOverlap >= 0) ? uint32_t(a.carry_mag[xe + kOverlap]) : 0u;
-        if (xe < n) return a.mag_in ? uint32_t(a.mag_in[xe]) : mag_iq(s_sq, a.iq[2 * xe], a.iq[2 * xe + 1]);
+        if (xe < n) return kMagIn ? uint32_t(a.mag_in[xe]) : mag_iq(s_sq, a.iq[2 * xe], a.iq[2 * xe + 1]);
         return 0u;
     };
     if (tile_base < seg_end) load_raw(tile_base);
@@ -245,7 +247,7 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
                 if (i0 + 8 * r >= v_lo && i0 + 8 * r + 8 <= v_hi) {
                     const uint4 d = raw[r];
                     const uint32_t c = central_bits(d.x) & central_bits(d.y) & central_bits(d.z) & central_bits(d.w);
-                    if (a.mag_in) {
+                    if (kMagIn) {
                         P[4 * r] = d.x; P[4 * r + 1] = d.y; P[4 * r + 2] = d.z; P[4 * r + 3] = d.w;
                     } else if ((c & 0x80808080u) == 0x80808080u) {
                         P[4 * r] = lut_pair(lut, d.x); P[4 * r + 1] = lut_pair(lut, d.y);
@@ -262,7 +264,7 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
             }
             if (i0 + 24 >= v_lo && i0 + 28 <= v_hi) {
                 const uint32_t c = central_bits(rawx.x) & central_bits(rawx.y);
-                if (a.mag_in) { P[12] = rawx.x; P[13] = rawx.y; }
+                if (kMagIn) { P[12] = rawx.x; P[13] = rawx.y; }
                 else if ((c & 0x80808080u) == 0x80808080u) { P[12] = lut_pair(lut, rawx.x); P[13] = lut_pair(lut, rawx.y); }
                 else { P[12] = mag_pair_any(s_sq, rawx.x); P[13] = mag_pair_any(s_sq, rawx.y); }
             } else {
@@ -760,13 +762,16 @@ extern "C" void adsbcu_debug_phase_cycles(unsigned long long *out, int reset)
 
 cudaError_t init_kernels()
 {
-    return cudaFuncSetAttribute(scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(ScanSmem)));
+    const cudaError_t e = cudaFuncSetAttribute(scan_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(ScanSmem)));
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(scan_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(ScanSmem)));
 }
 
 cudaError_t launch_scan(const ScanArgs &a, cudaStream_t s)
 {
     if (a.pos_end <= a.pos_begin || !a.nseg) return cudaSuccess;
-    scan_kernel<<<a.nseg / kGroups, kGroups * kGroupThreads, sizeof(ScanSmem), s>>>(a);
+    if (a.mag_in) scan_kernel<true><<<a.nseg / kGroups, kGroups * kGroupThreads, sizeof(ScanSmem), s>>>(a);
+    else scan_kernel<false><<<a.nseg / kGroups, kGroups * kGroupThreads, sizeof(ScanSmem), s>>>(a);
     return cudaGetLastError();
 }
 
