@@ -95,15 +95,6 @@ __device__ __forceinline__ uint32_t mag_pair_any(const float *sq, uint32_t w)
 }
 __host__ __device__ constexpr uint32_t w2(int lo, int hi) { return uint32_t(uint8_t(lo)) | (uint32_t(uint8_t(hi)) << 8); }
 
-// 32 consecutive decisions of one symbol plane starting at stream bit n, first one in the MSB
-__device__ __forceinline__ uint32_t plane_bits32(const uint16_t *pl, uint32_t n)
-{
-    const uint32_t f = n / 10u, r = n - 10u * f;
-    const uint64_t W = (uint64_t(pl[f]) << 40) | (uint64_t(pl[f + 1]) << 30) | (uint64_t(pl[f + 2]) << 20) |
-                       (uint64_t(pl[f + 3]) << 10) | uint64_t(pl[f + 4]);
-    return uint32_t(W >> (18u - r));
-}
-
 // Reference preamble test at p[0..18] (demod_2400.c:155-218).  `p` points into shared memory.
 __device__ __forceinline__ bool preamble_ok(const uint16_t *p)
 {
@@ -400,12 +391,21 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
                 const uint32_t pos = item & 0xFFFFu, ph = 4u + (item >> 16);
                 const uint32_t t0 = 5u * (pos + kTileLead + 19u) + ph;
                 const uint32_t c = t0 % 12u, n0 = t0 / 12u;
-                const uint16_t *pl = gs.plane[c];
-                uint32_t M[4] = {plane_bits32(pl, n0), plane_bits32(pl, n0 + 32u), 0u, 0u};
+                // the 10-bit fields from n0 on, repacked into a dense bit stream (every field is < 1024, so the
+                // shifted fields do not overlap and add up), then shifted to the message's first bit
+                const uint16_t *pf = gs.plane[c] + n0 / 10u;
+                const uint32_t r = n0 % 10u;
+                const uint32_t f3 = pf[3], f6 = pf[6], f9 = pf[9];
+                const uint32_t w0 = (uint32_t(pf[0]) << 22) + (uint32_t(pf[1]) << 12) + (uint32_t(pf[2]) << 2) + (f3 >> 8);
+                const uint32_t w1 = (f3 << 24) + (uint32_t(pf[4]) << 14) + (uint32_t(pf[5]) << 4) + (f6 >> 6);
+                const uint32_t w2 = (f6 << 26) + (uint32_t(pf[7]) << 16) + (uint32_t(pf[8]) << 6) + (f9 >> 4);
+                uint32_t M[4] = {__funnelshift_l(w1, w0, r), __funnelshift_l(w2, w1, r), 0u, 0u};
                 uint32_t xs = 0, xl = 0;
                 if (is_long) {
-                    M[2] = plane_bits32(pl, n0 + 64u);
-                    M[3] = plane_bits32(pl, n0 + 96u) & 0xFFFF0000u;
+                    const uint32_t f12 = pf[12];
+                    const uint32_t w3 = (f9 << 28) + (uint32_t(pf[10]) << 18) + (uint32_t(pf[11]) << 8) + (f12 >> 2);
+                    M[2] = __funnelshift_l(w3, w2, r);
+                    M[3] = __funnelshift_l(f12 << 30, w3, r) & 0xFFFF0000u;
                     xl = crc_long(M, s_crcb);
                     // the 56-bit syndrome is also needed when a short DF was sliced long (DF0/DF5 are within two
                     // bit flips of DF17/18, so --fix-2bit slices them to 14 bytes but scores them as 56-bit A/P)
