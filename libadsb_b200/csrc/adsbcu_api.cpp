@@ -9,12 +9,17 @@
 #include "adsbcu_internal.h"
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <condition_variable>
+#include <functional>
 #include <new>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 using namespace adsbcu;
@@ -77,15 +82,57 @@ struct IcaoFilter {
 
 constexpr int kSlots = 3;            // chunks in flight: GPU works on chunk c+1, c+2 while the host pass replays chunk c
 
+// One long-lived helper thread per handle for the ordered host pass of long feeds (a thread spawned per feed starts
+// on the submitting thread's core and steals the time the submissions need).
+struct Resolver {
+    std::thread th;
+    std::mutex m;
+    std::condition_variable cv;
+    std::function<void()> job;
+    bool has_job = false, quit = false;
+    std::atomic<bool> idle{true};
+    void post(std::function<void()> fn)
+    {
+        if (!th.joinable()) th = std::thread([this] { loop(); });
+        { std::lock_guard<std::mutex> g(m); job = std::move(fn); has_job = true; idle.store(false, std::memory_order_relaxed); }
+        cv.notify_one();
+    }
+    void wait() { while (!idle.load(std::memory_order_acquire)) std::this_thread::yield(); }
+    void loop()
+    {
+        for (;;) {
+            std::function<void()> fn;
+            {
+                std::unique_lock<std::mutex> g(m);
+                cv.wait(g, [this] { return has_job || quit; });
+                if (quit) return;
+                fn = std::move(job); has_job = false;
+            }
+            fn();
+            idle.store(true, std::memory_order_release);
+        }
+    }
+    ~Resolver()
+    {
+        if (th.joinable()) {
+            { std::lock_guard<std::mutex> g(m); quit = true; }
+            cv.notify_one();
+            th.join();
+        }
+    }
+};
+
 // Everything one in-flight chunk owns.
 struct Slot {
     PhaseRec *d_seg = nullptr;        // nseg segments of seg_cap records
     uint32_t *d_seg_count = nullptr;
     ChunkCounters *d_ctr = nullptr;
-    ChunkCounters *h_ctr = nullptr;   // pinned
+    ChunkCounters *h_ctr = nullptr;   // pinned + mapped
+    ChunkCounters *h_ctr_dev = nullptr;   // device alias of h_ctr
     FullRec *h_full = nullptr;        // pinned + mapped: the evaluate kernel writes it directly
     FullRec *d_full = nullptr;        // device alias of h_full
     cudaEvent_t ev[4]{};              // scan begin, scan end, evaluate end, done (counters on the host)
+    uint32_t seq = 0;                 // sequence number of the chunk the slot holds (threaded feeds: h_ctr->pad once it is done)
 };
 
 struct adsbcu_handle {
@@ -104,6 +151,11 @@ struct adsbcu_handle {
     int16_t *d_sc16 = nullptr;        // staging for SC16 / SC16Q11 host feeds (allocated on first use)
     uint32_t nseg = 0, seg_cap = 0, full_cap = 0;
     uint32_t skew = 0, skew_ns = 2500;   // measured on B200: no skew 0.5065 ms, sleep skew 0.506-0.516, short first tile 0.529 (profiles/sweep_skew.sh)
+    bool resolver_thread = true;       // ADSBCU_RESOLVER_THREAD=0: the ordered host pass stays on the calling thread
+    uint32_t chunk_seq = 0;
+    Resolver resolver;
+    int wait_policy = 50;              // ADSBCU_WAIT: microseconds the submitter sleeps while all slots are busy (0: both threads yield-spin)
+    uint32_t thread_tps = 8;
     uint32_t unit_positions = 0, max_tps = 1, host_tps = 4;   // chunk = unit_positions * (tiles per segment), at most max_tps
     Slot slot[kSlots];
     uint16_t *d_mag = nullptr;        // stage-level magnitude output
@@ -288,10 +340,13 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
     // fills quickly, later ones long so that per-launch costs (LUT load, tail) are amortised
     std::vector<uint32_t> bounds{0};
     // host feeds are bound by the upload: short chunks throughout keep the work left after the last byte arrived small
-    const uint32_t tps_cap = from_host ? std::min(h->host_tps, h->max_tps) : h->max_tps;
+    // (with the host pass on its own thread, 8 tiles per segment and chunk balance kernel launch overheads against the
+    // host work left when the GPU finishes: profiles/r01_host_pass_thread_sweep.txt)
+    const uint32_t tps_cap = from_host ? std::min(h->host_tps, h->max_tps) : h->resolver_thread ? std::min(h->max_tps, h->thread_tps) : h->max_tps;
     for (uint32_t tps = std::min(4u, tps_cap); bounds.back() < n; tps = std::min(2 * tps, tps_cap))
         bounds.push_back(uint32_t(std::min<uint64_t>(n, uint64_t(bounds.back()) + uint64_t(h->unit_positions) * tps)));
     const uint32_t nchunks = uint32_t(bounds.size() - 1);
+    const bool threaded = h->resolver_thread && nchunks >= 3;
     float ms_h2d = 0.f;
     if (from_host) CK(cudaEventRecord(h->ev_h2d[0], h->copy_stream));
 
@@ -336,13 +391,18 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
         CK(launch_filter(a, h->stream));
         CK(launch_evaluate(a, h->stream));
         CK(cudaEventRecord(s.ev[2], h->stream));
-        CK(cudaMemcpyAsync(s.h_ctr, s.d_ctr, sizeof(ChunkCounters), cudaMemcpyDeviceToHost, h->stream));
+        if (threaded) {
+            s.seq = ++h->chunk_seq;
+            CK(launch_signal(s.d_ctr, s.h_ctr_dev, s.seq, h->stream));
+        } else {
+            CK(cudaMemcpyAsync(s.h_ctr, s.d_ctr, sizeof(ChunkCounters), cudaMemcpyDeviceToHost, h->stream));
+        }
         CK(cudaEventRecord(s.ev[3], h->stream));
         return ADSBCU_OK;
     };
-    auto retire = [&](uint32_t c) -> int {
+    // host half of a chunk: counters are on the host, the records in mapped memory
+    auto host_pass = [&](uint32_t c) -> int {
         Slot &s = h->slot[c % kSlots];
-        CK(cudaEventSynchronize(s.ev[3]));
         const ChunkCounters k = *s.h_ctr;
         if (k.overflow || k.n_full > h->full_cap) {
             h->error = "internal candidate list overflow (traffic denser than the lists are sized for)";
@@ -352,27 +412,73 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
         if (sink.cands) copy_candidates(s.h_full, k.n_full, h->stream_pos, sink);
         else resolve(h, s.h_full, k.n_full, h->stream_pos, sink);
         const auto t1 = std::chrono::steady_clock::now();
-        float ms = 0.f;
         st.preambles += k.preambles; st.phase_records += k.n_cand; st.resolved_records += k.n_full;
+        st.ms_resolve += std::chrono::duration<float, std::milli>(t1 - t0).count();
+        return ADSBCU_OK;
+    };
+    auto kernel_times = [&](uint32_t c) {
+        Slot &s = h->slot[c % kSlots];
+        float ms = 0.f;
         cudaEventElapsedTime(&ms, s.ev[0], s.ev[1]); st.ms_scan += ms;
         cudaEventElapsedTime(&ms, s.ev[1], s.ev[2]); st.ms_finalize += ms;
-        st.ms_resolve += std::chrono::duration<float, std::milli>(t1 - t0).count();
         st.scan_launches += 3;
-        return ADSBCU_OK;
+    };
+    auto retire = [&](uint32_t c) -> int {
+        CK(cudaEventSynchronize(h->slot[c % kSlots].ev[3]));
+        const int r = host_pass(c);
+        if (r == ADSBCU_OK) kernel_times(c);
+        return r;
     };
 
     int rc = ADSBCU_OK;
-    uint32_t submitted = 0, retired = 0;
-    while (retired < nchunks) {
-        while (submitted < nchunks && submitted < retired + kSlots) {
-            rc = submit(submitted);
-            if (rc != ADSBCU_OK) break;
-            ++submitted;
+    if (threaded) {
+        // Long feeds: the ordered host pass runs on its own thread, which makes no CUDA call at all (it polls the
+        // sequence number the signal kernel writes into mapped host memory), so the ~10 runtime calls of every submit and the host pass do
+        // not queue behind each other on one core.
+        std::atomic<uint32_t> retired{0};
+        std::atomic<int> worker_rc{ADSBCU_OK};
+        std::atomic<bool> stop{false};
+        const uint32_t first_seq = h->chunk_seq + 1;
+        h->resolver.post([&] {
+            for (uint32_t c = 0; c < nchunks; ++c) {
+                Slot &s = h->slot[c % kSlots];
+                while (reinterpret_cast<const volatile ChunkCounters *>(s.h_ctr)->pad != first_seq + c) {
+                    if (stop.load(std::memory_order_relaxed)) return;
+                    if (h->wait_policy == 0) std::this_thread::yield(); else __builtin_ia32_pause();
+                }
+                std::atomic_thread_fence(std::memory_order_acquire);
+                const int r = host_pass(c);
+                if (r != ADSBCU_OK) { worker_rc.store(r); return; }
+                retired.store(c + 1, std::memory_order_release);
+            }
+        });
+        for (uint32_t c = 0; c < nchunks && rc == ADSBCU_OK; ++c) {
+            while (c >= retired.load(std::memory_order_acquire) + kSlots && worker_rc.load() == ADSBCU_OK) {
+                if (h->wait_policy == 0) std::this_thread::yield();
+                else std::this_thread::sleep_for(std::chrono::microseconds(h->wait_policy));
+            }
+            if (worker_rc.load() != ADSBCU_OK) break;
+            if (c >= kSlots) kernel_times(c - kSlots);          // the slot's previous chunk is done: read its events before reuse
+            rc = submit(c);
         }
-        if (rc != ADSBCU_OK) break;
-        rc = retire(retired);
-        if (rc != ADSBCU_OK) break;
-        ++retired;
+        if (rc != ADSBCU_OK) { cudaStreamSynchronize(h->stream); stop.store(true); }
+        h->resolver.wait();
+        if (rc == ADSBCU_OK) rc = worker_rc.load();
+        if (rc == ADSBCU_OK)
+            for (uint32_t c = nchunks > kSlots ? nchunks - kSlots : 0; c < nchunks; ++c) kernel_times(c);
+    } else {
+        uint32_t submitted = 0, retired = 0;
+        while (retired < nchunks) {
+            while (submitted < nchunks && submitted < retired + kSlots) {
+                rc = submit(submitted);
+                if (rc != ADSBCU_OK) break;
+                ++submitted;
+            }
+            if (rc != ADSBCU_OK) break;
+            rc = retire(retired);
+            if (rc != ADSBCU_OK) break;
+            ++retired;
+        }
     }
     if (rc != ADSBCU_OK) { cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->copy_stream); return rc; }
     if (sink.cands) CK(cudaMemcpyAsync(h->d_carry_prev, h->d_carry, kOverlap * sizeof(uint16_t), cudaMemcpyDeviceToDevice, h->stream));
@@ -474,6 +580,9 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
     uint32_t tps = 16;
     if (const char *e = std::getenv("ADSBCU_TILES_PER_SEG")) tps = uint32_t(std::max(1, std::atoi(e)));
     if (const char *e = std::getenv("ADSBCU_SKEW")) h->skew = uint32_t(std::atoi(e));
+    if (const char *e = std::getenv("ADSBCU_THREAD_TPS")) h->thread_tps = uint32_t(std::max(1, std::atoi(e)));
+    if (const char *e = std::getenv("ADSBCU_WAIT")) h->wait_policy = std::atoi(e);
+    if (const char *e = std::getenv("ADSBCU_RESOLVER_THREAD")) h->resolver_thread = std::atoi(e) != 0;
     if (const char *e = std::getenv("ADSBCU_HOST_TPS")) h->host_tps = uint32_t(std::max(1, std::atoi(e)));
     if (const char *e = std::getenv("ADSBCU_SKEW_NS")) h->skew_ns = uint32_t(std::max(0, std::atoi(e)));
     const size_t nmax = c.max_feed_samples;
@@ -494,7 +603,9 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
         CKC(cudaMalloc(&s.d_seg, size_t(h->nseg) * h->seg_cap * sizeof(PhaseRec)));
         CKC(cudaMalloc(&s.d_seg_count, size_t(h->nseg) * sizeof(uint32_t)));
         CKC(cudaMalloc(&s.d_ctr, sizeof(ChunkCounters)));
-        CKC(cudaHostAlloc(&s.h_ctr, sizeof(ChunkCounters), cudaHostAllocDefault));
+        CKC(cudaHostAlloc(&s.h_ctr, sizeof(ChunkCounters), cudaHostAllocMapped));
+        std::memset(s.h_ctr, 0, sizeof(ChunkCounters));
+        CKC(cudaHostGetDevicePointer(reinterpret_cast<void **>(&s.h_ctr_dev), s.h_ctr, 0));
         CKC(cudaHostAlloc(&s.h_full, size_t(h->full_cap) * sizeof(FullRec), cudaHostAllocMapped));
         CKC(cudaHostGetDevicePointer(&s.d_full, s.h_full, 0));
         for (int k = 0; k < 4; ++k) CKC(cudaEventCreate(&s.ev[k]));

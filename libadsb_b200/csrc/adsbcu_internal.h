@@ -173,6 +173,7 @@ cudaError_t launch_filter(const ScanArgs &a, cudaStream_t s);     // drop A/P re
 cudaError_t launch_evaluate(const ScanArgs &a, cudaStream_t s);   // survivors -> FullRec, stream order
 // deferred records whose address is in the bitmap now -> flat into a.seg (seg_count set per segment)
 cudaError_t launch_revive(const ScanArgs &a, cudaStream_t s);
+cudaError_t launch_signal(const ChunkCounters *d_ctr, ChunkCounters *h_ctr_dev, uint32_t seq, cudaStream_t s);
 cudaError_t launch_or_words(uint32_t *dst, const uint32_t *src, uint32_t nwords, cudaStream_t s);
 cudaError_t launch_build_lut(DevTables *tab, cudaStream_t s);     // fills tab->mag_lut with the register-computed magnitudes
 cudaError_t launch_carry(const uint8_t *iq, uint32_t nsamples, uint16_t *carry_mag, const DevTables *tab, cudaStream_t s);

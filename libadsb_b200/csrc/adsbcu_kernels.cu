@@ -803,6 +803,20 @@ cudaError_t launch_revive(const ScanArgs &a, cudaStream_t s)
     return cudaGetLastError();
 }
 
+// Chunk completion without a host call: the counters go to mapped host memory, the sequence number last (the
+// evaluate kernel's records were written to mapped memory earlier in the same stream).
+__global__ void signal_kernel(const ChunkCounters *d, volatile ChunkCounters *h, uint32_t seq)
+{
+    h->preambles = d->preambles; h->n_cand = d->n_cand; h->n_full = d->n_full; h->overflow = d->overflow;
+    __threadfence_system();
+    h->pad = seq;
+}
+cudaError_t launch_signal(const ChunkCounters *d_ctr, ChunkCounters *h_ctr_dev, uint32_t seq, cudaStream_t s)
+{
+    signal_kernel<<<1, 1, 0, s>>>(d_ctr, h_ctr_dev, seq);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_or_words(uint32_t *dst, const uint32_t *src, uint32_t nwords, cudaStream_t s)
 {
     or_words_kernel<<<296, 256, 0, s>>>(dst, src, nwords);
