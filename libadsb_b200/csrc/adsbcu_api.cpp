@@ -421,7 +421,7 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
         float ms = 0.f;
         cudaEventElapsedTime(&ms, s.ev[0], s.ev[1]); st.ms_scan += ms;
         cudaEventElapsedTime(&ms, s.ev[1], s.ev[2]); st.ms_finalize += ms;
-        st.scan_launches += 3;
+        st.scan_launches += threaded ? 4 : 3;        // scan, filter, evaluate (+ signal)
     };
     auto retire = [&](uint32_t c) -> int {
         CK(cudaEventSynchronize(h->slot[c % kSlots].ev[3]));
