@@ -433,12 +433,13 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
     int rc = ADSBCU_OK;
     if (threaded) {
         // Long feeds: the ordered host pass runs on its own thread, which makes no CUDA call at all (it polls the
-        // sequence number the signal kernel writes into mapped host memory), so the ~10 runtime calls of every submit and the host pass do
-        // not queue behind each other on one core.
+        // sequence number the signal kernel writes into mapped host memory), so the ~10 runtime calls of every
+        // submit and the host pass do not queue behind each other on one core.
         std::atomic<uint32_t> retired{0};
         std::atomic<int> worker_rc{ADSBCU_OK};
         std::atomic<bool> stop{false};
         const uint32_t first_seq = h->chunk_seq + 1;
+        uint32_t spins = 0;
         h->resolver.post([&] {
             for (uint32_t c = 0; c < nchunks; ++c) {
                 Slot &s = h->slot[c % kSlots];
@@ -456,13 +457,29 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
             while (c >= retired.load(std::memory_order_acquire) + kSlots && worker_rc.load() == ADSBCU_OK) {
                 if (h->wait_policy == 0) std::this_thread::yield();
                 else std::this_thread::sleep_for(std::chrono::microseconds(h->wait_policy));
+                if ((++spins & 63u) != 0) continue;         // every few milliseconds: has the pipeline died?
+                if (const cudaError_t q = cudaStreamQuery(h->stream); q != cudaSuccess && q != cudaErrorNotReady) {
+                    cuda_ok(h, q, "scan pipeline");
+                    rc = ADSBCU_ERR_CUDA;
+                    break;
+                }
             }
+            if (rc != ADSBCU_OK) break;
             if (worker_rc.load() != ADSBCU_OK) break;
             if (c >= kSlots) kernel_times(c - kSlots);          // the slot's previous chunk is done: read its events before reuse
             rc = submit(c);
         }
         if (rc != ADSBCU_OK) { cudaStreamSynchronize(h->stream); stop.store(true); }
-        h->resolver.wait();
+        // wait for the resolver; a failed kernel would never write its sequence number, so watch the stream for errors
+        while (!h->resolver.idle.load(std::memory_order_acquire)) {
+            std::this_thread::yield();                  // (a sleep here would add its timer slack to every feed)
+            if ((++spins & 4095u) != 0 || stop.load()) continue;
+            if (const cudaError_t q = cudaStreamQuery(h->stream); q != cudaSuccess && q != cudaErrorNotReady) {
+                cuda_ok(h, q, "scan pipeline");
+                rc = ADSBCU_ERR_CUDA;
+                stop.store(true);
+            }
+        }
         if (rc == ADSBCU_OK) rc = worker_rc.load();
         if (rc == ADSBCU_OK)
             for (uint32_t c = nchunks > kSlots ? nchunks - kSlots : 0; c < nchunks; ++c) kernel_times(c);
