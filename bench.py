@@ -258,7 +258,10 @@ def main():
         peak, peak_src = load_peaks()
         k_ms = float(np.mean(scan_ms))                    # all scan_kernel launches of one step (one per chunk)
         achieved = 2.0 * n / (k_ms * 1e-3) / 1e9
-        scan_per_step = (launches // args.steps - 2 - 1) // 3    # per chunk: scan, filter, evaluate; + carry + 2 memsets
+        # per chunk: scan, filter, evaluate (+ signal when the resolver thread runs, i.e. feeds of >= 3 chunks);
+        # per feed: + carry + 2 memsets
+        per_feed = launches // args.steps - 2 - 1
+        scan_per_step = per_feed // 4 if os.environ.get("ADSBCU_RESOLVER_THREAD", "1") != "0" and per_feed % 4 == 0 and per_feed >= 12 else per_feed // 3
         try:
             with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
                 traffic_ratio = float(json.load(f)["traffic_over_algorithmic"])
