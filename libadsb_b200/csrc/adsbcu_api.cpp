@@ -140,6 +140,8 @@ struct adsbcu_handle {
     int device = 0, sm_count = 148;
     cudaStream_t stream = nullptr;    // kernels + counter downloads
     cudaStream_t copy_stream = nullptr;   // host->device uploads of the feed, chunk by chunk
+    cudaStream_t post_stream = nullptr;   // ADSBCU_OVERLAP=1: filter/evaluate/signal of chunk c run here, beside the scan of chunk c+1
+    bool overlap = false;
     cudaEvent_t ev_h2d[2]{};
     cudaEvent_t ev_up[kSlots]{};      // upload of the chunk using that slot has finished
     std::string error;
@@ -226,6 +228,7 @@ void free_all(adsbcu_handle *h)
     for (auto &e : h->ev_up) if (e) cudaEventDestroy(e);
     if (h->stream) cudaStreamDestroy(h->stream);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+    if (h->post_stream) cudaStreamDestroy(h->post_stream);
 }
 
 // ---- ordered host pass ------------------------------------------------------------------
@@ -347,6 +350,7 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
         bounds.push_back(uint32_t(std::min<uint64_t>(n, uint64_t(bounds.back()) + uint64_t(h->unit_positions) * tps)));
     const uint32_t nchunks = uint32_t(bounds.size() - 1);
     const bool threaded = h->resolver_thread && nchunks >= 3;
+    const bool post = h->overlap && !sink.cands && nchunks >= 2;
     float ms_h2d = 0.f;
     if (from_host) CK(cudaEventRecord(h->ev_h2d[0], h->copy_stream));
 
@@ -388,16 +392,20 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
         CK(cudaEventRecord(s.ev[0], h->stream));
         CK(launch_scan(a, h->stream));
         CK(cudaEventRecord(s.ev[1], h->stream));
-        CK(launch_filter(a, h->stream));
-        CK(launch_evaluate(a, h->stream));
-        CK(cudaEventRecord(s.ev[2], h->stream));
+        // the sparse kernels of this chunk only touch the chunk's own slot (and read the address bitmap, where a
+        // superset keeps more records for the exact host pass): they may run beside the next chunk's scan
+        const cudaStream_t ps = post ? h->post_stream : h->stream;
+        if (post) CK(cudaStreamWaitEvent(ps, s.ev[1], 0));
+        CK(launch_filter(a, ps));
+        CK(launch_evaluate(a, ps));
+        CK(cudaEventRecord(s.ev[2], ps));
         if (threaded) {
             s.seq = ++h->chunk_seq;
-            CK(launch_signal(s.d_ctr, s.h_ctr_dev, s.seq, h->stream));
+            CK(launch_signal(s.d_ctr, s.h_ctr_dev, s.seq, ps));
         } else {
-            CK(cudaMemcpyAsync(s.h_ctr, s.d_ctr, sizeof(ChunkCounters), cudaMemcpyDeviceToHost, h->stream));
+            CK(cudaMemcpyAsync(s.h_ctr, s.d_ctr, sizeof(ChunkCounters), cudaMemcpyDeviceToHost, ps));
         }
-        CK(cudaEventRecord(s.ev[3], h->stream));
+        CK(cudaEventRecord(s.ev[3], ps));
         return ADSBCU_OK;
     };
     // host half of a chunk: counters are on the host, the records in mapped memory
@@ -469,7 +477,7 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
             if (c >= kSlots) kernel_times(c - kSlots);          // the slot's previous chunk is done: read its events before reuse
             rc = submit(c);
         }
-        if (rc != ADSBCU_OK) { cudaStreamSynchronize(h->stream); stop.store(true); }
+        if (rc != ADSBCU_OK) { cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->post_stream); stop.store(true); }
         // wait for the resolver; a failed kernel would never write its sequence number, so watch the stream for errors
         while (!h->resolver.idle.load(std::memory_order_acquire)) {
             std::this_thread::yield();                  // (a sleep here would add its timer slack to every feed)
@@ -497,7 +505,8 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
             ++retired;
         }
     }
-    if (rc != ADSBCU_OK) { cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->copy_stream); return rc; }
+    if (rc != ADSBCU_OK) { cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->post_stream); cudaStreamSynchronize(h->copy_stream); return rc; }
+    if (post) CK(cudaStreamWaitEvent(h->stream, h->slot[(nchunks - 1) % kSlots].ev[3], 0));
     if (sink.cands) CK(cudaMemcpyAsync(h->d_carry_prev, h->d_carry, kOverlap * sizeof(uint16_t), cudaMemcpyDeviceToDevice, h->stream));
     if (sc16_host) CK(launch_carry_mag(reinterpret_cast<const uint16_t *>(h->d_iq), n, h->d_carry, h->stream));
     else CK(launch_carry(d_iq, n, h->d_carry, h->d_tab, h->stream));
@@ -580,6 +589,11 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
     h->sm_count = prop.multiProcessorCount;
     CKC(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     CKC(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    {
+        int lo = 0, hi = 0;
+        CKC(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CKC(cudaStreamCreateWithPriority(&h->post_stream, cudaStreamNonBlocking, hi));
+    }
     for (auto &e : h->ev_h2d) CKC(cudaEventCreate(&e));
     for (auto &e : h->ev_up) CKC(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     CKC(init_kernels());
@@ -599,6 +613,7 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
     if (const char *e = std::getenv("ADSBCU_SKEW")) h->skew = uint32_t(std::atoi(e));
     if (const char *e = std::getenv("ADSBCU_THREAD_TPS")) h->thread_tps = uint32_t(std::max(1, std::atoi(e)));
     if (const char *e = std::getenv("ADSBCU_WAIT")) h->wait_policy = std::atoi(e);
+    if (const char *e = std::getenv("ADSBCU_OVERLAP")) h->overlap = std::atoi(e) != 0;
     if (const char *e = std::getenv("ADSBCU_RESOLVER_THREAD")) h->resolver_thread = std::atoi(e) != 0;
     if (const char *e = std::getenv("ADSBCU_HOST_TPS")) h->host_tps = uint32_t(std::max(1, std::atoi(e)));
     if (const char *e = std::getenv("ADSBCU_SKEW_NS")) h->skew_ns = uint32_t(std::max(0, std::atoi(e)));
