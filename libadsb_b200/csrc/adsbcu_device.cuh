@@ -80,6 +80,16 @@ __device__ __forceinline__ void slice_bits(MagFn mag, int ph, int first, int las
 // garbage (v0).  Samples are consumed as packed uint16 pairs straight from the shared-memory tile
 // with IDP.2A (u16 x s8 dot products); the two possible alignments of sample 0 inside a 32-bit
 // word are folded into per-lane weight registers, so there is no divergence on parity either.
+#ifdef ADSBCU_EMU      // (u16 x s8) two-way dot products, as the PTX instruction defines them
+__device__ __forceinline__ int dp2a_lo(uint32_t a, uint32_t b, int c)
+{
+    return c + int(a & 0xFFFFu) * int(int8_t(b & 0xFFu)) + int(a >> 16) * int(int8_t((b >> 8) & 0xFFu));
+}
+__device__ __forceinline__ int dp2a_hi(uint32_t a, uint32_t b, int c)
+{
+    return c + int(a & 0xFFFFu) * int(int8_t((b >> 16) & 0xFFu)) + int(a >> 16) * int(int8_t(b >> 24));
+}
+#else
 __device__ __forceinline__ int dp2a_lo(uint32_t a, uint32_t b, int c)
 {
     int d;
@@ -92,6 +102,7 @@ __device__ __forceinline__ int dp2a_hi(uint32_t a, uint32_t b, int c)
     asm("dp2a.hi.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
     return d;
 }
+#endif
 
 // weights are stored NEGATED so that (corr > 0) is the sign bit of the accumulated value
 __host__ __device__ constexpr uint32_t wpair(int lo, int hi) { return uint32_t(uint8_t(-lo)) | (uint32_t(uint8_t(-hi)) << 8); }

@@ -297,7 +297,7 @@ int fields_decode(Fields *&f, cudaStream_t s, const adsbcu_msg_b *msgs, size_t n
         return fail(err, "cudaMalloc(fields)", cudaGetLastError());
     if ((e = cudaMemcpyAsync(f->d_in, msgs, n * sizeof(adsbcu_msg_b), cudaMemcpyHostToDevice, s)) != cudaSuccess)
         return fail(err, "H2D(fields)", e);
-    fields_kernel<<<unsigned((n + 255) / 256), 256, 0, s>>>(static_cast<const uint4 *>(f->d_in), uint32_t(n),
+    ADSBCU_LAUNCH(fields_kernel, unsigned((n + 255) / 256), 256, 0, s, static_cast<const uint4 *>(f->d_in), uint32_t(n),
                                                             static_cast<uint4 *>(f->d_out), f->d_heading);
     if ((e = cudaGetLastError()) != cudaSuccess) return fail(err, "fields_kernel", e);
     if ((e = cudaMemcpyAsync(out, f->d_out, n * sizeof(adsbcu_fields_b), cudaMemcpyDeviceToHost, s)) != cudaSuccess)
@@ -315,7 +315,7 @@ int cpr_decode(Fields *&f, cudaStream_t s, const adsbcu_cpr_pair *pairs, size_t 
         return fail(err, "cudaMalloc(cpr)", cudaGetLastError());
     if ((e = cudaMemcpyAsync(f->d_in, pairs, n * sizeof(adsbcu_cpr_pair), cudaMemcpyHostToDevice, s)) != cudaSuccess)
         return fail(err, "H2D(cpr)", e);
-    cpr_kernel<<<unsigned((n + 255) / 256), 256, 0, s>>>(static_cast<const adsbcu_cpr_pair *>(f->d_in), uint32_t(n),
+    ADSBCU_LAUNCH(cpr_kernel, unsigned((n + 255) / 256), 256, 0, s, static_cast<const adsbcu_cpr_pair *>(f->d_in), uint32_t(n),
                                                          static_cast<adsbcu_cpr_fix *>(f->d_out));
     if ((e = cudaGetLastError()) != cudaSuccess) return fail(err, "cpr_kernel", e);
     if ((e = cudaMemcpyAsync(out, f->d_out, n * sizeof(adsbcu_cpr_fix), cudaMemcpyDeviceToHost, s)) != cudaSuccess)
@@ -336,7 +336,7 @@ int cpr_a_decode(Fields *&f, cudaStream_t s, const adsbcu_cpr_in *in, size_t n, 
         return fail(err, "cudaMalloc(cpr)", cudaGetLastError());
     if ((e = cudaMemcpyAsync(f->d_in, in, n * sizeof(adsbcu_cpr_in), cudaMemcpyHostToDevice, s)) != cudaSuccess)
         return fail(err, "H2D(cpr)", e);
-    cpr_a_kernel<<<unsigned((n + 255) / 256), 256, 0, s>>>(static_cast<const adsbcu_cpr_in *>(f->d_in), uint32_t(n),
+    ADSBCU_LAUNCH(cpr_a_kernel, unsigned((n + 255) / 256), 256, 0, s, static_cast<const adsbcu_cpr_in *>(f->d_in), uint32_t(n),
                                                            static_cast<adsbcu_cpr_out *>(f->d_out));
     if ((e = cudaGetLastError()) != cudaSuccess) return fail(err, "cpr_a_kernel", e);
     if ((e = cudaMemcpyAsync(out, f->d_out, n * sizeof(adsbcu_cpr_out), cudaMemcpyDeviceToHost, s)) != cudaSuccess)

@@ -7,6 +7,17 @@
 #include <cstdint>
 #include <cuda_runtime.h>
 
+// Kernel launches and dynamic shared memory go through two macros so that the CPU test suite can run these very
+// sources under its SIMT emulator (tests/emu, test infrastructure only: g++ with a shadow <cuda_runtime.h> that
+// defines ADSBCU_EMU).  The product is always the nvcc build for sm_100a, where they are the plain CUDA forms.
+#ifdef ADSBCU_EMU
+#define ADSBCU_LAUNCH(kernel, grid, block, smem, stream, ...) emu::launch(dim3(grid), dim3(block), (smem), [&] { kernel(__VA_ARGS__); })
+#define ADSBCU_DYN_SMEM(name) unsigned char *name = emu::dyn_smem()
+#else
+#define ADSBCU_LAUNCH(kernel, grid, block, smem, stream, ...) kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
+#define ADSBCU_DYN_SMEM(name) extern __shared__ __align__(16) unsigned char name[]
+#endif
+
 namespace adsbcu {
 
 constexpr int      kOverlap       = 326;      // dump1090.c:159 trailing_samples

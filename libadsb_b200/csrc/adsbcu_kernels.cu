@@ -78,7 +78,11 @@ static_assert(sizeof(ScanSmem) <= 227 * 1024, "scan kernel shared memory exceeds
 __device__ __forceinline__ uint32_t funnel_r(uint32_t lo, uint32_t hi, int sh) { return __funnelshift_r(lo, hi, sh); }
 __device__ __forceinline__ void group_sync(int g)
 {
+#ifdef ADSBCU_EMU
+    emu::barrier(g + 1, kGroupThreads);
+#else
     asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "n"(kGroupThreads) : "memory");
+#endif
 }
 // packed magnitudes {m(I0,Q0), m(I1,Q1)} of the two samples in a 32-bit word {I0,Q0,I1,Q1}; both must be
 // inside the central LUT (see lut_offset)
@@ -126,10 +130,18 @@ __device__ __forceinline__ bool preamble_ok(const uint16_t *p)
 template <bool kMagIn>
 __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanArgs a)
 {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+    ADSBCU_DYN_SMEM(smem_raw);
     ScanSmem &sm = *reinterpret_cast<ScanSmem *>(smem_raw);
 
     // ---- CTA prologue: magnitude LUT and CRC byte tables into shared memory (TMA bulk copies) ------
+#ifdef ADSBCU_EMU
+    for (uint32_t i = threadIdx.x; i < 32768u; i += blockDim.x) sm.lut[i] = a.tab->mag_lut[i];
+    for (uint32_t i = threadIdx.x; i < 11u * 256u; i += blockDim.x) sm.crcb[i] = (&a.tab->crc_byte[0][0])[i];
+    for (uint32_t i = threadIdx.x; i < 256u; i += blockDim.x) sm.sq[i] = a.tab->sq[i];
+    for (uint32_t i = threadIdx.x; i < kSyndSlotsLong / 32; i += blockDim.x) sm.occ_long[i] = a.tab->occ_long[i];
+    for (uint32_t i = threadIdx.x; i < kSyndSlotsShort / 32; i += blockDim.x) sm.occ_short[i] = a.tab->occ_short[i];
+    __syncthreads();
+#else
     {
         __shared__ __align__(8) unsigned long long s_bar;
         const uint32_t bar = uint32_t(__cvta_generic_to_shared(&s_bar));
@@ -156,6 +168,7 @@ __global__ void __launch_bounds__(kGroups * kGroupThreads, 1) scan_kernel(ScanAr
             asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }"
                          : "=r"(done) : "r"(bar) : "memory");
     }
+#endif
 
     const int grp = threadIdx.x / kGroupThreads, tid = threadIdx.x % kGroupThreads, lane = tid & 31;
     GroupSmem &gs = sm.grp[grp];
@@ -770,36 +783,36 @@ cudaError_t init_kernels()
 cudaError_t launch_scan(const ScanArgs &a, cudaStream_t s)
 {
     if (a.pos_end <= a.pos_begin || !a.nseg) return cudaSuccess;
-    if (a.mag_in) scan_kernel<true><<<a.nseg / kGroups, kGroups * kGroupThreads, sizeof(ScanSmem), s>>>(a);
-    else scan_kernel<false><<<a.nseg / kGroups, kGroups * kGroupThreads, sizeof(ScanSmem), s>>>(a);
+    if (a.mag_in) ADSBCU_LAUNCH(scan_kernel<true>, a.nseg / kGroups, kGroups * kGroupThreads, sizeof(ScanSmem), s, a);
+    else ADSBCU_LAUNCH(scan_kernel<false>, a.nseg / kGroups, kGroups * kGroupThreads, sizeof(ScanSmem), s, a);
     return cudaGetLastError();
 }
 
 cudaError_t launch_build_lut(DevTables *tab, cudaStream_t s)
 {
-    build_lut_kernel<<<256, 256, 0, s>>>(tab);
+    ADSBCU_LAUNCH(build_lut_kernel, 256, 256, 0, s, tab);
     return cudaGetLastError();
 }
 
 cudaError_t launch_filter(const ScanArgs &a, cudaStream_t s)
 {
     if (a.pos_end <= a.pos_begin || !a.nseg) return cudaSuccess;
-    filter_kernel<<<a.nseg, 256, 0, s>>>(a);
+    ADSBCU_LAUNCH(filter_kernel, a.nseg, 256, 0, s, a);
     return cudaGetLastError();
 }
 
 cudaError_t launch_evaluate(const ScanArgs &a, cudaStream_t s)
 {
     if (a.pos_end <= a.pos_begin || !a.nseg) return cudaSuccess;
-    evaluate_kernel<<<a.nseg, 256, 0, s>>>(a);
+    ADSBCU_LAUNCH(evaluate_kernel, a.nseg, 256, 0, s, a);
     return cudaGetLastError();
 }
 
 cudaError_t launch_revive(const ScanArgs &a, cudaStream_t s)
 {
-    revive_kernel<<<296, 256, 0, s>>>(a);
-    revive_counts_kernel<<<(a.nseg + 255) / 256, 256, 0, s>>>(a);
-    evaluate_kernel<<<a.nseg, 256, 0, s>>>(a);
+    ADSBCU_LAUNCH(revive_kernel, 296, 256, 0, s, a);
+    ADSBCU_LAUNCH(revive_counts_kernel, (a.nseg + 255) / 256, 256, 0, s, a);
+    ADSBCU_LAUNCH(evaluate_kernel, a.nseg, 256, 0, s, a);
     return cudaGetLastError();
 }
 
@@ -813,39 +826,39 @@ __global__ void signal_kernel(const ChunkCounters *d, volatile ChunkCounters *h,
 }
 cudaError_t launch_signal(const ChunkCounters *d_ctr, ChunkCounters *h_ctr_dev, uint32_t seq, cudaStream_t s)
 {
-    signal_kernel<<<1, 1, 0, s>>>(d_ctr, h_ctr_dev, seq);
+    ADSBCU_LAUNCH(signal_kernel, 1, 1, 0, s, d_ctr, h_ctr_dev, seq);
     return cudaGetLastError();
 }
 
 cudaError_t launch_or_words(uint32_t *dst, const uint32_t *src, uint32_t nwords, cudaStream_t s)
 {
-    or_words_kernel<<<296, 256, 0, s>>>(dst, src, nwords);
+    ADSBCU_LAUNCH(or_words_kernel, 296, 256, 0, s, dst, src, nwords);
     return cudaGetLastError();
 }
 
 cudaError_t launch_convert_sc16(const int16_t *in, uint32_t nsamples, uint16_t *mag, int q11, cudaStream_t s)
 {
     if (!nsamples) return cudaSuccess;
-    convert_sc16_kernel<<<148 * 8, 256, 0, s>>>(in, nsamples, mag, q11 ? 32 : 2);
+    ADSBCU_LAUNCH(convert_sc16_kernel, 148 * 8, 256, 0, s, in, nsamples, mag, q11 ? 32 : 2);
     return cudaGetLastError();
 }
 
 cudaError_t launch_carry_mag(const uint16_t *mag_in, uint32_t nsamples, uint16_t *carry_mag, cudaStream_t s)
 {
-    carry_mag_kernel<<<1, 352, 0, s>>>(mag_in, nsamples, carry_mag);
+    ADSBCU_LAUNCH(carry_mag_kernel, 1, 352, 0, s, mag_in, nsamples, carry_mag);
     return cudaGetLastError();
 }
 
 cudaError_t launch_carry(const uint8_t *iq, uint32_t nsamples, uint16_t *carry_mag, const DevTables *tab, cudaStream_t s)
 {
-    carry_kernel<<<1, 352, 0, s>>>(iq, nsamples, carry_mag, tab);
+    ADSBCU_LAUNCH(carry_kernel, 1, 352, 0, s, iq, nsamples, carry_mag, tab);
     return cudaGetLastError();
 }
 
 cudaError_t launch_magnitude(const uint8_t *iq, uint32_t nsamples, uint16_t *mag, const DevTables *tab, cudaStream_t s)
 {
     if (!nsamples) return cudaSuccess;
-    magnitude_kernel<<<148 * 8, 256, 0, s>>>(iq, nsamples, mag, tab);
+    ADSBCU_LAUNCH(magnitude_kernel, 148 * 8, 256, 0, s, iq, nsamples, mag, tab);
     return cudaGetLastError();
 }
 

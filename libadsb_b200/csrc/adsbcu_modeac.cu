@@ -110,11 +110,11 @@ cudaError_t launch_modeac(const DevTables *tab, int sm_count, cudaStream_t s, co
     cudaMemsetAsync(d_sums, 0, 2 * sizeof(unsigned long long), s);
     cudaMemsetAsync(d_count, 0, sizeof(uint32_t), s);
     cudaMemsetAsync(m + kOverlap + n, 0, 64, s);
-    if (n_overlap) acmag_kernel<<<(n_overlap + 255) / 256, 256, 0, s>>>(d_iq_overlap, n_overlap, m + (kOverlap - n_overlap), tab);
+    if (n_overlap) ADSBCU_LAUNCH(acmag_kernel, (n_overlap + 255) / 256, 256, 0, s, d_iq_overlap, n_overlap, m + (kOverlap - n_overlap), tab);
     cudaError_t e = launch_magnitude(d_iq_block, n, m + kOverlap, tab, s);
     if (e != cudaSuccess) return e;
-    acstats_kernel<<<sm_count * 4, 256, 0, s>>>(m + kOverlap, n, d_sums);
-    acscan_kernel<<<sm_count * 8, 256, 0, s>>>(m, n, d_sums, d_rec, cap, d_count);
+    ADSBCU_LAUNCH(acstats_kernel, sm_count * 4, 256, 0, s, m + kOverlap, n, d_sums);
+    ADSBCU_LAUNCH(acscan_kernel, sm_count * 8, 256, 0, s, m, n, d_sums, d_rec, cap, d_count);
     return cudaGetLastError();
 }
 

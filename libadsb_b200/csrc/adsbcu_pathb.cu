@@ -249,7 +249,7 @@ int pathb_feed(PathB *&b, const DevTables *d_tab, int sm_count, cudaStream_t s, 
     CKB(cudaMemsetAsync(b->d_ctr, 0, sizeof(CountersB), s));
     const uint32_t ntiles = uint32_t((n - 240 + kBTile - 1) / kBTile);
     const uint32_t grid = std::min<uint32_t>(ntiles, uint32_t(sm_count) * 4u);
-    scanb_kernel<<<grid, kBThreads, 0, s>>>(b->d_iq, uint32_t(n), b->d_lut, d_tab->bit_synd, b->d_rec, b->rec_cap, b->d_ctr);
+    ADSBCU_LAUNCH(scanb_kernel, grid, kBThreads, 0, s, b->d_iq, uint32_t(n), b->d_lut, d_tab->bit_synd, b->d_rec, b->rec_cap, b->d_ctr);
     CKB(cudaGetLastError());
     CKB(cudaMemcpyAsync(b->h_ctr, b->d_ctr, sizeof(CountersB), cudaMemcpyDeviceToHost, s));
     CKB(cudaStreamSynchronize(s));

@@ -355,7 +355,7 @@ int pathc_feed(PathC *&c, int sm_count, cudaStream_t st, const uint8_t *iq, size
     }
     CKC_(cudaMemcpyAsync(c->d_iq, iq, n * 2, cudaMemcpyHostToDevice, st));
     CKC_(cudaMemsetAsync(c->d_ctr, 0, sizeof(CountersC), st));
-    uat_phase_kernel<<<sm_count * 8, 256, 0, st>>>(c->d_iq, uint32_t(n), c->d_lut, c->d_phi + c->held);
+    ADSBCU_LAUNCH(uat_phase_kernel, sm_count * 8, 256, 0, st, c->d_iq, uint32_t(n), c->d_lut, c->d_phi + c->held);
     CKC_(cudaGetLastError());
     CKC_(cudaMemsetAsync(c->d_phi + c->held + n, 0, 128 * sizeof(uint16_t), st));
     const uint64_t new_end = c->abs_end + n;
@@ -364,14 +364,14 @@ int pathc_feed(PathC *&c, int sm_count, cudaStream_t st, const uint8_t *iq, size
     uint32_t nrec = 0;
     if (eval_end > c->eval_next) {
         const uint32_t first = uint32_t(c->eval_next - abs_of_index0), last = uint32_t(eval_end - abs_of_index0);
-        uat_sync_kernel<<<(last - first + 255) / 256, 256, 0, st>>>(c->d_phi, first, last, c->d_cand, c->cand_cap, c->d_ctr);
+        ADSBCU_LAUNCH(uat_sync_kernel, (last - first + 255) / 256, 256, 0, st, c->d_phi, first, last, c->d_cand, c->cand_cap, c->d_ctr);
         CKC_(cudaGetLastError());
         CKC_(cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(CountersC), cudaMemcpyDeviceToHost, st));
         CKC_(cudaStreamSynchronize(st));
         if (c->h_ctr->overflow || c->h_ctr->n_cand > c->cand_cap) { err = "internal candidate list overflow"; return ADSBCU_ERR_OVERFLOW; }
         const uint32_t ncand = c->h_ctr->n_cand;
         if (ncand) {
-            uat_decode_kernel<<<(ncand + 63) / 64, 64, 0, st>>>(c->d_phi, abs_of_index0, c->d_cand, c->d_rec, c->rec_cap, c->d_ctr, c->d_gf);
+            ADSBCU_LAUNCH(uat_decode_kernel, (ncand + 63) / 64, 64, 0, st, c->d_phi, abs_of_index0, c->d_cand, c->d_rec, c->rec_cap, c->d_ctr, c->d_gf);
             CKC_(cudaGetLastError());
             CKC_(cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(CountersC), cudaMemcpyDeviceToHost, st));
             CKC_(cudaStreamSynchronize(st));
@@ -508,7 +508,7 @@ int pathc_phase(PathC *&c, int sm_count, cudaStream_t st, const uint8_t *iq, siz
     if (c->iq_cap < n * 2) { cudaFree(c->d_iq); c->d_iq = nullptr; c->iq_cap = 0; CKC_(cudaMalloc(&c->d_iq, n * 2 + 64)); c->iq_cap = n * 2; }
     if (c->phi_out_cap < n) { cudaFree(c->d_phi_out); c->d_phi_out = nullptr; c->phi_out_cap = 0; CKC_(cudaMalloc(&c->d_phi_out, n * 2 + 64)); c->phi_out_cap = n; }
     CKC_(cudaMemcpyAsync(c->d_iq, iq, n * 2, cudaMemcpyHostToDevice, st));
-    uat_phase_kernel<<<sm_count * 8, 256, 0, st>>>(c->d_iq, uint32_t(n), c->d_lut, c->d_phi_out);
+    ADSBCU_LAUNCH(uat_phase_kernel, sm_count * 8, 256, 0, st, c->d_iq, uint32_t(n), c->d_lut, c->d_phi_out);
     CKC_(cudaGetLastError());
     CKC_(cudaMemcpyAsync(phi_out, c->d_phi_out, n * 2, cudaMemcpyDeviceToHost, st));
     CKC_(cudaStreamSynchronize(st));
