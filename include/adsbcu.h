@@ -128,6 +128,11 @@ int adsbcu_1090_magnitude(adsbcu_handle *h, const uint8_t *iq, size_t nsamples, 
 /* Filter access for host code that shares the reference's icaoFilterAdd/Test view. */
 int adsbcu_1090_filter_add(adsbcu_handle *h, uint32_t addr);
 int adsbcu_1090_filter_test(adsbcu_handle *h, uint32_t addr);   /* 1 = present, 0 = absent */
+/* icaoFilterExpire (icao_filter.c:112-127): the reference's main loop calls it once a minute for live SDR input, never
+ * for file input (dump1090.c:469-472).  The other table is cleared and becomes the active one, so an address stays
+ * known for one to two periods after it was last added.  The caller keeps the clock (the handler shim calls this
+ * every 60 s of wall time in live mode); between two calls the engine behaves like file mode. */
+int adsbcu_1090_filter_expire(adsbcu_handle *h);
 
 int adsbcu_get_stats(const adsbcu_handle *h, adsbcu_stats *out);
 

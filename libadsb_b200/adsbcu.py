@@ -47,7 +47,7 @@ KNOWN_WORDS = 1 << 20
 
 EXPORTS = ["adsbcu_abi_version", "adsbcu_last_error", "adsbcu_create", "adsbcu_destroy", "adsbcu_1090_reset",
            "adsbcu_1090_feed", "adsbcu_1090_feed_device", "adsbcu_1090_magnitude", "adsbcu_1090_filter_add",
-           "adsbcu_1090_filter_test", "adsbcu_get_stats", "adsbcu_1090b_feed", "adsbcu_1090b_reset",
+           "adsbcu_1090_filter_test", "adsbcu_1090_filter_expire", "adsbcu_get_stats", "adsbcu_1090b_feed", "adsbcu_1090b_reset",
            "adsbcu_978_feed", "adsbcu_978_reset", "adsbcu_978_phase", "adsbcu_1090_seek", "adsbcu_1090_scan_candidates",
            "adsbcu_1090_known_export", "adsbcu_1090_known_import", "adsbcu_1090_revive", "adsbcu_1090_resolve", "adsbcu_1090_modeac_block", "adsbcu_1090_feed_sc16",
            "adsbcu_1090b_decode_fields", "adsbcu_1090b_cpr_decode", "adsbcu_1090_cpr_decode"]
@@ -89,6 +89,7 @@ def load():
         L.adsbcu_1090_magnitude.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         L.adsbcu_1090_filter_add.argtypes = [C.c_void_p, C.c_uint32]
         L.adsbcu_1090_filter_test.argtypes = [C.c_void_p, C.c_uint32]
+        L.adsbcu_1090_filter_expire.argtypes = [C.c_void_p]
         L.adsbcu_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
         L.adsbcu_1090b_feed.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.adsbcu_1090b_reset.argtypes = [C.c_void_p]
@@ -275,6 +276,7 @@ class Demod1090:
 
     def filter_add(self, addr): self._check(load().adsbcu_1090_filter_add(self.h, addr))
     def filter_test(self, addr): return bool(load().adsbcu_1090_filter_test(self.h, addr))
+    def filter_expire(self): self._check(load().adsbcu_1090_filter_expire(self.h))
 
     def stats(self) -> dict:
         s = Stats()

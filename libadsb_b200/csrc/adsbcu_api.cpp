@@ -1,25 +1,21 @@
-// C ABI (include/adsbcu.h) and the ordered host pass.
+// C ABI (include/adsbcu.h): handle life cycle and the chunk pipeline of the 1090 MHz path.
 //
-// The GPU evaluates every start position and every phase without any stream state.  What is
-// left for the host is exactly the part of demodulate2400() that is sequential by definition
-// (demod_2400.c:222,336,349-355,410-419,432-443 and mode_s.c:781-788): pick the best-scoring
-// phase per position given the *current* ICAO filter, accept, skip over the message, add the
-// address to the filter, carry last_message_end across mag_buf boundaries.
+// Per chunk of a feed:   [upload]  ->  front_kernel  ->  message_kernel                  (stream `stream`)
+//                                                        -> order_kernel -> level_kernel  (stream `post_stream`, beside the next chunk)
+// The front kernel runs on all but a few SMs, so the order / level kernels of chunk c (late records, order, the ordered
+// pass of demodulate2400, signal levels, final adsbcu_msg records) have somewhere to run while chunk c+1 is scanned.  The host only
+// submits, waits for a slot before reusing it, and copies the finished messages out (or nothing at all when the
+// caller's out[] is pinned memory the GPU can write itself).  No step of the path runs on the CPU.
 #include "../../include/adsbcu.h"
 #include "adsbcu_internal.h"
 
 #include <algorithm>
-#include <atomic>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
-#include <condition_variable>
-#include <functional>
 #include <new>
-#include <mutex>
 #include <string>
-#include <thread>
 #include <vector>
 
 using namespace adsbcu;
@@ -28,18 +24,17 @@ namespace {
 
 thread_local std::string g_create_error;
 
-// Reference ICAO filter (icao_filter.c:23-109): two 4096-slot open-addressed tables, one
-// active; the flip (icaoFilterExpire) only happens for live SDR input (dump1090.c:469-472).
+// Reference ICAO filter (icao_filter.c:23-127) on the host: only adsbcu_1090_resolve uses it (merged candidates of
+// sharded captures; works on handles without a GPU).  Feeds keep their filter in device memory (StreamState).
 struct IcaoFilter {
     static constexpr uint32_t kSlots = 4096, kEmpty = 0xFFFFFFFFu;
-    uint32_t a[kSlots], b[kSlots];
-    uint32_t *active;
+    uint32_t t[2][kSlots];
+    int active = 0;
     IcaoFilter() { clear(); }
     void clear()
     {
-        std::memset(a, 0xFF, sizeof(a));
-        std::memset(b, 0xFF, sizeof(b));
-        active = a;
+        std::memset(t, 0xFF, sizeof(t));
+        active = 0;
     }
     static uint32_t hash(uint32_t v)
     {
@@ -56,92 +51,61 @@ struct IcaoFilter {
     }
     void add(uint32_t v)
     {
+        uint32_t *a = t[active];
         const uint32_t h0 = hash(v);
         uint32_t h = h0;
-        while (active[h] != kEmpty && active[h] != v) {
+        while (a[h] != kEmpty && a[h] != v) {
             h = (h + 1) & (kSlots - 1);
             if (h == h0) return;
         }
-        if (active[h] == kEmpty) active[h] = v;
+        if (a[h] == kEmpty) a[h] = v;
     }
-    static bool probe(const uint32_t *t, uint32_t v)
+    static bool probe(const uint32_t *a, uint32_t v)
     {
         const uint32_t h0 = hash(v);
         uint32_t h = h0;
-        while (t[h] != kEmpty && t[h] != v) {
+        while (a[h] != kEmpty && a[h] != v) {
             h = (h + 1) & (kSlots - 1);
             if (h == h0) break;
         }
-        return t[h] == v;
+        return a[h] == v;
     }
-    // table b only fills after an expiry flip (live SDR input, dump1090.c:469-472), which this engine never does
-    bool test(uint32_t v) const { return probe(a, v); }
+    bool test(uint32_t v) const { return probe(t[0], v) || probe(t[1], v); }
+    void expire()                       // icaoFilterExpire (icao_filter.c:112-127)
+    {
+        active ^= 1;
+        std::memset(t[active], 0xFF, sizeof(t[active]));
+    }
 };
 
 }  // namespace
 
-constexpr int kSlots = 3;            // chunks in flight: GPU works on chunk c+1, c+2 while the host pass replays chunk c
-
-// One long-lived helper thread per handle for the ordered host pass of long feeds (a thread spawned per feed starts
-// on the submitting thread's core and steals the time the submissions need).
-struct Resolver {
-    std::thread th;
-    std::mutex m;
-    std::condition_variable cv;
-    std::function<void()> job;
-    bool has_job = false, quit = false;
-    std::atomic<bool> idle{true};
-    void post(std::function<void()> fn)
-    {
-        if (!th.joinable()) th = std::thread([this] { loop(); });
-        { std::lock_guard<std::mutex> g(m); job = std::move(fn); has_job = true; idle.store(false, std::memory_order_relaxed); }
-        cv.notify_one();
-    }
-    void wait() { while (!idle.load(std::memory_order_acquire)) std::this_thread::yield(); }
-    void loop()
-    {
-        for (;;) {
-            std::function<void()> fn;
-            {
-                std::unique_lock<std::mutex> g(m);
-                cv.wait(g, [this] { return has_job || quit; });
-                if (quit) return;
-                fn = std::move(job); has_job = false;
-            }
-            fn();
-            idle.store(true, std::memory_order_release);
-        }
-    }
-    ~Resolver()
-    {
-        if (th.joinable()) {
-            { std::lock_guard<std::mutex> g(m); quit = true; }
-            cv.notify_one();
-            th.join();
-        }
-    }
-};
+constexpr int kSlots = 3;            // chunks in flight
 
 // Everything one in-flight chunk owns.
 struct Slot {
-    PhaseRec *d_seg = nullptr;        // nseg segments of seg_cap records
-    uint32_t *d_seg_count = nullptr;
+    uint16_t *d_planes = nullptr;
+    uint32_t *d_pre = nullptr, *d_pre_count = nullptr;
+    PhaseRec *d_pend = nullptr;
+    uint32_t *d_pend_count = nullptr;
+    FullRec *d_rec = nullptr;
+    uint32_t *d_rec_count = nullptr;
+    FullRec *d_ordered = nullptr;
+    FullRec *h_cand = nullptr, *d_cand = nullptr;     // sharded scans: the ordered array in mapped host memory (allocated on first use)
+    uint32_t *d_perm = nullptr, *d_seg_offset = nullptr, *d_run_start = nullptr, *d_ticket = nullptr;
+    uint4 *d_view = nullptr;
+    adsbcu_msg *d_chunk_msgs = nullptr;   // accepted messages of the chunk, before the level kernel finishes them
     ChunkCounters *d_ctr = nullptr;
-    ChunkCounters *h_ctr = nullptr;   // pinned + mapped
-    ChunkCounters *h_ctr_dev = nullptr;   // device alias of h_ctr
-    FullRec *h_full = nullptr;        // pinned + mapped: the evaluate kernel writes it directly
-    FullRec *d_full = nullptr;        // device alias of h_full
-    cudaEvent_t ev[4]{};              // scan begin, scan end, evaluate end, done (counters on the host)
-    uint32_t seq = 0;                 // sequence number of the chunk the slot holds (threaded feeds: h_ctr->pad once it is done)
+    ChunkCounters *h_ctr = nullptr;   // pinned
+    cudaEvent_t ev[6]{};              // front begin, front end, messages end | finish begin, finish end, counters on the host
 };
 
 struct adsbcu_handle {
     adsbcu_config cfg{};
     int device = 0, sm_count = 148;
-    cudaStream_t stream = nullptr;    // kernels + counter downloads
+    cudaStream_t stream = nullptr;        // front + message kernels
     cudaStream_t copy_stream = nullptr;   // host->device uploads of the feed, chunk by chunk
-    cudaStream_t post_stream = nullptr;   // ADSBCU_OVERLAP=1: filter/evaluate/signal of chunk c run here, beside the scan of chunk c+1
-    bool overlap = false;
+    cudaStream_t post_stream = nullptr;   // finish kernels (high priority: a few CTAs on the spare SMs)
     cudaEvent_t ev_h2d[2]{};
     cudaEvent_t ev_up[kSlots]{};      // upload of the chunk using that slot has finished
     std::string error;
@@ -151,42 +115,47 @@ struct adsbcu_handle {
     uint16_t *d_carry = nullptr;
     uint8_t *d_iq = nullptr;          // staging for host feeds
     int16_t *d_sc16 = nullptr;        // staging for SC16 / SC16Q11 host feeds (allocated on first use)
-    uint32_t nseg = 0, seg_cap = 0, full_cap = 0;
-    uint32_t skew = 0, skew_ns = 2500;   // measured on B200: no skew 0.5065 ms, sleep skew 0.506-0.516, short first tile 0.529 (profiles/sweep_skew.sh)
-    bool resolver_thread = true;       // ADSBCU_RESOLVER_THREAD=0: the ordered host pass stays on the calling thread
-    uint32_t chunk_seq = 0;
-    Resolver resolver;
-    int wait_policy = 50;              // ADSBCU_WAIT: microseconds the submitter sleeps while all slots are busy (0: both threads yield-spin)
-    uint32_t thread_tps = 8;
-    uint32_t unit_positions = 0, max_tps = 1, host_tps = 4;   // chunk = unit_positions * (tiles per segment), at most max_tps
+    StreamState *d_state = nullptr;
+    uint32_t *h_word = nullptr, *d_word = nullptr;    // one mapped word for small device->host answers
+    adsbcu_msg *h_msgs = nullptr, *d_msgs = nullptr;  // accepted messages of the running feed (pinned + mapped), grown on demand
+    size_t msgs_cap = 0;
+
+    // geometry
+    uint32_t nseg = 0, msg_grid = 0, level_grid = 128;
+    uint32_t unit_positions = 0, max_tps = 1, host_tps = 4, res_tps = 4;   // chunk = unit_positions * (tiles per segment)
+    uint32_t ntiles_max = 0, plane_stride = 0, pre_cap = 0, pend_cap = 0, rec_cap = 0, full_cap = 0;
+    uint32_t grow = 1;                // list capacities are `grow` times their base size (doubled after an overflow)
+    bool force_sequential = false;    // ADSBCU_RESOLVE_SEQ=1: the finish kernel always takes its one-thread replay (tests)
     Slot slot[kSlots];
     uint16_t *d_mag = nullptr;        // stage-level magnitude output
     size_t d_mag_cap = 0;
 
-    // stream state
+    // stream state that lives on the host
     uint64_t stream_pos = 0;          // samples consumed so far == padded coordinate of the next feed's first start
-    bool has_last = false;            // last accepted message: its start and last_message_end, both in
-    uint64_t last_a = 0, last_lme = 0; // stream coordinates counted from the first (zero) overlap sample
-    IcaoFilter filter;
     adsbcu_stats stats{};
     PathB *pathb = nullptr;
     Fields *fields = nullptr;
     PathC *pathc = nullptr;
 
-    // sharded captures (adsbcu_1090_scan_candidates / _revive)
+    // adsbcu_1090_resolve (merged candidates): host-side ordered pass with its own filter and skip state
     bool host_only = false;           // cfg.device == -1: merge-only handle, no CUDA at all
+    bool has_last = false;
+    uint64_t last_a = 0, last_lme = 0;
+    IcaoFilter filter;
+
+    // sharded captures (adsbcu_1090_scan_candidates / _revive)
     uint16_t *d_carry_prev = nullptr; // the carry the last scan started from (revive re-slices with it)
     PhaseRec *d_deferred = nullptr;
     uint32_t *d_n_deferred = nullptr, *d_known_tmp = nullptr;
     uint32_t deferred_cap = 0;
+    const uint8_t *last_iq = nullptr; // device samples of the last candidate scan
+    uint32_t last_n = 0;
+    uint64_t last_base = 0;
     // Mode A/C (adsbcu_1090_modeac_block)
     uint8_t *d_ac_ov = nullptr;
     unsigned long long *d_ac_sums = nullptr;      // [2] sums, then the record counter
     AcRec *d_ac_rec = nullptr, *h_ac_rec = nullptr;
     uint32_t ac_cap = 0;
-    const uint8_t *last_iq = nullptr; // device samples of the last candidate scan
-    uint32_t last_n = 0;
-    uint64_t last_base = 0;
 };
 
 namespace {
@@ -201,29 +170,80 @@ bool cuda_ok(adsbcu_handle *h, cudaError_t e, const char *what)
 }
 #define CK(call) do { if (!cuda_ok(h, (call), #call)) return ADSBCU_ERR_CUDA; } while (0)
 
+void free_slots(adsbcu_handle *h)
+{
+    for (Slot &s : h->slot) {
+        cudaFree(s.d_planes); cudaFree(s.d_pre); cudaFree(s.d_pre_count); cudaFree(s.d_pend); cudaFree(s.d_pend_count);
+        cudaFree(s.d_rec); cudaFree(s.d_rec_count); cudaFree(s.d_ordered); cudaFree(s.d_perm); cudaFree(s.d_seg_offset);
+        cudaFree(s.d_run_start); cudaFree(s.d_ticket); cudaFree(s.d_ctr); cudaFree(s.d_chunk_msgs); cudaFree(s.d_view);
+        if (s.h_cand) cudaFreeHost(s.h_cand);
+        if (s.h_ctr) cudaFreeHost(s.h_ctr);
+        cudaEvent_t ev[6];
+        std::memcpy(ev, s.ev, sizeof(ev));
+        s = Slot{};
+        std::memcpy(s.ev, ev, sizeof(ev));
+    }
+}
+
+// Slot buffers for chunks of up to max_tps tiles per segment; list capacities scale with h->grow.
+int alloc_slots(adsbcu_handle *h)
+{
+    const size_t chunk = size_t(h->unit_positions) * h->max_tps;
+    h->ntiles_max = uint32_t((chunk + kFNeed + kWTile - 1) / kWTile);
+    h->plane_stride = h->ntiles_max * 32 + 32;
+    const size_t seg_pos = size_t((h->ntiles_max + h->nseg - 1) / h->nseg) * kWTile;
+    // Gaussian noise confirms 1 preamble per 93 positions and parks 1 record per 90 (with --fix); full-scale uniform
+    // noise about 4x that.  Overflow is detected, the lists are doubled and the chunk is run again.
+    h->pre_cap = uint32_t(std::min<size_t>(seg_pos, std::max<size_t>(1024, seg_pos / 8 * h->grow)));
+    h->pend_cap = uint32_t(std::min<size_t>(5 * seg_pos, std::max<size_t>(1024, seg_pos / 8 * h->grow)));
+    h->rec_cap = uint32_t(std::min<size_t>(4096, std::max<size_t>(256, seg_pos / 16 * h->grow)));
+    h->full_cap = uint32_t(std::min<size_t>(size_t(h->nseg) * h->rec_cap, std::max<size_t>(1u << 13, chunk / 64 * h->grow)));
+    for (Slot &s : h->slot) {
+        CK(cudaMalloc(&s.d_planes, size_t(12) * h->plane_stride * sizeof(uint16_t)));
+        CK(cudaMalloc(&s.d_pre, size_t(h->nseg) * h->pre_cap * sizeof(uint32_t)));
+        CK(cudaMalloc(&s.d_pre_count, size_t(h->nseg) * sizeof(uint32_t)));
+        CK(cudaMalloc(&s.d_pend, size_t(h->nseg) * h->pend_cap * sizeof(PhaseRec)));
+        CK(cudaMalloc(&s.d_pend_count, size_t(h->nseg) * sizeof(uint32_t)));
+        CK(cudaMalloc(&s.d_rec, size_t(h->nseg) * h->rec_cap * sizeof(FullRec)));
+        CK(cudaMalloc(&s.d_rec_count, size_t(h->nseg) * sizeof(uint32_t)));
+        CK(cudaMalloc(&s.d_ordered, size_t(h->full_cap) * sizeof(FullRec)));
+        CK(cudaMalloc(&s.d_perm, size_t(h->nseg) * h->rec_cap * sizeof(uint32_t)));
+        CK(cudaMalloc(&s.d_seg_offset, size_t(h->nseg) * sizeof(uint32_t)));
+        CK(cudaMalloc(&s.d_run_start, (size_t(h->full_cap) + 1) * sizeof(uint32_t)));
+        CK(cudaMalloc(&s.d_chunk_msgs, size_t(h->full_cap) * sizeof(adsbcu_msg)));
+        CK(cudaMalloc(&s.d_view, size_t(h->full_cap) * sizeof(uint4)));
+        CK(cudaMalloc(&s.d_ticket, sizeof(uint32_t)));
+        CK(cudaMemset(s.d_ticket, 0, sizeof(uint32_t)));
+        CK(cudaMalloc(&s.d_ctr, sizeof(ChunkCounters)));
+        CK(cudaHostAlloc(&s.h_ctr, sizeof(ChunkCounters), cudaHostAllocDefault));
+        std::memset(s.h_ctr, 0, sizeof(ChunkCounters));
+    }
+    return ADSBCU_OK;
+}
+
 void free_all(adsbcu_handle *h)
 {
     if (h->host_only) return;
     cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->post_stream) cudaStreamSynchronize(h->post_stream);
+    if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
     cudaFree(h->d_sc16);
     cudaFree(h->d_ac_ov); cudaFree(h->d_ac_sums); cudaFree(h->d_ac_rec);
     if (h->h_ac_rec) cudaFreeHost(h->h_ac_rec);
     cudaFree(h->d_carry_prev); cudaFree(h->d_deferred); cudaFree(h->d_n_deferred); cudaFree(h->d_known_tmp);
-    if (h->stream) cudaStreamSynchronize(h->stream);
     pathb_free(h->pathb);
     h->pathb = nullptr;
     fields_free(h->fields);
     h->fields = nullptr;
     pathc_free(h->pathc);
     h->pathc = nullptr;
-    if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
-    cudaFree(h->d_tab); cudaFree(h->d_bitmap); cudaFree(h->d_carry); cudaFree(h->d_iq); cudaFree(h->d_mag);
-    for (Slot &s : h->slot) {
-        cudaFree(s.d_seg); cudaFree(s.d_seg_count); cudaFree(s.d_ctr);
-        if (s.h_ctr) cudaFreeHost(s.h_ctr);
-        if (s.h_full) cudaFreeHost(s.h_full);
+    cudaFree(h->d_tab); cudaFree(h->d_bitmap); cudaFree(h->d_carry); cudaFree(h->d_iq); cudaFree(h->d_mag); cudaFree(h->d_state);
+    if (h->h_word) cudaFreeHost(h->h_word);
+    if (h->h_msgs) cudaFreeHost(h->h_msgs);
+    free_slots(h);
+    for (Slot &s : h->slot)
         for (auto &e : s.ev) if (e) cudaEventDestroy(e);
-    }
     for (auto &e : h->ev_h2d) if (e) cudaEventDestroy(e);
     for (auto &e : h->ev_up) if (e) cudaEventDestroy(e);
     if (h->stream) cudaStreamDestroy(h->stream);
@@ -231,9 +251,7 @@ void free_all(adsbcu_handle *h)
     if (h->post_stream) cudaStreamDestroy(h->post_stream);
 }
 
-// ---- ordered host pass ------------------------------------------------------------------
-// recs: the surviving (position, phase) records of one chunk in (pos, phase) order.
-// feed_base: padded-stream coordinate of the feed's first start position.
+// ---- ordered pass on the host: adsbcu_1090_resolve only ---------------------------------------------------
 struct Sink {
     adsbcu_msg *out;
     size_t cap, n;
@@ -257,51 +275,37 @@ void copy_candidates(const FullRec *recs, size_t nrec, uint64_t feed_base, Sink 
     }
 }
 
-template <class Rec>
-void resolve(adsbcu_handle *h, const Rec *recs, size_t nrec, uint64_t feed_base, Sink &sink)
+// demodulate2400's sequential rules over candidates in ascending (pos, phase) order (demod_2400.c:336,349-355,
+// 410-443; mode_s.c:781-788).  The device twin of this loop is resolve_range() in adsbcu_finish.cu.
+void resolve_host(adsbcu_handle *h, const adsbcu_cand *recs, size_t nrec, Sink &sink)
 {
     const uint64_t block = h->cfg.block_samples;
-    // mag_buf index of a stream coordinate; block_samples is a power of two unless a test shrinks it oddly
-    const int bshift = (block & (block - 1)) == 0 ? __builtin_ctzll(block) : -1;
-    auto blk_of = [&](uint64_t x) { return bshift >= 0 ? x >> bshift : x / block; };
-    uint64_t last_blk = h->has_last ? blk_of(h->last_a) : 0;
-    uint64_t ts_blk = ~0ull, ts_bstart = 0, ts_base = 0;     // timestamp base of the mag_buf being replayed
+    auto blk_of = [&](uint64_t x) { return x / block; };
     size_t i = 0;
     while (i < nrec) {
-        // the records were written by the GPU into mapped host memory: keep a few cache lines in flight
-        __builtin_prefetch(reinterpret_cast<const char *>(recs + i) + 1024);
-        __builtin_prefetch(reinterpret_cast<const char *>(recs + i) + 1088);
-        const auto pos = recs[i].pos;
-        const uint64_t a = feed_base + pos;
+        const uint64_t a = recs[i].pos;
         size_t e = i + 1;
-        while (e < nrec && recs[e].pos == pos) ++e;
+        while (e < nrec && recs[e].pos == a) ++e;
         if (h->has_last) {
-            // inside the mag_buf of the last accepted message scanning resumes 18 samples before its
-            // end (j = last_message_end - 19, then ++j); a later mag_buf starts exactly at its end
-            const bool same_block = blk_of(a) == last_blk;
+            const bool same_block = blk_of(a) == blk_of(h->last_a);
             if (a < (same_block ? h->last_lme - 18 : h->last_lme)) { i = e; continue; }
         }
-
         int best = 0;                       // SR_NOT_SET
-        const Rec *bp = nullptr;
-        uint32_t last_key = kUnchecked, best_key = kUnchecked;
-        bool last_known = false, best_known = false;
+        const adsbcu_cand *bp = nullptr;
+        uint32_t last_key = kUnchecked;
+        bool last_known = false;
         for (size_t k = i; k < e; ++k) {    // phases ascending; strict > keeps the lowest phase on ties
             if (const uint32_t key = recs[k].test_key; key != last_key) { last_key = key; last_known = h->filter.test(key); }
             const int sc = rank_of(recs[k].kind, last_known);
-            if (sc > best) { best = sc; bp = &recs[k]; best_key = last_key; best_known = last_known; }
+            if (sc > best) { best = sc; bp = &recs[k]; }
         }
         i = e;
         if (best < kAcceptThreshold) continue;
-
-        const Rec &r = *bp;
+        const adsbcu_cand &r = *bp;
         if (sink.n < sink.cap) {
             adsbcu_msg &m = sink.out[sink.n];
-            // sampleTimestamp of the block (sdr_ifile.c:202) + 5*j + 768 + phase: with 12e6/2.4e6 == 5 this
-            // is 5*a + 768 + phase where a counts from the first overlap sample of the stream
-            const uint64_t blk = blk_of(a);
-            if (blk != ts_blk) { ts_blk = blk; ts_bstart = blk * block; ts_base = uint64_t(double(ts_bstart) * 12e6 / 2400000.0); }
-            m.timestamp = ts_base + (a - ts_bstart) * 5 + (8 + 56) * 12 + r.phase;
+            const uint64_t bstart = blk_of(a) * block;
+            m.timestamp = uint64_t(double(bstart) * 12e6 / 2400000.0) + (a - bstart) * 5 + (8 + 56) * 12 + r.phase;
             std::memcpy(m.msg, r.msg, 14);
             std::memcpy(m.verbatim, r.verbatim, 14);
             m.msgbits = (r.msgtype & 16) ? 112 : 56;
@@ -315,232 +319,249 @@ void resolve(adsbcu_handle *h, const Rec *recs, size_t nrec, uint64_t feed_base,
             sink.overflow = true;
         }
         ++sink.n;
-        // icaoFilterAdd of an address the filter just reported as present is a no-op: skip its hash + probe
-        if (const uint32_t add_key = r.add_key; add_key != kUnchecked && !(add_key == best_key && best_known)) h->filter.add(add_key);
-
-        // skip rule (demod_2400.c:410-419, :432-443): remember where this message ends
+        if (r.add_key != kUnchecked) h->filter.add(r.add_key);
         h->has_last = true;
         h->last_a = a;
-        last_blk = blk_of(a);
         h->last_lme = a + uint64_t((((r.verbatim[0] & 0x80) ? 112 : 56) + 8) * 12 / 5);
     }
 }
 
-// ---- one feed of at most max_feed_samples: a pipeline of chunks ---------------------------------
-// For every chunk: [upload its samples] -> scan -> filter -> evaluate -> counters to the host.
-// Everything is queued without host synchronisation; the host pass of chunk c runs while the GPU
-// works on the following chunks.  iq_host != nullptr: the samples are uploaded into d_iq chunk by
-// chunk on copy_stream (a chunk only looks at samples at or before its own end, see ScanArgs).
-// sc16_host != nullptr (then iq_host must be null): SC16 / SC16Q11 samples; they are uploaded chunk by chunk into
-// d_sc16, converted to uint16 magnitudes into d_iq (2 bytes per sample, like uc8 I/Q) and every kernel runs
-// in magnitudes-in mode (convert.c:46-92).
-int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint32_t n, Sink &sink,
-             const int16_t *sc16_host = nullptr, int q11 = 0)
+// ---- one feed of at most max_feed_samples: a pipeline of chunks ---------------------------------------------
+// iq_host != nullptr: the samples are uploaded into d_iq chunk by chunk on copy_stream (a chunk only looks at samples
+// before its own end, see ChunkArgs::nsamples).  sc16_host != nullptr (then iq_host must be null): SC16 / SC16Q11
+// samples are uploaded into d_sc16, converted to uint16 magnitudes into d_iq (2 bytes per sample, like uc8 I/Q) and
+// every kernel runs in magnitudes-in mode (convert.c:46-92).
+// Resolve mode (sink.cands == nullptr): accepted messages go to out_dev[0 .. out_cap) on the device side, the count
+// is StreamState::n_out.  Candidate mode: the ordered records of every chunk are copied to sink.cands.
+constexpr int kOverflowRetry = -100;
+
+int run_chunks(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint32_t n, Sink &sink, adsbcu_msg *out_dev, uint64_t out_cap,
+               const int16_t *sc16_host, int q11, const std::vector<uint32_t> &bounds, uint32_t first_chunk, uint32_t &failed_chunk,
+               bool already_uploaded)
 {
-    const bool from_host = iq_host || sc16_host;
     adsbcu_stats &st = h->stats;
-    // chunk boundaries: the first chunks are short so that the pipeline (upload -> kernels -> host pass)
-    // fills quickly, later ones long so that per-launch costs (LUT load, tail) are amortised
-    std::vector<uint32_t> bounds{0};
-    // host feeds are bound by the upload: short chunks throughout keep the work left after the last byte arrived small
-    // (with the host pass on its own thread, 8 tiles per segment and chunk balance kernel launch overheads against the
-    // host work left when the GPU finishes: profiles/r01_host_pass_thread_sweep.txt)
-    const uint32_t tps_cap = from_host ? std::min(h->host_tps, h->max_tps) : h->resolver_thread ? std::min(h->max_tps, h->thread_tps) : h->max_tps;
-    for (uint32_t tps = std::min(4u, tps_cap); bounds.back() < n; tps = std::min(2 * tps, tps_cap))
-        bounds.push_back(uint32_t(std::min<uint64_t>(n, uint64_t(bounds.back()) + uint64_t(h->unit_positions) * tps)));
     const uint32_t nchunks = uint32_t(bounds.size() - 1);
-    const bool threaded = h->resolver_thread && nchunks >= 3;
-    const bool post = h->overlap && !sink.cands && nchunks >= 2;
-    float ms_h2d = 0.f;
-    if (from_host) CK(cudaEventRecord(h->ev_h2d[0], h->copy_stream));
+    const bool upload = (iq_host || sc16_host) && !already_uploaded;
+    failed_chunk = nchunks;
 
     auto submit = [&](uint32_t c) -> int {
-        Slot &s = h->slot[c % kSlots];
-        ScanArgs a{};
+        const int si = int(c % kSlots);
+        Slot &s = h->slot[si];
+        ChunkArgs a{};
         a.iq = d_iq;
         a.carry_mag = h->d_carry;
-        a.nsamples = n;
         a.pos_begin = bounds[c];
         a.pos_end = bounds[c + 1];
+        a.nsamples = (iq_host || sc16_host) ? a.pos_end : n;      // host feeds: nothing past the chunk has been uploaded
         a.tab = h->d_tab;
         a.bitmap = h->d_bitmap;
-        a.seg = s.d_seg; a.seg_cap = h->seg_cap; a.nseg = h->nseg;
-        a.seg_count = s.d_seg_count;
-        a.full = s.d_full; a.full_cap = h->full_cap;
+        a.nseg = h->nseg;
+        a.planes = s.d_planes; a.plane_stride = h->plane_stride;
+        a.pre = s.d_pre; a.pre_cap = h->pre_cap; a.pre_count = s.d_pre_count;
+        a.pend = s.d_pend; a.pend_cap = h->pend_cap; a.pend_count = s.d_pend_count;
+        a.rec = s.d_rec; a.rec_cap = h->rec_cap; a.rec_count = s.d_rec_count;
+        a.ordered = sink.cands ? s.d_cand : s.d_ordered; a.full_cap = h->full_cap;
         a.ctr = s.d_ctr;
-        a.skew = h->skew; a.skew_ns = h->skew_ns;
-        if (sink.cands) { a.deferred = h->d_deferred; a.deferred_cap = h->deferred_cap; a.n_deferred = h->d_n_deferred; }
         if (sc16_host) {
             a.iq = nullptr;
             a.mag_in = reinterpret_cast<const uint16_t *>(h->d_iq);
-            CK(cudaMemcpyAsync(h->d_sc16 + 2 * size_t(a.pos_begin), sc16_host + 2 * size_t(a.pos_begin),
-                               4 * size_t(a.pos_end - a.pos_begin), cudaMemcpyHostToDevice, h->copy_stream));
-            CK(cudaEventRecord(h->ev_up[c % kSlots], h->copy_stream));
-            if (c + 1 == nchunks) CK(cudaEventRecord(h->ev_h2d[1], h->copy_stream));
-            CK(cudaStreamWaitEvent(h->stream, h->ev_up[c % kSlots], 0));
-            CK(launch_convert_sc16(h->d_sc16 + 2 * size_t(a.pos_begin), a.pos_end - a.pos_begin,
-                                   reinterpret_cast<uint16_t *>(h->d_iq) + a.pos_begin, q11, h->stream));
         }
-        if (iq_host) {
-            CK(cudaMemcpyAsync(h->d_iq + 2 * size_t(a.pos_begin), iq_host + 2 * size_t(a.pos_begin),
-                               2 * size_t(a.pos_end - a.pos_begin), cudaMemcpyHostToDevice, h->copy_stream));
-            CK(cudaEventRecord(h->ev_up[c % kSlots], h->copy_stream));
+        if (upload) {
+            if (sc16_host)
+                CK(cudaMemcpyAsync(h->d_sc16 + 2 * size_t(a.pos_begin), sc16_host + 2 * size_t(a.pos_begin),
+                                   4 * size_t(a.pos_end - a.pos_begin), cudaMemcpyHostToDevice, h->copy_stream));
+            else
+                CK(cudaMemcpyAsync(h->d_iq + 2 * size_t(a.pos_begin), iq_host + 2 * size_t(a.pos_begin),
+                                   2 * size_t(a.pos_end - a.pos_begin), cudaMemcpyHostToDevice, h->copy_stream));
+            CK(cudaEventRecord(h->ev_up[si], h->copy_stream));
             if (c + 1 == nchunks) CK(cudaEventRecord(h->ev_h2d[1], h->copy_stream));
-            CK(cudaStreamWaitEvent(h->stream, h->ev_up[c % kSlots], 0));
+            CK(cudaStreamWaitEvent(h->stream, h->ev_up[si], 0));
+            if (sc16_host)
+                CK(launch_convert_sc16(h->d_sc16 + 2 * size_t(a.pos_begin), a.pos_end - a.pos_begin,
+                                       reinterpret_cast<uint16_t *>(h->d_iq) + a.pos_begin, q11, h->stream));
         }
         CK(cudaMemsetAsync(s.d_ctr, 0, sizeof(ChunkCounters), h->stream));
+        CK(cudaMemsetAsync(s.d_rec_count, 0, size_t(h->nseg) * sizeof(uint32_t), h->stream));
+        CK(cudaMemsetAsync(s.d_pend_count, 0, size_t(h->nseg) * sizeof(uint32_t), h->stream));
         CK(cudaEventRecord(s.ev[0], h->stream));
-        CK(launch_scan(a, h->stream));
+        CK(launch_front(a, h->stream));
         CK(cudaEventRecord(s.ev[1], h->stream));
-        // the sparse kernels of this chunk only touch the chunk's own slot (and read the address bitmap, where a
-        // superset keeps more records for the exact host pass): they may run beside the next chunk's scan
-        const cudaStream_t ps = post ? h->post_stream : h->stream;
-        if (post) CK(cudaStreamWaitEvent(ps, s.ev[1], 0));
-        CK(launch_filter(a, ps));
-        CK(launch_evaluate(a, ps));
-        CK(cudaEventRecord(s.ev[2], ps));
-        if (threaded) {
-            s.seq = ++h->chunk_seq;
-            CK(launch_signal(s.d_ctr, s.h_ctr_dev, s.seq, ps));
-        } else {
-            CK(cudaMemcpyAsync(s.h_ctr, s.d_ctr, sizeof(ChunkCounters), cudaMemcpyDeviceToHost, ps));
-        }
-        CK(cudaEventRecord(s.ev[3], ps));
+        CK(launch_messages(a, h->msg_grid, h->stream));
+        CK(cudaEventRecord(s.ev[2], h->stream));
+        // the finish kernel only touches this chunk's slot, the stream state and (reading) the address set, where a
+        // superset merely keeps more records for the exact ordered pass: it runs beside the next chunk's scan
+        FinishArgs fa{};
+        fa.c = a;
+        fa.st = h->d_state;
+        fa.out = out_dev; fa.out_cap = out_cap;
+        fa.chunk_msgs = s.d_chunk_msgs;
+        fa.feed_base = h->stream_pos;
+        fa.block_samples = h->cfg.block_samples;
+        fa.candidates_only = sink.cands ? 1u : 0u;
+        fa.force_sequential = h->force_sequential ? 1u : 0u;
+        fa.ticket = s.d_ticket; fa.perm = s.d_perm; fa.seg_offset = s.d_seg_offset; fa.run_start = s.d_run_start; fa.view = s.d_view;
+        if (sink.cands) { fa.deferred = h->d_deferred; fa.deferred_cap = h->deferred_cap; fa.n_deferred = h->d_n_deferred; }
+        CK(cudaStreamWaitEvent(h->post_stream, s.ev[2], 0));
+        CK(cudaEventRecord(s.ev[3], h->post_stream));
+        CK(launch_finish(fa, h->level_grid, h->post_stream));
+        CK(cudaEventRecord(s.ev[4], h->post_stream));
+        CK(cudaMemcpyAsync(s.h_ctr, s.d_ctr, sizeof(ChunkCounters), cudaMemcpyDeviceToHost, h->post_stream));
+        CK(cudaEventRecord(s.ev[5], h->post_stream));
+        st.scan_launches += 4;
         return ADSBCU_OK;
     };
-    // host half of a chunk: counters are on the host, the records in mapped memory
-    auto host_pass = [&](uint32_t c) -> int {
+    // host half of a chunk: its counters are on the host; candidate mode also copies the records out
+    auto retire = [&](uint32_t c) -> int {
         Slot &s = h->slot[c % kSlots];
+        CK(cudaEventSynchronize(s.ev[5]));
         const ChunkCounters k = *s.h_ctr;
-        if (k.overflow || k.n_full > h->full_cap) {
-            h->error = "internal candidate list overflow (traffic denser than the lists are sized for)";
-            return ADSBCU_ERR_OVERFLOW;
-        }
-        const auto t0 = std::chrono::steady_clock::now();
-        if (sink.cands) copy_candidates(s.h_full, k.n_full, h->stream_pos, sink);
-        else resolve(h, s.h_full, k.n_full, h->stream_pos, sink);
-        const auto t1 = std::chrono::steady_clock::now();
-        st.preambles += k.preambles; st.phase_records += k.n_cand; st.resolved_records += k.n_full;
-        st.ms_resolve += std::chrono::duration<float, std::milli>(t1 - t0).count();
-        return ADSBCU_OK;
-    };
-    auto kernel_times = [&](uint32_t c) {
-        Slot &s = h->slot[c % kSlots];
+        if (k.overflow) { if (failed_chunk == nchunks) failed_chunk = c; return ADSBCU_OK; }
+        if (failed_chunk != nchunks) return ADSBCU_OK;                 // chunks after a failed one did not touch the state
+        if (sink.cands) copy_candidates(s.h_cand, k.n_full, h->stream_pos, sink);
+        st.preambles += k.preambles; st.phase_records += k.n_cand; st.resolved_records += k.n_full; st.messages += k.n_msgs;
         float ms = 0.f;
         cudaEventElapsedTime(&ms, s.ev[0], s.ev[1]); st.ms_scan += ms;
         cudaEventElapsedTime(&ms, s.ev[1], s.ev[2]); st.ms_finalize += ms;
-        st.scan_launches += threaded ? 4 : 3;        // scan, filter, evaluate (+ signal)
-    };
-    auto retire = [&](uint32_t c) -> int {
-        CK(cudaEventSynchronize(h->slot[c % kSlots].ev[3]));
-        const int r = host_pass(c);
-        if (r == ADSBCU_OK) kernel_times(c);
-        return r;
+        cudaEventElapsedTime(&ms, s.ev[3], s.ev[4]); st.ms_resolve += ms;
+        return ADSBCU_OK;
     };
 
     int rc = ADSBCU_OK;
-    if (threaded) {
-        // Long feeds: the ordered host pass runs on its own thread, which makes no CUDA call at all (it polls the
-        // sequence number the signal kernel writes into mapped host memory), so the ~10 runtime calls of every
-        // submit and the host pass do not queue behind each other on one core.
-        std::atomic<uint32_t> retired{0};
-        std::atomic<int> worker_rc{ADSBCU_OK};
-        std::atomic<bool> stop{false};
-        const uint32_t first_seq = h->chunk_seq + 1;
-        uint32_t spins = 0;
-        h->resolver.post([&] {
-            for (uint32_t c = 0; c < nchunks; ++c) {
-                Slot &s = h->slot[c % kSlots];
-                while (reinterpret_cast<const volatile ChunkCounters *>(s.h_ctr)->pad != first_seq + c) {
-                    if (stop.load(std::memory_order_relaxed)) return;
-                    if (h->wait_policy == 0) std::this_thread::yield(); else __builtin_ia32_pause();
-                }
-                std::atomic_thread_fence(std::memory_order_acquire);
-                const int r = host_pass(c);
-                if (r != ADSBCU_OK) { worker_rc.store(r); return; }
-                retired.store(c + 1, std::memory_order_release);
-            }
-        });
-        for (uint32_t c = 0; c < nchunks && rc == ADSBCU_OK; ++c) {
-            while (c >= retired.load(std::memory_order_acquire) + kSlots && worker_rc.load() == ADSBCU_OK) {
-                if (h->wait_policy == 0) std::this_thread::yield();
-                else std::this_thread::sleep_for(std::chrono::microseconds(h->wait_policy));
-                if ((++spins & 63u) != 0) continue;         // every few milliseconds: has the pipeline died?
-                if (const cudaError_t q = cudaStreamQuery(h->stream); q != cudaSuccess && q != cudaErrorNotReady) {
-                    cuda_ok(h, q, "scan pipeline");
-                    rc = ADSBCU_ERR_CUDA;
-                    break;
-                }
-            }
+    uint32_t submitted = first_chunk, retired = first_chunk;
+    while (retired < nchunks) {
+        while (submitted < nchunks && submitted < retired + kSlots && failed_chunk == nchunks) {
+            rc = submit(submitted);
             if (rc != ADSBCU_OK) break;
-            if (worker_rc.load() != ADSBCU_OK) break;
-            if (c >= kSlots) kernel_times(c - kSlots);          // the slot's previous chunk is done: read its events before reuse
-            rc = submit(c);
+            ++submitted;
         }
-        if (rc != ADSBCU_OK) { cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->post_stream); stop.store(true); }
-        // wait for the resolver; a failed kernel would never write its sequence number, so watch the stream for errors
-        while (!h->resolver.idle.load(std::memory_order_acquire)) {
-            std::this_thread::yield();                  // (a sleep here would add its timer slack to every feed)
-            if ((++spins & 4095u) != 0 || stop.load()) continue;
-            if (const cudaError_t q = cudaStreamQuery(h->stream); q != cudaSuccess && q != cudaErrorNotReady) {
-                cuda_ok(h, q, "scan pipeline");
-                rc = ADSBCU_ERR_CUDA;
-                stop.store(true);
-            }
-        }
-        if (rc == ADSBCU_OK) rc = worker_rc.load();
-        if (rc == ADSBCU_OK)
-            for (uint32_t c = nchunks > kSlots ? nchunks - kSlots : 0; c < nchunks; ++c) kernel_times(c);
-    } else {
-        uint32_t submitted = 0, retired = 0;
-        while (retired < nchunks) {
-            while (submitted < nchunks && submitted < retired + kSlots) {
-                rc = submit(submitted);
-                if (rc != ADSBCU_OK) break;
-                ++submitted;
-            }
-            if (rc != ADSBCU_OK) break;
-            rc = retire(retired);
-            if (rc != ADSBCU_OK) break;
-            ++retired;
-        }
+        if (rc != ADSBCU_OK || retired >= submitted) break;
+        rc = retire(retired);
+        if (rc != ADSBCU_OK) break;
+        ++retired;
     }
-    if (rc != ADSBCU_OK) { cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->post_stream); cudaStreamSynchronize(h->copy_stream); return rc; }
-    if (post) CK(cudaStreamWaitEvent(h->stream, h->slot[(nchunks - 1) % kSlots].ev[3], 0));
+    if (rc != ADSBCU_OK) {
+        cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->post_stream); cudaStreamSynchronize(h->copy_stream);
+        return rc;
+    }
+    return failed_chunk != nchunks ? kOverflowRetry : ADSBCU_OK;
+}
+
+int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint32_t n, Sink &sink, adsbcu_msg *out_dev, uint64_t out_cap,
+             const int16_t *sc16_host = nullptr, int q11 = 0)
+{
+    const bool from_host = iq_host || sc16_host;
+    // chunk boundaries: the first chunks are short so that the pipeline fills quickly, later ones long so that
+    // per-launch costs (LUT load, tails) are amortised; host feeds are bound by the upload and keep short chunks
+    // throughout, so that little work is left when the last byte has arrived
+    std::vector<uint32_t> bounds{0};
+    const uint32_t tps_cap = std::min(h->max_tps, from_host ? h->host_tps : h->res_tps);
+    for (uint32_t tps = std::min(2u, tps_cap); bounds.back() < n; tps = std::min(2 * tps, tps_cap))
+        bounds.push_back(uint32_t(std::min<uint64_t>(n, uint64_t(bounds.back()) + uint64_t(h->unit_positions) * tps)));
+    const uint32_t nchunks = uint32_t(bounds.size() - 1);
+    if (from_host) CK(cudaEventRecord(h->ev_h2d[0], h->copy_stream));
+
+    uint32_t first = 0, failed = nchunks;
+    bool uploaded = false;
+    int rc = ADSBCU_OK;
+    for (int attempt = 0;; ++attempt) {
+        rc = run_chunks(h, d_iq, iq_host, n, sink, out_dev, out_cap, sc16_host, q11, bounds, first, failed, uploaded);
+        if (rc != kOverflowRetry) break;
+        // a list of chunk `failed` overflowed: nothing from that chunk on has touched the stream state.  Double the
+        // lists and run again from there (the samples are on the device already).
+        CK(cudaStreamSynchronize(h->stream));
+        CK(cudaStreamSynchronize(h->post_stream));
+        CK(cudaStreamSynchronize(h->copy_stream));
+        if (attempt >= 5) {
+            h->error = "internal candidate list overflow (traffic denser than the lists can be grown for)";
+            return ADSBCU_ERR_OVERFLOW;
+        }
+        h->grow *= 2;
+        free_slots(h);
+        if (const int r = alloc_slots(h); r != ADSBCU_OK) return r;
+        if (sink.cands)
+            for (Slot &s : h->slot) {
+                CK(cudaHostAlloc(&s.h_cand, size_t(h->full_cap) * sizeof(FullRec), cudaHostAllocMapped));
+                CK(cudaHostGetDevicePointer(&s.d_cand, s.h_cand, 0));
+            }
+        CK(launch_state_begin_feed(h->d_state, 0, h->post_stream));  // clears the poison mark, keeps the message count
+        first = failed;
+        uploaded = true;
+    }
+    if (rc != ADSBCU_OK) return rc;
     if (sink.cands) CK(cudaMemcpyAsync(h->d_carry_prev, h->d_carry, kOverlap * sizeof(uint16_t), cudaMemcpyDeviceToDevice, h->stream));
     if (sc16_host) CK(launch_carry_mag(reinterpret_cast<const uint16_t *>(h->d_iq), n, h->d_carry, h->stream));
     else CK(launch_carry(d_iq, n, h->d_carry, h->d_tab, h->stream));
-    st.scan_launches += 1;
+    h->stats.scan_launches += 1;
     CK(cudaStreamSynchronize(h->stream));
-    if (from_host && nchunks) { cudaEventElapsedTime(&ms_h2d, h->ev_h2d[0], h->ev_h2d[1]); st.ms_h2d += ms_h2d; }
-    st.samples += n;
+    CK(cudaStreamSynchronize(h->post_stream));
+    if (from_host && nchunks) { float ms = 0.f; cudaEventElapsedTime(&ms, h->ev_h2d[0], h->ev_h2d[1]); h->stats.ms_h2d += ms; }
+    h->stats.samples += n;
     h->stream_pos += n;
     return ADSBCU_OK;
 }
 
-int feed_common(adsbcu_handle *h, const uint8_t *iq, bool on_device, size_t nsamples, adsbcu_msg *out, size_t cap,
-                size_t *n_out)
+// accepted messages of a feed: where the finish kernel writes them
+struct OutTarget {
+    adsbcu_msg *dev = nullptr;        // device-visible address
+    bool direct = false;              // the caller's out[] itself (pinned memory): nothing to copy afterwards
+};
+
+int prepare_out(adsbcu_handle *h, adsbcu_msg *out, size_t cap, OutTarget &t)
+{
+    t = OutTarget{};
+    if (!cap) return ADSBCU_OK;
+    // out[] in pinned (cudaHostAlloc / cudaHostRegister) memory: the GPU writes the messages there itself
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, out) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer &&
+        (reinterpret_cast<uintptr_t>(at.devicePointer) & 7u) == 0) {
+        t.dev = static_cast<adsbcu_msg *>(at.devicePointer);
+        t.direct = true;
+        return ADSBCU_OK;
+    }
+    cudaGetLastError();
+    if (h->msgs_cap < cap) {
+        if (h->h_msgs) { cudaFreeHost(h->h_msgs); h->h_msgs = nullptr; h->msgs_cap = 0; }
+        CK(cudaHostAlloc(&h->h_msgs, cap * sizeof(adsbcu_msg), cudaHostAllocMapped));
+        CK(cudaHostGetDevicePointer(&h->d_msgs, h->h_msgs, 0));
+        h->msgs_cap = cap;
+    }
+    t.dev = h->d_msgs;
+    return ADSBCU_OK;
+}
+
+// Demodulate nsamples (device memory if on_device, else host memory; int16 pairs if sc16) that continue the stream.
+int feed_common(adsbcu_handle *h, const uint8_t *iq, bool on_device, const int16_t *sc16, int q11, size_t nsamples, adsbcu_msg *out,
+                size_t cap, size_t *n_out)
 {
     CK(cudaSetDevice(h->device));
     h->stats = adsbcu_stats{};
+    OutTarget target;
+    if (const int r = prepare_out(h, out, cap, target); r != ADSBCU_OK) return r;
+    CK(launch_state_begin_feed(h->d_state, 1, h->post_stream));
     Sink sink{out, cap, 0, false};
-    size_t done = 0;
     // a feed larger than max_feed_samples is cut into takes (multiples of 8 samples keep device pointers 16 B aligned)
     const size_t max_take = h->cfg.max_feed_samples & ~size_t(7);
-    while (done < nsamples) {
+    for (size_t done = 0; done < nsamples;) {
         const size_t take = std::min<size_t>(nsamples - done, max_take);
-        const int r = on_device ? run_feed(h, iq + 2 * done, nullptr, uint32_t(take), sink)
-                                : run_feed(h, h->d_iq, iq + 2 * done, uint32_t(take), sink);
+        const int r = sc16        ? run_feed(h, h->d_iq, nullptr, uint32_t(take), sink, target.dev, cap, sc16 + 2 * done, q11)
+                      : on_device ? run_feed(h, iq + 2 * done, nullptr, uint32_t(take), sink, target.dev, cap)
+                                  : run_feed(h, h->d_iq, iq + 2 * done, uint32_t(take), sink, target.dev, cap);
         if (r != ADSBCU_OK) return r;
         done += take;
     }
-    h->stats.messages = sink.n;
-    if (n_out) *n_out = sink.n;
-    if (sink.overflow) { h->error = "out[] too small for the accepted messages"; return ADSBCU_ERR_OVERFLOW; }
+    const size_t n = size_t(h->stats.messages);
+    if (!target.direct && n) std::memcpy(out, h->h_msgs, std::min(n, cap) * sizeof(adsbcu_msg));
+    if (n_out) *n_out = n;
+    if (n > cap) { h->error = "out[] too small for the accepted messages"; return ADSBCU_ERR_OVERFLOW; }
     return ADSBCU_OK;
 }
 
 }  // namespace
+
+// No C++ exception crosses the C ABI: allocation failures inside the library become ADSBCU_ERR_NOMEM
+#define ABI_GUARD_BEGIN try {
+#define ABI_GUARD_END(h) } catch (const std::bad_alloc &) { if (h) (h)->error = "out of host memory"; return ADSBCU_ERR_NOMEM; } \
+                         catch (...) { if (h) (h)->error = "unexpected C++ exception"; return ADSBCU_ERR_NOMEM; }
 
 extern "C" {
 
@@ -552,6 +573,8 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
 {
     if (!out) return ADSBCU_ERR_ARG;
     *out = nullptr;
+    adsbcu_handle *h = nullptr;
+    ABI_GUARD_BEGIN
     adsbcu_config c{};
     c.struct_size = sizeof(c); c.fix_df = 1;
     if (cfg) {
@@ -562,6 +585,8 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
     if (!c.block_samples) c.block_samples = 131072;
     if (!c.max_feed_samples) c.max_feed_samples = 1u << 24;
     if (c.block_samples < 1024) { g_create_error = "block_samples too small"; return ADSBCU_ERR_ARG; }
+    if (c.max_feed_samples < 4096) { g_create_error = "max_feed_samples must be at least 4096"; return ADSBCU_ERR_ARG; }
+    c.max_feed_samples = (c.max_feed_samples + 7u) & ~7u;
 
     if (c.device == -1) {              // merge-only handle: ICAO filter + skip state for adsbcu_1090_resolve, no CUDA
         adsbcu_handle *m = new (std::nothrow) adsbcu_handle;
@@ -576,11 +601,11 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
         g_create_error = "no usable CUDA device (this library has no CPU fallback)";
         return ADSBCU_ERR_NO_DEVICE;
     }
-    adsbcu_handle *h = new (std::nothrow) adsbcu_handle;
+    h = new (std::nothrow) adsbcu_handle;
     if (!h) return ADSBCU_ERR_NOMEM;
     h->cfg = c;
     h->device = c.device;
-    auto fail = [&](int code) { g_create_error = h->error; free_all(h); delete h; return code; };
+    auto fail = [&](int code) { g_create_error = h->error; free_all(h); delete h; h = nullptr; return code; };
 #define CKC(call) do { if (!cuda_ok(h, (call), #call)) return fail(ADSBCU_ERR_CUDA); } while (0)
     CKC(cudaSetDevice(h->device));
     cudaDeviceProp prop{};
@@ -596,7 +621,12 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
     }
     for (auto &e : h->ev_h2d) CKC(cudaEventCreate(&e));
     for (auto &e : h->ev_up) CKC(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (Slot &s : h->slot)
+        for (auto &e : s.ev) CKC(cudaEventCreate(&e));
     CKC(init_kernels());
+    CKC(init_front());
+    CKC(init_messages());
+    CKC(init_finish());
 
     DevTables *tab = new (std::nothrow) DevTables;
     if (!tab) return fail(ADSBCU_ERR_NOMEM);
@@ -606,45 +636,43 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
     delete tab;
     CKC(e);
     CKC(launch_build_lut(h->d_tab, h->stream));
+    CKC(launch_build_lutf(h->d_tab, h->stream));
 
-    // chunk geometry: every scan group (kGroups per SM) owns up to max_tps consecutive tiles of a chunk
-    uint32_t tps = 16;
-    if (const char *e = std::getenv("ADSBCU_TILES_PER_SEG")) tps = uint32_t(std::max(1, std::atoi(e)));
-    if (const char *e = std::getenv("ADSBCU_SKEW")) h->skew = uint32_t(std::atoi(e));
-    if (const char *e = std::getenv("ADSBCU_THREAD_TPS")) h->thread_tps = uint32_t(std::max(1, std::atoi(e)));
-    if (const char *e = std::getenv("ADSBCU_WAIT")) h->wait_policy = std::atoi(e);
-    if (const char *e = std::getenv("ADSBCU_OVERLAP")) h->overlap = std::atoi(e) != 0;
-    if (const char *e = std::getenv("ADSBCU_RESOLVER_THREAD")) h->resolver_thread = std::atoi(e) != 0;
-    if (const char *e = std::getenv("ADSBCU_HOST_TPS")) h->host_tps = uint32_t(std::max(1, std::atoi(e)));
-    if (const char *e = std::getenv("ADSBCU_SKEW_NS")) h->skew_ns = uint32_t(std::max(0, std::atoi(e)));
+    // geometry: the front kernel leaves `spare` SMs to the order / level kernels of the previous chunk; every front
+    // warp (kFWarps per SM) owns up to max_tps warp-tiles of a chunk
+    uint32_t tps = 16, spare = h->sm_count > 16 ? 4 : 0;
+    if (const char *v = std::getenv("ADSBCU_TILES_PER_SEG")) tps = uint32_t(std::max(1, std::atoi(v)));
+    if (const char *v = std::getenv("ADSBCU_SPARE_SMS")) spare = uint32_t(std::max(0, std::min(h->sm_count - 1, std::atoi(v))));
+    if (const char *v = std::getenv("ADSBCU_RES_TPS")) h->res_tps = uint32_t(std::max(1, std::atoi(v)));
+    if (const char *v = std::getenv("ADSBCU_HOST_TPS")) h->host_tps = uint32_t(std::max(1, std::atoi(v)));
+    if (const char *v = std::getenv("ADSBCU_LEVEL_GRID")) h->level_grid = uint32_t(std::max(1, std::atoi(v)));
+    if (const char *v = std::getenv("ADSBCU_RESOLVE_SEQ")) h->force_sequential = std::atoi(v) != 0;
     const size_t nmax = c.max_feed_samples;
-    h->nseg = uint32_t(h->sm_count) * uint32_t(kGroups);
-    h->unit_positions = h->nseg * uint32_t(kTile);
+    h->nseg = uint32_t(h->sm_count) - spare;
+    h->unit_positions = h->nseg * uint32_t(kFWarps) * uint32_t(kWTile);
+    h->msg_grid = uint32_t(h->sm_count) * 6;
+    if (const char *v = std::getenv("ADSBCU_MSG_GRID")) h->msg_grid = uint32_t(std::max(1, std::atoi(v)));
     h->max_tps = uint32_t(std::max<size_t>(1, std::min<size_t>(tps, (nmax + h->unit_positions - 1) / h->unit_positions)));
-    const size_t chunk = size_t(h->unit_positions) * h->max_tps;
-    // list sizes: 1 (position, phase) record per 8 positions of a segment (Gaussian noise keeps 1 per 90),
-    // 1 evaluated record per 96 positions of a chunk (real traffic needs 1 per ~800); overflow is reported, never silent
-    h->seg_cap = uint32_t(std::max<size_t>(2048, chunk / h->nseg / 8));
-    h->full_cap = uint32_t(std::max<size_t>(1u << 13, chunk / 96));
+    h->max_tps = std::max(h->max_tps, std::min(std::max(h->res_tps, h->host_tps), uint32_t((nmax + h->unit_positions - 1) / h->unit_positions)));
     CKC(cudaMalloc(&h->d_bitmap, (size_t(1) << 25) / 8));
     CKC(cudaMemset(h->d_bitmap, 0, (size_t(1) << 25) / 8));
     CKC(cudaMalloc(&h->d_carry, kOverlap * sizeof(uint16_t) + 32));
     CKC(cudaMemset(h->d_carry, 0, kOverlap * sizeof(uint16_t) + 32));
     CKC(cudaMalloc(&h->d_iq, nmax * 2 + 64));
-    for (Slot &s : h->slot) {
-        CKC(cudaMalloc(&s.d_seg, size_t(h->nseg) * h->seg_cap * sizeof(PhaseRec)));
-        CKC(cudaMalloc(&s.d_seg_count, size_t(h->nseg) * sizeof(uint32_t)));
-        CKC(cudaMalloc(&s.d_ctr, sizeof(ChunkCounters)));
-        CKC(cudaHostAlloc(&s.h_ctr, sizeof(ChunkCounters), cudaHostAllocMapped));
-        std::memset(s.h_ctr, 0, sizeof(ChunkCounters));
-        CKC(cudaHostGetDevicePointer(reinterpret_cast<void **>(&s.h_ctr_dev), s.h_ctr, 0));
-        CKC(cudaHostAlloc(&s.h_full, size_t(h->full_cap) * sizeof(FullRec), cudaHostAllocMapped));
-        CKC(cudaHostGetDevicePointer(&s.d_full, s.h_full, 0));
-        for (int k = 0; k < 4; ++k) CKC(cudaEventCreate(&s.ev[k]));
-    }
+    CKC(cudaMalloc(&h->d_state, sizeof(StreamState)));
+    CKC(launch_state_reset(h->d_state, 1, 1, h->stream));
+    CKC(cudaHostAlloc(&h->h_word, 64, cudaHostAllocMapped));
+    CKC(cudaHostGetDevicePointer(&h->d_word, h->h_word, 0));
+    if (alloc_slots(h) != ADSBCU_OK) return fail(ADSBCU_ERR_CUDA);
+    CKC(cudaStreamSynchronize(h->stream));
 #undef CKC
     *out = h;
     return ADSBCU_OK;
+    } catch (...) {
+        if (h) { free_all(h); delete h; }
+        g_create_error = "out of host memory";
+        return ADSBCU_ERR_NOMEM;
+    }
 }
 
 void adsbcu_destroy(adsbcu_handle *h)
@@ -659,21 +687,14 @@ void adsbcu_destroy(adsbcu_handle *h)
 int adsbcu_1090_reset(adsbcu_handle *h, int clear_filter)
 {
     if (!h) return ADSBCU_ERR_ARG;
-    if (h->host_only) {
-        if (clear_filter) h->filter.clear();
-        h->stream_pos = 0; h->has_last = false; h->last_a = h->last_lme = 0;
-        return ADSBCU_OK;
-    }
+    if (clear_filter) h->filter.clear();
+    h->stream_pos = 0; h->has_last = false; h->last_a = h->last_lme = 0;
+    if (h->host_only) return ADSBCU_OK;
     CK(cudaSetDevice(h->device));
     CK(cudaMemsetAsync(h->d_carry, 0, kOverlap * sizeof(uint16_t), h->stream));
-    if (clear_filter) {
-        h->filter.clear();
-        CK(cudaMemsetAsync(h->d_bitmap, 0, (size_t(1) << 25) / 8, h->stream));
-    }
+    if (clear_filter) CK(cudaMemsetAsync(h->d_bitmap, 0, (size_t(1) << 25) / 8, h->stream));
+    CK(launch_state_reset(h->d_state, clear_filter, 1, h->stream));
     CK(cudaStreamSynchronize(h->stream));
-    h->stream_pos = 0;
-    h->has_last = false;
-    h->last_a = h->last_lme = 0;
     return ADSBCU_OK;
 }
 
@@ -687,7 +708,9 @@ int adsbcu_1090_feed_device(adsbcu_handle *h, const uint8_t *iq_dev, size_t nsam
         h->error = "bad argument (null or misaligned pointer)";
         return ADSBCU_ERR_ARG;
     }
-    return feed_common(h, iq_dev, true, nsamples, out, cap, n_out);
+    ABI_GUARD_BEGIN
+    return feed_common(h, iq_dev, true, nullptr, 0, nsamples, out, cap, n_out);
+    ABI_GUARD_END(h)
 }
 
 int adsbcu_1090_feed(adsbcu_handle *h, const uint8_t *iq, size_t nsamples, adsbcu_msg *out, size_t cap, size_t *n_out)
@@ -696,7 +719,22 @@ int adsbcu_1090_feed(adsbcu_handle *h, const uint8_t *iq, size_t nsamples, adsbc
     if (n_out) *n_out = 0;
     NEED_DEVICE(h);
     if ((!iq && nsamples) || (!out && cap)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
-    return feed_common(h, iq, false, nsamples, out, cap, n_out);
+    ABI_GUARD_BEGIN
+    return feed_common(h, iq, false, nullptr, 0, nsamples, out, cap, n_out);
+    ABI_GUARD_END(h)
+}
+
+int adsbcu_1090_feed_sc16(adsbcu_handle *h, const int16_t *iq, size_t nsamples, int q11, adsbcu_msg *out, size_t cap, size_t *n_out)
+{
+    if (!h) return ADSBCU_ERR_ARG;
+    if (n_out) *n_out = 0;
+    NEED_DEVICE(h);
+    if ((!iq && nsamples) || (!out && cap)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
+    ABI_GUARD_BEGIN
+    CK(cudaSetDevice(h->device));
+    if (!h->d_sc16) CK(cudaMalloc(&h->d_sc16, size_t(h->cfg.max_feed_samples) * 4 + 64));
+    return feed_common(h, nullptr, false, iq, q11 ? 1 : 0, nsamples, out, cap, n_out);
+    ABI_GUARD_END(h)
 }
 
 int adsbcu_1090_magnitude(adsbcu_handle *h, const uint8_t *iq, size_t nsamples, uint16_t *mag_out)
@@ -723,22 +761,31 @@ int adsbcu_1090_filter_add(adsbcu_handle *h, uint32_t addr)
     if (!h) return ADSBCU_ERR_ARG;
     h->filter.add(addr);
     if (h->host_only) return ADSBCU_OK;
-    // keep the device-side superset consistent: queries use the 24-bit address (+ NT table bit)
-    if (!(addr & kNonIcao)) {
-        const uint32_t bi = (addr & 0xFFFFFFu) | ((addr & kNtFlag) ? (1u << 24) : 0u);
-        uint32_t word = 0;
-        CK(cudaSetDevice(h->device));
-        CK(cudaMemcpy(&word, h->d_bitmap + (bi >> 5), 4, cudaMemcpyDeviceToHost));
-        word |= 1u << (bi & 31);
-        CK(cudaMemcpy(h->d_bitmap + (bi >> 5), &word, 4, cudaMemcpyHostToDevice));
-    }
+    CK(cudaSetDevice(h->device));
+    CK(launch_filter_add(h->d_state, h->d_bitmap, addr, h->stream));      // table insert + the scan's address set, one thread
+    CK(cudaStreamSynchronize(h->stream));
     return ADSBCU_OK;
 }
 
 int adsbcu_1090_filter_test(adsbcu_handle *h, uint32_t addr)
 {
     if (!h) return ADSBCU_ERR_ARG;
-    return h->filter.test(addr) ? 1 : 0;
+    if (h->host_only) return h->filter.test(addr) ? 1 : 0;
+    CK(cudaSetDevice(h->device));
+    CK(launch_filter_test(h->d_state, addr, h->d_word, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return *reinterpret_cast<volatile uint32_t *>(h->h_word) ? 1 : 0;
+}
+
+int adsbcu_1090_filter_expire(adsbcu_handle *h)
+{
+    if (!h) return ADSBCU_ERR_ARG;
+    h->filter.expire();
+    if (h->host_only) return ADSBCU_OK;
+    CK(cudaSetDevice(h->device));
+    CK(launch_filter_expire(h->d_state, h->d_bitmap, ADSBCU_KNOWN_WORDS, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return ADSBCU_OK;
 }
 
 int adsbcu_1090b_feed(adsbcu_handle *h, const uint8_t *iq, size_t nbytes, adsbcu_msg_b *out, size_t cap, size_t *n_out)
@@ -843,6 +890,7 @@ int adsbcu_1090_scan_candidates(adsbcu_handle *h, const uint8_t *iq, size_t nsam
         h->error = "bad argument (null or misaligned pointer, or nsamples > max_feed_samples)";
         return ADSBCU_ERR_ARG;
     }
+    ABI_GUARD_BEGIN
     CK(cudaSetDevice(h->device));
     if (!h->d_deferred) {
         // noise leaves ~1 unknown-address record per 100 positions with --fix; dense traffic more
@@ -852,19 +900,27 @@ int adsbcu_1090_scan_candidates(adsbcu_handle *h, const uint8_t *iq, size_t nsam
         CK(cudaMalloc(&h->d_carry_prev, kOverlap * sizeof(uint16_t) + 32));
         CK(cudaMalloc(&h->d_known_tmp, size_t(ADSBCU_KNOWN_WORDS) * sizeof(uint32_t)));
     }
-    CK(cudaMemsetAsync(h->d_n_deferred, 0, sizeof(uint32_t), h->stream));
+    for (Slot &s : h->slot)
+        if (!s.h_cand) {
+            CK(cudaHostAlloc(&s.h_cand, size_t(h->full_cap) * sizeof(FullRec), cudaHostAllocMapped));
+            CK(cudaHostGetDevicePointer(&s.d_cand, s.h_cand, 0));
+        }
+    CK(cudaMemsetAsync(h->d_n_deferred, 0, sizeof(uint32_t), h->post_stream));
+    CK(launch_state_begin_feed(h->d_state, 1, h->post_stream));
     h->stats = adsbcu_stats{};
     Sink sink{nullptr, cap, 0, false, out};
     h->last_base = h->stream_pos;
     h->last_n = uint32_t(nsamples);
     h->last_iq = on_device ? iq : h->d_iq;
     if (nsamples) {
-        const int r = on_device ? run_feed(h, iq, nullptr, uint32_t(nsamples), sink) : run_feed(h, h->d_iq, iq, uint32_t(nsamples), sink);
+        const int r = on_device ? run_feed(h, iq, nullptr, uint32_t(nsamples), sink, nullptr, 0)
+                                : run_feed(h, h->d_iq, iq, uint32_t(nsamples), sink, nullptr, 0);
         if (r != ADSBCU_OK) return r;
     }
     if (n_out) *n_out = sink.n;
     if (sink.overflow) { h->error = "out[] too small for the candidates"; return ADSBCU_ERR_OVERFLOW; }
     return ADSBCU_OK;
+    ABI_GUARD_END(h)
 }
 
 int adsbcu_1090_known_export(adsbcu_handle *h, uint32_t *words)
@@ -895,14 +951,17 @@ int adsbcu_1090_revive(adsbcu_handle *h, adsbcu_cand *out, size_t cap, size_t *n
     if (n_out) *n_out = 0;
     NEED_DEVICE(h);
     if (!h->d_deferred || !h->last_n) return ADSBCU_OK;
+    ABI_GUARD_BEGIN
     CK(cudaSetDevice(h->device));
     Slot &s = h->slot[0];
+    // the parked records whose address another shard announced are sliced again from the samples (the planes of
+    // their chunk are gone): evaluate_kernel, one warp per record
     ScanArgs a{};
     a.iq = h->last_iq; a.carry_mag = h->d_carry_prev; a.nsamples = h->last_n;
     a.pos_begin = 0; a.pos_end = h->last_n;
     a.tab = h->d_tab; a.bitmap = h->d_bitmap;
-    a.seg = s.d_seg; a.seg_cap = h->seg_cap; a.nseg = h->nseg; a.seg_count = s.d_seg_count;
-    a.full = s.d_full; a.full_cap = h->full_cap; a.ctr = s.d_ctr;
+    a.seg = s.d_pend; a.seg_cap = h->pend_cap; a.nseg = h->nseg; a.seg_count = s.d_pend_count;
+    a.full = s.d_cand; a.full_cap = h->full_cap; a.ctr = s.d_ctr;
     a.deferred = h->d_deferred; a.deferred_cap = h->deferred_cap; a.n_deferred = h->d_n_deferred;
     CK(cudaMemsetAsync(s.d_ctr, 0, sizeof(ChunkCounters), h->stream));
     CK(launch_revive(a, h->stream));
@@ -911,43 +970,21 @@ int adsbcu_1090_revive(adsbcu_handle *h, adsbcu_cand *out, size_t cap, size_t *n
     CK(cudaStreamSynchronize(h->stream));
     const ChunkCounters k = *s.h_ctr;
     if (k.overflow || k.n_full > h->full_cap) { h->error = "revive: candidate list overflow"; return ADSBCU_ERR_OVERFLOW; }
-    std::vector<FullRec> v(s.h_full, s.h_full + k.n_full);
+    std::vector<FullRec> v(s.h_cand, s.h_cand + k.n_full);
     std::sort(v.begin(), v.end(), [](const FullRec &x, const FullRec &y) { return x.pos != y.pos ? x.pos < y.pos : x.phase < y.phase; });
     Sink sink{nullptr, cap, 0, false, out};
     copy_candidates(v.data(), v.size(), h->last_base, sink);
     if (n_out) *n_out = sink.n;
     if (sink.overflow) { h->error = "out[] too small for the revived candidates"; return ADSBCU_ERR_OVERFLOW; }
     return ADSBCU_OK;
+    ABI_GUARD_END(h)
 }
 
 int adsbcu_1090_resolve(adsbcu_handle *h, const adsbcu_cand *cands, size_t n, adsbcu_msg *out, size_t cap, size_t *n_out)
 {
     if (!h || (!cands && n) || (!out && cap)) return ADSBCU_ERR_ARG;
     Sink sink{out, cap, 0, false};
-    resolve(h, cands, n, 0, sink);
-    if (n_out) *n_out = sink.n;
-    if (sink.overflow) { h->error = "out[] too small for the accepted messages"; return ADSBCU_ERR_OVERFLOW; }
-    return ADSBCU_OK;
-}
-
-int adsbcu_1090_feed_sc16(adsbcu_handle *h, const int16_t *iq, size_t nsamples, int q11, adsbcu_msg *out, size_t cap, size_t *n_out)
-{
-    if (!h) return ADSBCU_ERR_ARG;
-    if (n_out) *n_out = 0;
-    NEED_DEVICE(h);
-    if ((!iq && nsamples) || (!out && cap)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
-    CK(cudaSetDevice(h->device));
-    if (!h->d_sc16) CK(cudaMalloc(&h->d_sc16, size_t(h->cfg.max_feed_samples) * 4 + 64));
-    h->stats = adsbcu_stats{};
-    Sink sink{out, cap, 0, false};
-    const size_t max_take = h->cfg.max_feed_samples & ~size_t(7);
-    for (size_t done = 0; done < nsamples;) {
-        const size_t take = std::min<size_t>(nsamples - done, max_take);
-        const int r = run_feed(h, h->d_iq, nullptr, uint32_t(take), sink, iq + 2 * done, q11 ? 1 : 0);
-        if (r != ADSBCU_OK) return r;
-        done += take;
-    }
-    h->stats.messages = sink.n;
+    resolve_host(h, cands, n, sink);
     if (n_out) *n_out = sink.n;
     if (sink.overflow) { h->error = "out[] too small for the accepted messages"; return ADSBCU_ERR_OVERFLOW; }
     return ADSBCU_OK;

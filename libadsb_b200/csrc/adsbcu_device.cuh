@@ -334,6 +334,99 @@ __device__ __forceinline__ Classified classify(const Frame &in, uint32_t xs, uin
     return r;
 }
 
+// ---- symbol planes -> message bits (front kernel layout: planes[c][run] holds 10 decisions, MSB first) ----------
+// The message whose first data symbol is at time t0 = 5 * (staged sample) + phase occupies the bits n0 .. n0+111 of
+// plane c = t0 mod 12 (n0 = t0 div 12).  `pf` points at the field holding bit n0, `r` = n0 mod 10.  The 10-bit fields
+// from there on are repacked into a dense bit stream (every field is < 1024, so the shifted fields add up without
+// overlap) and shifted to the message's first bit.  Also returns both CRC-24 syndromes.
+__device__ __forceinline__ void slice_planes(const uint16_t *pf, uint32_t r, bool is_long, const uint32_t *crcb, uint32_t fixable_short,
+                                             uint32_t (&M)[4], uint32_t &xs, uint32_t &xl)
+{
+    const uint32_t f3 = pf[3], f6 = pf[6], f9 = pf[9];
+    const uint32_t w0 = (uint32_t(pf[0]) << 22) + (uint32_t(pf[1]) << 12) + (uint32_t(pf[2]) << 2) + (f3 >> 8);
+    const uint32_t w1 = (f3 << 24) + (uint32_t(pf[4]) << 14) + (uint32_t(pf[5]) << 4) + (f6 >> 6);
+    const uint32_t w2 = (f6 << 26) + (uint32_t(pf[7]) << 16) + (uint32_t(pf[8]) << 6) + (f9 >> 4);
+    M[0] = __funnelshift_l(w1, w0, r); M[1] = __funnelshift_l(w2, w1, r); M[2] = 0u; M[3] = 0u;
+    xs = 0; xl = 0;
+    if (is_long) {
+        const uint32_t f12 = pf[12];
+        const uint32_t w3 = (f9 << 28) + (uint32_t(pf[10]) << 18) + (uint32_t(pf[11]) << 8) + (f12 >> 2);
+        M[2] = __funnelshift_l(w3, w2, r);
+        M[3] = __funnelshift_l(f12 << 30, w3, r) & 0xFFFF0000u;
+        xl = crc_long(M, crcb);
+        // the 56-bit syndrome is also needed when a short DF was sliced long (DF0/DF5 are within two bit flips of
+        // DF17/18, so --fix-2bit slices them to 14 bytes but scores them as 56-bit Address/Parity replies)
+        if (!(M[0] >> 31) || (fixable_short & (1u << (M[0] >> 27)))) xs = crc_short(M, crcb);
+    } else {
+        M[1] &= 0xFFFFFF00u;
+        xs = crc_short(M, crcb);
+    }
+}
+
+// The evaluated record of one kept (position, phase): what decodeModesMessage fills before the field decode
+// (mode_s.c:520-626) plus the keys of the two filter calls.  signal_level is filled in by the caller.
+__device__ __forceinline__ void fill_rec(FullRec &q, uint32_t pos, uint32_t ph, const Frame &f, const Classified &c)
+{
+    q.pos = pos;
+    q.phase = uint8_t(ph);
+    q.kind = uint8_t(c.keep ? c.kind : K_COUNT);
+    q.corrections = int8_t(c.corrections < 0 ? 0 : c.corrections);
+    q.msgtype = uint8_t(frame_df(c.fixed));
+#pragma unroll
+    for (int b = 0; b < 14; ++b) {
+        q.verbatim[b] = uint8_t(frame_byte(f, b));
+        q.msg[b] = uint8_t(frame_byte(c.fixed, b));
+    }
+    q.crc = c.crc;
+    q.test_key = c.test_key;
+    q.add_key = kUnchecked;
+    const uint32_t aa = frame_aa(c.fixed);
+    switch (q.msgtype) {
+    case 11: q.addr = aa; if (c.kind == K_DF11_ACQ_0) q.add_key = aa; break;
+    case 17: q.addr = aa; if (c.kind == K_DF17_0) q.add_key = aa; break;
+    case 18:
+        q.addr = aa | (df18_non_icao(c.fixed) ? kNonIcao : 0u);
+        if (c.kind == K_DF18_0) q.add_key = q.addr | kNtFlag;
+        break;
+    default: q.addr = c.crc; break;
+    }
+    q.signal_level = 0.0;
+}
+
+// mean squared magnitude over the signal window of the message at start position `pos` (demod_2400.c:382-403):
+// IEEE double divisions, the same on the device as on the host.  One warp per record.
+__device__ __forceinline__ double signal_level_warp(const ChunkArgs &a, uint32_t pos, uint32_t df_uncorrected, int lane)
+{
+    const int siglen = (df_uncorrected & 16u) ? 268 : 134;
+    const int64_t xb = int64_t(pos) - kOverlap + 19;               // feed sample of m[j+19]
+    const int64_t n = a.nsamples;
+    unsigned long long acc = 0;
+    if (!a.mag_in && xb >= 0 && xb + 288 <= n) {
+        // the whole window lies inside the feed: nine independent sample loads per lane, then nine LUT gathers
+        const uint16_t *s16 = reinterpret_cast<const uint16_t *>(a.iq) + xb;
+        uint32_t s[9];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) s[k] = lane + 32 * k < siglen ? uint32_t(s16[lane + 32 * k]) : 0u;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) {
+            const uint32_t v = lane + 32 * k < siglen ? uint32_t(a.tab->mag_lut_full[lutf_index(s[k])]) : 0u;
+            acc += uint64_t(v * v);
+        }
+    } else {
+        for (int i = lane; i < siglen; i += 32) {
+            const int64_t x = xb + i;
+            uint32_t v = 0;
+            if (x < 0) v = (x + kOverlap >= 0) ? a.carry_mag[x + kOverlap] : 0u;
+            else if (x < n) v = a.mag_in ? uint32_t(a.mag_in[x])
+                                         : uint32_t(a.tab->mag_lut_full[lutf_index(uint32_t(a.iq[2 * x]) | (uint32_t(a.iq[2 * x + 1]) << 8))]);
+            acc += uint64_t(v * v);
+        }
+    }
+#pragma unroll
+    for (int d = 16; d; d >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, d);
+    return double(acc) / 65535.0 / 65535.0 / double(siglen);
+}
+
 // bitmap of addresses that may ever be in the filter: bit index = 24-bit address (+2^24 for the NT table)
 __device__ __forceinline__ uint32_t bitmap_index(uint32_t key) { return (key & 0xFFFFFFu) | ((key & kNtFlag) ? (1u << 24) : 0u); }
 

@@ -18,6 +18,7 @@
 #define ADSBCU_DYN_SMEM(name) extern __shared__ __align__(16) unsigned char name[]
 #endif
 
+struct adsbcu_msg;
 namespace adsbcu {
 
 constexpr int      kOverlap       = 326;      // dump1090.c:159 trailing_samples
@@ -126,6 +127,7 @@ struct DevTables {
                                  // table (tables.c:9-41) in the bank-swizzled layout of lut_offset(); filled on the
                                  // device by build_lut at create time.  Samples outside it (|I-128| > 64: strong
                                  // signals only) take the register path mag_iq().
+    alignas(16) uint16_t mag_lut_full[65536];   // the whole table, element lutf_index(I | Q << 8): front kernel (128 KiB of shared memory)
 };
 
 // Byte offset of magnitude(I, Q) inside mag_lut, for I, Q in [64, 192): [64,192) -> (x & 127) is a bijection
@@ -147,6 +149,9 @@ struct ChunkCounters {
     unsigned int n_full;         // FullRec written by the evaluate kernel
     unsigned int overflow;       // a tile list, a segment or full[] overflowed: results are incomplete
     unsigned int pad;
+    unsigned int n_msgs;         // messages the ordered pass accepted in this chunk
+    unsigned int pad2;
+    unsigned long long msg_base; // ... and how many the feed had accepted before it
 };
 
 // One chunk = a contiguous range of start positions of the current feed.  Position p (feed-relative,
@@ -176,6 +181,82 @@ struct ScanArgs {
 };
 
 void build_tables(DevTables &t, int nfix_crc, int fix_df);
+
+// ---- round-2 pipeline: front kernel -> message kernel -> finish kernel --------------------------------------
+// front kernel geometry: kFWarps autonomous warps per CTA, a lane owns kFRun consecutive samples of a warp-tile
+constexpr int kFRun = 24, kFWarps = 32;
+constexpr int kWTile = kFRun * 32;            // 768 samples staged per warp-tile == start positions per warp-tile
+constexpr int kFLead = 2;                     // staged index of a tile's first start position (16 B alignment of the I/Q vectors)
+constexpr int kFHalo = 24;                    // magnitudes staged past the tile: the preamble test looks 18 samples ahead
+constexpr int kFNeed = 296;                   // samples past a chunk's last start position whose slicer decisions its messages use
+                                              // (lead 2 + 19 + 269 data samples + 3 correlator taps, rounded up)
+// element of mag_lut_full for the 16-bit sample s = I | Q << 8: three low bits of Q are xor-ed into index bits 3..5.
+// The shared-memory bank is index bits 1..5 and bit 0 picks the half of the bank word, so an 8 x 8 window of (I, Q)
+// around the DC point maps onto 64 different (bank, half) slots: the gather of near-DC noise is almost conflict-free
+__host__ __device__ inline uint32_t lutf_index(uint32_t s) { return s ^ ((s >> 5) & 0x38u); }
+
+// One chunk of a feed.  Position p (feed-relative, the reference's padded mag_buf coordinate) looks at feed samples
+// p-326 .. p-326+289.  Segment g of `nseg` (one front-kernel CTA) owns a contiguous run of the chunk's warp-tiles;
+// segments in index order are the chunk in stream order.
+struct ChunkArgs {
+    const uint8_t  *iq;          // feed samples (device), 16 B aligned
+    const uint16_t *mag_in;      // or, for SC16 / SC16Q11 inputs, their magnitudes (then iq is unused); 16 B aligned
+    const uint16_t *carry_mag;   // kOverlap magnitudes preceding the feed (zeros at stream start)
+    uint32_t        nsamples;    // feed samples this chunk may read (a host feed is uploaded chunk by chunk)
+    uint32_t        pos_begin, pos_end;   // this chunk's start positions; pos_begin is a multiple of 8
+    const DevTables *tab;
+    uint32_t       *bitmap;      // 2 x 2^24 bits: [plain | NT] addresses that may enter the filter
+    uint32_t        nseg;
+    uint16_t       *planes;      uint32_t plane_stride;   // [12][plane_stride] 10-bit fields, field index = chunk-local (sample + kFLead) / 24
+    uint32_t       *pre;         uint32_t pre_cap;   uint32_t *pre_count;    // [nseg][pre_cap] confirmed preambles, chunk-local positions
+    PhaseRec       *pend;        uint32_t pend_cap;  uint32_t *pend_count;   // [nseg][pend_cap] parked records (address not announced yet)
+    FullRec        *rec;         uint32_t rec_cap;   uint32_t *rec_count;    // [nseg][rec_cap] evaluated records, unordered inside a segment
+    FullRec        *ordered;     uint32_t full_cap;  // the chunk's records in stream order (device memory)
+    ChunkCounters  *ctr;
+};
+
+// The reference's ICAO filter (icao_filter.c:23-109) and demodulate2400's carried skip state, device resident.
+constexpr uint32_t kIcaoSlots = 4096, kIcaoEmpty = 0xFFFFFFFFu;
+struct StreamState {
+    uint32_t table[2][kIcaoSlots];   // icao_filter_a / icao_filter_b
+    uint32_t active;                 // index of icao_filter_active
+    uint32_t active_count;           // occupied slots of the active table
+    uint32_t has_last;               // last accepted message: its start and last_message_end, both in
+    uint32_t poison;                 // a chunk of the running feed overflowed: later chunks must leave the state alone
+    uint64_t last_a, last_lme;       // stream coordinates counted from the first (zero) overlap sample
+    uint64_t n_out;                  // messages accepted so far in the running feed
+};
+
+struct FinishArgs {
+    ChunkArgs    c;
+    StreamState *st;
+    struct ::adsbcu_msg *out;    uint64_t out_cap;       // accepted messages of the feed, stream order (device-visible memory)
+    struct ::adsbcu_msg *chunk_msgs;                     // [full_cap] this chunk's accepted messages before their signal level is known
+    uint64_t     feed_base;      // stream coordinate of the feed's position 0
+    uint32_t     block_samples;  // the reference's mag_buf length (skip rule at block boundaries, timestamps)
+    uint32_t     candidates_only;    // sharded scans: stop after the ordered array
+    uint32_t     force_sequential;   // test knob: always take the one-thread replay
+    uint32_t    *ticket;         // phase-1 completion counter
+    uint32_t    *perm;           // [nseg][rec_cap] sorted order of every segment
+    uint32_t    *seg_offset;     // [nseg]
+    uint32_t    *run_start;      // [full_cap + 1]
+    uint4       *view;           // [full_cap] 16-byte view of the ordered records for the ordered pass
+    PhaseRec    *deferred;       uint32_t deferred_cap;  uint32_t *n_deferred;   // sharded scans: still-unknown parked records
+};
+
+// launchers of the round-2 pipeline
+cudaError_t init_front();
+cudaError_t init_finish();
+cudaError_t launch_build_lutf(DevTables *tab, cudaStream_t s);
+cudaError_t init_messages();
+cudaError_t launch_front(const ChunkArgs &a, cudaStream_t s);        // grid = a.nseg
+cudaError_t launch_messages(const ChunkArgs &a, uint32_t grid, cudaStream_t s);
+cudaError_t launch_finish(const FinishArgs &fa, uint32_t level_grid, cudaStream_t s);   // order_kernel (+ level_kernel)
+cudaError_t launch_state_reset(StreamState *st, int clear_filter, int clear_stream, cudaStream_t s);
+cudaError_t launch_state_begin_feed(StreamState *st, int reset_count, cudaStream_t s);
+cudaError_t launch_filter_add(StreamState *st, uint32_t *bitmap, uint32_t addr, cudaStream_t s);
+cudaError_t launch_filter_test(const StreamState *st, uint32_t addr, uint32_t *result_dev, cudaStream_t s);
+cudaError_t launch_filter_expire(StreamState *st, uint32_t *bitmap, uint32_t nwords, cudaStream_t s);
 
 // launchers (adsbcu_kernels.cu)
 cudaError_t init_kernels();                                        // per device, once (opt-in shared memory size)

@@ -36,6 +36,13 @@ def golden():
 @pytest.fixture(scope="session")
 def adsbcu_mod():
     """The CUDA library binding.  Built in-tree if missing; never replaced by a CPU path."""
+    if os.environ.get("ADSBCU_TEST_EMU") == "1":
+        # CPU test suite only (tests/test_emu_kernels.py runs selected -m gpu tests in a subprocess with this set):
+        # the same kernel sources, compiled by g++ against the SIMT emulator of tests/emu.  Test infrastructure;
+        # the product binding has no such switch.
+        sys.path.insert(0, os.path.join(ROOT, "tests", "emu"))
+        import emu_load
+        return emu_load.load_emulated()
     from libadsb_b200 import adsbcu, build
     build.build()
     adsbcu.load()

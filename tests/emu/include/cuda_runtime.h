@@ -213,6 +213,8 @@ static inline float __uint2float_rn(unsigned x) { return float(x); }
 static inline unsigned __float_as_uint(float f) { unsigned u; std::memcpy(&u, &f, 4); return u; }
 static inline float __uint_as_float(unsigned u) { float f; std::memcpy(&f, &u, 4); return f; }
 static inline int __float_as_int(float f) { int u; std::memcpy(&u, &f, 4); return u; }
+static inline long long __double_as_longlong(double d) { long long u; std::memcpy(&u, &d, 8); return u; }
+static inline double __longlong_as_double(long long u) { double d; std::memcpy(&d, &u, 8); return d; }
 static inline size_t __cvta_generic_to_shared(const void *p) { return size_t(p); }
 
 // CUDA's overloaded min/max (mixed signedness promotes to unsigned, like the device headers)
