@@ -92,7 +92,8 @@ struct Slot {
     uint32_t *d_rec_count = nullptr;
     FullRec *d_ordered = nullptr;
     FullRec *h_cand = nullptr, *d_cand = nullptr;     // sharded scans: the ordered array in mapped host memory (allocated on first use)
-    uint32_t *d_perm = nullptr, *d_seg_offset = nullptr, *d_run_start = nullptr, *d_ticket = nullptr;
+    unsigned long long *d_seg_flag = nullptr;
+    uint32_t *d_run_start = nullptr, *d_ticket = nullptr;
     uint4 *d_view = nullptr;
     adsbcu_msg *d_chunk_msgs = nullptr;   // accepted messages of the chunk, before the level kernel finishes them
     ChunkCounters *d_ctr = nullptr;
@@ -124,6 +125,7 @@ struct adsbcu_handle {
     uint32_t nseg = 0, msg_grid = 0, level_grid = 128;
     uint32_t unit_positions = 0, max_tps = 1, host_tps = 4, res_tps = 4;   // chunk = unit_positions * (tiles per segment)
     uint32_t ntiles_max = 0, plane_stride = 0, pre_cap = 0, pend_cap = 0, rec_cap = 0, full_cap = 0;
+    uint32_t chunk_epoch = 0;         // sequence number of the last submitted chunk (never 0 in a launch)
     uint32_t grow = 1;                // list capacities are `grow` times their base size (doubled after an overflow)
     bool force_sequential = false;    // ADSBCU_RESOLVE_SEQ=1: the finish kernel always takes its one-thread replay (tests)
     Slot slot[kSlots];
@@ -174,7 +176,7 @@ void free_slots(adsbcu_handle *h)
 {
     for (Slot &s : h->slot) {
         cudaFree(s.d_planes); cudaFree(s.d_pre); cudaFree(s.d_pre_count); cudaFree(s.d_pend); cudaFree(s.d_pend_count);
-        cudaFree(s.d_rec); cudaFree(s.d_rec_count); cudaFree(s.d_ordered); cudaFree(s.d_perm); cudaFree(s.d_seg_offset);
+        cudaFree(s.d_rec); cudaFree(s.d_rec_count); cudaFree(s.d_ordered); cudaFree(s.d_seg_flag);
         cudaFree(s.d_run_start); cudaFree(s.d_ticket); cudaFree(s.d_ctr); cudaFree(s.d_chunk_msgs); cudaFree(s.d_view);
         if (s.h_cand) cudaFreeHost(s.h_cand);
         if (s.h_ctr) cudaFreeHost(s.h_ctr);
@@ -207,8 +209,8 @@ int alloc_slots(adsbcu_handle *h)
         CK(cudaMalloc(&s.d_rec, size_t(h->nseg) * h->rec_cap * sizeof(FullRec)));
         CK(cudaMalloc(&s.d_rec_count, size_t(h->nseg) * sizeof(uint32_t)));
         CK(cudaMalloc(&s.d_ordered, size_t(h->full_cap) * sizeof(FullRec)));
-        CK(cudaMalloc(&s.d_perm, size_t(h->nseg) * h->rec_cap * sizeof(uint32_t)));
-        CK(cudaMalloc(&s.d_seg_offset, size_t(h->nseg) * sizeof(uint32_t)));
+        CK(cudaMalloc(&s.d_seg_flag, size_t(h->nseg) * sizeof(unsigned long long)));
+        CK(cudaMemset(s.d_seg_flag, 0, size_t(h->nseg) * sizeof(unsigned long long)));
         CK(cudaMalloc(&s.d_run_start, (size_t(h->full_cap) + 1) * sizeof(uint32_t)));
         CK(cudaMalloc(&s.d_chunk_msgs, size_t(h->full_cap) * sizeof(adsbcu_msg)));
         CK(cudaMalloc(&s.d_view, size_t(h->full_cap) * sizeof(uint4)));
@@ -399,7 +401,7 @@ int run_chunks(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, ui
         fa.block_samples = h->cfg.block_samples;
         fa.candidates_only = sink.cands ? 1u : 0u;
         fa.force_sequential = h->force_sequential ? 1u : 0u;
-        fa.ticket = s.d_ticket; fa.perm = s.d_perm; fa.seg_offset = s.d_seg_offset; fa.run_start = s.d_run_start; fa.view = s.d_view;
+        fa.ticket = s.d_ticket; fa.seg_flag = s.d_seg_flag; fa.epoch = ++h->chunk_epoch ? h->chunk_epoch : ++h->chunk_epoch; fa.run_start = s.d_run_start; fa.view = s.d_view;
         if (sink.cands) { fa.deferred = h->d_deferred; fa.deferred_cap = h->deferred_cap; fa.n_deferred = h->d_n_deferred; }
         CK(cudaStreamWaitEvent(h->post_stream, s.ev[2], 0));
         CK(cudaEventRecord(s.ev[3], h->post_stream));

@@ -188,7 +188,7 @@ struct FinishSmem {
 };
 struct SortSmem {
     uint32_t key[kSortCap];
-    uint32_t nrec, is_last;
+    uint32_t nrec, is_last, offset;
 };
 
 __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t *scratch, uint32_t &total)
@@ -253,19 +253,40 @@ __global__ void __launch_bounds__(kXThreads) order_kernel(FinishArgs fa)
         __syncthreads();
         const uint32_t n = min(ss.nrec, a.rec_cap);
         // rank sort by (position, phase): keys are unique
-        uint32_t *perm = fa.perm + size_t(seg) * a.rec_cap;
         if (n > uint32_t(kSortCap)) { if (tid == 0) a.ctr->overflow = 1u; }
-        else {
-            for (uint32_t i = tid; i < n; i += kXThreads) ss.key[i] = ((rec[i].pos - a.pos_begin) << 3) | (rec[i].phase - 4u);
-            __syncthreads();
+        for (uint32_t i = tid; i < n && i < uint32_t(kSortCap); i += kXThreads) ss.key[i] = ((rec[i].pos - a.pos_begin) << 3) | (rec[i].phase - 4u);
+        // Segments in index order are the chunk in stream order: publish this segment's count, sum the counts of the
+        // segments before it (CTAs start in index order, so the ones waited for are running or done), and write the
+        // sorted records straight to their place in the chunk's ordered array.
+        if (tid == 0) {
+            a.rec_count[seg] = n;
+            *reinterpret_cast<volatile unsigned long long *>(&fa.seg_flag[seg]) = (unsigned long long)fa.epoch << 32 | n;
+            ss.offset = 0;
+        }
+        __syncthreads();
+        uint32_t before = 0;
+        for (uint32_t s2 = tid; s2 < seg; s2 += kXThreads) {
+            unsigned long long v;
+            do { v = *reinterpret_cast<volatile unsigned long long *>(&fa.seg_flag[s2]); } while (uint32_t(v >> 32) != fa.epoch);
+            before += uint32_t(v);
+        }
+        before = __reduce_add_sync(0xFFFFFFFFu, before);
+        if (lane == 0 && before) atomicAdd(&ss.offset, before);
+        __syncthreads();
+        const uint32_t offset = ss.offset;
+        if (offset + n > a.full_cap) { if (tid == 0) a.ctr->overflow = 1u; }
+        else if (n <= uint32_t(kSortCap)) {
             for (uint32_t i = tid; i < n; i += kXThreads) {
                 const uint32_t me = ss.key[i];
                 uint32_t rank = 0;
                 for (uint32_t j = 0; j < n; ++j) rank += ss.key[j] < me;
-                perm[rank] = i;
+                const uint4 *src = reinterpret_cast<const uint4 *>(rec + i);
+                uint4 *dst = reinterpret_cast<uint4 *>(a.ordered + offset + rank);
+                const uint4 q0 = src[0], q1 = src[1], q2 = src[2], q3 = src[3];
+                dst[0] = q0; dst[1] = q1; dst[2] = q2; dst[3] = q3;
+                fa.view[offset + rank] = view_of(rec[i]);
             }
         }
-        if (tid == 0) a.rec_count[seg] = n;
         __syncthreads();
         __threadfence();
         if (tid == 0) ss.is_last = atomicAdd(fa.ticket, 1u) == gridDim.x - 1;
@@ -274,33 +295,17 @@ __global__ void __launch_bounds__(kXThreads) order_kernel(FinishArgs fa)
         __threadfence();
     }
 
-    // ================= phase 2: the last CTA -- stream order, ordered pass ======================================
+    // ================= phase 2: the last CTA -- the ordered pass ===============================================
     FinishSmem &sm = *reinterpret_cast<FinishSmem *>(smem_raw);
     StreamState *st = fa.st;
     __syncthreads();
     if (tid == 0) *fa.ticket = 0;                                             // ready for the next chunk
-    // prefix over the segments, compaction into one array in stream order
     uint32_t n_full = 0;
     {
-        const uint32_t per = (a.nseg + kXThreads - 1) / kXThreads;
-        const uint32_t s0 = min(a.nseg, tid * per), s1 = min(a.nseg, s0 + per);
         uint32_t mine = 0;
-        for (uint32_t s = s0; s < s1; ++s) mine += a.rec_count[s];
-        uint32_t off = block_exclusive_scan(mine, sm.scan, n_full);
-        for (uint32_t s = s0; s < s1; ++s) { fa.seg_offset[s] = off; off += a.rec_count[s]; }
-        __syncthreads();
-        if (n_full > a.full_cap) { if (tid == 0) a.ctr->overflow = 1u; n_full = 0; }
-        else {
-            // 16-byte pieces of the 64-byte records, a warp per record quartet
-            for (uint32_t s = warp; s < a.nseg; s += kXThreads / 32) {
-                const uint32_t cnt = a.rec_count[s], base = fa.seg_offset[s];
-                const uint4 *src = reinterpret_cast<const uint4 *>(a.rec + size_t(s) * a.rec_cap);
-                const uint32_t *perm = fa.perm + size_t(s) * a.rec_cap;
-                uint4 *dst = reinterpret_cast<uint4 *>(a.ordered + base);
-                for (uint32_t q = lane; q < 4u * cnt; q += 32) dst[q] = src[4u * perm[q >> 2] + (q & 3u)];
-            }
-        }
-        __syncthreads();
+        for (uint32_t s2 = tid; s2 < a.nseg; s2 += kXThreads) mine += a.rec_count[s2];
+        block_exclusive_scan(mine, sm.scan, n_full);
+        if (n_full > a.full_cap) n_full = 0;                                   // (the overflow flag is set)
     }
     const bool failed = a.ctr->overflow != 0u || st->poison != 0u;
     if (tid == 0) {
@@ -315,9 +320,8 @@ __global__ void __launch_bounds__(kXThreads) order_kernel(FinishArgs fa)
 
     const FullRec *recs = a.ordered;
     const uint32_t n = n_full;
-    // the ordered pass works on a 16-byte view of every record and on the filter tables in shared memory
-    uint4 *view = fa.view;
-    for (uint32_t i = tid; i < n; i += kXThreads) view[i] = view_of(recs[i]);
+    // the ordered pass works on the 16-byte views of the records and on the filter tables in shared memory
+    const uint4 *view = fa.view;
     for (uint32_t i = tid; i < 2u * kIcaoSlots; i += kXThreads) sm.table[0][i] = st->table[0][i];
     const uint32_t active = st->active;
     __syncthreads();
@@ -452,8 +456,23 @@ __global__ void __launch_bounds__(kXThreads) order_kernel(FinishArgs fa)
         sm.cur.key[rank] = sm.next.key[j];
     }
     __syncthreads();
+    // (in the shared copy of the active table, which then replaces the one in global memory)
     if (tid == 0) {
-        for (uint32_t r = 0; r < nnew; ++r) icao_add(st, sm.cur.key[r]);
+        uint32_t *t = sm.table[active];
+        uint32_t added = 0;
+        for (uint32_t r = 0; r < nnew; ++r) {
+            const uint32_t v = sm.cur.key[r], h0 = icao_hash(v);
+            uint32_t h = h0;
+            bool full = false;
+            while (t[h] != kIcaoEmpty && t[h] != v) { h = (h + 1) & (kIcaoSlots - 1); if (h == h0) { full = true; break; } }
+            if (!full && t[h] == kIcaoEmpty) { t[h] = v; ++added; }
+        }
+        sm.total = added;
+    }
+    __syncthreads();
+    if (nnew) for (uint32_t i = tid; i < kIcaoSlots; i += kXThreads) st->table[active][i] = sm.table[active][i];
+    if (tid == 0) {
+        st->active_count += sm.total;
         st->n_out = feed_count + total;
         a.ctr->n_msgs = total;
         a.ctr->msg_base = feed_count;

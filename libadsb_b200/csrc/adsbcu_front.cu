@@ -154,29 +154,25 @@ __global__ void __launch_bounds__(kFWarps * 32, 1) front_kernel(ChunkArgs a)
     uint32_t *pre_out = a.pre + size_t(segi) * a.pre_cap;
     const int64_t nvis = a.nsamples;               // feed samples this chunk may read
 
-    uint4 raw[3], rawh;
-    uint2 rawx;
-    // staged index j of a tile <-> feed sample x0 + j; [lo, hi) are the staged indices that exist in the feed
-    auto valid_range = [&](int64_t x0, int &lo, int &hi) {
-        lo = int(max(int64_t(0), -x0));
-        hi = int(min(int64_t(kWTile + kFHalo + 8), nvis - x0));
-    };
-    auto x0_of = [&](uint32_t tile) { return int64_t(a.pos_begin) + int64_t(tile) * kWTile - kOverlap - kFLead; };
+    uint4 raw[3];
+    uint32_t rawh = 0;
+    int nx_lo = 0, nx_hi = 0;                      // staged indices [lo, hi) of the prefetched tile that exist in the feed
+    // staged index j of a tile <-> feed sample x0 + j
+    const int64_t x0_base = int64_t(a.pos_begin) - kOverlap - kFLead;
+    auto x0_of = [&](uint32_t tile) { return x0_base + int64_t(tile) * kWTile; };
     const uint8_t *src = kMagIn ? reinterpret_cast<const uint8_t *>(a.mag_in) : a.iq;   // both 2 bytes per sample
+    const int j0 = kFRun * lane;
     auto load_raw = [&](uint32_t tile) {
         const int64_t x0 = x0_of(tile);
-        int lo, hi;
-        valid_range(x0, lo, hi);
-        const int j = kFRun * lane;
-        const uint8_t *p = src + 2 * (x0 + j);
+        nx_lo = int(max(int64_t(0), -x0));
+        nx_hi = int(min(int64_t(kWTile + kFHalo + 8), nvis - x0));
+        const uint8_t *p = src + 2 * (x0 + j0);
 #pragma unroll
         for (int r = 0; r < 3; ++r)
-            if (j + 8 * r >= lo && j + 8 * r + 8 <= hi) raw[r] = __ldg(reinterpret_cast<const uint4 *>(p + 16 * r));
-        if (j + 24 >= lo && j + 28 <= hi) rawx = __ldg(reinterpret_cast<const uint2 *>(p + 48));
-        if (lane < 3) {
-            const int jh = kWTile + 8 * lane;
-            if (jh >= lo && jh + 8 <= hi) rawh = __ldg(reinterpret_cast<const uint4 *>(src + 2 * (x0 + jh)));
-        }
+            if (j0 + 8 * r >= nx_lo && j0 + 8 * r + 8 <= nx_hi) raw[r] = __ldg(reinterpret_cast<const uint4 *>(p + 16 * r));
+        // the 24 samples of look-ahead past the tile: one pair per lane, lanes 0..11
+        const int jh = kWTile + 2 * lane;
+        if (lane < 12 && jh >= nx_lo && jh + 2 <= nx_hi) rawh = __ldg(reinterpret_cast<const uint32_t *>(src + 2 * (x0 + jh)));
     };
     // magnitude of feed sample x on the slow path (stream edges): carry, one sample, or zero padding
     auto mag_edge = [&](int64_t x) -> int {
@@ -195,9 +191,7 @@ __global__ void __launch_bounds__(kFWarps * 32, 1) front_kernel(ChunkArgs a)
         const int64_t x0 = x0_of(tile);
         const uint32_t tile_pos = tile * kWTile;           // chunk-local position of staged index kFLead
         const int npos = int(min(int64_t(kWTile), int64_t(npos_chunk) - int64_t(tile_pos)));   // <= 0: decisions only
-        int v_lo, v_hi;
-        valid_range(x0, v_lo, v_hi);
-        const int j0 = kFRun * lane;
+        const int v_lo = nx_lo, v_hi = nx_hi;
         const bool interior = v_lo == 0 && v_hi == kWTile + kFHalo + 8;       // whole tile inside the feed (warp-uniform)
 
         // ---- phase A: magnitudes, falling-edge bits and all slicer decisions of 24 samples per lane ---------
@@ -206,7 +200,7 @@ __global__ void __launch_bounds__(kFWarps * 32, 1) front_kernel(ChunkArgs a)
         for (int c = 0; c < 12; ++c) acc[c] = 0;
         {
             int m[12];
-            // vector r of the lane: samples 8r .. 8r+7; mh[]: the first four samples of the next vector
+            // vector r of the lane: samples 8r .. 8r+7
             auto vec8 = [&](int r, const uint4 &d, int (&o)[8]) {
                 if (interior || (j0 + 8 * r >= v_lo && j0 + 8 * r + 8 <= v_hi)) {
                     two(d.x, o[0], o[1]); two(d.y, o[2], o[3]); two(d.z, o[4], o[5]); two(d.w, o[6], o[7]);
@@ -216,9 +210,18 @@ __global__ void __launch_bounds__(kFWarps * 32, 1) front_kernel(ChunkArgs a)
                 }
                 *reinterpret_cast<uint4 *>(&s_mag[j0 + 8 * r]) = make_uint4(pack(o[0], o[1]), pack(o[2], o[3]), pack(o[4], o[5]), pack(o[6], o[7]));
             };
-            int v0[8], v1[8], v2[8], vx[4];
+            int v0[8], v1[8], v2[8];
             vec8(0, raw[0], v0);
             vec8(1, raw[1], v1);
+            // look-ahead past the tile (lanes 0..11, one pair each): the preamble test of the tile's last start positions
+            // needs it, and so do the last three correlators of lane 31
+            int h0 = 0, h1 = 0;
+            if (lane < 12) {
+                const int jh = kWTile + 2 * lane;
+                if (interior || (jh >= v_lo && jh + 2 <= v_hi)) two(rawh, h0, h1);
+                else { h0 = mag_edge(x0 + jh); h1 = mag_edge(x0 + jh + 1); }
+                *reinterpret_cast<uint32_t *>(&s_mag[jh]) = pack(h0, h1);
+            }
 #pragma unroll
             for (int k = 0; k < 8; ++k) m[k] = v0[k];
 #pragma unroll
@@ -230,28 +233,14 @@ __global__ void __launch_bounds__(kFWarps * 32, 1) front_kernel(ChunkArgs a)
 #pragma unroll
             for (int k = 0; k < 4; ++k) m[8 + k] = v2[k];
             decide8<8>(m, acc, G);
-            if (interior || (j0 + 24 >= v_lo && j0 + 28 <= v_hi)) {
-                two(rawx.x, vx[0], vx[1]); two(rawx.y, vx[2], vx[3]);
-            } else {
-#pragma unroll
-                for (int e = 0; e < 4; ++e) vx[e] = mag_edge(x0 + j0 + 24 + e);
-            }
+            // the three magnitudes after the lane's run: the next lane's first three, or the look-ahead for lane 31
+            int n0 = __shfl_down_sync(0xFFFFFFFFu, v0[0], 1), n1 = __shfl_down_sync(0xFFFFFFFFu, v0[1], 1), n2 = __shfl_down_sync(0xFFFFFFFFu, v0[2], 1);
+            const int e0 = __shfl_sync(0xFFFFFFFFu, h0, 0), e1 = __shfl_sync(0xFFFFFFFFu, h1, 0), e2 = __shfl_sync(0xFFFFFFFFu, h0, 1);
+            if (lane == 31) { n0 = e0; n1 = e1; n2 = e2; }
 #pragma unroll
             for (int k = 0; k < 8; ++k) m[k] = v2[k];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) m[8 + k] = vx[k];
+            m[8] = n0; m[9] = n1; m[10] = n2; m[11] = 0;
             decide8<16>(m, acc, G);
-        }
-        if (lane < 3) {                                 // 24 magnitudes of look-ahead for the tile's last start positions
-            const int jh = kWTile + 8 * lane;
-            int h[8];
-            if (interior || (jh >= v_lo && jh + 8 <= v_hi)) {
-                two(rawh.x, h[0], h[1]); two(rawh.y, h[2], h[3]); two(rawh.z, h[4], h[5]); two(rawh.w, h[6], h[7]);
-            } else {
-#pragma unroll
-                for (int e = 0; e < 8; ++e) h[e] = mag_edge(x0 + jh + e);
-            }
-            *reinterpret_cast<uint4 *>(&s_mag[jh]) = make_uint4(pack(h[0], h[1]), pack(h[2], h[3]), pack(h[4], h[5]), pack(h[6], h[7]));
         }
         {
             const size_t run = size_t(tile) * 32 + lane;

@@ -237,8 +237,8 @@ struct FinishArgs {
     uint32_t     candidates_only;    // sharded scans: stop after the ordered array
     uint32_t     force_sequential;   // test knob: always take the one-thread replay
     uint32_t    *ticket;         // phase-1 completion counter
-    uint32_t    *perm;           // [nseg][rec_cap] sorted order of every segment
-    uint32_t    *seg_offset;     // [nseg]
+    unsigned long long *seg_flag;    // [nseg] epoch << 32 | records of the segment, published by its CTA
+    uint32_t     epoch;          // chunk sequence number (never 0): tells this chunk's flags from older ones
     uint32_t    *run_start;      // [full_cap + 1]
     uint4       *view;           // [full_cap] 16-byte view of the ordered records for the ordered pass
     PhaseRec    *deferred;       uint32_t deferred_cap;  uint32_t *n_deferred;   // sharded scans: still-unknown parked records

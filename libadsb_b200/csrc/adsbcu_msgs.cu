@@ -9,39 +9,40 @@
 //     is already in the "may ever be in the filter" set, are written out as evaluated records (FullRec);
 //   * records whose address has not been announced yet are parked as 8-byte (position, info) entries; the order
 //     kernel looks at them again when the whole chunk's announcements are known.
-// The work list is flat: a "round" is up to 256 preambles of one front-kernel segment, and the CTAs of a fixed grid
-// (a few per SM, high occupancy: 19 KiB of shared memory) take rounds in turn.
+// The work list is flat: a "round" is up to 256 preambles of one front-kernel segment, the CTAs of a fixed grid take
+// rounds in turn, and inside a round every warp handles its 32 preambles on its own (ballot-compacted work queues,
+// no CTA barrier), so that many independent warps hide the latency of the plane reads.
 #include "adsbcu_device.cuh"
 
 namespace adsbcu {
 namespace {
 
 constexpr int kMThreads = 256;
-constexpr int kMRound = kMThreads;             // preambles per round
-constexpr int kMQueue = 5 * kMRound;           // (preamble, phase) items per round
+constexpr int kMWarps = kMThreads / 32;
+constexpr int kMRound = kMThreads;             // preambles per round: 32 per warp
 constexpr int kMaxSeg = 160;                   // front-kernel CTAs (one per SM)
 
 struct MsgSmem {
     uint32_t crcb[11 * 256];                   // DevTables::crc_byte
     uint32_t occ_long[kSyndSlotsLong / 32], occ_short[kSyndSlotsShort / 32];
-    uint32_t queue[kMQueue];                   // 112-bit items from the front, 56-bit items from the back: index | (phase-4) << 16
-    uint32_t pos[kMRound];
-    PhaseRec pend[kMQueue];                    // parked records of this round
+    uint32_t queue[kMWarps][160];              // per warp: 112-bit items from the front, 56-bit items from the back: lane | (phase-4) << 8
     uint32_t round_first[kMaxSeg + 1];         // first round of every segment
-    uint32_t nq[2], npend, pend_base;
 };
 
 __global__ void __launch_bounds__(kMThreads) message_kernel(ChunkArgs a)
 {
     ADSBCU_DYN_SMEM(smem_raw);
     MsgSmem &sm = *reinterpret_cast<MsgSmem *>(smem_raw);
-    const int tid = threadIdx.x;
-    for (int i = tid; i < 11 * 256; i += kMThreads) sm.crcb[i] = (&a.tab->crc_byte[0][0])[i];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(&a.tab->crc_byte[0][0]);
+        uint4 *dst = reinterpret_cast<uint4 *>(sm.crcb);
+        for (int i = tid; i < 11 * 256 / 4; i += kMThreads) dst[i] = src[i];
+    }
     for (int i = tid; i < kSyndSlotsLong / 32; i += kMThreads) sm.occ_long[i] = a.tab->occ_long[i];
     for (int i = tid; i < kSyndSlotsShort / 32; i += kMThreads) sm.occ_short[i] = a.tab->occ_short[i];
     // rounds of every segment: exclusive prefix of ceil(count / 256) over the (at most kMaxSeg) segments
     if (tid < kMaxSeg + 1) sm.round_first[tid] = tid < int(a.nseg) ? (min(a.pre_count[tid], a.pre_cap) + kMRound - 1) / kMRound : 0u;
-    if (tid == 0) { sm.nq[0] = 0; sm.nq[1] = 0; sm.npend = 0; }
     const uint32_t valid_long = a.tab->valid_long, valid_short = a.tab->valid_short, fixable_short = a.tab->fixable_short;
     __syncthreads();
     if (tid < 32) {                            // one warp: each lane scans kMaxSeg / 32 consecutive counts
@@ -58,71 +59,81 @@ __global__ void __launch_bounds__(kMThreads) message_kernel(ChunkArgs a)
     }
     __syncthreads();
     const uint32_t nrounds = sm.round_first[a.nseg];
+    uint32_t *queue = sm.queue[warp];
 
+    // From here on every warp works alone: 32 preambles of the round, no CTA barrier.
     for (uint32_t round = blockIdx.x; round < nrounds; round += gridDim.x) {
         uint32_t seg = 0;                      // last segment whose first round is <= round and that has rounds
         for (uint32_t step = 128; step; step >>= 1)
             if (seg + step < a.nseg && sm.round_first[seg + step] <= round) seg += step;
-        const uint32_t c0 = (round - sm.round_first[seg]) * kMRound;
+        const uint32_t c0 = (round - sm.round_first[seg]) * kMRound + 32u * warp;
         const uint32_t npre = min(a.pre_count[seg], a.pre_cap);
-        const uint32_t nthis = min(uint32_t(kMRound), npre - c0);
-        const uint32_t *pre = a.pre + size_t(seg) * a.pre_cap + c0;
-        if (tid < int(nthis)) sm.pos[tid] = pre[tid];
-        __syncthreads();
-        // C1: the DF field (first five bits) of every (preamble, phase) decides 112 bits, 56 bits or nothing
-        for (uint32_t it = tid; it < 5u * nthis; it += kMThreads) {
-            const uint32_t k = it / 5u, ph = 4u + it % 5u;
-            const uint32_t t0 = 5u * (sm.pos[k] + kFLead + 19u) + ph;
+        if (c0 >= npre) continue;              // warp-uniform
+        const bool have = c0 + lane < npre;
+        const uint32_t mypos = have ? a.pre[size_t(seg) * a.pre_cap + c0 + lane] : 0u;     // chunk-local position
+        // C1: the DF field (first five bits) of the lane's preamble at each try_phase decides 112 bits, 56 bits or nothing
+        uint32_t nlong = 0, nshort = 0;
+#pragma unroll
+        for (uint32_t k = 0; k < 5u; ++k) {
+            const uint32_t t0 = 5u * (mypos + kFLead + 19u) + 4u + k;
             const uint32_t c = t0 % 12u, n0 = t0 / 12u, f = n0 / 10u, r = n0 - 10u * f;
             const uint16_t *pf = a.planes + size_t(c) * a.plane_stride + f;
-            const uint32_t w20 = (uint32_t(pf[0]) << 10) | pf[1];
+            const uint32_t w20 = have ? (uint32_t(pf[0]) << 10) | pf[1] : 0u;
             const uint32_t dfbit = 1u << ((w20 >> (15u - r)) & 31u);
-            const uint32_t item = k | ((ph - 4u) << 16);
-            if (valid_long & dfbit) sm.queue[atomicAdd(&sm.nq[0], 1u)] = item;
-            else if (valid_short & dfbit) sm.queue[kMQueue - 1 - atomicAdd(&sm.nq[1], 1u)] = item;
+            const bool is_l = have && (valid_long & dfbit), is_s = have && !is_l && (valid_short & dfbit);
+            const uint32_t bl = __ballot_sync(0xFFFFFFFFu, is_l), bs = __ballot_sync(0xFFFFFFFFu, is_s);
+            const uint32_t below = (1u << lane) - 1u;
+            if (is_l) queue[nlong + __popc(bl & below)] = uint32_t(lane) | (k << 8);
+            if (is_s) queue[159u - nshort - __popc(bs & below)] = uint32_t(lane) | (k << 8);
+            nlong += __popc(bl);
+            nshort += __popc(bs);
         }
-        __syncthreads();
-        // C2: one item per thread
-        const uint32_t nlong = sm.nq[0], nshort = sm.nq[1];
-        for (uint32_t it = tid; it < nlong + nshort; it += kMThreads) {
+        __syncwarp();
+        // C2: one item per lane and pass
+        for (uint32_t it0 = 0; it0 < nlong + nshort; it0 += 32) {
+            const uint32_t it = it0 + lane;
+            const bool live = it < nlong + nshort;
             const bool is_long = it < nlong;
-            const uint32_t item = is_long ? sm.queue[it] : sm.queue[kMQueue - 1 - (it - nlong)];
-            const uint32_t cpos = sm.pos[item & 0xFFFFu], ph = 4u + (item >> 16);    // chunk-local position
-            const uint32_t t0 = 5u * (cpos + kFLead + 19u) + ph;
-            const uint32_t c = t0 % 12u, n0 = t0 / 12u;
-            uint32_t M[4], xs, xl;
-            slice_planes(a.planes + size_t(c) * a.plane_stride + n0 / 10u, n0 % 10u, is_long, sm.crcb, fixable_short, M, xs, xl);
-            const Frame f = frame_from_words(M, is_long);
-            const Classified cl = classify(f, xs, xl, a.tab, sm.occ_long, sm.occ_short);
-            if (!cl.keep) continue;
-            const uint32_t bi = bitmap_index(cl.test_key);
-            if (cl.kind == K_DF17_0 || cl.kind == K_DF11_ACQ_0 || (cl.kind == K_DF18_0 && !df18_non_icao(cl.fixed)))
-                atomicOr(&a.bitmap[bi >> 5], 1u << (bi & 31));
-            const uint32_t pos = a.pos_begin + cpos;                                  // feed-relative position
-            if (rank_of(cl.kind, false) < kAcceptThreshold && !((a.bitmap[bi >> 5] >> (bi & 31)) & 1u)) {
-                // acceptable only for a known address that nobody has announced so far: parked
-                sm.pend[atomicAdd(&sm.npend, 1u)] = PhaseRec{pos, bi | ((ph - 4u) << 25) | (cl.kind << 28)};
-            } else {
-                const uint32_t slot = atomicAdd(&a.rec_count[seg], 1u);
-                if (slot < a.rec_cap) fill_rec(a.rec[size_t(seg) * a.rec_cap + slot], pos, ph, f, cl);
-                else a.ctr->overflow = 1u;
+            const uint32_t item = live ? (is_long ? queue[it] : queue[159u - (it - nlong)]) : 0u;
+            const uint32_t cpos = __shfl_sync(0xFFFFFFFFu, mypos, int(item & 31u)), ph = 4u + (item >> 8);
+            bool park = false;
+            PhaseRec parked{0u, 0u};
+            if (live) {
+                const uint32_t t0 = 5u * (cpos + kFLead + 19u) + ph;
+                const uint32_t c = t0 % 12u, n0 = t0 / 12u;
+                uint32_t M[4], xs, xl;
+                slice_planes(a.planes + size_t(c) * a.plane_stride + n0 / 10u, n0 % 10u, is_long, sm.crcb, fixable_short, M, xs, xl);
+                const Frame f = frame_from_words(M, is_long);
+                const Classified cl = classify(f, xs, xl, a.tab, sm.occ_long, sm.occ_short);
+                if (cl.keep) {
+                    const uint32_t bi = bitmap_index(cl.test_key);
+                    if (cl.kind == K_DF17_0 || cl.kind == K_DF11_ACQ_0 || (cl.kind == K_DF18_0 && !df18_non_icao(cl.fixed)))
+                        atomicOr(&a.bitmap[bi >> 5], 1u << (bi & 31));
+                    const uint32_t pos = a.pos_begin + cpos;                          // feed-relative position
+                    if (rank_of(cl.kind, false) < kAcceptThreshold && !((a.bitmap[bi >> 5] >> (bi & 31)) & 1u)) {
+                        // acceptable only for a known address that nobody has announced so far: parked
+                        park = true;
+                        parked = PhaseRec{pos, bi | ((ph - 4u) << 25) | (cl.kind << 28)};
+                    } else {
+                        const uint32_t slot = atomicAdd(&a.rec_count[seg], 1u);
+                        if (slot < a.rec_cap) fill_rec(a.rec[size_t(seg) * a.rec_cap + slot], pos, ph, f, cl);
+                        else a.ctr->overflow = 1u;
+                    }
+                }
+            }
+            // the pass's parked records: one reservation in the segment's list per warp
+            const uint32_t bp = __ballot_sync(0xFFFFFFFFu, park);
+            if (bp) {
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(&a.pend_count[seg], uint32_t(__popc(bp)));
+                base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                if (park) {
+                    const uint32_t slot = base + __popc(bp & ((1u << lane) - 1u));
+                    if (slot < a.pend_cap) a.pend[size_t(seg) * a.pend_cap + slot] = parked; else a.ctr->overflow = 1u;
+                }
             }
         }
-        __syncthreads();
-        // the round's parked records: one reservation in the segment's list, then a plain copy
-        const uint32_t np = sm.npend;
-        if (tid == 0 && np) sm.pend_base = atomicAdd(&a.pend_count[seg], np);
-        __syncthreads();
-        if (np) {
-            const uint32_t base = sm.pend_base;
-            if (base + np > a.pend_cap) { if (tid == 0) a.ctr->overflow = 1u; }
-            else {
-                PhaseRec *dst = a.pend + size_t(seg) * a.pend_cap + base;
-                for (uint32_t i = tid; i < np; i += kMThreads) dst[i] = sm.pend[i];
-            }
-        }
-        __syncthreads();
-        if (tid == 0) { sm.nq[0] = 0; sm.nq[1] = 0; sm.npend = 0; }
+        __syncwarp();
     }
 }
 
