@@ -95,6 +95,7 @@ struct Slot {
     unsigned long long *d_seg_flag = nullptr;
     uint32_t *d_run_start = nullptr, *d_ticket = nullptr;
     uint4 *d_view = nullptr;
+    uint8_t *d_dec = nullptr;
     adsbcu_msg *d_chunk_msgs = nullptr;   // accepted messages of the chunk, before the level kernel finishes them
     ChunkCounters *d_ctr = nullptr;
     ChunkCounters *h_ctr = nullptr;   // pinned
@@ -177,7 +178,7 @@ void free_slots(adsbcu_handle *h)
     for (Slot &s : h->slot) {
         cudaFree(s.d_planes); cudaFree(s.d_pre); cudaFree(s.d_pre_count); cudaFree(s.d_pend); cudaFree(s.d_pend_count);
         cudaFree(s.d_rec); cudaFree(s.d_rec_count); cudaFree(s.d_ordered); cudaFree(s.d_seg_flag);
-        cudaFree(s.d_run_start); cudaFree(s.d_ticket); cudaFree(s.d_ctr); cudaFree(s.d_chunk_msgs); cudaFree(s.d_view);
+        cudaFree(s.d_run_start); cudaFree(s.d_ticket); cudaFree(s.d_ctr); cudaFree(s.d_chunk_msgs); cudaFree(s.d_view); cudaFree(s.d_dec);
         if (s.h_cand) cudaFreeHost(s.h_cand);
         if (s.h_ctr) cudaFreeHost(s.h_ctr);
         cudaEvent_t ev[6];
@@ -214,6 +215,7 @@ int alloc_slots(adsbcu_handle *h)
         CK(cudaMalloc(&s.d_run_start, (size_t(h->full_cap) + 1) * sizeof(uint32_t)));
         CK(cudaMalloc(&s.d_chunk_msgs, size_t(h->full_cap) * sizeof(adsbcu_msg)));
         CK(cudaMalloc(&s.d_view, size_t(h->full_cap) * sizeof(uint4)));
+        CK(cudaMalloc(&s.d_dec, size_t(h->full_cap) + 16));
         CK(cudaMalloc(&s.d_ticket, sizeof(uint32_t)));
         CK(cudaMemset(s.d_ticket, 0, sizeof(uint32_t)));
         CK(cudaMalloc(&s.d_ctr, sizeof(ChunkCounters)));
@@ -401,7 +403,7 @@ int run_chunks(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, ui
         fa.block_samples = h->cfg.block_samples;
         fa.candidates_only = sink.cands ? 1u : 0u;
         fa.force_sequential = h->force_sequential ? 1u : 0u;
-        fa.ticket = s.d_ticket; fa.seg_flag = s.d_seg_flag; fa.epoch = ++h->chunk_epoch ? h->chunk_epoch : ++h->chunk_epoch; fa.run_start = s.d_run_start; fa.view = s.d_view;
+        fa.ticket = s.d_ticket; fa.seg_flag = s.d_seg_flag; fa.epoch = ++h->chunk_epoch ? h->chunk_epoch : ++h->chunk_epoch; fa.run_start = s.d_run_start; fa.view = s.d_view; fa.dec = s.d_dec;
         if (sink.cands) { fa.deferred = h->d_deferred; fa.deferred_cap = h->deferred_cap; fa.n_deferred = h->d_n_deferred; }
         CK(cudaStreamWaitEvent(h->post_stream, s.ev[2], 0));
         CK(cudaEventRecord(s.ev[3], h->post_stream));

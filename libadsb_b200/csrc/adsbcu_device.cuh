@@ -427,6 +427,33 @@ __device__ __forceinline__ double signal_level_warp(const ChunkArgs &a, uint32_t
     return double(acc) / 65535.0 / 65535.0 / double(siglen);
 }
 
+// ---- the common case of classify(), branch-light --------------------------------------------------------------
+// Almost every sliced candidate is noise: its syndromes are neither zero nor in the repair tables.  For those
+// correctMessage changes nothing and scoreModesMessage only looks at the DF: Address/Parity formats (DF0/4/5 with the
+// 56-bit syndrome as address, DF16/20/21 with the 112-bit one) can be accepted for a known address, everything else is
+// SR_UNCORRECTABLE / SR_UNKNOWN_DF.  Returns 0: dropped, 1: Address/Parity candidate with filter key `key`,
+// 2: anything else (a syndrome that is zero, DF11-clean or present in a repair table) -> run classify().
+// `occ_*`: occupancy bitmaps of the syndrome hash tables; a syndrome whose home slot is empty is in no table.
+__device__ __forceinline__ int classify_fast(uint32_t m0, bool zero56, uint32_t xs, uint32_t xl, uint32_t fixable_long, uint32_t fixable_short,
+                                             const uint32_t *occ_long, const uint32_t *occ_short, uint32_t &key)
+{
+    if (zero56) return 0;                                           // SR_ALL_ZEROS
+    const uint32_t df = m0 >> 27, dfbit = 1u << df;
+    if (fixable_long & dfbit) {
+        const uint32_t h = synd_hash(xl, kSyndSlotsLong);
+        if (xl == 0u || ((occ_long[h >> 5] >> (h & 31)) & 1u)) return 2;
+    }
+    if (fixable_short & dfbit) {
+        const uint32_t h = synd_hash(xs, kSyndSlotsShort);
+        if ((xs & 0xFFFF80u) == 0u || ((occ_short[h >> 5] >> (h & 31)) & 1u)) return 2;
+    }
+    // no correction applies: corrected == uncorrected, corrections == -1
+    const uint32_t ap_short = (1u << 0) | (1u << 4) | (1u << 5), ap_long = (1u << 16) | (1u << 20) | (1u << 21);
+    if (dfbit & ap_short) { key = xs; return 1; }
+    if (dfbit & ap_long) { key = xl; return 1; }
+    return 0;
+}
+
 // bitmap of addresses that may ever be in the filter: bit index = 24-bit address (+2^24 for the NT table)
 __device__ __forceinline__ uint32_t bitmap_index(uint32_t key) { return (key & 0xFFFFFFu) | ((key & kNtFlag) ? (1u << 24) : 0u); }
 

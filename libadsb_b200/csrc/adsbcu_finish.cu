@@ -134,7 +134,9 @@ struct SkipState {
 };
 
 // Compact view of a record for the ordered pass: x = feed position, y = key of icaoFilterTest, z = key of
-// icaoFilterAdd (or 0xFFFFFFFF), w = kind | 112-bit flag << 8.  16 bytes, so a thread walking its runs stays in L1.
+// icaoFilterAdd (or 0xFFFFFFFF), w = kind | 112-bit flag << 8 (| 0x200: the key is in the filter when the chunk starts,
+// | 0x400: accepting the record adds an address the active table does not hold; both set by phase 1).  16 bytes, so a
+// thread walking its runs stays in L1.
 __device__ __forceinline__ uint4 view_of(const FullRec &r)
 {
     return make_uint4(r.pos, r.test_key, r.add_key, uint32_t(r.kind) | ((r.verbatim[0] & 0x80u) ? 0x100u : 0u));
@@ -180,11 +182,11 @@ __device__ __forceinline__ void resolve_range(const uint4 *view, uint32_t i0, ui
 }
 
 struct FinishSmem {
-    uint32_t table[2][kIcaoSlots];             // the reference's two filter tables as of the chunk's start
     AddMap cur, next;
     uint32_t scan[kXThreads];
     uint32_t nkeys_cur, nkeys_next, changed;
     uint32_t total;
+    uint8_t rank[24];                          // score_rank by (kind, known)
 };
 struct SortSmem {
     uint32_t key[kSortCap];
@@ -284,7 +286,10 @@ __global__ void __launch_bounds__(kXThreads) order_kernel(FinishArgs fa)
                 uint4 *dst = reinterpret_cast<uint4 *>(a.ordered + offset + rank);
                 const uint4 q0 = src[0], q1 = src[1], q2 = src[2], q3 = src[3];
                 dst[0] = q0; dst[1] = q1; dst[2] = q2; dst[3] = q3;
-                fa.view[offset + rank] = view_of(rec[i]);
+                uint4 v = view_of(rec[i]);
+                if (icao_test(fa.st, v.y)) v.w |= 0x200u;                                              // known when the chunk starts
+                if (v.z != kUnchecked && !icao_probe(fa.st->table[fa.st->active], v.z)) v.w |= 0x400u;    // accepting it adds a new address
+                fa.view[offset + rank] = v;
             }
         }
         __syncthreads();
@@ -320,18 +325,18 @@ __global__ void __launch_bounds__(kXThreads) order_kernel(FinishArgs fa)
 
     const FullRec *recs = a.ordered;
     const uint32_t n = n_full;
-    // the ordered pass works on the 16-byte views of the records and on the filter tables in shared memory
-    const uint4 *view = fa.view;
-    for (uint32_t i = tid; i < 2u * kIcaoSlots; i += kXThreads) sm.table[0][i] = st->table[0][i];
-    const uint32_t active = st->active;
-    __syncthreads();
-    auto in_tables = [&](uint32_t key) { return icao_probe(sm.table[0], key) || icao_probe(sm.table[1], key); };
+    const uint4 *view = fa.view;                  // 16-byte views, filter state as of the chunk's start folded in by phase 1
+    uint8_t *dec = fa.dec;                        // score of every accepted record, 0 for the others
     const uint32_t block = fa.block_samples;
+    const int bshift = (block & (block - 1u)) == 0u ? 31 - __clz(int(block)) : -1;
+    auto blk_of = [&](uint64_t x) { return bshift >= 0 ? x >> bshift : x / block; };
     const uint64_t feed_base = fa.feed_base;
     adsbcu_msg *out = fa.chunk_msgs;              // n_full entries at most: every accepted message has its own record
-    const uint64_t out_base = 0, out_cap = a.full_cap;
     const uint64_t feed_count = st->n_out;
     uint32_t *run_start = fa.run_start;
+    if (tid < 22) sm.rank[tid] = uint8_t(rank_of(uint32_t(tid) >> 1, (tid & 1) != 0));
+    for (uint32_t i = tid; i < kMapSlots; i += kXThreads) { sm.cur.key[i] = kMapEmpty; sm.cur.pos[i] = kMapEmpty; sm.next.key[i] = kMapEmpty; sm.next.pos[i] = kMapEmpty; }
+    if (tid == 0) { sm.nkeys_cur = 0; sm.nkeys_next = 0; sm.changed = 0; sm.total = 0; }
 
     // runs: a record starts a run when it is 288 or more samples after its predecessor
     uint32_t R = 0;
@@ -348,31 +353,38 @@ __global__ void __launch_bounds__(kXThreads) order_kernel(FinishArgs fa)
     }
     const uint32_t rper = (R + kXThreads - 1) / kXThreads;
     const uint32_t r0 = min(R, tid * rper), r1 = min(R, r0 + rper);
-
-    for (uint32_t i = tid; i < kMapSlots; i += kXThreads) { sm.cur.key[i] = kMapEmpty; sm.cur.pos[i] = kMapEmpty; sm.next.key[i] = kMapEmpty; sm.next.pos[i] = kMapEmpty; }
-    if (tid == 0) { sm.nkeys_cur = 0; sm.nkeys_next = 0; sm.changed = 0; }
-    __syncthreads();
+    const SkipState carried{st->has_last, st->last_a, st->last_lme};
 
     bool sequential = fa.force_sequential != 0;
-    uint32_t my_count = 0;
-    SkipState my_last{0u, 0, 0};
-    bool my_has = false;
-    const SkipState carried{st->has_last, st->last_a, st->last_lme};
     for (int round = 0; !sequential; ++round) {
-        my_count = 0;
-        my_has = false;
+        const bool use_map = sm.nkeys_cur != 0u;
         for (uint32_t r = r0; r < r1; ++r) {
             SkipState ss = r == 0 ? carried : SkipState{0u, 0, 0};
-            bool any = false;
-            resolve_range(view, run_start[r], run_start[r + 1], feed_base, block, ss,
-                          [&](uint32_t key, uint32_t pos) { return in_tables(key) || map_lookup(sm.cur, key) < pos; },
-                          [&](uint32_t idx, int, uint64_t) {
-                              ++my_count;
-                              any = true;
-                              const uint4 v = view[idx];
-                              if (v.z != kUnchecked && !icao_probe(sm.table[active], v.z)) map_insert_min(sm.next, v.z, v.x, &sm.nkeys_next);
-                          });
-            if (any) { my_last = ss; my_has = true; }
+            uint32_t i = run_start[r];
+            const uint32_t i1 = run_start[r + 1];
+            uint4 cur = view[i];
+            while (i < i1) {
+                const uint32_t pos = cur.x;
+                const uint64_t pa = feed_base + pos;
+                // inside the mag_buf of the last accepted message scanning resumes 18 samples before its end
+                // (j = last_message_end - 19, then ++j); a later mag_buf starts exactly at its end (demod_2400.c:410-443)
+                const bool skip = ss.has_last && pa < (blk_of(pa) == blk_of(ss.last_a) ? ss.last_lme - 18 : ss.last_lme);
+                uint32_t best = 0, bi = i, best_w = 0, best_add = kUnchecked;     // SR_NOT_SET
+                do {                                // phases ascending; strict > keeps the lowest phase on ties
+                    const bool known = (cur.w & 0x200u) || (use_map && map_lookup(sm.cur, cur.y) < pos);
+                    const uint32_t sc = sm.rank[2u * (cur.w & 0xFFu) + (known ? 1u : 0u)];
+                    if (sc > best) { best = sc; bi = i; best_w = cur.w; best_add = cur.z; }
+                    dec[i] = 0;
+                    ++i;
+                    if (i < i1) cur = view[i];
+                } while (i < i1 && cur.x == pos);
+                if (skip || best < uint32_t(kAcceptThreshold)) continue;
+                dec[bi] = uint8_t(best);
+                if (best_w & 0x400u) map_insert_min(sm.next, best_add, pos, &sm.nkeys_next);
+                ss.has_last = 1u;
+                ss.last_a = pa;
+                ss.last_lme = pa + uint64_t((((best_w & 0x100u) ? 112 : 56) + 8) * 12 / 5);
+            }
         }
         __syncthreads();
         // did this round reproduce the map it was computed with?
@@ -394,14 +406,14 @@ __global__ void __launch_bounds__(kXThreads) order_kernel(FinishArgs fa)
     }
 
     if (sequential) {
-        // the reference's own loop, one thread: exact whatever the tables hold
+        // the reference's own loop, one thread, on the tables in global memory: exact whatever they hold
         if (tid == 0) {
             SkipState ss = carried;
             uint64_t k = 0;
             resolve_range(view, 0, n, feed_base, block, ss,
                           [&](uint32_t key, uint32_t) { return icao_test(st, key); },
                           [&](uint32_t idx, int score, uint64_t pa) {
-                              if (out_base + k < out_cap) write_msg(out + out_base + k, recs[idx], pa, score, block);
+                              write_msg(out + k, recs[idx], pa, score, block);
                               ++k;
                               if (recs[idx].add_key != kUnchecked) icao_add(st, recs[idx].add_key);
                           });
@@ -414,70 +426,56 @@ __global__ void __launch_bounds__(kXThreads) order_kernel(FinishArgs fa)
         return;
     }
 
-    // emission: offsets of every thread's block of runs, then the same pass once more writing the messages
-    uint32_t total = 0;
-    uint32_t off = block_exclusive_scan(my_count, sm.scan, total);
-    for (uint32_t r = r0; r < r1; ++r) {
-        SkipState ss = r == 0 ? carried : SkipState{0u, 0, 0};
-        resolve_range(view, run_start[r], run_start[r + 1], feed_base, block, ss,
-                      [&](uint32_t key, uint32_t pos) { return in_tables(key) || map_lookup(sm.cur, key) < pos; },
-                      [&](uint32_t idx, int score, uint64_t pa) {
-                          if (out_base + off < out_cap) write_msg(out + out_base + off, recs[idx], pa, score, block);
-                          ++off;
-                      });
-    }
-    // the stream's skip state: the last accepted message of the chunk (highest thread that accepted anything)
-    sm.scan[tid] = my_has ? uint32_t(tid) + 1u : 0u;
-    __syncthreads();
-    for (int d = kXThreads / 2; d; d >>= 1) {
-        if (tid < d) sm.scan[tid] = max(sm.scan[tid], sm.scan[tid + d]);
+    // emission, parallel over the records: every accepted record becomes one message, in stream order
+    {
+        const uint32_t per = (n + kXThreads - 1) / kXThreads;
+        const uint32_t i0 = min(n, tid * per), i1 = min(n, i0 + per);
+        uint32_t mine = 0, last = 0;                                       // last: index + 1 of my last accepted record
+        for (uint32_t i = i0; i < i1; ++i) if (dec[i]) { ++mine; last = i + 1; }
+        uint32_t total = 0;
+        uint32_t off = block_exclusive_scan(mine, sm.scan, total);
+        for (uint32_t i = i0; i < i1; ++i)
+            if (const uint32_t sc = dec[i]) write_msg(out + off++, recs[i], feed_base + recs[i].pos, int(sc), block);
+        // the stream's skip state: the last accepted message of the chunk
+        sm.scan[tid] = last;
         __syncthreads();
-    }
-    const uint32_t winner = sm.scan[0];
-    __syncthreads();                                                           // (every thread is past the filter reads of its runs)
-    if (winner && uint32_t(tid) + 1u == winner) { st->has_last = my_last.has_last; st->last_a = my_last.last_a; st->last_lme = my_last.last_lme; }
-    // New addresses enter the reference's table in stream order (icao_filter.c:71-84): the map is compacted into a
-    // list (in the storage of `next`, which equals `cur` by now), ranked by position, and one thread inserts.
-    if (tid == 0) sm.total = 0;
-    __syncthreads();
-    for (uint32_t i = tid; i < kMapSlots; i += kXThreads)
-        if (sm.cur.key[i] != kMapEmpty) {
-            const uint32_t j = atomicAdd(&sm.total, 1u);
-            sm.next.key[j] = sm.cur.key[i];
-            sm.next.pos[j] = sm.cur.pos[i];
+        for (int d = kXThreads / 2; d; d >>= 1) {
+            if (tid < d) sm.scan[tid] = max(sm.scan[tid], sm.scan[tid + d]);
+            __syncthreads();
         }
-    __syncthreads();
-    const uint32_t nnew = sm.total;
-    __syncthreads();
-    for (uint32_t j = tid; j < nnew; j += kXThreads) {
-        const uint32_t me = sm.next.pos[j];
-        uint32_t rank = 0;
-        for (uint32_t k = 0; k < nnew; ++k) rank += sm.next.pos[k] < me;      // one accepted message per position: unique
-        sm.cur.key[rank] = sm.next.key[j];
+        if (tid == 0) {
+            if (const uint32_t li = sm.scan[0]) {
+                const uint4 v = view[li - 1];
+                const uint64_t pa = feed_base + v.x;
+                st->has_last = 1u; st->last_a = pa;
+                st->last_lme = pa + uint64_t((((v.w & 0x100u) ? 112 : 56) + 8) * 12 / 5);
+            }
+            st->n_out = feed_count + total;
+            a.ctr->n_msgs = total;
+            a.ctr->msg_base = feed_count;
+        }
     }
-    __syncthreads();
-    // (in the shared copy of the active table, which then replaces the one in global memory)
-    if (tid == 0) {
-        uint32_t *t = sm.table[active];
+    // New addresses enter the active table (icao_filter.c:71-84).  The reference inserts them in stream order; which
+    // slot of a probe chain an address lands in changes no answer of icaoFilterTest while the table has room (and a
+    // chunk that could fill it took the sequential replay above), so the insertions run in parallel.
+    {
+        uint32_t *t = st->table[st->active];
         uint32_t added = 0;
-        for (uint32_t r = 0; r < nnew; ++r) {
-            const uint32_t v = sm.cur.key[r], h0 = icao_hash(v);
-            uint32_t h = h0;
-            bool full = false;
-            while (t[h] != kIcaoEmpty && t[h] != v) { h = (h + 1) & (kIcaoSlots - 1); if (h == h0) { full = true; break; } }
-            if (!full && t[h] == kIcaoEmpty) { t[h] = v; ++added; }
+        for (uint32_t i = tid; i < kMapSlots; i += kXThreads) {
+            const uint32_t v = sm.cur.key[i];
+            if (v == kMapEmpty) continue;
+            uint32_t h = icao_hash(v);
+            for (uint32_t probes = 0; probes < kIcaoSlots; ++probes) {
+                const uint32_t e = atomicCAS(&t[h], kIcaoEmpty, v);
+                if (e == kIcaoEmpty) { ++added; break; }
+                if (e == v) break;
+                h = (h + 1) & (kIcaoSlots - 1);
+            }
         }
-        sm.total = added;
+        if (added) atomicAdd(&st->active_count, added);
     }
     __syncthreads();
-    if (nnew) for (uint32_t i = tid; i < kIcaoSlots; i += kXThreads) st->table[active][i] = sm.table[active][i];
-    if (tid == 0) {
-        st->active_count += sm.total;
-        st->n_out = feed_count + total;
-        a.ctr->n_msgs = total;
-        a.ctr->msg_base = feed_count;
-        __threadfence_system();
-    }
+    if (tid == 0) __threadfence_system();
 }
 
 // mm.signalLevel of the accepted messages of one chunk (demod_2400.c:382-403): mean squared magnitude over the

@@ -240,6 +240,7 @@ struct FinishArgs {
     unsigned long long *seg_flag;    // [nseg] epoch << 32 | records of the segment, published by its CTA
     uint32_t     epoch;          // chunk sequence number (never 0): tells this chunk's flags from older ones
     uint32_t    *run_start;      // [full_cap + 1]
+    uint8_t     *dec;            // [full_cap] score of the accepted records
     uint4       *view;           // [full_cap] 16-byte view of the ordered records for the ordered pass
     PhaseRec    *deferred;       uint32_t deferred_cap;  uint32_t *n_deferred;   // sharded scans: still-unknown parked records
 };

@@ -43,7 +43,8 @@ __global__ void __launch_bounds__(kMThreads) message_kernel(ChunkArgs a)
     for (int i = tid; i < kSyndSlotsShort / 32; i += kMThreads) sm.occ_short[i] = a.tab->occ_short[i];
     // rounds of every segment: exclusive prefix of ceil(count / 256) over the (at most kMaxSeg) segments
     if (tid < kMaxSeg + 1) sm.round_first[tid] = tid < int(a.nseg) ? (min(a.pre_count[tid], a.pre_cap) + kMRound - 1) / kMRound : 0u;
-    const uint32_t valid_long = a.tab->valid_long, valid_short = a.tab->valid_short, fixable_short = a.tab->fixable_short;
+    const uint32_t valid_long = a.tab->valid_long, valid_short = a.tab->valid_short, fixable_short = a.tab->fixable_short,
+                   fixable_long = a.tab->fixable_long;
     __syncthreads();
     if (tid < 32) {                            // one warp: each lane scans kMaxSeg / 32 consecutive counts
         constexpr int kPer = (kMaxSeg + 32) / 32;
@@ -101,23 +102,36 @@ __global__ void __launch_bounds__(kMThreads) message_kernel(ChunkArgs a)
             if (live) {
                 const uint32_t t0 = 5u * (cpos + kFLead + 19u) + ph;
                 const uint32_t c = t0 % 12u, n0 = t0 / 12u;
-                uint32_t M[4], xs, xl;
+                uint32_t M[4], xs, xl, key = 0;
                 slice_planes(a.planes + size_t(c) * a.plane_stride + n0 / 10u, n0 % 10u, is_long, sm.crcb, fixable_short, M, xs, xl);
-                const Frame f = frame_from_words(M, is_long);
-                const Classified cl = classify(f, xs, xl, a.tab, sm.occ_long, sm.occ_short);
-                if (cl.keep) {
-                    const uint32_t bi = bitmap_index(cl.test_key);
-                    if (cl.kind == K_DF17_0 || cl.kind == K_DF11_ACQ_0 || (cl.kind == K_DF18_0 && !df18_non_icao(cl.fixed)))
-                        atomicOr(&a.bitmap[bi >> 5], 1u << (bi & 31));
-                    const uint32_t pos = a.pos_begin + cpos;                          // feed-relative position
-                    if (rank_of(cl.kind, false) < kAcceptThreshold && !((a.bitmap[bi >> 5] >> (bi & 31)) & 1u)) {
+                const uint32_t pos = a.pos_begin + cpos;                              // feed-relative position
+                // the common case first (noise: no repair applies), the general classification only where it does not
+                int verdict = classify_fast(M[0], M[0] == 0u && (M[1] >> 8) == 0u, xs, xl, fixable_long, fixable_short, sm.occ_long, sm.occ_short, key);
+                if (verdict == 1) {
+                    const uint32_t bi = bitmap_index(key);
+                    if (!((a.bitmap[bi >> 5] >> (bi & 31)) & 1u)) {
                         // acceptable only for a known address that nobody has announced so far: parked
                         park = true;
-                        parked = PhaseRec{pos, bi | ((ph - 4u) << 25) | (cl.kind << 28)};
+                        parked = PhaseRec{pos, bi | ((ph - 4u) << 25) | (uint32_t(K_AP) << 28)};
                     } else {
-                        const uint32_t slot = atomicAdd(&a.rec_count[seg], 1u);
-                        if (slot < a.rec_cap) fill_rec(a.rec[size_t(seg) * a.rec_cap + slot], pos, ph, f, cl);
-                        else a.ctr->overflow = 1u;
+                        verdict = 2;                                                  // announced address: evaluated record
+                    }
+                }
+                if (verdict == 2) {
+                    const Frame f = frame_from_words(M, is_long);
+                    const Classified cl = classify(f, xs, xl, a.tab, sm.occ_long, sm.occ_short);
+                    if (cl.keep) {
+                        const uint32_t bi = bitmap_index(cl.test_key);
+                        if (cl.kind == K_DF17_0 || cl.kind == K_DF11_ACQ_0 || (cl.kind == K_DF18_0 && !df18_non_icao(cl.fixed)))
+                            atomicOr(&a.bitmap[bi >> 5], 1u << (bi & 31));
+                        if (rank_of(cl.kind, false) < kAcceptThreshold && !((a.bitmap[bi >> 5] >> (bi & 31)) & 1u)) {
+                            park = true;
+                            parked = PhaseRec{pos, bi | ((ph - 4u) << 25) | (cl.kind << 28)};
+                        } else {
+                            const uint32_t slot = atomicAdd(&a.rec_count[seg], 1u);
+                            if (slot < a.rec_cap) fill_rec(a.rec[size_t(seg) * a.rec_cap + slot], pos, ph, f, cl);
+                            else a.ctr->overflow = 1u;
+                        }
                     }
                 }
             }
