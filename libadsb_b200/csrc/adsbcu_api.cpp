@@ -93,10 +93,9 @@ struct Slot {
     FullRec *d_ordered = nullptr;
     FullRec *h_cand = nullptr, *d_cand = nullptr;     // sharded scans: the ordered array in mapped host memory (allocated on first use)
     unsigned long long *d_seg_flag = nullptr;
-    uint32_t *d_run_start = nullptr, *d_ticket = nullptr;
+    uint32_t *d_run_start = nullptr;
     uint4 *d_view = nullptr;
-    uint8_t *d_dec = nullptr;
-    adsbcu_msg *d_chunk_msgs = nullptr;   // accepted messages of the chunk, before the level kernel finishes them
+    uint2 *d_accepted = nullptr;      // accepted records of the chunk: the level kernel turns them into messages
     ChunkCounters *d_ctr = nullptr;
     ChunkCounters *h_ctr = nullptr;   // pinned
     cudaEvent_t ev[6]{};              // front begin, front end, messages end | finish begin, finish end, counters on the host
@@ -128,6 +127,7 @@ struct adsbcu_handle {
     uint32_t ntiles_max = 0, plane_stride = 0, pre_cap = 0, pend_cap = 0, rec_cap = 0, full_cap = 0;
     uint32_t chunk_epoch = 0;         // sequence number of the last submitted chunk (never 0 in a launch)
     uint32_t grow = 1;                // list capacities are `grow` times their base size (doubled after an overflow)
+    uint32_t resolve_batch = 1u << 30; // ADSBCU_RESOLVE_BATCH: records per batch of the ordered pass (tests)
     bool force_sequential = false;    // ADSBCU_RESOLVE_SEQ=1: the finish kernel always takes its one-thread replay (tests)
     Slot slot[kSlots];
     uint16_t *d_mag = nullptr;        // stage-level magnitude output
@@ -178,7 +178,7 @@ void free_slots(adsbcu_handle *h)
     for (Slot &s : h->slot) {
         cudaFree(s.d_planes); cudaFree(s.d_pre); cudaFree(s.d_pre_count); cudaFree(s.d_pend); cudaFree(s.d_pend_count);
         cudaFree(s.d_rec); cudaFree(s.d_rec_count); cudaFree(s.d_ordered); cudaFree(s.d_seg_flag);
-        cudaFree(s.d_run_start); cudaFree(s.d_ticket); cudaFree(s.d_ctr); cudaFree(s.d_chunk_msgs); cudaFree(s.d_view); cudaFree(s.d_dec);
+        cudaFree(s.d_run_start); cudaFree(s.d_ctr); cudaFree(s.d_accepted); cudaFree(s.d_view);
         if (s.h_cand) cudaFreeHost(s.h_cand);
         if (s.h_ctr) cudaFreeHost(s.h_ctr);
         cudaEvent_t ev[6];
@@ -213,11 +213,8 @@ int alloc_slots(adsbcu_handle *h)
         CK(cudaMalloc(&s.d_seg_flag, size_t(h->nseg) * sizeof(unsigned long long)));
         CK(cudaMemset(s.d_seg_flag, 0, size_t(h->nseg) * sizeof(unsigned long long)));
         CK(cudaMalloc(&s.d_run_start, (size_t(h->full_cap) + 1) * sizeof(uint32_t)));
-        CK(cudaMalloc(&s.d_chunk_msgs, size_t(h->full_cap) * sizeof(adsbcu_msg)));
+        CK(cudaMalloc(&s.d_accepted, size_t(h->full_cap) * sizeof(uint2)));
         CK(cudaMalloc(&s.d_view, size_t(h->full_cap) * sizeof(uint4)));
-        CK(cudaMalloc(&s.d_dec, size_t(h->full_cap) + 16));
-        CK(cudaMalloc(&s.d_ticket, sizeof(uint32_t)));
-        CK(cudaMemset(s.d_ticket, 0, sizeof(uint32_t)));
         CK(cudaMalloc(&s.d_ctr, sizeof(ChunkCounters)));
         CK(cudaHostAlloc(&s.h_ctr, sizeof(ChunkCounters), cudaHostAllocDefault));
         std::memset(s.h_ctr, 0, sizeof(ChunkCounters));
@@ -398,12 +395,13 @@ int run_chunks(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, ui
         fa.c = a;
         fa.st = h->d_state;
         fa.out = out_dev; fa.out_cap = out_cap;
-        fa.chunk_msgs = s.d_chunk_msgs;
+        fa.accepted = s.d_accepted;
         fa.feed_base = h->stream_pos;
         fa.block_samples = h->cfg.block_samples;
         fa.candidates_only = sink.cands ? 1u : 0u;
         fa.force_sequential = h->force_sequential ? 1u : 0u;
-        fa.ticket = s.d_ticket; fa.seg_flag = s.d_seg_flag; fa.epoch = ++h->chunk_epoch ? h->chunk_epoch : ++h->chunk_epoch; fa.run_start = s.d_run_start; fa.view = s.d_view; fa.dec = s.d_dec;
+        fa.batch = h->resolve_batch;
+        fa.seg_flag = s.d_seg_flag; fa.epoch = ++h->chunk_epoch ? h->chunk_epoch : ++h->chunk_epoch; fa.run_start = s.d_run_start; fa.view = s.d_view;
         if (sink.cands) { fa.deferred = h->d_deferred; fa.deferred_cap = h->deferred_cap; fa.n_deferred = h->d_n_deferred; }
         CK(cudaStreamWaitEvent(h->post_stream, s.ev[2], 0));
         CK(cudaEventRecord(s.ev[3], h->post_stream));
@@ -411,7 +409,7 @@ int run_chunks(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, ui
         CK(cudaEventRecord(s.ev[4], h->post_stream));
         CK(cudaMemcpyAsync(s.h_ctr, s.d_ctr, sizeof(ChunkCounters), cudaMemcpyDeviceToHost, h->post_stream));
         CK(cudaEventRecord(s.ev[5], h->post_stream));
-        st.scan_launches += 4;
+        st.scan_launches += 5;
         return ADSBCU_OK;
     };
     // host half of a chunk: its counters are on the host; candidate mode also copies the records out
@@ -419,6 +417,10 @@ int run_chunks(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, ui
         Slot &s = h->slot[c % kSlots];
         CK(cudaEventSynchronize(s.ev[5]));
         const ChunkCounters k = *s.h_ctr;
+        if (std::getenv("ADSBCU_ORDER_TIMING_PRINT"))
+            std::fprintf(stderr, "order chunk %u: revive %.1f us, look-back %.1f us, resolve starts +%.1f us, load+runs %.1f, rounds %.1f, emit %.1f, insert+end %.1f (n_full %u)\n", c,
+                         (k.dbg[1] - k.dbg[0]) * 1e-3, (k.dbg[2] - k.dbg[1]) * 1e-3, (k.dbg[3] - k.dbg[0]) * 1e-3, (k.dbg[4] - k.dbg[3]) * 1e-3,
+                         (k.dbg[5] - k.dbg[4]) * 1e-3, (k.dbg[6] - k.dbg[5]) * 1e-3, (k.dbg[7] - k.dbg[6]) * 1e-3, k.n_full);
         if (k.overflow) { if (failed_chunk == nchunks) failed_chunk = c; return ADSBCU_OK; }
         if (failed_chunk != nchunks) return ADSBCU_OK;                 // chunks after a failed one did not touch the state
         if (sink.cands) copy_candidates(s.h_cand, k.n_full, h->stream_pos, sink);
@@ -651,6 +653,7 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
     if (const char *v = std::getenv("ADSBCU_HOST_TPS")) h->host_tps = uint32_t(std::max(1, std::atoi(v)));
     if (const char *v = std::getenv("ADSBCU_LEVEL_GRID")) h->level_grid = uint32_t(std::max(1, std::atoi(v)));
     if (const char *v = std::getenv("ADSBCU_RESOLVE_SEQ")) h->force_sequential = std::atoi(v) != 0;
+    if (const char *v = std::getenv("ADSBCU_RESOLVE_BATCH")) h->resolve_batch = uint32_t(std::max(2, std::atoi(v)));
     const size_t nmax = c.max_feed_samples;
     h->nseg = uint32_t(h->sm_count) - spare;
     h->unit_positions = h->nseg * uint32_t(kFWarps) * uint32_t(kWTile);

@@ -5,12 +5,13 @@
 // address to the filter, carry last_message_end across mag_buf boundaries.  Round 1 replayed this on one host thread
 // (0.7 ms per 60 s capture, the slowest stage of the resident step).  Here it runs on the GPU, exactly:
 //
-//  phase 1 (one CTA per front-kernel segment)
+//  order_kernel (one CTA per front-kernel segment)
 //    * parked Address/Parity-style records whose address has been announced by now are evaluated from the symbol
 //      planes like the message kernel does;
 //    * the segment's records are rank-sorted by (position, phase);
-//  phase 2 (the CTA that finishes phase 1 last)
-//    * segments in index order are the chunk in stream order: prefix sum, compaction into one array;
+//    * segments in index order are the chunk in stream order: every CTA publishes its count, sums the counts before
+//      it and writes its sorted records (and a 16-byte view with the filter state folded in) to their final place;
+//  resolve_kernel (one CTA of 1024 threads)
 //    * the skip rule cannot reach across a gap of 288 samples (a message ends at most 288 samples after its start),
 //      so the record stream splits into independent RUNS there; the only state shared between runs is the ICAO
 //      filter.  Runs are resolved in parallel (contiguous blocks of runs per thread) against
@@ -105,14 +106,15 @@ __device__ __forceinline__ void map_insert_min(AddMap &m, uint32_t k, uint32_t p
 }
 
 // ---- one accepted message -> adsbcu_msg (what demodulate2400 hands to useModesMessage) ------------------------
-__device__ __forceinline__ void write_msg(adsbcu_msg *out, const FullRec &r, uint64_t a, int score, uint32_t block)
+__device__ __forceinline__ void write_msg(adsbcu_msg *out, const FullRec &r, uint64_t a, int score, uint32_t block, double level)
 {
     union { adsbcu_msg m; uint64_t w[7]; } u;
     static_assert(sizeof(adsbcu_msg) == 56, "adsbcu_msg layout");
     // sampleTimestamp of the mag_buf (sdr_ifile.c:202) + 5*j + 768 + phase; with 12e6/2.4e6 == 5 this is 5*a + 768 + phase
     // up to the double rounding of the block's base, which is reproduced here
-    const uint64_t blk = a / block, bstart = blk * block;
-    const uint64_t ts_base = uint64_t(__ddiv_rn(__dmul_rn(double(bstart), 12e6), 2400000.0));
+    const uint64_t bstart = (block & (block - 1u)) == 0u ? a & ~uint64_t(block - 1u) : a / block * block;
+    // (below 2^53 / 12e6 samples the product is exact and so is the quotient 5 * bstart: no double arithmetic needed)
+    const uint64_t ts_base = bstart < 750000000ull ? 5ull * bstart : uint64_t(__ddiv_rn(__dmul_rn(double(bstart), 12e6), 2400000.0));
     u.m.timestamp = ts_base + (a - bstart) * 5 + (8 + 56) * 12 + r.phase;
 #pragma unroll
     for (int b = 0; b < 14; ++b) { u.m.msg[b] = r.msg[b]; u.m.verbatim[b] = r.verbatim[b]; }
@@ -122,7 +124,7 @@ __device__ __forceinline__ void write_msg(adsbcu_msg *out, const FullRec &r, uin
     u.m.score = uint8_t(score);
     u.m.crc = r.crc;
     u.m.addr = r.addr;
-    u.w[6] = uint64_t(r.pos);                  // the level kernel turns the feed position into mm.signalLevel
+    u.m.signal_level = level;
     uint64_t *dst = reinterpret_cast<uint64_t *>(out);
 #pragma unroll
     for (int k = 0; k < 7; ++k) dst[k] = u.w[k];
@@ -181,34 +183,17 @@ __device__ __forceinline__ void resolve_range(const uint4 *view, uint32_t i0, ui
     }
 }
 
-struct FinishSmem {
-    AddMap cur, next;
-    uint32_t scan[kXThreads];
-    uint32_t nkeys_cur, nkeys_next, changed;
-    uint32_t total;
-    uint8_t rank[24];                          // score_rank by (kind, known)
-};
 struct SortSmem {
     uint32_t key[kSortCap];
-    uint32_t nrec, is_last, offset;
+    uint32_t nrec, offset;
 };
 
-__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t *scratch, uint32_t &total)
-{
-    const int tid = threadIdx.x;
-    scratch[tid] = v;
-    __syncthreads();
-    for (int d = 1; d < kXThreads; d <<= 1) {
-        const uint32_t t = tid >= d ? scratch[tid - d] : 0u;
-        __syncthreads();
-        scratch[tid] += t;
-        __syncthreads();
-    }
-    total = scratch[kXThreads - 1];
-    const uint32_t incl = scratch[tid];
-    __syncthreads();
-    return incl - v;
-}
+#ifdef ADSBCU_ORDER_TIMING            // debug: nanosecond marks of the order kernel in ChunkCounters::dbg (profiles/order_probe.py)
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define ORDER_MARK(k) do { if (threadIdx.x == 0) fa.c.ctr->dbg[k] = gtime(); } while (0)
+#else
+#define ORDER_MARK(k) do { } while (0)
+#endif
 
 __global__ void __launch_bounds__(kXThreads) order_kernel(FinishArgs fa)
 {
@@ -222,6 +207,7 @@ __global__ void __launch_bounds__(kXThreads) order_kernel(FinishArgs fa)
     {
         SortSmem &ss = *reinterpret_cast<SortSmem *>(smem_raw);
         const uint32_t seg = blockIdx.x;
+        if (seg == 0) ORDER_MARK(0);
         FullRec *rec = a.rec + size_t(seg) * a.rec_cap;
         const PhaseRec *pend = a.pend + size_t(seg) * a.pend_cap;
         const uint32_t n0 = min(a.rec_count[seg], a.rec_cap), npend = min(a.pend_count[seg], a.pend_cap);
@@ -253,6 +239,7 @@ __global__ void __launch_bounds__(kXThreads) order_kernel(FinishArgs fa)
             if (slot < a.rec_cap) fill_rec(rec[slot], p.pos, ph, fr, cl); else a.ctr->overflow = 1u;
         }
         __syncthreads();
+        if (seg == gridDim.x - 1) ORDER_MARK(1);
         const uint32_t n = min(ss.nrec, a.rec_cap);
         // rank sort by (position, phase): keys are unique
         if (n > uint32_t(kSortCap)) { if (tid == 0) a.ctr->overflow = 1u; }
@@ -275,6 +262,7 @@ __global__ void __launch_bounds__(kXThreads) order_kernel(FinishArgs fa)
         before = __reduce_add_sync(0xFFFFFFFFu, before);
         if (lane == 0 && before) atomicAdd(&ss.offset, before);
         __syncthreads();
+        if (seg == gridDim.x - 1) ORDER_MARK(2);
         const uint32_t offset = ss.offset;
         if (offset + n > a.full_cap) { if (tid == 0) a.ctr->overflow = 1u; }
         else if (n <= uint32_t(kSortCap)) {
@@ -292,194 +280,280 @@ __global__ void __launch_bounds__(kXThreads) order_kernel(FinishArgs fa)
                 fa.view[offset + rank] = v;
             }
         }
-        __syncthreads();
-        __threadfence();
-        if (tid == 0) ss.is_last = atomicAdd(fa.ticket, 1u) == gridDim.x - 1;
-        __syncthreads();
-        if (!ss.is_last) return;
-        __threadfence();
     }
+}
 
-    // ================= phase 2: the last CTA -- the ordered pass ===============================================
-    FinishSmem &sm = *reinterpret_cast<FinishSmem *>(smem_raw);
-    StreamState *st = fa.st;
+// ================= resolve_kernel: the ordered pass of demodulate2400 ===========================================
+// One CTA of 1024 threads.  The chunk's records are taken in batches of up to kRBatch that end at run boundaries; a
+// batch's 8-byte (position, flags) entries live in shared memory, so the per-run walks -- which are sequential by
+// nature and would otherwise pay an uncoalesced global load per record -- run at shared-memory latency.  A batch is
+// iterated to its fixed point (see the file header), its messages are written, its new addresses enter the filter
+// table, then the next batch starts from that state: exactly the chunk algorithm at a finer grain.
+constexpr int kRThreads = 1024;
+constexpr uint32_t kRBatch = 16384;
+
+struct ResolveSmem {
+    uint2 ent[kRBatch];                        // x: feed position, y: view flags (bits 0..15) | score of the accepted record << 16
+    AddMap cur, next;
+    uint32_t scan[kRThreads];
+    uint32_t warp_tot[kRThreads / 32 + 1];
+    uint32_t nkeys_cur, nkeys_next, changed, nruns, cut, last_acc, batch_msgs;
+    uint8_t rank[24];                          // score_rank by (kind, known)
+};
+
+// exclusive prefix of a per-thread flag over the CTA: ballot inside the warp, one shuffle scan of the 32 warp totals
+__device__ __forceinline__ uint32_t block_flag_scan(bool f, uint32_t *warp_tot, uint32_t &total)
+{
+    static_assert(kRThreads == 1024, "one lane per warp total");
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t bal = __ballot_sync(0xFFFFFFFFu, f);
+    if (lane == 0) warp_tot[warp] = __popc(bal);
     __syncthreads();
-    if (tid == 0) *fa.ticket = 0;                                             // ready for the next chunk
-    uint32_t n_full = 0;
+    if (warp == 0) {
+        const uint32_t c = warp_tot[lane];
+        uint32_t incl = c;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
+        warp_tot[lane] = incl - c;             // exclusive prefix of this warp's total
+        if (lane == 31) warp_tot[32] = incl;
+    }
+    __syncthreads();
+    const uint32_t before = warp_tot[warp];
+    total = warp_tot[32];
+    __syncthreads();
+    return before + __popc(bal & ((1u << lane) - 1u));
+}
+
+__global__ void __launch_bounds__(kRThreads, 1) resolve_kernel(FinishArgs fa)
+{
+    ADSBCU_DYN_SMEM(smem_raw);
+    ResolveSmem &sm = *reinterpret_cast<ResolveSmem *>(smem_raw);
+    const ChunkArgs &a = fa.c;
+    StreamState *st = fa.st;
+    const int tid = threadIdx.x;
+
+    ORDER_MARK(3);
+    // records of the chunk; a failed chunk (or a failed earlier chunk of the feed) leaves the stream state alone
+    uint32_t n = 0;
     {
         uint32_t mine = 0;
-        for (uint32_t s2 = tid; s2 < a.nseg; s2 += kXThreads) mine += a.rec_count[s2];
-        block_exclusive_scan(mine, sm.scan, n_full);
-        if (n_full > a.full_cap) n_full = 0;                                   // (the overflow flag is set)
-    }
-    const bool failed = a.ctr->overflow != 0u || st->poison != 0u;
-    if (tid == 0) {
-        a.ctr->n_full = n_full;
-        if (failed) st->poison = 1u;                                           // later chunks in flight must not touch the state
-    }
-    if (failed || fa.candidates_only) {
+        for (uint32_t s2 = tid; s2 < a.nseg; s2 += kRThreads) mine += a.rec_count[s2];
+        mine = __reduce_add_sync(0xFFFFFFFFu, mine);
+        if (tid == 0) sm.cut = 0;
         __syncthreads();
-        if (tid == 0) { __threadfence_system(); }
-        return;
+        if ((tid & 31) == 0 && mine) atomicAdd(&sm.cut, mine);
+        __syncthreads();
+        n = sm.cut;
+        __syncthreads();
     }
+    const bool failed = a.ctr->overflow != 0u || st->poison != 0u || n > a.full_cap;
+    if (tid == 0) {
+        a.ctr->n_full = failed ? 0u : n;
+        if (failed) { st->poison = 1u; a.ctr->overflow = 1u; }                 // later chunks in flight must not touch the state
+    }
+    if (failed || fa.candidates_only) return;
 
     const FullRec *recs = a.ordered;
-    const uint32_t n = n_full;
-    const uint4 *view = fa.view;                  // 16-byte views, filter state as of the chunk's start folded in by phase 1
-    uint8_t *dec = fa.dec;                        // score of every accepted record, 0 for the others
+    const uint4 *view = fa.view;                  // 16-byte views, filter state as of the chunk's start folded in by the order kernel
     const uint32_t block = fa.block_samples;
     const int bshift = (block & (block - 1u)) == 0u ? 31 - __clz(int(block)) : -1;
     auto blk_of = [&](uint64_t x) { return bshift >= 0 ? x >> bshift : x / block; };
     const uint64_t feed_base = fa.feed_base;
-    adsbcu_msg *out = fa.chunk_msgs;              // n_full entries at most: every accepted message has its own record
+    uint2 *out = fa.accepted;                     // (record index, score) of every accepted message: n entries at most
     const uint64_t feed_count = st->n_out;
     uint32_t *run_start = fa.run_start;
-    if (tid < 22) sm.rank[tid] = uint8_t(rank_of(uint32_t(tid) >> 1, (tid & 1) != 0));
-    for (uint32_t i = tid; i < kMapSlots; i += kXThreads) { sm.cur.key[i] = kMapEmpty; sm.cur.pos[i] = kMapEmpty; sm.next.key[i] = kMapEmpty; sm.next.pos[i] = kMapEmpty; }
-    if (tid == 0) { sm.nkeys_cur = 0; sm.nkeys_next = 0; sm.changed = 0; sm.total = 0; }
-
-    // runs: a record starts a run when it is 288 or more samples after its predecessor
-    uint32_t R = 0;
-    {
-        const uint32_t per = (n + kXThreads - 1) / kXThreads;
-        const uint32_t i0 = min(n, tid * per), i1 = min(n, i0 + per);
-        uint32_t mine = 0;
-        for (uint32_t i = i0; i < i1; ++i) mine += (i == 0 || view[i].x - view[i - 1].x >= 288u);
-        uint32_t off = block_exclusive_scan(mine, sm.scan, R);
-        for (uint32_t i = i0; i < i1; ++i)
-            if (i == 0 || view[i].x - view[i - 1].x >= 288u) run_start[off++] = i;
-        if (tid == 0) run_start[R] = n;
-        __syncthreads();
-    }
-    const uint32_t rper = (R + kXThreads - 1) / kXThreads;
-    const uint32_t r0 = min(R, tid * rper), r1 = min(R, r0 + rper);
     const SkipState carried{st->has_last, st->last_a, st->last_lme};
-
+    if (tid < 22) sm.rank[tid] = uint8_t(rank_of(uint32_t(tid) >> 1, (tid & 1) != 0));
+    if (tid == 0) sm.last_acc = 0;
+    uint32_t total = 0;                           // messages written so far (uniform)
+    uint32_t ia = 0;
     bool sequential = fa.force_sequential != 0;
-    for (int round = 0; !sequential; ++round) {
-        const bool use_map = sm.nkeys_cur != 0u;
-        for (uint32_t r = r0; r < r1; ++r) {
-            SkipState ss = r == 0 ? carried : SkipState{0u, 0, 0};
-            uint32_t i = run_start[r];
-            const uint32_t i1 = run_start[r + 1];
-            uint4 cur = view[i];
-            while (i < i1) {
-                const uint32_t pos = cur.x;
-                const uint64_t pa = feed_base + pos;
-                // inside the mag_buf of the last accepted message scanning resumes 18 samples before its end
-                // (j = last_message_end - 19, then ++j); a later mag_buf starts exactly at its end (demod_2400.c:410-443)
-                const bool skip = ss.has_last && pa < (blk_of(pa) == blk_of(ss.last_a) ? ss.last_lme - 18 : ss.last_lme);
-                uint32_t best = 0, bi = i, best_w = 0, best_add = kUnchecked;     // SR_NOT_SET
-                do {                                // phases ascending; strict > keeps the lowest phase on ties
-                    const bool known = (cur.w & 0x200u) || (use_map && map_lookup(sm.cur, cur.y) < pos);
-                    const uint32_t sc = sm.rank[2u * (cur.w & 0xFFu) + (known ? 1u : 0u)];
-                    if (sc > best) { best = sc; bi = i; best_w = cur.w; best_add = cur.z; }
-                    dec[i] = 0;
-                    ++i;
-                    if (i < i1) cur = view[i];
-                } while (i < i1 && cur.x == pos);
-                if (skip || best < uint32_t(kAcceptThreshold)) continue;
-                dec[bi] = uint8_t(best);
-                if (best_w & 0x400u) map_insert_min(sm.next, best_add, pos, &sm.nkeys_next);
-                ss.has_last = 1u;
-                ss.last_a = pa;
-                ss.last_lme = pa + uint64_t((((best_w & 0x100u) ? 112 : 56) + 8) * 12 / 5);
+
+    while (ia < n && !sequential) {
+        // ---- the batch's entries into shared memory (coalesced); later batches see the table the earlier ones left ----
+        const uint32_t ib_t = min(n, ia + min(kRBatch, max(fa.batch, 2u)));
+#pragma unroll 4
+        for (uint32_t i = ia + tid; i < ib_t; i += kRThreads) {
+            const uint4 v = view[i];
+            uint32_t w = v.w & 0xFFFFu;
+            if (ia) {
+                if (!(w & 0x200u) && icao_test(st, v.y)) w |= 0x200u;
+                if (v.z != kUnchecked) w = (w & ~0x400u) | (icao_probe(st->table[st->active], v.z) ? 0u : 0x400u);
             }
+            sm.ent[i - ia] = make_uint2(v.x, w);
         }
+        for (uint32_t i = tid; i < kMapSlots; i += kRThreads) { sm.cur.key[i] = kMapEmpty; sm.cur.pos[i] = kMapEmpty; sm.next.key[i] = kMapEmpty; sm.next.pos[i] = kMapEmpty; }
+        if (tid == 0) { sm.nkeys_cur = 0; sm.nkeys_next = 0; sm.changed = 0; sm.nruns = 0; sm.cut = 0; sm.batch_msgs = 0; }
         __syncthreads();
-        // did this round reproduce the map it was computed with?
-        if (sm.nkeys_next != sm.nkeys_cur && tid == 0) sm.changed = 1u;
-        for (uint32_t i = tid; i < kMapSlots; i += kXThreads)
-            if (sm.next.key[i] != kMapEmpty && map_lookup(sm.cur, sm.next.key[i]) != sm.next.pos[i]) sm.changed = 1u;
-        __syncthreads();
-        const bool changed = sm.changed != 0u;
-        const uint32_t nk = sm.nkeys_next;
-        __syncthreads();
-        if (nk > kMapMaxKeys || st->active_count + nk >= kIcaoSlots - 1 || round >= 12) { sequential = true; break; }
-        if (!changed) break;
-        for (uint32_t i = tid; i < kMapSlots; i += kXThreads) {
-            sm.cur.key[i] = sm.next.key[i]; sm.cur.pos[i] = sm.next.pos[i];
-            sm.next.key[i] = kMapEmpty; sm.next.pos[i] = kMapEmpty;
+        auto starts_run = [&](uint32_t i) { return i == ia || sm.ent[i - ia].x - sm.ent[i - 1 - ia].x >= 288u; };
+        // ---- the batch ends at a run boundary: the last run start inside it, unless it reaches the chunk's end ----
+        uint32_t ib = ib_t;
+        if (ib_t < n) {
+            uint32_t best = 0;
+            for (uint32_t i = ia + 1 + tid; i < ib_t; i += kRThreads) if (starts_run(i)) best = i;    // ascending per thread
+            best = __reduce_max_sync(0xFFFFFFFFu, best);
+            if ((tid & 31) == 0 && best) atomicMax(&sm.cut, best);
+            __syncthreads();
+            ib = sm.cut;
+            if (ib == 0) { sequential = true; break; }                   // one run longer than a batch: replay sequentially
         }
-        if (tid == 0) { sm.nkeys_cur = nk; sm.nkeys_next = 0; sm.changed = 0; }
+        // ---- runs: a record starts a run when it is 288 or more samples after its predecessor ----------------------
+        uint32_t R = 0;
+        for (uint32_t t0 = ia; t0 < ib; t0 += kRThreads) {
+            const uint32_t i = t0 + tid;
+            const bool f = i < ib && starts_run(i);
+            uint32_t cnt = 0;
+            const uint32_t off = block_flag_scan(f, sm.warp_tot, cnt);
+            if (f) run_start[R + off] = i;
+            R += cnt;
+        }
+        if (tid == 0) run_start[R] = ib;
         __syncthreads();
-    }
+        if (ia == 0) ORDER_MARK(4);
 
-    if (sequential) {
-        // the reference's own loop, one thread, on the tables in global memory: exact whatever they hold
-        if (tid == 0) {
-            SkipState ss = carried;
-            uint64_t k = 0;
-            resolve_range(view, 0, n, feed_base, block, ss,
-                          [&](uint32_t key, uint32_t) { return icao_test(st, key); },
-                          [&](uint32_t idx, int score, uint64_t pa) {
-                              write_msg(out + k, recs[idx], pa, score, block);
-                              ++k;
-                              if (recs[idx].add_key != kUnchecked) icao_add(st, recs[idx].add_key);
-                          });
-            st->has_last = ss.has_last; st->last_a = ss.last_a; st->last_lme = ss.last_lme;
-            st->n_out = feed_count + k;
-            a.ctr->n_msgs = uint32_t(k);
-            a.ctr->msg_base = feed_count;
-            __threadfence_system();
-        }
-        return;
-    }
-
-    // emission, parallel over the records: every accepted record becomes one message, in stream order
-    {
-        const uint32_t per = (n + kXThreads - 1) / kXThreads;
-        const uint32_t i0 = min(n, tid * per), i1 = min(n, i0 + per);
-        uint32_t mine = 0, last = 0;                                       // last: index + 1 of my last accepted record
-        for (uint32_t i = i0; i < i1; ++i) if (dec[i]) { ++mine; last = i + 1; }
-        uint32_t total = 0;
-        uint32_t off = block_exclusive_scan(mine, sm.scan, total);
-        for (uint32_t i = i0; i < i1; ++i)
-            if (const uint32_t sc = dec[i]) write_msg(out + off++, recs[i], feed_base + recs[i].pos, int(sc), block);
-        // the stream's skip state: the last accepted message of the chunk
-        sm.scan[tid] = last;
-        __syncthreads();
-        for (int d = kXThreads / 2; d; d >>= 1) {
-            if (tid < d) sm.scan[tid] = max(sm.scan[tid], sm.scan[tid + d]);
+        // ---- rounds: every thread walks its runs (r = tid, tid + 1024, ...) against the batch's first_add map ----------
+        for (int round = 0;; ++round) {
+            const bool use_map = sm.nkeys_cur != 0u;
+            for (uint32_t r = tid; r < R; r += kRThreads) {
+                SkipState ss = (ia == 0 && r == 0) ? carried : SkipState{0u, 0, 0};
+                uint32_t i = run_start[r];
+                const uint32_t i1 = run_start[r + 1];
+                uint2 cur = sm.ent[i - ia];
+                while (i < i1) {
+                    const uint32_t pos = cur.x;
+                    const uint64_t pa = feed_base + pos;
+                    // inside the mag_buf of the last accepted message scanning resumes 18 samples before its end
+                    // (j = last_message_end - 19, then ++j); a later mag_buf starts exactly at its end (demod_2400.c:410-443)
+                    const bool skip = ss.has_last && pa < (blk_of(pa) == blk_of(ss.last_a) ? ss.last_lme - 18 : ss.last_lme);
+                    uint32_t best = 0, bi = i, best_w = 0;                          // SR_NOT_SET
+                    do {                            // phases ascending; strict > keeps the lowest phase on ties
+                        const uint32_t w = cur.y & 0xFFFFu;
+                        const bool known = (w & 0x200u) || (use_map && map_lookup(sm.cur, view[i].y) < pos);
+                        const uint32_t sc = sm.rank[2u * (w & 0xFFu) + (known ? 1u : 0u)];
+                        if (sc > best) { best = sc; bi = i; best_w = w; }
+                        sm.ent[i - ia].y = w;      // no score
+                        ++i;
+                        if (i < i1) cur = sm.ent[i - ia];
+                    } while (i < i1 && cur.x == pos);
+                    if (skip || best < uint32_t(kAcceptThreshold)) continue;
+                    sm.ent[bi - ia].y = best_w | (best << 16);
+                    if (best_w & 0x400u) map_insert_min(sm.next, view[bi].z, pos, &sm.nkeys_next);
+                    ss.has_last = 1u;
+                    ss.last_a = pa;
+                    ss.last_lme = pa + uint64_t((((best_w & 0x100u) ? 112 : 56) + 8) * 12 / 5);
+                }
+            }
+            __syncthreads();
+            // did this round reproduce the map it was computed with?
+            if (sm.nkeys_next != sm.nkeys_cur && tid == 0) sm.changed = 1u;
+            for (uint32_t i = tid; i < kMapSlots; i += kRThreads)
+                if (sm.next.key[i] != kMapEmpty && map_lookup(sm.cur, sm.next.key[i]) != sm.next.pos[i]) sm.changed = 1u;
+            __syncthreads();
+            const bool changed = sm.changed != 0u;
+            const uint32_t nk = sm.nkeys_next;
+            __syncthreads();
+            if (nk > kMapMaxKeys || st->active_count + nk >= kIcaoSlots - 1 || round >= 12) { sequential = true; break; }
+            if (!changed) break;
+            for (uint32_t i = tid; i < kMapSlots; i += kRThreads) {
+                sm.cur.key[i] = sm.next.key[i]; sm.cur.pos[i] = sm.next.pos[i];
+                sm.next.key[i] = kMapEmpty; sm.next.pos[i] = kMapEmpty;
+            }
+            if (tid == 0) { sm.nkeys_cur = nk; sm.nkeys_next = 0; sm.changed = 0; }
             __syncthreads();
         }
-        if (tid == 0) {
-            if (const uint32_t li = sm.scan[0]) {
-                const uint4 v = view[li - 1];
-                const uint64_t pa = feed_base + v.x;
-                st->has_last = 1u; st->last_a = pa;
-                st->last_lme = pa + uint64_t((((v.w & 0x100u) ? 112 : 56) + 8) * 12 / 5);
-            }
-            st->n_out = feed_count + total;
-            a.ctr->n_msgs = total;
-            a.ctr->msg_base = feed_count;
+        if (sequential) break;
+        if (ia == 0) ORDER_MARK(5);
+
+        // ---- emission, parallel over the batch's records: every accepted record becomes one message, in stream order.
+        // First the offsets (a block scan per 1024 records; the offset replaces the position in the entry), then all
+        // the messages without a barrier in between, so that the record reads of the whole batch are in flight together.
+        uint32_t batch_total = 0;
+        for (uint32_t t0 = ia; t0 < ib; t0 += kRThreads) {
+            const uint32_t i = t0 + tid;
+            const uint32_t sc = i < ib ? sm.ent[i - ia].y >> 16 : 0u;
+            uint32_t cnt = 0;
+            const uint32_t off = block_flag_scan(sc != 0u, sm.warp_tot, cnt);
+            if (sc) sm.ent[i - ia].x = batch_total + off;
+            batch_total += cnt;
         }
+        uint32_t my_last = 0;
+#pragma unroll 4
+        for (uint32_t i = ia + tid; i < ib; i += kRThreads) {
+            const uint2 e = sm.ent[i - ia];
+            if (e.y >> 16) {
+                out[total + e.x] = make_uint2(i, e.y >> 16);
+                my_last = i + 1u;
+            }
+        }
+        my_last = __reduce_max_sync(0xFFFFFFFFu, my_last);
+        if ((tid & 31) == 0 && my_last) atomicMax(&sm.last_acc, my_last);
+        total += batch_total;
+        if (ia == 0) ORDER_MARK(6);
+        // ---- new addresses enter the active table (icao_filter.c:71-84).  The reference inserts them in stream order;
+        // which slot of a probe chain an address lands in changes no answer of icaoFilterTest while the table has room
+        // (and a batch that could fill it takes the sequential replay), so the insertions run in parallel.
+        {
+            uint32_t *t = st->table[st->active];
+            uint32_t added = 0;
+            for (uint32_t i = tid; i < kMapSlots; i += kRThreads) {
+                const uint32_t v = sm.cur.key[i];
+                if (v == kMapEmpty) continue;
+                uint32_t h = icao_hash(v);
+                for (uint32_t probes = 0; probes < kIcaoSlots; ++probes) {
+                    const uint32_t e = atomicCAS(&t[h], kIcaoEmpty, v);
+                    if (e == kIcaoEmpty) { ++added; break; }
+                    if (e == v) break;
+                    h = (h + 1) & (kIcaoSlots - 1);
+                }
+            }
+            if (added) atomicAdd(&st->active_count, added);
+        }
+        __threadfence();
+        __syncthreads();
+        ia = ib;
     }
-    // New addresses enter the active table (icao_filter.c:71-84).  The reference inserts them in stream order; which
-    // slot of a probe chain an address lands in changes no answer of icaoFilterTest while the table has room (and a
-    // chunk that could fill it took the sequential replay above), so the insertions run in parallel.
-    {
-        uint32_t *t = st->table[st->active];
-        uint32_t added = 0;
-        for (uint32_t i = tid; i < kMapSlots; i += kXThreads) {
-            const uint32_t v = sm.cur.key[i];
-            if (v == kMapEmpty) continue;
-            uint32_t h = icao_hash(v);
-            for (uint32_t probes = 0; probes < kIcaoSlots; ++probes) {
-                const uint32_t e = atomicCAS(&t[h], kIcaoEmpty, v);
-                if (e == kIcaoEmpty) { ++added; break; }
-                if (e == v) break;
-                h = (h + 1) & (kIcaoSlots - 1);
-            }
+
+    if (sequential && ia < n) {
+        // the reference's own loop from record `ia` on, one thread, on the tables in global memory: exact whatever they hold
+        __syncthreads();
+        if (tid == 0) {
+            SkipState ss = ia == 0 ? carried : SkipState{0u, 0, 0};
+            uint64_t k = total;
+            uint32_t last = sm.last_acc;
+            resolve_range(view, ia, n, feed_base, block, ss,
+                          [&](uint32_t key, uint32_t) { return icao_test(st, key); },
+                          [&](uint32_t idx, int score, uint64_t) {
+                              out[k] = make_uint2(idx, uint32_t(score));
+                              ++k;
+                              last = idx + 1u;
+                              if (recs[idx].add_key != kUnchecked) icao_add(st, recs[idx].add_key);
+                          });
+            sm.last_acc = last;
+            sm.batch_msgs = uint32_t(k);
         }
-        if (added) atomicAdd(&st->active_count, added);
+        __syncthreads();
+        total = sm.batch_msgs;
     }
     __syncthreads();
-    if (tid == 0) __threadfence_system();
+    if (tid == 0) {
+        // the stream's skip state: the last accepted message of the chunk
+        if (const uint32_t li = sm.last_acc) {
+            const uint4 v = view[li - 1];
+            const uint64_t pa = feed_base + v.x;
+            st->has_last = 1u; st->last_a = pa;
+            st->last_lme = pa + uint64_t((((v.w & 0x100u) ? 112 : 56) + 8) * 12 / 5);
+        }
+        st->n_out = feed_count + total;
+        a.ctr->n_msgs = total;
+        a.ctr->msg_base = feed_count;
+        __threadfence_system();
+    }
+    ORDER_MARK(7);
 }
 
-// mm.signalLevel of the accepted messages of one chunk (demod_2400.c:382-403): mean squared magnitude over the
-// signal window, IEEE double divisions as on the host.  One warp per message; the finished 56-byte record goes to the
+
+// The accepted messages of one chunk, one warp per message: mm.signalLevel (demod_2400.c:382-403: mean squared
+// magnitude over the signal window, IEEE double divisions as on the host), then the 56-byte adsbcu_msg goes to the
 // feed's output array (mapped host memory or the caller's pinned buffer), where the host never touches it again.
 __global__ void __launch_bounds__(256) level_kernel(FinishArgs fa)
 {
@@ -489,15 +563,10 @@ __global__ void __launch_bounds__(256) level_kernel(FinishArgs fa)
     const uint32_t n = a.ctr->n_msgs;
     const uint64_t base = a.ctr->msg_base;
     for (uint32_t k = gwarp; k < n; k += nwarps) {
-        const uint64_t *src = reinterpret_cast<const uint64_t *>(fa.chunk_msgs + k);
-        const uint64_t w = lane < 7 ? src[lane] : 0ull;
-        const uint32_t pos = uint32_t(__shfl_sync(0xFFFFFFFFu, w, 6));
-        const uint32_t vb0 = uint32_t(__shfl_sync(0xFFFFFFFFu, w, 2) >> 48) & 0xFFu;       // verbatim[0]: byte 22 of the record
-        const double lvl = signal_level_warp(a, pos, vb0 >> 3, lane);
-        if (base + k < fa.out_cap && lane < 7) {
-            uint64_t *dst = reinterpret_cast<uint64_t *>(fa.out + base + k);
-            dst[lane] = lane == 6 ? uint64_t(__double_as_longlong(lvl)) : w;
-        }
+        const uint2 acc = fa.accepted[k];
+        const FullRec &r = a.ordered[acc.x];
+        const double lvl = signal_level_warp(a, r.pos, uint32_t(r.verbatim[0]) >> 3, lane);
+        if (lane == 0 && base + k < fa.out_cap) write_msg(fa.out + base + k, r, fa.feed_base + r.pos, int(acc.y), fa.block_samples, lvl);
     }
 }
 
@@ -557,18 +626,17 @@ __global__ void filter_expire_kernel(StreamState *st, uint32_t *bitmap, uint32_t
 
 }  // namespace
 
-size_t finish_smem_bytes() { return sizeof(FinishSmem) > sizeof(SortSmem) ? sizeof(FinishSmem) : sizeof(SortSmem); }
-
 cudaError_t init_finish()
 {
-    return cudaFuncSetAttribute(order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(finish_smem_bytes()));
+    return cudaFuncSetAttribute(resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(ResolveSmem)));
 }
 
-// order_kernel: one CTA per segment; level_kernel: `level_grid` CTAs of 8 warps (skipped for candidate scans)
+// order_kernel: one CTA per segment; resolve_kernel: one CTA; level kernels: `level_grid` CTAs of 8 warps
 cudaError_t launch_finish(const FinishArgs &fa, uint32_t level_grid, cudaStream_t s)
 {
     if (fa.c.pos_end <= fa.c.pos_begin || !fa.c.nseg) return cudaSuccess;
-    ADSBCU_LAUNCH(order_kernel, fa.c.nseg, kXThreads, finish_smem_bytes(), s, fa);
+    ADSBCU_LAUNCH(order_kernel, fa.c.nseg, kXThreads, sizeof(SortSmem), s, fa);
+    ADSBCU_LAUNCH(resolve_kernel, 1, kRThreads, sizeof(ResolveSmem), s, fa);
     if (fa.candidates_only) ADSBCU_LAUNCH(level_records_kernel, level_grid, 256, 0, s, fa);
     else ADSBCU_LAUNCH(level_kernel, level_grid, 256, 0, s, fa);
     return cudaGetLastError();

@@ -152,6 +152,7 @@ struct ChunkCounters {
     unsigned int n_msgs;         // messages the ordered pass accepted in this chunk
     unsigned int pad2;
     unsigned long long msg_base; // ... and how many the feed had accepted before it
+    unsigned long long dbg[8];   // -DADSBCU_ORDER_TIMING: globaltimer marks of the order kernel
 };
 
 // One chunk = a contiguous range of start positions of the current feed.  Position p (feed-relative,
@@ -231,16 +232,15 @@ struct FinishArgs {
     ChunkArgs    c;
     StreamState *st;
     struct ::adsbcu_msg *out;    uint64_t out_cap;       // accepted messages of the feed, stream order (device-visible memory)
-    struct ::adsbcu_msg *chunk_msgs;                     // [full_cap] this chunk's accepted messages before their signal level is known
+    uint2       *accepted;       // [full_cap] (index into ordered[], score_rank) of this chunk's accepted messages, stream order
     uint64_t     feed_base;      // stream coordinate of the feed's position 0
     uint32_t     block_samples;  // the reference's mag_buf length (skip rule at block boundaries, timestamps)
     uint32_t     candidates_only;    // sharded scans: stop after the ordered array
     uint32_t     force_sequential;   // test knob: always take the one-thread replay
-    uint32_t    *ticket;         // phase-1 completion counter
+    uint32_t     batch;              // records per batch of the ordered pass (test knob; the kernel caps it at its shared-memory size)
     unsigned long long *seg_flag;    // [nseg] epoch << 32 | records of the segment, published by its CTA
     uint32_t     epoch;          // chunk sequence number (never 0): tells this chunk's flags from older ones
     uint32_t    *run_start;      // [full_cap + 1]
-    uint8_t     *dec;            // [full_cap] score of the accepted records
     uint4       *view;           // [full_cap] 16-byte view of the ordered records for the ordered pass
     PhaseRec    *deferred;       uint32_t deferred_cap;  uint32_t *n_deferred;   // sharded scans: still-unknown parked records
 };

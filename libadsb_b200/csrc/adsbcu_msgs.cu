@@ -17,6 +17,9 @@
 namespace adsbcu {
 namespace {
 
+#ifndef ADSBCU_MSG_MINCTAS            // resident CTAs per SM the register allocation aims for (measurement knob)
+#define ADSBCU_MSG_MINCTAS 6
+#endif
 constexpr int kMThreads = 256;
 constexpr int kMWarps = kMThreads / 32;
 constexpr int kMRound = kMThreads;             // preambles per round: 32 per warp
@@ -26,10 +29,11 @@ struct MsgSmem {
     uint32_t crcb[11 * 256];                   // DevTables::crc_byte
     uint32_t occ_long[kSyndSlotsLong / 32], occ_short[kSyndSlotsShort / 32];
     uint32_t queue[kMWarps][160];              // per warp: 112-bit items from the front, 56-bit items from the back: lane | (phase-4) << 8
+    uint32_t slow[kMWarps][160];               // per warp: items that need the general classification
     uint32_t round_first[kMaxSeg + 1];         // first round of every segment
 };
 
-__global__ void __launch_bounds__(kMThreads) message_kernel(ChunkArgs a)
+__global__ void __launch_bounds__(kMThreads, ADSBCU_MSG_MINCTAS) message_kernel(ChunkArgs a)
 {
     ADSBCU_DYN_SMEM(smem_raw);
     MsgSmem &sm = *reinterpret_cast<MsgSmem *>(smem_raw);
@@ -90,14 +94,27 @@ __global__ void __launch_bounds__(kMThreads) message_kernel(ChunkArgs a)
             nshort += __popc(bs);
         }
         __syncwarp();
+        // parked records of a pass: one reservation in the segment's list per warp
+        auto park_records = [&](bool park, const PhaseRec &parked) {
+            const uint32_t bp = __ballot_sync(0xFFFFFFFFu, park);
+            if (!bp) return;
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(&a.pend_count[seg], uint32_t(__popc(bp)));
+            base = __shfl_sync(0xFFFFFFFFu, base, 0);
+            if (park) {
+                const uint32_t slot = base + __popc(bp & ((1u << lane) - 1u));
+                if (slot < a.pend_cap) a.pend[size_t(seg) * a.pend_cap + slot] = parked; else a.ctr->overflow = 1u;
+            }
+        };
         // C2: one item per lane and pass
+        uint32_t nslow = 0;
         for (uint32_t it0 = 0; it0 < nlong + nshort; it0 += 32) {
             const uint32_t it = it0 + lane;
             const bool live = it < nlong + nshort;
             const bool is_long = it < nlong;
             const uint32_t item = live ? (is_long ? queue[it] : queue[159u - (it - nlong)]) : 0u;
             const uint32_t cpos = __shfl_sync(0xFFFFFFFFu, mypos, int(item & 31u)), ph = 4u + (item >> 8);
-            bool park = false;
+            bool park = false, slow = false;
             PhaseRec parked{0u, 0u};
             if (live) {
                 const uint32_t t0 = 5u * (cpos + kFLead + 19u) + ph;
@@ -117,35 +134,46 @@ __global__ void __launch_bounds__(kMThreads) message_kernel(ChunkArgs a)
                         verdict = 2;                                                  // announced address: evaluated record
                     }
                 }
-                if (verdict == 2) {
-                    const Frame f = frame_from_words(M, is_long);
-                    const Classified cl = classify(f, xs, xl, a.tab, sm.occ_long, sm.occ_short);
-                    if (cl.keep) {
-                        const uint32_t bi = bitmap_index(cl.test_key);
-                        if (cl.kind == K_DF17_0 || cl.kind == K_DF11_ACQ_0 || (cl.kind == K_DF18_0 && !df18_non_icao(cl.fixed)))
-                            atomicOr(&a.bitmap[bi >> 5], 1u << (bi & 31));
-                        if (rank_of(cl.kind, false) < kAcceptThreshold && !((a.bitmap[bi >> 5] >> (bi & 31)) & 1u)) {
-                            park = true;
-                            parked = PhaseRec{pos, bi | ((ph - 4u) << 25) | (cl.kind << 28)};
-                        } else {
-                            const uint32_t slot = atomicAdd(&a.rec_count[seg], 1u);
-                            if (slot < a.rec_cap) fill_rec(a.rec[size_t(seg) * a.rec_cap + slot], pos, ph, f, cl);
-                            else a.ctr->overflow = 1u;
-                        }
+                slow = verdict == 2;
+            }
+            // the rare general case is queued: it runs after the passes, several lanes at a time instead of one
+            const uint32_t bq = __ballot_sync(0xFFFFFFFFu, slow);
+            if (slow) sm.slow[warp][nslow + __popc(bq & ((1u << lane) - 1u))] = item | (is_long ? 0x10000u : 0u);
+            nslow += __popc(bq);
+            park_records(park, parked);
+        }
+        __syncwarp();
+        // the queued items: slicing again is cheaper than carrying 112 bits per lane through the passes
+        for (uint32_t s0 = 0; s0 < nslow; s0 += 32) {
+            const bool live = s0 + lane < nslow;
+            const uint32_t item = live ? sm.slow[warp][s0 + lane] : 0u;
+            const bool is_long = (item & 0x10000u) != 0u;
+            const uint32_t cpos = __shfl_sync(0xFFFFFFFFu, mypos, int(item & 31u)), ph = 4u + ((item >> 8) & 7u);
+            bool park = false;
+            PhaseRec parked{0u, 0u};
+            if (live) {
+                const uint32_t t0 = 5u * (cpos + kFLead + 19u) + ph;
+                const uint32_t c = t0 % 12u, n0 = t0 / 12u;
+                uint32_t M[4], xs, xl;
+                slice_planes(a.planes + size_t(c) * a.plane_stride + n0 / 10u, n0 % 10u, is_long, sm.crcb, fixable_short, M, xs, xl);
+                const uint32_t pos = a.pos_begin + cpos;
+                const Frame f = frame_from_words(M, is_long);
+                const Classified cl = classify(f, xs, xl, a.tab, sm.occ_long, sm.occ_short);
+                if (cl.keep) {
+                    const uint32_t bi = bitmap_index(cl.test_key);
+                    if (cl.kind == K_DF17_0 || cl.kind == K_DF11_ACQ_0 || (cl.kind == K_DF18_0 && !df18_non_icao(cl.fixed)))
+                        atomicOr(&a.bitmap[bi >> 5], 1u << (bi & 31));
+                    if (rank_of(cl.kind, false) < kAcceptThreshold && !((a.bitmap[bi >> 5] >> (bi & 31)) & 1u)) {
+                        park = true;
+                        parked = PhaseRec{pos, bi | ((ph - 4u) << 25) | (cl.kind << 28)};
+                    } else {
+                        const uint32_t slot = atomicAdd(&a.rec_count[seg], 1u);
+                        if (slot < a.rec_cap) fill_rec(a.rec[size_t(seg) * a.rec_cap + slot], pos, ph, f, cl);
+                        else a.ctr->overflow = 1u;
                     }
                 }
             }
-            // the pass's parked records: one reservation in the segment's list per warp
-            const uint32_t bp = __ballot_sync(0xFFFFFFFFu, park);
-            if (bp) {
-                uint32_t base = 0;
-                if (lane == 0) base = atomicAdd(&a.pend_count[seg], uint32_t(__popc(bp)));
-                base = __shfl_sync(0xFFFFFFFFu, base, 0);
-                if (park) {
-                    const uint32_t slot = base + __popc(bp & ((1u << lane) - 1u));
-                    if (slot < a.pend_cap) a.pend[size_t(seg) * a.pend_cap + slot] = parked; else a.ctr->overflow = 1u;
-                }
-            }
+            park_records(park, parked);
         }
         __syncwarp();
     }
