@@ -196,7 +196,9 @@ def main():
     dev = host.cuda(non_blocking=False)
     hview = host.numpy()
     d = adsbcu.Demod1090(nfix_crc=args.nfix, fix_df=1, max_feed_samples=max(n, 1 << 20), device=local_rank)
-    out = np.zeros(max(4096, n // 500), dtype=adsbcu.MSG_DTYPE)
+    # out[] in pinned memory: the engine's level kernel writes the accepted messages there itself (no host copy)
+    out_pinned = torch.zeros(max(4096, n // 500) * adsbcu.MSG_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
+    out = out_pinned.numpy().view(adsbcu.MSG_DTYPE)
 
     def step_resident():
         d.reset(True)

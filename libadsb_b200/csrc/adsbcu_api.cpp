@@ -80,7 +80,7 @@ struct IcaoFilter {
 
 }  // namespace
 
-constexpr int kSlots = 3;            // chunks in flight
+constexpr int kSlots = 4;            // chunks in flight
 
 // Everything one in-flight chunk owns.
 struct Slot {
@@ -98,7 +98,7 @@ struct Slot {
     uint2 *d_accepted = nullptr;      // accepted records of the chunk: the level kernel turns them into messages
     ChunkCounters *d_ctr = nullptr;
     ChunkCounters *h_ctr = nullptr;   // pinned
-    cudaEvent_t ev[6]{};              // front begin, front end, messages end | finish begin, finish end, counters on the host
+    cudaEvent_t ev[7]{};              // front begin, front end, messages end | resolve begin, resolve end, counters on the host | order end
 };
 
 struct adsbcu_handle {
@@ -106,7 +106,9 @@ struct adsbcu_handle {
     int device = 0, sm_count = 148;
     cudaStream_t stream = nullptr;        // front + message kernels
     cudaStream_t copy_stream = nullptr;   // host->device uploads of the feed, chunk by chunk
-    cudaStream_t post_stream = nullptr;   // finish kernels (high priority: a few CTAs on the spare SMs)
+    cudaStream_t post_stream = nullptr;   // resolve kernels, in chunk order (high priority, like the next two)
+    cudaStream_t order_stream = nullptr;  // order kernels
+    cudaStream_t level_stream = nullptr;  // level kernels + the chunk counters to the host
     cudaEvent_t ev_h2d[2]{};
     cudaEvent_t ev_up[kSlots]{};      // upload of the chunk using that slot has finished
     std::string error;
@@ -181,7 +183,7 @@ void free_slots(adsbcu_handle *h)
         cudaFree(s.d_run_start); cudaFree(s.d_ctr); cudaFree(s.d_accepted); cudaFree(s.d_view);
         if (s.h_cand) cudaFreeHost(s.h_cand);
         if (s.h_ctr) cudaFreeHost(s.h_ctr);
-        cudaEvent_t ev[6];
+        cudaEvent_t ev[7];
         std::memcpy(ev, s.ev, sizeof(ev));
         s = Slot{};
         std::memcpy(s.ev, ev, sizeof(ev));
@@ -228,6 +230,8 @@ void free_all(adsbcu_handle *h)
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->post_stream) cudaStreamSynchronize(h->post_stream);
+    if (h->order_stream) cudaStreamSynchronize(h->order_stream);
+    if (h->level_stream) cudaStreamSynchronize(h->level_stream);
     if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
     cudaFree(h->d_sc16);
     cudaFree(h->d_ac_ov); cudaFree(h->d_ac_sums); cudaFree(h->d_ac_rec);
@@ -250,6 +254,8 @@ void free_all(adsbcu_handle *h)
     if (h->stream) cudaStreamDestroy(h->stream);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->post_stream) cudaStreamDestroy(h->post_stream);
+    if (h->order_stream) cudaStreamDestroy(h->order_stream);
+    if (h->level_stream) cudaStreamDestroy(h->level_stream);
 }
 
 // ---- ordered pass on the host: adsbcu_1090_resolve only ---------------------------------------------------
@@ -403,12 +409,19 @@ int run_chunks(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, ui
         fa.batch = h->resolve_batch;
         fa.seg_flag = s.d_seg_flag; fa.epoch = ++h->chunk_epoch ? h->chunk_epoch : ++h->chunk_epoch; fa.run_start = s.d_run_start; fa.view = s.d_view;
         if (sink.cands) { fa.deferred = h->d_deferred; fa.deferred_cap = h->deferred_cap; fa.n_deferred = h->d_n_deferred; }
-        CK(cudaStreamWaitEvent(h->post_stream, s.ev[2], 0));
+        // order(c) needs messages(c); resolve(c) needs order(c) and resolve(c-1); level(c) needs resolve(c): three
+        // streams, so that the one-CTA ordered pass of a chunk overlaps the wide kernels of its neighbours
+        CK(cudaStreamWaitEvent(h->order_stream, s.ev[2], 0));
+        CK(launch_order(fa, h->order_stream));
+        CK(cudaEventRecord(s.ev[6], h->order_stream));
+        CK(cudaStreamWaitEvent(h->post_stream, s.ev[6], 0));
         CK(cudaEventRecord(s.ev[3], h->post_stream));
-        CK(launch_finish(fa, h->level_grid, h->post_stream));
+        CK(launch_resolve(fa, h->post_stream));
         CK(cudaEventRecord(s.ev[4], h->post_stream));
-        CK(cudaMemcpyAsync(s.h_ctr, s.d_ctr, sizeof(ChunkCounters), cudaMemcpyDeviceToHost, h->post_stream));
-        CK(cudaEventRecord(s.ev[5], h->post_stream));
+        CK(cudaStreamWaitEvent(h->level_stream, s.ev[4], 0));
+        CK(launch_level(fa, h->level_grid, h->level_stream));
+        CK(cudaMemcpyAsync(s.h_ctr, s.d_ctr, sizeof(ChunkCounters), cudaMemcpyDeviceToHost, h->level_stream));
+        CK(cudaEventRecord(s.ev[5], h->level_stream));
         st.scan_launches += 5;
         return ADSBCU_OK;
     };
@@ -417,10 +430,13 @@ int run_chunks(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, ui
         Slot &s = h->slot[c % kSlots];
         CK(cudaEventSynchronize(s.ev[5]));
         const ChunkCounters k = *s.h_ctr;
-        if (std::getenv("ADSBCU_ORDER_TIMING_PRINT"))
-            std::fprintf(stderr, "order chunk %u: revive %.1f us, look-back %.1f us, resolve starts +%.1f us, load+runs %.1f, rounds %.1f, emit %.1f, insert+end %.1f (n_full %u)\n", c,
-                         (k.dbg[1] - k.dbg[0]) * 1e-3, (k.dbg[2] - k.dbg[1]) * 1e-3, (k.dbg[3] - k.dbg[0]) * 1e-3, (k.dbg[4] - k.dbg[3]) * 1e-3,
-                         (k.dbg[5] - k.dbg[4]) * 1e-3, (k.dbg[6] - k.dbg[5]) * 1e-3, (k.dbg[7] - k.dbg[6]) * 1e-3, k.n_full);
+        if (std::getenv("ADSBCU_ORDER_TIMING_PRINT")) {
+            static unsigned long long t_base = 0;
+            if (c == 0) t_base = k.dbg[0];
+            std::fprintf(stderr, "chunk %u: order starts @%.1f us (%.1f), resolve @%.1f..%.1f (load+runs %.1f, rounds %.1f, emit %.1f, end %.1f; n_full %u)\n", c,
+                         (k.dbg[0] - t_base) * 1e-3, (k.dbg[2] - k.dbg[0]) * 1e-3, (k.dbg[3] - t_base) * 1e-3, (k.dbg[7] - t_base) * 1e-3,
+                         (k.dbg[4] - k.dbg[3]) * 1e-3, (k.dbg[5] - k.dbg[4]) * 1e-3, (k.dbg[6] - k.dbg[5]) * 1e-3, (k.dbg[7] - k.dbg[6]) * 1e-3, k.n_full);
+        }
         if (k.overflow) { if (failed_chunk == nchunks) failed_chunk = c; return ADSBCU_OK; }
         if (failed_chunk != nchunks) return ADSBCU_OK;                 // chunks after a failed one did not touch the state
         if (sink.cands) copy_candidates(s.h_cand, k.n_full, h->stream_pos, sink);
@@ -446,7 +462,7 @@ int run_chunks(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, ui
         ++retired;
     }
     if (rc != ADSBCU_OK) {
-        cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->post_stream); cudaStreamSynchronize(h->copy_stream);
+        cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->order_stream); cudaStreamSynchronize(h->post_stream); cudaStreamSynchronize(h->level_stream); cudaStreamSynchronize(h->copy_stream);
         return rc;
     }
     return failed_chunk != nchunks ? kOverflowRetry : ADSBCU_OK;
@@ -475,7 +491,9 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
         // a list of chunk `failed` overflowed: nothing from that chunk on has touched the stream state.  Double the
         // lists and run again from there (the samples are on the device already).
         CK(cudaStreamSynchronize(h->stream));
+        CK(cudaStreamSynchronize(h->order_stream));
         CK(cudaStreamSynchronize(h->post_stream));
+        CK(cudaStreamSynchronize(h->level_stream));
         CK(cudaStreamSynchronize(h->copy_stream));
         if (attempt >= 5) {
             h->error = "internal candidate list overflow (traffic denser than the lists can be grown for)";
@@ -499,7 +517,9 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
     else CK(launch_carry(d_iq, n, h->d_carry, h->d_tab, h->stream));
     h->stats.scan_launches += 1;
     CK(cudaStreamSynchronize(h->stream));
+    CK(cudaStreamSynchronize(h->order_stream));
     CK(cudaStreamSynchronize(h->post_stream));
+    CK(cudaStreamSynchronize(h->level_stream));
     if (from_host && nchunks) { float ms = 0.f; cudaEventElapsedTime(&ms, h->ev_h2d[0], h->ev_h2d[1]); h->stats.ms_h2d += ms; }
     h->stats.samples += n;
     h->stream_pos += n;
@@ -624,6 +644,8 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
         int lo = 0, hi = 0;
         CKC(cudaDeviceGetStreamPriorityRange(&lo, &hi));
         CKC(cudaStreamCreateWithPriority(&h->post_stream, cudaStreamNonBlocking, hi));
+        CKC(cudaStreamCreateWithPriority(&h->order_stream, cudaStreamNonBlocking, hi));
+        CKC(cudaStreamCreateWithPriority(&h->level_stream, cudaStreamNonBlocking, hi));
     }
     for (auto &e : h->ev_h2d) CKC(cudaEventCreate(&e));
     for (auto &e : h->ev_up) CKC(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -912,7 +934,7 @@ int adsbcu_1090_scan_candidates(adsbcu_handle *h, const uint8_t *iq, size_t nsam
             CK(cudaHostAlloc(&s.h_cand, size_t(h->full_cap) * sizeof(FullRec), cudaHostAllocMapped));
             CK(cudaHostGetDevicePointer(&s.d_cand, s.h_cand, 0));
         }
-    CK(cudaMemsetAsync(h->d_n_deferred, 0, sizeof(uint32_t), h->post_stream));
+    CK(cudaMemsetAsync(h->d_n_deferred, 0, sizeof(uint32_t), h->stream));     // (the order kernels wait for this stream)
     CK(launch_state_begin_feed(h->d_state, 1, h->post_stream));
     h->stats = adsbcu_stats{};
     Sink sink{nullptr, cap, 0, false, out};

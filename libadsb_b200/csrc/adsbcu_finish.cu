@@ -136,9 +136,8 @@ struct SkipState {
 };
 
 // Compact view of a record for the ordered pass: x = feed position, y = key of icaoFilterTest, z = key of
-// icaoFilterAdd (or 0xFFFFFFFF), w = kind | 112-bit flag << 8 (| 0x200: the key is in the filter when the chunk starts,
-// | 0x400: accepting the record adds an address the active table does not hold; both set by phase 1).  16 bytes, so a
-// thread walking its runs stays in L1.
+// icaoFilterAdd (or 0xFFFFFFFF), w = kind | 112-bit flag << 8.  The resolve kernel adds 0x200 (the key is in the filter
+// when the batch starts) and 0x400 (accepting the record adds an address the active table does not hold).
 __device__ __forceinline__ uint4 view_of(const FullRec &r)
 {
     return make_uint4(r.pos, r.test_key, r.add_key, uint32_t(r.kind) | ((r.verbatim[0] & 0x80u) ? 0x100u : 0u));
@@ -274,10 +273,7 @@ __global__ void __launch_bounds__(kXThreads) order_kernel(FinishArgs fa)
                 uint4 *dst = reinterpret_cast<uint4 *>(a.ordered + offset + rank);
                 const uint4 q0 = src[0], q1 = src[1], q2 = src[2], q3 = src[3];
                 dst[0] = q0; dst[1] = q1; dst[2] = q2; dst[3] = q3;
-                uint4 v = view_of(rec[i]);
-                if (icao_test(fa.st, v.y)) v.w |= 0x200u;                                              // known when the chunk starts
-                if (v.z != kUnchecked && !icao_probe(fa.st->table[fa.st->active], v.z)) v.w |= 0x400u;    // accepting it adds a new address
-                fa.view[offset + rank] = v;
+                fa.view[offset + rank] = view_of(rec[i]);
             }
         }
     }
@@ -293,6 +289,7 @@ constexpr int kRThreads = 1024;
 constexpr uint32_t kRBatch = 16384;
 
 struct ResolveSmem {
+    uint32_t table[2][kIcaoSlots];             // the reference's two filter tables as of the batch's start
     uint2 ent[kRBatch];                        // x: feed position, y: view flags (bits 0..15) | score of the accepted record << 16
     AddMap cur, next;
     uint32_t scan[kRThreads];
@@ -365,6 +362,7 @@ __global__ void __launch_bounds__(kRThreads, 1) resolve_kernel(FinishArgs fa)
     const SkipState carried{st->has_last, st->last_a, st->last_lme};
     if (tid < 22) sm.rank[tid] = uint8_t(rank_of(uint32_t(tid) >> 1, (tid & 1) != 0));
     if (tid == 0) sm.last_acc = 0;
+    const uint32_t active = st->active;
     uint32_t total = 0;                           // messages written so far (uniform)
     uint32_t ia = 0;
     bool sequential = fa.force_sequential != 0;
@@ -372,14 +370,14 @@ __global__ void __launch_bounds__(kRThreads, 1) resolve_kernel(FinishArgs fa)
     while (ia < n && !sequential) {
         // ---- the batch's entries into shared memory (coalesced); later batches see the table the earlier ones left ----
         const uint32_t ib_t = min(n, ia + min(kRBatch, max(fa.batch, 2u)));
+        for (uint32_t i = tid; i < 2u * kIcaoSlots; i += kRThreads) sm.table[0][i] = __ldcg(&st->table[0][i]);   // (past L1: the batch before wrote them)
+        __syncthreads();
 #pragma unroll 4
         for (uint32_t i = ia + tid; i < ib_t; i += kRThreads) {
             const uint4 v = view[i];
-            uint32_t w = v.w & 0xFFFFu;
-            if (ia) {
-                if (!(w & 0x200u) && icao_test(st, v.y)) w |= 0x200u;
-                if (v.z != kUnchecked) w = (w & ~0x400u) | (icao_probe(st->table[st->active], v.z) ? 0u : 0x400u);
-            }
+            uint32_t w = v.w & 0x1FFu;
+            if (icao_probe(sm.table[0], v.y) || icao_probe(sm.table[1], v.y)) w |= 0x200u;         // known when the batch starts
+            if (v.z != kUnchecked && !icao_probe(sm.table[active], v.z)) w |= 0x400u;              // accepting it adds a new address
             sm.ent[i - ia] = make_uint2(v.x, w);
         }
         for (uint32_t i = tid; i < kMapSlots; i += kRThreads) { sm.cur.key[i] = kMapEmpty; sm.cur.pos[i] = kMapEmpty; sm.next.key[i] = kMapEmpty; sm.next.pos[i] = kMapEmpty; }
@@ -631,12 +629,23 @@ cudaError_t init_finish()
     return cudaFuncSetAttribute(resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(ResolveSmem)));
 }
 
-// order_kernel: one CTA per segment; resolve_kernel: one CTA; level kernels: `level_grid` CTAs of 8 warps
-cudaError_t launch_finish(const FinishArgs &fa, uint32_t level_grid, cudaStream_t s)
+// order_kernel: one CTA per segment; resolve_kernel: one CTA; level kernels: `level_grid` CTAs of 8 warps.  The three
+// only depend on each other in this order (and resolve on the resolve of the chunk before): the host gives each its own stream.
+cudaError_t launch_order(const FinishArgs &fa, cudaStream_t s)
 {
     if (fa.c.pos_end <= fa.c.pos_begin || !fa.c.nseg) return cudaSuccess;
     ADSBCU_LAUNCH(order_kernel, fa.c.nseg, kXThreads, sizeof(SortSmem), s, fa);
+    return cudaGetLastError();
+}
+cudaError_t launch_resolve(const FinishArgs &fa, cudaStream_t s)
+{
+    if (fa.c.pos_end <= fa.c.pos_begin || !fa.c.nseg) return cudaSuccess;
     ADSBCU_LAUNCH(resolve_kernel, 1, kRThreads, sizeof(ResolveSmem), s, fa);
+    return cudaGetLastError();
+}
+cudaError_t launch_level(const FinishArgs &fa, uint32_t level_grid, cudaStream_t s)
+{
+    if (fa.c.pos_end <= fa.c.pos_begin || !fa.c.nseg) return cudaSuccess;
     if (fa.candidates_only) ADSBCU_LAUNCH(level_records_kernel, level_grid, 256, 0, s, fa);
     else ADSBCU_LAUNCH(level_kernel, level_grid, 256, 0, s, fa);
     return cudaGetLastError();

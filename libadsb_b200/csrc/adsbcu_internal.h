@@ -252,7 +252,9 @@ cudaError_t launch_build_lutf(DevTables *tab, cudaStream_t s);
 cudaError_t init_messages();
 cudaError_t launch_front(const ChunkArgs &a, cudaStream_t s);        // grid = a.nseg
 cudaError_t launch_messages(const ChunkArgs &a, uint32_t grid, cudaStream_t s);
-cudaError_t launch_finish(const FinishArgs &fa, uint32_t level_grid, cudaStream_t s);   // order_kernel (+ level_kernel)
+cudaError_t launch_order(const FinishArgs &fa, cudaStream_t s);      // late records, stream order (one CTA per segment)
+cudaError_t launch_resolve(const FinishArgs &fa, cudaStream_t s);    // the ordered pass (one CTA)
+cudaError_t launch_level(const FinishArgs &fa, uint32_t level_grid, cudaStream_t s);   // signal levels, final messages
 cudaError_t launch_state_reset(StreamState *st, int clear_filter, int clear_stream, cudaStream_t s);
 cudaError_t launch_state_begin_feed(StreamState *st, int reset_count, cudaStream_t s);
 cudaError_t launch_filter_add(StreamState *st, uint32_t *bitmap, uint32_t addr, cudaStream_t s);

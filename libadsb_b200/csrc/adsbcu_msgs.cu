@@ -30,6 +30,7 @@ struct MsgSmem {
     uint32_t occ_long[kSyndSlotsLong / 32], occ_short[kSyndSlotsShort / 32];
     uint32_t queue[kMWarps][160];              // per warp: 112-bit items from the front, 56-bit items from the back: lane | (phase-4) << 8
     uint32_t slow[kMWarps][160];               // per warp: items that need the general classification
+    PhaseRec park[kMWarps][160];               // per warp: the round's parked records (one list reservation per round)
     uint32_t round_first[kMaxSeg + 1];         // first round of every segment
 };
 
@@ -94,17 +95,12 @@ __global__ void __launch_bounds__(kMThreads, ADSBCU_MSG_MINCTAS) message_kernel(
             nshort += __popc(bs);
         }
         __syncwarp();
-        // parked records of a pass: one reservation in the segment's list per warp
+        // parked records collect in the warp's buffer; the round ends with one reservation in the segment's list
+        uint32_t npark = 0;
         auto park_records = [&](bool park, const PhaseRec &parked) {
             const uint32_t bp = __ballot_sync(0xFFFFFFFFu, park);
-            if (!bp) return;
-            uint32_t base = 0;
-            if (lane == 0) base = atomicAdd(&a.pend_count[seg], uint32_t(__popc(bp)));
-            base = __shfl_sync(0xFFFFFFFFu, base, 0);
-            if (park) {
-                const uint32_t slot = base + __popc(bp & ((1u << lane) - 1u));
-                if (slot < a.pend_cap) a.pend[size_t(seg) * a.pend_cap + slot] = parked; else a.ctr->overflow = 1u;
-            }
+            if (park) sm.park[warp][npark + __popc(bp & ((1u << lane) - 1u))] = parked;
+            npark += __popc(bp);
         };
         // C2: one item per lane and pass
         uint32_t nslow = 0;
@@ -125,14 +121,10 @@ __global__ void __launch_bounds__(kMThreads, ADSBCU_MSG_MINCTAS) message_kernel(
                 // the common case first (noise: no repair applies), the general classification only where it does not
                 int verdict = classify_fast(M[0], M[0] == 0u && (M[1] >> 8) == 0u, xs, xl, fixable_long, fixable_short, sm.occ_long, sm.occ_short, key);
                 if (verdict == 1) {
-                    const uint32_t bi = bitmap_index(key);
-                    if (!((a.bitmap[bi >> 5] >> (bi & 31)) & 1u)) {
-                        // acceptable only for a known address that nobody has announced so far: parked
-                        park = true;
-                        parked = PhaseRec{pos, bi | ((ph - 4u) << 25) | (uint32_t(K_AP) << 28)};
-                    } else {
-                        verdict = 2;                                                  // announced address: evaluated record
-                    }
+                    // acceptable only for a known address: parked; the order kernel evaluates the ones whose address has
+                    // been announced by the end of the chunk (no look at the address set here: one memory round trip less)
+                    park = true;
+                    parked = PhaseRec{pos, bitmap_index(key) | ((ph - 4u) << 25) | (uint32_t(K_AP) << 28)};
                 }
                 slow = verdict == 2;
             }
@@ -174,6 +166,14 @@ __global__ void __launch_bounds__(kMThreads, ADSBCU_MSG_MINCTAS) message_kernel(
                 }
             }
             park_records(park, parked);
+        }
+        __syncwarp();
+        if (npark) {
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(&a.pend_count[seg], npark);
+            base = __shfl_sync(0xFFFFFFFFu, base, 0);
+            if (base + npark > a.pend_cap) { if (lane == 0) a.ctr->overflow = 1u; }
+            else for (uint32_t i = lane; i < npark; i += 32) a.pend[size_t(seg) * a.pend_cap + base + i] = sm.park[warp][i];
         }
         __syncwarp();
     }

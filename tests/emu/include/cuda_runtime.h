@@ -185,6 +185,7 @@ static inline unsigned __byte_perm(unsigned a, unsigned b, unsigned s)
 static inline unsigned __umulhi(unsigned a, unsigned b) { return unsigned(((unsigned long long)a * b) >> 32); }
 template <class T> static inline T __ldg(const T *p) { return *p; }
 template <class T> static inline T __ldcs(const T *p) { return *p; }
+template <class T> static inline T __ldcg(const T *p) { return *p; }
 template <class T> static inline void __stcs(T *p, T v) { *p = v; }
 // IEEE single/double operations with explicit rounding: the emulator is built with -ffp-contract=off on x86-64 (SSE2)
 static inline float __fadd_rn(float a, float b) { volatile float r = a + b; return r; }
