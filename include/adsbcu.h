@@ -199,6 +199,30 @@ int adsbcu_1090_modeac_block(adsbcu_handle *h, const uint8_t *iq, size_t nsample
                              const uint8_t *overlap_iq, size_t n_overlap, uint64_t block_timestamp,
                              adsbcu_msg *out, size_t cap, size_t *n_out);
 
+/* The same Mode A/C block for callers that may not allocate device memory (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same detector, same kernels and same replies as adsbcu_1090_modeac_block, but
+ *   - all scratch (magnitudes, level / power sums, candidate records) lives in ONE file-scope device array of the
+ *     library, about 386 KiB, that every GPU which loads the library holds until the process exits: the call makes
+ *     no cudaMalloc / cudaFree / cudaHostAlloc and no host<->device copy, and never waits for the GPU;
+ *   - nsamples is limited to ADSBCU_MODEAC_STATIC_MAX_SAMPLES (the reference's mag_buf, MODES_MAG_BUF_SAMPLES);
+ *     a larger block is rejected with ADSBCU_ERR_ARG and a message in adsbcu_last_error();
+ *   - iq_dev (16-byte aligned), overlap_iq_dev, out_dev and result_dev are DEVICE pointers owned by the caller;
+ *     the work is enqueued on cuda_stream (a cudaStream_t; NULL = the default stream) and the results are valid
+ *     once that stream has reached this point: result_dev[0] = number of replies (if it exceeds cap only the
+ *     first cap were written), result_dev[1] = ADSBCU_STATIC_* flags (0 = complete);
+ *   - every call on a GPU uses the same array, so calls that overlap on that GPU (different streams, different
+ *     handles or threads) race; calls on one stream, or otherwise ordered, are safe.  The array keeps the last
+ *     call's contents; each call clears what must start at zero itself.
+ * `h` supplies the device and its lookup tables; nothing in it is modified except the error string.  The first
+ * call on a device looks the array's address up (cudaGetSymbolAddress): make that call outside stream capture. */
+#define ADSBCU_MODEAC_STATIC_MAX_SAMPLES 131072
+enum { ADSBCU_STATIC_CANDIDATE_OVERFLOW = 1,   /* more than MAX_SAMPLES/16 candidate positions: no replies written */
+       ADSBCU_STATIC_OUT_OVERFLOW = 2 };       /* more replies than cap */
+int adsbcu_1090_modeac_block_static(adsbcu_handle *h, const uint8_t *iq_dev, size_t nsamples,
+                                    const uint8_t *overlap_iq_dev, size_t n_overlap, uint64_t block_timestamp,
+                                    adsbcu_msg *out_dev, size_t cap, uint32_t *result_dev /* [2] */, void *cuda_stream);
+
 /* ---- Path A, next layer: CPR position decode ----------------------------------
  * The three decoders of the flightaware tree's cpr.c, many records per call, results as the same IEEE
  * doubles the reference computes (bit for bit; dump1090's own cprtests.c vectors are in tests/golden):

@@ -50,6 +50,7 @@ EXPORTS = ["adsbcu_abi_version", "adsbcu_last_error", "adsbcu_create", "adsbcu_d
            "adsbcu_1090_filter_test", "adsbcu_1090_filter_expire", "adsbcu_get_stats", "adsbcu_1090b_feed", "adsbcu_1090b_reset",
            "adsbcu_978_feed", "adsbcu_978_reset", "adsbcu_978_phase", "adsbcu_1090_seek", "adsbcu_1090_scan_candidates",
            "adsbcu_1090_known_export", "adsbcu_1090_known_import", "adsbcu_1090_revive", "adsbcu_1090_resolve", "adsbcu_1090_modeac_block", "adsbcu_1090_feed_sc16",
+           "adsbcu_1090_modeac_block_static",
            "adsbcu_1090b_decode_fields", "adsbcu_1090b_cpr_decode", "adsbcu_1090_cpr_decode"]
 
 
@@ -109,6 +110,8 @@ def load():
         L.adsbcu_1090_modeac_block.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_uint64, C.c_void_p,
                                                C.c_size_t, C.POINTER(C.c_size_t)]
         L.adsbcu_1090_feed_sc16.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.adsbcu_1090_modeac_block_static.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_uint64, C.c_void_p,
+                                                      C.c_size_t, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -273,6 +276,13 @@ class Demod1090:
         self._check(load().adsbcu_1090_modeac_block(self.h, iq.ctypes.data, iq.size // 2, ov.ctypes.data if ov.size else None,
                                                     ov.size // 2, block_timestamp, out.ctypes.data, cap, C.byref(got)))
         return out[:got.value]
+
+    def modeac_block_static(self, iq_dev: int, nsamples: int, overlap_iq_dev: int, n_overlap: int, block_timestamp: int,
+                            out_dev: int, cap: int, result_dev: int, stream: int = 0) -> None:
+        """adsbcu_1090_modeac_block_static: DEVICE addresses in and out, scratch in the library's static device array, nothing
+        allocated, nothing awaited.  result_dev[0] = replies, result_dev[1] = flags once `stream` has reached this point."""
+        self._check(load().adsbcu_1090_modeac_block_static(self.h, iq_dev or None, nsamples, overlap_iq_dev or None, n_overlap,
+                                                           block_timestamp, out_dev or None, cap, result_dev or None, stream or None))
 
     def filter_add(self, addr): self._check(load().adsbcu_1090_filter_add(self.h, addr))
     def filter_test(self, addr): return bool(load().adsbcu_1090_filter_test(self.h, addr))

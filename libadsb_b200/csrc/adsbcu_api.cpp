@@ -163,6 +163,11 @@ struct adsbcu_handle {
     uint32_t ac_cap = 0;
 };
 
+namespace adsbcu {
+HandleView handle_view(const adsbcu_handle *h) { return HandleView{h->device, h->sm_count, h->d_tab, h->host_only}; }
+void handle_set_error(adsbcu_handle *h, const char *what) { h->error = what; }
+}  // namespace adsbcu
+
 namespace {
 
 bool cuda_ok(adsbcu_handle *h, cudaError_t e, const char *what)

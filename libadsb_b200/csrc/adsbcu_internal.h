@@ -288,6 +288,13 @@ cudaError_t launch_modeac(const DevTables *tab, int sm_count, cudaStream_t s, co
 struct PathB;
 }  // namespace adsbcu
 #include <string>
+struct adsbcu_handle;
+namespace adsbcu {
+// What an entry point that lives outside adsbcu_api.cpp may know about a handle (adsbcu_api.cpp defines both).
+struct HandleView { int device, sm_count; const DevTables *tab; bool host_only; };
+HandleView handle_view(const adsbcu_handle *h);
+void handle_set_error(adsbcu_handle *h, const char *what);
+}  // namespace adsbcu
 struct adsbcu_msg_b;
 namespace adsbcu {
 int  pathb_feed(PathB *&b, const DevTables *d_tab, int sm_count, cudaStream_t s, const uint8_t *iq, size_t nbytes,

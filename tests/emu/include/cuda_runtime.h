@@ -323,6 +323,7 @@ static inline cudaError_t cudaMemcpyAsync(void *d, const void *s, size_t n, cuda
 static inline cudaError_t cudaMemcpyPeerAsync(void *d, int, const void *s, int, size_t n, cudaStream_t = nullptr) { if (n) std::memmove(d, s, n); return cudaSuccess; }
 static inline cudaError_t cudaMemset(void *d, int v, size_t n) { if (n) std::memset(d, v, n); return cudaSuccess; }
 static inline cudaError_t cudaMemsetAsync(void *d, int v, size_t n, cudaStream_t = nullptr) { if (n) std::memset(d, v, n); return cudaSuccess; }
+template <class T> static inline cudaError_t cudaGetSymbolAddress(void **p, T &sym) { *p = static_cast<void *>(&sym); return cudaSuccess; }
 template <class T> static inline cudaError_t cudaMemcpyFromSymbol(void *d, const T &sym, size_t n) { std::memcpy(d, &sym, n); return cudaSuccess; }
 template <class T> static inline cudaError_t cudaMemcpyToSymbol(T &sym, const void *s, size_t n) { std::memcpy(&sym, s, n); return cudaSuccess; }
 template <class F> static inline cudaError_t cudaFuncSetAttribute(F, cudaFuncAttribute, int) { return cudaSuccess; }
