@@ -217,13 +217,16 @@ def main():
     while len(sampler.rows) < 2 and time.perf_counter() - t_w < 3.0:   # keep the GPU under the same load until sampling runs
         step_resident()
     barrier()
-    scan_ms, fin_ms, res_ms, launches = [], [], [], 0
+    kms = {"front": [], "messages": [], "order": [], "resolve": []}
+    launches, chunks = 0, 0
     t0 = time.perf_counter()
     for _ in range(args.steps):
         step_resident()
         st = d.stats()
-        scan_ms.append(st["ms_scan"]); fin_ms.append(st["ms_finalize"]); res_ms.append(st["ms_resolve"])
-        launches += st["scan_launches"] + 2          # + counters memset, carry memset of reset()
+        for k in kms:
+            kms[k].append(st["ms_" + k])
+        launches += st["launches"] + 1               # + the one-thread state kernel of reset(); memsets and copies are not counted
+        chunks = st["chunks"]
     barrier()
     t_res = time.perf_counter() - t0
 
@@ -258,17 +261,25 @@ def main():
 
     if rank == 0:
         peak, peak_src = load_peaks()
-        k_ms = float(np.mean(scan_ms))                    # all scan_kernel launches of one step (one per chunk)
-        achieved = 2.0 * n / (k_ms * 1e-3) / 1e9
-        # per chunk: scan, filter, evaluate (+ signal when the resolver thread runs, i.e. feeds of >= 3 chunks);
-        # per feed: + carry + 2 memsets
-        per_feed = launches // args.steps - 2 - 1
-        scan_per_step = per_feed // 4 if os.environ.get("ADSBCU_RESOLVER_THREAD", "1") != "0" and per_feed % 4 == 0 and per_feed >= 12 else per_feed // 3
+        # Per-kernel device time of one step (CUDA events on the launching streams, summed over the step's chunks).
+        # The roofline object describes the kernel with the largest share; both dense kernels are listed under
+        # "kernels".  Algorithmic bytes: 2 B per sample, each kernel makes one launch per chunk.
+        per_kernel = {k: float(np.mean(v)) for k, v in kms.items()}
         try:
             with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
-                traffic_ratio = float(json.load(f)["traffic_over_algorithmic"])
+                traffic_tab = json.load(f)
         except Exception:
-            traffic_ratio = None
+            traffic_tab = {}
+        kernels = {}
+        for k, name in (("front", "front_kernel"), ("messages", "message_kernel")):
+            ms = per_kernel[k]
+            gbs = 2.0 * n / (ms * 1e-3) / 1e9
+            ratio = traffic_tab.get(name, {}).get("traffic_over_algorithmic")
+            kernels[name] = {"ms_per_step": ms, "launches_per_step": chunks, "avg_launch_ms": ms / max(chunks, 1),
+                             "algorithmic_bytes_per_launch": 2.0 * n / max(chunks, 1), "achieved": gbs, "frac": gbs / peak,
+                             "traffic": None if ratio is None else ratio * 2.0 * n / max(chunks, 1)}
+        dom = max(kernels, key=lambda name: kernels[name]["ms_per_step"])
+        kd = kernels[dom]
         line = {
             "metric": METRIC, "value": world * n * args.steps / t_res / 1e6, "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_res / args.steps * 1e3,
@@ -276,17 +287,17 @@ def main():
             "data": "synthetic", "config": config, "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": world * n * args.steps / t_e2e / 1e6, "unit": UNIT, "h2d_bytes_per_step": 2 * n,
                     "d2h_bytes_per_step": d2h // args.steps},
-            "roofline": {"bound": "hbm", "kernel": "scan_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "peak_source": peak_src,
-                         "launches_per_step": scan_per_step,
-                         "algorithmic_bytes_per_launch": 2 * n / max(scan_per_step, 1),
-                         "avg_launch_ms": k_ms / max(scan_per_step, 1),
-                         "traffic": None if traffic_ratio is None else traffic_ratio * 2 * n / max(scan_per_step, 1),
-                         "traffic_source": "profiles/ncu_traffic.json: dram read+write of one ncu --set full launch / its algorithmic bytes",
-                         "kernel_ms_per_step": k_ms},
+            "roofline": {"bound": "hbm", "kernel": dom, "achieved": kd["achieved"], "peak": peak, "unit": "GB/s",
+                         "frac": kd["frac"], "peak_source": peak_src, "launches_per_step": kd["launches_per_step"],
+                         "algorithmic_bytes_per_launch": kd["algorithmic_bytes_per_launch"], "avg_launch_ms": kd["avg_launch_ms"],
+                         "traffic": kd["traffic"],
+                         "traffic_source": "profiles/ncu_traffic.json: dram read+write of one ncu --set full launch / that launch's algorithmic bytes",
+                         "kernel_ms_per_step": kd["ms_per_step"],
+                         "step_frac": 2.0 * n / (t_res / args.steps) / 1e9 / peak},
+            "kernels": kernels,
             "pcie": {"h2d_gbs": h2d_gbs, "h2d_ceiling_msamples_s": h2d_gbs * 1e3 / 2.0,
                      "note": "plain pinned cudaMemcpy of the capture on this box; e2e cannot exceed world * this"},
-            "breakdown_ms": {"scan": k_ms, "finalize": float(np.mean(fin_ms)), "host_resolve": float(np.mean(res_ms))},
+            "breakdown_ms": dict(per_kernel, note="device time per kernel summed over the chunks; order / resolve run on their own streams beside the next chunk's front + message kernels"),
             "messages_per_step": nmsg,
         }
         if world == 1 and not args.no_cpu_baseline:

@@ -81,12 +81,12 @@ typedef struct adsbcu_stats {
     uint64_t resolved_records; /* records that survived the known-address filter */
     uint64_t messages;         /* accepted messages */
     float    ms_h2d;           /* host->device copy (0 for device feeds) */
-    float    ms_scan;          /* scan kernel (magnitude+preamble+slice+CRC+compaction) */
-    float    ms_finalize;      /* filter/finalize kernel */
-    float    ms_d2h;           /* record download */
-    float    ms_resolve;       /* sequential host pass (wall clock) */
-    uint32_t scan_launches;    /* kernels launched by the feed */
-    uint32_t reserved;
+    float    ms_front;         /* front kernels (magnitude, slicer decisions, preambles), summed over the chunks */
+    float    ms_messages;      /* message kernels (DF filter, CRC, repair, scoring) */
+    float    ms_order;         /* order kernels (late records, position order) */
+    float    ms_resolve;       /* resolve kernels (the ordered pass of demodulate2400, on the device) */
+    uint32_t launches;         /* kernels launched by the feed */
+    uint32_t chunks;           /* chunks the feed was cut into (= launches of each per-chunk kernel) */
 } adsbcu_stats;
 
 typedef struct adsbcu_handle adsbcu_handle;

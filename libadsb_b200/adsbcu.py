@@ -62,8 +62,8 @@ class Config(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("samples", C.c_uint64), ("preambles", C.c_uint64), ("phase_records", C.c_uint64),
                 ("resolved_records", C.c_uint64), ("messages", C.c_uint64), ("ms_h2d", C.c_float),
-                ("ms_scan", C.c_float), ("ms_finalize", C.c_float), ("ms_d2h", C.c_float), ("ms_resolve", C.c_float),
-                ("scan_launches", C.c_uint32), ("reserved", C.c_uint32)]
+                ("ms_front", C.c_float), ("ms_messages", C.c_float), ("ms_order", C.c_float), ("ms_resolve", C.c_float),
+                ("launches", C.c_uint32), ("chunks", C.c_uint32)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved"}
@@ -134,8 +134,8 @@ class Demod1090:
             raise AdsbcuError(f"adsbcu_create failed ({rc}): {msg.decode() if msg else ''}")
 
     def close(self):
-        if getattr(self, "h", None):
-            load().adsbcu_destroy(self.h)
+        if getattr(self, "h", None) and _lib is not None:       # (at interpreter exit the module globals may be gone already)
+            _lib.adsbcu_destroy(self.h)
             self.h = None
 
     __del__ = close

@@ -96,9 +96,11 @@ struct Slot {
     uint32_t *d_run_start = nullptr;
     uint4 *d_view = nullptr;
     uint2 *d_accepted = nullptr;      // accepted records of the chunk: the level kernel turns them into messages
-    ChunkCounters *d_ctr = nullptr;
+    ChunkCounters *d_ctr = nullptr;   // = d_zero
+    unsigned char *d_zero = nullptr;  // what a chunk must find zeroed, one block: counters | rec_count[nseg] | pend_count[nseg]
+    size_t zero_bytes = 0;
     ChunkCounters *h_ctr = nullptr;   // pinned
-    cudaEvent_t ev[7]{};              // front begin, front end, messages end | resolve begin, resolve end, counters on the host | order end
+    cudaEvent_t ev[8]{};              // front begin, front end, messages end | resolve begin, resolve end, counters on the host | order end, order begin
 };
 
 struct adsbcu_handle {
@@ -125,7 +127,7 @@ struct adsbcu_handle {
 
     // geometry
     uint32_t nseg = 0, msg_grid = 0, level_grid = 128;
-    uint32_t unit_positions = 0, max_tps = 1, host_tps = 4, res_tps = 4;   // chunk = unit_positions * (tiles per segment)
+    uint32_t unit_positions = 0, max_tps = 1, host_tps = 4, res_tps = 8;   // chunk = unit_positions * (tiles per segment)
     uint32_t ntiles_max = 0, plane_stride = 0, pre_cap = 0, pend_cap = 0, rec_cap = 0, full_cap = 0;
     uint32_t chunk_epoch = 0;         // sequence number of the last submitted chunk (never 0 in a launch)
     uint32_t grow = 1;                // list capacities are `grow` times their base size (doubled after an overflow)
@@ -183,12 +185,12 @@ bool cuda_ok(adsbcu_handle *h, cudaError_t e, const char *what)
 void free_slots(adsbcu_handle *h)
 {
     for (Slot &s : h->slot) {
-        cudaFree(s.d_planes); cudaFree(s.d_pre); cudaFree(s.d_pre_count); cudaFree(s.d_pend); cudaFree(s.d_pend_count);
-        cudaFree(s.d_rec); cudaFree(s.d_rec_count); cudaFree(s.d_ordered); cudaFree(s.d_seg_flag);
-        cudaFree(s.d_run_start); cudaFree(s.d_ctr); cudaFree(s.d_accepted); cudaFree(s.d_view);
+        cudaFree(s.d_planes); cudaFree(s.d_pre); cudaFree(s.d_pre_count); cudaFree(s.d_pend);
+        cudaFree(s.d_rec); cudaFree(s.d_ordered); cudaFree(s.d_seg_flag);
+        cudaFree(s.d_run_start); cudaFree(s.d_zero); cudaFree(s.d_accepted); cudaFree(s.d_view);
         if (s.h_cand) cudaFreeHost(s.h_cand);
         if (s.h_ctr) cudaFreeHost(s.h_ctr);
-        cudaEvent_t ev[7];
+        cudaEvent_t ev[8];
         std::memcpy(ev, s.ev, sizeof(ev));
         s = Slot{};
         std::memcpy(s.ev, ev, sizeof(ev));
@@ -213,16 +215,20 @@ int alloc_slots(adsbcu_handle *h)
         CK(cudaMalloc(&s.d_pre, size_t(h->nseg) * h->pre_cap * sizeof(uint32_t)));
         CK(cudaMalloc(&s.d_pre_count, size_t(h->nseg) * sizeof(uint32_t)));
         CK(cudaMalloc(&s.d_pend, size_t(h->nseg) * h->pend_cap * sizeof(PhaseRec)));
-        CK(cudaMalloc(&s.d_pend_count, size_t(h->nseg) * sizeof(uint32_t)));
         CK(cudaMalloc(&s.d_rec, size_t(h->nseg) * h->rec_cap * sizeof(FullRec)));
-        CK(cudaMalloc(&s.d_rec_count, size_t(h->nseg) * sizeof(uint32_t)));
         CK(cudaMalloc(&s.d_ordered, size_t(h->full_cap) * sizeof(FullRec)));
         CK(cudaMalloc(&s.d_seg_flag, size_t(h->nseg) * sizeof(unsigned long long)));
         CK(cudaMemset(s.d_seg_flag, 0, size_t(h->nseg) * sizeof(unsigned long long)));
         CK(cudaMalloc(&s.d_run_start, (size_t(h->full_cap) + 1) * sizeof(uint32_t)));
         CK(cudaMalloc(&s.d_accepted, size_t(h->full_cap) * sizeof(uint2)));
         CK(cudaMalloc(&s.d_view, size_t(h->full_cap) * sizeof(uint4)));
-        CK(cudaMalloc(&s.d_ctr, sizeof(ChunkCounters)));
+        static_assert(sizeof(ChunkCounters) <= 256, "zero block layout");
+        s.zero_bytes = 256 + 2 * size_t(h->nseg) * sizeof(uint32_t);
+        CK(cudaMalloc(&s.d_zero, s.zero_bytes));
+        CK(cudaMemset(s.d_zero, 0, s.zero_bytes));
+        s.d_ctr = reinterpret_cast<ChunkCounters *>(s.d_zero);
+        s.d_rec_count = reinterpret_cast<uint32_t *>(s.d_zero + 256);
+        s.d_pend_count = s.d_rec_count + h->nseg;
         CK(cudaHostAlloc(&s.h_ctr, sizeof(ChunkCounters), cudaHostAllocDefault));
         std::memset(s.h_ctr, 0, sizeof(ChunkCounters));
     }
@@ -392,9 +398,7 @@ int run_chunks(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, ui
                 CK(launch_convert_sc16(h->d_sc16 + 2 * size_t(a.pos_begin), a.pos_end - a.pos_begin,
                                        reinterpret_cast<uint16_t *>(h->d_iq) + a.pos_begin, q11, h->stream));
         }
-        CK(cudaMemsetAsync(s.d_ctr, 0, sizeof(ChunkCounters), h->stream));
-        CK(cudaMemsetAsync(s.d_rec_count, 0, size_t(h->nseg) * sizeof(uint32_t), h->stream));
-        CK(cudaMemsetAsync(s.d_pend_count, 0, size_t(h->nseg) * sizeof(uint32_t), h->stream));
+        // the slot's counters are zero: cleared when the slot was allocated and after every use (below)
         CK(cudaEventRecord(s.ev[0], h->stream));
         CK(launch_front(a, h->stream));
         CK(cudaEventRecord(s.ev[1], h->stream));
@@ -417,6 +421,7 @@ int run_chunks(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, ui
         // order(c) needs messages(c); resolve(c) needs order(c) and resolve(c-1); level(c) needs resolve(c): three
         // streams, so that the one-CTA ordered pass of a chunk overlaps the wide kernels of its neighbours
         CK(cudaStreamWaitEvent(h->order_stream, s.ev[2], 0));
+        CK(cudaEventRecord(s.ev[7], h->order_stream));
         CK(launch_order(fa, h->order_stream));
         CK(cudaEventRecord(s.ev[6], h->order_stream));
         CK(cudaStreamWaitEvent(h->post_stream, s.ev[6], 0));
@@ -426,8 +431,10 @@ int run_chunks(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, ui
         CK(cudaStreamWaitEvent(h->level_stream, s.ev[4], 0));
         CK(launch_level(fa, h->level_grid, h->level_stream));
         CK(cudaMemcpyAsync(s.h_ctr, s.d_ctr, sizeof(ChunkCounters), cudaMemcpyDeviceToHost, h->level_stream));
+        CK(cudaMemsetAsync(s.d_zero, 0, s.zero_bytes, h->level_stream));      // ready for the slot's next chunk (submitted after ev[5])
         CK(cudaEventRecord(s.ev[5], h->level_stream));
-        st.scan_launches += 5;
+        st.launches += 5 + (upload && sc16_host ? 1 : 0);      // front, messages, order, resolve, level (+ SC16 converter)
+        st.chunks += 1;
         return ADSBCU_OK;
     };
     // host half of a chunk: its counters are on the host; candidate mode also copies the records out
@@ -447,8 +454,9 @@ int run_chunks(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, ui
         if (sink.cands) copy_candidates(s.h_cand, k.n_full, h->stream_pos, sink);
         st.preambles += k.preambles; st.phase_records += k.n_cand; st.resolved_records += k.n_full; st.messages += k.n_msgs;
         float ms = 0.f;
-        cudaEventElapsedTime(&ms, s.ev[0], s.ev[1]); st.ms_scan += ms;
-        cudaEventElapsedTime(&ms, s.ev[1], s.ev[2]); st.ms_finalize += ms;
+        cudaEventElapsedTime(&ms, s.ev[0], s.ev[1]); st.ms_front += ms;
+        cudaEventElapsedTime(&ms, s.ev[1], s.ev[2]); st.ms_messages += ms;
+        cudaEventElapsedTime(&ms, s.ev[7], s.ev[6]); st.ms_order += ms;
         cudaEventElapsedTime(&ms, s.ev[3], s.ev[4]); st.ms_resolve += ms;
         return ADSBCU_OK;
     };
@@ -468,6 +476,7 @@ int run_chunks(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, ui
     }
     if (rc != ADSBCU_OK) {
         cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->order_stream); cudaStreamSynchronize(h->post_stream); cudaStreamSynchronize(h->level_stream); cudaStreamSynchronize(h->copy_stream);
+        for (Slot &s : h->slot) if (s.d_zero) cudaMemset(s.d_zero, 0, s.zero_bytes);
         return rc;
     }
     return failed_chunk != nchunks ? kOverflowRetry : ADSBCU_OK;
@@ -485,6 +494,11 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
     for (uint32_t tps = std::min(2u, tps_cap); bounds.back() < n; tps = std::min(2 * tps, tps_cap))
         bounds.push_back(uint32_t(std::min<uint64_t>(n, uint64_t(bounds.back()) + uint64_t(h->unit_positions) * tps)));
     const uint32_t nchunks = uint32_t(bounds.size() - 1);
+    if (std::getenv("ADSBCU_DEBUG_CHUNKS")) {            // profiling runs: which launch covers how many samples
+        std::fprintf(stderr, "feed of %u samples, %u chunks:", n, nchunks);
+        for (uint32_t c = 0; c < nchunks; ++c) std::fprintf(stderr, " %u", bounds[c + 1] - bounds[c]);
+        std::fprintf(stderr, "\n");
+    }
     if (from_host) CK(cudaEventRecord(h->ev_h2d[0], h->copy_stream));
 
     uint32_t first = 0, failed = nchunks;
@@ -520,7 +534,7 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
     if (sink.cands) CK(cudaMemcpyAsync(h->d_carry_prev, h->d_carry, kOverlap * sizeof(uint16_t), cudaMemcpyDeviceToDevice, h->stream));
     if (sc16_host) CK(launch_carry_mag(reinterpret_cast<const uint16_t *>(h->d_iq), n, h->d_carry, h->stream));
     else CK(launch_carry(d_iq, n, h->d_carry, h->d_tab, h->stream));
-    h->stats.scan_launches += 1;
+    h->stats.launches += 1;               // carry kernel
     CK(cudaStreamSynchronize(h->stream));
     CK(cudaStreamSynchronize(h->order_stream));
     CK(cudaStreamSynchronize(h->post_stream));
@@ -569,6 +583,7 @@ int feed_common(adsbcu_handle *h, const uint8_t *iq, bool on_device, const int16
     OutTarget target;
     if (const int r = prepare_out(h, out, cap, target); r != ADSBCU_OK) return r;
     CK(launch_state_begin_feed(h->d_state, 1, h->post_stream));
+    h->stats.launches += 1;
     Sink sink{out, cap, 0, false};
     // a feed larger than max_feed_samples is cut into takes (multiples of 8 samples keep device pointers 16 B aligned)
     const size_t max_take = h->cfg.max_feed_samples & ~size_t(7);
@@ -1001,6 +1016,7 @@ int adsbcu_1090_revive(adsbcu_handle *h, adsbcu_cand *out, size_t cap, size_t *n
     CK(launch_revive(a, h->stream));
     CK(cudaMemcpyAsync(s.h_ctr, s.d_ctr, sizeof(ChunkCounters), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaMemsetAsync(h->d_n_deferred, 0, sizeof(uint32_t), h->stream));   // consumed
+    CK(cudaMemsetAsync(s.d_zero, 0, s.zero_bytes, h->stream));              // the slot goes back to the feeds zeroed
     CK(cudaStreamSynchronize(h->stream));
     const ChunkCounters k = *s.h_ctr;
     if (k.overflow || k.n_full > h->full_cap) { h->error = "revive: candidate list overflow"; return ADSBCU_ERR_OVERFLOW; }
