@@ -120,34 +120,87 @@ def cpu_baseline(iq: np.ndarray, nfix: int, cores: int, sample_desc: str):
     return {"value": n / dt / 1e6, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample_desc}, dt
 
 
+def message_set_hash(msgs: np.ndarray) -> tuple[int, int]:
+    """Order- and partition-independent 64-bit digest of a message list (sum of per-message mixes mod 2^64)."""
+    if len(msgs) == 0:
+        return 0, 0
+    raw = np.ascontiguousarray(msgs).view(np.uint8).reshape(len(msgs), -1)
+    pad = (-raw.shape[1]) % 8
+    if pad:
+        raw = np.concatenate([raw, np.zeros((len(msgs), pad), np.uint8)], axis=1)
+    w = raw.view(np.uint64)
+    acc = np.full(len(msgs), 0x9E3779B97F4A7C15, np.uint64)
+    with np.errstate(over="ignore"):
+        for k in range(w.shape[1]):
+            acc = (acc ^ w[:, k]) * np.uint64(0xFF51AFD7ED558CCD)
+            acc ^= acc >> np.uint64(33)
+        return len(msgs), int(acc.sum(dtype=np.uint64))
+
+
+def pieces_of(base_ptr: int, tile_samples: int, lo: int, hi: int):
+    """[lo, hi) of the capture `tile repeated` as (address, nsamples) pieces, cut at tile boundaries."""
+    out, pos = [], lo
+    while pos < hi:
+        off = pos % tile_samples
+        take = min(tile_samples - off, hi - pos)
+        out.append((base_ptr + 2 * off, take))
+        pos += take
+    return out
+
+
+def main_978(args):
+    raise SystemExit("config5: see profiles/bench_paths.py (not wired into bench.py yet)")
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--steps", type=int, default=None)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--seconds", type=float, default=60.0, help="capture length per GPU (config 2: 60 s)")
-    ap.add_argument("--nfix", type=int, default=1, help="0 none, 1 --fix, 2 --fix-2bit")
+    ap.add_argument("--seconds", type=float, default=60.0, help="length of the synthetic tile (60 s)")
+    ap.add_argument("--hours", type=float, default=None, help="capture length: the tile repeated (config3: 1, config4: 24)")
+    ap.add_argument("--nfix", type=int, default=None, help="0 none, 1 --fix, 2 --fix-2bit (default: 1; config3: 2)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="config2", choices=["config2", "config3"],
-                    help="config2 (default, the metric's configuration) or config3 (dense overlapping traffic, use --nfix 2)")
+    ap.add_argument("--workload", default="config2", choices=["config2", "config3", "config4", "config5"],
+                    help="config2 (default, the metric's configuration), config3 (1 h dense traffic, --fix-2bit), "
+                         "config4 (24 h sharded over the GPUs, strong scaling), config5 (UAT 978)")
     args = ap.parse_args()
+    if args.workload == "config5":
+        return main_978(args)
+    if args.steps is None:
+        args.steps = 100 if args.workload == "config2" else 3
+    if args.nfix is None:
+        args.nfix = 2 if args.workload == "config3" else 1
+    if args.hours is None:
+        args.hours = {"config2": 0.0, "config3": 1.0, "config4": 24.0}[args.workload]
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     from libadsb_b200 import synth
-    if args.workload == "config2":
-        workload = (f"config2: synthetic 2.4 MS/s uint8 I/Q, {args.seconds:g} s per GPU, 1000 msg/s DF17/DF11, "
-                    f"6-30 dB SNR, sigma=2 LSB, nfix_crc={args.nfix}")
-        make = lambda seed: synth.config2(seconds=args.seconds, seed=seed)[0]                   # noqa: E731
-    else:
-        workload = (f"config3: synthetic 2.4 MS/s uint8 I/Q, {args.seconds:g} s per GPU, Poisson 2000 msg/s with overlaps, "
-                    f"DF17/11/4/5/20/21/18 mix, 1-2 bit errors, sigma=2 LSB, nfix_crc={args.nfix}")
+    tile_n = int(round(args.seconds * synth.FS_1090)) // 8 * 8
+    ntiles = max(1, int(round(args.hours * 3600.0 / args.seconds)))      # tiles per capture (strong) or per GPU (weak)
+    strong = args.workload == "config4"
+    if args.workload == "config3":
+        traffic = "Poisson 2000 msg/s with overlaps, DF17/11/4/5/20/21/18 mix, 1-2 bit errors"
         make = lambda seed: synth.config3(seconds=args.seconds, seed=seed)[0]                   # noqa: E731
-    config = {"workload": workload, "samples_per_gpu": int(round(args.seconds * synth.FS_1090)),
-              "l2_policy": "input (2 B/sample, 288 MB at 60 s) larger than L2", "sharding": "contiguous ranges, weak"}
+    else:
+        traffic = "1000 msg/s DF17/DF11, 6-30 dB SNR"
+        make = lambda seed: synth.config2(seconds=args.seconds, seed=seed)[0]                   # noqa: E731
+    total_tiles = ntiles if strong else ntiles * world
+    total = tile_n * total_tiles
+    sharded = world > 1 or ntiles > 1
+    workload = (f"{args.workload}: synthetic 2.4 MS/s uint8 I/Q, {traffic}, sigma=2 LSB, nfix_crc={args.nfix}; "
+                + (f"ONE capture of {total_tiles} x {args.seconds:g} s ({total / synth.FS_1090 / 3600:.3g} h; the {args.seconds:g} s tile repeated), "
+                   f"contiguous ranges over {world} GPU(s)" if sharded else f"{args.seconds:g} s capture on one GPU"))
+    config = {"workload": workload, "samples_per_gpu": total // world, "capture_samples": total,
+              "l2_policy": f"input tile ({2 * tile_n / 1e6:.0f} MB) larger than L2",
+              "sharding": ("none" if world == 1 else
+                           "adsbcu_1090_replay_sharded: contiguous sample ranges of one capture, rank 0 gets 2 of world+1 parts (it needs one "
+                           "pass, the others two); start states by fixed-point exchange of <= 16 KiB per rank; no data-path collective")}
+    scaling = "strong" if strong else "weak"
 
     # ------------------------------------------------------------------ reference arm
     if args.impl == "reference":
@@ -158,7 +211,7 @@ def main():
         for _ in range(args.warmup):
             cpu_baseline(iq, args.nfix, cores, "")
         times = []
-        desc = f"the whole {args.seconds:g} s capture per step, split into {cores} contiguous shards, one dump1090 process each"
+        desc = (f"one {args.seconds:g} s tile of the workload per step, split into {cores} contiguous shards, one dump1090 process each")
         cb = None
         for _ in range(args.steps):
             cb, dt = cpu_baseline(iq, args.nfix, cores, desc)
@@ -168,7 +221,7 @@ def main():
         cb["value"] = v
         print(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
                           "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
-                          "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u16/i32",
+                          "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "u16/i32",
                           "data": "synthetic", "config": config, "cpu_baseline": cb,
                           "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
         return
@@ -180,9 +233,11 @@ def main():
     if rank == 0 or world == 1:
         build.build()
     torch.cuda.set_device(local_rank)
+    host_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         dist.barrier()
+        host_group = dist.new_group(backend="gloo")       # the orchestrator's exchange is host side: <= 16 KiB per rank and round
 
     def barrier():
         torch.cuda.synchronize()
@@ -190,47 +245,79 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
-    iq = make(0x10900002 + rank)
-    n = iq.size // 2
-    host = torch.from_numpy(iq).pin_memory()
+    def allgather(words: np.ndarray):
+        buf = torch.zeros(adsbcu.SHARD_WORDS + 1, dtype=torch.int32)
+        buf[0] = int(words.size)
+        buf[1:1 + words.size] = torch.from_numpy(words.view(np.int32))
+        parts = [torch.empty_like(buf) for _ in range(world)]
+        dist.all_gather(parts, buf, group=host_group)
+        return [p[1:1 + int(p[0])].numpy().view(np.uint32) for p in parts]
+
+    iq = make(0x10900002)                   # the tile: the same on every rank (one capture)
+    n = tile_n
+    host = torch.from_numpy(iq[:2 * n]).pin_memory()
     dev = host.cuda(non_blocking=False)
     hview = host.numpy()
+    # this rank's range of the capture
+    if world == 1:
+        lo, hi = 0, total
+    else:
+        cut = lambda k: total if k >= world + 1 else (total * k // (world + 1)) // 8 * 8      # noqa: E731
+        lo, hi = (0, cut(2)) if rank == 0 else (cut(rank + 1), cut(rank + 2))
+    my_n = hi - lo
+    off = lo % n
+    halo = None if lo == 0 else (hview[2 * (off - 326):2 * off] if off >= 326 else np.concatenate([hview[2 * (n - (326 - off)):], hview[:2 * off]]))
+    dev_pieces = pieces_of(dev.data_ptr(), n, lo, hi)
+    host_pieces = pieces_of(hview.ctypes.data, n, lo, hi)
     d = adsbcu.Demod1090(nfix_crc=args.nfix, fix_df=1, max_feed_samples=max(n, 1 << 20), device=local_rank)
     # out[] in pinned memory: the engine's level kernel writes the accepted messages there itself (no host copy)
-    out_pinned = torch.zeros(max(4096, n // 500) * adsbcu.MSG_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
+    probe = adsbcu.Demod1090(nfix_crc=args.nfix, fix_df=1, max_feed_samples=1 << 24, device=local_rank)
+    per_sample = (len(probe.feed_device(dev.data_ptr(), min(n, 1 << 24), np.zeros(1 << 18, adsbcu.MSG_DTYPE))) + 64) / min(n, 1 << 24)
+    probe.close()
+    out_cap = max(4096, int(my_n * per_sample * 1.5))       # sized from the message density of the tile's first 7 s
+    out_pinned = torch.zeros(out_cap * adsbcu.MSG_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
     out = out_pinned.numpy().view(adsbcu.MSG_DTYPE)
+    KEYS = ("front", "messages", "order", "resolve")
 
     def step_resident():
-        d.reset(True)
-        return d.feed_device(dev.data_ptr(), n, out)
+        """-> messages, {ms per kernel}, launches, chunks, passes, rounds"""
+        if not sharded:
+            d.reset(True)
+            m = d.feed_device(dev.data_ptr(), n, out)
+            st = d.stats()
+            return m, {k: st["ms_" + k] for k in KEYS}, st["launches"] + 1, st["chunks"], 1, 0
+        m, rep = d.replay_sharded(rank, world, dev_pieces, lo, halo, allgather, out)
+        return m, {k: getattr(rep, "ms_" + k) for k in KEYS}, rep.launches, rep.chunks, rep.passes, rep.rounds
 
     def step_e2e():
-        d.reset(True)
-        return d.feed(hview, out=out)
+        if not sharded:
+            d.reset(True)
+            m = d.feed(hview, out=out)
+            return m, len(m) * adsbcu.MSG_DTYPE.itemsize, 2 * n
+        m, rep = d.replay_sharded(rank, world, host_pieces, lo, halo, allgather, out, host_pieces=True)
+        return m, len(m) * adsbcu.MSG_DTYPE.itemsize, 2 * my_n * rep.passes
 
     sampler = ClockSampler(local_rank)
     sampler.start()                      # nvidia-smi needs ~100 ms to deliver its first row: start before the warm-up
     for _ in range(args.warmup):
-        msgs = step_resident()
-    nmsg = len(msgs)
+        msgs = step_resident()[0]
+    nmsg, digest = message_set_hash(msgs)
     t_w = time.perf_counter()
-    while len(sampler.rows) < 2 and time.perf_counter() - t_w < 3.0:   # keep the GPU under the same load until sampling runs
+    while world == 1 and len(sampler.rows) < 2 and time.perf_counter() - t_w < 3.0:   # keep the GPU under load until sampling runs
         step_resident()
     barrier()
-    kms = {"front": [], "messages": [], "order": [], "resolve": []}
-    launches, chunks = 0, 0
+    kms = {k: [] for k in KEYS}
+    launches, chunks, passes, rounds = 0, 0, 0, 0
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        step_resident()
-        st = d.stats()
-        for k in kms:
-            kms[k].append(st["ms_" + k])
-        launches += st["launches"] + 1               # + the one-thread state kernel of reset(); memsets and copies are not counted
-        chunks = st["chunks"]
+        _, ms, nl, chunks, passes, rounds = step_resident()
+        for k in KEYS:
+            kms[k].append(ms[k])
+        launches += nl
     barrier()
     t_res = time.perf_counter() - t0
 
-    # host->device ceiling for the e2e arm: one plain pinned-memory copy of the same capture, CUDA events
+    # host->device ceiling for the e2e arm: one plain pinned-memory copy of the tile, CUDA events
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     h2d_ms = []
     for _ in range(4):
@@ -241,27 +328,32 @@ def main():
         h2d_ms.append(ev0.elapsed_time(ev1))
     h2d_gbs = 2.0 * n / (min(h2d_ms[1:]) * 1e-3) / 1e9
 
-    for _ in range(2):
+    e2e_steps = args.steps if total <= 4 * n else max(1, min(args.steps, 2))
+    for _ in range(2 if total <= 4 * n else 0):
         step_e2e()
     barrier()
     t0 = time.perf_counter()
-    d2h = 0
-    for _ in range(args.steps):
-        m = step_e2e()
-        st = d.stats()
-        d2h += st["resolved_records"] * 64 + 24
+    d2h = h2d = 0
+    for _ in range(e2e_steps):
+        _, b_out, b_in = step_e2e()
+        d2h += b_out
+        h2d += b_in
     barrier()
     t_e2e = time.perf_counter() - t0
     clocks = sampler.stop()              # sampled over both timed regions (resident and end to end)
 
     tt = torch.tensor([t_res, t_e2e], dtype=torch.float64, device="cuda")
+    cnt = torch.tensor([nmsg, digest & 0xFFFFFFFF, digest >> 32, launches, passes], dtype=torch.int64, device="cuda")
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
     t_res, t_e2e = float(tt[0]), float(tt[1])
+    nmsg_all = int(cnt[0])
+    digest_all = (int(cnt[1]) + (int(cnt[2]) << 32)) & 0xFFFFFFFFFFFFFFFF
 
     if rank == 0:
         peak, peak_src = load_peaks()
-        # Per-kernel device time of one step (CUDA events on the launching streams, summed over the step's chunks).
+        # Per-kernel device time of one step ON RANK 0 (CUDA events on the launching streams, summed over the step's chunks).
         # The roofline object describes the kernel with the largest share; both dense kernels are listed under
         # "kernels".  Algorithmic bytes: 2 B per sample, each kernel makes one launch per chunk.
         per_kernel = {k: float(np.mean(v)) for k, v in kms.items()}
@@ -271,40 +363,43 @@ def main():
         except Exception:
             traffic_tab = {}
         kernels = {}
+        bytes_step = 2.0 * my_n * max(passes, 1) if sharded else 2.0 * n      # what rank 0's kernels streamed in one step
         for k, name in (("front", "front_kernel"), ("messages", "message_kernel")):
             ms = per_kernel[k]
-            gbs = 2.0 * n / (ms * 1e-3) / 1e9
+            gbs = bytes_step / (ms * 1e-3) / 1e9
             ratio = traffic_tab.get(name, {}).get("traffic_over_algorithmic")
             kernels[name] = {"ms_per_step": ms, "launches_per_step": chunks, "avg_launch_ms": ms / max(chunks, 1),
-                             "algorithmic_bytes_per_launch": 2.0 * n / max(chunks, 1), "achieved": gbs, "frac": gbs / peak,
-                             "traffic": None if ratio is None else ratio * 2.0 * n / max(chunks, 1)}
+                             "algorithmic_bytes_per_launch": bytes_step / max(chunks, 1), "achieved": gbs, "frac": gbs / peak,
+                             "traffic": None if ratio is None else ratio * bytes_step / max(chunks, 1)}
         dom = max(kernels, key=lambda name: kernels[name]["ms_per_step"])
         kd = kernels[dom]
         line = {
-            "metric": METRIC, "value": world * n * args.steps / t_res / 1e6, "unit": UNIT, "n_gpus": world,
+            "metric": METRIC, "value": total * args.steps / t_res / 1e6, "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_res / args.steps * 1e3,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u16/i32",
-            "data": "synthetic", "config": config, "clocks": clocks, "gpu_launches": launches,
-            "e2e": {"value": world * n * args.steps / t_e2e / 1e6, "unit": UNIT, "h2d_bytes_per_step": 2 * n,
-                    "d2h_bytes_per_step": d2h // args.steps},
+            "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "u16/i32",
+            "data": "synthetic", "config": config, "clocks": clocks, "gpu_launches": int(cnt[3]),
+            "e2e": {"value": total * e2e_steps / t_e2e / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d // e2e_steps,
+                    "d2h_bytes_per_step": d2h // e2e_steps, "steps": e2e_steps},
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": kd["achieved"], "peak": peak, "unit": "GB/s",
                          "frac": kd["frac"], "peak_source": peak_src, "launches_per_step": kd["launches_per_step"],
                          "algorithmic_bytes_per_launch": kd["algorithmic_bytes_per_launch"], "avg_launch_ms": kd["avg_launch_ms"],
                          "traffic": kd["traffic"],
                          "traffic_source": "profiles/ncu_traffic.json: dram read+write of one ncu --set full launch / that launch's algorithmic bytes",
                          "kernel_ms_per_step": kd["ms_per_step"],
-                         "step_frac": 2.0 * n / (t_res / args.steps) / 1e9 / peak},
+                         "step_frac": 2.0 * total / world / (t_res / args.steps) / 1e9 / peak},
             "kernels": kernels,
             "pcie": {"h2d_gbs": h2d_gbs, "h2d_ceiling_msamples_s": h2d_gbs * 1e3 / 2.0,
-                     "note": "plain pinned cudaMemcpy of the capture on this box; e2e cannot exceed world * this"},
-            "breakdown_ms": dict(per_kernel, note="device time per kernel summed over the chunks; order / resolve run on their own streams beside the next chunk's front + message kernels"),
-            "messages_per_step": nmsg,
+                     "note": "plain pinned cudaMemcpy of the tile on this box; e2e cannot exceed world * this"},
+            "breakdown_ms": dict(per_kernel, note="rank 0, device time per kernel summed over the chunks; order / resolve run on their own streams beside the next chunk's front + message kernels"),
+            "messages_per_step": nmsg_all,
+            "message_set": {"count": nmsg_all, "hash": f"{digest_all:016x}", "note": "sum mod 2^64 of a 64-bit mix of every accepted message record: independent of order and of the number of GPUs"},
         }
+        if sharded:
+            line["sharded"] = {"passes_rank0": passes, "passes_all_ranks": int(cnt[4]), "rounds": rounds, "range_samples_rank0": my_n}
         if world == 1 and not args.no_cpu_baseline:
-            from oracle import oracle1090 as O
             cores = 1
             cb, _ = cpu_baseline(iq, args.nfix, cores,
-                                 f"the whole {args.seconds:g} s capture, one dump1090 process (1 demod thread + 1 reader thread)")
+                                 f"one {args.seconds:g} s tile of the workload, one dump1090 process (1 demod thread + 1 reader thread)")
             line["cpu_baseline"] = cb
         print(json.dumps(line))
     if world > 1:

@@ -186,6 +186,55 @@ int adsbcu_1090_revive(adsbcu_handle *h, adsbcu_cand *out, size_t cap, size_t *n
 int adsbcu_1090_resolve(adsbcu_handle *h, const adsbcu_cand *cands, size_t n,
                         adsbcu_msg *out, size_t cap, size_t *n_out);
 
+/* ---- One long capture over several GPUs, every shard resolved on its own GPU (BASELINE config 4) -----
+ * The reference's unbounded-stream mechanism is the 131072-sample block + 326-sample overlap + carried
+ * last_message_end (fifo.c:173-210, demod_2400.c:106-115,432-443, dump1090.c:159-167): what one sample range
+ * needs from everything in front of it is (a) the 326 samples before it, (b) the skip state the last accepted
+ * message left behind and (c) the contents of the ICAO filter (file mode: entries are never removed,
+ * icao_filter.c:58-83).  (b) and (c) are a few KiB:
+ *
+ *   adsbcu_1090_state_export   after a feed: the skip state + every address in the filter
+ *   adsbcu_1090_state_import   after adsbcu_1090_seek, before the first feed of a range: start from that state
+ *
+ * adsbcu_1090_replay_sharded is the orchestrator on top of them.  Rank r of `world` holds ITS contiguous range of
+ * the capture in device memory (a list of pieces in stream order) and gets the messages of that range; the only
+ * exchange is the callback, an all-gather of at most ADSBCU_SHARD_WORDS 32-bit words per rank (host side; MPI,
+ * torch.distributed, threads -- whatever the caller has).  Round 0: every rank demodulates its range as if
+ * nothing preceded it.  Round k+1: a rank whose start state (skip state of rank r-1's end, union of the filters
+ * of all ranks in front of it) differs from the one it used runs its range again.  When no start state changes
+ * any more every rank has used exactly the state the sequential run would have had -- by induction over the
+ * ranks the fixed point is unique -- so the message set equals the single-stream one whatever `world` is.
+ * Typically rank 0 makes one pass and every other rank two; give rank 0 a range twice as long.
+ * Not exact (ADSBCU_ERR_OVERFLOW) once the filter holds ADSBCU_SHARD_MAX_ADDRS addresses: from there on the
+ * reference's table drops insertions and membership depends on the insertion order. */
+typedef struct adsbcu_1090_state {
+    uint64_t stream_pos;       /* samples consumed so far (information on export, ignored on import) */
+    uint64_t last_a, last_lme; /* start and last_message_end of the last accepted message, stream coordinates */
+    uint32_t has_last;
+    uint32_t reserved;
+} adsbcu_1090_state;
+int adsbcu_1090_state_export(adsbcu_handle *h, adsbcu_1090_state *st, uint32_t *addrs, size_t cap, size_t *n_addrs);
+int adsbcu_1090_state_import(adsbcu_handle *h, const adsbcu_1090_state *st, const uint32_t *addrs, size_t n_addrs);
+
+#define ADSBCU_SHARD_MAX_ADDRS 4000u
+#define ADSBCU_SHARD_WORDS     (ADSBCU_SHARD_MAX_ADDRS + 8u)
+typedef struct adsbcu_piece { const uint8_t *iq; uint64_t nsamples; } adsbcu_piece;   /* device memory, 16-byte aligned (or host, see flags) */
+/* Collective: contributes mine[0..n_mine) and fills all[q * ADSBCU_SHARD_WORDS + i] / counts[q] for every rank q. */
+typedef int (*adsbcu_allgather_fn)(void *ctx, const uint32_t *mine, uint32_t n_mine, uint32_t *all, uint32_t *counts);
+typedef struct adsbcu_shard_report {
+    uint32_t passes;           /* times THIS rank demodulated its range */
+    uint32_t rounds;           /* exchange rounds until no start state changed (same on every rank) */
+    uint32_t start_addrs;      /* filter entries this rank started its final pass with */
+    uint32_t chunks;           /* the adsbcu_stats counters below, summed over all feeds of all passes of this rank */
+    uint64_t launches;
+    double   ms_front, ms_messages, ms_order, ms_resolve, ms_h2d;
+} adsbcu_shard_report;
+enum { ADSBCU_SHARD_HOST_PIECES = 1 };  /* flags: the pieces are HOST memory (uploaded chunk by chunk, on every pass) */
+int adsbcu_1090_replay_sharded(adsbcu_handle *h, int rank, int world, const adsbcu_piece *pieces, size_t npieces,
+                               uint64_t range_start, const uint8_t *halo_iq /* HOST, <= 326 samples */, size_t n_halo,
+                               adsbcu_allgather_fn allgather, void *ctx, unsigned flags,
+                               adsbcu_msg *out, size_t cap, size_t *n_out, adsbcu_shard_report *report);
+
 /* ---- Mode A/C on one mag_buf (dump1090 --modeac) ----------------------------------------------------
  * One call == one demodulate2400AC(struct mag_buf*) call of the reference (demod_2400.c:539-726), which
  * dump1090's main loop makes right after demodulate2400 on the same buffer (dump1090.c:902-905).  The

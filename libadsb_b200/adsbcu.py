@@ -50,8 +50,26 @@ EXPORTS = ["adsbcu_abi_version", "adsbcu_last_error", "adsbcu_create", "adsbcu_d
            "adsbcu_1090_filter_test", "adsbcu_1090_filter_expire", "adsbcu_get_stats", "adsbcu_1090b_feed", "adsbcu_1090b_reset",
            "adsbcu_978_feed", "adsbcu_978_reset", "adsbcu_978_phase", "adsbcu_1090_seek", "adsbcu_1090_scan_candidates",
            "adsbcu_1090_known_export", "adsbcu_1090_known_import", "adsbcu_1090_revive", "adsbcu_1090_resolve", "adsbcu_1090_modeac_block", "adsbcu_1090_feed_sc16",
-           "adsbcu_1090_modeac_block_static",
+           "adsbcu_1090_modeac_block_static", "adsbcu_1090_state_export", "adsbcu_1090_state_import", "adsbcu_1090_replay_sharded",
            "adsbcu_1090b_decode_fields", "adsbcu_1090b_cpr_decode", "adsbcu_1090_cpr_decode"]
+
+
+class StreamStateC(C.Structure):
+    _fields_ = [("stream_pos", C.c_uint64), ("last_a", C.c_uint64), ("last_lme", C.c_uint64), ("has_last", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+class Piece(C.Structure):
+    _fields_ = [("iq_dev", C.c_void_p), ("nsamples", C.c_uint64)]
+
+
+class ShardReport(C.Structure):
+    _fields_ = [("passes", C.c_uint32), ("rounds", C.c_uint32), ("start_addrs", C.c_uint32), ("chunks", C.c_uint32), ("launches", C.c_uint64),
+                ("ms_front", C.c_double), ("ms_messages", C.c_double), ("ms_order", C.c_double), ("ms_resolve", C.c_double), ("ms_h2d", C.c_double)]
+
+
+SHARD_MAX_ADDRS = 4000
+SHARD_WORDS = SHARD_MAX_ADDRS + 8
+ALLGATHER_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_uint32), C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32))
 
 
 class Config(C.Structure):
@@ -110,6 +128,10 @@ def load():
         L.adsbcu_1090_modeac_block.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_uint64, C.c_void_p,
                                                C.c_size_t, C.POINTER(C.c_size_t)]
         L.adsbcu_1090_feed_sc16.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.adsbcu_1090_state_export.argtypes = [C.c_void_p, C.POINTER(StreamStateC), C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.adsbcu_1090_state_import.argtypes = [C.c_void_p, C.POINTER(StreamStateC), C.c_void_p, C.c_size_t]
+        L.adsbcu_1090_replay_sharded.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(Piece), C.c_size_t, C.c_uint64, C.c_void_p, C.c_size_t,
+                                                 ALLGATHER_FN, C.c_void_p, C.c_uint, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(ShardReport)]
         L.adsbcu_1090_modeac_block_static.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_uint64, C.c_void_p,
                                                       C.c_size_t, C.c_void_p, C.c_void_p]
         _lib = L
@@ -283,6 +305,46 @@ class Demod1090:
         allocated, nothing awaited.  result_dev[0] = replies, result_dev[1] = flags once `stream` has reached this point."""
         self._check(load().adsbcu_1090_modeac_block_static(self.h, iq_dev or None, nsamples, overlap_iq_dev or None, n_overlap,
                                                            block_timestamp, out_dev or None, cap, result_dev or None, stream or None))
+
+    def state_export(self):
+        """(stream_pos, has_last, last_a, last_lme), addresses in the ICAO filter."""
+        st, addrs, n = StreamStateC(), np.zeros(8192, np.uint32), C.c_size_t(0)
+        self._check(load().adsbcu_1090_state_export(self.h, C.byref(st), addrs.ctypes.data, addrs.size, C.byref(n)))
+        return (st.stream_pos, st.has_last, st.last_a, st.last_lme), addrs[:n.value].copy()
+
+    def state_import(self, has_last: int, last_a: int, last_lme: int, addrs: np.ndarray):
+        st = StreamStateC(0, last_a, last_lme, has_last, 0)
+        addrs = np.ascontiguousarray(addrs, np.uint32)
+        self._check(load().adsbcu_1090_state_import(self.h, C.byref(st), addrs.ctypes.data if addrs.size else None, addrs.size))
+
+    def replay_sharded(self, rank: int, world: int, pieces, range_start: int, halo_iq: np.ndarray | None, allgather, out: np.ndarray,
+                       host_pieces: bool = False):
+        """adsbcu_1090_replay_sharded.  pieces: [(device address, nsamples)] of THIS rank's range in stream order;
+        allgather(words: np.ndarray[uint32]) -> list of world np.ndarray[uint32] (the transport: torch.distributed, MPI, ...).
+        Returns (messages of this range, ShardReport)."""
+        arr = (Piece * max(1, len(pieces)))(*[Piece(int(p), int(n)) for p, n in pieces])
+        halo = np.ascontiguousarray(halo_iq if halo_iq is not None else np.zeros(0, np.uint8), np.uint8)
+
+        def cb(_ctx, mine, n_mine, all_, counts):
+            try:
+                parts = allgather(np.ctypeslib.as_array(mine, shape=(n_mine,)).copy())
+                for q, part in enumerate(parts):
+                    part = np.ascontiguousarray(part, np.uint32)
+                    counts[q] = part.size
+                    C.memmove(C.addressof(all_.contents) + 4 * q * SHARD_WORDS, part.ctypes.data, 4 * part.size)
+                return 0
+            except Exception as e:      # noqa: BLE001  (an exception must not cross the C frame)
+                self._cb_error = e
+                return 1
+        self._cb_error = None
+        fn = ALLGATHER_FN(cb)
+        got, rep = C.c_size_t(0), ShardReport()
+        rc = load().adsbcu_1090_replay_sharded(self.h, rank, world, arr, len(pieces), range_start, halo.ctypes.data if halo.size else None,
+                                               halo.size // 2, fn, None, 1 if host_pieces else 0, out.ctypes.data, len(out), C.byref(got), C.byref(rep))
+        if self._cb_error is not None:
+            raise self._cb_error
+        self._check(rc)
+        return out[:got.value], rep
 
     def filter_add(self, addr): self._check(load().adsbcu_1090_filter_add(self.h, addr))
     def filter_test(self, addr): return bool(load().adsbcu_1090_filter_test(self.h, addr))

@@ -837,6 +837,51 @@ int adsbcu_1090_filter_expire(adsbcu_handle *h)
     return ADSBCU_OK;
 }
 
+int adsbcu_1090_state_export(adsbcu_handle *h, adsbcu_1090_state *st, uint32_t *addrs, size_t cap, size_t *n_addrs)
+{
+    if (!h || !st || (!addrs && cap)) return ADSBCU_ERR_ARG;
+    if (n_addrs) *n_addrs = 0;
+    NEED_DEVICE(h);
+    ABI_GUARD_BEGIN
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaStreamSynchronize(h->post_stream));
+    std::vector<unsigned char> raw(sizeof(StreamState));
+    CK(cudaMemcpy(raw.data(), h->d_state, sizeof(StreamState), cudaMemcpyDeviceToHost));
+    const StreamState &ss = *reinterpret_cast<const StreamState *>(raw.data());
+    *st = adsbcu_1090_state{h->stream_pos, ss.last_a, ss.last_lme, ss.has_last, 0u};
+    size_t n = 0;
+    for (int t = 0; t < 2; ++t)
+        for (uint32_t i = 0; i < kIcaoSlots; ++i)
+            if (const uint32_t v = ss.table[t][i]; v != kIcaoEmpty) {
+                if (n < cap) addrs[n] = v;
+                ++n;
+            }
+    if (n_addrs) *n_addrs = n;
+    if (n > cap) { h->error = "addrs[] too small for the filter's entries"; return ADSBCU_ERR_OVERFLOW; }
+    return ADSBCU_OK;
+    ABI_GUARD_END(h)
+}
+
+int adsbcu_1090_state_import(adsbcu_handle *h, const adsbcu_1090_state *st, const uint32_t *addrs, size_t n_addrs)
+{
+    if (!h || !st || (!addrs && n_addrs) || n_addrs > 2 * size_t(kIcaoSlots)) return ADSBCU_ERR_ARG;
+    NEED_DEVICE(h);
+    for (size_t k = 0; k < n_addrs; ++k) h->filter.add(addrs[k]);       // (the merge-only resolver's copy, as adsbcu_1090_filter_add does)
+    CK(cudaSetDevice(h->device));
+    uint32_t *d_list = nullptr;
+    if (n_addrs) {
+        CK(cudaMalloc(&d_list, n_addrs * sizeof(uint32_t)));
+        if (!cuda_ok(h, cudaMemcpyAsync(d_list, addrs, n_addrs * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream), "cudaMemcpyAsync")) { cudaFree(d_list); return ADSBCU_ERR_CUDA; }
+    }
+    const cudaError_t e = launch_state_import(h->d_state, h->d_bitmap, st->has_last, st->last_a, st->last_lme, d_list, uint32_t(n_addrs), h->stream);
+    const cudaError_t e2 = cudaStreamSynchronize(h->stream);
+    cudaFree(d_list);
+    CK(e);
+    CK(e2);
+    return ADSBCU_OK;
+}
+
 int adsbcu_1090b_feed(adsbcu_handle *h, const uint8_t *iq, size_t nbytes, adsbcu_msg_b *out, size_t cap, size_t *n_out)
 {
     if (!h) return ADSBCU_ERR_ARG;

@@ -602,6 +602,20 @@ __global__ void filter_add_kernel(StreamState *st, uint32_t *bitmap, uint32_t ad
         atomicOr(&bitmap[bi >> 5], 1u << (bi & 31));
     }
 }
+// adsbcu_1090_state_import: the start state of a sample range (one thread; a few thousand insertions at most)
+__global__ void state_import_kernel(StreamState *st, uint32_t *bitmap, uint32_t has_last, unsigned long long last_a,
+                                    unsigned long long last_lme, const uint32_t *addrs, uint32_t n)
+{
+    st->has_last = has_last; st->last_a = last_a; st->last_lme = last_lme;
+    for (uint32_t k = 0; k < n; ++k) {
+        const uint32_t addr = addrs[k];
+        icao_add(st, addr);
+        if (!(addr & kNonIcao)) {
+            const uint32_t bi = bitmap_index(addr);
+            atomicOr(&bitmap[bi >> 5], 1u << (bi & 31));
+        }
+    }
+}
 __global__ void filter_test_kernel(const StreamState *st, uint32_t addr, uint32_t *result) { *result = icao_test(st, addr) ? 1u : 0u; }
 // icaoFilterExpire (icao_filter.c:112-127): the other table is cleared and becomes the active one; the scan's
 // "may ever be in the filter" set is rebuilt from the table that survives
@@ -663,6 +677,12 @@ cudaError_t launch_state_begin_feed(StreamState *st, int reset_count, cudaStream
 cudaError_t launch_filter_add(StreamState *st, uint32_t *bitmap, uint32_t addr, cudaStream_t s)
 {
     ADSBCU_LAUNCH(filter_add_kernel, 1, 1, 0, s, st, bitmap, addr);
+    return cudaGetLastError();
+}
+cudaError_t launch_state_import(StreamState *st, uint32_t *bitmap, uint32_t has_last, uint64_t last_a, uint64_t last_lme,
+                                const uint32_t *addrs_dev, uint32_t n, cudaStream_t s)
+{
+    ADSBCU_LAUNCH(state_import_kernel, 1, 1, 0, s, st, bitmap, has_last, (unsigned long long)last_a, (unsigned long long)last_lme, addrs_dev, n);
     return cudaGetLastError();
 }
 cudaError_t launch_filter_test(const StreamState *st, uint32_t addr, uint32_t *result_dev, cudaStream_t s)

@@ -260,6 +260,8 @@ cudaError_t launch_state_begin_feed(StreamState *st, int reset_count, cudaStream
 cudaError_t launch_filter_add(StreamState *st, uint32_t *bitmap, uint32_t addr, cudaStream_t s);
 cudaError_t launch_filter_test(const StreamState *st, uint32_t addr, uint32_t *result_dev, cudaStream_t s);
 cudaError_t launch_filter_expire(StreamState *st, uint32_t *bitmap, uint32_t nwords, cudaStream_t s);
+cudaError_t launch_state_import(StreamState *st, uint32_t *bitmap, uint32_t has_last, uint64_t last_a, uint64_t last_lme,
+                                const uint32_t *addrs_dev, uint32_t n, cudaStream_t s);
 
 // launchers (adsbcu_kernels.cu)
 cudaError_t init_kernels();                                        // per device, once (opt-in shared memory size)
