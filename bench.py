@@ -198,8 +198,8 @@ def main():
     config = {"workload": workload, "samples_per_gpu": total // world, "capture_samples": total,
               "l2_policy": f"input tile ({2 * tile_n / 1e6:.0f} MB) larger than L2",
               "sharding": ("none" if world == 1 else
-                           "adsbcu_1090_replay_sharded: contiguous sample ranges of one capture, rank 0 gets 2 of world+1 parts (it needs one "
-                           "pass, the others two); start states by fixed-point exchange of <= 16 KiB per rank; no data-path collective")}
+                           "adsbcu_1090_replay_sharded: equal contiguous sample ranges of one capture; start states (skip state + ICAO filter) by "
+                           "fixed-point exchange of <= 16 KiB per rank and round (rank 0 makes one pass, the others two); no data-path collective")}
     scaling = "strong" if strong else "weak"
 
     # ------------------------------------------------------------------ reference arm
@@ -262,8 +262,8 @@ def main():
     if world == 1:
         lo, hi = 0, total
     else:
-        cut = lambda k: total if k >= world + 1 else (total * k // (world + 1)) // 8 * 8      # noqa: E731
-        lo, hi = (0, cut(2)) if rank == 0 else (cut(rank + 1), cut(rank + 2))
+        cut = lambda k: total if k >= world else (total * k // world) // 8 * 8      # noqa: E731
+        lo, hi = cut(rank), cut(rank + 1)
     my_n = hi - lo
     off = lo % n
     halo = None if lo == 0 else (hview[2 * (off - 326):2 * off] if off >= 326 else np.concatenate([hview[2 * (n - (326 - off)):], hview[:2 * off]]))

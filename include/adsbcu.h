@@ -204,7 +204,8 @@ int adsbcu_1090_resolve(adsbcu_handle *h, const adsbcu_cand *cands, size_t n,
  * of all ranks in front of it) differs from the one it used runs its range again.  When no start state changes
  * any more every rank has used exactly the state the sequential run would have had -- by induction over the
  * ranks the fixed point is unique -- so the message set equals the single-stream one whatever `world` is.
- * Typically rank 0 makes one pass and every other rank two; give rank 0 a range twice as long.
+ * Typically rank 0 makes one pass and every other rank two (the second can only start when every rank in front has
+ * finished its first), so `world` equal ranges take the time of two passes over one of them.
  * Not exact (ADSBCU_ERR_OVERFLOW) once the filter holds ADSBCU_SHARD_MAX_ADDRS addresses: from there on the
  * reference's table drops insertions and membership depends on the insertion order. */
 typedef struct adsbcu_1090_state {

@@ -122,6 +122,7 @@ struct adsbcu_handle {
     int16_t *d_sc16 = nullptr;        // staging for SC16 / SC16Q11 host feeds (allocated on first use)
     StreamState *d_state = nullptr;
     uint32_t *h_word = nullptr, *d_word = nullptr;    // one mapped word for small device->host answers
+    uint32_t *d_import = nullptr;     // adsbcu_1090_state_import: the address list on the device (allocated on first use)
     adsbcu_msg *h_msgs = nullptr, *d_msgs = nullptr;  // accepted messages of the running feed (pinned + mapped), grown on demand
     size_t msgs_cap = 0;
 
@@ -244,7 +245,7 @@ void free_all(adsbcu_handle *h)
     if (h->order_stream) cudaStreamSynchronize(h->order_stream);
     if (h->level_stream) cudaStreamSynchronize(h->level_stream);
     if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
-    cudaFree(h->d_sc16);
+    cudaFree(h->d_sc16); cudaFree(h->d_import);
     cudaFree(h->d_ac_ov); cudaFree(h->d_ac_sums); cudaFree(h->d_ac_rec);
     if (h->h_ac_rec) cudaFreeHost(h->h_ac_rec);
     cudaFree(h->d_carry_prev); cudaFree(h->d_deferred); cudaFree(h->d_n_deferred); cudaFree(h->d_known_tmp);
@@ -869,16 +870,10 @@ int adsbcu_1090_state_import(adsbcu_handle *h, const adsbcu_1090_state *st, cons
     NEED_DEVICE(h);
     for (size_t k = 0; k < n_addrs; ++k) h->filter.add(addrs[k]);       // (the merge-only resolver's copy, as adsbcu_1090_filter_add does)
     CK(cudaSetDevice(h->device));
-    uint32_t *d_list = nullptr;
-    if (n_addrs) {
-        CK(cudaMalloc(&d_list, n_addrs * sizeof(uint32_t)));
-        if (!cuda_ok(h, cudaMemcpyAsync(d_list, addrs, n_addrs * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream), "cudaMemcpyAsync")) { cudaFree(d_list); return ADSBCU_ERR_CUDA; }
-    }
-    const cudaError_t e = launch_state_import(h->d_state, h->d_bitmap, st->has_last, st->last_a, st->last_lme, d_list, uint32_t(n_addrs), h->stream);
-    const cudaError_t e2 = cudaStreamSynchronize(h->stream);
-    cudaFree(d_list);
-    CK(e);
-    CK(e2);
+    if (n_addrs && !h->d_import) CK(cudaMalloc(&h->d_import, 2 * size_t(kIcaoSlots) * sizeof(uint32_t)));
+    if (n_addrs) CK(cudaMemcpyAsync(h->d_import, addrs, n_addrs * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+    CK(launch_state_import(h->d_state, h->d_bitmap, st->has_last, st->last_a, st->last_lme, h->d_import, uint32_t(n_addrs), h->stream));
+    CK(cudaStreamSynchronize(h->stream));           // addrs[] may be pageable: it is free again when the call returns
     return ADSBCU_OK;
 }
 

@@ -602,16 +602,24 @@ __global__ void filter_add_kernel(StreamState *st, uint32_t *bitmap, uint32_t ad
         atomicOr(&bitmap[bi >> 5], 1u << (bi & 31));
     }
 }
-// adsbcu_1090_state_import: the start state of a sample range (one thread; a few thousand insertions at most)
-__global__ void state_import_kernel(StreamState *st, uint32_t *bitmap, uint32_t has_last, unsigned long long last_a,
-                                    unsigned long long last_lme, const uint32_t *addrs, uint32_t n)
+// adsbcu_1090_state_import: the start state of a sample range.  Only membership matters (file mode never removes an
+// entry), so the addresses go in concurrently, each claiming its slot with a CAS as the resolve kernel's insertion does.
+__global__ void __launch_bounds__(256) state_import_kernel(StreamState *st, uint32_t *bitmap, uint32_t has_last, unsigned long long last_a,
+                                                            unsigned long long last_lme, const uint32_t *addrs, uint32_t n)
 {
-    st->has_last = has_last; st->last_a = last_a; st->last_lme = last_lme;
-    for (uint32_t k = 0; k < n; ++k) {
-        const uint32_t addr = addrs[k];
-        icao_add(st, addr);
-        if (!(addr & kNonIcao)) {
-            const uint32_t bi = bitmap_index(addr);
+    if (threadIdx.x == 0) { st->has_last = has_last; st->last_a = last_a; st->last_lme = last_lme; }
+    uint32_t *t = st->table[st->active];
+    for (uint32_t k = threadIdx.x; k < n; k += blockDim.x) {
+        const uint32_t v = addrs[k];
+        uint32_t h = icao_hash(v);
+        for (uint32_t probe = 0; probe < kIcaoSlots; ++probe) {
+            const uint32_t e = atomicCAS(&t[h], kIcaoEmpty, v);
+            if (e == kIcaoEmpty) { atomicAdd(&st->active_count, 1u); break; }
+            if (e == v) break;
+            h = (h + 1) & (kIcaoSlots - 1);
+        }
+        if (!(v & kNonIcao)) {
+            const uint32_t bi = bitmap_index(v);
             atomicOr(&bitmap[bi >> 5], 1u << (bi & 31));
         }
     }
@@ -682,7 +690,7 @@ cudaError_t launch_filter_add(StreamState *st, uint32_t *bitmap, uint32_t addr, 
 cudaError_t launch_state_import(StreamState *st, uint32_t *bitmap, uint32_t has_last, uint64_t last_a, uint64_t last_lme,
                                 const uint32_t *addrs_dev, uint32_t n, cudaStream_t s)
 {
-    ADSBCU_LAUNCH(state_import_kernel, 1, 1, 0, s, st, bitmap, has_last, (unsigned long long)last_a, (unsigned long long)last_lme, addrs_dev, n);
+    ADSBCU_LAUNCH(state_import_kernel, 1, 256, 0, s, st, bitmap, has_last, (unsigned long long)last_a, (unsigned long long)last_lme, addrs_dev, n);
     return cudaGetLastError();
 }
 cudaError_t launch_filter_test(const StreamState *st, uint32_t addr, uint32_t *result_dev, cudaStream_t s)

@@ -6,7 +6,11 @@
  * oracle978: plain-C CPU restatement of the 978 MHz UAT path behind libadsb's
  * UAT978Handler::HandleData (reference UAT978.cpp:43-60,76-100).
  *
- * Parity status: PARITY UNPINNED.  The arithmetic of this path lives in a dependency
+ * Parity status: stages C1 (InitATan2Table) and C2 (HandleData staging / carry) are PINNED to the reference's own
+ * UAT978.cpp compiled where it lies (oracle/_ref/libref978.so, oracle/ref_harness_978.cpp; reference-generated
+ * fixture tests/golden/uat_ref.npz): all 65536 table entries and the exact sequence of process_buffer(len, offset)
+ * calls.  Stages C3-C5 (sync search, frame demodulation, Reed-Solomon) remain PARITY UNPINNED: their arithmetic
+ * lives in a dependency
  * that is absent from /root/reference: the `dump978` submodule, pinned by
  * .SUBMODULES.json to github.com/ankurvdev/dump978 @ a461b30732162bfe1424d37ba4475e0db62b893b
  * (a fork of flightaware/dump978; the reference builds legacy/dump978.c, legacy/fec.c,
@@ -309,6 +313,9 @@ typedef struct oracle978 {
     uint64_t offset;
     oracle978_frame *out;
     size_t cap, nout;
+    int64_t calls[3 * 4096];    /* (len, offset, returned) of the process_buffer() calls HandleData made: compared with the
+                                   calls the compiled reference makes (oracle/_ref/libref978.so) */
+    size_t ncalls;
 } oracle978;
 
 static void emit(oracle978 *o, uint8_t updown, const uint8_t *data, int len, int rs_errors, uint64_t offset)
@@ -401,15 +408,36 @@ size_t oracle978_handle_data(oracle978 *o, const uint8_t *iq, size_t nbytes, ora
     o->out = out; o->cap = cap; o->nout = 0;
     while (j < n) {
         for (i = o->used; i < 65536 && j < n; i++, j++) o->buffer[i] = o->iqphase[iq[2 * j] | (iq[2 * j + 1] << 8)];
-        if ((int)i / 2 - (SYNC_BITS + UPLINK_FRAME_BITS) <= 0) { o->used = i; continue; }   /* nothing scannable yet (the
+        if ((int)i / 2 - (SYNC_BITS + UPLINK_FRAME_BITS) <= 0) {
+            if (o->ncalls < 4096) { o->calls[3 * o->ncalls] = (int64_t)i; o->calls[3 * o->ncalls + 1] = (int64_t)o->offset; o->calls[3 * o->ncalls + 2] = 0; }
+            o->ncalls++;
+            o->used = i;
+            continue;
+        }   /* nothing scannable yet (the
             reference's buffers are 262144 bytes, so it never gets here; its return value would be negative) */
         const int done = process_buffer(o, o->buffer, (int)i, o->offset);
+        if (o->ncalls < 4096) { o->calls[3 * o->ncalls] = (int64_t)i; o->calls[3 * o->ncalls + 1] = (int64_t)o->offset; o->calls[3 * o->ncalls + 2] = done; }
+        o->ncalls++;
         o->offset += (uint64_t)done;
-        memmove(o->buffer, o->buffer + done, sizeof(uint16_t) * (size_t)((int)i - done));
+        /* UAT978.cpp:57 passes the number of remaining SAMPLES as memmove's BYTE count: only the first half of the
+         * unconsumed samples moves to the front; indices [(i-done)/2, i-done) keep what they held before (for an odd
+         * remainder one sample gets its low byte only).  The compiled reference does exactly this
+         * (oracle/_ref/libref978.so, tests/golden/uat_ref.npz), so frames that reach into that stretch are seen
+         * corrupted, and a drop-in has to see them the same way. */
+        memmove(o->buffer, o->buffer + done, (size_t)((int)i - done));
         o->used = (size_t)((int)i - done);
     }
     return o->nout;
 }
+
+/* the calls logged so far: 3 int64 each; returns their number (the log keeps the first 4096) */
+size_t oracle978_calls(const oracle978 *o, int64_t *out, size_t cap)
+{
+    const size_t n = o->ncalls < 4096 ? o->ncalls : 4096;
+    memcpy(out, o->calls, 3 * sizeof(int64_t) * (n < cap ? n : cap));
+    return o->ncalls;
+}
+void oracle978_state(const oracle978 *o, uint64_t out[2]) { out[0] = o->used; out[1] = o->offset; }
 
 /* one process_buffer() call on explicit phase samples (the extern "C" entry of UAT978.cpp:10) */
 int oracle978_process_buffer(oracle978 *o, const uint16_t *phi, int len, uint64_t offset, oracle978_frame *out, size_t cap, size_t *nout)

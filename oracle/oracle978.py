@@ -28,6 +28,9 @@ def lib():
         L.oracle978_handle_data.restype = C.c_size_t
         L.oracle978_handle_data.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
         L.oracle978_process_buffer.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_uint64, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.oracle978_calls.restype = C.c_size_t
+        L.oracle978_calls.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+        L.oracle978_state.argtypes = [C.c_void_p, C.c_void_p]
         L.oracle978_rs_encode.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
         L.oracle978_rs_decode.argtypes = [C.c_int, C.c_void_p]
         L.oracle978_correct_adsb.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
@@ -58,6 +61,18 @@ class Oracle978:
         n = lib().oracle978_handle_data(self.h, iq.ctypes.data, iq.size, out.ctypes.data, cap)
         assert n <= cap
         return out[:n]
+
+    def calls(self) -> np.ndarray:
+        """(len, offset, returned) of every process_buffer() call HandleData made so far."""
+        buf = np.zeros((4096, 3), np.int64)
+        n = lib().oracle978_calls(self.h, buf.ctypes.data, 4096)
+        assert n <= 4096
+        return buf[:n]
+
+    def state(self):
+        s = np.zeros(2, np.uint64)
+        lib().oracle978_state(self.h, s.ctypes.data)
+        return int(s[0]), int(s[1])
 
     def process_buffer(self, phi: np.ndarray, offset: int = 0, cap: int = 1 << 14):
         phi = np.ascontiguousarray(phi, dtype=np.uint16)
