@@ -149,7 +149,100 @@ def pieces_of(base_ptr: int, tile_samples: int, lo: int, hi: int):
 
 
 def main_978(args):
-    raise SystemExit("config5: see profiles/bench_paths.py (not wired into bench.py yet)")
+    """config5: UAT 978 MHz, 2.083334 MS/s, through UAT978Handler::HandleData's replacement (adsbcu_978_feed).
+    A step = one 60 s capture.  value: samples resident in HBM (adsbcu_978_feed_device, one call); e2e: host buffers fed in the
+    reference's 262144-byte HandleData buffers (RTLSDR.hpp:55).  cpu_baseline: the oracle port (dump978 itself is not in the
+    reference tree, so there is no reference binary for this path) on a bounded sample."""
+    import torch
+    from libadsb_b200 import adsbcu, build, synth978
+    build.build()
+    metric, unit = "Msamples/s UAT demod+RS", "Msamples/s"
+    steps = args.steps if args.steps is not None else 5
+    iq = synth978.config5(seconds=args.seconds)[0]
+    n = iq.size // 2
+    config = {"workload": f"config5: synthetic 2.083334 MS/s uint8 I/Q, {args.seconds:g} s, 200 ADS-B frames/s (80 % long) + 1 uplink frame/s, "
+                          "0..t corrupted bytes per RS block, sigma=2 LSB", "samples_per_gpu": n,
+              "l2_policy": f"input ({2 * n / 1e6:.0f} MB) larger than L2"}
+    if args.impl == "reference":
+        from oracle import oracle978 as O
+        sample = iq[:2 * min(n, int(10 * synth978.FS_978))]
+        times = []
+        for _ in range(max(1, args.warmup) + steps):
+            o = O.Oracle978()
+            t0 = time.perf_counter()
+            o.handle_data(sample, cap=1 << 16)
+            times.append(time.perf_counter() - t0)
+        dt = float(np.mean(times[max(1, args.warmup):]))
+        v = sample.size / 2 / dt / 1e6
+        cb = {"value": v, "unit": unit, "cores": 1, "kind": "port",
+              "sample": "first 10 s of the capture, one call (oracle/oracle978.c; dump978 is an absent submodule of the reference)"}
+        print(json.dumps({"impl": "reference", "metric": metric, "value": v, "unit": unit, "n_gpus": args.gpus, "steps": steps,
+                          "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                          "dtype": "u16/i16/gf256", "data": "synthetic", "config": config, "cpu_baseline": cb,
+                          "e2e": {"value": v, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+    torch.cuda.set_device(0)
+    host = torch.from_numpy(iq).pin_memory()
+    dev = host.cuda()
+    hview = host.numpy()
+    d = adsbcu.Demod1090()
+    out = np.zeros(1 << 16, adsbcu.UAT_DTYPE)
+    BUF = 262144
+
+    def step_resident():
+        d.reset_uat()
+        f = d.handle_data_uat_device(dev.data_ptr(), iq.size, out)
+        return f, d.uat_stats()
+
+    def step_e2e():
+        d.reset_uat()
+        return sum(len(d.handle_data_uat(hview[k:k + BUF])) for k in range(0, iq.size, BUF))
+
+    sampler = ClockSampler(0)
+    sampler.start()
+    for _ in range(max(3, args.warmup)):
+        frames, st = step_resident()
+    nframes = len(frames)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    dev_ms, launches, calls = [], 0, 0
+    for _ in range(steps):
+        _, st = step_resident()
+        dev_ms.append(st["ms_device"]); launches += st["launches"]; calls = st["calls"]
+    torch.cuda.synchronize()
+    t_res = time.perf_counter() - t0
+    step_e2e()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        ne = step_e2e()
+    t_e2e = time.perf_counter() - t0
+    clocks = sampler.stop()
+    peak, peak_src = load_peaks()
+    k_ms = float(np.mean(dev_ms))
+    achieved = 2.0 * n / (k_ms * 1e-3) / 1e9
+    line = {"metric": metric, "value": n * steps / t_res / 1e6, "unit": unit, "n_gpus": 1, "steps": steps, "warmup": max(3, args.warmup),
+            "ms_per_step": t_res / steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u16/i16/gf256",
+            "data": "synthetic", "config": config, "clocks": clocks, "gpu_launches": launches,
+            "e2e": {"value": n * steps / t_e2e / 1e6, "unit": unit, "h2d_bytes_per_step": 2 * n, "d2h_bytes_per_step": int(ne) * adsbcu.UAT_DTYPE.itemsize,
+                    "note": "262144-byte HandleData buffers from pageable host memory, as the reference's RTL-SDR callback delivers them"},
+            "roofline": {"bound": "hbm", "kernel": "all kernels of the feed (phase table gather + per process_buffer() call: sync search, frame decode, staging shift)",
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
+                         "launches_per_step": launches // steps, "algorithmic_bytes_per_launch": 2.0 * n / max(launches // steps, 1),
+                         "avg_launch_ms": k_ms / max(launches // steps, 1), "traffic": None, "kernel_ms_per_step": k_ms,
+                         "note": "device time includes the host round trip between process_buffer() calls: the reference's staging is a serial "
+                                 "state machine (what a call presents depends on what the previous one consumed), so the calls run one after another"},
+            "process_buffer_calls_per_step": calls, "frames_per_step": nframes,
+            "realtime_factor": n * steps / t_res / synth978.FS_978}
+    if not args.no_cpu_baseline:
+        from oracle import oracle978 as O
+        sample = iq[:2 * min(n, int(10 * synth978.FS_978))]
+        o = O.Oracle978()
+        t0 = time.perf_counter()
+        o.handle_data(sample, cap=1 << 16)
+        dt = time.perf_counter() - t0
+        line["cpu_baseline"] = {"value": sample.size / 2 / dt / 1e6, "unit": unit, "cores": 1, "kind": "port",
+                                "sample": "first 10 s of the capture, one call (oracle/oracle978.c; dump978 is an absent submodule of the reference)"}
+    print(json.dumps(line))
 
 
 def main():

@@ -387,6 +387,16 @@ typedef struct adsbcu_uat_frame {
  * sampled at 2.083334 MS/s (HOST memory).  The stream continues across calls. */
 int adsbcu_978_feed(adsbcu_handle *h, const uint8_t *iq, size_t nbytes,
                     adsbcu_uat_frame *out, size_t cap, size_t *n_out);
+/* The same with the samples already in DEVICE memory (resident replay; bench.py's `value`). */
+int adsbcu_978_feed_device(adsbcu_handle *h, const uint8_t *iq_dev, size_t nbytes,
+                           adsbcu_uat_frame *out, size_t cap, size_t *n_out);
+typedef struct adsbcu_978_stats {
+    float    ms_device;        /* device time of the last feed: upload + phase kernel + every process_buffer() call's kernels */
+    uint32_t calls;            /* process_buffer() calls the feed made (UAT978.cpp:54) */
+    uint32_t launches;         /* kernels launched */
+    uint32_t reserved;
+} adsbcu_978_stats;
+int adsbcu_978_get_stats(const adsbcu_handle *h, adsbcu_978_stats *out);
 /* A fresh UAT978Handler: forget the staged samples and the stream offset. */
 int adsbcu_978_reset(adsbcu_handle *h);
 /* Stage-level entry: phi_out[k] = iqphase[{I,Q}] (UAT978.cpp:52) for k < nsamples, HOST pointers. */

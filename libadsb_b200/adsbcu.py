@@ -48,7 +48,7 @@ KNOWN_WORDS = 1 << 20
 EXPORTS = ["adsbcu_abi_version", "adsbcu_last_error", "adsbcu_create", "adsbcu_destroy", "adsbcu_1090_reset",
            "adsbcu_1090_feed", "adsbcu_1090_feed_device", "adsbcu_1090_magnitude", "adsbcu_1090_filter_add",
            "adsbcu_1090_filter_test", "adsbcu_1090_filter_expire", "adsbcu_get_stats", "adsbcu_1090b_feed", "adsbcu_1090b_reset",
-           "adsbcu_978_feed", "adsbcu_978_reset", "adsbcu_978_phase", "adsbcu_1090_seek", "adsbcu_1090_scan_candidates",
+           "adsbcu_978_feed", "adsbcu_978_feed_device", "adsbcu_978_get_stats", "adsbcu_978_reset", "adsbcu_978_phase", "adsbcu_1090_seek", "adsbcu_1090_scan_candidates",
            "adsbcu_1090_known_export", "adsbcu_1090_known_import", "adsbcu_1090_revive", "adsbcu_1090_resolve", "adsbcu_1090_modeac_block", "adsbcu_1090_feed_sc16",
            "adsbcu_1090_modeac_block_static", "adsbcu_1090_state_export", "adsbcu_1090_state_import", "adsbcu_1090_replay_sharded",
            "adsbcu_1090b_decode_fields", "adsbcu_1090b_cpr_decode", "adsbcu_1090_cpr_decode"]
@@ -70,6 +70,10 @@ class ShardReport(C.Structure):
 SHARD_MAX_ADDRS = 4000
 SHARD_WORDS = SHARD_MAX_ADDRS + 8
 ALLGATHER_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_uint32), C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32))
+
+
+class Stats978(C.Structure):
+    _fields_ = [("ms_device", C.c_float), ("calls", C.c_uint32), ("launches", C.c_uint32), ("reserved", C.c_uint32)]
 
 
 class Config(C.Structure):
@@ -116,6 +120,8 @@ def load():
         L.adsbcu_1090b_cpr_decode.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         L.adsbcu_1090_cpr_decode.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         L.adsbcu_978_feed.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.adsbcu_978_feed_device.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.adsbcu_978_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats978)]
         L.adsbcu_978_reset.argtypes = [C.c_void_p]
         L.adsbcu_978_phase.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         L.adsbcu_1090_seek.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_size_t]
@@ -239,6 +245,17 @@ class Demod1090:
         got = C.c_size_t(0)
         self._check(load().adsbcu_978_feed(self.h, iq.ctypes.data, iq.size, out.ctypes.data, cap, C.byref(got)))
         return out[:got.value]
+
+    def handle_data_uat_device(self, iq_dev: int, nbytes: int, out: np.ndarray) -> np.ndarray:
+        """Path C with the samples already in device memory (iq_dev: device address)."""
+        got = C.c_size_t(0)
+        self._check(load().adsbcu_978_feed_device(self.h, iq_dev, nbytes, out.ctypes.data, len(out), C.byref(got)))
+        return out[:got.value]
+
+    def uat_stats(self) -> dict:
+        s = Stats978()
+        self._check(load().adsbcu_978_get_stats(self.h, C.byref(s)))
+        return {"ms_device": s.ms_device, "calls": s.calls, "launches": s.launches}
 
     def reset_uat(self):
         self._check(load().adsbcu_978_reset(self.h))

@@ -932,7 +932,29 @@ int adsbcu_978_feed(adsbcu_handle *h, const uint8_t *iq, size_t nbytes, adsbcu_u
     NEED_DEVICE(h);
     if ((!iq && nbytes) || (!out && cap)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
     CK(cudaSetDevice(h->device));
-    return pathc_feed(h->pathc, h->sm_count, h->stream, iq, nbytes, out, cap, n_out, h->error);
+    ABI_GUARD_BEGIN
+    return pathc_feed(h->pathc, h->sm_count, h->stream, iq, nbytes, false, out, cap, n_out, h->error);
+    ABI_GUARD_END(h)
+}
+
+int adsbcu_978_feed_device(adsbcu_handle *h, const uint8_t *iq_dev, size_t nbytes, adsbcu_uat_frame *out, size_t cap, size_t *n_out)
+{
+    if (!h) return ADSBCU_ERR_ARG;
+    if (n_out) *n_out = 0;
+    NEED_DEVICE(h);
+    if ((!iq_dev && nbytes) || (!out && cap) || (reinterpret_cast<uintptr_t>(iq_dev) & 1u)) { h->error = "bad argument (null or odd device pointer)"; return ADSBCU_ERR_ARG; }
+    CK(cudaSetDevice(h->device));
+    ABI_GUARD_BEGIN
+    return pathc_feed(h->pathc, h->sm_count, h->stream, iq_dev, nbytes, true, out, cap, n_out, h->error);
+    ABI_GUARD_END(h)
+}
+
+int adsbcu_978_get_stats(const adsbcu_handle *h, adsbcu_978_stats *out)
+{
+    if (!h || !out) return ADSBCU_ERR_ARG;
+    *out = adsbcu_978_stats{};
+    pathc_stats(h->pathc, &out->ms_device, &out->calls, &out->launches);
+    return ADSBCU_OK;
 }
 
 int adsbcu_978_reset(adsbcu_handle *h)

@@ -320,8 +320,9 @@ void fields_free(Fields *f);
 
 // Path C (adsbcu_uat.cu): 978 MHz UAT
 struct PathC;
-int  pathc_feed(PathC *&c, int sm_count, cudaStream_t s, const uint8_t *iq, size_t nbytes, adsbcu_uat_frame *out, size_t cap,
+int  pathc_feed(PathC *&c, int sm_count, cudaStream_t s, const uint8_t *iq, size_t nbytes, bool on_device, adsbcu_uat_frame *out, size_t cap,
                 size_t *n_out, std::string &err);
+void pathc_stats(const PathC *c, float *ms_device, uint32_t *calls, uint32_t *launches);
 int  pathc_phase(PathC *&c, int sm_count, cudaStream_t s, const uint8_t *iq, size_t n, uint16_t *phi_out, std::string &err);
 void pathc_reset(PathC *c);
 void pathc_free(PathC *c);

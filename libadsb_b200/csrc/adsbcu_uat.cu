@@ -242,30 +242,50 @@ __global__ void __launch_bounds__(64) uat_decode_kernel(const uint16_t *phi, uin
     for (int i = 0; i < len; ++i) r.data[i] = out[i];
 }
 
+// UAT978.cpp:57 as compiled: memmove(buffer, buffer + done, len - done) -- the count is in BYTES although it is the number
+// of SAMPLES left, so only the first half of the unconsumed samples reaches the front and indices [(len-done)/2, len-done)
+// keep what they held (oracle/_ref/libref978.so shows it; tests/golden/uat_ref.npz).  Out of place: src -> dst, all 65536.
+__global__ void __launch_bounds__(256) uat_shift_kernel(const uint16_t *src, uint16_t *dst, uint32_t done, uint32_t len)
+{
+    const uint32_t moved_bytes = len - done;
+    const uint8_t *sb = reinterpret_cast<const uint8_t *>(src);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < 65536u; i += gridDim.x * blockDim.x) {
+        uint32_t lo = sb[2 * i], hi = sb[2 * i + 1];
+        if (2 * i < moved_bytes) lo = sb[2 * (done + i)];
+        if (2 * i + 1 < moved_bytes) hi = sb[2 * (done + i) + 1];
+        dst[i] = uint16_t(lo | (hi << 8));
+    }
+}
+
 }  // namespace
 
 struct PathC {
     uint16_t *d_lut = nullptr;
     Gf *d_gf = nullptr;
-    uint8_t *d_iq = nullptr;      size_t iq_cap = 0;
-    uint16_t *d_phi = nullptr;    size_t phi_cap = 0;     // [tail of the stream | new samples]
+    uint8_t *d_iq = nullptr;      size_t iq_cap = 0;      // upload staging for host feeds
+    uint16_t *d_new = nullptr;    size_t new_cap = 0;     // phases of the feed's samples
+    uint16_t *d_buf[2] = {nullptr, nullptr};              // UAT978Handler::buffer as the reference sees it (+ slack), double-buffered
+    int cur = 0;
     uint16_t *d_phi_out = nullptr; size_t phi_out_cap = 0;
     CandC *d_cand = nullptr;      uint32_t cand_cap = 0;
     RecC *d_rec = nullptr, *h_rec = nullptr; uint32_t rec_cap = 0;
     CountersC *d_ctr = nullptr, *h_ctr = nullptr;
-    uint64_t abs_end = 0;         // samples received so far
-    uint32_t held = 0;            // samples kept in d_phi from earlier calls (the last `held` of the stream)
-    uint64_t eval_next = 0;       // first absolute position not yet evaluated on the device
+    cudaEvent_t ev[2] = {nullptr, nullptr};
     // UAT978Handler state (UAT978.cpp:106-107)
     uint64_t offset = 0;          // absolute sample of buffer[0]
     uint64_t used = 0;            // samples in the staging buffer
-    std::vector<RecC> pending;    // decoded candidates not yet passed by the emulated scan, sorted by s
+    std::vector<RecC> pending;    // decoded candidates of the running process_buffer() call, sorted by s
+    // timings of the last feed (bench.py)
+    float ms_device = 0.f;
+    uint32_t calls = 0, launches = 0;
 };
 
 void pathc_free(PathC *c)
 {
     if (!c) return;
-    cudaFree(c->d_lut); cudaFree(c->d_gf); cudaFree(c->d_iq); cudaFree(c->d_phi); cudaFree(c->d_phi_out); cudaFree(c->d_cand); cudaFree(c->d_rec);
+    cudaFree(c->d_lut); cudaFree(c->d_gf); cudaFree(c->d_iq); cudaFree(c->d_new); cudaFree(c->d_buf[0]); cudaFree(c->d_buf[1]); cudaFree(c->d_phi_out);
+    cudaFree(c->d_cand); cudaFree(c->d_rec);
+    for (auto &e : c->ev) if (e) cudaEventDestroy(e);
     cudaFree(c->d_ctr);
     if (c->h_rec) cudaFreeHost(c->h_rec);
     if (c->h_ctr) cudaFreeHost(c->h_ctr);
@@ -298,13 +318,28 @@ static int pathc_init(PathC *&c, std::string &err)
     CKC_(cudaMemcpy(c->d_gf, &gf, sizeof(Gf), cudaMemcpyHostToDevice));
     CKC_(cudaMalloc(&c->d_ctr, sizeof(CountersC)));
     CKC_(cudaHostAlloc(&c->h_ctr, sizeof(CountersC), cudaHostAllocDefault));
+    for (auto &b : c->d_buf) {
+        CKC_(cudaMalloc(&b, (65536 + 512) * sizeof(uint16_t)));
+        CKC_(cudaMemset(b, 0, (65536 + 512) * sizeof(uint16_t)));              // std::ranges::fill(buffer, 0) (UAT978.cpp:32)
+    }
+    c->cand_cap = c->rec_cap = 8192;                                           // per process_buffer() call (<= 65536 samples)
+    CKC_(cudaMalloc(&c->d_cand, size_t(c->cand_cap) * sizeof(CandC)));
+    CKC_(cudaMalloc(&c->d_rec, size_t(c->rec_cap) * sizeof(RecC)));
+    CKC_(cudaHostAlloc(&c->h_rec, size_t(c->rec_cap) * sizeof(RecC), cudaHostAllocDefault));
+    for (auto &e : c->ev) CKC_(cudaEventCreate(&e));
     return ADSBCU_OK;
+}
+
+void pathc_stats(const PathC *c, float *ms_device, uint32_t *calls, uint32_t *launches)
+{
+    *ms_device = c ? c->ms_device : 0.f; *calls = c ? c->calls : 0u; *launches = c ? c->launches : 0u;
 }
 
 void pathc_reset(PathC *c)
 {
     if (!c) return;
-    c->abs_end = 0; c->held = 0; c->eval_next = 0; c->offset = 0; c->used = 0; c->pending.clear();
+    c->offset = 0; c->used = 0; c->pending.clear();
+    for (auto &b : c->d_buf) if (b) cudaMemset(b, 0, (65536 + 512) * sizeof(uint16_t));
 }
 
 namespace {
@@ -324,7 +359,7 @@ inline uint32_t sigma_at(const RecC &r, int64_t x)           // x: absolute samp
 
 }  // namespace
 
-int pathc_feed(PathC *&c, int sm_count, cudaStream_t st, const uint8_t *iq, size_t nbytes, adsbcu_uat_frame *out, size_t cap,
+int pathc_feed(PathC *&c, int sm_count, cudaStream_t st, const uint8_t *iq, size_t nbytes, bool on_device, adsbcu_uat_frame *out, size_t cap,
                size_t *n_out, std::string &err)
 {
     if (n_out) *n_out = 0;
@@ -333,81 +368,16 @@ int pathc_feed(PathC *&c, int sm_count, cudaStream_t st, const uint8_t *iq, size
     const size_t n = nbytes / 2;
     if (!n) return ADSBCU_OK;
     if (n > 0x7FFF0000ull) { err = "buffer too large"; return ADSBCU_ERR_ARG; }
+    c->ms_device = 0.f; c->calls = 0; c->launches = 0;
 
-    // ---- device: phases of the new samples behind the carried tail, sync search, frame decode ----------
-    if (c->iq_cap < n * 2) { cudaFree(c->d_iq); c->d_iq = nullptr; c->iq_cap = 0; CKC_(cudaMalloc(&c->d_iq, n * 2 + 64)); c->iq_cap = n * 2; }
-    if (c->phi_cap < c->held + n + 128) {
-        uint16_t *np = nullptr;
-        CKC_(cudaMalloc(&np, (kTail + n + 128) * sizeof(uint16_t)));
-        if (c->held) CKC_(cudaMemcpyAsync(np, c->d_phi, c->held * sizeof(uint16_t), cudaMemcpyDeviceToDevice, st));
-        CKC_(cudaStreamSynchronize(st));
-        cudaFree(c->d_phi);
-        c->d_phi = np; c->phi_cap = kTail + n + 128;
-    }
-    const uint32_t want_cand = uint32_t(std::max<size_t>(4096, n / 256));
-    if (c->cand_cap < want_cand) {
-        cudaFree(c->d_cand); cudaFree(c->d_rec); if (c->h_rec) cudaFreeHost(c->h_rec);
-        c->d_cand = nullptr; c->d_rec = nullptr; c->h_rec = nullptr; c->cand_cap = c->rec_cap = 0;
-        CKC_(cudaMalloc(&c->d_cand, size_t(want_cand) * sizeof(CandC)));
-        CKC_(cudaMalloc(&c->d_rec, size_t(want_cand) * sizeof(RecC)));
-        CKC_(cudaHostAlloc(&c->h_rec, size_t(want_cand) * sizeof(RecC), cudaHostAllocDefault));
-        c->cand_cap = c->rec_cap = want_cand;
-    }
-    CKC_(cudaMemcpyAsync(c->d_iq, iq, n * 2, cudaMemcpyHostToDevice, st));
-    CKC_(cudaMemsetAsync(c->d_ctr, 0, sizeof(CountersC), st));
-    ADSBCU_LAUNCH(uat_phase_kernel, sm_count * 8, 256, 0, st, c->d_iq, uint32_t(n), c->d_lut, c->d_phi + c->held);
+    // ---- device: phases of the feed's samples (UAT978.cpp:52), once per feed ------------------------------
+    if (!on_device && c->iq_cap < n * 2) { cudaFree(c->d_iq); c->d_iq = nullptr; c->iq_cap = 0; CKC_(cudaMalloc(&c->d_iq, n * 2 + 64)); c->iq_cap = n * 2; }
+    if (c->new_cap < n) { cudaFree(c->d_new); c->d_new = nullptr; c->new_cap = 0; CKC_(cudaMalloc(&c->d_new, n * 2 + 64)); c->new_cap = n; }
+    CKC_(cudaEventRecord(c->ev[0], st));
+    if (!on_device) CKC_(cudaMemcpyAsync(c->d_iq, iq, n * 2, cudaMemcpyHostToDevice, st));
+    ADSBCU_LAUNCH(uat_phase_kernel, sm_count * 8, 256, 0, st, on_device ? iq : c->d_iq, uint32_t(n), c->d_lut, c->d_new);
     CKC_(cudaGetLastError());
-    CKC_(cudaMemsetAsync(c->d_phi + c->held + n, 0, 128 * sizeof(uint16_t), st));
-    const uint64_t new_end = c->abs_end + n;
-    const uint64_t abs_of_index0 = c->abs_end - c->held;                   // absolute sample of d_phi[0]
-    const uint64_t eval_end = new_end >= uint64_t(kNeed) ? new_end - kNeed + 1 : 0;   // positions s with s + kNeed <= new_end
-    uint32_t nrec = 0;
-    if (eval_end > c->eval_next) {
-        const uint32_t first = uint32_t(c->eval_next - abs_of_index0), last = uint32_t(eval_end - abs_of_index0);
-        ADSBCU_LAUNCH(uat_sync_kernel, (last - first + 255) / 256, 256, 0, st, c->d_phi, first, last, c->d_cand, c->cand_cap, c->d_ctr);
-        CKC_(cudaGetLastError());
-        CKC_(cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(CountersC), cudaMemcpyDeviceToHost, st));
-        CKC_(cudaStreamSynchronize(st));
-        if (c->h_ctr->overflow || c->h_ctr->n_cand > c->cand_cap) { err = "internal candidate list overflow"; return ADSBCU_ERR_OVERFLOW; }
-        const uint32_t ncand = c->h_ctr->n_cand;
-        if (ncand) {
-            ADSBCU_LAUNCH(uat_decode_kernel, (ncand + 63) / 64, 64, 0, st, c->d_phi, abs_of_index0, c->d_cand, c->d_rec, c->rec_cap, c->d_ctr, c->d_gf);
-            CKC_(cudaGetLastError());
-            CKC_(cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(CountersC), cudaMemcpyDeviceToHost, st));
-            CKC_(cudaStreamSynchronize(st));
-            if (c->h_ctr->overflow) { err = "internal record list overflow"; return ADSBCU_ERR_OVERFLOW; }
-            nrec = c->h_ctr->n_rec;
-            if (nrec) {
-                CKC_(cudaMemcpyAsync(c->h_rec, c->d_rec, size_t(nrec) * sizeof(RecC), cudaMemcpyDeviceToHost, st));
-                CKC_(cudaStreamSynchronize(st));
-            }
-        }
-        c->eval_next = eval_end;
-    }
-    // keep the tail of the stream for the next call
-    {
-        const uint64_t total = c->held + n;
-        const uint32_t keep = uint32_t(std::min<uint64_t>(total, kTail));
-        if (total > keep) {
-            // ranges may overlap when n < kTail: stage through the (now free) candidate-independent iq buffer is not
-            // large enough in general, so copy in two steps via d_phi's own slack only when disjoint
-            if (total - keep >= keep) {
-                CKC_(cudaMemcpyAsync(c->d_phi, c->d_phi + (total - keep), keep * sizeof(uint16_t), cudaMemcpyDeviceToDevice, st));
-            } else {
-                uint16_t *tmp = nullptr;
-                CKC_(cudaMalloc(&tmp, keep * sizeof(uint16_t)));
-                CKC_(cudaMemcpyAsync(tmp, c->d_phi + (total - keep), keep * sizeof(uint16_t), cudaMemcpyDeviceToDevice, st));
-                CKC_(cudaMemcpyAsync(c->d_phi, tmp, keep * sizeof(uint16_t), cudaMemcpyDeviceToDevice, st));
-                CKC_(cudaStreamSynchronize(st));
-                cudaFree(tmp);
-            }
-        }
-        CKC_(cudaStreamSynchronize(st));
-        c->held = keep;
-        c->abs_end = new_end;
-    }
-    std::sort(c->h_rec, c->h_rec + nrec, [](const RecC &a, const RecC &b) { return a.s != b.s ? a.s < b.s : a.uplink < b.uplink; });
-    c->pending.insert(c->pending.end(), c->h_rec, c->h_rec + nrec);
+    ++c->launches;
 
     // ---- host: replay UAT978Handler::HandleData's staging and process_buffer()'s scan ----------------------
     size_t nout = 0;
@@ -430,12 +400,40 @@ int pathc_feed(PathC *&c, int sm_count, cudaStream_t st, const uint8_t *iq, size
         }
         ++nout;
     };
-    uint64_t fed = new_end - n;                              // absolute index of the next sample HandleData copies in
-    while (fed < new_end) {
-        const uint64_t i = std::min<uint64_t>(65536, c->used + (new_end - fed));   // UAT978.cpp:52
+    // One iteration == one process_buffer() call of the reference (UAT978.cpp:48-59).  The staging buffer lives on the
+    // device exactly as the reference's does on the host -- including what its short memmove leaves behind -- and every
+    // call gets its own sync search and frame decode over that buffer: the positions a call presents are not a window
+    // of the stream.
+    size_t fed = 0;                                          // samples of this feed already copied into the buffer
+    while (fed < n) {
+        const uint64_t i = std::min<uint64_t>(65536, c->used + (n - fed));   // UAT978.cpp:52
+        uint16_t *buf = c->d_buf[c->cur];
+        CKC_(cudaMemcpyAsync(buf + c->used, c->d_new + fed, (i - c->used) * sizeof(uint16_t), cudaMemcpyDeviceToDevice, st));
         fed += i - c->used;
         const int64_t len = int64_t(i), lenbits = len / 2 - (kSyncBits + kUpBits);
-        if (lenbits <= 0) { c->used = i; continue; }          // never happens with the reference's 262144-byte buffers
+        // fewer than 36 scannable bits: the reference's process_buffer would return a negative count and its caller would
+        // memmove from in front of the buffer (undefined); it needs a feed that ends within 72 samples of the scan limit.
+        // Defined here (and in the oracle) as "nothing consumed".
+        if (lenbits < kSyncBits) { c->used = i; continue; }
+        // candidates the scan can try: index = 2 * startbit + {0, 1} (+ 1 for the second alignment), startbit <= lenbits - 36
+        const uint32_t last = uint32_t(2 * (lenbits - kSyncBits + 1) + 3);
+        CKC_(cudaMemsetAsync(c->d_ctr, 0, sizeof(CountersC), st));
+        ADSBCU_LAUNCH(uat_sync_kernel, (last + 255) / 256, 256, 0, st, buf, 0u, last, c->d_cand, c->cand_cap, c->d_ctr);
+        ADSBCU_LAUNCH(uat_decode_kernel, c->cand_cap / 64, 64, 0, st, buf, c->offset, c->d_cand, c->d_rec, c->rec_cap, c->d_ctr, c->d_gf);
+        CKC_(cudaGetLastError());
+        constexpr uint32_t kFirst = 32;                       // records fetched together with the counters
+        CKC_(cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(CountersC), cudaMemcpyDeviceToHost, st));
+        CKC_(cudaMemcpyAsync(c->h_rec, c->d_rec, kFirst * sizeof(RecC), cudaMemcpyDeviceToHost, st));
+        CKC_(cudaStreamSynchronize(st));
+        c->launches += 2; ++c->calls;
+        if (c->h_ctr->overflow || c->h_ctr->n_cand > c->cand_cap) { err = "internal candidate list overflow"; return ADSBCU_ERR_OVERFLOW; }
+        const uint32_t nrec = c->h_ctr->n_rec;
+        if (nrec > kFirst) {
+            CKC_(cudaMemcpyAsync(c->h_rec + kFirst, c->d_rec + kFirst, size_t(nrec - kFirst) * sizeof(RecC), cudaMemcpyDeviceToHost, st));
+            CKC_(cudaStreamSynchronize(st));
+        }
+        std::sort(c->h_rec, c->h_rec + nrec, [](const RecC &a, const RecC &b) { return a.s != b.s ? a.s < b.s : a.uplink < b.uplink; });
+        c->pending.assign(c->h_rec, c->h_rec + nrec);
         const uint64_t B = c->offset;
         int64_t bit = 0;                                      // the scan's loop variable
         Regs regs;
@@ -490,10 +488,16 @@ int pathc_feed(PathC *&c, int sm_count, cudaStream_t st, const uint8_t *iq, size
         const int64_t done = (bit - kSyncBits) * 2;
         c->offset += uint64_t(done);
         c->used = uint64_t(len - done);
-        // records before the new buffer start can never be tried again
-        auto cut = std::lower_bound(c->pending.begin(), c->pending.end(), c->offset, [](const RecC &r, uint64_t v) { return r.s < v; });
-        c->pending.erase(c->pending.begin(), cut);
+        // UAT978.cpp:57: the (short) memmove, into the other buffer
+        ADSBCU_LAUNCH(uat_shift_kernel, 64, 256, 0, st, buf, c->d_buf[c->cur ^ 1], uint32_t(done), uint32_t(len));
+        CKC_(cudaGetLastError());
+        ++c->launches;
+        c->cur ^= 1;
     }
+    CKC_(cudaEventRecord(c->ev[1], st));
+    CKC_(cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&c->ms_device, c->ev[0], c->ev[1]);
+    c->pending.clear();
     if (n_out) *n_out = nout;
     if (overflow) { err = "out[] too small for the decoded frames"; return ADSBCU_ERR_OVERFLOW; }
     return ADSBCU_OK;

@@ -408,7 +408,7 @@ size_t oracle978_handle_data(oracle978 *o, const uint8_t *iq, size_t nbytes, ora
     o->out = out; o->cap = cap; o->nout = 0;
     while (j < n) {
         for (i = o->used; i < 65536 && j < n; i++, j++) o->buffer[i] = o->iqphase[iq[2 * j] | (iq[2 * j + 1] << 8)];
-        if ((int)i / 2 - (SYNC_BITS + UPLINK_FRAME_BITS) <= 0) {
+        if ((int)i / 2 - (SYNC_BITS + UPLINK_FRAME_BITS) < SYNC_BITS) {   /* fewer than 36 scannable bits: see below */
             if (o->ncalls < 4096) { o->calls[3 * o->ncalls] = (int64_t)i; o->calls[3 * o->ncalls + 1] = (int64_t)o->offset; o->calls[3 * o->ncalls + 2] = 0; }
             o->ncalls++;
             o->used = i;
@@ -443,7 +443,7 @@ void oracle978_state(const oracle978 *o, uint64_t out[2]) { out[0] = o->used; ou
 int oracle978_process_buffer(oracle978 *o, const uint16_t *phi, int len, uint64_t offset, oracle978_frame *out, size_t cap, size_t *nout)
 {
     o->out = out; o->cap = cap; o->nout = 0;
-    const int done = len / 2 - (SYNC_BITS + UPLINK_FRAME_BITS) > 0 ? process_buffer(o, phi, len, offset) : 0;
+    const int done = len / 2 - (SYNC_BITS + UPLINK_FRAME_BITS) >= SYNC_BITS ? process_buffer(o, phi, len, offset) : 0;
     *nout = o->nout;
     return done;
 }

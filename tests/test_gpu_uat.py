@@ -57,3 +57,39 @@ def test_uat_edges(adsbcu_mod, O):
     iq = S.synth_capture(200000, bits, starts, np.full(40, 50.0), 1.0, rng)
     want, got = O.Oracle978().handle_data(iq), adsbcu_mod.Demod1090().handle_data_uat(iq)
     assert len(want) >= 30 and same(want, got)
+
+
+def test_gpu_uat_equals_reference_fixture(adsbcu_mod):
+    """tests/golden/uat_ref.npz was produced by the reference's own UAT978.cpp compiled in place (phase table, staging loop with
+    its short memmove, UAT978.cpp:43-60,76-100; tests/make_golden_978.py): same table, same frames at the same offsets."""
+    import os
+    from libadsb_b200 import synth978 as S
+    with np.load(os.path.join(os.path.dirname(__file__), "golden", "uat_ref.npz")) as z:
+        table, offs, rs, ln = z["phase_table"], z["frame_offsets"], z["frame_rs"], z["frame_len"]
+        iq = S.config5(seconds=float(z["seconds"]), seed=int(z["seed"]))[0]
+        buf = int(z["buf"])
+    d = adsbcu_mod.Demod1090()
+    idx = np.arange(65536)
+    probe = np.zeros(2 * 65536, dtype=np.uint8)
+    probe[0::2], probe[1::2] = idx & 255, idx >> 8
+    assert np.array_equal(d.uat_phase(probe), table)
+    frames = np.concatenate([d.handle_data_uat(iq[k:k + buf]) for k in range(0, iq.size, buf)])
+    assert np.array_equal(frames["offset"], offs) and np.array_equal(frames["rs_errors"], rs) and np.array_equal(frames["len"], ln)
+
+
+def test_gpu_uat_device_feed_equals_host_feed(adsbcu_mod):
+    import os
+    from libadsb_b200 import synth978 as S
+    iq = S.config5(seconds=1.0, seed=12)[0]
+    d = adsbcu_mod.Demod1090()
+    want = d.handle_data_uat(iq)
+    d.reset_uat()
+    if os.environ.get("ADSBCU_TEST_EMU") == "1":
+        keep, ptr = iq, iq.ctypes.data
+    else:
+        import torch
+        keep = torch.from_numpy(iq).cuda()
+        ptr = keep.data_ptr()
+    got = d.handle_data_uat_device(ptr, iq.size, np.zeros(1 << 14, adsbcu_mod.UAT_DTYPE))
+    assert len(want) > 100 and same(want, got)
+    assert d.uat_stats()["calls"] >= 30
