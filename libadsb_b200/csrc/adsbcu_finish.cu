@@ -292,7 +292,7 @@ struct ResolveSmem {
     uint32_t table[2][kIcaoSlots];             // the reference's two filter tables as of the batch's start
     uint2 ent[kRBatch];                        // x: feed position, y: view flags (bits 0..15) | score of the accepted record << 16
     AddMap cur, next;
-    uint32_t scan[kRThreads];
+    uint16_t cand[kRBatch];                    // batch-relative indices of the records that can be accepted, ascending
     uint32_t warp_tot[kRThreads / 32 + 1];
     uint32_t nkeys_cur, nkeys_next, changed, nruns, cut, last_acc, batch_msgs;
     uint8_t rank[24];                          // score_rank by (kind, known)
@@ -366,6 +366,7 @@ __global__ void __launch_bounds__(kRThreads, 1) resolve_kernel(FinishArgs fa)
     uint32_t total = 0;                           // messages written so far (uniform)
     uint32_t ia = 0;
     bool sequential = fa.force_sequential != 0;
+    SkipState entry = carried;                    // skip state in front of the batch: the last accepted message so far
 
     while (ia < n && !sequential) {
         // ---- the batch's entries into shared memory (coalesced); later batches see the table the earlier ones left ----
@@ -383,62 +384,88 @@ __global__ void __launch_bounds__(kRThreads, 1) resolve_kernel(FinishArgs fa)
         for (uint32_t i = tid; i < kMapSlots; i += kRThreads) { sm.cur.key[i] = kMapEmpty; sm.cur.pos[i] = kMapEmpty; sm.next.key[i] = kMapEmpty; sm.next.pos[i] = kMapEmpty; }
         if (tid == 0) { sm.nkeys_cur = 0; sm.nkeys_next = 0; sm.changed = 0; sm.nruns = 0; sm.cut = 0; sm.batch_msgs = 0; }
         __syncthreads();
-        auto starts_run = [&](uint32_t i) { return i == ia || sm.ent[i - ia].x - sm.ent[i - 1 - ia].x >= 288u; };
-        // ---- the batch ends at a run boundary: the last run start inside it, unless it reaches the chunk's end ----
+        // ---- the batch ends between two start positions (records of one position are never split) ---------------------
         uint32_t ib = ib_t;
         if (ib_t < n) {
             uint32_t best = 0;
-            for (uint32_t i = ia + 1 + tid; i < ib_t; i += kRThreads) if (starts_run(i)) best = i;    // ascending per thread
+            for (uint32_t i = max(ia + 1, ib_t - min(ib_t - ia, 8u)) + tid; i < ib_t; i += kRThreads)
+                if (sm.ent[i - ia].x != sm.ent[i - 1 - ia].x) best = i;
             best = __reduce_max_sync(0xFFFFFFFFu, best);
             if ((tid & 31) == 0 && best) atomicMax(&sm.cut, best);
             __syncthreads();
             ib = sm.cut;
-            if (ib == 0) { sequential = true; break; }                   // one run longer than a batch: replay sequentially
+            if (ib == 0) { sequential = true; break; }                   // (a batch of a handful of records at one position)
         }
-        // ---- runs: a record starts a run when it is 288 or more samples after its predecessor ----------------------
-        uint32_t R = 0;
-        for (uint32_t t0 = ia; t0 < ib; t0 += kRThreads) {
-            const uint32_t i = t0 + tid;
-            const bool f = i < ib && starts_run(i);
-            uint32_t cnt = 0;
-            const uint32_t off = block_flag_scan(f, sm.warp_tot, cnt);
-            if (f) run_start[R + off] = i;
-            R += cnt;
-        }
-        if (tid == 0) run_start[R] = ib;
-        __syncthreads();
         if (ia == 0) ORDER_MARK(4);
 
-        // ---- rounds: every thread walks its runs (r = tid, tid + 1024, ...) against the batch's first_add map ----------
+        // ---- rounds: scores and best-of-phases in parallel over the records, then the skip rule over the few records
+        // that can be accepted at all ("candidates": the winner of a position whose score reaches the threshold).  Only an
+        // accepted message changes the skip state, and it reaches at most 288 samples ahead, so the candidate list falls
+        // apart into runs wherever two neighbours are 288 or more samples apart; every thread walks its runs (r = tid,
+        // tid + 1024, ...) on its own against the batch's first_add map.  The gaps are between CANDIDATES, not between
+        // records: dense noise records (--fix-2bit) that can never win do not glue runs together.
         for (int round = 0;; ++round) {
             const bool use_map = sm.nkeys_cur != 0u;
+            // scores (provisional, in the high half of the entry)
+            for (uint32_t i = ia + tid; i < ib; i += kRThreads) {
+                const uint2 e = sm.ent[i - ia];
+                const uint32_t w = e.y & 0xFFFFu;
+                const bool known = (w & 0x200u) || (use_map && map_lookup(sm.cur, view[i].y) < e.x);
+                const uint32_t sc = sm.rank[2u * (w & 0xFFu) + (known ? 1u : 0u)];
+                sm.ent[i - ia].y = w | (sc << 16);
+            }
+            __syncthreads();
+            // winners: the first record of its position with the highest score (phases ascending; strict > keeps the lowest
+            // phase on ties), if that score reaches the threshold.  Compacted in index order into sm.cand.
+            uint32_t ncand = 0;
+            for (uint32_t t0 = ia; t0 < ib; t0 += kRThreads) {
+                const uint32_t i = t0 + tid;
+                bool win = false;
+                if (i < ib) {
+                    const uint2 e = sm.ent[i - ia];
+                    const uint32_t sc = e.y >> 16;
+                    win = sc >= uint32_t(kAcceptThreshold);
+                    for (uint32_t j = i; win && j > ia && sm.ent[j - 1 - ia].x == e.x; --j) win = (sm.ent[j - 1 - ia].y >> 16) < sc;
+                    for (uint32_t j = i + 1; win && j < ib && sm.ent[j - ia].x == e.x; ++j) win = (sm.ent[j - ia].y >> 16) <= sc;
+                }
+                uint32_t cnt = 0;
+                const uint32_t off = block_flag_scan(win, sm.warp_tot, cnt);
+                if (win) sm.cand[ncand + off] = uint16_t(i - ia);
+                ncand += cnt;
+            }
+            __syncthreads();
+            // every record that is not a winner loses its provisional score; runs of the candidate list
+            for (uint32_t i = ia + tid; i < ib; i += kRThreads) sm.ent[i - ia].y &= 0xFFFFu;
+            __syncthreads();
+            uint32_t R = 0;
+            for (uint32_t t0 = 0; t0 < ncand; t0 += kRThreads) {
+                const uint32_t k = t0 + tid;
+                const bool f = k < ncand && (k == 0 || sm.ent[sm.cand[k]].x - sm.ent[sm.cand[k - 1]].x >= 288u);
+                uint32_t cnt = 0;
+                const uint32_t off = block_flag_scan(f, sm.warp_tot, cnt);
+                if (f) run_start[R + off] = k;
+                R += cnt;
+            }
+            if (tid == 0) run_start[R] = ncand;
+            __syncthreads();
             for (uint32_t r = tid; r < R; r += kRThreads) {
-                SkipState ss = (ia == 0 && r == 0) ? carried : SkipState{0u, 0, 0};
-                uint32_t i = run_start[r];
-                const uint32_t i1 = run_start[r + 1];
-                uint2 cur = sm.ent[i - ia];
-                while (i < i1) {
-                    const uint32_t pos = cur.x;
+                SkipState ss = r == 0 ? entry : SkipState{0u, 0, 0};
+                const uint32_t k1 = run_start[r + 1];
+                for (uint32_t k = run_start[r]; k < k1; ++k) {
+                    const uint32_t j = sm.cand[k];
+                    const uint2 e = sm.ent[j];
+                    const uint32_t pos = e.x, w = e.y & 0xFFFFu;
                     const uint64_t pa = feed_base + pos;
                     // inside the mag_buf of the last accepted message scanning resumes 18 samples before its end
                     // (j = last_message_end - 19, then ++j); a later mag_buf starts exactly at its end (demod_2400.c:410-443)
                     const bool skip = ss.has_last && pa < (blk_of(pa) == blk_of(ss.last_a) ? ss.last_lme - 18 : ss.last_lme);
-                    uint32_t best = 0, bi = i, best_w = 0;                          // SR_NOT_SET
-                    do {                            // phases ascending; strict > keeps the lowest phase on ties
-                        const uint32_t w = cur.y & 0xFFFFu;
-                        const bool known = (w & 0x200u) || (use_map && map_lookup(sm.cur, view[i].y) < pos);
-                        const uint32_t sc = sm.rank[2u * (w & 0xFFu) + (known ? 1u : 0u)];
-                        if (sc > best) { best = sc; bi = i; best_w = w; }
-                        sm.ent[i - ia].y = w;      // no score
-                        ++i;
-                        if (i < i1) cur = sm.ent[i - ia];
-                    } while (i < i1 && cur.x == pos);
-                    if (skip || best < uint32_t(kAcceptThreshold)) continue;
-                    sm.ent[bi - ia].y = best_w | (best << 16);
-                    if (best_w & 0x400u) map_insert_min(sm.next, view[bi].z, pos, &sm.nkeys_next);
+                    if (skip) continue;
+                    const bool known = (w & 0x200u) || (use_map && map_lookup(sm.cur, view[ia + j].y) < pos);
+                    sm.ent[j].y = w | (uint32_t(sm.rank[2u * (w & 0xFFu) + (known ? 1u : 0u)]) << 16);
+                    if (w & 0x400u) map_insert_min(sm.next, view[ia + j].z, pos, &sm.nkeys_next);
                     ss.has_last = 1u;
                     ss.last_a = pa;
-                    ss.last_lme = pa + uint64_t((((best_w & 0x100u) ? 112 : 56) + 8) * 12 / 5);
+                    ss.last_lme = pa + uint64_t((((w & 0x100u) ? 112 : 56) + 8) * 12 / 5);
                 }
             }
             __syncthreads();
@@ -508,6 +535,12 @@ __global__ void __launch_bounds__(kRThreads, 1) resolve_kernel(FinishArgs fa)
         }
         __threadfence();
         __syncthreads();
+        if (const uint32_t li = sm.last_acc; li > ia) { // (uniform) the next batch starts behind this batch's last accepted message
+            const uint4 v = view[li - 1];
+            const uint64_t pa = feed_base + v.x;
+            entry = SkipState{1u, pa, pa + uint64_t((((v.w & 0x100u) ? 112 : 56) + 8) * 12 / 5)};
+        }
+        __syncthreads();
         ia = ib;
     }
 
@@ -515,7 +548,7 @@ __global__ void __launch_bounds__(kRThreads, 1) resolve_kernel(FinishArgs fa)
         // the reference's own loop from record `ia` on, one thread, on the tables in global memory: exact whatever they hold
         __syncthreads();
         if (tid == 0) {
-            SkipState ss = ia == 0 ? carried : SkipState{0u, 0, 0};
+            SkipState ss = entry;
             uint64_t k = total;
             uint32_t last = sm.last_acc;
             resolve_range(view, ia, n, feed_base, block, ss,
