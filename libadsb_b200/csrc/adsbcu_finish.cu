@@ -289,7 +289,10 @@ constexpr int kRThreads = 1024;
 constexpr uint32_t kRBatch = 16384;
 
 struct ResolveSmem {
-    uint32_t table[2][kIcaoSlots];             // the reference's two filter tables as of the batch's start
+    uint32_t set[2 * kIcaoSlots];              // the contents of the reference's two filter tables as of the batch's start, as ONE
+                                               // open-addressing set (entry = address | kInActive if the active table holds it): the
+                                               // answers of icaoFilterTest without its probe chains, which are 4096 long once a
+                                               // table is full (file mode never empties it)
     uint2 ent[kRBatch];                        // x: feed position, y: view flags (bits 0..15) | score of the accepted record << 16
     AddMap cur, next;
     uint16_t cand[kRBatch];                    // batch-relative indices of the records that can be accepted, ascending
@@ -297,6 +300,29 @@ struct ResolveSmem {
     uint32_t nkeys_cur, nkeys_next, changed, nruns, cut, last_acc, batch_msgs;
     uint8_t rank[24];                          // score_rank by (kind, known)
 };
+
+constexpr uint32_t kInActive = 1u << 30, kSetMask = 2u * kIcaoSlots - 1u;
+__device__ __forceinline__ uint32_t set_hash(uint32_t v) { return (v * 2654435761u) >> 19 & kSetMask; }
+__device__ __forceinline__ void set_insert(uint32_t *set, uint32_t v, uint32_t flag)
+{
+    uint32_t h = set_hash(v);
+    for (uint32_t n = 0; n <= kSetMask; ++n) {
+        const uint32_t e = atomicCAS(&set[h], kIcaoEmpty, v | flag);
+        if (e == kIcaoEmpty) return;
+        if ((e & ~kInActive) == v) { if (flag) atomicOr(&set[h], flag); return; }
+        h = (h + 1) & kSetMask;
+    }
+}
+__device__ __forceinline__ uint32_t set_find(const uint32_t *set, uint32_t v)     // the entry, or kIcaoEmpty
+{
+    uint32_t h = set_hash(v);
+    for (uint32_t n = 0; n <= kSetMask; ++n) {
+        const uint32_t e = set[h];
+        if (e == kIcaoEmpty || (e & ~kInActive) == v) return e;
+        h = (h + 1) & kSetMask;
+    }
+    return kIcaoEmpty;
+}
 
 // exclusive prefix of a per-thread flag over the CTA: ballot inside the warp, one shuffle scan of the 32 warp totals
 __device__ __forceinline__ uint32_t block_flag_scan(bool f, uint32_t *warp_tot, uint32_t &total)
@@ -371,14 +397,23 @@ __global__ void __launch_bounds__(kRThreads, 1) resolve_kernel(FinishArgs fa)
     while (ia < n && !sequential) {
         // ---- the batch's entries into shared memory (coalesced); later batches see the table the earlier ones left ----
         const uint32_t ib_t = min(n, ia + min(kRBatch, max(fa.batch, 2u)));
-        for (uint32_t i = tid; i < 2u * kIcaoSlots; i += kRThreads) sm.table[0][i] = __ldcg(&st->table[0][i]);   // (past L1: the batch before wrote them)
+        for (uint32_t i = tid; i < 2u * kIcaoSlots; i += kRThreads) sm.set[i] = kIcaoEmpty;
+        __syncthreads();
+        for (uint32_t i = tid; i < 2u * kIcaoSlots; i += kRThreads) {
+            const uint32_t v = __ldcg(&st->table[0][i]);                 // (past L1: the batch before wrote them); both tables are contiguous
+            if (v != kIcaoEmpty) set_insert(sm.set, v, (i >> 12) == active ? kInActive : 0u);
+        }
+        const bool table_full = __ldcg(&st->active_count) >= kIcaoSlots;  // every insertion would be dropped (icao_filter.c:71-84)
         __syncthreads();
 #pragma unroll 4
         for (uint32_t i = ia + tid; i < ib_t; i += kRThreads) {
             const uint4 v = view[i];
             uint32_t w = v.w & 0x1FFu;
-            if (icao_probe(sm.table[0], v.y) || icao_probe(sm.table[1], v.y)) w |= 0x200u;         // known when the batch starts
-            if (v.z != kUnchecked && !icao_probe(sm.table[active], v.z)) w |= 0x400u;              // accepting it adds a new address
+            if (set_find(sm.set, v.y) != kIcaoEmpty) w |= 0x200u;                                   // known when the batch starts
+            if (v.z != kUnchecked && !table_full) {
+                const uint32_t e = set_find(sm.set, v.z);
+                if (e == kIcaoEmpty || !(e & kInActive)) w |= 0x400u;                               // accepting it adds a new address
+            }
             sm.ent[i - ia] = make_uint2(v.x, w);
         }
         for (uint32_t i = tid; i < kMapSlots; i += kRThreads) { sm.cur.key[i] = kMapEmpty; sm.cur.pos[i] = kMapEmpty; sm.next.key[i] = kMapEmpty; sm.next.pos[i] = kMapEmpty; }
@@ -477,7 +512,8 @@ __global__ void __launch_bounds__(kRThreads, 1) resolve_kernel(FinishArgs fa)
             const bool changed = sm.changed != 0u;
             const uint32_t nk = sm.nkeys_next;
             __syncthreads();
-            if (nk > kMapMaxKeys || st->active_count + nk >= kIcaoSlots - 1 || round >= 12) { sequential = true; break; }
+            // a batch that could FILL the table takes the sequential replay (which addresses still get in depends on the order)
+            if (nk > kMapMaxKeys || (nk && st->active_count + nk > kIcaoSlots) || round >= 12) { sequential = true; break; }
             if (!changed) break;
             for (uint32_t i = tid; i < kMapSlots; i += kRThreads) {
                 sm.cur.key[i] = sm.next.key[i]; sm.cur.pos[i] = sm.next.pos[i];

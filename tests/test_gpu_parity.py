@@ -155,3 +155,22 @@ def test_full_size_properties(adsbcu_mod, oracle_mod):
     t_end = 5 * (n5 - 326)
     head = msgs[msgs["timestamp"] < t_end]
     assert oracle_mod.same_messages(want[want["timestamp"] < t_end], head) == []
+
+
+@pytest.mark.gpu
+def test_filter_saturation(adsbcu_mod, oracle_mod):
+    """More aircraft than the reference's filter has slots (4096, icao_filter.c:26): insertions are dropped once the table is full
+    and membership then depends on the insertion order.  The engine has to follow the reference through the transition (its
+    ordered pass falls back to the sequential replay for the batch that fills the table) and afterwards (static table)."""
+    from libadsb_b200 import synth
+    iq = synth.config3(seconds=7.0, seed=4096, msgs_per_s=3500.0, pool=20000)[0]
+    want = oracle_mod.Oracle1090(1, 1).feed(iq, cap=1 << 18)
+    d = adsbcu_mod.Demod1090(1, 1)
+    got = d.feed(iq)
+    assert oracle_mod.same_messages(want, got) == []
+    _, addrs = d.state_export()
+    assert len(addrs) == 4096                              # the table is full
+    got2 = d.feed(iq)                                      # and stays as it is: a second pass over the same samples
+    want2 = oracle_mod.Oracle1090(1, 1)
+    want2.feed(iq, cap=1 << 18)
+    assert oracle_mod.same_messages(want2.feed(iq, cap=1 << 18), got2) == []
