@@ -82,13 +82,23 @@ public:
     using Sink = std::function<void(adsbcu_msg const &)>;   // == useModesMessage(struct modesMessage*)
     // mode_ac: also run demodulate2400AC on every buffer, after the Mode S pass (dump1090 --modeac, dump1090.c:902-905);
     // one HandleData call is then treated as one mag_buf of the reference
+    // live: the samples come from an SDR, not from a file -- the reference then flips its two ICAO filter tables every
+    // MODES_ICAO_FILTER_TTL = 60 s of wall time (backgroundTasks -> icaoFilterExpire, dump1090.c:469-472,
+    // icao_filter.c:112-127; the first call flips at once); file replays never do
     ModeS2400Handler(Sink sink, int nfix_crc = 0, int fix_df = 1, int device = 0, uint32_t max_feed_samples = 1u << 24,
-                     bool mode_ac = false)
-        : eng_(make_config(device, nfix_crc, fix_df, max_feed_samples)), sink_(std::move(sink)), out_(1u << 16), mode_ac_(mode_ac)
+                     bool mode_ac = false, bool live = false)
+        : eng_(make_config(device, nfix_crc, fix_df, max_feed_samples)), sink_(std::move(sink)), out_(1u << 16), mode_ac_(mode_ac), live_(live)
     {
     }
     void HandleData(std::span<uint8_t const> const &data) override
     {
+        if (live_) {
+            const auto now = std::chrono::steady_clock::now();
+            if (now >= next_flip_) {
+                eng_.check(adsbcu_1090_filter_expire(eng_.get()), "adsbcu_1090_filter_expire");
+                next_flip_ = now + std::chrono::seconds(60);
+            }
+        }
         size_t n = 0;
         const size_t cap = out_.size();
         int rc = adsbcu_1090_feed(eng_.get(), data.data(), data.size() / 2, out_.data(), cap, &n);
@@ -130,7 +140,8 @@ private:
     Engine eng_;
     Sink sink_;
     std::vector<adsbcu_msg> out_;
-    bool mode_ac_ = false;
+    bool mode_ac_ = false, live_ = false;
+    std::chrono::steady_clock::time_point next_flip_{};
     std::vector<uint8_t> tail_;
     uint64_t samples_seen_ = 0;
 };

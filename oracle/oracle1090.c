@@ -44,7 +44,8 @@ struct oracle1090 {
     synd_entry *tab_short, *tab_long;
     int n_short, n_long;
     uint32_t valid_short, valid_long;   /* DF pre-filter bitsets */
-    uint32_t filter[FILTER_SLOTS];      /* file mode: the active table never flips (dump1090.c:469-472) */
+    uint32_t filter2[2][FILTER_SLOTS];  /* icao_filter_a / icao_filter_b (icao_filter.c:28-30) */
+    int filter_active;                  /* file mode: never flips (dump1090.c:469-472); oracle1090_filter_expire() is the live-mode flip */
     uint16_t lut[65536];
     uint16_t *mag;                      /* OVERLAP + block */
     uint16_t tail[OVERLAP];             /* fifo.c overlap_buffer */
@@ -161,7 +162,7 @@ static synd_entry *build_table(const oracle1090 *o, int bits, int max_correct, i
     return t;
 }
 
-/* ---- ICAO filter: dump1090/icao_filter.c:40-109 (single active table, no expiry) ----- */
+/* ---- ICAO filter: dump1090/icao_filter.c:40-109 (two tables; expiry only when the test injects it) ----- */
 static uint32_t filter_hash(uint32_t a)
 {
     uint32_t h = 0;
@@ -176,24 +177,39 @@ static uint32_t filter_hash(uint32_t a)
     return h & (FILTER_SLOTS - 1);
 }
 
-void oracle1090_filter_add(oracle1090 *o, uint32_t addr)
+void oracle1090_filter_add(oracle1090 *o, uint32_t addr)        /* icaoFilterAdd, icao_filter.c:58-84: the active table only */
 {
+    uint32_t *t = o->filter2[o->filter_active];
     uint32_t h0 = filter_hash(addr), h = h0;
-    while (o->filter[h] != FILTER_EMPTY && o->filter[h] != addr) {
+    while (t[h] != FILTER_EMPTY && t[h] != addr) {
         h = (h + 1) & (FILTER_SLOTS - 1);
         if (h == h0) return;            /* table full: silently dropped */
     }
-    if (o->filter[h] == FILTER_EMPTY) o->filter[h] = addr;
+    if (t[h] == FILTER_EMPTY) t[h] = addr;
 }
 
-int oracle1090_filter_test(oracle1090 *o, uint32_t addr)
+static int filter_probe(const uint32_t *t, uint32_t addr)
 {
     uint32_t h0 = filter_hash(addr), h = h0;
-    while (o->filter[h] != FILTER_EMPTY && o->filter[h] != addr) {
+    while (t[h] != FILTER_EMPTY && t[h] != addr) {
         h = (h + 1) & (FILTER_SLOTS - 1);
         if (h == h0) break;
     }
-    return o->filter[h] == addr;
+    return t[h] == addr;
+}
+
+int oracle1090_filter_test(oracle1090 *o, uint32_t addr)         /* icaoFilterTest, icao_filter.c:86-109: both tables */
+{
+    return filter_probe(o->filter2[0], addr) || filter_probe(o->filter2[1], addr);
+}
+
+/* icaoFilterExpire when its 60 s timer fires (icao_filter.c:112-127): the OTHER table is emptied and becomes the
+ * active one; what was active stays readable until the next flip.  The reference calls it from backgroundTasks for
+ * live SDR input only (dump1090.c:469-472); the tests inject the flips at chosen points of the stream. */
+void oracle1090_filter_expire(oracle1090 *o)
+{
+    o->filter_active ^= 1;
+    memset(o->filter2[o->filter_active], 0xFF, sizeof(o->filter2[0]));
 }
 
 /* ---- message correction: dump1090/mode_s.c:252-346 ----------------------------------- */
@@ -628,7 +644,8 @@ oracle1090 *oracle1090_create(int nfix_crc, int fix_df, unsigned block_samples)
         o->valid_short |= damage_set(11, 1);
         o->valid_long |= damage_set(17, o->nfix) | damage_set(18, o->nfix);
     }
-    memset(o->filter, 0xFF, sizeof(o->filter));
+    memset(o->filter2, 0xFF, sizeof(o->filter2));
+    o->filter_active = 0;
     oracle1090_mag_table(o->lut);
     o->mag = calloc(OVERLAP + o->block, sizeof(uint16_t));
     if (!o->mag) { oracle1090_destroy(o); return NULL; }

@@ -68,6 +68,7 @@ int      oracle1090_score(oracle1090 *o, const uint8_t msg[14]); /* mode_s.c:350
 size_t   oracle1090_syndrome_table(oracle1090 *o, int bits, uint32_t *out, size_t cap);
 void     oracle1090_filter_add(oracle1090 *o, uint32_t addr);
 int      oracle1090_filter_test(oracle1090 *o, uint32_t addr);
+void     oracle1090_filter_expire(oracle1090 *o);   /* one firing of icaoFilterExpire's timer (icao_filter.c:112-127) */
 /* preamble test only: returns 1 if demodulate2400 would try phases at m[j] */
 int      oracle1090_preamble(const uint16_t *m);
 /* slice one phase (4..8) at m[j]: writes 14 bytes */

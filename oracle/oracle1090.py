@@ -48,6 +48,7 @@ def lib():
         L.oracle1090_syndrome_table.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]
         L.oracle1090_filter_add.argtypes = [C.c_void_p, C.c_uint32]
         L.oracle1090_filter_test.argtypes = [C.c_void_p, C.c_uint32]
+        L.oracle1090_filter_expire.argtypes = [C.c_void_p]
         L.oracle1090_preamble.argtypes = [C.c_void_p]
         L.oracle1090_slice.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         _lib = L
@@ -93,6 +94,7 @@ class Oracle1090:
 
     def filter_add(self, a): lib().oracle1090_filter_add(self.h, a)
     def filter_test(self, a): return bool(lib().oracle1090_filter_test(self.h, a))
+    def filter_expire(self): lib().oracle1090_filter_expire(self.h)
 
 
 def mag_table() -> np.ndarray:

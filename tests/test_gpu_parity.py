@@ -174,3 +174,36 @@ def test_filter_saturation(adsbcu_mod, oracle_mod):
     want2 = oracle_mod.Oracle1090(1, 1)
     want2.feed(iq, cap=1 << 18)
     assert oracle_mod.same_messages(want2.feed(iq, cap=1 << 18), got2) == []
+
+
+@pytest.mark.gpu
+def test_live_mode_filter_expiry(adsbcu_mod, oracle_mod):
+    """Live SDR input: the reference flips its two filter tables every 60 s (icaoFilterExpire, icao_filter.c:112-127,
+    dump1090.c:469-472), so an address not heard for two flips is forgotten.  adsbcu_1090_filter_expire is that flip; the
+    flips are injected between feeds at the same stream positions on both sides.  Traffic: every aircraft announces itself
+    (DF17/DF11) only in the first part of the capture and keeps sending Address/Parity replies afterwards, so the accepted
+    set depends on the flips."""
+    from libadsb_b200 import synth
+    rng = np.random.default_rng(60)
+    icaos = [int(x) for x in rng.integers(1, 1 << 24, size=40)]
+
+    def part(dfs, m=300):
+        n = int(0.12 * synth.FS_1090)
+        frames = [synth.make_frame(int(rng.choice(dfs)), icaos[int(rng.integers(0, len(icaos)))], rng) for _ in range(m)]
+        starts = (np.arange(m) + rng.random(m) * 0.2) * (n - 400) / m              # no overlaps
+        return synth.synth_capture(n, frames, starts, np.full(m, 40.0), rng.uniform(0, 2 * np.pi, m), 2.0, rng)
+    parts = [part([17, 11])] + [part([4, 5, 20, 21]) for _ in range(5)]
+    o = oracle_mod.Oracle1090(1, 1)
+    d = adsbcu_mod.Demod1090(1, 1)
+    plain = adsbcu_mod.Demod1090(1, 1)
+    n_diff = 0
+    for k, p in enumerate(parts):
+        if k in (1, 2, 4, 5):                       # the first flip comes at once in the reference (next_flip starts at 0)
+            o.filter_expire()
+            d.filter_expire()
+        want = o.feed(p, cap=1 << 16)
+        got = d.feed(p)
+        assert oracle_mod.same_messages(want, got) == []
+        n_diff += len(plain.feed(p)) != len(got)
+    assert n_diff > 0                                # the flips changed what is accepted: the test can tell
+    del rng
