@@ -450,6 +450,8 @@ int run_chunks(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, ui
                          (k.dbg[0] - t_base) * 1e-3, (k.dbg[2] - k.dbg[0]) * 1e-3, (k.dbg[3] - t_base) * 1e-3, (k.dbg[7] - t_base) * 1e-3,
                          (k.dbg[4] - k.dbg[3]) * 1e-3, (k.dbg[5] - k.dbg[4]) * 1e-3, (k.dbg[6] - k.dbg[5]) * 1e-3, (k.dbg[7] - k.dbg[6]) * 1e-3, k.n_full);
         }
+        if (k.n_sequential && std::getenv("ADSBCU_DEBUG_CHUNKS"))
+            std::fprintf(stderr, "chunk %u: %u of %u records went through the one-thread replay\n", c, k.n_sequential, k.n_full);
         if (k.overflow) { if (failed_chunk == nchunks) failed_chunk = c; return ADSBCU_OK; }
         if (failed_chunk != nchunks) return ADSBCU_OK;                 // chunks after a failed one did not touch the state
         if (sink.cands) copy_candidates(s.h_cand, k.n_full, h->stream_pos, sink);

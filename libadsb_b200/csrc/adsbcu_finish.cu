@@ -36,6 +36,7 @@ namespace {
 
 constexpr int kXThreads = 256;
 constexpr uint32_t kMapSlots = 2048, kMapMaxKeys = 1024, kMapEmpty = 0xFFFFFFFFu;
+constexpr uint32_t kMapDropped = 0xFFFFFFFEu;     // first_add of an address that was announced when the table was already full
 constexpr int kSortCap = 4096;                 // records of one segment that phase 1 can sort in shared memory
 
 // ---- the reference's ICAO filter on the device (icao_filter.c:40-109), verbatim -------------------------------
@@ -297,6 +298,7 @@ struct ResolveSmem {
     AddMap cur, next;
     uint16_t cand[kRBatch];                    // batch-relative indices of the records that can be accepted, ascending
     uint32_t warp_tot[kRThreads / 32 + 1];
+    uint8_t scratch[kMapSlots];
     uint32_t nkeys_cur, nkeys_next, changed, nruns, cut, last_acc, batch_msgs;
     uint8_t rank[24];                          // score_rank by (kind, known)
 };
@@ -393,10 +395,12 @@ __global__ void __launch_bounds__(kRThreads, 1) resolve_kernel(FinishArgs fa)
     uint32_t ia = 0;
     bool sequential = fa.force_sequential != 0;
     SkipState entry = carried;                    // skip state in front of the batch: the last accepted message so far
+    const uint32_t batch_max = min(kRBatch, max(fa.batch, 2u));
+    uint32_t batch_cap = batch_max;               // halved when a batch announces more new addresses than the map holds
 
     while (ia < n && !sequential) {
         // ---- the batch's entries into shared memory (coalesced); later batches see the table the earlier ones left ----
-        const uint32_t ib_t = min(n, ia + min(kRBatch, max(fa.batch, 2u)));
+        const uint32_t ib_t = min(n, ia + batch_cap);
         for (uint32_t i = tid; i < 2u * kIcaoSlots; i += kRThreads) sm.set[i] = kIcaoEmpty;
         __syncthreads();
         for (uint32_t i = tid; i < 2u * kIcaoSlots; i += kRThreads) {
@@ -439,6 +443,7 @@ __global__ void __launch_bounds__(kRThreads, 1) resolve_kernel(FinishArgs fa)
         // apart into runs wherever two neighbours are 288 or more samples apart; every thread walks its runs (r = tid,
         // tid + 1024, ...) on its own against the batch's first_add map.  The gaps are between CANDIDATES, not between
         // records: dense noise records (--fix-2bit) that can never win do not glue runs together.
+        bool retry = false;
         for (int round = 0;; ++round) {
             const bool use_map = sm.nkeys_cur != 0u;
             // scores (provisional, in the high half of the entry)
@@ -504,6 +509,21 @@ __global__ void __launch_bounds__(kRThreads, 1) resolve_kernel(FinishArgs fa)
                 }
             }
             __syncthreads();
+            // The table takes insertions until its last slot is used and drops them from then on (icao_filter.c:71-84): if this
+            // batch's new addresses do not all fit, the ones announced first get in and the others count as never added.
+            if (const uint32_t room = kIcaoSlots - min(kIcaoSlots, st->active_count); sm.nkeys_next > room) {
+                for (uint32_t i = tid; i < kMapSlots; i += kRThreads) {
+                    const uint32_t mine = sm.next.pos[i];
+                    if (sm.next.key[i] == kMapEmpty) continue;
+                    uint32_t rank = 0;
+                    for (uint32_t j = 0; j < kMapSlots; ++j) rank += sm.next.key[j] != kMapEmpty && sm.next.pos[j] < mine;
+                    if (rank >= room) sm.scratch[i] = 1u; else sm.scratch[i] = 0u;
+                }
+                __syncthreads();
+                for (uint32_t i = tid; i < kMapSlots; i += kRThreads)
+                    if (sm.next.key[i] != kMapEmpty && sm.scratch[i]) sm.next.pos[i] = kMapDropped;
+                __syncthreads();
+            }
             // did this round reproduce the map it was computed with?
             if (sm.nkeys_next != sm.nkeys_cur && tid == 0) sm.changed = 1u;
             for (uint32_t i = tid; i < kMapSlots; i += kRThreads)
@@ -512,8 +532,11 @@ __global__ void __launch_bounds__(kRThreads, 1) resolve_kernel(FinishArgs fa)
             const bool changed = sm.changed != 0u;
             const uint32_t nk = sm.nkeys_next;
             __syncthreads();
-            // a batch that could FILL the table takes the sequential replay (which addresses still get in depends on the order)
-            if (nk > kMapMaxKeys || (nk && st->active_count + nk > kIcaoSlots) || round >= 12) { sequential = true; break; }
+            if (nk > kMapMaxKeys) {                   // more new addresses than the map is sized for: the same records in smaller batches
+                if (ib - ia > 64u) { batch_cap = (ib - ia) / 2u; retry = true; } else sequential = true;
+                break;
+            }
+            if (round >= 12) { sequential = true; break; }
             if (!changed) break;
             for (uint32_t i = tid; i < kMapSlots; i += kRThreads) {
                 sm.cur.key[i] = sm.next.key[i]; sm.cur.pos[i] = sm.next.pos[i];
@@ -522,6 +545,8 @@ __global__ void __launch_bounds__(kRThreads, 1) resolve_kernel(FinishArgs fa)
             if (tid == 0) { sm.nkeys_cur = nk; sm.nkeys_next = 0; sm.changed = 0; }
             __syncthreads();
         }
+        if (retry) { __syncthreads(); continue; }
+        batch_cap = batch_max;
         if (sequential) break;
         if (ia == 0) ORDER_MARK(5);
 
@@ -558,7 +583,7 @@ __global__ void __launch_bounds__(kRThreads, 1) resolve_kernel(FinishArgs fa)
             uint32_t added = 0;
             for (uint32_t i = tid; i < kMapSlots; i += kRThreads) {
                 const uint32_t v = sm.cur.key[i];
-                if (v == kMapEmpty) continue;
+                if (v == kMapEmpty || sm.cur.pos[i] == kMapDropped) continue;
                 uint32_t h = icao_hash(v);
                 for (uint32_t probes = 0; probes < kIcaoSlots; ++probes) {
                     const uint32_t e = atomicCAS(&t[h], kIcaoEmpty, v);
@@ -580,6 +605,7 @@ __global__ void __launch_bounds__(kRThreads, 1) resolve_kernel(FinishArgs fa)
         ia = ib;
     }
 
+    if (tid == 0) a.ctr->n_sequential = sequential && ia < n ? n - ia : 0u;
     if (sequential && ia < n) {
         // the reference's own loop from record `ia` on, one thread, on the tables in global memory: exact whatever they hold
         __syncthreads();

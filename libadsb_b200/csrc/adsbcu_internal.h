@@ -150,7 +150,7 @@ struct ChunkCounters {
     unsigned int overflow;       // a tile list, a segment or full[] overflowed: results are incomplete
     unsigned int pad;
     unsigned int n_msgs;         // messages the ordered pass accepted in this chunk
-    unsigned int pad2;
+    unsigned int n_sequential;   // records the ordered pass took through its one-thread replay (0 in the steady state)
     unsigned long long msg_base; // ... and how many the feed had accepted before it
     unsigned long long dbg[8];   // -DADSBCU_ORDER_TIMING: globaltimer marks of the order kernel
 };
