@@ -326,11 +326,9 @@ def main():
     if rank == 0 or world == 1:
         build.build()
     torch.cuda.set_device(local_rank)
-    host_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         dist.barrier()
-        host_group = dist.new_group(backend="gloo")       # the orchestrator's exchange is host side: <= 16 KiB per rank and round
 
     def barrier():
         torch.cuda.synchronize()
@@ -338,13 +336,22 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
+    W1 = adsbcu.SHARD_WORDS + 1
+    if world > 1:                           # exchange buffers: pinned staging + device tensors (NCCL all-gather: ~50 us per round)
+        ag_send_h = torch.zeros(W1, dtype=torch.int32).pin_memory()
+        ag_recv_h = torch.zeros(world * W1, dtype=torch.int32).pin_memory()
+        ag_send_d = torch.zeros(W1, dtype=torch.int32, device="cuda")
+        ag_recv_d = torch.zeros(world * W1, dtype=torch.int32, device="cuda")
+
     def allgather(words: np.ndarray):
-        buf = torch.zeros(adsbcu.SHARD_WORDS + 1, dtype=torch.int32)
-        buf[0] = int(words.size)
-        buf[1:1 + words.size] = torch.from_numpy(words.view(np.int32))
-        parts = [torch.empty_like(buf) for _ in range(world)]
-        dist.all_gather(parts, buf, group=host_group)
-        return [p[1:1 + int(p[0])].numpy().view(np.uint32) for p in parts]
+        ag_send_h[0] = int(words.size)
+        ag_send_h[1:1 + words.size] = torch.from_numpy(words.view(np.int32))
+        ag_send_d.copy_(ag_send_h, non_blocking=True)
+        dist.all_gather_into_tensor(ag_recv_d, ag_send_d)
+        ag_recv_h.copy_(ag_recv_d, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        flat = ag_recv_h.numpy().view(np.uint32)
+        return [flat[q * W1 + 1:q * W1 + 1 + int(flat[q * W1])] for q in range(world)]
 
     iq = make(0x10900002)                   # the tile: the same on every rank (one capture)
     n = tile_n
@@ -382,11 +389,25 @@ def main():
         m, rep = d.replay_sharded(rank, world, dev_pieces, lo, halo, allgather, out)
         return m, {k: getattr(rep, "ms_" + k) for k in KEYS}, rep.launches, rep.chunks, rep.passes, rep.rounds
 
+    # sharded e2e: the range goes host -> device once (pinned pieces, inside the timed region) and both passes read it from
+    # HBM; a range that does not fit (24 h on one GPU) is uploaded chunk by chunk on every pass instead
+    range_fits = sharded and 2 * my_n <= 64 * (1 << 30)
+    range_dev = torch.empty(2 * my_n, dtype=torch.uint8, device="cuda") if range_fits else None
+
     def step_e2e():
         if not sharded:
             d.reset(True)
             m = d.feed(hview, out=out)
             return m, len(m) * adsbcu.MSG_DTYPE.itemsize, 2 * n
+        if range_fits:
+            pos = 0
+            for p, cnt in host_pieces:
+                o = (p - hview.ctypes.data)
+                range_dev[pos:pos + 2 * cnt].copy_(host[o:o + 2 * cnt], non_blocking=True)
+                pos += 2 * cnt
+            torch.cuda.current_stream().synchronize()
+            m, rep = d.replay_sharded(rank, world, [(range_dev.data_ptr(), my_n)], lo, halo, allgather, out)
+            return m, len(m) * adsbcu.MSG_DTYPE.itemsize, 2 * my_n
         m, rep = d.replay_sharded(rank, world, host_pieces, lo, halo, allgather, out, host_pieces=True)
         return m, len(m) * adsbcu.MSG_DTYPE.itemsize, 2 * my_n * rep.passes
 
