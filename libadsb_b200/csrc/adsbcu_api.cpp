@@ -100,7 +100,7 @@ struct Slot {
     unsigned char *d_zero = nullptr;  // what a chunk must find zeroed, one block: counters | rec_count[nseg] | pend_count[nseg]
     size_t zero_bytes = 0;
     ChunkCounters *h_ctr = nullptr;   // pinned
-    cudaEvent_t ev[8]{};              // front begin, front end, messages end | resolve begin, resolve end, counters on the host | order end, order begin
+    cudaEvent_t ev[9]{};              // front begin, front end, messages end | resolve begin, resolve end, counters on the host | order end, order begin | messages begin
 };
 
 struct adsbcu_handle {
@@ -108,6 +108,9 @@ struct adsbcu_handle {
     int device = 0, sm_count = 148;
     cudaStream_t stream = nullptr;        // front + message kernels
     cudaStream_t copy_stream = nullptr;   // host->device uploads of the feed, chunk by chunk
+    cudaStream_t msg_stream = nullptr;    // message kernels when they run beside the next chunk's front kernel (msg_overlap)
+    bool msg_overlap = true;
+    SmPartition part;                     // dense kernels / post kernels on disjoint SM sets (green contexts), if available
     cudaStream_t post_stream = nullptr;   // resolve kernels, in chunk order (high priority, like the next two)
     cudaStream_t order_stream = nullptr;  // order kernels
     cudaStream_t level_stream = nullptr;  // level kernels + the chunk counters to the host
@@ -191,7 +194,7 @@ void free_slots(adsbcu_handle *h)
         cudaFree(s.d_run_start); cudaFree(s.d_zero); cudaFree(s.d_accepted); cudaFree(s.d_view);
         if (s.h_cand) cudaFreeHost(s.h_cand);
         if (s.h_ctr) cudaFreeHost(s.h_ctr);
-        cudaEvent_t ev[8];
+        cudaEvent_t ev[9];
         std::memcpy(ev, s.ev, sizeof(ev));
         s = Slot{};
         std::memcpy(s.ev, ev, sizeof(ev));
@@ -245,6 +248,7 @@ void free_all(adsbcu_handle *h)
     if (h->order_stream) cudaStreamSynchronize(h->order_stream);
     if (h->level_stream) cudaStreamSynchronize(h->level_stream);
     if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
+    if (h->msg_stream) cudaStreamSynchronize(h->msg_stream);
     cudaFree(h->d_sc16); cudaFree(h->d_import);
     cudaFree(h->d_ac_ov); cudaFree(h->d_ac_sums); cudaFree(h->d_ac_rec);
     if (h->h_ac_rec) cudaFreeHost(h->h_ac_rec);
@@ -265,6 +269,7 @@ void free_all(adsbcu_handle *h)
     for (auto &e : h->ev_up) if (e) cudaEventDestroy(e);
     if (h->stream) cudaStreamDestroy(h->stream);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+    if (h->msg_stream) cudaStreamDestroy(h->msg_stream);
     if (h->post_stream) cudaStreamDestroy(h->post_stream);
     if (h->order_stream) cudaStreamDestroy(h->order_stream);
     if (h->level_stream) cudaStreamDestroy(h->level_stream);
@@ -403,8 +408,11 @@ int run_chunks(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, ui
         CK(cudaEventRecord(s.ev[0], h->stream));
         CK(launch_front(a, h->stream));
         CK(cudaEventRecord(s.ev[1], h->stream));
-        CK(launch_messages(a, h->msg_grid, h->stream));
-        CK(cudaEventRecord(s.ev[2], h->stream));
+        cudaStream_t ms = h->msg_overlap ? h->msg_stream : h->stream;
+        if (h->msg_overlap) CK(cudaStreamWaitEvent(ms, s.ev[1], 0));
+        CK(cudaEventRecord(s.ev[8], ms));
+        CK(launch_messages(a, h->msg_grid, ms));
+        CK(cudaEventRecord(s.ev[2], ms));
         // the finish kernel only touches this chunk's slot, the stream state and (reading) the address set, where a
         // superset merely keeps more records for the exact ordered pass: it runs beside the next chunk's scan
         FinishArgs fa{};
@@ -458,7 +466,7 @@ int run_chunks(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, ui
         st.preambles += k.preambles; st.phase_records += k.n_cand; st.resolved_records += k.n_full; st.messages += k.n_msgs;
         float ms = 0.f;
         cudaEventElapsedTime(&ms, s.ev[0], s.ev[1]); st.ms_front += ms;
-        cudaEventElapsedTime(&ms, s.ev[1], s.ev[2]); st.ms_messages += ms;
+        cudaEventElapsedTime(&ms, s.ev[8], s.ev[2]); st.ms_messages += ms;
         cudaEventElapsedTime(&ms, s.ev[7], s.ev[6]); st.ms_order += ms;
         cudaEventElapsedTime(&ms, s.ev[3], s.ev[4]); st.ms_resolve += ms;
         return ADSBCU_OK;
@@ -478,7 +486,7 @@ int run_chunks(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, ui
         ++retired;
     }
     if (rc != ADSBCU_OK) {
-        cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->order_stream); cudaStreamSynchronize(h->post_stream); cudaStreamSynchronize(h->level_stream); cudaStreamSynchronize(h->copy_stream);
+        cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->msg_stream); cudaStreamSynchronize(h->order_stream); cudaStreamSynchronize(h->post_stream); cudaStreamSynchronize(h->level_stream); cudaStreamSynchronize(h->copy_stream);
         for (Slot &s : h->slot) if (s.d_zero) cudaMemset(s.d_zero, 0, s.zero_bytes);
         return rc;
     }
@@ -513,6 +521,7 @@ int run_feed(adsbcu_handle *h, const uint8_t *d_iq, const uint8_t *iq_host, uint
         // a list of chunk `failed` overflowed: nothing from that chunk on has touched the stream state.  Double the
         // lists and run again from there (the samples are on the device already).
         CK(cudaStreamSynchronize(h->stream));
+        CK(cudaStreamSynchronize(h->msg_stream));
         CK(cudaStreamSynchronize(h->order_stream));
         CK(cudaStreamSynchronize(h->post_stream));
         CK(cudaStreamSynchronize(h->level_stream));
@@ -661,14 +670,34 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
     CKC(cudaGetDeviceProperties(&prop, h->device));
     if (prop.major < 10) { h->error = "device is not sm_100 class"; return fail(ADSBCU_ERR_NO_DEVICE); }
     h->sm_count = prop.multiProcessorCount;
-    CKC(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     CKC(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    if (const char *v = std::getenv("ADSBCU_MSG_OVERLAP")) h->msg_overlap = std::atoi(v) != 0;
     {
-        int lo = 0, hi = 0;
-        CKC(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-        CKC(cudaStreamCreateWithPriority(&h->post_stream, cudaStreamNonBlocking, hi));
-        CKC(cudaStreamCreateWithPriority(&h->order_stream, cudaStreamNonBlocking, hi));
-        CKC(cudaStreamCreateWithPriority(&h->level_stream, cudaStreamNonBlocking, hi));
+        // a few SMs of their own for the order / resolve / level kernels (green contexts), else priorities on one partition
+        int post_sms = 0;                                   // off by default: measured slower (profiles/r02_partition_sweep.txt)
+        if (const char *v = std::getenv("ADSBCU_SM_PARTITION")) post_sms = std::atoi(v);
+        CKC(cudaFree(nullptr));                             // the primary context exists before the driver API is used
+        if (post_sms > 0 && h->sm_count >= 64 && make_partition(h->device, post_sms, h->part)) {
+            h->stream = h->part.main; h->msg_stream = h->part.msg;
+            h->post_stream = h->part.resolve;
+            if (std::getenv("ADSBCU_PARTITION_RESOLVE_ONLY")) {      // order / level kernels stay with the dense kernels (many CTAs)
+                int lo = 0, hi = 0;
+                CKC(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+                CKC(cudaStreamCreateWithPriority(&h->order_stream, cudaStreamNonBlocking, hi));
+                CKC(cudaStreamCreateWithPriority(&h->level_stream, cudaStreamNonBlocking, hi));
+                cudaStreamDestroy(h->part.order); cudaStreamDestroy(h->part.level);
+            } else {
+                h->order_stream = h->part.order; h->level_stream = h->part.level;
+            }
+        } else {
+            int lo = 0, hi = 0;
+            CKC(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+            CKC(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+            CKC(cudaStreamCreateWithFlags(&h->msg_stream, cudaStreamNonBlocking));
+            CKC(cudaStreamCreateWithPriority(&h->post_stream, cudaStreamNonBlocking, hi));
+            CKC(cudaStreamCreateWithPriority(&h->order_stream, cudaStreamNonBlocking, hi));
+            CKC(cudaStreamCreateWithPriority(&h->level_stream, cudaStreamNonBlocking, hi));
+        }
     }
     for (auto &e : h->ev_h2d) CKC(cudaEventCreate(&e));
     for (auto &e : h->ev_up) CKC(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -700,9 +729,9 @@ int adsbcu_create(const adsbcu_config *cfg, adsbcu_handle **out)
     if (const char *v = std::getenv("ADSBCU_RESOLVE_SEQ")) h->force_sequential = std::atoi(v) != 0;
     if (const char *v = std::getenv("ADSBCU_RESOLVE_BATCH")) h->resolve_batch = uint32_t(std::max(2, std::atoi(v)));
     const size_t nmax = c.max_feed_samples;
-    h->nseg = uint32_t(h->sm_count) - spare;
+    h->nseg = h->part.ok ? uint32_t(h->part.sm_main) : uint32_t(h->sm_count) - spare;
     h->unit_positions = h->nseg * uint32_t(kFWarps) * uint32_t(kWTile);
-    h->msg_grid = uint32_t(h->sm_count) * 6;
+    h->msg_grid = (h->part.ok ? uint32_t(h->part.sm_main) : uint32_t(h->sm_count)) * 6;
     if (const char *v = std::getenv("ADSBCU_MSG_GRID")) h->msg_grid = uint32_t(std::max(1, std::atoi(v)));
     h->max_tps = uint32_t(std::max<size_t>(1, std::min<size_t>(tps, (nmax + h->unit_positions - 1) / h->unit_positions)));
     h->max_tps = std::max(h->max_tps, std::min(std::max(h->res_tps, h->host_tps), uint32_t((nmax + h->unit_positions - 1) / h->unit_positions)));

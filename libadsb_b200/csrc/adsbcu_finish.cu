@@ -287,7 +287,7 @@ __global__ void __launch_bounds__(kXThreads) order_kernel(FinishArgs fa)
 // iterated to its fixed point (see the file header), its messages are written, its new addresses enter the filter
 // table, then the next batch starts from that state: exactly the chunk algorithm at a finer grain.
 constexpr int kRThreads = 1024;
-constexpr uint32_t kRBatch = 16384;
+constexpr uint32_t kRBatch = 15 * 1024;
 
 struct ResolveSmem {
     uint32_t set[2 * kIcaoSlots];              // the contents of the reference's two filter tables as of the batch's start, as ONE
@@ -299,6 +299,7 @@ struct ResolveSmem {
     uint16_t cand[kRBatch];                    // batch-relative indices of the records that can be accepted, ascending
     uint32_t warp_tot[kRThreads / 32 + 1];
     uint8_t scratch[kMapSlots];
+    uint32_t cnt[kRBatch / kRThreads * 32];    // strided_compact: flags per (iteration, warp)
     uint32_t nkeys_cur, nkeys_next, changed, nruns, cut, last_acc, batch_msgs;
     uint8_t rank[24];                          // score_rank by (kind, known)
 };
@@ -348,6 +349,48 @@ __device__ __forceinline__ uint32_t block_flag_scan(bool f, uint32_t *warp_tot, 
     __syncthreads();
     return before + __popc(bal & ((1u << lane) - 1u));
 }
+
+// Compaction of up to 32 x 1024 flags held one bit per thread and iteration (bit `it` of `mask` belongs to element
+// it * 1024 + tid): exclusive offsets in element order with three barriers in all, instead of one block scan per 1024
+// elements.  emit(it, offset) is called for every set flag; returns the number of set flags.
+template <class Emit>
+__device__ __forceinline__ uint32_t strided_compact(uint32_t mask, uint32_t nit, uint32_t *cnt /* [32 * nit] */, uint32_t *warp_tot, Emit &&emit)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (uint32_t it = 0; it < nit; ++it) {
+        const uint32_t b = __ballot_sync(0xFFFFFFFFu, (mask >> it) & 1u);
+        if (lane == 0) cnt[it * 32u + warp] = __popc(b);
+    }
+    __syncthreads();
+    // exclusive scan of the 32 * nit (<= 1024) counts, one per thread
+    const uint32_t nval = 32u * nit;
+    const uint32_t c = uint32_t(threadIdx.x) < nval ? cnt[threadIdx.x] : 0u;
+    uint32_t incl = c;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
+    if (lane == 31) warp_tot[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        const uint32_t w = warp_tot[lane];
+        uint32_t wi = w;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, wi, d); if (lane >= d) wi += t; }
+        warp_tot[lane] = wi - w;
+        if (lane == 31) warp_tot[32] = wi;
+    }
+    __syncthreads();
+    if (uint32_t(threadIdx.x) < nval) cnt[threadIdx.x] = warp_tot[warp] + incl - c;
+    const uint32_t total = warp_tot[32];
+    __syncthreads();
+    for (uint32_t it = 0; it < nit; ++it) {
+        const uint32_t b = __ballot_sync(0xFFFFFFFFu, (mask >> it) & 1u);
+        if ((mask >> it) & 1u) emit(it, cnt[it * 32u + warp] + __popc(b & ((1u << lane) - 1u)));
+    }
+    __syncthreads();
+    return total;
+}
+
+static_assert(sizeof(ResolveSmem) <= 227 * 1024, "resolve kernel shared memory exceeds the sm_100 per-CTA limit");
 
 __global__ void __launch_bounds__(kRThreads, 1) resolve_kernel(FinishArgs fa)
 {
@@ -457,35 +500,32 @@ __global__ void __launch_bounds__(kRThreads, 1) resolve_kernel(FinishArgs fa)
             __syncthreads();
             // winners: the first record of its position with the highest score (phases ascending; strict > keeps the lowest
             // phase on ties), if that score reaches the threshold.  Compacted in index order into sm.cand.
-            uint32_t ncand = 0;
-            for (uint32_t t0 = ia; t0 < ib; t0 += kRThreads) {
-                const uint32_t i = t0 + tid;
-                bool win = false;
-                if (i < ib) {
-                    const uint2 e = sm.ent[i - ia];
-                    const uint32_t sc = e.y >> 16;
-                    win = sc >= uint32_t(kAcceptThreshold);
-                    for (uint32_t j = i; win && j > ia && sm.ent[j - 1 - ia].x == e.x; --j) win = (sm.ent[j - 1 - ia].y >> 16) < sc;
-                    for (uint32_t j = i + 1; win && j < ib && sm.ent[j - ia].x == e.x; ++j) win = (sm.ent[j - ia].y >> 16) <= sc;
-                }
-                uint32_t cnt = 0;
-                const uint32_t off = block_flag_scan(win, sm.warp_tot, cnt);
-                if (win) sm.cand[ncand + off] = uint16_t(i - ia);
-                ncand += cnt;
+            const uint32_t nit = (ib - ia + kRThreads - 1u) / kRThreads;
+            uint32_t wmask = 0;
+            for (uint32_t it = 0; it < nit; ++it) {
+                const uint32_t i = ia + it * kRThreads + tid;
+                if (i >= ib) break;
+                const uint2 e = sm.ent[i - ia];
+                const uint32_t sc = e.y >> 16;
+                bool win = sc >= uint32_t(kAcceptThreshold);
+                for (uint32_t j = i; win && j > ia && sm.ent[j - 1 - ia].x == e.x; --j) win = (sm.ent[j - 1 - ia].y >> 16) < sc;
+                for (uint32_t j = i + 1; win && j < ib && sm.ent[j - ia].x == e.x; ++j) win = (sm.ent[j - ia].y >> 16) <= sc;
+                if (win) wmask |= 1u << it;
             }
+            const uint32_t ncand = strided_compact(wmask, nit, sm.cnt, sm.warp_tot,
+                                                   [&](uint32_t it, uint32_t off) { sm.cand[off] = uint16_t(it * kRThreads + tid); });
             __syncthreads();
             // every record that is not a winner loses its provisional score; runs of the candidate list
             for (uint32_t i = ia + tid; i < ib; i += kRThreads) sm.ent[i - ia].y &= 0xFFFFu;
             __syncthreads();
-            uint32_t R = 0;
-            for (uint32_t t0 = 0; t0 < ncand; t0 += kRThreads) {
-                const uint32_t k = t0 + tid;
-                const bool f = k < ncand && (k == 0 || sm.ent[sm.cand[k]].x - sm.ent[sm.cand[k - 1]].x >= 288u);
-                uint32_t cnt = 0;
-                const uint32_t off = block_flag_scan(f, sm.warp_tot, cnt);
-                if (f) run_start[R + off] = k;
-                R += cnt;
+            const uint32_t nitc = (ncand + kRThreads - 1u) / kRThreads;
+            uint32_t rmask = 0;
+            for (uint32_t it = 0; it < nitc; ++it) {
+                const uint32_t k = it * kRThreads + tid;
+                if (k < ncand && (k == 0 || sm.ent[sm.cand[k]].x - sm.ent[sm.cand[k - 1]].x >= 288u)) rmask |= 1u << it;
             }
+            const uint32_t R = strided_compact(rmask, nitc, sm.cnt, sm.warp_tot,
+                                               [&](uint32_t it, uint32_t off) { run_start[off] = it * kRThreads + tid; });
             if (tid == 0) run_start[R] = ncand;
             __syncthreads();
             for (uint32_t r = tid; r < R; r += kRThreads) {
@@ -553,15 +593,14 @@ __global__ void __launch_bounds__(kRThreads, 1) resolve_kernel(FinishArgs fa)
         // ---- emission, parallel over the batch's records: every accepted record becomes one message, in stream order.
         // First the offsets (a block scan per 1024 records; the offset replaces the position in the entry), then all
         // the messages without a barrier in between, so that the record reads of the whole batch are in flight together.
-        uint32_t batch_total = 0;
-        for (uint32_t t0 = ia; t0 < ib; t0 += kRThreads) {
-            const uint32_t i = t0 + tid;
-            const uint32_t sc = i < ib ? sm.ent[i - ia].y >> 16 : 0u;
-            uint32_t cnt = 0;
-            const uint32_t off = block_flag_scan(sc != 0u, sm.warp_tot, cnt);
-            if (sc) sm.ent[i - ia].x = batch_total + off;
-            batch_total += cnt;
+        const uint32_t nit_e = (ib - ia + kRThreads - 1u) / kRThreads;
+        uint32_t emask = 0;
+        for (uint32_t it = 0; it < nit_e; ++it) {
+            const uint32_t i = ia + it * kRThreads + tid;
+            if (i < ib && (sm.ent[i - ia].y >> 16)) emask |= 1u << it;
         }
+        const uint32_t batch_total = strided_compact(emask, nit_e, sm.cnt, sm.warp_tot,
+                                                     [&](uint32_t it, uint32_t off) { sm.ent[it * kRThreads + tid].x = off; });
         uint32_t my_last = 0;
 #pragma unroll 4
         for (uint32_t i = ia + tid; i < ib; i += kRThreads) {

@@ -185,7 +185,10 @@ void build_tables(DevTables &t, int nfix_crc, int fix_df);
 
 // ---- round-2 pipeline: front kernel -> message kernel -> finish kernel --------------------------------------
 // front kernel geometry: kFWarps autonomous warps per CTA, a lane owns kFRun consecutive samples of a warp-tile
-constexpr int kFRun = 24, kFWarps = 32;
+#ifndef ADSBCU_FWARPS                 // warps per front-kernel CTA (measurement knob; fewer leave registers for message-kernel CTAs on the same SM)
+#define ADSBCU_FWARPS 32
+#endif
+constexpr int kFRun = 24, kFWarps = ADSBCU_FWARPS;
 constexpr int kWTile = kFRun * 32;            // 768 samples staged per warp-tile == start positions per warp-tile
 constexpr int kFLead = 2;                     // staged index of a tile's first start position (16 B alignment of the I/Q vectors)
 constexpr int kFHalo = 24;                    // magnitudes staged past the tile: the preamble test looks 18 samples ahead
@@ -285,6 +288,15 @@ constexpr int kAcLead = 2;    // magnitudes buffer: m[0] at base + kAcLead puts 
 cudaError_t launch_modeac(const DevTables *tab, int sm_count, cudaStream_t s, const uint8_t *d_iq_block, uint32_t n,
                           const uint8_t *d_iq_overlap, uint32_t n_overlap, uint16_t *d_mag_base, unsigned long long *d_sums,
                           AcRec *d_rec, uint32_t cap, uint32_t *d_count);
+
+// SM partition (adsbcu_partition.cpp): streams bound to disjoint SM sets, dense kernels / post kernels
+struct SmPartition {
+    bool ok = false;
+    int sm_main = 0, sm_post = 0;
+    cudaStream_t main = nullptr, msg = nullptr, order = nullptr, resolve = nullptr, level = nullptr;
+};
+bool make_partition(int device, int post_sms, SmPartition &p);
+void free_partition(SmPartition &p);
 
 // Path B (adsbcu_pathb.cu): libadsb's own 2.0 MS/s demodulator
 struct PathB;
