@@ -1,5 +1,5 @@
 // Shared between the host side (adsbcu_api.cpp, adsbcu_tables.cpp) and the
-// kernels (adsbcu_kernels.cu).  Domain vocabulary follows the reference:
+// kernels (adsbcu_front.cu, adsbcu_msgs.cu, adsbcu_finish.cu, adsbcu_kernels.cu).  Domain vocabulary follows the reference:
 // samples, magnitudes, preambles, phases, syndromes, the ICAO filter.
 #pragma once
 
@@ -26,25 +26,6 @@ constexpr int      kLookahead     = 290;      // samples read past a start posit
 constexpr uint32_t kNtFlag        = 1u << 25; // icao_filter.h:24
 constexpr uint32_t kNonIcao       = 1u << 24; // dump1090.h:262
 constexpr uint32_t kUnchecked     = 0xFFFFFFFFu;
-
-// ---- scan kernel tiling --------------------------------------------------------------
-// One CTA per SM; a CTA is kGroups independent groups of kGroupThreads threads that share the
-// 32 KiB central magnitude LUT in shared memory.  Every thread of a group owns kRun consecutive
-// samples of a tile (kRun = 24 samples = 120 fifths of a sample = 10 symbols on each of the 12
-// sampling grids of the 2.4 MS/s slicer); a tile scans the kTile start positions whose 290-sample
-// lookahead fits in it.
-constexpr int kRun         = 24;              // samples per thread and tile
-#ifndef ADSBCU_GROUPS               // measurement knobs: -DADSBCU_GROUPS=8 -DADSBCU_GROUP_THREADS=128 (profiles/sweep_groups.sh)
-#define ADSBCU_GROUPS 4
-#define ADSBCU_GROUP_THREADS 256
-#endif
-constexpr int kGroups      = ADSBCU_GROUPS;
-constexpr int kGroupThreads = ADSBCU_GROUP_THREADS;
-constexpr int kTileSamples = kRun * kGroupThreads;   // 6144 magnitudes staged per tile
-constexpr int kTileLead    = 2;               // smem index of the tile's first start position (16 B alignment of x0)
-constexpr int kTile        = kTileSamples - 296;   // start positions per tile (lead + lookahead + pad to a multiple of 8)
-constexpr int kTilePad     = 32;
-static_assert(kTile % 8 == 0, "tile starts must keep 16-byte alignment of the I/Q vectors");
 
 // State-independent classification of one sliced phase.  The host combines it
 // with the filter state to get the reference's score_rank (mode_s.h:32-80).
@@ -178,7 +159,6 @@ struct ScanArgs {
     // bitmap are appended here (unordered); another shard's addresses may revive them later
     PhaseRec       *deferred;    uint32_t deferred_cap;
     uint32_t       *n_deferred;
-    uint32_t        skew, skew_ns;   // how the groups of a CTA are put out of step (scan_kernel)
 };
 
 void build_tables(DevTables &t, int nfix_crc, int fix_df);
@@ -268,12 +248,8 @@ cudaError_t launch_state_import(StreamState *st, uint32_t *bitmap, uint32_t has_
 
 // launchers (adsbcu_kernels.cu)
 cudaError_t init_kernels();                                        // per device, once (opt-in shared memory size)
-cudaError_t launch_scan(const ScanArgs &a, cudaStream_t s);       // grid = a.nseg
-cudaError_t launch_filter(const ScanArgs &a, cudaStream_t s);     // drop A/P records whose address can never be known
-cudaError_t launch_evaluate(const ScanArgs &a, cudaStream_t s);   // survivors -> FullRec, stream order
 // deferred records whose address is in the bitmap now -> flat into a.seg (seg_count set per segment)
 cudaError_t launch_revive(const ScanArgs &a, cudaStream_t s);
-cudaError_t launch_signal(const ChunkCounters *d_ctr, ChunkCounters *h_ctr_dev, uint32_t seq, cudaStream_t s);
 cudaError_t launch_or_words(uint32_t *dst, const uint32_t *src, uint32_t nwords, cudaStream_t s);
 cudaError_t launch_build_lut(DevTables *tab, cudaStream_t s);     // fills tab->mag_lut with the register-computed magnitudes
 cudaError_t launch_carry(const uint8_t *iq, uint32_t nsamples, uint16_t *carry_mag, const DevTables *tab, cudaStream_t s);

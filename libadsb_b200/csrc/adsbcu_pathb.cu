@@ -230,7 +230,7 @@ int pathb_feed(PathB *&b, const DevTables *d_tab, int sm_count, cudaStream_t s, 
         CKB(cudaHostAlloc(&b->h_ctr, sizeof(CountersB), cudaHostAllocDefault));
     }
     const size_t n = nbytes / 2;
-    if (n < 240) return ADSBCU_OK;                     // nothing can be scanned (the reference's loop bound would wrap)
+    if (n <= 240) return ADSBCU_OK;                    // nothing can be scanned: the reference runs j < size - 240 (zero iterations at 240, and its bound would wrap below)
     if (n > 0xFFFFFFF0ull) { err = "buffer too large"; return ADSBCU_ERR_ARG; }
     if (b->iq_cap < nbytes) {
         cudaFree(b->d_iq); b->d_iq = nullptr; b->iq_cap = 0;

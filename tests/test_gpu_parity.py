@@ -207,3 +207,20 @@ def test_live_mode_filter_expiry(adsbcu_mod, oracle_mod):
         n_diff += len(plain.feed(p)) != len(got)
     assert n_diff > 0                                # the flips changed what is accepted: the test can tell
     del rng
+
+
+@pytest.mark.gpu
+def test_overflow_recovery_full_scale_noise(adsbcu_mod, oracle_mod):
+    """2^24 samples of full-scale uniform noise with --fix-2bit: several times more preambles and records per position than the
+    lists of a chunk are sized for.  The engine has to notice the overflow, double its lists, run the chunk again and still
+    return exactly the reference's set; the stream state must be usable afterwards."""
+    rng = np.random.default_rng(2 ** 24)
+    n = 1 << 24
+    iq = rng.integers(0, 256, size=2 * n, dtype=np.uint8)
+    d = adsbcu_mod.Demod1090(2, 1, max_feed_samples=n)
+    o = oracle_mod.Oracle1090(2, 1)
+    want = o.feed(iq, cap=1 << 20)
+    got = d.feed(iq, cap=1 << 20)
+    assert oracle_mod.same_messages(want, got) == []
+    tail = iq[:2 * 400_000]
+    assert oracle_mod.same_messages(o.feed(tail, cap=1 << 18), d.feed(tail, cap=1 << 18)) == []
