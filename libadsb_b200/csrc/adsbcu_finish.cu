@@ -184,8 +184,12 @@ __device__ __forceinline__ void resolve_range(const uint4 *view, uint32_t i0, ui
 }
 
 struct SortSmem {
-    uint32_t key[kSortCap];
-    uint32_t nrec, offset;
+    uint32_t key[kSortCap];                    // (position << 3 | phase - 4) of record i
+    uint32_t tkey[kSortCap];                   // its filter key (argument of icaoFilterTest)
+    uint16_t by_rank[kSortCap];                // record index at sorted position r; 0xFFFF once the record is dropped
+    uint8_t  kind[kSortCap];
+    uint32_t warp_tot[kXThreads / 32];
+    uint32_t nrec, offset, nkeep;
 };
 
 #ifdef ADSBCU_ORDER_TIMING            // debug: nanosecond marks of the order kernel in ChunkCounters::dbg (profiles/order_probe.py)
@@ -243,13 +247,65 @@ __global__ void __launch_bounds__(kXThreads) order_kernel(FinishArgs fa)
         const uint32_t n = min(ss.nrec, a.rec_cap);
         // rank sort by (position, phase): keys are unique
         if (n > uint32_t(kSortCap)) { if (tid == 0) a.ctr->overflow = 1u; }
-        for (uint32_t i = tid; i < n && i < uint32_t(kSortCap); i += kXThreads) ss.key[i] = ((rec[i].pos - a.pos_begin) << 3) | (rec[i].phase - 4u);
-        // Segments in index order are the chunk in stream order: publish this segment's count, sum the counts of the
-        // segments before it (CTAs start in index order, so the ones waited for are running or done), and write the
-        // sorted records straight to their place in the chunk's ordered array.
+        const uint32_t ns = min(n, uint32_t(kSortCap));
+        for (uint32_t i = tid; i < ns; i += kXThreads) {
+            ss.key[i] = ((rec[i].pos - a.pos_begin) << 3) | (rec[i].phase - 4u);
+            ss.tkey[i] = rec[i].test_key;
+            ss.kind[i] = rec[i].kind;
+        }
+        __syncthreads();
+        for (uint32_t i = tid; i < ns; i += kXThreads) {
+            const uint32_t me = ss.key[i];
+            uint32_t rank = 0;
+            for (uint32_t j = 0; j < ns; ++j) rank += ss.key[j] < me;
+            ss.by_rank[rank] = uint16_t(i);
+        }
+        __syncthreads();
+        // A record can never be the accepted phase of its position when another phase of the SAME position with the SAME filter
+        // key beats it whether or not that key is known (higher score_rank, or equal rank and lower phase: demod_2400.c:336 keeps
+        // the first best).  Most records are such losers -- a clean message decodes on three or four of the five phases -- and
+        // dropping them here cuts the work of the one-CTA ordered pass about three times.  (Neighbours in sorted order.)
+        bool drop[(kSortCap + kXThreads - 1) / kXThreads];
+        uint32_t mykeep = 0;
+        constexpr uint32_t kPer = kSortCap / kXThreads;           // a thread owns kPer consecutive sorted positions
+        for (uint32_t q = 0; q < kPer; ++q) {
+            const uint32_t r = tid * kPer + q;
+            drop[q] = true;
+            if (r >= ns) continue;
+            const uint32_t i = ss.by_rank[r], me = ss.key[i], tk = ss.tkey[i], kd = ss.kind[i];
+            const int m0 = rank_of(kd, false), m1 = rank_of(kd, true);
+            bool dead = false;
+            for (int dlt = -4; dlt <= 4 && !dead; ++dlt) {
+                const int64_t r2 = int64_t(r) + dlt;
+                if (dlt == 0 || r2 < 0 || r2 >= int64_t(ns)) continue;
+                const uint32_t j = ss.by_rank[r2];
+                if ((ss.key[j] >> 3) != (me >> 3) || ss.tkey[j] != tk) continue;
+                const int o0 = rank_of(ss.kind[j], false), o1 = rank_of(ss.kind[j], true);
+                const bool first = ss.key[j] < me;                    // lower phase
+                dead = (o0 > m0 || (o0 == m0 && first)) && (o1 > m1 || (o1 == m1 && first));
+            }
+            drop[q] = dead;
+            mykeep += !dead;
+        }
+        // exclusive scan of the per-thread keep counts, then the survivors move up in sorted order
+        uint32_t incl = mykeep;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
+        if (lane == 31) ss.warp_tot[warp] = incl;
+        __syncthreads();
+        uint32_t base = incl - mykeep;
+        for (int w2 = 0; w2 < warp; ++w2) base += ss.warp_tot[w2];
+        uint32_t nkeep_all = 0;
+        for (int w2 = 0; w2 < kXThreads / 32; ++w2) nkeep_all += ss.warp_tot[w2];
+        uint16_t mine[kPer];
+        for (uint32_t q = 0; q < kPer; ++q) mine[q] = (tid * kPer + q < ns) ? ss.by_rank[tid * kPer + q] : uint16_t(0xFFFF);
+        __syncthreads();
+        for (uint32_t q = 0, k = base; q < kPer; ++q) if (!drop[q]) ss.by_rank[k++] = mine[q];
+        __syncthreads();
+        const uint32_t nk = n > uint32_t(kSortCap) ? n : nkeep_all;      // (an oversized segment already raised the overflow flag)
         if (tid == 0) {
-            a.rec_count[seg] = n;
-            *reinterpret_cast<volatile unsigned long long *>(&fa.seg_flag[seg]) = (unsigned long long)fa.epoch << 32 | n;
+            a.rec_count[seg] = nk;
+            *reinterpret_cast<volatile unsigned long long *>(&fa.seg_flag[seg]) = (unsigned long long)fa.epoch << 32 | nk;
             ss.offset = 0;
         }
         __syncthreads();
@@ -264,17 +320,15 @@ __global__ void __launch_bounds__(kXThreads) order_kernel(FinishArgs fa)
         __syncthreads();
         if (seg == gridDim.x - 1) ORDER_MARK(2);
         const uint32_t offset = ss.offset;
-        if (offset + n > a.full_cap) { if (tid == 0) a.ctr->overflow = 1u; }
+        if (offset + nk > a.full_cap) { if (tid == 0) a.ctr->overflow = 1u; }
         else if (n <= uint32_t(kSortCap)) {
-            for (uint32_t i = tid; i < n; i += kXThreads) {
-                const uint32_t me = ss.key[i];
-                uint32_t rank = 0;
-                for (uint32_t j = 0; j < n; ++j) rank += ss.key[j] < me;
+            for (uint32_t r = tid; r < nk; r += kXThreads) {
+                const uint32_t i = ss.by_rank[r];
                 const uint4 *src = reinterpret_cast<const uint4 *>(rec + i);
-                uint4 *dst = reinterpret_cast<uint4 *>(a.ordered + offset + rank);
+                uint4 *dst = reinterpret_cast<uint4 *>(a.ordered + offset + r);
                 const uint4 q0 = src[0], q1 = src[1], q2 = src[2], q3 = src[3];
                 dst[0] = q0; dst[1] = q1; dst[2] = q2; dst[3] = q3;
-                fa.view[offset + rank] = view_of(rec[i]);
+                fa.view[offset + r] = view_of(rec[i]);
             }
         }
     }
