@@ -251,13 +251,17 @@ int pathb_feed(PathB *&b, const DevTables *d_tab, int sm_count, cudaStream_t s, 
     const uint32_t grid = std::min<uint32_t>(ntiles, uint32_t(sm_count) * 4u);
     ADSBCU_LAUNCH(scanb_kernel, grid, kBThreads, 0, s, b->d_iq, uint32_t(n), b->d_lut, d_tab->bit_synd, b->d_rec, b->rec_cap, b->d_ctr);
     CKB(cudaGetLastError());
+    // the counters and the first records come back together: a live-size buffer (262144 bytes, RTLSDR.hpp:55) rarely holds more,
+    // so one HandleData call costs one synchronisation
+    constexpr uint32_t kFirstB = 512;
     CKB(cudaMemcpyAsync(b->h_ctr, b->d_ctr, sizeof(CountersB), cudaMemcpyDeviceToHost, s));
+    CKB(cudaMemcpyAsync(b->h_rec, b->d_rec, size_t(std::min(kFirstB, b->rec_cap)) * sizeof(RecB), cudaMemcpyDeviceToHost, s));
     CKB(cudaStreamSynchronize(s));
     const CountersB c = *b->h_ctr;
     if (c.overflow || c.n_rec > b->rec_cap) { err = "internal candidate list overflow"; return ADSBCU_ERR_OVERFLOW; }
     b->preambles = c.preambles;
-    if (c.n_rec) {
-        CKB(cudaMemcpyAsync(b->h_rec, b->d_rec, size_t(c.n_rec) * sizeof(RecB), cudaMemcpyDeviceToHost, s));
+    if (c.n_rec > kFirstB) {
+        CKB(cudaMemcpyAsync(b->h_rec + kFirstB, b->d_rec + kFirstB, size_t(c.n_rec - kFirstB) * sizeof(RecB), cudaMemcpyDeviceToHost, s));
         CKB(cudaStreamSynchronize(s));
     }
     RecB *recs = b->h_rec;
