@@ -196,7 +196,7 @@ def main_978(args):
 
     def step_e2e():
         d.reset_uat()
-        return sum(len(d.handle_data_uat(hview[k:k + BUF])) for k in range(0, iq.size, BUF))
+        return sum(len(d.handle_data_uat(hview[k:k + BUF], out=out)) for k in range(0, iq.size, BUF))
 
     sampler = ClockSampler(0)
     sampler.start()

@@ -206,10 +206,12 @@ class Demod1090:
         self._check(load().adsbcu_1090_magnitude(self.h, iq.ctypes.data, n, out.ctypes.data))
         return out
 
-    def handle_data_b(self, iq: np.ndarray, cap: int = 1 << 16) -> np.ndarray:
-        """Path B: one ADSB1090Handler::HandleData(span) call (libadsb's own 2.0 MS/s demodulator)."""
+    def handle_data_b(self, iq: np.ndarray, cap: int = 1 << 16, out: np.ndarray | None = None) -> np.ndarray:
+        """Path B: one ADSB1090Handler::HandleData(span) call (libadsb's own 2.0 MS/s demodulator).  `out`: an array to reuse."""
         iq = np.ascontiguousarray(iq, dtype=np.uint8)
-        out = np.zeros(cap, dtype=MSG_B_DTYPE)
+        if out is None:
+            out = np.zeros(cap, dtype=MSG_B_DTYPE)
+        cap = len(out)
         got = C.c_size_t(0)
         self._check(load().adsbcu_1090b_feed(self.h, iq.ctypes.data, iq.size, out.ctypes.data, cap, C.byref(got)))
         return out[:got.value]
@@ -238,10 +240,12 @@ class Demod1090:
     def reset_b(self):
         self._check(load().adsbcu_1090b_reset(self.h))
 
-    def handle_data_uat(self, iq: np.ndarray, cap: int = 1 << 14) -> np.ndarray:
-        """Path C: one UAT978Handler::HandleData(span) call (978 MHz UAT, 2.083334 MS/s)."""
+    def handle_data_uat(self, iq: np.ndarray, cap: int = 1 << 14, out: np.ndarray | None = None) -> np.ndarray:
+        """Path C: one UAT978Handler::HandleData(span) call (978 MHz UAT, 2.083334 MS/s).  `out`: a frame array to reuse."""
         iq = np.ascontiguousarray(iq, dtype=np.uint8)
-        out = np.zeros(cap, dtype=UAT_DTYPE)
+        if out is None:
+            out = np.zeros(cap, dtype=UAT_DTYPE)
+        cap = len(out)
         got = C.c_size_t(0)
         self._check(load().adsbcu_978_feed(self.h, iq.ctypes.data, iq.size, out.ctypes.data, cap, C.byref(got)))
         return out[:got.value]

@@ -115,17 +115,22 @@ __device__ __forceinline__ int mod255(int x) { while (x >= 255) { x -= 255; x = 
 // In-place decode of a shortened code word of n = 255 - pad symbols with `nroots` parity symbols.
 // Returns the number of error locations found, or -1 (block untouched) if the locator has fewer roots than
 // its degree.  A location inside the virtual padding is counted but not applied, as libfec does.
-__device__ int rs_correct(const Gf &gf, uint8_t *blk, int nroots, int pad)
+// syndrome i of the block (libfec's Horner form): the O(n * nroots) part of the decoder, one syndrome per lane
+__device__ __forceinline__ uint8_t rs_syndrome(const Gf &gf, const uint8_t *blk, int n, int i)
+{
+    constexpr int kFcr = 120;
+    uint32_t s = blk[0];
+    for (int j = 1; j < n; ++j) s = s == 0 ? blk[j] : blk[j] ^ gf.exp[mod255(gf.log[s] + kFcr + i)];
+    return uint8_t(s);
+}
+
+// The rest of the decoder on the syndromes `syn_raw` (nroots values): Berlekamp-Massey, Chien, Forney; corrects blk in place.
+__device__ int rs_solve(const Gf &gf, uint8_t *blk, const uint8_t *syn_raw, int nroots, int pad)
 {
     constexpr int kA0 = 255, kFcr = 120, kMax = 20;
     uint8_t syn[kMax], lam[kMax + 1], bb[kMax + 1], tt[kMax + 1], omg[kMax + 1], reg[kMax + 1], root[kMax], loc[kMax];
-    const int n = 255 - pad;
-    for (int i = 0; i < nroots; ++i) syn[i] = blk[0];
-    for (int j = 1; j < n; ++j)
-        for (int i = 0; i < nroots; ++i)
-            syn[i] = syn[i] == 0 ? blk[j] : blk[j] ^ gf.exp[mod255(gf.log[syn[i]] + kFcr + i)];
     int any = 0;
-    for (int i = 0; i < nroots; ++i) { any |= syn[i]; syn[i] = gf.log[syn[i]]; }
+    for (int i = 0; i < nroots; ++i) { any |= syn_raw[i]; syn[i] = gf.log[syn_raw[i]]; }
     if (!any) return 0;
     // Berlekamp-Massey: error locator lam (polynomial form), bb in log form
     for (int i = 1; i <= nroots; ++i) { lam[i] = 0; bb[i] = kA0; }
@@ -194,52 +199,85 @@ __device__ __forceinline__ uint8_t slice_byte(const uint16_t *p, int center)
     return uint8_t(b);
 }
 
-__global__ void __launch_bounds__(64) uat_decode_kernel(const uint16_t *phi, uint64_t abs_of_index0, const CandC *cand, RecC *rec,
-                                                        uint32_t rec_cap, CountersC *ctr, const Gf *gf_g)
+// One WARP per candidate (the per-call latency of the staging loop is the latency of its slowest candidate): the lanes
+// slice the frame bytes and form the Reed-Solomon syndromes in parallel, the short algebraic part runs on one lane per
+// RS block (six lanes for an uplink frame), the sign bits of the record come from ballots.
+constexpr int kDecWarps = 4;
+struct DecSmem {
+    Gf gf;
+    uint8_t buf[kDecWarps][kUpBlocks * kUpBlockBytes + 8];     // ADS-B: 48 frame bytes; uplink: six de-interleaved blocks of 92
+    uint8_t syn[kDecWarps][kUpBlocks][20];
+    int     res[kDecWarps][kUpBlocks];
+};
+
+__global__ void __launch_bounds__(kDecWarps * 32) uat_decode_kernel(const uint16_t *phi, uint64_t abs_of_index0, const CandC *cand, RecC *rec,
+                                                                    uint32_t rec_cap, CountersC *ctr, const Gf *gf_g)
 {
-    __shared__ Gf gf;
-    for (int i = threadIdx.x; i < 256; i += blockDim.x) { gf.exp[i] = gf_g->exp[i]; gf.log[i] = gf_g->log[i]; }
+    __shared__ DecSmem sm;
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) { sm.gf.exp[i] = gf_g->exp[i]; sm.gf.log[i] = gf_g->log[i]; }
     __syncthreads();
-    const uint32_t ncand = min(ctr->n_cand, 0xFFFFFFFFu);
-    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= ncand) return;
-    const CandC cd = cand[c];
-    const uint16_t *p = phi + cd.x + 2 * kSyncBits;
-    uint8_t out[kUpData + 20];
-    int rs = 0, type = 0;
-    if (!cd.uplink) {
-        for (int b = 0; b < kLongBytes; ++b) out[b] = slice_byte(p + 16 * b, cd.center);
-        int nfix = rs_correct(gf, out, 14, 207);                          // long: RS(48,34)
-        if (nfix >= 0 && nfix <= 7 && (out[0] >> 3) != 0) { type = 2; rs = nfix; }
-        else {
-            nfix = rs_correct(gf, out, 12, 225);                          // basic: RS(30,18)
-            if (nfix >= 0 && nfix <= 6 && (out[0] >> 3) == 0) { type = 1; rs = nfix; }
-            else return;
+    const Gf &gf = sm.gf;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint8_t *buf = sm.buf[warp];
+    const uint32_t ncand = ctr->n_cand;
+    for (uint32_t c = blockIdx.x * kDecWarps + warp; c < ncand; c += gridDim.x * kDecWarps) {
+        const CandC cd = cand[c];
+        const uint16_t *p = phi + cd.x + 2 * kSyncBits;
+        int rs = 0, type = 0;
+        bool ok = false;
+        __syncwarp();
+        if (!cd.uplink) {
+            for (int b = lane; b < kLongBytes; b += 32) buf[b] = slice_byte(p + 16 * b, cd.center);
+            __syncwarp();
+            if (lane < 14) sm.syn[warp][0][lane] = rs_syndrome(gf, buf, kLongBytes, lane);          // long: RS(48,34)
+            __syncwarp();
+            int nfix = 0;
+            if (lane == 0) nfix = rs_solve(gf, buf, sm.syn[warp][0], 14, 207);
+            nfix = __shfl_sync(0xFFFFFFFFu, nfix, 0);
+            __syncwarp();
+            if (nfix >= 0 && nfix <= 7 && (buf[0] >> 3) != 0) { type = 2; rs = nfix; ok = true; }
+            else {                                                                                  // basic: RS(30,18) on the same bytes
+                if (lane < 12) sm.syn[warp][0][lane] = rs_syndrome(gf, buf, kShortBytes, lane);
+                __syncwarp();
+                if (lane == 0) nfix = rs_solve(gf, buf, sm.syn[warp][0], 12, 225);
+                nfix = __shfl_sync(0xFFFFFFFFu, nfix, 0);
+                __syncwarp();
+                if (nfix >= 0 && nfix <= 6 && (buf[0] >> 3) == 0) { type = 1; rs = nfix; ok = true; }
+            }
+        } else {
+            // de-interleave: byte i of block b is frame byte 6 i + b
+            for (int q = lane; q < kUpBytes; q += 32) buf[(q % kUpBlocks) * kUpBlockBytes + q / kUpBlocks] = slice_byte(p + 16 * q, cd.center);
+            __syncwarp();
+            for (int t = lane; t < kUpBlocks * 20; t += 32) sm.syn[warp][t / 20][t % 20] = rs_syndrome(gf, buf + (t / 20) * kUpBlockBytes, kUpBlockBytes, t % 20);
+            __syncwarp();
+            if (lane < kUpBlocks) sm.res[warp][lane] = rs_solve(gf, buf + lane * kUpBlockBytes, sm.syn[warp][lane], 20, 163);   // RS(92,72)
+            __syncwarp();
+            ok = true;
+            for (int blk = 0; blk < kUpBlocks; ++blk) {
+                const int nfix = sm.res[warp][blk];
+                if (nfix < 0 || nfix > 10) { ok = false; break; }
+                rs += nfix;
+            }
         }
-    } else {
-        for (int blk = 0; blk < kUpBlocks; ++blk) {                       // de-interleave: byte i of block b is frame byte 6i+b
-            uint8_t *bd = &out[blk * kUpBlockData];
-            for (int i = 0; i < kUpBlockBytes; ++i) bd[i] = slice_byte(p + 16 * (i * kUpBlocks + blk), cd.center);
-            const int nfix = rs_correct(gf, bd, 20, 163);                 // RS(92,72); the next block overwrites the parity
-            if (nfix < 0 || nfix > 10) return;
-            rs += nfix;
+        if (!ok) continue;                                    // warp-uniform
+        uint32_t slot = 0;
+        if (lane == 0) slot = atomicAdd(&ctr->n_rec, 1u);
+        slot = __shfl_sync(0xFFFFFFFFu, slot, 0);
+        if (slot >= rec_cap) { if (lane == 0) ctr->overflow = 1u; continue; }
+        RecC &r = rec[slot];
+        for (int w = 0; w < 3; ++w) {
+            const int64_t x = int64_t(cd.x) - kSigmaLead + 32 * w + lane;
+            const uint32_t bits = __ballot_sync(0xFFFFFFFFu, x >= 0 && phi_diff(phi[x >= 0 ? x : 0], phi[(x >= 0 ? x : 0) + 1]) > 0);
+            if (lane == 0) r.sigma[w] = bits;
+        }
+        if (lane == 0) { r.s = abs_of_index0 + cd.x; r.rs_errors = int16_t(rs); r.uplink = uint8_t(cd.uplink); r.type = uint8_t(type); }
+        if (!cd.uplink) {
+            const int len = type == 2 ? kLongData : kShortData;
+            for (int i = lane; i < len; i += 32) r.data[i] = buf[i];
+        } else {
+            for (int i = lane; i < kUpData; i += 32) r.data[i] = buf[(i / kUpBlockData) * kUpBlockBytes + i % kUpBlockData];
         }
     }
-    const uint32_t slot = atomicAdd(&ctr->n_rec, 1u);
-    if (slot >= rec_cap) { ctr->overflow = 1u; return; }
-    RecC &r = rec[slot];
-    r.s = abs_of_index0 + cd.x;
-    for (int w = 0; w < 3; ++w) {
-        uint32_t bits = 0;
-        for (int i = 0; i < 32; ++i) {
-            const int64_t x = int64_t(cd.x) - kSigmaLead + 32 * w + i;
-            if (x >= 0) bits |= uint32_t(phi_diff(phi[x], phi[x + 1]) > 0) << i;
-        }
-        r.sigma[w] = bits;
-    }
-    r.rs_errors = int16_t(rs); r.uplink = uint8_t(cd.uplink); r.type = uint8_t(type);
-    const int len = cd.uplink ? kUpData : (type == 2 ? kLongData : kShortData);
-    for (int i = 0; i < len; ++i) r.data[i] = out[i];
 }
 
 // UAT978.cpp:57 as compiled: memmove(buffer, buffer + done, len - done) -- the count is in BYTES although it is the number
@@ -419,7 +457,7 @@ int pathc_feed(PathC *&c, int sm_count, cudaStream_t st, const uint8_t *iq, size
         const uint32_t last = uint32_t(2 * (lenbits - kSyncBits + 1) + 3);
         CKC_(cudaMemsetAsync(c->d_ctr, 0, sizeof(CountersC), st));
         ADSBCU_LAUNCH(uat_sync_kernel, (last + 255) / 256, 256, 0, st, buf, 0u, last, c->d_cand, c->cand_cap, c->d_ctr);
-        ADSBCU_LAUNCH(uat_decode_kernel, c->cand_cap / 64, 64, 0, st, buf, c->offset, c->d_cand, c->d_rec, c->rec_cap, c->d_ctr, c->d_gf);
+        ADSBCU_LAUNCH(uat_decode_kernel, 128, kDecWarps * 32, 0, st, buf, c->offset, c->d_cand, c->d_rec, c->rec_cap, c->d_ctr, c->d_gf);
         CKC_(cudaGetLastError());
         constexpr uint32_t kFirst = 32;                       // records fetched together with the counters
         CKC_(cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(CountersC), cudaMemcpyDeviceToHost, st));

@@ -32,9 +32,11 @@ def timed(fn, reps=3):
 iq = synth.config_b(seconds=seconds, seed=0x1090B002)[0]
 d = adsbcu.Demod1090()
 for name, step in (("262144-byte buffers", BUF), ("8 MiB buffers", 8 << 20)):
+    out_b = np.zeros(1 << 17, dtype=adsbcu.MSG_B_DTYPE)      # reused: a fresh 4 MB array per call would be most of a live-size call
+
     def run_b():
         d.reset_b()
-        return sum(len(d.handle_data_b(iq[k:k + step], cap=1 << 17)) for k in range(0, iq.size, step))
+        return sum(len(d.handle_data_b(iq[k:k + step], out=out_b)) for k in range(0, iq.size, step))
     dt, n = timed(run_b)
     line = {"path": "B (ADSB1090Handler, 2.0 MS/s)", "feed": name, "msamples_s": iq.size / 2 / dt / 1e6, "messages": n,
             "realtime_factor": iq.size / 2 / dt / 2.0e6}
@@ -43,9 +45,11 @@ for name, step in (("262144-byte buffers", BUF), ("8 MiB buffers", 8 << 20)):
 # ---- Path C
 iq = synth978.config5(seconds=seconds)[0]
 for name, step in (("262144-byte buffers", BUF), ("whole capture", iq.size)):
+    out_c = np.zeros(1 << 14, dtype=adsbcu.UAT_DTYPE)
+
     def run_c():
         d.reset_uat()
-        return sum(len(d.handle_data_uat(iq[k:k + step])) for k in range(0, iq.size, step))
+        return sum(len(d.handle_data_uat(iq[k:k + step], out=out_c)) for k in range(0, iq.size, step))
     dt, n = timed(run_c)
     print(json.dumps({"path": "C (UAT978Handler, 2.083334 MS/s)", "feed": name, "msamples_s": iq.size / 2 / dt / 1e6,
                       "frames": n, "realtime_factor": iq.size / 2 / dt / 2083334.0}))
