@@ -124,13 +124,24 @@ __device__ __forceinline__ uint8_t rs_syndrome(const Gf &gf, const uint8_t *blk,
     return uint8_t(s);
 }
 
-// The rest of the decoder on the syndromes `syn_raw` (nroots values): Berlekamp-Massey, Chien, Forney; corrects blk in place.
-__device__ int rs_solve(const Gf &gf, uint8_t *blk, const uint8_t *syn_raw, int nroots, int pad)
+// The rest of the decoder, in three steps around a small per-block work area in shared memory.  Berlekamp-Massey and Forney
+// are short (O(nroots^2)) and run on one lane; the Chien search -- 255 evaluations of the locator, the long serial part of
+// libfec's decode_rs -- is spread over the warp, each lane evaluating the polynomial directly at its own field elements.
+struct RsWork {
+    uint8_t syn[20];          // syndromes, log form
+    uint8_t lam[21];          // error locator, log form
+    uint8_t root[20], loc[20];
+    int deg, count, nroots;
+};
+
+// syndromes -> locator.  Returns 0 when all syndromes are zero (nothing to correct), else 1.
+__device__ int rs_bm(const Gf &gf, RsWork &w, const uint8_t *syn_raw, int nroots)
 {
-    constexpr int kA0 = 255, kFcr = 120, kMax = 20;
-    uint8_t syn[kMax], lam[kMax + 1], bb[kMax + 1], tt[kMax + 1], omg[kMax + 1], reg[kMax + 1], root[kMax], loc[kMax];
+    constexpr int kA0 = 255, kMax = 20;
+    uint8_t syn[kMax], lam[kMax + 1], bb[kMax + 1], tt[kMax + 1];
     int any = 0;
-    for (int i = 0; i < nroots; ++i) { any |= syn_raw[i]; syn[i] = gf.log[syn_raw[i]]; }
+    for (int i = 0; i < nroots; ++i) { any |= syn_raw[i]; syn[i] = gf.log[syn_raw[i]]; w.syn[i] = syn[i]; }
+    w.nroots = nroots; w.deg = 0; w.count = 0;
     if (!any) return 0;
     // Berlekamp-Massey: error locator lam (polynomial form), bb in log form
     for (int i = 1; i <= nroots; ++i) { lam[i] = 0; bb[i] = kA0; }
@@ -158,37 +169,77 @@ __device__ int rs_solve(const Gf &gf, uint8_t *blk, const uint8_t *syn_raw, int 
         }
     }
     int deg = 0;
-    for (int i = 0; i <= nroots; ++i) { lam[i] = gf.log[lam[i]]; if (lam[i] != kA0) deg = i; }
-    // Chien search
-    for (int i = 1; i <= nroots; ++i) reg[i] = lam[i];
+    for (int i = 0; i <= nroots; ++i) { w.lam[i] = gf.log[lam[i]]; if (w.lam[i] != kA0) deg = i; }
+    w.deg = deg;
+    return 1;
+}
+
+// Chien search by the whole warp: libfec walks i = 1..255 and stops at the deg-th root; here lane l evaluates
+// lambda(alpha^i) for i = 32 r + l + 1 and the roots are collected in ascending i, the first deg of them.
+__device__ void rs_chien_warp(const Gf &gf, RsWork &w, int lane)
+{
+    constexpr int kA0 = 255;
+    const int deg = w.deg;
     int count = 0;
-    for (int i = 1, k = 0; i <= 255; ++i, k = mod255(k + 1)) {
-        int q = 1;
-        for (int j = deg; j > 0; --j)
-            if (reg[j] != kA0) { reg[j] = uint8_t(mod255(reg[j] + j)); q ^= gf.exp[reg[j]]; }
-        if (q != 0) continue;
-        root[count] = uint8_t(i); loc[count] = uint8_t(k);
-        if (++count == deg) break;
+    for (int r = 0; r < 8 && count < deg; ++r) {
+        const int i = 32 * r + lane + 1;
+        bool is_root = false;
+        if (i <= 255) {
+            int q = 1;
+            for (int j = deg; j > 0; --j)
+                if (w.lam[j] != kA0) q ^= gf.exp[(int(w.lam[j]) + i * j) % 255];
+            is_root = q == 0;
+        }
+        const uint32_t b = __ballot_sync(0xFFFFFFFFu, is_root);
+        const int at = count + __popc(b & ((1u << lane) - 1u));
+        if (is_root && at < deg) { w.root[at] = uint8_t(i); w.loc[at] = uint8_t(i - 1); }
+        count += __popc(b);
     }
+    __syncwarp();
+    if (lane == 0) w.count = min(count, deg);
+    __syncwarp();
+}
+
+// error evaluator and Forney; returns the number of corrected locations, or -1 when the locator has fewer roots than its degree
+__device__ int rs_forney(const Gf &gf, const RsWork &w, uint8_t *blk, int pad)
+{
+    constexpr int kA0 = 255, kFcr = 120, kMax = 20;
+    const int deg = w.deg, count = w.count, nroots = w.nroots;
     if (deg != count) return -1;
-    // error evaluator and Forney
+    uint8_t omg[kMax + 1];
     const int dego = deg - 1;
     for (int i = 0; i <= dego; ++i) {
         int t = 0;
         for (int j = i; j >= 0; --j)
-            if (syn[i - j] != kA0 && lam[j] != kA0) t ^= gf.exp[mod255(syn[i - j] + lam[j])];
+            if (w.syn[i - j] != kA0 && w.lam[j] != kA0) t ^= gf.exp[mod255(w.syn[i - j] + w.lam[j])];
         omg[i] = gf.log[t];
     }
     for (int j = count - 1; j >= 0; --j) {
         int num1 = 0, den = 0;
         for (int i = dego; i >= 0; --i)
-            if (omg[i] != kA0) num1 ^= gf.exp[mod255(omg[i] + i * root[j])];
-        const int num2 = gf.exp[mod255(root[j] * (kFcr - 1) + 255)];
+            if (omg[i] != kA0) num1 ^= gf.exp[mod255(omg[i] + i * w.root[j])];
+        const int num2 = gf.exp[mod255(w.root[j] * (kFcr - 1) + 255)];
         for (int i = min(deg, nroots - 1) & ~1; i >= 0; i -= 2)
-            if (lam[i + 1] != kA0) den ^= gf.exp[mod255(lam[i + 1] + i * root[j])];
-        if (num1 != 0 && loc[j] >= pad) blk[loc[j] - pad] ^= gf.exp[mod255(gf.log[num1] + gf.log[num2] + 255 - gf.log[den])];
+            if (w.lam[i + 1] != kA0) den ^= gf.exp[mod255(w.lam[i + 1] + i * w.root[j])];
+        if (num1 != 0 && w.loc[j] >= pad) blk[w.loc[j] - pad] ^= gf.exp[mod255(gf.log[num1] + gf.log[num2] + 255 - gf.log[den])];
     }
     return count;
+}
+
+// one block, whole warp: -> corrections (or -1)
+__device__ int rs_decode_warp(const Gf &gf, RsWork &w, uint8_t *blk, const uint8_t *syn_raw, int nroots, int pad, int lane)
+{
+    int e = 0;
+    if (lane == 0) e = rs_bm(gf, w, syn_raw, nroots);
+    e = __shfl_sync(0xFFFFFFFFu, e, 0);
+    __syncwarp();
+    if (!e) return 0;
+    rs_chien_warp(gf, w, lane);
+    int n = 0;
+    if (lane == 0) n = rs_forney(gf, w, blk, pad);
+    n = __shfl_sync(0xFFFFFFFFu, n, 0);
+    __syncwarp();
+    return n;
 }
 
 __device__ __forceinline__ uint8_t slice_byte(const uint16_t *p, int center)
@@ -208,6 +259,7 @@ struct DecSmem {
     uint8_t buf[kDecWarps][kUpBlocks * kUpBlockBytes + 8];     // ADS-B: 48 frame bytes; uplink: six de-interleaved blocks of 92
     uint8_t syn[kDecWarps][kUpBlocks][20];
     int     res[kDecWarps][kUpBlocks];
+    RsWork  work[kDecWarps][kUpBlocks];
 };
 
 __global__ void __launch_bounds__(kDecWarps * 32) uat_decode_kernel(const uint16_t *phi, uint64_t abs_of_index0, const CandC *cand, RecC *rec,
@@ -231,17 +283,12 @@ __global__ void __launch_bounds__(kDecWarps * 32) uat_decode_kernel(const uint16
             __syncwarp();
             if (lane < 14) sm.syn[warp][0][lane] = rs_syndrome(gf, buf, kLongBytes, lane);          // long: RS(48,34)
             __syncwarp();
-            int nfix = 0;
-            if (lane == 0) nfix = rs_solve(gf, buf, sm.syn[warp][0], 14, 207);
-            nfix = __shfl_sync(0xFFFFFFFFu, nfix, 0);
-            __syncwarp();
+            int nfix = rs_decode_warp(gf, sm.work[warp][0], buf, sm.syn[warp][0], 14, 207, lane);
             if (nfix >= 0 && nfix <= 7 && (buf[0] >> 3) != 0) { type = 2; rs = nfix; ok = true; }
             else {                                                                                  // basic: RS(30,18) on the same bytes
                 if (lane < 12) sm.syn[warp][0][lane] = rs_syndrome(gf, buf, kShortBytes, lane);
                 __syncwarp();
-                if (lane == 0) nfix = rs_solve(gf, buf, sm.syn[warp][0], 12, 225);
-                nfix = __shfl_sync(0xFFFFFFFFu, nfix, 0);
-                __syncwarp();
+                nfix = rs_decode_warp(gf, sm.work[warp][0], buf, sm.syn[warp][0], 12, 225, lane);
                 if (nfix >= 0 && nfix <= 6 && (buf[0] >> 3) == 0) { type = 1; rs = nfix; ok = true; }
             }
         } else {
@@ -250,7 +297,12 @@ __global__ void __launch_bounds__(kDecWarps * 32) uat_decode_kernel(const uint16
             __syncwarp();
             for (int t = lane; t < kUpBlocks * 20; t += 32) sm.syn[warp][t / 20][t % 20] = rs_syndrome(gf, buf + (t / 20) * kUpBlockBytes, kUpBlockBytes, t % 20);
             __syncwarp();
-            if (lane < kUpBlocks) sm.res[warp][lane] = rs_solve(gf, buf + lane * kUpBlockBytes, sm.syn[warp][lane], 20, 163);   // RS(92,72)
+            int e = 0;                                                                              // RS(92,72): locators on six lanes,
+            if (lane < kUpBlocks) e = rs_bm(gf, sm.work[warp][lane], sm.syn[warp][lane], 20);       // the Chien searches warp-wide, Forney on six lanes
+            __syncwarp();
+            for (int blk = 0; blk < kUpBlocks; ++blk)
+                if (__shfl_sync(0xFFFFFFFFu, e, blk)) rs_chien_warp(gf, sm.work[warp][blk], lane);
+            if (lane < kUpBlocks) sm.res[warp][lane] = e ? rs_forney(gf, sm.work[warp][lane], buf + lane * kUpBlockBytes, 163) : 0;
             __syncwarp();
             ok = true;
             for (int blk = 0; blk < kUpBlocks; ++blk) {
