@@ -273,6 +273,17 @@ int adsbcu_1090_modeac_block_static(adsbcu_handle *h, const uint8_t *iq_dev, siz
                                     const uint8_t *overlap_iq_dev, size_t n_overlap, uint64_t block_timestamp,
                                     adsbcu_msg *out_dev, size_t cap, uint32_t *result_dev /* [2] */, void *cuda_stream);
 
+/* ---- Wire formats of the decoded set ---------------------------------------------
+ * Host-side formatting of adsbcu_msg records exactly as dump1090's network outputs write them; no handle, no GPU.
+ *   adsbcu_1090_encode_beast   writeBeastMessage (net_io.c:440-487) per message.  verbatim != 0: the bytes as sliced,
+ *                              every message (the --net-verbatim Beast port, net_io.c:405-412); verbatim == 0: corrected
+ *                              bytes, messages with two repaired bits left out (cooked port, net_io.c:423-438).
+ *   adsbcu_1090_encode_avr     the raw port's "@<12 hex timestamp><frame hex>;\n" line (net_io.c:510-545 with --mlat).
+ * Both return the number of bytes the output needs; at most cap bytes are written (call with out = NULL to size it).
+ * tests/golden/beast_ref.npz holds the bytes the reference itself sent on its Beast port for the golden capture. */
+size_t adsbcu_1090_encode_beast(const adsbcu_msg *msgs, size_t n, int verbatim, uint8_t *out, size_t cap);
+size_t adsbcu_1090_encode_avr(const adsbcu_msg *msgs, size_t n, uint8_t *out, size_t cap);
+
 /* ---- Path A, next layer: CPR position decode ----------------------------------
  * The three decoders of the flightaware tree's cpr.c, many records per call, results as the same IEEE
  * doubles the reference computes (bit for bit; dump1090's own cprtests.c vectors are in tests/golden):

@@ -50,7 +50,7 @@ EXPORTS = ["adsbcu_abi_version", "adsbcu_last_error", "adsbcu_create", "adsbcu_d
            "adsbcu_1090_filter_test", "adsbcu_1090_filter_expire", "adsbcu_get_stats", "adsbcu_1090b_feed", "adsbcu_1090b_reset",
            "adsbcu_978_feed", "adsbcu_978_feed_device", "adsbcu_978_get_stats", "adsbcu_978_reset", "adsbcu_978_phase", "adsbcu_1090_seek", "adsbcu_1090_scan_candidates",
            "adsbcu_1090_known_export", "adsbcu_1090_known_import", "adsbcu_1090_revive", "adsbcu_1090_resolve", "adsbcu_1090_modeac_block", "adsbcu_1090_feed_sc16",
-           "adsbcu_1090_modeac_block_static", "adsbcu_1090_state_export", "adsbcu_1090_state_import", "adsbcu_1090_replay_sharded",
+           "adsbcu_1090_modeac_block_static", "adsbcu_1090_encode_beast", "adsbcu_1090_encode_avr", "adsbcu_1090_state_export", "adsbcu_1090_state_import", "adsbcu_1090_replay_sharded",
            "adsbcu_1090b_decode_fields", "adsbcu_1090b_cpr_decode", "adsbcu_1090_cpr_decode"]
 
 
@@ -134,6 +134,10 @@ def load():
         L.adsbcu_1090_modeac_block.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_uint64, C.c_void_p,
                                                C.c_size_t, C.POINTER(C.c_size_t)]
         L.adsbcu_1090_feed_sc16.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.adsbcu_1090_encode_beast.restype = C.c_size_t
+        L.adsbcu_1090_encode_beast.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t]
+        L.adsbcu_1090_encode_avr.restype = C.c_size_t
+        L.adsbcu_1090_encode_avr.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
         L.adsbcu_1090_state_export.argtypes = [C.c_void_p, C.POINTER(StreamStateC), C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.adsbcu_1090_state_import.argtypes = [C.c_void_p, C.POINTER(StreamStateC), C.c_void_p, C.c_size_t]
         L.adsbcu_1090_replay_sharded.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(Piece), C.c_size_t, C.c_uint64, C.c_void_p, C.c_size_t,
@@ -146,6 +150,23 @@ def load():
 
 class AdsbcuError(RuntimeError):
     pass
+
+
+def encode_beast(msgs: np.ndarray, verbatim: bool = True) -> bytes:
+    """adsbcu_1090_encode_beast on a MSG_DTYPE array."""
+    msgs = np.ascontiguousarray(msgs, dtype=MSG_DTYPE)
+    need = load().adsbcu_1090_encode_beast(msgs.ctypes.data, len(msgs), int(verbatim), None, 0)
+    out = np.zeros(max(need, 1), np.uint8)
+    load().adsbcu_1090_encode_beast(msgs.ctypes.data, len(msgs), int(verbatim), out.ctypes.data, need)
+    return out[:need].tobytes()
+
+
+def encode_avr(msgs: np.ndarray) -> bytes:
+    msgs = np.ascontiguousarray(msgs, dtype=MSG_DTYPE)
+    need = load().adsbcu_1090_encode_avr(msgs.ctypes.data, len(msgs), None, 0)
+    out = np.zeros(max(need, 1), np.uint8)
+    load().adsbcu_1090_encode_avr(msgs.ctypes.data, len(msgs), out.ctypes.data, need)
+    return out[:need].tobytes()
 
 
 class Demod1090:

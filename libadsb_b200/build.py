@@ -7,7 +7,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libadsbcu.so")
-SOURCES = ["adsbcu_front.cu", "adsbcu_msgs.cu", "adsbcu_finish.cu", "adsbcu_kernels.cu", "adsbcu_pathb.cu", "adsbcu_uat.cu", "adsbcu_modeac.cu", "adsbcu_fields.cu", "adsbcu_api.cpp", "adsbcu_partition.cpp", "adsbcu_shard.cpp", "adsbcu_tables.cpp"]
+SOURCES = ["adsbcu_front.cu", "adsbcu_msgs.cu", "adsbcu_finish.cu", "adsbcu_kernels.cu", "adsbcu_pathb.cu", "adsbcu_uat.cu", "adsbcu_modeac.cu", "adsbcu_fields.cu", "adsbcu_api.cpp", "adsbcu_partition.cpp", "adsbcu_shard.cpp", "adsbcu_wire.cpp", "adsbcu_tables.cpp"]
 HOST_SRC = [os.path.join("..", "host", "adsbcu_replay.cpp"), os.path.join("..", "host", "adsbcu_handlers.hpp")]
 HEADERS = ["adsbcu_internal.h", "adsbcu_device.cuh", os.path.join("..", "..", "include", "adsbcu.h")]
 

@@ -18,25 +18,6 @@
 
 using namespace adsbcu_host;
 
-static void beast_put(std::vector<uint8_t> &o, uint8_t ch)
-{
-    o.push_back(ch);
-    if (ch == 0x1A) o.push_back(ch);
-}
-
-// writeBeastMessage (net_io.c:440-487)
-static void beast_message(std::vector<uint8_t> &o, uint64_t ts, double signal, const uint8_t *msg, int len)
-{
-    o.push_back(0x1A);
-    o.push_back(len == 7 ? '2' : '3');
-    for (int s = 40; s >= 0; s -= 8) beast_put(o, uint8_t(ts >> s));
-    int sig = int(std::round(std::sqrt(signal) * 255));
-    if (signal > 0 && sig < 1) sig = 1;
-    if (sig > 255) sig = 255;
-    beast_put(o, uint8_t(sig));
-    for (int j = 0; j < len; ++j) beast_put(o, msg[j]);
-}
-
 int main(int argc, char **argv)
 {
     std::string path = "a", file, beast_file;
@@ -67,7 +48,11 @@ int main(int argc, char **argv)
                 std::printf("@%012llX", (unsigned long long) m.timestamp);
                 for (int j = 0; j < m.msgbits / 8; ++j) std::printf("%02x", m.msg[j]);
                 std::printf(";\n");
-                if (!beast_file.empty()) beast_message(beast, m.timestamp, m.signal_level, m.verbatim, m.msgbits / 8);
+                if (!beast_file.empty()) {          // the --net-verbatim Beast stream (writeBeastMessage, net_io.c:440-487), behind the C ABI
+                    uint8_t tmp[64];
+                    const size_t nb = adsbcu_1090_encode_beast(&m, 1, 1, tmp, sizeof(tmp));
+                    beast.insert(beast.end(), tmp, tmp + nb);
+                }
                 ++count;
             }, nfix, fix_df, 0, uint32_t(std::max<size_t>(block / 2, 1u << 20)), mode_ac);
         } else if (path == "b") {
