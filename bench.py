@@ -291,8 +291,9 @@ def main():
     config = {"workload": workload, "samples_per_gpu": total // world, "capture_samples": total,
               "l2_policy": f"input tile ({2 * tile_n / 1e6:.0f} MB) larger than L2",
               "sharding": ("none" if world == 1 else
-                           "adsbcu_1090_replay_sharded: equal contiguous sample ranges of one capture; start states (skip state + ICAO filter) by "
-                           "fixed-point exchange of <= 16 KiB per rank and round (rank 0 makes one pass, the others two); no data-path collective")}
+                           "adsbcu_1090_replay_sharded_tail: world + 1 equal contiguous sample ranges of one capture, range r on rank r, the last one on "
+                           "rank 0 too (one pass over each of its two, the other ranks two passes over theirs); start states (skip state + ICAO "
+                           "filter) by fixed-point exchange of <= 16 KiB per rank and round; no data-path collective")}
     scaling = "strong" if strong else "weak"
 
     # ------------------------------------------------------------------ reference arm
@@ -358,17 +359,25 @@ def main():
     host = torch.from_numpy(iq[:2 * n]).pin_memory()
     dev = host.cuda(non_blocking=False)
     hview = host.numpy()
-    # this rank's range of the capture
+    # this rank's range(s) of the capture: world + 1 equal ranges, range r on rank r and the last one (the "tail") on rank 0
+    # as well -- the first range never runs twice and nobody waits for the last one's end state (adsbcu_1090_replay_sharded_tail)
+    def halo_of(pos):
+        o = pos % n
+        return None if pos == 0 else (hview[2 * (o - 326):2 * o] if o >= 326 else np.concatenate([hview[2 * (n - (326 - o)):], hview[:2 * o]]))
+    has_tail = world > 1
     if world == 1:
         lo, hi = 0, total
+        tlo = thi = total
     else:
-        cut = lambda k: total if k >= world else (total * k // world) // 8 * 8      # noqa: E731
+        cut = lambda k: total if k >= world + 1 else (total * k // (world + 1)) // 8 * 8      # noqa: E731
         lo, hi = cut(rank), cut(rank + 1)
-    my_n = hi - lo
-    off = lo % n
-    halo = None if lo == 0 else (hview[2 * (off - 326):2 * off] if off >= 326 else np.concatenate([hview[2 * (n - (326 - off)):], hview[:2 * off]]))
+        tlo, thi = (cut(world), total) if rank == 0 else (total, total)
+    my_n = (hi - lo) + (thi - tlo)
+    halo = halo_of(lo)
     dev_pieces = pieces_of(dev.data_ptr(), n, lo, hi)
     host_pieces = pieces_of(hview.ctypes.data, n, lo, hi)
+    dev_tail = (pieces_of(dev.data_ptr(), n, tlo, thi), tlo, halo_of(tlo)) if thi > tlo else None
+    host_tail = (pieces_of(hview.ctypes.data, n, tlo, thi), tlo, halo_of(tlo)) if thi > tlo else None
     d = adsbcu.Demod1090(nfix_crc=args.nfix, fix_df=1, max_feed_samples=max(n, 1 << 20), device=local_rank)
     # out[] in pinned memory: the engine's level kernel writes the accepted messages there itself (no host copy)
     probe = adsbcu.Demod1090(nfix_crc=args.nfix, fix_df=1, max_feed_samples=1 << 24, device=local_rank)
@@ -386,7 +395,7 @@ def main():
             m = d.feed_device(dev.data_ptr(), n, out)
             st = d.stats()
             return m, {k: st["ms_" + k] for k in KEYS}, st["launches"] + 1, st["chunks"], 1, 0
-        m, rep = d.replay_sharded(rank, world, dev_pieces, lo, halo, allgather, out)
+        m, rep = d.replay_sharded(rank, world, dev_pieces, lo, halo, allgather, out, has_tail=has_tail, tail=dev_tail)
         return m, {k: getattr(rep, "ms_" + k) for k in KEYS}, rep.launches, rep.chunks, rep.passes, rep.rounds
 
     # sharded e2e: the range goes host -> device once (pinned pieces, inside the timed region) and both passes read it from
@@ -401,15 +410,16 @@ def main():
             return m, len(m) * adsbcu.MSG_DTYPE.itemsize, 2 * n
         if range_fits:
             pos = 0
-            for p, cnt in host_pieces:
+            for p, cnt in host_pieces + (host_tail[0] if host_tail else []):
                 o = (p - hview.ctypes.data)
                 range_dev[pos:pos + 2 * cnt].copy_(host[o:o + 2 * cnt], non_blocking=True)
                 pos += 2 * cnt
             torch.cuda.current_stream().synchronize()
-            m, rep = d.replay_sharded(rank, world, [(range_dev.data_ptr(), my_n)], lo, halo, allgather, out)
+            t = ([(range_dev.data_ptr() + 2 * (hi - lo), thi - tlo)], tlo, host_tail[2]) if host_tail else None
+            m, rep = d.replay_sharded(rank, world, [(range_dev.data_ptr(), hi - lo)], lo, halo, allgather, out, has_tail=has_tail, tail=t)
             return m, len(m) * adsbcu.MSG_DTYPE.itemsize, 2 * my_n
-        m, rep = d.replay_sharded(rank, world, host_pieces, lo, halo, allgather, out, host_pieces=True)
-        return m, len(m) * adsbcu.MSG_DTYPE.itemsize, 2 * my_n * rep.passes
+        m, rep = d.replay_sharded(rank, world, host_pieces, lo, halo, allgather, out, host_pieces=True, has_tail=has_tail, tail=host_tail)
+        return m, len(m) * adsbcu.MSG_DTYPE.itemsize, 2 * (hi - lo) * (rep.passes - (1 if host_tail else 0)) + 2 * (thi - tlo)
 
     sampler = ClockSampler(local_rank)
     sampler.start()                      # nvidia-smi needs ~100 ms to deliver its first row: start before the warm-up
@@ -495,7 +505,7 @@ def main():
         d_iso.close()
         os.environ.pop("ADSBCU_MSG_OVERLAP", None)
         kernels = {}
-        bytes_step = 2.0 * my_n * max(passes, 1) if sharded else 2.0 * n      # what rank 0's kernels streamed in one step
+        bytes_step = 2.0 * my_n if sharded else 2.0 * n      # what rank 0's kernels streamed in one step (one pass over each of its ranges)
         for k, name in (("front", "front_kernel"), ("messages", "message_kernel")):
             ms = float(np.mean(iso[k]))
             gbs = 2.0 * n / (ms * 1e-3) / 1e9

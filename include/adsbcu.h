@@ -230,11 +230,24 @@ typedef struct adsbcu_shard_report {
     uint64_t launches;
     double   ms_front, ms_messages, ms_order, ms_resolve, ms_h2d;
 } adsbcu_shard_report;
-enum { ADSBCU_SHARD_HOST_PIECES = 1 };  /* flags: the pieces are HOST memory (uploaded chunk by chunk, on every pass) */
+enum { ADSBCU_SHARD_HOST_PIECES = 1,     /* flags: the pieces are HOST memory (uploaded chunk by chunk, on every pass) */
+       ADSBCU_SHARD_HAS_TAIL = 2 };      /* _tail only, the same on every rank: the capture ends with a range that rank 0 holds */
 int adsbcu_1090_replay_sharded(adsbcu_handle *h, int rank, int world, const adsbcu_piece *pieces, size_t npieces,
                                uint64_t range_start, const uint8_t *halo_iq /* HOST, <= 326 samples */, size_t n_halo,
                                adsbcu_allgather_fn allgather, void *ctx, unsigned flags,
                                adsbcu_msg *out, size_t cap, size_t *n_out, adsbcu_shard_report *report);
+/* The same with world + 1 ranges: range r on rank r, and the LAST range of the capture (the "tail") on rank 0 as well.  The
+ * first range never runs twice and nobody waits for the end state of the last one, so rank 0 demodulates its own range in
+ * round 0 and the tail in round 1 while the other ranks make their two passes: two passes over 1 / (world + 1) of the capture.
+ * Every rank sets ADSBCU_SHARD_HAS_TAIL; rank 0 passes the tail's pieces, start and halo (ignored elsewhere).  Rank 0's
+ * out[] holds the messages of its own range, then the tail's: *n_first tells where the tail begins.  The capture's message
+ * list is rank 0's first part, ranks 1 .. world-1, rank 0's tail part. */
+int adsbcu_1090_replay_sharded_tail(adsbcu_handle *h, int rank, int world, const adsbcu_piece *pieces, size_t npieces,
+                                    uint64_t range_start, const uint8_t *halo_iq, size_t n_halo,
+                                    const adsbcu_piece *tail_pieces, size_t n_tail_pieces, uint64_t tail_start,
+                                    const uint8_t *tail_halo_iq, size_t n_tail_halo,
+                                    adsbcu_allgather_fn allgather, void *ctx, unsigned flags,
+                                    adsbcu_msg *out, size_t cap, size_t *n_out, size_t *n_first, adsbcu_shard_report *report);
 
 /* ---- Mode A/C on one mag_buf (dump1090 --modeac) ----------------------------------------------------
  * One call == one demodulate2400AC(struct mag_buf*) call of the reference (demod_2400.c:539-726), which

@@ -50,7 +50,7 @@ EXPORTS = ["adsbcu_abi_version", "adsbcu_last_error", "adsbcu_create", "adsbcu_d
            "adsbcu_1090_filter_test", "adsbcu_1090_filter_expire", "adsbcu_get_stats", "adsbcu_1090b_feed", "adsbcu_1090b_reset",
            "adsbcu_978_feed", "adsbcu_978_feed_device", "adsbcu_978_get_stats", "adsbcu_978_reset", "adsbcu_978_phase", "adsbcu_1090_seek", "adsbcu_1090_scan_candidates",
            "adsbcu_1090_known_export", "adsbcu_1090_known_import", "adsbcu_1090_revive", "adsbcu_1090_resolve", "adsbcu_1090_modeac_block", "adsbcu_1090_feed_sc16",
-           "adsbcu_1090_modeac_block_static", "adsbcu_1090_encode_beast", "adsbcu_1090_encode_avr", "adsbcu_1090_state_export", "adsbcu_1090_state_import", "adsbcu_1090_replay_sharded",
+           "adsbcu_1090_modeac_block_static", "adsbcu_1090_encode_beast", "adsbcu_1090_encode_avr", "adsbcu_1090_state_export", "adsbcu_1090_state_import", "adsbcu_1090_replay_sharded", "adsbcu_1090_replay_sharded_tail",
            "adsbcu_1090b_decode_fields", "adsbcu_1090b_cpr_decode", "adsbcu_1090_cpr_decode"]
 
 
@@ -142,6 +142,10 @@ def load():
         L.adsbcu_1090_state_import.argtypes = [C.c_void_p, C.POINTER(StreamStateC), C.c_void_p, C.c_size_t]
         L.adsbcu_1090_replay_sharded.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(Piece), C.c_size_t, C.c_uint64, C.c_void_p, C.c_size_t,
                                                  ALLGATHER_FN, C.c_void_p, C.c_uint, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(ShardReport)]
+        L.adsbcu_1090_replay_sharded_tail.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(Piece), C.c_size_t, C.c_uint64, C.c_void_p, C.c_size_t,
+                                                      C.POINTER(Piece), C.c_size_t, C.c_uint64, C.c_void_p, C.c_size_t,
+                                                      ALLGATHER_FN, C.c_void_p, C.c_uint, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t),
+                                                      C.POINTER(C.c_size_t), C.POINTER(ShardReport)]
         L.adsbcu_1090_modeac_block_static.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_uint64, C.c_void_p,
                                                       C.c_size_t, C.c_void_p, C.c_void_p]
         _lib = L
@@ -360,12 +364,17 @@ class Demod1090:
         self._check(load().adsbcu_1090_state_import(self.h, C.byref(st), addrs.ctypes.data if addrs.size else None, addrs.size))
 
     def replay_sharded(self, rank: int, world: int, pieces, range_start: int, halo_iq: np.ndarray | None, allgather, out: np.ndarray,
-                       host_pieces: bool = False):
-        """adsbcu_1090_replay_sharded.  pieces: [(device address, nsamples)] of THIS rank's range in stream order;
+                       host_pieces: bool = False, has_tail: bool = False, tail=None):
+        """adsbcu_1090_replay_sharded[_tail].  pieces: [(device address, nsamples)] of THIS rank's range in stream order;
         allgather(words: np.ndarray[uint32]) -> list of world np.ndarray[uint32] (the transport: torch.distributed, MPI, ...).
-        Returns (messages of this range, ShardReport)."""
+        has_tail (the same on every rank): the capture has world + 1 ranges and rank 0 also holds the last one,
+        tail = (pieces, start, halo_iq).  Returns (messages of this range [rank 0 with a tail: own range, then the tail;
+        self.n_first tells where the tail begins], ShardReport)."""
         arr = (Piece * max(1, len(pieces)))(*[Piece(int(p), int(n)) for p, n in pieces])
         halo = np.ascontiguousarray(halo_iq if halo_iq is not None else np.zeros(0, np.uint8), np.uint8)
+        t_pieces, t_start, t_halo = tail if (tail is not None and rank == 0) else ([], 0, None)
+        t_arr = (Piece * max(1, len(t_pieces)))(*[Piece(int(p), int(n)) for p, n in t_pieces])
+        t_halo = np.ascontiguousarray(t_halo if t_halo is not None else np.zeros(0, np.uint8), np.uint8)
 
         def cb(_ctx, mine, n_mine, all_, counts):
             try:
@@ -380,12 +389,16 @@ class Demod1090:
                 return 1
         self._cb_error = None
         fn = ALLGATHER_FN(cb)
-        got, rep = C.c_size_t(0), ShardReport()
-        rc = load().adsbcu_1090_replay_sharded(self.h, rank, world, arr, len(pieces), range_start, halo.ctypes.data if halo.size else None,
-                                               halo.size // 2, fn, None, 1 if host_pieces else 0, out.ctypes.data, len(out), C.byref(got), C.byref(rep))
+        got, first, rep = C.c_size_t(0), C.c_size_t(0), ShardReport()
+        flags = (1 if host_pieces else 0) | (2 if has_tail else 0)
+        rc = load().adsbcu_1090_replay_sharded_tail(self.h, rank, world, arr, len(pieces), range_start, halo.ctypes.data if halo.size else None,
+                                                    halo.size // 2, t_arr, len(t_pieces), t_start, t_halo.ctypes.data if t_halo.size else None,
+                                                    t_halo.size // 2, fn, None, flags, out.ctypes.data, len(out), C.byref(got), C.byref(first),
+                                                    C.byref(rep))
         if self._cb_error is not None:
             raise self._cb_error
         self._check(rc)
+        self.n_first = first.value
         return out[:got.value], rep
 
     def filter_add(self, addr): self._check(load().adsbcu_1090_filter_add(self.h, addr))

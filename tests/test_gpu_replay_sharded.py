@@ -34,9 +34,9 @@ def device_copy(iq):
     return t, t.data_ptr()
 
 
-def replay(adsbcu, iq, cuts, nfix, fdf, pieces_per_rank=1):
-    """cuts: sample indices [0, c1, ..., n] -> len(cuts)-1 ranks."""
-    world = len(cuts) - 1
+def replay(adsbcu, iq, cuts, nfix, fdf, pieces_per_rank=1, tail=False):
+    """cuts: sample indices [0, c1, ..., n] -> len(cuts)-1 ranks; tail: the last range is rank 0's second one (len(cuts)-2 ranks)."""
+    world = len(cuts) - 1 - (1 if tail else 0)
     keep, base = device_copy(iq)
     group = ThreadGroup(world)
     results, errors = [None] * world, []
@@ -48,9 +48,13 @@ def replay(adsbcu, iq, cuts, nfix, fdf, pieces_per_rank=1):
             edges = [lo + (hi - lo) * k // pieces_per_rank // 8 * 8 for k in range(pieces_per_rank)] + [hi]
             pieces = [(base + 2 * a, b - a) for a, b in zip(edges[:-1], edges[1:])]
             out = np.zeros(1 << 16, adsbcu.MSG_DTYPE)
+            t = None
+            if tail and rank == 0:
+                tlo, thi = cuts[-2], cuts[-1]
+                t = ([(base + 2 * tlo, thi - tlo)], tlo, iq[2 * max(0, tlo - 326):2 * tlo])
             msgs, rep = d.replay_sharded(rank, world, pieces, lo, iq[2 * max(0, lo - 326):2 * lo],
-                                         lambda w: group.allgather(rank, w), out)
-            results[rank] = (msgs.copy(), rep.passes, rep.rounds, rep.start_addrs)
+                                         lambda w: group.allgather(rank, w), out, has_tail=tail, tail=t)
+            results[rank] = (msgs.copy(), rep.passes, rep.rounds, rep.start_addrs, d.n_first)
         except Exception as e:      # noqa: BLE001
             errors.append(e)
             group.bar.abort()
@@ -90,3 +94,19 @@ def test_replay_sharded_cut_inside_messages(adsbcu_mod, oracle_mod):
     got = np.concatenate([r[0] for r in res])
     assert len(want) > 200
     assert oracle_mod.same_messages(want, got) == []
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_replay_sharded_with_tail_on_rank0(adsbcu_mod, oracle_mod, golden, world):
+    """world + 1 ranges: rank 0 demodulates the first range in round 0 and the last one in round 1 (nobody waits for the
+    last range's end state), the others make their two passes.  Same message set."""
+    g = golden["c3_dense"]
+    iq = g["iq"]
+    n = iq.size // 2
+    cuts = [0] + [(n * k // (world + 1)) // 8 * 8 for k in range(1, world + 1)] + [n]
+    res = replay(adsbcu_mod, iq, cuts, 2, 1, tail=True)
+    first = res[0][4]
+    got = np.concatenate([res[0][0][:first]] + [r[0] for r in res[1:]] + [res[0][0][first:]])
+    assert oracle_mod.same_messages(g["ref_fix2_df1"], got) == []
+    assert res[0][1] == 2 and first > 0 and len(res[0][0]) > first     # one pass over each of its two ranges
+    assert all(r[2] == res[0][2] for r in res)
