@@ -402,7 +402,7 @@ def main():
     probe = adsbcu.Demod1090(nfix_crc=args.nfix, fix_df=1, max_feed_samples=1 << 24, device=local_rank)
     per_sample = (len(probe.feed_device(dev.data_ptr(), min(n, 1 << 24), np.zeros(1 << 18, adsbcu.MSG_DTYPE))) + 64) / min(n, 1 << 24)
     probe.close()
-    out_cap = max(4096, int(my_n * per_sample * 1.5))       # sized from the message density of the tile's first 7 s
+    out_cap = max(4096, int(max(my_n, total // world + 8) * per_sample * 1.5))       # sized from the message density of the tile's first 7 s
     out_pinned = torch.zeros(out_cap * adsbcu.MSG_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
     out = out_pinned.numpy().view(adsbcu.MSG_DTYPE)
     KEYS = ("front", "messages", "order", "resolve")
@@ -419,8 +419,18 @@ def main():
 
     # sharded e2e: the range goes host -> device once (pinned pieces, inside the timed region) and both passes read it from
     # HBM; a range that does not fit (24 h on one GPU) is uploaded chunk by chunk on every pass instead
-    range_fits = sharded and 2 * my_n <= 64 * (1 << 30)
-    range_dev = torch.empty(2 * my_n, dtype=torch.uint8, device="cuda") if range_fits else None
+    # With host buffers the upload is the bottleneck, and the tail would make rank 0 upload twice what the others do: the
+    # end-to-end arm cuts the capture into `world` equal ranges instead (adsbcu_1090_replay_sharded without a tail).
+    if world == 1:
+        elo, ehi = 0, total
+    else:
+        ecut = lambda k: total if k >= world else (total * k // world) // 8 * 8      # noqa: E731
+        elo, ehi = ecut(rank), ecut(rank + 1)
+    e_n = ehi - elo
+    e_halo = halo_of(elo)
+    e_host_pieces = pieces_of(hview.ctypes.data, n, elo, ehi)
+    range_fits = sharded and 2 * e_n <= 64 * (1 << 30)
+    range_dev = torch.empty(2 * e_n, dtype=torch.uint8, device="cuda") if range_fits else None
 
     def step_e2e():
         if not sharded:
@@ -429,16 +439,15 @@ def main():
             return m, len(m) * adsbcu.MSG_DTYPE.itemsize, 2 * n
         if range_fits:
             pos = 0
-            for p, cnt in host_pieces + (host_tail[0] if host_tail else []):
+            for p, cnt in e_host_pieces:
                 o = (p - hview.ctypes.data)
                 range_dev[pos:pos + 2 * cnt].copy_(host[o:o + 2 * cnt], non_blocking=True)
                 pos += 2 * cnt
             torch.cuda.current_stream().synchronize()
-            t = ([(range_dev.data_ptr() + 2 * (hi - lo), thi - tlo)], tlo, host_tail[2]) if host_tail else None
-            m, rep = d.replay_sharded(rank, world, [(range_dev.data_ptr(), hi - lo)], lo, halo, allgather, out, has_tail=has_tail, tail=t)
-            return m, len(m) * adsbcu.MSG_DTYPE.itemsize, 2 * my_n
-        m, rep = d.replay_sharded(rank, world, host_pieces, lo, halo, allgather, out, host_pieces=True, has_tail=has_tail, tail=host_tail)
-        return m, len(m) * adsbcu.MSG_DTYPE.itemsize, 2 * (hi - lo) * (rep.passes - (1 if host_tail else 0)) + 2 * (thi - tlo)
+            m, rep = d.replay_sharded(rank, world, [(range_dev.data_ptr(), e_n)], elo, e_halo, allgather, out)
+            return m, len(m) * adsbcu.MSG_DTYPE.itemsize, 2 * e_n
+        m, rep = d.replay_sharded(rank, world, e_host_pieces, elo, e_halo, allgather, out, host_pieces=True)
+        return m, len(m) * adsbcu.MSG_DTYPE.itemsize, 2 * e_n * rep.passes
 
     sampler = ClockSampler(local_rank)
     sampler.start()                      # nvidia-smi needs ~100 ms to deliver its first row: start before the warm-up
