@@ -286,6 +286,25 @@ int adsbcu_1090_modeac_block_static(adsbcu_handle *h, const uint8_t *iq_dev, siz
                                     const uint8_t *overlap_iq_dev, size_t n_overlap, uint64_t block_timestamp,
                                     adsbcu_msg *out_dev, size_t cap, uint32_t *result_dev /* [2] */, void *cuda_stream);
 
+/* ---- Path A, next layer: dump1090's surveillance field decode ---------------------
+ * What decodeModesMessage does with an accepted frame outside the ME / MB payloads (mode_s.c:626-779): the header
+ * fields of every downlink format (AC, CA, CC, CF, DR, FS, ID, KE, ND, RI, SL, UM, VS), the 13-bit altitude
+ * (decodeAC13Field incl. the Gillham path, mode_s.c:122-150, mode_ac.c:61-122), the squawk (decodeID13Field,
+ * mode_s.c:96-116), air/ground state and alert / SPI flags.  Many messages per call, host arrays in and out.
+ * For DF17 / DF18 the reference's extended-squitter decoder (mode_s.c:798-1587, not built here) may refine airground,
+ * altitude, squawk, alert and spi afterwards: es_pending = 1 marks those records. */
+typedef struct adsbcu_fields_a {
+    uint16_t AC, ID;             /* raw 13-bit fields (0 where the format has none) */
+    uint8_t  CA, CC, CF, DR, FS, KE, ND, RI, SL, UM, VS;
+    uint8_t  airground;          /* airground_t: 0 AG_INVALID, 1 AG_GROUND, 2 AG_AIRBORNE, 3 AG_UNCERTAIN (dump1090.h:179-184) */
+    uint8_t  alert_valid, alert, spi_valid, spi;
+    uint8_t  altitude_baro_valid, altitude_baro_unit;   /* unit: 0 UNIT_FEET, 1 UNIT_METERS */
+    uint8_t  squawk_valid, es_pending;
+    uint16_t squawk;             /* hex-coded octal digits, as dump1090 prints it (%04x) */
+    int32_t  altitude_baro;      /* feet; INVALID_ALTITUDE = -9999 */
+} adsbcu_fields_a;
+int adsbcu_1090_decode_fields(adsbcu_handle *h, const adsbcu_msg *msgs, size_t n, adsbcu_fields_a *out);
+
 /* ---- Wire formats of the decoded set ---------------------------------------------
  * Host-side formatting of adsbcu_msg records exactly as dump1090's network outputs write them; no handle, no GPU.
  *   adsbcu_1090_encode_beast   writeBeastMessage (net_io.c:440-487) per message.  verbatim != 0: the bytes as sliced,

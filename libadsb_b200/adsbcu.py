@@ -20,6 +20,10 @@ assert MSG_DTYPE.itemsize == 56
 MSG_B_DTYPE = np.dtype([("pos", "<u4"), ("crc", "<u4"), ("addr", "<u4"), ("msg", "u1", 14), ("msgbits", "u1"),
                         ("msgtype", "u1"), ("errorbit", "i1"), ("corrected", "u1"), ("reserved", "<u2")])
 assert MSG_B_DTYPE.itemsize == 32
+FIELDS_A_DTYPE = np.dtype([("AC", "<u2"), ("ID", "<u2")] + [(k, "u1") for k in (
+    "CA", "CC", "CF", "DR", "FS", "KE", "ND", "RI", "SL", "UM", "VS", "airground", "alert_valid", "alert", "spi_valid", "spi",
+    "altitude_baro_valid", "altitude_baro_unit", "squawk_valid", "es_pending")] + [("squawk", "<u2"), ("pad", "<u2"), ("altitude_baro", "<i4")])
+assert FIELDS_A_DTYPE.itemsize == 32
 UAT_DTYPE = np.dtype([("offset", "<u8"), ("rs_errors", "<i2"), ("len", "<u2"), ("updown", "u1"), ("reserved", "u1", 3),
                       ("data", "u1", 432)])
 assert UAT_DTYPE.itemsize == 448
@@ -50,7 +54,7 @@ EXPORTS = ["adsbcu_abi_version", "adsbcu_last_error", "adsbcu_create", "adsbcu_d
            "adsbcu_1090_filter_test", "adsbcu_1090_filter_expire", "adsbcu_get_stats", "adsbcu_1090b_feed", "adsbcu_1090b_reset",
            "adsbcu_978_feed", "adsbcu_978_feed_device", "adsbcu_978_get_stats", "adsbcu_978_reset", "adsbcu_978_phase", "adsbcu_1090_seek", "adsbcu_1090_scan_candidates",
            "adsbcu_1090_known_export", "adsbcu_1090_known_import", "adsbcu_1090_revive", "adsbcu_1090_resolve", "adsbcu_1090_modeac_block", "adsbcu_1090_feed_sc16",
-           "adsbcu_1090_modeac_block_static", "adsbcu_1090_encode_beast", "adsbcu_1090_encode_avr", "adsbcu_1090_state_export", "adsbcu_1090_state_import", "adsbcu_1090_replay_sharded", "adsbcu_1090_replay_sharded_tail",
+           "adsbcu_1090_modeac_block_static", "adsbcu_1090_decode_fields", "adsbcu_1090_encode_beast", "adsbcu_1090_encode_avr", "adsbcu_1090_state_export", "adsbcu_1090_state_import", "adsbcu_1090_replay_sharded", "adsbcu_1090_replay_sharded_tail",
            "adsbcu_1090b_decode_fields", "adsbcu_1090b_cpr_decode", "adsbcu_1090_cpr_decode"]
 
 
@@ -134,6 +138,7 @@ def load():
         L.adsbcu_1090_modeac_block.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_uint64, C.c_void_p,
                                                C.c_size_t, C.POINTER(C.c_size_t)]
         L.adsbcu_1090_feed_sc16.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.adsbcu_1090_decode_fields.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         L.adsbcu_1090_encode_beast.restype = C.c_size_t
         L.adsbcu_1090_encode_beast.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t]
         L.adsbcu_1090_encode_avr.restype = C.c_size_t
@@ -240,6 +245,13 @@ class Demod1090:
         got = C.c_size_t(0)
         self._check(load().adsbcu_1090b_feed(self.h, iq.ctypes.data, iq.size, out.ctypes.data, cap, C.byref(got)))
         return out[:got.value]
+
+    def decode_fields_a(self, msgs: np.ndarray) -> np.ndarray:
+        """dump1090's surveillance fields (mode_s.c:626-779) of every MSG_DTYPE record."""
+        msgs = np.ascontiguousarray(msgs, dtype=MSG_DTYPE)
+        out = np.zeros(len(msgs), dtype=FIELDS_A_DTYPE)
+        self._check(load().adsbcu_1090_decode_fields(self.h, msgs.ctypes.data, len(msgs), out.ctypes.data))
+        return out
 
     def cpr_decode_a(self, rec: np.ndarray) -> np.ndarray:
         """dump1090's decodeCPRairborne / decodeCPRsurface / decodeCPRrelative on every CPR_IN_DTYPE record."""

@@ -345,6 +345,144 @@ int cpr_a_decode(Fields *&f, cudaStream_t s, const adsbcu_cpr_in *in, size_t n, 
     return ADSBCU_OK;
 }
 
+// ---- Path A: surveillance fields of decodeModesMessage (mode_s.c:626-779) ----------------------------------------------
+namespace {
+
+__device__ __forceinline__ uint32_t msg_bits(const uint8_t *m, int first, int last)     // getbits (mode_s.h:104-150): bits numbered from 1
+{
+    uint32_t v = 0;
+    for (int b = first; b <= last; ++b) v = (v << 1) | ((m[(b - 1) >> 3] >> (7 - ((b - 1) & 7))) & 1u);
+    return v;
+}
+
+// decodeID13Field (mode_s.c:96-116): the 13-bit identity field as the hex-coded Gillham word 0ABC0...
+__device__ __forceinline__ uint32_t id13_to_gillham(uint32_t f)
+{
+    uint32_t g = 0;
+    if (f & 0x1000) g |= 0x0010;   // C1
+    if (f & 0x0800) g |= 0x1000;   // A1
+    if (f & 0x0400) g |= 0x0020;   // C2
+    if (f & 0x0200) g |= 0x2000;   // A2
+    if (f & 0x0100) g |= 0x0040;   // C4
+    if (f & 0x0080) g |= 0x4000;   // A4
+    if (f & 0x0020) g |= 0x0100;   // B1
+    if (f & 0x0010) g |= 0x0001;   // D1 or Q
+    if (f & 0x0008) g |= 0x0200;   // B2
+    if (f & 0x0004) g |= 0x0002;   // D2
+    if (f & 0x0002) g |= 0x0400;   // B4
+    if (f & 0x0001) g |= 0x0004;   // D4
+    return g;
+}
+
+// modeAToModeC (mode_ac.c:61-122): the table lookup of the reference indexes by the twelve A/B/C/D bits only
+// (track.h:332-341), i.e. it is internalModeAToModeC of the word with every other bit cleared
+__device__ __forceinline__ int mode_a_to_c(uint32_t mode_a)
+{
+    mode_a &= 0x7777u;
+    if ((mode_a & 0xFFFF8889u) != 0 || (mode_a & 0x000000F0u) == 0) return -9999;
+    uint32_t one = 0, five = 0;
+    if (mode_a & 0x0010) one ^= 7;
+    if (mode_a & 0x0020) one ^= 3;
+    if (mode_a & 0x0040) one ^= 1;
+    if ((one & 5) == 5) one ^= 2;
+    if (one > 5) return -9999;
+    if (mode_a & 0x0002) five ^= 0x0FF;
+    if (mode_a & 0x0004) five ^= 0x07F;
+    if (mode_a & 0x1000) five ^= 0x03F;
+    if (mode_a & 0x2000) five ^= 0x01F;
+    if (mode_a & 0x4000) five ^= 0x00F;
+    if (mode_a & 0x0100) five ^= 0x007;
+    if (mode_a & 0x0200) five ^= 0x003;
+    if (mode_a & 0x0400) five ^= 0x001;
+    if (five & 1) one = 6 - one;
+    return int(five * 5 + one) - 13;
+}
+
+__global__ void __launch_bounds__(256) fields_a_kernel(const adsbcu_msg *msgs, uint32_t n, adsbcu_fields_a *out)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    uint8_t m[14];
+    const uint8_t *src = reinterpret_cast<const uint8_t *>(&msgs[k]) + 8;        // adsbcu_msg::msg (packed record: byte loads)
+    for (int i = 0; i < 14; ++i) m[i] = src[i];
+    const int df = reinterpret_cast<const uint8_t *>(&msgs[k])[8 + 14 + 14 + 2];   // adsbcu_msg::msgtype
+    adsbcu_fields_a f;
+    memset(&f, 0, sizeof(f));
+    f.altitude_baro = 0;
+    if (df == 0 || df == 4 || df == 16 || df == 20) {                             // AC (mode_s.c:628-637)
+        f.AC = uint16_t(msg_bits(m, 20, 32));
+        if (f.AC) {
+            const uint32_t ac = f.AC;
+            int alt;
+            if (!(ac & 0x0040)) {                                                  // decodeAC13Field (mode_s.c:122-150)
+                f.altitude_baro_unit = 0;
+                if (ac & 0x0010) alt = int(((ac & 0x1F80) >> 2) | ((ac & 0x0020) >> 1) | (ac & 0x000F)) * 25 - 1000;
+                else { const int c = mode_a_to_c(id13_to_gillham(ac)); alt = c < -12 ? -9999 : 100 * c; }
+            } else {
+                f.altitude_baro_unit = 1;
+                alt = -9999;
+            }
+            f.altitude_baro = alt;
+            if (alt != -9999) f.altitude_baro_valid = 1;
+        }
+    }
+    if (df == 11 || df == 17) {                                                    // CA (:641-661)
+        f.CA = uint8_t(msg_bits(m, 6, 8));
+        if (f.CA == 0 || f.CA == 6 || f.CA == 7) f.airground = 3;
+        else if (f.CA == 4) f.airground = 1;
+        else if (f.CA == 5) f.airground = 2;
+    }
+    if (df == 0) f.CC = uint8_t(msg_bits(m, 7, 7));
+    if (df == 18) f.CF = uint8_t(msg_bits(m, 6, 8));
+    if (df == 4 || df == 5 || df == 20 || df == 21) {
+        f.DR = uint8_t(msg_bits(m, 9, 13));
+        f.FS = uint8_t(msg_bits(m, 6, 8));                                         // FS (:678-712)
+        f.alert_valid = 1; f.spi_valid = 1;
+        switch (f.FS) {
+        case 0: f.airground = 3; break;
+        case 1: f.airground = 1; break;
+        case 2: f.airground = 3; f.alert = 1; break;
+        case 3: f.airground = 1; f.alert = 1; break;
+        case 4: f.airground = 3; f.alert = 1; f.spi = 1; break;
+        case 5: f.airground = 3; f.spi = 1; break;
+        default: f.spi_valid = 0; f.alert_valid = 0; break;
+        }
+        f.UM = uint8_t(msg_bits(m, 14, 19));
+    }
+    if (df == 5 || df == 21) {                                                     // ID (:715-723)
+        f.ID = uint16_t(msg_bits(m, 20, 32));
+        if (f.ID) { f.squawk = uint16_t(id13_to_gillham(f.ID)); f.squawk_valid = 1; }
+    }
+    if (df == 24) { f.KE = uint8_t(msg_bits(m, 4, 4)); f.ND = uint8_t(msg_bits(m, 5, 8)); }
+    if (df == 0 || df == 16) {
+        f.RI = uint8_t(msg_bits(m, 14, 17));
+        f.SL = uint8_t(msg_bits(m, 9, 11));
+        f.VS = uint8_t(msg_bits(m, 6, 6));                                         // VS (:772-779)
+        f.airground = f.VS ? 1 : 3;
+    }
+    f.es_pending = (df == 17 || df == 18) ? 1 : 0;
+    out[k] = f;
+}
+
+}  // namespace
+
+int fields_a_decode(Fields *&f, cudaStream_t s, const adsbcu_msg *msgs, size_t n, adsbcu_fields_a *out, std::string &err)
+{
+    static_assert(sizeof(adsbcu_fields_a) == 32 && sizeof(adsbcu_msg) == 56, "record layout");
+    if (!f) f = new Fields();
+    if (!n) return ADSBCU_OK;
+    cudaError_t e;
+    if (!grow(f->d_in, f->cap_in, n * sizeof(adsbcu_msg)) || !grow(f->d_out, f->cap_out, n * sizeof(adsbcu_fields_a)))
+        return fail(err, "cudaMalloc(fields)", cudaGetLastError());
+    if ((e = cudaMemcpyAsync(f->d_in, msgs, n * sizeof(adsbcu_msg), cudaMemcpyHostToDevice, s)) != cudaSuccess) return fail(err, "H2D(fields)", e);
+    ADSBCU_LAUNCH(fields_a_kernel, unsigned((n + 255) / 256), 256, 0, s, static_cast<const adsbcu_msg *>(f->d_in), uint32_t(n),
+                  static_cast<adsbcu_fields_a *>(f->d_out));
+    if ((e = cudaGetLastError()) != cudaSuccess) return fail(err, "fields_a_kernel", e);
+    if ((e = cudaMemcpyAsync(out, f->d_out, n * sizeof(adsbcu_fields_a), cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(err, "D2H(fields)", e);
+    if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail(err, "fields sync", e);
+    return ADSBCU_OK;
+}
+
 void fields_free(Fields *f)
 {
     if (!f) return;

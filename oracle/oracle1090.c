@@ -657,3 +657,105 @@ void oracle1090_destroy(oracle1090 *o)
     if (!o) return;
     free(o->tab_short); free(o->tab_long); free(o->mag); free(o);
 }
+
+/* ---- surveillance fields of decodeModesMessage (mode_s.c:626-779), for adsbcu_1090_decode_fields ----------------
+ * Pinned against the reference binary's own struct modesMessage through the second tap of oracle/ref_harness.c
+ * (tests/golden/fields_a.npz).  Layout == adsbcu_fields_a (include/adsbcu.h). */
+typedef struct oracle_fields_a {
+    uint16_t AC, ID;
+    uint8_t  CA, CC, CF, DR, FS, KE, ND, RI, SL, UM, VS, airground, alert_valid, alert, spi_valid, spi;
+    uint8_t  altitude_baro_valid, altitude_baro_unit, squawk_valid, es_pending;
+    uint16_t squawk, pad;
+    int32_t  altitude_baro;
+} oracle_fields_a;
+
+static unsigned f_getbits(const uint8_t *m, unsigned first, unsigned last)      /* mode_s.h:104-150, bits numbered from 1 */
+{
+    unsigned v = 0, b;
+    for (b = first; b <= last; ++b) v = (v << 1) | ((m[(b - 1) >> 3] >> (7 - ((b - 1) & 7))) & 1u);
+    return v;
+}
+
+static int f_id13(int f)                                                          /* decodeID13Field, mode_s.c:96-116 */
+{
+    static const struct { int in, out; } map[12] = {
+        {0x1000, 0x0010}, {0x0800, 0x1000}, {0x0400, 0x0020}, {0x0200, 0x2000}, {0x0100, 0x0040}, {0x0080, 0x4000},
+        {0x0020, 0x0100}, {0x0010, 0x0001}, {0x0008, 0x0200}, {0x0004, 0x0002}, {0x0002, 0x0400}, {0x0001, 0x0004}};
+    int g = 0, k;
+    for (k = 0; k < 12; ++k) if (f & map[k].in) g |= map[k].out;
+    return g;
+}
+
+static int f_mode_a_to_c(unsigned a)                                              /* modeAToModeC, mode_ac.c:61-122 via track.h:332-341 */
+{
+    unsigned one = 0, five = 0;
+    a = ((a & 0x0007) | (a & 0x0070) | (a & 0x0700) | (a & 0x7000));           /* indexToModeA(modeAToIndex(a)) */
+    if ((a & 0xFFFF8889u) != 0 || (a & 0xF0u) == 0) return -9999;
+    if (a & 0x0010) one ^= 7;
+    if (a & 0x0020) one ^= 3;
+    if (a & 0x0040) one ^= 1;
+    if ((one & 5) == 5) one ^= 2;
+    if (one > 5) return -9999;
+    if (a & 0x0002) five ^= 0x0FF;
+    if (a & 0x0004) five ^= 0x07F;
+    if (a & 0x1000) five ^= 0x03F;
+    if (a & 0x2000) five ^= 0x01F;
+    if (a & 0x4000) five ^= 0x00F;
+    if (a & 0x0100) five ^= 0x007;
+    if (a & 0x0200) five ^= 0x003;
+    if (a & 0x0400) five ^= 0x001;
+    if (five & 1) one = 6 - one;
+    return (int)(five * 5 + one) - 13;
+}
+
+void oracle1090_decode_fields(const uint8_t *msg, int df, oracle_fields_a *f)
+{
+    memset(f, 0, sizeof(*f));
+    if (df == 0 || df == 4 || df == 16 || df == 20) {
+        f->AC = (uint16_t)f_getbits(msg, 20, 32);
+        if (f->AC) {
+            const int ac = f->AC;
+            int alt;
+            if (!(ac & 0x0040)) {                                                 /* decodeAC13Field, mode_s.c:122-150 */
+                f->altitude_baro_unit = 0;
+                if (ac & 0x0010) alt = (((ac & 0x1F80) >> 2) | ((ac & 0x0020) >> 1) | (ac & 0x000F)) * 25 - 1000;
+                else { const int n = f_mode_a_to_c((unsigned)f_id13(ac)); alt = n < -12 ? -9999 : 100 * n; }
+            } else { f->altitude_baro_unit = 1; alt = -9999; }
+            f->altitude_baro = alt;
+            if (alt != -9999) f->altitude_baro_valid = 1;
+        }
+    }
+    if (df == 11 || df == 17) {
+        f->CA = (uint8_t)f_getbits(msg, 6, 8);
+        switch (f->CA) { case 0: case 6: case 7: f->airground = 3; break; case 4: f->airground = 1; break; case 5: f->airground = 2; break; default: break; }
+    }
+    if (df == 0) f->CC = (uint8_t)f_getbits(msg, 7, 7);
+    if (df == 18) f->CF = (uint8_t)f_getbits(msg, 6, 8);
+    if (df == 4 || df == 5 || df == 20 || df == 21) {
+        f->DR = (uint8_t)f_getbits(msg, 9, 13);
+        f->FS = (uint8_t)f_getbits(msg, 6, 8);
+        f->alert_valid = f->spi_valid = 1;
+        switch (f->FS) {
+        case 0: f->airground = 3; break;
+        case 1: f->airground = 1; break;
+        case 2: f->airground = 3; f->alert = 1; break;
+        case 3: f->airground = 1; f->alert = 1; break;
+        case 4: f->airground = 3; f->alert = 1; f->spi = 1; break;
+        case 5: f->airground = 3; f->spi = 1; break;
+        default: f->spi_valid = f->alert_valid = 0; break;
+        }
+        f->UM = (uint8_t)f_getbits(msg, 14, 19);
+    }
+    if (df == 5 || df == 21) {
+        f->ID = (uint16_t)f_getbits(msg, 20, 32);
+        if (f->ID) { f->squawk = (uint16_t)f_id13(f->ID); f->squawk_valid = 1; }
+    }
+    if (df == 24) { f->KE = (uint8_t)f_getbits(msg, 4, 4); f->ND = (uint8_t)f_getbits(msg, 5, 8); }
+    if (df == 0 || df == 16) {
+        f->RI = (uint8_t)f_getbits(msg, 14, 17);
+        f->SL = (uint8_t)f_getbits(msg, 9, 11);
+        f->VS = (uint8_t)f_getbits(msg, 6, 6);
+        f->airground = f->VS ? 1 : 3;
+    }
+    f->es_pending = (df == 17 || df == 18);
+}

@@ -112,6 +112,35 @@ def have_ref() -> bool:
     return os.path.exists(REF_BIN) and os.access(REF_BIN, os.X_OK)
 
 
+FIELDS_A_DTYPE = np.dtype([("AC", "<u2"), ("ID", "<u2")] + [(k, "u1") for k in (
+    "CA", "CC", "CF", "DR", "FS", "KE", "ND", "RI", "SL", "UM", "VS", "airground", "alert_valid", "alert", "spi_valid", "spi",
+    "altitude_baro_valid", "altitude_baro_unit", "squawk_valid", "es_pending")] + [("squawk", "<u2"), ("pad", "<u2"), ("altitude_baro", "<i4")])
+assert FIELDS_A_DTYPE.itemsize == 32
+
+
+def decode_fields(msgs: np.ndarray) -> np.ndarray:
+    """oracle1090_decode_fields on every record of a MSG_DTYPE array."""
+    L = lib()
+    L.oracle1090_decode_fields.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+    out = np.zeros(len(msgs), FIELDS_A_DTYPE)
+    for k in range(len(msgs)):
+        m = np.ascontiguousarray(msgs["msg"][k])
+        L.oracle1090_decode_fields(m.ctypes.data, int(msgs["msgtype"][k]), out[k:k + 1].ctypes.data)
+    return out
+
+
+def run_ref_fields(iq: np.ndarray, nfix_crc=0, fix_df=1):
+    """The reference's accepted messages AND the surveillance fields its decodeModesMessage filled in for them."""
+    flags = {0: [], 1: ["--fix"], 2: ["--fix-2bit"]}[nfix_crc] + ([] if fix_df else ["--no-fix-df"])
+    tmpdir = "/dev/shm" if os.path.isdir("/dev/shm") else None
+    with tempfile.TemporaryDirectory(dir=tmpdir) as d:
+        cap, rec, fld = os.path.join(d, "cap.uc8"), os.path.join(d, "out.rec"), os.path.join(d, "out.fields")
+        np.ascontiguousarray(iq).tofile(cap)
+        env = dict(os.environ, REF1090_OUT=rec, REF1090_FIELDS=fld)
+        subprocess.run([REF_BIN, "--ifile", cap, "--quiet", *flags], env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, check=False)
+        return np.fromfile(rec, dtype=MSG_DTYPE), np.fromfile(fld, dtype=FIELDS_A_DTYPE)
+
+
 def run_ref(iq: np.ndarray, nfix_crc=0, fix_df=1, extra=()) -> np.ndarray:
     """Run the reference's own dump1090 (--ifile) on `iq`; returns its accepted messages."""
     flags = {0: [], 1: ["--fix"], 2: ["--fix-2bit"]}[nfix_crc] + ([] if fix_df else ["--no-fix-df"])

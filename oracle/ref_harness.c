@@ -79,5 +79,30 @@ void __wrap_useModesMessage(struct modesMessage *mm)
         r.signal_level = mm->signalLevel;
         fwrite(&r, sizeof(r), 1, out_fp);
     }
+    {
+        /* second tap (REF1090_FIELDS=path): the surveillance fields decodeModesMessage filled in (mode_s.c:626-779), in the
+         * layout of adsbcu_fields_a, for tests/make_golden_fields.py */
+        static FILE *ffp;
+        static int fchecked;
+        if (!fchecked) {
+            const char *p = getenv("REF1090_FIELDS");
+            fchecked = 1;
+            if (p && *p) ffp = fopen(p, "wb");
+        }
+        if (ffp) {
+            struct { uint16_t AC, ID; uint8_t CA, CC, CF, DR, FS, KE, ND, RI, SL, UM, VS, airground, alert_valid, alert, spi_valid, spi,
+                     altitude_baro_valid, altitude_baro_unit, squawk_valid, es_pending; uint16_t squawk; uint16_t pad; int32_t altitude_baro; } f;
+            memset(&f, 0, sizeof(f));
+            f.AC = (uint16_t) mm->AC; f.ID = (uint16_t) mm->ID; f.CA = (uint8_t) mm->CA; f.CC = (uint8_t) mm->CC; f.CF = (uint8_t) mm->CF;
+            f.DR = (uint8_t) mm->DR; f.FS = (uint8_t) mm->FS; f.KE = (uint8_t) mm->KE; f.ND = (uint8_t) mm->ND; f.RI = (uint8_t) mm->RI;
+            f.SL = (uint8_t) mm->SL; f.UM = (uint8_t) mm->UM; f.VS = (uint8_t) mm->VS; f.airground = (uint8_t) mm->airground;
+            f.alert_valid = mm->alert_valid; f.alert = mm->alert; f.spi_valid = mm->spi_valid; f.spi = mm->spi;
+            f.altitude_baro_valid = mm->altitude_baro_valid; f.altitude_baro_unit = (uint8_t) mm->altitude_baro_unit;
+            f.squawk_valid = mm->squawk_valid; f.es_pending = (mm->msgtype == 17 || mm->msgtype == 18);
+            f.squawk = (uint16_t) mm->squawk; f.altitude_baro = mm->altitude_baro;
+            fwrite(&f, sizeof(f), 1, ffp);
+            fflush(ffp);
+        }
+    }
     __real_useModesMessage(mm);
 }
