@@ -169,10 +169,10 @@ __global__ void __launch_bounds__(kFWarps * 32, 1) front_kernel(ChunkArgs a)
         const uint8_t *p = src + 2 * (x0 + j0);
 #pragma unroll
         for (int r = 0; r < 3; ++r)
-            if (j0 + 8 * r >= nx_lo && j0 + 8 * r + 8 <= nx_hi) raw[r] = __ldg(reinterpret_cast<const uint4 *>(p + 16 * r));
+            if (j0 + 8 * r >= nx_lo && j0 + 8 * r + 8 <= nx_hi) raw[r] = __ldcs(reinterpret_cast<const uint4 *>(p + 16 * r));
         // the 24 samples of look-ahead past the tile: one pair per lane, lanes 0..11
         const int jh = kWTile + 2 * lane;
-        if (lane < 12 && jh >= nx_lo && jh + 2 <= nx_hi) rawh = __ldg(reinterpret_cast<const uint32_t *>(src + 2 * (x0 + jh)));
+        if (lane < 12 && jh >= nx_lo && jh + 2 <= nx_hi) rawh = __ldcs(reinterpret_cast<const uint32_t *>(src + 2 * (x0 + jh)));
     };
     // magnitude of feed sample x on the slow path (stream edges): carry, one sample, or zero padding
     auto mag_edge = [&](int64_t x) -> int {
