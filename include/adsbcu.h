@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define ADSBCU_ABI_VERSION 1
+#define ADSBCU_ABI_VERSION 2   /* 2: adsbcu_stats fields renamed (round-2 kernels), entry points added; nothing removed */
 
 typedef enum adsbcu_status {
     ADSBCU_OK            = 0,

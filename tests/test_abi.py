@@ -22,7 +22,7 @@ def test_header_symbols_exported(adsbcu_mod):
     for n in names:
         assert hasattr(L, n), f"{n} declared in include/adsbcu.h but not exported"
     assert sorted(adsbcu_mod.EXPORTS) == names
-    assert L.adsbcu_abi_version() == 1
+    assert L.adsbcu_abi_version() == 2
 
 
 def test_struct_layouts(adsbcu_mod):
