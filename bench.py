@@ -1,12 +1,15 @@
 #!/usr/bin/env python
 """bench.py -- Msamples/s through the 1090 MHz demod+CRC hot path (BASELINE.json metric).
 
-A step is one pass of the whole path (magnitude -> preamble -> 5-phase slicer -> CRC/repair ->
-compaction -> ordered host pass) over one synthetic 60 s, 2.4 MS/s capture (configs[1]).
+A step is one pass of the whole path (magnitude -> slicer decisions -> preamble -> CRC/repair -> order -> the ordered
+pass of demodulate2400 -> signal level -> messages; every stage on the GPU) over one synthetic capture.
 
-  value   whole-job Msamples/s, I/Q already resident in HBM (adsbcu_1090_feed_device)
-  e2e     same metric through adsbcu_1090_feed with HOST buffers (H2D + record D2H inside)
-  roofline   the scan kernel: 2 algorithmic bytes per complex sample / its CUDA-event duration
+  --workload config2 (default: 60 s, 2.4 MS/s, configs[1]) | config3 (1 h dense, --fix-2bit) | config4 (24 h, strong
+             scaling) | config5 (UAT 978)
+  N > 1      ONE capture cut into contiguous sample ranges (adsbcu_1090_replay_sharded_tail), no data-path collective
+  value      whole-job Msamples/s, I/Q already resident in HBM
+  e2e        the same metric with HOST buffers (H2D inside the timed region, messages written into pinned out[])
+  roofline   per kernel: 2 algorithmic bytes per complex sample / its CUDA-event duration, against MEASURED_PEAKS hbm_gbs
   cpu_baseline / --impl reference   the reference's own dump1090 (oracle/_ref) on the host cores
 """
 from __future__ import annotations

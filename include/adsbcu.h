@@ -77,7 +77,7 @@ typedef struct adsbcu_msg {
 typedef struct adsbcu_stats {
     uint64_t samples;          /* samples in the feed */
     uint64_t preambles;        /* positions that passed the preamble detector */
-    uint64_t phase_records;    /* (position, phase) records kept by the scan kernel */
+    uint64_t phase_records;    /* (unused since the round-2 kernels: always 0) */
     uint64_t resolved_records; /* records that survived the known-address filter */
     uint64_t messages;         /* accepted messages */
     float    ms_h2d;           /* host->device copy (0 for device feeds) */
