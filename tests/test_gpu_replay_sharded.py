@@ -110,3 +110,13 @@ def test_replay_sharded_with_tail_on_rank0(adsbcu_mod, oracle_mod, golden, world
     assert oracle_mod.same_messages(g["ref_fix2_df1"], got) == []
     assert res[0][1] == 2 and first > 0 and len(res[0][0]) > first     # one pass over each of its two ranges
     assert all(r[2] == res[0][2] for r in res)
+
+
+def test_replay_sharded_refuses_a_saturating_filter(adsbcu_mod):
+    """Once the reference's 4096-slot filter is (nearly) full its contents depend on the insertion order, so a sharded replay could
+    not be exact: the orchestrator must say so instead of returning a different message set."""
+    from libadsb_b200 import synth
+    iq = synth.config3(seconds=7.0, seed=4096, msgs_per_s=3500.0, pool=20000)[0]
+    n = iq.size // 2
+    with pytest.raises(adsbcu_mod.AdsbcuError, match="ADSBCU_SHARD_MAX_ADDRS"):
+        replay(adsbcu_mod, iq, [0, n // 2 // 8 * 8, n], 1, 1)
