@@ -124,55 +124,16 @@ __device__ __forceinline__ uint8_t rs_syndrome(const Gf &gf, const uint8_t *blk,
     return uint8_t(s);
 }
 
-// The rest of the decoder, in three steps around a small per-block work area in shared memory.  Berlekamp-Massey and Forney
-// are short (O(nroots^2)) and run on one lane; the Chien search -- 255 evaluations of the locator, the long serial part of
-// libfec's decode_rs -- is spread over the warp, each lane evaluating the polynomial directly at its own field elements.
+// The rest of the decoder, in three warp-wide steps around a small per-block work area in shared memory: Berlekamp-Massey
+// (one coefficient per lane), the Chien search -- 255 evaluations of the locator, the long serial part of libfec's decode_rs,
+// each lane evaluating the polynomial directly at its own field elements -- and Forney (one root per lane).
 struct RsWork {
     uint8_t syn[20];          // syndromes, log form
     uint8_t lam[21];          // error locator, log form
     uint8_t root[20], loc[20];
+    uint8_t omg[21];          // error evaluator, log form
     int deg, count, nroots;
 };
-
-// syndromes -> locator.  Returns 0 when all syndromes are zero (nothing to correct), else 1.
-__device__ int rs_bm(const Gf &gf, RsWork &w, const uint8_t *syn_raw, int nroots)
-{
-    constexpr int kA0 = 255, kMax = 20;
-    uint8_t syn[kMax], lam[kMax + 1], bb[kMax + 1], tt[kMax + 1];
-    int any = 0;
-    for (int i = 0; i < nroots; ++i) { any |= syn_raw[i]; syn[i] = gf.log[syn_raw[i]]; w.syn[i] = syn[i]; }
-    w.nroots = nroots; w.deg = 0; w.count = 0;
-    if (!any) return 0;
-    // Berlekamp-Massey: error locator lam (polynomial form), bb in log form
-    for (int i = 1; i <= nroots; ++i) { lam[i] = 0; bb[i] = kA0; }
-    lam[0] = 1; bb[0] = 0;
-    int el = 0;
-    for (int r = 1; r <= nroots; ++r) {
-        int disc = 0;
-        for (int i = 0; i < r; ++i)
-            if (lam[i] != 0 && syn[r - i - 1] != kA0) disc ^= gf.exp[mod255(gf.log[lam[i]] + syn[r - i - 1])];
-        disc = gf.log[disc];
-        if (disc == kA0) {
-            for (int i = nroots; i > 0; --i) bb[i] = bb[i - 1];
-            bb[0] = kA0;
-        } else {
-            tt[0] = lam[0];
-            for (int i = 0; i < nroots; ++i) tt[i + 1] = bb[i] != kA0 ? lam[i + 1] ^ gf.exp[mod255(disc + bb[i])] : lam[i + 1];
-            if (2 * el <= r - 1) {
-                el = r - el;
-                for (int i = 0; i <= nroots; ++i) bb[i] = lam[i] == 0 ? kA0 : uint8_t(mod255(gf.log[lam[i]] - disc + 255));
-            } else {
-                for (int i = nroots; i > 0; --i) bb[i] = bb[i - 1];
-                bb[0] = kA0;
-            }
-            for (int i = 0; i <= nroots; ++i) lam[i] = tt[i];
-        }
-    }
-    int deg = 0;
-    for (int i = 0; i <= nroots; ++i) { w.lam[i] = gf.log[lam[i]]; if (w.lam[i] != kA0) deg = i; }
-    w.deg = deg;
-    return 1;
-}
 
 // Chien search by the whole warp: libfec walks i = 1..255 and stops at the deg-th root; here lane l evaluates
 // lambda(alpha^i) for i = 32 r + l + 1 and the roots are collected in ascending i, the first deg of them.
@@ -200,46 +161,84 @@ __device__ void rs_chien_warp(const Gf &gf, RsWork &w, int lane)
     __syncwarp();
 }
 
-// error evaluator and Forney; returns the number of corrected locations, or -1 when the locator has fewer roots than its degree
-__device__ int rs_forney(const Gf &gf, const RsWork &w, uint8_t *blk, int pad)
+// Berlekamp-Massey by the whole warp: lane j holds coefficient j of the locator (polynomial form) and of the auxiliary
+// polynomial (log form); a round is one XOR reduction for the discrepancy and one shuffle for the shift.  Same arithmetic and
+// same order of updates as libfec's decode_rs loop (restated in oracle/oracle978.c).  Returns 0 when all syndromes are zero.
+__device__ int rs_bm_warp(const Gf &gf, RsWork &w, const uint8_t *syn_raw, int nroots, int lane)
 {
-    constexpr int kA0 = 255, kFcr = 120, kMax = 20;
+    constexpr int kA0 = 255;
+    const uint32_t raw = lane < nroots ? syn_raw[lane] : 0u;
+    if (lane < nroots) w.syn[lane] = gf.log[raw];
+    if (lane == 0) { w.nroots = nroots; w.deg = 0; w.count = 0; }
+    const uint32_t any = __ballot_sync(0xFFFFFFFFu, raw != 0u);
+    __syncwarp();
+    if (!any) return 0;
+    uint32_t lam = lane == 0 ? 1u : 0u, bb = lane == 0 ? 0u : uint32_t(kA0);
+    int el = 0;
+    for (int r = 1; r <= nroots; ++r) {
+        uint32_t term = 0;
+        if (lane < r && lam != 0u) {
+            const uint32_t sy = w.syn[r - lane - 1];
+            if (sy != uint32_t(kA0)) term = gf.exp[mod255(int(gf.log[lam]) + int(sy))];
+        }
+        const uint32_t disc = gf.log[__reduce_xor_sync(0xFFFFFFFFu, term)];
+        uint32_t bprev = __shfl_up_sync(0xFFFFFFFFu, bb, 1);
+        if (lane == 0) bprev = uint32_t(kA0);
+        if (disc == uint32_t(kA0)) {
+            bb = bprev;
+        } else {
+            const uint32_t tt = (lane >= 1 && bprev != uint32_t(kA0)) ? lam ^ gf.exp[mod255(int(disc) + int(bprev))] : lam;
+            if (2 * el <= r - 1) {
+                el = r - el;
+                bb = lam == 0u ? uint32_t(kA0) : uint32_t(mod255(int(gf.log[lam]) - int(disc) + 255));
+            } else {
+                bb = bprev;
+            }
+            lam = tt;
+        }
+    }
+    const uint32_t ll = lane <= nroots ? uint32_t(gf.log[lam]) : uint32_t(kA0);
+    if (lane <= nroots) w.lam[lane] = uint8_t(ll);
+    const uint32_t nz = __ballot_sync(0xFFFFFFFFu, ll != uint32_t(kA0));
+    if (lane == 0) w.deg = nz ? 31 - __clz(int(nz)) : 0;
+    __syncwarp();
+    return 1;
+}
+
+// error evaluator and Forney by the whole warp: lane i forms omega_i, then lane j corrects the location of root j
+__device__ int rs_forney_warp(const Gf &gf, RsWork &w, uint8_t *blk, int pad, int lane)
+{
+    constexpr int kA0 = 255, kFcr = 120;
     const int deg = w.deg, count = w.count, nroots = w.nroots;
     if (deg != count) return -1;
-    uint8_t omg[kMax + 1];
     const int dego = deg - 1;
-    for (int i = 0; i <= dego; ++i) {
+    if (lane <= dego) {
         int t = 0;
-        for (int j = i; j >= 0; --j)
-            if (w.syn[i - j] != kA0 && w.lam[j] != kA0) t ^= gf.exp[mod255(w.syn[i - j] + w.lam[j])];
-        omg[i] = gf.log[t];
+        for (int j = lane; j >= 0; --j)
+            if (w.syn[lane - j] != kA0 && w.lam[j] != kA0) t ^= gf.exp[mod255(w.syn[lane - j] + w.lam[j])];
+        w.omg[lane] = gf.log[t];
     }
-    for (int j = count - 1; j >= 0; --j) {
+    __syncwarp();
+    if (lane < count) {
+        const int rt = w.root[lane];
         int num1 = 0, den = 0;
         for (int i = dego; i >= 0; --i)
-            if (omg[i] != kA0) num1 ^= gf.exp[mod255(omg[i] + i * w.root[j])];
-        const int num2 = gf.exp[mod255(w.root[j] * (kFcr - 1) + 255)];
+            if (w.omg[i] != kA0) num1 ^= gf.exp[mod255(w.omg[i] + i * rt)];
+        const int num2 = gf.exp[mod255(rt * (kFcr - 1) + 255)];
         for (int i = min(deg, nroots - 1) & ~1; i >= 0; i -= 2)
-            if (w.lam[i + 1] != kA0) den ^= gf.exp[mod255(w.lam[i + 1] + i * w.root[j])];
-        if (num1 != 0 && w.loc[j] >= pad) blk[w.loc[j] - pad] ^= gf.exp[mod255(gf.log[num1] + gf.log[num2] + 255 - gf.log[den])];
+            if (w.lam[i + 1] != kA0) den ^= gf.exp[mod255(w.lam[i + 1] + i * rt)];
+        if (num1 != 0 && w.loc[lane] >= pad) blk[w.loc[lane] - pad] ^= gf.exp[mod255(gf.log[num1] + gf.log[num2] + 255 - gf.log[den])];
     }
+    __syncwarp();
     return count;
 }
 
 // one block, whole warp: -> corrections (or -1)
 __device__ int rs_decode_warp(const Gf &gf, RsWork &w, uint8_t *blk, const uint8_t *syn_raw, int nroots, int pad, int lane)
 {
-    int e = 0;
-    if (lane == 0) e = rs_bm(gf, w, syn_raw, nroots);
-    e = __shfl_sync(0xFFFFFFFFu, e, 0);
-    __syncwarp();
-    if (!e) return 0;
+    if (!rs_bm_warp(gf, w, syn_raw, nroots, lane)) return 0;
     rs_chien_warp(gf, w, lane);
-    int n = 0;
-    if (lane == 0) n = rs_forney(gf, w, blk, pad);
-    n = __shfl_sync(0xFFFFFFFFu, n, 0);
-    __syncwarp();
-    return n;
+    return rs_forney_warp(gf, w, blk, pad, lane);
 }
 
 __device__ __forceinline__ uint8_t slice_byte(const uint16_t *p, int center)
@@ -297,12 +296,10 @@ __global__ void __launch_bounds__(kDecWarps * 32) uat_decode_kernel(const uint16
             __syncwarp();
             for (int t = lane; t < kUpBlocks * 20; t += 32) sm.syn[warp][t / 20][t % 20] = rs_syndrome(gf, buf + (t / 20) * kUpBlockBytes, kUpBlockBytes, t % 20);
             __syncwarp();
-            int e = 0;                                                                              // RS(92,72): locators on six lanes,
-            if (lane < kUpBlocks) e = rs_bm(gf, sm.work[warp][lane], sm.syn[warp][lane], 20);       // the Chien searches warp-wide, Forney on six lanes
-            __syncwarp();
-            for (int blk = 0; blk < kUpBlocks; ++blk)
-                if (__shfl_sync(0xFFFFFFFFu, e, blk)) rs_chien_warp(gf, sm.work[warp][blk], lane);
-            if (lane < kUpBlocks) sm.res[warp][lane] = e ? rs_forney(gf, sm.work[warp][lane], buf + lane * kUpBlockBytes, 163) : 0;
+            for (int blk = 0; blk < kUpBlocks; ++blk) {                                             // RS(92,72), block after block, warp-wide
+                const int nfix = rs_decode_warp(gf, sm.work[warp][blk], buf + blk * kUpBlockBytes, sm.syn[warp][blk], 20, 163, lane);
+                if (lane == 0) sm.res[warp][blk] = nfix;
+            }
             __syncwarp();
             ok = true;
             for (int blk = 0; blk < kUpBlocks; ++blk) {
