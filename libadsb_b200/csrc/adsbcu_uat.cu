@@ -332,11 +332,16 @@ __global__ void __launch_bounds__(kDecWarps * 32) uat_decode_kernel(const uint16
 // UAT978.cpp:57 as compiled: memmove(buffer, buffer + done, len - done) -- the count is in BYTES although it is the number
 // of SAMPLES left, so only the first half of the unconsumed samples reaches the front and indices [(len-done)/2, len-done)
 // keep what they held (oracle/_ref/libref978.so shows it; tests/golden/uat_ref.npz).  Out of place: src -> dst, all 65536.
-__global__ void __launch_bounds__(256) uat_shift_kernel(const uint16_t *src, uint16_t *dst, uint32_t done, uint32_t len)
+// One kernel per call prepares the buffer: the previous call's memmove (done / len of that call; len == 0: none pending), then the
+// call's new phases behind the `used` samples that are left, and the counters of the call cleared.
+__global__ void __launch_bounds__(256) uat_stage_kernel(const uint16_t *src, uint16_t *dst, uint32_t done, uint32_t len, uint32_t used,
+                                                        const uint16_t *fresh, uint32_t n_fresh, CountersC *ctr)
 {
+    if (blockIdx.x == 0 && threadIdx.x == 0) *ctr = CountersC{0u, 0u, 0u, 0u};
     const uint32_t moved_bytes = len - done;
     const uint8_t *sb = reinterpret_cast<const uint8_t *>(src);
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < 65536u; i += gridDim.x * blockDim.x) {
+        if (i >= used && i < used + n_fresh) { dst[i] = fresh[i - used]; continue; }
         uint32_t lo = sb[2 * i], hi = sb[2 * i + 1];
         if (2 * i < moved_bytes) lo = sb[2 * (done + i)];
         if (2 * i + 1 < moved_bytes) hi = sb[2 * (done + i) + 1];
@@ -361,6 +366,7 @@ struct PathC {
     // UAT978Handler state (UAT978.cpp:106-107)
     uint64_t offset = 0;          // absolute sample of buffer[0]
     uint64_t used = 0;            // samples in the staging buffer
+    uint32_t shift_done = 0, shift_len = 0;   // the last call's memmove, applied by the next call's stage kernel (len 0: none)
     std::vector<RecC> pending;    // decoded candidates of the running process_buffer() call, sorted by s
     // timings of the last feed (bench.py)
     float ms_device = 0.f;
@@ -425,7 +431,7 @@ void pathc_stats(const PathC *c, float *ms_device, uint32_t *calls, uint32_t *la
 void pathc_reset(PathC *c)
 {
     if (!c) return;
-    c->offset = 0; c->used = 0; c->pending.clear();
+    c->offset = 0; c->used = 0; c->shift_done = 0; c->shift_len = 0; c->pending.clear();
     for (auto &b : c->d_buf) if (b) cudaMemset(b, 0, (65536 + 512) * sizeof(uint16_t));
 }
 
@@ -494,8 +500,14 @@ int pathc_feed(PathC *&c, int sm_count, cudaStream_t st, const uint8_t *iq, size
     size_t fed = 0;                                          // samples of this feed already copied into the buffer
     while (fed < n) {
         const uint64_t i = std::min<uint64_t>(65536, c->used + (n - fed));   // UAT978.cpp:52
+        // stage: the last call's (short) memmove, then the new phases, out of place into the other buffer
+        ADSBCU_LAUNCH(uat_stage_kernel, 64, 256, 0, st, c->d_buf[c->cur], c->d_buf[c->cur ^ 1], c->shift_done, c->shift_len, uint32_t(c->used),
+                      c->d_new + fed, uint32_t(i - c->used), c->d_ctr);
+        CKC_(cudaGetLastError());
+        c->cur ^= 1;
+        c->shift_done = 0; c->shift_len = 0;
+        ++c->launches;
         uint16_t *buf = c->d_buf[c->cur];
-        CKC_(cudaMemcpyAsync(buf + c->used, c->d_new + fed, (i - c->used) * sizeof(uint16_t), cudaMemcpyDeviceToDevice, st));
         fed += i - c->used;
         const int64_t len = int64_t(i), lenbits = len / 2 - (kSyncBits + kUpBits);
         // fewer than 36 scannable bits: the reference's process_buffer would return a negative count and its caller would
@@ -504,7 +516,6 @@ int pathc_feed(PathC *&c, int sm_count, cudaStream_t st, const uint8_t *iq, size
         if (lenbits < kSyncBits) { c->used = i; continue; }
         // candidates the scan can try: index = 2 * startbit + {0, 1} (+ 1 for the second alignment), startbit <= lenbits - 36
         const uint32_t last = uint32_t(2 * (lenbits - kSyncBits + 1) + 3);
-        CKC_(cudaMemsetAsync(c->d_ctr, 0, sizeof(CountersC), st));
         ADSBCU_LAUNCH(uat_sync_kernel, (last + 255) / 256, 256, 0, st, buf, 0u, last, c->d_cand, c->cand_cap, c->d_ctr);
         ADSBCU_LAUNCH(uat_decode_kernel, 128, kDecWarps * 32, 0, st, buf, c->offset, c->d_cand, c->d_rec, c->rec_cap, c->d_ctr, c->d_gf);
         CKC_(cudaGetLastError());
@@ -575,11 +586,7 @@ int pathc_feed(PathC *&c, int sm_count, cudaStream_t st, const uint8_t *iq, size
         const int64_t done = (bit - kSyncBits) * 2;
         c->offset += uint64_t(done);
         c->used = uint64_t(len - done);
-        // UAT978.cpp:57: the (short) memmove, into the other buffer
-        ADSBCU_LAUNCH(uat_shift_kernel, 64, 256, 0, st, buf, c->d_buf[c->cur ^ 1], uint32_t(done), uint32_t(len));
-        CKC_(cudaGetLastError());
-        ++c->launches;
-        c->cur ^= 1;
+        c->shift_done = uint32_t(done); c->shift_len = uint32_t(len);      // UAT978.cpp:57, applied when the next call stages its buffer
     }
     CKC_(cudaEventRecord(c->ev[1], st));
     CKC_(cudaStreamSynchronize(st));
