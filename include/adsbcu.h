@@ -291,8 +291,8 @@ int adsbcu_1090_modeac_block_static(adsbcu_handle *h, const uint8_t *iq_dev, siz
  * fields of every downlink format (AC, CA, CC, CF, DR, FS, ID, KE, ND, RI, SL, UM, VS), the 13-bit altitude
  * (decodeAC13Field incl. the Gillham path, mode_s.c:122-150, mode_ac.c:61-122), the squawk (decodeID13Field,
  * mode_s.c:96-116), air/ground state and alert / SPI flags.  Many messages per call, host arrays in and out.
- * For DF17 / DF18 the reference's extended-squitter decoder (mode_s.c:798-1587, not built here) may refine airground,
- * altitude, squawk, alert and spi afterwards: es_pending = 1 marks those records. */
+ * For DF17 / DF18 the reference's extended-squitter decoder (mode_s.c:798-1551, adsbcu_1090_decode_es below) may refine
+ * airground, altitude, squawk, alert and spi afterwards: es_pending = 1 marks those records. */
 typedef struct adsbcu_fields_a {
     uint16_t AC, ID;             /* raw 13-bit fields (0 where the format has none) */
     uint8_t  CA, CC, CF, DR, FS, KE, ND, RI, SL, UM, VS;
@@ -304,6 +304,56 @@ typedef struct adsbcu_fields_a {
     int32_t  altitude_baro;      /* feet; INVALID_ALTITUDE = -9999 */
 } adsbcu_fields_a;
 int adsbcu_1090_decode_fields(adsbcu_handle *h, const adsbcu_msg *msgs, size_t n, adsbcu_fields_a *out);
+
+/* ---- Path A, next layer: the extended-squitter payload (second half) -------------------------
+ * Replaces decodeExtendedSquitter and the nine decodeES* functions behind it (mode_s.c:798-1551) for DF17 / DF18
+ * records: one record per message with everything the reference's struct modesMessage (dump1090.h:444-655) holds
+ * after decodeModesMessage returns, for the fields the ES decoder can touch.  The values that depend on the
+ * surveillance header are folded in (airground from CA, mode_s.c:636-657; source / reliable, mode_s.c:580-585), so a
+ * caller needs adsbcu_fields_a only for the other downlink formats.  Records of other DFs come back zeroed (es = 0).
+ * valid is the OR of the ADSBCU_ES_* bits == the reference's *_valid bit-fields; enumerations carry the reference's
+ * values (dump1090.h:133-242).  Integer fields are bit-exact; the four float fields of metype 19 subtypes 1/2
+ * (sqrtf / atan2 of the velocity components, mode_s.c:894-902) are IEEE results of the same expressions - sqrtf is
+ * correctly rounded on both sides, the heading goes through the device's double atan2 (tests/test_gpu_fields_es.py
+ * walks every (E/W, N/S) pair against glibc).
+ * Pinned against the reference binary's own decodeModesMessage (oracle/ref_harness.c, third tap;
+ * tests/golden/fields_es.npz). */
+enum {
+    ADSBCU_ES_ALTITUDE_BARO = 1u << 0,  ADSBCU_ES_ALTITUDE_GEOM = 1u << 1,  ADSBCU_ES_HEADING = 1u << 2,      ADSBCU_ES_GS = 1u << 3,
+    ADSBCU_ES_IAS = 1u << 4,            ADSBCU_ES_TAS = 1u << 5,            ADSBCU_ES_BARO_RATE = 1u << 6,    ADSBCU_ES_GEOM_RATE = 1u << 7,
+    ADSBCU_ES_SQUAWK = 1u << 8,         ADSBCU_ES_CALLSIGN = 1u << 9,       ADSBCU_ES_CPR = 1u << 10,         ADSBCU_ES_CATEGORY = 1u << 11,
+    ADSBCU_ES_GEOM_DELTA = 1u << 12,    ADSBCU_ES_SPI = 1u << 13,           ADSBCU_ES_ALERT = 1u << 14,       ADSBCU_ES_EMERGENCY = 1u << 15,
+    ADSBCU_ES_NIC_A = 1u << 16,         ADSBCU_ES_NIC_B = 1u << 17,         ADSBCU_ES_NIC_C = 1u << 18,       ADSBCU_ES_NIC_BARO = 1u << 19,
+    ADSBCU_ES_NAC_P = 1u << 20,         ADSBCU_ES_NAC_V = 1u << 21,         ADSBCU_ES_GVA = 1u << 22,         ADSBCU_ES_SDA = 1u << 23,
+    ADSBCU_ES_NAV_HEADING = 1u << 24,   ADSBCU_ES_NAV_FMS_ALTITUDE = 1u << 25, ADSBCU_ES_NAV_MCP_ALTITUDE = 1u << 26, ADSBCU_ES_NAV_QNH = 1u << 27,
+    ADSBCU_ES_NAV_MODES = 1u << 28,     ADSBCU_ES_OPSTATUS = 1u << 29,      ADSBCU_ES_CC_LW = 1u << 30
+};
+/* opstatus flag bits (the one-bit members of modesMessage.opstatus, dump1090.h:596-610) */
+enum {
+    ADSBCU_OPS_OM_ACAS_RA = 1u << 0, ADSBCU_OPS_OM_IDENT = 1u << 1, ADSBCU_OPS_OM_ATC = 1u << 2,  ADSBCU_OPS_OM_SAF = 1u << 3,
+    ADSBCU_OPS_CC_ACAS = 1u << 4,    ADSBCU_OPS_CC_CDTI = 1u << 5,  ADSBCU_OPS_CC_1090_IN = 1u << 6, ADSBCU_OPS_CC_ARV = 1u << 7,
+    ADSBCU_OPS_CC_TS = 1u << 8,      ADSBCU_OPS_CC_UAT_IN = 1u << 9, ADSBCU_OPS_CC_POA = 1u << 10,  ADSBCU_OPS_CC_B2_LOW = 1u << 11
+};
+typedef struct adsbcu_fields_es {
+    uint32_t addr;               /* AA, with MODES_NON_ICAO_ADDRESS (1 << 24) where the reference sets it */
+    uint32_t valid;              /* ADSBCU_ES_* */
+    uint8_t  es, metype, mesub, addrtype;            /* es: 1 for DF17 / DF18; addrtype_t (dump1090.h:147-161) */
+    uint8_t  source, reliable, airground, CA_CF;     /* datasource_t; CA (DF17) or CF (DF18) */
+    uint8_t  cpr_type, cpr_odd, heading_type, nav_heading_type;
+    uint8_t  alert, spi, emergency, category;
+    uint8_t  altitude_baro_unit, altitude_geom_unit, nav_altitude_source, nav_modes;
+    char     callsign[8];        /* as decoded, also when ADSBCU_ES_CALLSIGN is off (the reference keeps the bad one too) */
+    int32_t  altitude_baro, altitude_geom, geom_delta, baro_rate, geom_rate;
+    uint32_t cpr_lat, cpr_lon;
+    uint16_t ias, tas, squawk, ops_flags;            /* ops_flags: ADSBCU_OPS_* */
+    float    heading, gs_v0, gs_v2, gs_selected;
+    float    nav_heading, nav_qnh;
+    int32_t  nav_fms_altitude, nav_mcp_altitude;
+    uint8_t  nic_a, nic_b, nic_c, nic_baro, nac_p, nac_v, sil, sil_type, gva, sda;
+    uint8_t  ops_version, ops_tah, ops_hrd, ops_cc_tc, ops_cc_lw, ops_cc_antenna_offset;
+} adsbcu_fields_es;              /* 120 bytes */
+/* HOST arrays of n records; the decode runs on the handle's device (one thread per message). */
+int adsbcu_1090_decode_es(adsbcu_handle *h, const adsbcu_msg *msgs, size_t n, adsbcu_fields_es *out);
 
 /* ---- Wire formats of the decoded set ---------------------------------------------
  * Host-side formatting of adsbcu_msg records exactly as dump1090's network outputs write them; no handle, no GPU.

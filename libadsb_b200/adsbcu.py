@@ -24,6 +24,21 @@ FIELDS_A_DTYPE = np.dtype([("AC", "<u2"), ("ID", "<u2")] + [(k, "u1") for k in (
     "CA", "CC", "CF", "DR", "FS", "KE", "ND", "RI", "SL", "UM", "VS", "airground", "alert_valid", "alert", "spi_valid", "spi",
     "altitude_baro_valid", "altitude_baro_unit", "squawk_valid", "es_pending")] + [("squawk", "<u2"), ("pad", "<u2"), ("altitude_baro", "<i4")])
 assert FIELDS_A_DTYPE.itemsize == 32
+# adsbcu_fields_es (include/adsbcu.h); valid bits ADSBCU_ES_*
+FIELDS_ES_DTYPE = np.dtype([("addr", "<u4"), ("valid", "<u4")] + [(k, "u1") for k in (
+    "es", "metype", "mesub", "addrtype", "source", "reliable", "airground", "CA_CF", "cpr_type", "cpr_odd", "heading_type", "nav_heading_type",
+    "alert", "spi", "emergency", "category", "altitude_baro_unit", "altitude_geom_unit", "nav_altitude_source", "nav_modes")] +
+    [("callsign", "S8")] + [(k, "<i4") for k in ("altitude_baro", "altitude_geom", "geom_delta", "baro_rate", "geom_rate")] +
+    [("cpr_lat", "<u4"), ("cpr_lon", "<u4"), ("ias", "<u2"), ("tas", "<u2"), ("squawk", "<u2"), ("ops_flags", "<u2")] +
+    [(k, "<f4") for k in ("heading", "gs_v0", "gs_v2", "gs_selected", "nav_heading", "nav_qnh")] +
+    [("nav_fms_altitude", "<i4"), ("nav_mcp_altitude", "<i4")] + [(k, "u1") for k in (
+        "nic_a", "nic_b", "nic_c", "nic_baro", "nac_p", "nac_v", "sil", "sil_type", "gva", "sda",
+        "ops_version", "ops_tah", "ops_hrd", "ops_cc_tc", "ops_cc_lw", "ops_cc_antenna_offset")])
+assert FIELDS_ES_DTYPE.itemsize == 120
+ES_VALID = {name: 1 << k for k, name in enumerate((
+    "altitude_baro", "altitude_geom", "heading", "gs", "ias", "tas", "baro_rate", "geom_rate", "squawk", "callsign", "cpr", "category",
+    "geom_delta", "spi", "alert", "emergency", "nic_a", "nic_b", "nic_c", "nic_baro", "nac_p", "nac_v", "gva", "sda", "nav_heading",
+    "nav_fms_altitude", "nav_mcp_altitude", "nav_qnh", "nav_modes", "opstatus", "cc_lw"))}
 UAT_DTYPE = np.dtype([("offset", "<u8"), ("rs_errors", "<i2"), ("len", "<u2"), ("updown", "u1"), ("reserved", "u1", 3),
                       ("data", "u1", 432)])
 assert UAT_DTYPE.itemsize == 448
@@ -54,7 +69,7 @@ EXPORTS = ["adsbcu_abi_version", "adsbcu_last_error", "adsbcu_create", "adsbcu_d
            "adsbcu_1090_filter_test", "adsbcu_1090_filter_expire", "adsbcu_get_stats", "adsbcu_1090b_feed", "adsbcu_1090b_reset",
            "adsbcu_978_feed", "adsbcu_978_feed_device", "adsbcu_978_get_stats", "adsbcu_978_reset", "adsbcu_978_phase", "adsbcu_1090_seek", "adsbcu_1090_scan_candidates",
            "adsbcu_1090_known_export", "adsbcu_1090_known_import", "adsbcu_1090_revive", "adsbcu_1090_resolve", "adsbcu_1090_modeac_block", "adsbcu_1090_feed_sc16",
-           "adsbcu_1090_modeac_block_static", "adsbcu_1090_decode_fields", "adsbcu_1090_encode_beast", "adsbcu_1090_encode_avr", "adsbcu_1090_state_export", "adsbcu_1090_state_import", "adsbcu_1090_replay_sharded", "adsbcu_1090_replay_sharded_tail",
+           "adsbcu_1090_modeac_block_static", "adsbcu_1090_decode_fields", "adsbcu_1090_decode_es", "adsbcu_1090_encode_beast", "adsbcu_1090_encode_avr", "adsbcu_1090_state_export", "adsbcu_1090_state_import", "adsbcu_1090_replay_sharded", "adsbcu_1090_replay_sharded_tail",
            "adsbcu_1090b_decode_fields", "adsbcu_1090b_cpr_decode", "adsbcu_1090_cpr_decode"]
 
 
@@ -139,6 +154,7 @@ def load():
                                                C.c_size_t, C.POINTER(C.c_size_t)]
         L.adsbcu_1090_feed_sc16.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.adsbcu_1090_decode_fields.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.adsbcu_1090_decode_es.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         L.adsbcu_1090_encode_beast.restype = C.c_size_t
         L.adsbcu_1090_encode_beast.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t]
         L.adsbcu_1090_encode_avr.restype = C.c_size_t
@@ -251,6 +267,13 @@ class Demod1090:
         msgs = np.ascontiguousarray(msgs, dtype=MSG_DTYPE)
         out = np.zeros(len(msgs), dtype=FIELDS_A_DTYPE)
         self._check(load().adsbcu_1090_decode_fields(self.h, msgs.ctypes.data, len(msgs), out.ctypes.data))
+        return out
+
+    def decode_es(self, msgs: np.ndarray) -> np.ndarray:
+        """dump1090's extended-squitter payload decode (mode_s.c:798-1551) of every MSG_DTYPE record (zeroed for other DFs)."""
+        msgs = np.ascontiguousarray(msgs, dtype=MSG_DTYPE)
+        out = np.zeros(len(msgs), dtype=FIELDS_ES_DTYPE)
+        self._check(load().adsbcu_1090_decode_es(self.h, msgs.ctypes.data, len(msgs), out.ctypes.data))
         return out
 
     def cpr_decode_a(self, rec: np.ndarray) -> np.ndarray:

@@ -483,6 +483,343 @@ int fields_a_decode(Fields *&f, cudaStream_t s, const adsbcu_msg *msgs, size_t n
     return ADSBCU_OK;
 }
 
+// ---- Path A: extended-squitter payload (decodeExtendedSquitter and its nine decoders, mode_s.c:798-1551) ----------------
+// One thread per message; the 56 ME bits sit in one 64-bit register and every field is a shift and a mask of it.  A CTA
+// stages its 256 input records and its 256 output records in shared memory so that both directions are coalesced word
+// copies (the records are 56 and 120 bytes: neither is a power of two).
+namespace {
+
+constexpr uint32_t kNonIcao = 1u << 24;                                        // MODES_NON_ICAO_ADDRESS, dump1090.h:262
+// addrtype_t, heading_type_t, nav_altitude_source_t, nav_modes_t, datasource_t (dump1090.h:133-242)
+enum : uint8_t { kAdsbIcao = 0, kAdsbIcaoNt = 1, kAdsrIcao = 2, kTisbIcao = 3, kAdsbOther = 4, kAdsrOther = 5, kTisbTrackfile = 6, kTisbOther = 7,
+                 kAddrUnknown = 9 };
+enum : uint8_t { kHdgGroundTrack = 1, kHdgTrue = 2, kHdgMagnetic = 3, kHdgMagneticOrTrue = 4, kHdgTrackOrHeading = 5 };
+enum : uint8_t { kAltAircraft = 2, kAltMcp = 3, kAltFms = 4 };
+enum : uint8_t { kNavAutopilot = 1, kNavVnav = 2, kNavAltHold = 4, kNavApproach = 8, kNavLnav = 16, kNavTcas = 32 };
+enum : uint8_t { kSrcTisb = 5, kSrcAdsr = 6, kSrcAdsb = 7 };
+
+struct MeBits {
+    uint64_t v;                                                                // ME bit 1 is bit 55
+    __device__ __forceinline__ uint32_t operator()(int first, int last) const { return uint32_t(v >> (56 - last)) & ((1u << (last - first + 1)) - 1u); }
+    __device__ __forceinline__ uint32_t operator()(int bit) const { return uint32_t(v >> (56 - bit)) & 1u; }
+};
+
+__device__ __forceinline__ void non_icao(adsbcu_fields_es &e)                  // setIMF (mode_s.c:832-854)
+{
+    e.addr |= kNonIcao;
+    if (e.addrtype == kAdsbIcao || e.addrtype == kAdsbIcaoNt) e.addrtype = kAdsbOther;
+    else if (e.addrtype == kTisbIcao) e.addrtype = kTisbTrackfile;
+    else if (e.addrtype == kAdsrIcao) e.addrtype = kAdsrOther;
+}
+
+// decodeMovementFieldV0 / V2 (mode_s.c:184-230): midpoints of the piecewise-linear movement scale, computed in double
+// and narrowed once, as the reference's `return <double expression>` from a float function does
+__device__ __forceinline__ float movement_knots(uint32_t m, bool v2)
+{
+    const double half = double(m) + 0.5;
+    double kt;
+    if (m >= 125) kt = 0;
+    else if (m == 124) kt = 180;
+    else if (m >= 109) kt = __dadd_rn(100, __dmul_rn(half - 109, 5));
+    else if (m >= 94) kt = __dadd_rn(70, __dmul_rn(half - 94, 2));
+    else if (m >= 39) kt = __dadd_rn(15, half - 39);
+    else if (m >= 13) kt = __dadd_rn(2, __dmul_rn(half - 13, 0.50));
+    else if (m >= 9) kt = __dadd_rn(1, __dmul_rn(half - 9, 0.25));
+    else if (v2) kt = m >= 3 ? __dadd_rn(0.125, __ddiv_rn(__dmul_rn(half - 3, 0.875), 6)) : m >= 2 ? 0.125 / 2 : 0;
+    else kt = m >= 2 ? __dadd_rn(0.125, __dmul_rn(half - 2, 0.125)) : 0;
+    return __double2float_rn(kt);
+}
+
+__device__ __forceinline__ int ac12_altitude(uint32_t f)                       // decodeAC12Field (mode_s.c:156-178); always feet
+{
+    if (f & 0x10) return int(((f & 0x0FE0) >> 1) | (f & 0x000F)) * 25 - 1000;
+    const int c = mode_a_to_c(id13_to_gillham(((f & 0x0FC0) << 1) | (f & 0x003F)));
+    return c < -12 ? -9999 : 100 * c;
+}
+
+__device__ void es_decode_one(const uint8_t *m, int df, int corrected, adsbcu_fields_es &e)
+{
+    memset(&e, 0, sizeof(e));
+    if (df != 17 && df != 18) return;
+    MeBits me;
+    me.v = 0;
+    for (int i = 0; i < 7; ++i) me.v = (me.v << 8) | m[4 + i];
+    e.es = 1;
+    e.source = kSrcAdsb;                                                       // mode_s.c:580-585
+    e.reliable = corrected == 0;
+    e.addr = (uint32_t(m[1]) << 16) | (uint32_t(m[2]) << 8) | m[3];            // AA, :624-626
+    const uint32_t ca_cf = m[0] & 7u;
+    e.CA_CF = uint8_t(ca_cf);
+    const uint32_t metype = me(1, 5);
+    e.metype = uint8_t(metype);
+    bool imf_bit_counts = false;                                               // check_imf of decodeExtendedSquitter (:1447-1503)
+    if (df == 17) {
+        e.airground = ca_cf == 4 ? 1 : ca_cf == 5 ? 2 : (ca_cf == 0 || ca_cf >= 6) ? 3 : 0;     // CA, :636-657
+    } else {
+        switch (ca_cf) {
+        case 0: e.addrtype = kAdsbIcaoNt; break;
+        case 1: e.addrtype = kAdsbOther; e.addr |= kNonIcao; break;
+        case 2: e.source = kSrcTisb; e.addrtype = kTisbIcao; imf_bit_counts = true; break;
+        case 3: e.source = kSrcTisb; e.addrtype = kTisbIcao; if (me(1)) non_icao(e); return;      // coarse TIS-B: nothing else is read
+        case 5: e.source = kSrcTisb; e.addrtype = kTisbOther; e.addr |= kNonIcao; break;
+        case 6: e.source = kSrcAdsr; e.addrtype = kAdsrIcao; imf_bit_counts = true; break;
+        default: e.addrtype = kAddrUnknown; e.addr |= kNonIcao; return;
+        }
+    }
+    uint32_t valid = 0;
+    if (metype >= 1 && metype <= 4) {                                          // identification and category (:798-829)
+        e.mesub = uint8_t(me(6, 8));
+        bool good = true;
+        for (int k = 0; k < 8; ++k) {
+            const uint32_t six = me(9 + 6 * k, 14 + 6 * k);
+            // ais_charset.c:3 - "@A-Z[\]^_" | " !"#$%&'()*+,-./" | "0-9:;<=>?": codes 0..31 are '@' + code, 32..63 are ' ' + (code - 32)
+            const char c = char(six < 32 ? 0x40 + six : six);
+            e.callsign[k] = c;
+            good = good && ((c >= 'A' && c <= 'Z') || (c >= '0' && c <= '9') || c == ' ');
+        }
+        valid |= ADSBCU_ES_CATEGORY | (good ? ADSBCU_ES_CALLSIGN : 0u);
+        e.category = uint8_t(((0x0E - metype) << 4) | e.mesub);
+    } else if (metype == 19) {                                                 // airborne velocity (:856-963)
+        const uint32_t sub = me(6, 8);
+        e.mesub = uint8_t(sub);
+        if (sub >= 1 && sub <= 4) {
+            if (imf_bit_counts && me(9)) non_icao(e);
+            valid |= ADSBCU_ES_NAC_V;
+            e.nac_v = uint8_t(me(11, 13));
+            if (sub <= 2) {
+                const uint32_t ew_raw = me(15, 24), ns_raw = me(26, 35);
+                if (ew_raw && ns_raw) {
+                    const int scale = sub == 2 ? 4 : 1;
+                    const int ew = int(ew_raw - 1) * (me(14) ? -scale : scale), ns = int(ns_raw - 1) * (me(25) ? -scale : scale);
+                    // sqrtf((ns*ns) + (ew*ew) + 0.5): the sum is a double, narrowed for sqrtf
+                    const float gs = __fsqrt_rn(__double2float_rn(__dadd_rn(double(ns * ns + ew * ew), 0.5)));
+                    e.gs_v0 = e.gs_v2 = e.gs_selected = gs;
+                    valid |= ADSBCU_ES_GS;
+                    if (gs > 0) {
+                        // float ground_track = atan2(ew_vel, ns_vel) * 180.0 / M_PI
+                        float track = __double2float_rn(__ddiv_rn(__dmul_rn(atan2(double(ew), double(ns)), 180.0), 3.14159265358979323846));
+                        if (track < 0) track = __fadd_rn(track, 360.f);
+                        e.heading = track;
+                        e.heading_type = kHdgGroundTrack;
+                        valid |= ADSBCU_ES_HEADING;
+                    }
+                }
+            } else {
+                if (me(14)) { valid |= ADSBCU_ES_HEADING; e.heading = float(me(15, 24)) * (360.f / 1024.f); e.heading_type = kHdgMagneticOrTrue; }
+                const uint32_t airspeed = me(26, 35);
+                if (airspeed) {
+                    const uint32_t kt = (airspeed - 1) * (sub == 4 ? 4u : 1u);
+                    if (me(25)) { valid |= ADSBCU_ES_TAS; e.tas = uint16_t(kt); } else { valid |= ADSBCU_ES_IAS; e.ias = uint16_t(kt); }
+                }
+            }
+            const uint32_t vr = me(38, 46);
+            if (vr) {
+                const int fpm = int(vr - 1) * (me(37) ? -64 : 64);
+                if (me(36)) { e.baro_rate = fpm; valid |= ADSBCU_ES_BARO_RATE; } else { e.geom_rate = fpm; valid |= ADSBCU_ES_GEOM_RATE; }
+            }
+            const uint32_t delta = me(50, 56);
+            if (delta) { valid |= ADSBCU_ES_GEOM_DELTA; e.geom_delta = int(delta - 1) * (me(49) ? -25 : 25); }
+        }
+    } else if (metype >= 5 && metype <= 8) {                                   // surface position (:965-1001)
+        e.airground = 1;
+        valid |= ADSBCU_ES_CPR;
+        e.cpr_type = 0;
+        const uint32_t movement = me(6, 12);
+        if (movement > 0 && movement < 125) {
+            valid |= ADSBCU_ES_GS;
+            e.gs_selected = e.gs_v0 = movement_knots(movement, false);
+            e.gs_v2 = movement_knots(movement, true);
+        }
+        if (me(13)) { valid |= ADSBCU_ES_HEADING; e.heading = float(me(14, 20)) * (360.f / 128.f); e.heading_type = kHdgTrackOrHeading; }
+        if (imf_bit_counts && me(21)) non_icao(e);
+        e.cpr_odd = uint8_t(me(22));
+        e.cpr_lat = me(23, 39);
+        e.cpr_lon = me(40, 56);
+    } else if (metype == 0 || (metype >= 9 && metype <= 18) || (metype >= 20 && metype <= 22)) {   // airborne position (:1003-1092)
+        const uint32_t ss = me(6, 7);
+        if (ss == 1 || ss == 2) { valid |= ADSBCU_ES_ALERT; e.alert = 1; }
+        else { valid |= ADSBCU_ES_ALERT | ADSBCU_ES_SPI; e.spi = ss == 3; }
+        if (imf_bit_counts) { if (me(8)) non_icao(e); }
+        else { valid |= ADSBCU_ES_NIC_B; e.nic_b = uint8_t(me(8)); }
+        const uint32_t ac12 = me(9, 20);
+        if (metype != 0) {
+            e.cpr_lat = me(23, 39);
+            e.cpr_lon = me(40, 56);
+            const bool stuck = ac12 == 0 && e.cpr_lon == 0 && (e.cpr_lat & 0x0fff) == 0 && metype == 15;   // :1056, not used for positioning
+            if (!stuck) { valid |= ADSBCU_ES_CPR; e.cpr_type = 1; e.cpr_odd = uint8_t(me(22)); }
+        }
+        if (ac12 && e.airground != 1) {
+            const int alt = ac12_altitude(ac12);
+            if (alt != -9999) {
+                if (e.airground == 0) e.airground = 3;
+                if (metype >= 20) { e.altitude_geom = alt; valid |= ADSBCU_ES_ALTITUDE_GEOM; }
+                else { e.altitude_baro = alt; valid |= ADSBCU_ES_ALTITUDE_BARO; }
+            }
+        }
+    } else if (metype == 23) {                                                 // test message (:1094-1107)
+        e.mesub = uint8_t(me(6, 8));
+        const uint32_t id = me(9, 21);
+        if (e.mesub == 7 && id) { valid |= ADSBCU_ES_SQUAWK; e.squawk = uint16_t(id13_to_gillham(id)); }
+    } else if (metype == 28) {                                                 // aircraft status (:1109-1129)
+        e.mesub = uint8_t(me(6, 8));
+        if (e.mesub == 1) {
+            valid |= ADSBCU_ES_EMERGENCY;
+            e.emergency = uint8_t(me(9, 11));
+            const uint32_t id = me(12, 24);
+            if (id) { valid |= ADSBCU_ES_SQUAWK; e.squawk = uint16_t(id13_to_gillham(id)); }
+            if (imf_bit_counts && me(56)) non_icao(e);
+        }
+    } else if (metype == 29) {                                                 // target state and status (:1131-1324)
+        const uint32_t sub = me(6, 7);
+        e.mesub = uint8_t(sub);
+        if (imf_bit_counts && me(51)) non_icao(e);
+        if ((sub == 0 && me(11) == 0) || sub == 1) {
+            valid |= ADSBCU_ES_NAC_P | ADSBCU_ES_NIC_BARO;                     // bits 40-46 mean the same in both versions
+            e.nac_p = uint8_t(me(40, 43));
+            e.nic_baro = uint8_t(me(44));
+            e.sil = uint8_t(me(45, 46));
+            e.sil_type = 1;
+        }
+        if (sub == 0 && me(11) == 0) {                                         // version 1 layout
+            const uint32_t vsrc = me(8, 9), vmode = me(14, 15), hsrc = me(26, 27), hmode = me(38, 39), tcas = me(52, 53);
+            const uint8_t src = vsrc == 1 ? kAltMcp : vsrc == 2 ? kAltAircraft : vsrc == 3 ? kAltFms : 0;
+            uint8_t modes = 0;
+            e.nav_altitude_source = src;
+            if (vmode == 1 || vmode == 2) {
+                valid |= ADSBCU_ES_NAV_MODES;
+                modes |= src == kAltFms ? kNavVnav : (vmode == 2 && src == kAltAircraft) ? kNavAltHold : kNavAutopilot;
+            }
+            const int alt = -1000 + 100 * int(me(16, 25));
+            if (src == kAltMcp) { valid |= ADSBCU_ES_NAV_MCP_ALTITUDE; e.nav_mcp_altitude = alt; }
+            else if (src == kAltFms) { valid |= ADSBCU_ES_NAV_FMS_ALTITUDE; e.nav_fms_altitude = alt; }
+            if (hsrc) {
+                valid |= ADSBCU_ES_NAV_HEADING;
+                e.nav_heading = float(me(28, 36));
+                e.nav_heading_type = me(37) ? kHdgGroundTrack : kHdgMagneticOrTrue;
+            }
+            if (hmode == 1 || hmode == 2) { valid |= ADSBCU_ES_NAV_MODES; modes |= hsrc == 3 ? kNavLnav : kNavAutopilot; }
+            if (tcas != 0) valid |= ADSBCU_ES_NAV_MODES;                        // 0: TCAS assumed, but it does not make the modes valid
+            if (tcas != 1) modes |= kNavTcas;
+            e.nav_modes = modes;
+            valid |= ADSBCU_ES_EMERGENCY;
+            e.emergency = uint8_t(me(54, 56));
+        } else if (sub == 1) {                                                 // version 2 layout
+            const uint32_t alt_bits = me(10, 20), baro_bits = me(21, 29);
+            if (alt_bits) {
+                const int alt = int(alt_bits - 1) * 32;
+                if (me(9)) { valid |= ADSBCU_ES_NAV_FMS_ALTITUDE; e.nav_fms_altitude = alt; }
+                else { valid |= ADSBCU_ES_NAV_MCP_ALTITUDE; e.nav_mcp_altitude = alt; }
+            }
+            if (baro_bits) { valid |= ADSBCU_ES_NAV_QNH; e.nav_qnh = __double2float_rn(__dadd_rn(800.0, __dmul_rn(double(baro_bits - 1), 0.8))); }
+            if (me(30)) { valid |= ADSBCU_ES_NAV_HEADING; e.nav_heading = float(me(31, 39)) * (180.f / 256.f); e.nav_heading_type = kHdgMagneticOrTrue; }
+            if (me(47)) {
+                valid |= ADSBCU_ES_NAV_MODES;
+                e.nav_modes = uint8_t((me(48) ? kNavAutopilot : 0) | (me(49) ? kNavVnav : 0) | (me(50) ? kNavAltHold : 0) | (me(52) ? kNavApproach : 0) |
+                                      (me(53) ? kNavTcas : 0) | (me(54) ? kNavLnav : 0));
+            }
+        }
+    } else if (metype == 31) {                                                 // operational status (:1326-1445)
+        const uint32_t sub = me(6, 8);
+        e.mesub = uint8_t(sub);
+        if (imf_bit_counts && me(56)) non_icao(e);
+        if (sub <= 1) {
+            const uint32_t version = me(41, 43);
+            const bool surface = sub == 1;
+            uint32_t ops = 0;
+            valid |= ADSBCU_ES_OPSTATUS;
+            e.ops_version = uint8_t(version);
+            if (version == 0) {
+                if (!surface && me(9, 10) == 0) ops |= (me(12) ? 0u : ADSBCU_OPS_CC_ACAS) | (me(13) ? ADSBCU_OPS_CC_CDTI : 0u);
+            } else if (version <= 2) {
+                const bool v2 = version == 2;
+                if (me(25, 26) == 0) {                                         // operational mode codes
+                    ops |= (me(27) ? ADSBCU_OPS_OM_ACAS_RA : 0u) | (me(28) ? ADSBCU_OPS_OM_IDENT : 0u) | (me(29) ? ADSBCU_OPS_OM_ATC : 0u);
+                    if (v2) { ops |= me(30) ? ADSBCU_OPS_OM_SAF : 0u; valid |= ADSBCU_ES_SDA; e.sda = uint8_t(me(31, 32)); }
+                }
+                if (me(9, 10) == 0 && (v2 || me(13, 14) == 0)) {               // capability class codes
+                    if (!surface) {
+                        if (v2) ops |= (me(11) ? ADSBCU_OPS_CC_ACAS : 0u) | (me(12) ? ADSBCU_OPS_CC_1090_IN : 0u) | (me(19) ? ADSBCU_OPS_CC_UAT_IN : 0u);
+                        else ops |= (me(11) ? 0u : ADSBCU_OPS_CC_ACAS) | (me(12) ? ADSBCU_OPS_CC_CDTI : 0u);
+                        ops |= (me(15) ? ADSBCU_OPS_CC_ARV : 0u) | (me(16) ? ADSBCU_OPS_CC_TS : 0u);
+                        e.ops_cc_tc = uint8_t(me(17, 18));
+                    } else {
+                        ops |= (me(11) ? ADSBCU_OPS_CC_POA : 0u) | (me(15) ? ADSBCU_OPS_CC_B2_LOW : 0u);
+                        valid |= ADSBCU_ES_CC_LW;
+                        e.ops_cc_lw = uint8_t(me(21, 24));
+                        if (v2) {
+                            ops |= (me(12) ? ADSBCU_OPS_CC_1090_IN : 0u) | (me(16) ? ADSBCU_OPS_CC_UAT_IN : 0u);
+                            valid |= ADSBCU_ES_NAC_V | ADSBCU_ES_NIC_C;
+                            e.nac_v = uint8_t(me(17, 19));
+                            e.nic_c = uint8_t(me(20));
+                            e.ops_cc_antenna_offset = uint8_t(me(33, 40));
+                        } else {
+                            ops |= me(12) ? ADSBCU_OPS_CC_CDTI : 0u;
+                        }
+                    }
+                }
+                valid |= ADSBCU_ES_NIC_A | ADSBCU_ES_NAC_P;
+                e.nic_a = uint8_t(me(44));
+                e.nac_p = uint8_t(me(45, 48));
+                e.sil = uint8_t(me(51, 52));
+                e.sil_type = v2 ? (me(55) ? 2 : 3) : 1;
+                e.ops_hrd = me(54) ? kHdgMagnetic : kHdgTrue;
+                if (!surface) {
+                    valid |= ADSBCU_ES_NIC_BARO;
+                    e.nic_baro = uint8_t(me(53));
+                    if (v2) { valid |= ADSBCU_ES_GVA; e.gva = uint8_t(me(49, 50)); }
+                } else {
+                    e.ops_tah = me(53) ? e.ops_hrd : kHdgGroundTrack;
+                }
+            }
+            e.ops_flags = uint16_t(ops);
+        }
+    } else if (metype != 24 && metype != 30) {
+        e.reliable = 0;                                                        // "Dubious" (:1546-1549)
+    }
+    e.valid = valid;
+}
+
+constexpr int kEsThreads = 256;
+
+__global__ void __launch_bounds__(kEsThreads) fields_es_kernel(const uint32_t *msgs, uint32_t n, uint32_t *out)
+{
+    constexpr uint32_t kInWords = sizeof(adsbcu_msg) / 4, kOutWords = sizeof(adsbcu_fields_es) / 4;
+    __shared__ uint32_t s_in[kEsThreads * kInWords];
+    __shared__ uint32_t s_out[kEsThreads * kOutWords];
+    const uint32_t first = blockIdx.x * kEsThreads;
+    const uint32_t count = min(uint32_t(kEsThreads), n - first);
+    for (uint32_t w = threadIdx.x; w < count * kInWords; w += kEsThreads) s_in[w] = msgs[size_t(first) * kInWords + w];
+    __syncthreads();
+    if (threadIdx.x < count) {
+        const uint8_t *rec = reinterpret_cast<const uint8_t *>(s_in + threadIdx.x * kInWords);
+        adsbcu_fields_es e;
+        es_decode_one(rec + 8, rec[8 + 14 + 14 + 2], rec[8 + 14 + 14 + 1], e);      // adsbcu_msg::msg, ::msgtype, ::correctedbits
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(&e);
+        for (uint32_t w = 0; w < kOutWords; ++w) s_out[threadIdx.x * kOutWords + w] = src[w];
+    }
+    __syncthreads();
+    for (uint32_t w = threadIdx.x; w < count * kOutWords; w += kEsThreads) out[size_t(first) * kOutWords + w] = s_out[w];
+}
+
+}  // namespace
+
+int fields_es_decode(Fields *&f, cudaStream_t s, const adsbcu_msg *msgs, size_t n, adsbcu_fields_es *out, std::string &err)
+{
+    static_assert(sizeof(adsbcu_fields_es) == 120 && sizeof(adsbcu_msg) == 56, "record layout");
+    if (!f) f = new Fields();
+    if (!n) return ADSBCU_OK;
+    cudaError_t e;
+    if (!grow(f->d_in, f->cap_in, n * sizeof(adsbcu_msg)) || !grow(f->d_out, f->cap_out, n * sizeof(adsbcu_fields_es)))
+        return fail(err, "cudaMalloc(fields)", cudaGetLastError());
+    if ((e = cudaMemcpyAsync(f->d_in, msgs, n * sizeof(adsbcu_msg), cudaMemcpyHostToDevice, s)) != cudaSuccess) return fail(err, "H2D(es)", e);
+    ADSBCU_LAUNCH(fields_es_kernel, unsigned((n + kEsThreads - 1) / kEsThreads), kEsThreads, 0, s, static_cast<const uint32_t *>(f->d_in), uint32_t(n),
+                  static_cast<uint32_t *>(f->d_out));
+    if ((e = cudaGetLastError()) != cudaSuccess) return fail(err, "fields_es_kernel", e);
+    if ((e = cudaMemcpyAsync(out, f->d_out, n * sizeof(adsbcu_fields_es), cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(err, "D2H(es)", e);
+    if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail(err, "es sync", e);
+    return ADSBCU_OK;
+}
+
 void fields_free(Fields *f)
 {
     if (!f) return;

@@ -759,3 +759,385 @@ void oracle1090_decode_fields(const uint8_t *msg, int df, oracle_fields_a *f)
     }
     f->es_pending = (df == 17 || df == 18);
 }
+
+/* ---- extended-squitter payload of decodeModesMessage (mode_s.c:798-1551), for adsbcu_1090_decode_es ---------------
+ * Pinned against the reference binary's own decodeModesMessage through the third tap of oracle/ref_harness.c
+ * (tests/golden/fields_es.npz: frames in, struct modesMessage fields out).  Layout == adsbcu_fields_es. */
+typedef struct oracle_fields_es {
+    uint32_t addr, valid;
+    uint8_t  es, metype, mesub, addrtype, source, reliable, airground, CA_CF;
+    uint8_t  cpr_type, cpr_odd, heading_type, nav_heading_type, alert, spi, emergency, category;
+    uint8_t  altitude_baro_unit, altitude_geom_unit, nav_altitude_source, nav_modes;
+    char     callsign[8];
+    int32_t  altitude_baro, altitude_geom, geom_delta, baro_rate, geom_rate;
+    uint32_t cpr_lat, cpr_lon;
+    uint16_t ias, tas, squawk, ops_flags;
+    float    heading, gs_v0, gs_v2, gs_selected, nav_heading, nav_qnh;
+    int32_t  nav_fms_altitude, nav_mcp_altitude;
+    uint8_t  nic_a, nic_b, nic_c, nic_baro, nac_p, nac_v, sil, sil_type, gva, sda;
+    uint8_t  ops_version, ops_tah, ops_hrd, ops_cc_tc, ops_cc_lw, ops_cc_antenna_offset;
+} oracle_fields_es;
+
+enum { V_ALT_BARO = 1u << 0, V_ALT_GEOM = 1u << 1, V_HEADING = 1u << 2, V_GS = 1u << 3, V_IAS = 1u << 4, V_TAS = 1u << 5, V_BARO_RATE = 1u << 6,
+       V_GEOM_RATE = 1u << 7, V_SQUAWK = 1u << 8, V_CALLSIGN = 1u << 9, V_CPR = 1u << 10, V_CATEGORY = 1u << 11, V_GEOM_DELTA = 1u << 12,
+       V_SPI = 1u << 13, V_ALERT = 1u << 14, V_EMERGENCY = 1u << 15, V_NIC_A = 1u << 16, V_NIC_B = 1u << 17, V_NIC_C = 1u << 18,
+       V_NIC_BARO = 1u << 19, V_NAC_P = 1u << 20, V_NAC_V = 1u << 21, V_GVA = 1u << 22, V_SDA = 1u << 23, V_NAV_HEADING = 1u << 24,
+       V_NAV_FMS = 1u << 25, V_NAV_MCP = 1u << 26, V_NAV_QNH = 1u << 27, V_NAV_MODES = 1u << 28, V_OPSTATUS = 1u << 29, V_CC_LW = 1u << 30 };
+enum { O_OM_ACAS_RA = 1, O_OM_IDENT = 2, O_OM_ATC = 4, O_OM_SAF = 8, O_CC_ACAS = 16, O_CC_CDTI = 32, O_CC_1090_IN = 64, O_CC_ARV = 128,
+       O_CC_TS = 256, O_CC_UAT_IN = 512, O_CC_POA = 1024, O_CC_B2_LOW = 2048 };
+/* dump1090.h:147-161, 186-201, 219-242 */
+enum { AT_ADSB_ICAO, AT_ADSB_ICAO_NT, AT_ADSR_ICAO, AT_TISB_ICAO, AT_ADSB_OTHER, AT_ADSR_OTHER, AT_TISB_TRACKFILE, AT_TISB_OTHER, AT_MODE_A, AT_UNKNOWN };
+enum { H_INVALID, H_GROUND_TRACK, H_TRUE, H_MAGNETIC, H_MAGNETIC_OR_TRUE, H_TRACK_OR_HEADING };
+enum { NM_AUTOPILOT = 1, NM_VNAV = 2, NM_ALT_HOLD = 4, NM_APPROACH = 8, NM_LNAV = 16, NM_TCAS = 32 };
+enum { NA_INVALID, NA_UNKNOWN, NA_AIRCRAFT, NA_MCP, NA_FMS };
+enum { SRC_TISB = 5, SRC_ADSR = 6, SRC_ADSB = 7 };
+#define NON_ICAO (1u << 24)
+
+static void es_set_imf(oracle_fields_es *e)                                      /* setIMF, mode_s.c:832-854 */
+{
+    e->addr |= NON_ICAO;
+    if (e->addrtype == AT_ADSB_ICAO || e->addrtype == AT_ADSB_ICAO_NT) e->addrtype = AT_ADSB_OTHER;
+    else if (e->addrtype == AT_TISB_ICAO) e->addrtype = AT_TISB_TRACKFILE;
+    else if (e->addrtype == AT_ADSR_ICAO) e->addrtype = AT_ADSR_OTHER;
+}
+
+static int es_ac12(int f, uint8_t *unit)                                          /* decodeAC12Field, mode_s.c:156-178 */
+{
+    *unit = 0;
+    if (f & 0x10) return ((((f & 0x0FE0) >> 1) | (f & 0x000F)) * 25) - 1000;
+    {
+        const int n = f_mode_a_to_c((unsigned)f_id13(((f & 0x0FC0) << 1) | (f & 0x003F)));
+        return n < -12 ? -9999 : 100 * n;
+    }
+}
+
+static float es_movement(unsigned m, int v2)                                      /* decodeMovementFieldV0 / V2, mode_s.c:184-230 */
+{
+    if (m >= 125) return 0;
+    if (m == 124) return 180;
+    if (m >= 109) return 100 + (m - 109 + 0.5) * 5;
+    if (m >= 94) return 70 + (m - 94 + 0.5) * 2;
+    if (m >= 39) return 15 + (m - 39 + 0.5) * 1;
+    if (m >= 13) return 2 + (m - 13 + 0.5) * 0.50;
+    if (m >= 9) return 1 + (m - 9 + 0.5) * 0.25;
+    if (v2) {
+        if (m >= 3) return 0.125 + (m - 3 + 0.5) * 0.875 / 6;
+        if (m >= 2) return 0.125 / 2;
+        return 0;
+    }
+    if (m >= 2) return 0.125 + (m - 2 + 0.5) * 0.125;
+    return 0;
+}
+
+#define MEBITS(a, b) f_getbits(me, (a), (b))
+#define MEBIT(a) f_getbits(me, (a), (a))
+
+static void es_velocity(oracle_fields_es *e, const uint8_t *me, int check_imf)   /* decodeESAirborneVelocity, mode_s.c:856-963 */
+{
+    unsigned raw;
+    e->mesub = (uint8_t)MEBITS(6, 8);
+    if (e->mesub < 1 || e->mesub > 4) return;
+    if (check_imf && MEBIT(9)) es_set_imf(e);
+    e->valid |= V_NAC_V;
+    e->nac_v = (uint8_t)MEBITS(11, 13);
+    if (e->mesub <= 2) {
+        const unsigned ew_raw = MEBITS(15, 24), ns_raw = MEBITS(26, 35);
+        if (ew_raw && ns_raw) {
+            const int mul = e->mesub == 2 ? 4 : 1;
+            const int ew = (int)(ew_raw - 1) * (MEBIT(14) ? -1 : 1) * mul, ns = (int)(ns_raw - 1) * (MEBIT(25) ? -1 : 1) * mul;
+            e->gs_v0 = e->gs_v2 = e->gs_selected = sqrtf((ns * ns) + (ew * ew) + 0.5);
+            e->valid |= V_GS;
+            if (e->gs_selected > 0) {
+                float track = atan2(ew, ns) * 180.0 / M_PI;
+                if (track < 0) track += 360;
+                e->heading = track;
+                e->heading_type = H_GROUND_TRACK;
+                e->valid |= V_HEADING;
+            }
+        }
+    } else {
+        unsigned airspeed;
+        if (MEBIT(14)) {
+            e->valid |= V_HEADING;
+            e->heading = MEBITS(15, 24) * 360.0 / 1024.0;
+            e->heading_type = H_MAGNETIC_OR_TRUE;
+        }
+        airspeed = MEBITS(26, 35);
+        if (airspeed) {
+            const unsigned speed = (airspeed - 1) * (e->mesub == 4 ? 4 : 1);
+            if (MEBIT(25)) { e->valid |= V_TAS; e->tas = (uint16_t)speed; } else { e->valid |= V_IAS; e->ias = (uint16_t)speed; }
+        }
+    }
+    raw = MEBITS(38, 46);
+    if (raw) {
+        const int rate = (int)(raw - 1) * (MEBIT(37) ? -64 : 64);
+        if (MEBIT(36)) { e->baro_rate = rate; e->valid |= V_BARO_RATE; } else { e->geom_rate = rate; e->valid |= V_GEOM_RATE; }
+    }
+    raw = MEBITS(50, 56);
+    if (raw) { e->valid |= V_GEOM_DELTA; e->geom_delta = (int)(raw - 1) * (MEBIT(49) ? -25 : 25); }
+}
+
+static void es_surface(oracle_fields_es *e, const uint8_t *me, int check_imf)    /* decodeESSurfacePosition, mode_s.c:965-1001 */
+{
+    const unsigned movement = MEBITS(6, 12);
+    e->airground = 1;
+    e->valid |= V_CPR;
+    e->cpr_type = 0;
+    if (movement > 0 && movement < 125) {
+        e->valid |= V_GS;
+        e->gs_selected = e->gs_v0 = es_movement(movement, 0);
+        e->gs_v2 = es_movement(movement, 1);
+    }
+    if (MEBIT(13)) { e->valid |= V_HEADING; e->heading = MEBITS(14, 20) * 360.0 / 128.0; e->heading_type = H_TRACK_OR_HEADING; }
+    if (check_imf && MEBIT(21)) es_set_imf(e);
+    e->cpr_odd = (uint8_t)MEBIT(22);
+    e->cpr_lat = MEBITS(23, 39);
+    e->cpr_lon = MEBITS(40, 56);
+}
+
+static void es_airborne(oracle_fields_es *e, const uint8_t *me, int check_imf)   /* decodeESAirbornePosition, mode_s.c:1003-1092 */
+{
+    const unsigned ac12 = MEBITS(9, 20);
+    switch (MEBITS(6, 7)) {
+    case 0: e->valid |= V_ALERT | V_SPI; e->alert = e->spi = 0; break;
+    case 1: case 2: e->valid |= V_ALERT; e->alert = 1; break;
+    default: e->valid |= V_ALERT | V_SPI; e->alert = 0; e->spi = 1; break;
+    }
+    if (check_imf) { if (MEBIT(8)) es_set_imf(e); }
+    else { e->valid |= V_NIC_B; e->nic_b = (uint8_t)MEBIT(8); }
+    if (e->metype != 0) {
+        e->cpr_lat = MEBITS(23, 39);
+        e->cpr_lon = MEBITS(40, 56);
+        if (!(ac12 == 0 && e->cpr_lon == 0 && (e->cpr_lat & 0x0fff) == 0 && e->metype == 15)) {
+            e->valid |= V_CPR;
+            e->cpr_type = 1;
+            e->cpr_odd = (uint8_t)MEBIT(22);
+        }
+    }
+    if (ac12 && e->airground != 1) {
+        uint8_t unit;
+        const int alt = es_ac12((int)ac12, &unit);
+        if (alt != -9999) {
+            if (e->airground == 0) e->airground = 3;
+            if (e->metype >= 20 && e->metype <= 22) { e->altitude_geom = alt; e->altitude_geom_unit = unit; e->valid |= V_ALT_GEOM; }
+            else { e->altitude_baro = alt; e->altitude_baro_unit = unit; e->valid |= V_ALT_BARO; }
+        }
+    }
+}
+
+static void es_target(oracle_fields_es *e, const uint8_t *me, int check_imf)     /* decodeESTargetStatus, mode_s.c:1131-1324 */
+{
+    e->mesub = (uint8_t)MEBITS(6, 7);
+    if (check_imf && MEBIT(51)) es_set_imf(e);
+    if (e->mesub == 0 && MEBIT(11) == 0) {
+        unsigned h_source;
+        int alt;
+        switch (MEBITS(8, 9)) { case 1: e->nav_altitude_source = NA_MCP; break; case 2: e->nav_altitude_source = NA_AIRCRAFT; break;
+                                case 3: e->nav_altitude_source = NA_FMS; break; default: break; }
+        switch (MEBITS(14, 15)) {
+        case 1:
+            e->valid |= V_NAV_MODES;
+            e->nav_modes |= e->nav_altitude_source == NA_FMS ? NM_VNAV : NM_AUTOPILOT;
+            break;
+        case 2:
+            e->valid |= V_NAV_MODES;
+            e->nav_modes |= e->nav_altitude_source == NA_FMS ? NM_VNAV : e->nav_altitude_source == NA_AIRCRAFT ? NM_ALT_HOLD : NM_AUTOPILOT;
+            break;
+        default: break;
+        }
+        alt = -1000 + 100 * (int)MEBITS(16, 25);
+        if (e->nav_altitude_source == NA_MCP) { e->valid |= V_NAV_MCP; e->nav_mcp_altitude = alt; }
+        else if (e->nav_altitude_source == NA_FMS) { e->valid |= V_NAV_FMS; e->nav_fms_altitude = alt; }
+        h_source = MEBITS(26, 27);
+        if (h_source != 0) {
+            e->valid |= V_NAV_HEADING;
+            e->nav_heading = MEBITS(28, 36);
+            e->nav_heading_type = MEBIT(37) ? H_GROUND_TRACK : H_MAGNETIC_OR_TRUE;
+        }
+        switch (MEBITS(38, 39)) {
+        case 1: case 2: e->valid |= V_NAV_MODES; e->nav_modes |= h_source == 3 ? NM_LNAV : NM_AUTOPILOT; break;
+        default: break;
+        }
+        e->valid |= V_NAC_P | V_NIC_BARO;
+        e->nac_p = (uint8_t)MEBITS(40, 43);
+        e->nic_baro = (uint8_t)MEBIT(44);
+        e->sil = (uint8_t)MEBITS(45, 46);
+        e->sil_type = 1;
+        switch (MEBITS(52, 53)) {
+        case 1: e->valid |= V_NAV_MODES; break;
+        case 2: case 3: e->valid |= V_NAV_MODES; e->nav_modes |= NM_TCAS; break;
+        default: e->nav_modes |= NM_TCAS; break;
+        }
+        e->valid |= V_EMERGENCY;
+        e->emergency = (uint8_t)MEBITS(54, 56);
+    } else if (e->mesub == 1) {
+        const unsigned is_fms = MEBIT(9), alt_bits = MEBITS(10, 20), baro_bits = MEBITS(21, 29);
+        if (alt_bits != 0) {
+            if (is_fms) { e->valid |= V_NAV_FMS; e->nav_fms_altitude = (int)(alt_bits - 1) * 32; }
+            else { e->valid |= V_NAV_MCP; e->nav_mcp_altitude = (int)(alt_bits - 1) * 32; }
+        }
+        if (baro_bits != 0) { e->valid |= V_NAV_QNH; e->nav_qnh = 800.0 + (baro_bits - 1) * 0.8; }
+        if (MEBIT(30)) { e->valid |= V_NAV_HEADING; e->nav_heading = MEBITS(31, 39) * 180.0 / 256.0; e->nav_heading_type = H_MAGNETIC_OR_TRUE; }
+        e->valid |= V_NAC_P | V_NIC_BARO;
+        e->nac_p = (uint8_t)MEBITS(40, 43);
+        e->nic_baro = (uint8_t)MEBIT(44);
+        e->sil = (uint8_t)MEBITS(45, 46);
+        e->sil_type = 1;
+        if (MEBIT(47)) {
+            e->valid |= V_NAV_MODES;
+            e->nav_modes = (uint8_t)((MEBIT(48) ? NM_AUTOPILOT : 0) | (MEBIT(49) ? NM_VNAV : 0) | (MEBIT(50) ? NM_ALT_HOLD : 0) |
+                                     (MEBIT(52) ? NM_APPROACH : 0) | (MEBIT(53) ? NM_TCAS : 0) | (MEBIT(54) ? NM_LNAV : 0));
+        }
+    }
+}
+
+static void es_opstatus(oracle_fields_es *e, const uint8_t *me, int check_imf)   /* decodeESOperationalStatus, mode_s.c:1326-1445 */
+{
+    unsigned o = 0;
+    e->mesub = (uint8_t)MEBITS(6, 8);
+    if (check_imf && MEBIT(56)) es_set_imf(e);
+    if (e->mesub > 1) return;
+    e->valid |= V_OPSTATUS;
+    e->ops_version = (uint8_t)MEBITS(41, 43);
+    switch (e->ops_version) {
+    case 0:
+        if (e->mesub == 0 && MEBITS(9, 10) == 0) { if (!MEBIT(12)) o |= O_CC_ACAS; if (MEBIT(13)) o |= O_CC_CDTI; }
+        break;
+    case 1:
+        if (MEBITS(25, 26) == 0) { if (MEBIT(27)) o |= O_OM_ACAS_RA; if (MEBIT(28)) o |= O_OM_IDENT; if (MEBIT(29)) o |= O_OM_ATC; }
+        if (e->mesub == 0 && MEBITS(9, 10) == 0 && MEBITS(13, 14) == 0) {
+            if (!MEBIT(11)) o |= O_CC_ACAS;
+            if (MEBIT(12)) o |= O_CC_CDTI;
+            if (MEBIT(15)) o |= O_CC_ARV;
+            if (MEBIT(16)) o |= O_CC_TS;
+            e->ops_cc_tc = (uint8_t)MEBITS(17, 18);
+        } else if (e->mesub == 1 && MEBITS(9, 10) == 0 && MEBITS(13, 14) == 0) {
+            if (MEBIT(11)) o |= O_CC_POA;
+            if (MEBIT(12)) o |= O_CC_CDTI;
+            if (MEBIT(15)) o |= O_CC_B2_LOW;
+            e->valid |= V_CC_LW;
+            e->ops_cc_lw = (uint8_t)MEBITS(21, 24);
+        }
+        e->valid |= V_NIC_A | V_NAC_P;
+        e->nic_a = (uint8_t)MEBIT(44);
+        e->nac_p = (uint8_t)MEBITS(45, 48);
+        e->sil_type = 1;
+        e->sil = (uint8_t)MEBITS(51, 52);
+        e->ops_hrd = MEBIT(54) ? H_MAGNETIC : H_TRUE;
+        if (e->mesub == 0) { e->valid |= V_NIC_BARO; e->nic_baro = (uint8_t)MEBIT(53); }
+        else e->ops_tah = MEBIT(53) ? e->ops_hrd : H_GROUND_TRACK;
+        break;
+    case 2:
+        if (MEBITS(25, 26) == 0) {
+            if (MEBIT(27)) o |= O_OM_ACAS_RA;
+            if (MEBIT(28)) o |= O_OM_IDENT;
+            if (MEBIT(29)) o |= O_OM_ATC;
+            if (MEBIT(30)) o |= O_OM_SAF;
+            e->valid |= V_SDA;
+            e->sda = (uint8_t)MEBITS(31, 32);
+        }
+        if (e->mesub == 0 && MEBITS(9, 10) == 0) {
+            if (MEBIT(11)) o |= O_CC_ACAS;
+            if (MEBIT(12)) o |= O_CC_1090_IN;
+            if (MEBIT(15)) o |= O_CC_ARV;
+            if (MEBIT(16)) o |= O_CC_TS;
+            e->ops_cc_tc = (uint8_t)MEBITS(17, 18);
+            if (MEBIT(19)) o |= O_CC_UAT_IN;
+        } else if (e->mesub == 1 && MEBITS(9, 10) == 0) {
+            if (MEBIT(11)) o |= O_CC_POA;
+            if (MEBIT(12)) o |= O_CC_1090_IN;
+            if (MEBIT(15)) o |= O_CC_B2_LOW;
+            if (MEBIT(16)) o |= O_CC_UAT_IN;
+            e->valid |= V_NAC_V | V_NIC_C | V_CC_LW;
+            e->nac_v = (uint8_t)MEBITS(17, 19);
+            e->nic_c = (uint8_t)MEBIT(20);
+            e->ops_cc_lw = (uint8_t)MEBITS(21, 24);
+            e->ops_cc_antenna_offset = (uint8_t)MEBITS(33, 40);
+        }
+        e->valid |= V_NIC_A | V_NAC_P;
+        e->nic_a = (uint8_t)MEBIT(44);
+        e->nac_p = (uint8_t)MEBITS(45, 48);
+        e->sil = (uint8_t)MEBITS(51, 52);
+        e->sil_type = MEBIT(55) ? 2 : 3;
+        e->ops_hrd = MEBIT(54) ? H_MAGNETIC : H_TRUE;
+        if (e->mesub == 0) { e->valid |= V_GVA | V_NIC_BARO; e->gva = (uint8_t)MEBITS(49, 50); e->nic_baro = (uint8_t)MEBIT(53); }
+        else e->ops_tah = MEBIT(53) ? e->ops_hrd : H_GROUND_TRACK;
+        break;
+    default: break;
+    }
+    e->ops_flags = (uint16_t)o;
+}
+
+/* msg: the 14 corrected bytes; df: the downlink format; corrected: bits repaired (mm->correctedbits). */
+void oracle1090_decode_es(const uint8_t *msg, int df, int corrected, oracle_fields_es *e)
+{
+    static const char ais[65] = "@ABCDEFGHIJKLMNOPQRSTUVWXYZ[\\]^_ !\"#$%&'()*+,-./0123456789:;<=>?";   /* ais_charset.c:3 */
+    const uint8_t *me = msg + 4;
+    int check_imf = 0, k;
+    memset(e, 0, sizeof(*e));
+    if (df != 17 && df != 18) return;
+    e->es = 1;
+    e->source = SRC_ADSB;                                                         /* mode_s.c:580-585 */
+    e->reliable = corrected == 0;
+    e->addr = f_getbits(msg, 9, 32);                                              /* mode_s.c:624-626 */
+    e->CA_CF = (uint8_t)f_getbits(msg, 6, 8);
+    if (df == 17)                                                                 /* CA, mode_s.c:636-657 */
+        switch (e->CA_CF) { case 0: case 6: case 7: e->airground = 3; break; case 4: e->airground = 1; break; case 5: e->airground = 2; break; default: break; }
+    e->metype = (uint8_t)MEBITS(1, 5);                                            /* decodeExtendedSquitter, mode_s.c:1447-1551 */
+    if (df == 18) {
+        switch (e->CA_CF) {
+        case 0: e->addrtype = AT_ADSB_ICAO_NT; break;
+        case 1: e->addrtype = AT_ADSB_OTHER; e->addr |= NON_ICAO; break;
+        case 2: e->source = SRC_TISB; e->addrtype = AT_TISB_ICAO; check_imf = 1; break;
+        case 3: e->source = SRC_TISB; e->addrtype = AT_TISB_ICAO; if (MEBIT(1)) es_set_imf(e); return;
+        case 5: e->addrtype = AT_TISB_OTHER; e->source = SRC_TISB; e->addr |= NON_ICAO; break;
+        case 6: e->addrtype = AT_ADSR_ICAO; e->source = SRC_ADSR; check_imf = 1; break;
+        default: e->addrtype = AT_UNKNOWN; e->addr |= NON_ICAO; return;
+        }
+    }
+    switch (e->metype) {
+    case 1: case 2: case 3: case 4:                                               /* decodeESIdentAndCategory, mode_s.c:798-829 */
+        e->mesub = (uint8_t)MEBITS(6, 8);
+        e->valid |= V_CALLSIGN | V_CATEGORY;
+        for (k = 0; k < 8; ++k) {
+            const char c = ais[MEBITS(9 + 6 * k, 14 + 6 * k)];
+            e->callsign[k] = c;
+        }
+        for (k = 0; k < 8; ++k) {
+            const char c = e->callsign[k];
+            if (!((c >= 'A' && c <= 'Z') || (c >= '0' && c <= '9') || c == ' ')) { e->valid &= ~(uint32_t)V_CALLSIGN; break; }
+        }
+        e->category = (uint8_t)(((0x0E - e->metype) << 4) | e->mesub);
+        break;
+    case 19: es_velocity(e, me, check_imf); break;
+    case 5: case 6: case 7: case 8: es_surface(e, me, check_imf); break;
+    case 0: case 9: case 10: case 11: case 12: case 13: case 14: case 15: case 16: case 17: case 18: case 20: case 21: case 22:
+        es_airborne(e, me, check_imf);
+        break;
+    case 23:                                                                      /* decodeESTestMessage, mode_s.c:1094-1107 */
+        e->mesub = (uint8_t)MEBITS(6, 8);
+        if (e->mesub == 7) { const int id = (int)MEBITS(9, 21); if (id) { e->valid |= V_SQUAWK; e->squawk = (uint16_t)f_id13(id); } }
+        break;
+    case 28:                                                                      /* decodeESAircraftStatus, mode_s.c:1109-1129 */
+        e->mesub = (uint8_t)MEBITS(6, 8);
+        if (e->mesub == 1) {
+            const int id = (int)MEBITS(12, 24);
+            e->valid |= V_EMERGENCY;
+            e->emergency = (uint8_t)MEBITS(9, 11);
+            if (id) { e->valid |= V_SQUAWK; e->squawk = (uint16_t)f_id13(id); }
+            if (check_imf && MEBIT(56)) es_set_imf(e);
+        }
+        break;
+    case 29: es_target(e, me, check_imf); break;
+    case 31: es_opstatus(e, me, check_imf); break;
+    case 24: case 30: break;
+    default: e->reliable = 0; break;                                              /* "Dubious", mode_s.c:1546-1549 */
+    }
+}
+
+/* n frames of 14 corrected bytes each; corrected[k] = bits repaired (NULL: none); DF from the first five bits. */
+void oracle1090_decode_es_batch(const uint8_t *frames, size_t n, const uint8_t *corrected, oracle_fields_es *out)
+{
+    size_t k;
+    for (k = 0; k < n; ++k) oracle1090_decode_es(frames + 14 * k, frames[14 * k] >> 3, corrected ? corrected[k] : 0, out + k);
+}

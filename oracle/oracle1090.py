@@ -129,6 +129,46 @@ def decode_fields(msgs: np.ndarray) -> np.ndarray:
     return out
 
 
+FIELDS_ES_DTYPE = np.dtype([("addr", "<u4"), ("valid", "<u4")] + [(k, "u1") for k in (
+    "es", "metype", "mesub", "addrtype", "source", "reliable", "airground", "CA_CF", "cpr_type", "cpr_odd", "heading_type", "nav_heading_type",
+    "alert", "spi", "emergency", "category", "altitude_baro_unit", "altitude_geom_unit", "nav_altitude_source", "nav_modes")] +
+    [("callsign", "S8")] + [(k, "<i4") for k in ("altitude_baro", "altitude_geom", "geom_delta", "baro_rate", "geom_rate")] +
+    [("cpr_lat", "<u4"), ("cpr_lon", "<u4"), ("ias", "<u2"), ("tas", "<u2"), ("squawk", "<u2"), ("ops_flags", "<u2")] +
+    [(k, "<f4") for k in ("heading", "gs_v0", "gs_v2", "gs_selected", "nav_heading", "nav_qnh")] +
+    [("nav_fms_altitude", "<i4"), ("nav_mcp_altitude", "<i4")] + [(k, "u1") for k in (
+        "nic_a", "nic_b", "nic_c", "nic_baro", "nac_p", "nac_v", "sil", "sil_type", "gva", "sda",
+        "ops_version", "ops_tah", "ops_hrd", "ops_cc_tc", "ops_cc_lw", "ops_cc_antenna_offset")])
+assert FIELDS_ES_DTYPE.itemsize == 120
+
+
+def decode_es(frames: np.ndarray, corrected=None) -> np.ndarray:
+    """oracle1090_decode_es on n corrected 14-byte frames (uint8 [n, 14]); corrected: bits repaired per frame."""
+    frames = np.ascontiguousarray(frames, np.uint8).reshape(-1, 14)
+    L = lib()
+    L.oracle1090_decode_es_batch.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
+    L.oracle1090_decode_es_batch.restype = None
+    out = np.zeros(len(frames), FIELDS_ES_DTYPE)
+    cor = None if corrected is None else np.ascontiguousarray(corrected, np.uint8)
+    L.oracle1090_decode_es_batch(frames.ctypes.data, len(frames), None if cor is None else cor.ctypes.data, out.ctypes.data)
+    return out
+
+
+def run_ref_decode(frames: np.ndarray):
+    """The reference's own decodeModesMessage on 14-byte frames as received (third tap of ref_harness.c): the ES
+    record of each frame and decodeModesMessage's return code."""
+    frames = np.ascontiguousarray(frames, np.uint8).reshape(-1, 14)
+    rec = np.dtype([("es", FIELDS_ES_DTYPE), ("rc", "<i4")])
+    tmpdir = "/dev/shm" if os.path.isdir("/dev/shm") else None
+    with tempfile.TemporaryDirectory(dir=tmpdir) as d:
+        fin, fout = os.path.join(d, "frames.bin"), os.path.join(d, "es.bin")
+        frames.tofile(fin)
+        subprocess.run([REF_BIN], env=dict(os.environ, REF1090_DECODE_IN=fin, REF1090_DECODE_OUT=fout), check=True,
+                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        r = np.fromfile(fout, dtype=rec)
+    assert len(r) == len(frames)
+    return r["es"].copy(), r["rc"].copy()
+
+
 def run_ref_fields(iq: np.ndarray, nfix_crc=0, fix_df=1):
     """The reference's accepted messages AND the surveillance fields its decodeModesMessage filled in for them."""
     flags = {0: [], 1: ["--fix"], 2: ["--fix-2bit"]}[nfix_crc] + ([] if fix_df else ["--no-fix-df"])

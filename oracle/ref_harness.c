@@ -3,7 +3,7 @@
  *
  * Harness linked into oracle/_ref/dump1090_ref, the UNMODIFIED flightaware
  * dump1090 compiled from the sources where they lie under
- * /root/reference/dump1090 (see oracle/Makefile).  It adds exactly two things:
+ * /root/reference/dump1090 (see oracle/Makefile).  It adds exactly three things:
  *
  *  1. the four interactive* entry points declared in dump1090.h (the real
  *     interactive.c needs <curses.h>, absent in this image); all no-ops, never
@@ -14,8 +14,13 @@
  *     message (the parity tuple: bytes, verbatim, crc, corrected bits,
  *     12 MHz timestamp, score, addr, RSSI) and then calls the real sink, so
  *     the reference's own behaviour (tracking, stats, printing) is unchanged.
+ *  3. a link-time wrap of main(): with REF1090_DECODE_IN / REF1090_DECODE_OUT set the binary does not demodulate
+ *     anything; it reads 14-byte frames, hands each to the reference's decodeModesMessage() (mode_s.c:520) exactly
+ *     as demodulate2400 does (zeroed struct, score from scoreModesMessage) and writes what the extended-squitter
+ *     decoder left in struct modesMessage, in the layout of adsbcu_fields_es, for tests/make_golden_es.py.
  */
 #include "dump1090.h"
+#include "adsbcu.h"
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -105,4 +110,108 @@ void __wrap_useModesMessage(struct modesMessage *mm)
         }
     }
     __real_useModesMessage(mm);
+}
+
+/* ---- third tap: decodeModesMessage on frames from a file ------------------------------------------------------- */
+int __real_main(int argc, char **argv);
+
+static void es_record(const struct modesMessage *mm, adsbcu_fields_es *e)
+{
+    unsigned v = 0, o = 0;
+    memset(e, 0, sizeof(*e));
+    if (mm->msgtype != 17 && mm->msgtype != 18) return;
+    e->es = 1;
+    e->addr = mm->addr;
+    e->metype = (uint8_t) mm->metype; e->mesub = (uint8_t) mm->mesub; e->addrtype = (uint8_t) mm->addrtype;
+    e->source = (uint8_t) mm->source; e->reliable = (uint8_t) mm->reliable; e->airground = (uint8_t) mm->airground;
+    e->CA_CF = (uint8_t) (mm->msgtype == 17 ? mm->CA : mm->CF);
+    e->cpr_type = (uint8_t) mm->cpr_type; e->cpr_odd = mm->cpr_odd; e->heading_type = (uint8_t) mm->heading_type;
+    e->nav_heading_type = (uint8_t) mm->nav.heading_type;
+    e->alert = mm->alert; e->spi = mm->spi; e->emergency = (uint8_t) mm->emergency; e->category = (uint8_t) mm->category;
+    e->altitude_baro_unit = (uint8_t) mm->altitude_baro_unit; e->altitude_geom_unit = (uint8_t) mm->altitude_geom_unit;
+    e->nav_altitude_source = (uint8_t) mm->nav.altitude_source; e->nav_modes = (uint8_t) mm->nav.modes;
+    memcpy(e->callsign, mm->callsign, 8);
+    e->altitude_baro = mm->altitude_baro; e->altitude_geom = mm->altitude_geom; e->geom_delta = mm->geom_delta;
+    e->baro_rate = mm->baro_rate; e->geom_rate = mm->geom_rate;
+    e->cpr_lat = mm->cpr_lat; e->cpr_lon = mm->cpr_lon;
+    e->ias = (uint16_t) mm->ias; e->tas = (uint16_t) mm->tas; e->squawk = (uint16_t) mm->squawk;
+    e->heading = mm->heading; e->gs_v0 = mm->gs.v0; e->gs_v2 = mm->gs.v2; e->gs_selected = mm->gs.selected;
+    e->nav_heading = mm->nav.heading; e->nav_qnh = mm->nav.qnh;
+    e->nav_fms_altitude = mm->nav.fms_altitude; e->nav_mcp_altitude = mm->nav.mcp_altitude;
+    e->nic_a = mm->accuracy.nic_a; e->nic_b = mm->accuracy.nic_b; e->nic_c = mm->accuracy.nic_c; e->nic_baro = mm->accuracy.nic_baro;
+    e->nac_p = (uint8_t) mm->accuracy.nac_p; e->nac_v = (uint8_t) mm->accuracy.nac_v; e->sil = (uint8_t) mm->accuracy.sil;
+    e->sil_type = (uint8_t) mm->accuracy.sil_type; e->gva = (uint8_t) mm->accuracy.gva; e->sda = (uint8_t) mm->accuracy.sda;
+    e->ops_version = (uint8_t) mm->opstatus.version; e->ops_tah = (uint8_t) mm->opstatus.tah; e->ops_hrd = (uint8_t) mm->opstatus.hrd;
+    e->ops_cc_tc = (uint8_t) mm->opstatus.cc_tc; e->ops_cc_lw = (uint8_t) mm->opstatus.cc_lw;
+    e->ops_cc_antenna_offset = (uint8_t) mm->opstatus.cc_antenna_offset;
+    if (mm->altitude_baro_valid) v |= ADSBCU_ES_ALTITUDE_BARO;
+    if (mm->altitude_geom_valid) v |= ADSBCU_ES_ALTITUDE_GEOM;
+    if (mm->heading_valid) v |= ADSBCU_ES_HEADING;
+    if (mm->gs_valid) v |= ADSBCU_ES_GS;
+    if (mm->ias_valid) v |= ADSBCU_ES_IAS;
+    if (mm->tas_valid) v |= ADSBCU_ES_TAS;
+    if (mm->baro_rate_valid) v |= ADSBCU_ES_BARO_RATE;
+    if (mm->geom_rate_valid) v |= ADSBCU_ES_GEOM_RATE;
+    if (mm->squawk_valid) v |= ADSBCU_ES_SQUAWK;
+    if (mm->callsign_valid) v |= ADSBCU_ES_CALLSIGN;
+    if (mm->cpr_valid) v |= ADSBCU_ES_CPR;
+    if (mm->category_valid) v |= ADSBCU_ES_CATEGORY;
+    if (mm->geom_delta_valid) v |= ADSBCU_ES_GEOM_DELTA;
+    if (mm->spi_valid) v |= ADSBCU_ES_SPI;
+    if (mm->alert_valid) v |= ADSBCU_ES_ALERT;
+    if (mm->emergency_valid) v |= ADSBCU_ES_EMERGENCY;
+    if (mm->accuracy.nic_a_valid) v |= ADSBCU_ES_NIC_A;
+    if (mm->accuracy.nic_b_valid) v |= ADSBCU_ES_NIC_B;
+    if (mm->accuracy.nic_c_valid) v |= ADSBCU_ES_NIC_C;
+    if (mm->accuracy.nic_baro_valid) v |= ADSBCU_ES_NIC_BARO;
+    if (mm->accuracy.nac_p_valid) v |= ADSBCU_ES_NAC_P;
+    if (mm->accuracy.nac_v_valid) v |= ADSBCU_ES_NAC_V;
+    if (mm->accuracy.gva_valid) v |= ADSBCU_ES_GVA;
+    if (mm->accuracy.sda_valid) v |= ADSBCU_ES_SDA;
+    if (mm->nav.heading_valid) v |= ADSBCU_ES_NAV_HEADING;
+    if (mm->nav.fms_altitude_valid) v |= ADSBCU_ES_NAV_FMS_ALTITUDE;
+    if (mm->nav.mcp_altitude_valid) v |= ADSBCU_ES_NAV_MCP_ALTITUDE;
+    if (mm->nav.qnh_valid) v |= ADSBCU_ES_NAV_QNH;
+    if (mm->nav.modes_valid) v |= ADSBCU_ES_NAV_MODES;
+    if (mm->opstatus.valid) v |= ADSBCU_ES_OPSTATUS;
+    if (mm->opstatus.cc_lw_valid) v |= ADSBCU_ES_CC_LW;
+    e->valid = v;
+    if (mm->opstatus.om_acas_ra) o |= ADSBCU_OPS_OM_ACAS_RA;
+    if (mm->opstatus.om_ident) o |= ADSBCU_OPS_OM_IDENT;
+    if (mm->opstatus.om_atc) o |= ADSBCU_OPS_OM_ATC;
+    if (mm->opstatus.om_saf) o |= ADSBCU_OPS_OM_SAF;
+    if (mm->opstatus.cc_acas) o |= ADSBCU_OPS_CC_ACAS;
+    if (mm->opstatus.cc_cdti) o |= ADSBCU_OPS_CC_CDTI;
+    if (mm->opstatus.cc_1090_in) o |= ADSBCU_OPS_CC_1090_IN;
+    if (mm->opstatus.cc_arv) o |= ADSBCU_OPS_CC_ARV;
+    if (mm->opstatus.cc_ts) o |= ADSBCU_OPS_CC_TS;
+    if (mm->opstatus.cc_uat_in) o |= ADSBCU_OPS_CC_UAT_IN;
+    if (mm->opstatus.cc_poa) o |= ADSBCU_OPS_CC_POA;
+    if (mm->opstatus.cc_b2_low) o |= ADSBCU_OPS_CC_B2_LOW;
+    e->ops_flags = (uint16_t) o;
+}
+
+int __wrap_main(int argc, char **argv)
+{
+    const char *in = getenv("REF1090_DECODE_IN"), *out = getenv("REF1090_DECODE_OUT");
+    if (!in || !out || !*in || !*out) return __real_main(argc, argv);
+    FILE *fi = fopen(in, "rb"), *fo = fopen(out, "wb");
+    if (!fi || !fo) { fprintf(stderr, "ref decode tap: cannot open files\n"); return 2; }
+    modesChecksumInit(1);            /* what modesInit() does for the decoder (dump1090.c:206-208) */
+    icaoFilterInit();
+    modeACInit();
+    unsigned char frame[14];
+    while (fread(frame, 1, 14, fi) == 14) {
+        struct modesMessage mm;
+        adsbcu_fields_es e;
+        int32_t rc;
+        memset(&mm, 0, sizeof(mm));  /* demod_2400.c:355 */
+        mm.score = scoreModesMessage(frame);
+        rc = decodeModesMessage(&mm, frame);
+        if (rc < 0) memset(&e, 0, sizeof(e)); else es_record(&mm, &e);
+        fwrite(&e, sizeof(e), 1, fo);
+        fwrite(&rc, sizeof(rc), 1, fo);
+    }
+    fclose(fi); fclose(fo);
+    return 0;
 }

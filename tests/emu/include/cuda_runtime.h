@@ -199,6 +199,7 @@ static inline double __dsub_rn(double a, double b) { volatile double r = a - b; 
 static inline double __dmul_rn(double a, double b) { volatile double r = a * b; return r; }
 static inline double __ddiv_rn(double a, double b) { volatile double r = a / b; return r; }
 static inline double __dsqrt_rn(double a) { return sqrt(a); }
+static inline float __double2float_rn(double a) { volatile float r = float(a); return r; }
 static inline unsigned __float2uint_rz(float x) { return x <= 0.f ? 0u : x >= 4294967296.f ? 0xFFFFFFFFu : unsigned(x); }
 static inline int __float2int_rz(float x) { return int(x); }
 static inline int __float2int_rn(float x) { return int(nearbyintf(x)); }

@@ -36,3 +36,9 @@ def test_emulated_resolve_kernel_small_batches_and_sequential_replay():
 def test_emulated_filter_expiry_and_static_scratch():
     out = run_selection(["tests/test_gpu_parity.py", "tests/test_zz_no_alloc.py", "-k", "expiry or static_scratch"])
     assert " passed" in out
+
+
+def test_emulated_es_payload_decode_matches_reference_fixture():
+    """fields_es_kernel's source against what the reference binary's decodeModesMessage produced (tests/golden/fields_es.npz)."""
+    out = run_selection(["tests/test_fields_es.py", "-k", "gpu_es_equals_reference_fixture"])
+    assert " passed" in out
