@@ -355,6 +355,37 @@ typedef struct adsbcu_fields_es {
 /* HOST arrays of n records; the decode runs on the handle's device (one thread per message). */
 int adsbcu_1090_decode_es(adsbcu_handle *h, const adsbcu_msg *msgs, size_t n, adsbcu_fields_es *out);
 
+/* ---- Path A, next layer: the Comm-B payload of DF20 / DF21 (third part) -----------------------
+ * Replaces decodeCommB (comm_b.c:50-86) and its ten register decoders (comm_b.c:88-985): the MB field is scored as
+ * an empty response, BDS 1,0 / 2,0 / 3,0 / 1,7 / 4,0 / 5,0 / 6,0 / 4,4 / 0,5 in the reference's order, the single
+ * best-scoring interpretation is decoded, a tie gives COMMB_AMBIGUOUS, no positive score COMMB_UNKNOWN, and replies
+ * with DR != 0 or repaired bits are COMMB_NOT_DECODED.  (The reference also tests UM, but decodeModesMessage fills
+ * UM in only after it has called decodeCommB - mode_s.c:731-734 against :757-760 - so that test never fires; the
+ * same here.)  One record per message, zeroed with commb_format = 0 for other downlink formats.  commb_format carries
+ * commb_format_t (dump1090.h:203-217); valid is the OR of ADSBCU_MB_*.  Floats are the reference's expressions
+ * narrowed as it narrows them (mach: the float the reference widens into its double member).
+ * Pinned against the reference binary's own decodeModesMessage (oracle/ref_harness.c, third tap;
+ * tests/golden/fields_mb.npz). */
+enum {
+    ADSBCU_MB_CALLSIGN = 1u << 0,   ADSBCU_MB_ROLL = 1u << 1,        ADSBCU_MB_HEADING = 1u << 2,      ADSBCU_MB_GS = 1u << 3,
+    ADSBCU_MB_TRACK_RATE = 1u << 4, ADSBCU_MB_TAS = 1u << 5,         ADSBCU_MB_IAS = 1u << 6,          ADSBCU_MB_MACH = 1u << 7,
+    ADSBCU_MB_BARO_RATE = 1u << 8,  ADSBCU_MB_GEOM_RATE = 1u << 9,   ADSBCU_MB_NAV_MCP_ALTITUDE = 1u << 10, ADSBCU_MB_NAV_FMS_ALTITUDE = 1u << 11,
+    ADSBCU_MB_NAV_QNH = 1u << 12,   ADSBCU_MB_NAV_MODES = 1u << 13,  ADSBCU_MB_MRAR_SOURCE = 1u << 14, ADSBCU_MB_WIND = 1u << 15,
+    ADSBCU_MB_TEMPERATURE = 1u << 16, ADSBCU_MB_PRESSURE = 1u << 17, ADSBCU_MB_TURBULENCE = 1u << 18,  ADSBCU_MB_HUMIDITY = 1u << 19
+};
+typedef struct adsbcu_fields_commb {
+    uint32_t valid;              /* ADSBCU_MB_* */
+    uint8_t  commb_format, heading_type, nav_modes, nav_altitude_source;
+    uint8_t  mrar_source, turbulence, reserved[2];
+    char     callsign[8];
+    float    roll, heading, track_rate, gs, mach, nav_qnh;
+    float    wind_speed, wind_dir, temperature, pressure, humidity;
+    int32_t  baro_rate, geom_rate, nav_mcp_altitude, nav_fms_altitude;
+    uint16_t ias, tas;
+} adsbcu_fields_commb;           /* 84 bytes */
+/* HOST arrays of n records; the decode runs on the handle's device (one thread per message). */
+int adsbcu_1090_decode_commb(adsbcu_handle *h, const adsbcu_msg *msgs, size_t n, adsbcu_fields_commb *out);
+
 /* ---- Wire formats of the decoded set ---------------------------------------------
  * Host-side formatting of adsbcu_msg records exactly as dump1090's network outputs write them; no handle, no GPU.
  *   adsbcu_1090_encode_beast   writeBeastMessage (net_io.c:440-487) per message.  verbatim != 0: the bytes as sliced,

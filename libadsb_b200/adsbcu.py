@@ -35,6 +35,14 @@ FIELDS_ES_DTYPE = np.dtype([("addr", "<u4"), ("valid", "<u4")] + [(k, "u1") for 
         "nic_a", "nic_b", "nic_c", "nic_baro", "nac_p", "nac_v", "sil", "sil_type", "gva", "sda",
         "ops_version", "ops_tah", "ops_hrd", "ops_cc_tc", "ops_cc_lw", "ops_cc_antenna_offset")])
 assert FIELDS_ES_DTYPE.itemsize == 120
+# adsbcu_fields_commb; valid bits ADSBCU_MB_*
+FIELDS_MB_DTYPE = np.dtype([("valid", "<u4")] + [(k, "u1") for k in (
+    "commb_format", "heading_type", "nav_modes", "nav_altitude_source", "mrar_source", "turbulence")] + [("reserved", "u1", 2), ("callsign", "S8")] +
+    [(k, "<f4") for k in ("roll", "heading", "track_rate", "gs", "mach", "nav_qnh", "wind_speed", "wind_dir", "temperature", "pressure", "humidity")] +
+    [(k, "<i4") for k in ("baro_rate", "geom_rate", "nav_mcp_altitude", "nav_fms_altitude")] + [("ias", "<u2"), ("tas", "<u2")])
+assert FIELDS_MB_DTYPE.itemsize == 84
+COMMB_FORMATS = ("unknown", "ambiguous", "not_decoded", "empty_response", "datalink_caps", "gicb_caps", "aircraft_ident", "acas_ra",
+                 "vertical_intent", "track_turn", "heading_speed", "mrar", "airborne_position")
 ES_VALID = {name: 1 << k for k, name in enumerate((
     "altitude_baro", "altitude_geom", "heading", "gs", "ias", "tas", "baro_rate", "geom_rate", "squawk", "callsign", "cpr", "category",
     "geom_delta", "spi", "alert", "emergency", "nic_a", "nic_b", "nic_c", "nic_baro", "nac_p", "nac_v", "gva", "sda", "nav_heading",
@@ -69,7 +77,7 @@ EXPORTS = ["adsbcu_abi_version", "adsbcu_last_error", "adsbcu_create", "adsbcu_d
            "adsbcu_1090_filter_test", "adsbcu_1090_filter_expire", "adsbcu_get_stats", "adsbcu_1090b_feed", "adsbcu_1090b_reset",
            "adsbcu_978_feed", "adsbcu_978_feed_device", "adsbcu_978_get_stats", "adsbcu_978_reset", "adsbcu_978_phase", "adsbcu_1090_seek", "adsbcu_1090_scan_candidates",
            "adsbcu_1090_known_export", "adsbcu_1090_known_import", "adsbcu_1090_revive", "adsbcu_1090_resolve", "adsbcu_1090_modeac_block", "adsbcu_1090_feed_sc16",
-           "adsbcu_1090_modeac_block_static", "adsbcu_1090_decode_fields", "adsbcu_1090_decode_es", "adsbcu_1090_encode_beast", "adsbcu_1090_encode_avr", "adsbcu_1090_state_export", "adsbcu_1090_state_import", "adsbcu_1090_replay_sharded", "adsbcu_1090_replay_sharded_tail",
+           "adsbcu_1090_modeac_block_static", "adsbcu_1090_decode_fields", "adsbcu_1090_decode_es", "adsbcu_1090_decode_commb", "adsbcu_1090_encode_beast", "adsbcu_1090_encode_avr", "adsbcu_1090_state_export", "adsbcu_1090_state_import", "adsbcu_1090_replay_sharded", "adsbcu_1090_replay_sharded_tail",
            "adsbcu_1090b_decode_fields", "adsbcu_1090b_cpr_decode", "adsbcu_1090_cpr_decode"]
 
 
@@ -155,6 +163,7 @@ def load():
         L.adsbcu_1090_feed_sc16.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.adsbcu_1090_decode_fields.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         L.adsbcu_1090_decode_es.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.adsbcu_1090_decode_commb.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         L.adsbcu_1090_encode_beast.restype = C.c_size_t
         L.adsbcu_1090_encode_beast.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t]
         L.adsbcu_1090_encode_avr.restype = C.c_size_t
@@ -274,6 +283,13 @@ class Demod1090:
         msgs = np.ascontiguousarray(msgs, dtype=MSG_DTYPE)
         out = np.zeros(len(msgs), dtype=FIELDS_ES_DTYPE)
         self._check(load().adsbcu_1090_decode_es(self.h, msgs.ctypes.data, len(msgs), out.ctypes.data))
+        return out
+
+    def decode_commb(self, msgs: np.ndarray) -> np.ndarray:
+        """dump1090's Comm-B payload decode (decodeCommB, comm_b.c:50-985) of every MSG_DTYPE record (zeroed unless DF20 / DF21)."""
+        msgs = np.ascontiguousarray(msgs, dtype=MSG_DTYPE)
+        out = np.zeros(len(msgs), dtype=FIELDS_MB_DTYPE)
+        self._check(load().adsbcu_1090_decode_commb(self.h, msgs.ctypes.data, len(msgs), out.ctypes.data))
         return out
 
     def cpr_decode_a(self, rec: np.ndarray) -> np.ndarray:

@@ -976,6 +976,16 @@ int adsbcu_1090_decode_es(adsbcu_handle *h, const adsbcu_msg *msgs, size_t n, ad
     return fields_es_decode(h->fields, h->stream, msgs, n, out, h->error);
 }
 
+int adsbcu_1090_decode_commb(adsbcu_handle *h, const adsbcu_msg *msgs, size_t n, adsbcu_fields_commb *out)
+{
+    if (!h) return ADSBCU_ERR_ARG;
+    NEED_DEVICE(h);
+    if (n && (!msgs || !out)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
+    if (n > (size_t(1) << 24)) { h->error = "bad argument (more than 2^24 records in one call)"; return ADSBCU_ERR_ARG; }
+    CK(cudaSetDevice(h->device));
+    return fields_commb_decode(h->fields, h->stream, msgs, n, out, h->error);
+}
+
 int adsbcu_978_feed(adsbcu_handle *h, const uint8_t *iq, size_t nbytes, adsbcu_uat_frame *out, size_t cap, size_t *n_out)
 {
     if (!h) return ADSBCU_ERR_ARG;

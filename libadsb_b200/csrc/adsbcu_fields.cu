@@ -502,6 +502,7 @@ struct MeBits {
     uint64_t v;                                                                // ME bit 1 is bit 55
     __device__ __forceinline__ uint32_t operator()(int first, int last) const { return uint32_t(v >> (56 - last)) & ((1u << (last - first + 1)) - 1u); }
     __device__ __forceinline__ uint32_t operator()(int bit) const { return uint32_t(v >> (56 - bit)) & 1u; }
+    __device__ __forceinline__ uint64_t wide(int first, int last) const { return (v >> (56 - last)) & ((1ull << (last - first + 1)) - 1ull); }   // fields of 32 bits and more
 };
 
 __device__ __forceinline__ void non_icao(adsbcu_fields_es &e)                  // setIMF (mode_s.c:832-854)
@@ -817,6 +818,307 @@ int fields_es_decode(Fields *&f, cudaStream_t s, const adsbcu_msg *msgs, size_t 
     if ((e = cudaGetLastError()) != cudaSuccess) return fail(err, "fields_es_kernel", e);
     if ((e = cudaMemcpyAsync(out, f->d_out, n * sizeof(adsbcu_fields_es), cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(err, "D2H(es)", e);
     if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail(err, "es sync", e);
+    return ADSBCU_OK;
+}
+
+// ---- Path A: Comm-B payload of DF20 / DF21 (decodeCommB and its register decoders, comm_b.c:50-985) ----------------------
+// One thread per reply.  The reference walks ten scoring functions twice (score, then store); here every register's
+// plausibility score is computed once from the 56 MB bits in a 64-bit register, the unique maximum picks the register, and
+// only that one is decoded into the record.  Records are staged in shared memory like the ES decoder's.
+namespace {
+
+enum : uint8_t { kCbUnknown = 0, kCbAmbiguous = 1, kCbNotDecoded = 2, kCbEmpty = 3, kCbDatalinkCaps = 4, kCbGicbCaps = 5, kCbIdent = 6, kCbAcasRa = 7,
+                 kCbVerticalIntent = 8, kCbTrackTurn = 9, kCbHeadingSpeed = 10, kCbMrar = 11, kCbAirbornePosition = 12 };   // commb_format_t
+
+// 0 = not this register.  `in range or out` helpers keep the scoring tables readable.
+__device__ __forceinline__ bool within(uint32_t v, uint32_t lo, uint32_t hi) { return v >= lo && v <= hi; }
+
+__device__ __forceinline__ int score_caps17(const MeBits &mb)                    // BDS 1,7 (comm_b.c:153-234)
+{
+    if (mb.wide(25, 56) != 0) return 0;
+    const uint32_t caps = mb(1, 24);                                           // capability bit k is bit (24 - k)
+    auto has = [caps](int k) { return (caps >> (24 - k)) & 1u; };
+    int score = has(7) ? 1 : -2;
+    score -= 2 * int(has(10) + has(11) + has(12) + has(20) + has(21) + has(22)) + int(has(13) + has(14));
+    const uint32_t es = caps >> 18;                                            // bits 1..6: the extended-squitter registers
+    if ((es >> 1) == 0x1F) score += 5 + int(es & 1);
+    else if (es == 0) score += 1;
+    else if ((es >> 1) == 0x07) score += 3;
+    else score -= 12;
+    if (has(16) && has(24)) score += 2 + int(has(9));
+    else if (!has(16) && !has(24) && !has(9)) score += 1;
+    else score -= 6;
+    return score;
+}
+
+__device__ __forceinline__ int score_ident20(const MeBits &mb, bool *usable)    // BDS 2,0 (comm_b.c:237-281)
+{
+    if (mb(1, 8) != 0x20) return 0;
+    int score = 8;
+    bool all_real = true;
+    for (int k = 0; k < 8; ++k) {
+        const uint32_t six = mb(9 + 6 * k, 14 + 6 * k);
+        const bool letter = six >= 1 && six <= 26, digit = six >= 48 && six <= 57, space = six == 32;
+        if (letter || digit || space) score += 6;
+        else if (six == 0) all_real = false;                                   // '@' padding: still BDS 2,0, callsign not used
+        else return 0;
+    }
+    *usable = all_real;
+    return score;
+}
+
+// an optional field of BDS 4,0 / 5,0 / 6,0: status bit set and value plausible -> `gain`; status clear and field zero -> 1; else reject (-1)
+__device__ __forceinline__ int field_score(bool status, bool nonzero, bool plausible, int gain)
+{
+    if (status && nonzero) return plausible ? gain : -1;
+    if (!status && !nonzero) return 1;
+    return -1;
+}
+
+struct Bds40 { uint32_t mcp_alt, fms_alt; float qnh; };
+
+__device__ __forceinline__ int score_intent40(const MeBits &mb, Bds40 &d)       // BDS 4,0 (comm_b.c:302-465)
+{
+    const bool mcp_on = mb(1), fms_on = mb(14), baro_on = mb(27), mode_on = mb(48), source_on = mb(54);
+    if (!mcp_on && !fms_on && !baro_on && !mode_on && !source_on) return 0;
+    const uint32_t mcp_raw = mb(2, 13), fms_raw = mb(15, 26), baro_raw = mb(28, 39);
+    d.mcp_alt = mcp_on ? mcp_raw * 16 : 0;
+    d.fms_alt = fms_on ? fms_raw * 16 : 0;
+    // float baro_setting = 800 + baro_raw * 0.1
+    d.qnh = (baro_on && baro_raw) ? __double2float_rn(__dadd_rn(800.0, __dmul_rn(double(baro_raw), 0.1))) : 0.f;
+    const int s_mcp = field_score(mcp_on, mcp_raw != 0, within(mcp_raw * 16, 1000, 50000), 13);
+    const int s_fms = field_score(fms_on, fms_raw != 0, within(fms_raw * 16, 1000, 50000), 13);
+    const int s_baro = field_score(baro_on, baro_raw != 0, d.qnh >= 900.f && d.qnh <= 1100.f, 13);
+    const int s_mode = mode_on ? 4 : mb(49, 51) == 0 ? 1 : -1;
+    const int s_source = source_on ? 3 : mb(55, 56) == 0 ? 1 : -1;
+    if (s_mcp < 0 || s_fms < 0 || s_baro < 0 || s_mode < 0 || s_source < 0 || mb(40, 47) != 0 || mb(52, 53) != 0) return 0;
+    int score = s_mcp + s_fms + s_baro + s_mode + s_source;
+    auto off_grid = [](uint32_t alt) { const uint32_t r = alt % 500; return !(r < 16 || r > 484); };   // selected altitudes are multiples of 500 ft
+    if (mcp_on && fms_on && d.mcp_alt != d.fms_alt) score -= 4;
+    if (mcp_on && off_grid(d.mcp_alt)) score -= 4;
+    if (fms_on && off_grid(d.fms_alt)) score -= 4;
+    return score;
+}
+
+struct Bds50 { float roll, track, track_rate; uint32_t gs, tas; bool rate_on; };
+
+__device__ __forceinline__ int score_track50(const MeBits &mb, Bds50 &d)        // BDS 5,0 (comm_b.c:468-623)
+{
+    if (!mb(1) || !mb(12) || !mb(24) || !mb(46)) return 0;                     // roll, track, ground speed and TAS must all be there
+    // all of these are exact in float: k * 45/256 - 90, k * 90/512 + 180, k * 8/256 - 16
+    d.roll = float(mb(3, 11)) * (45.f / 256.f) - (mb(2) ? 90.f : 0.f);
+    d.track = float(mb(14, 23)) * (90.f / 512.f) + (mb(13) ? 180.f : 0.f);
+    d.gs = mb(25, 34) * 2;
+    d.tas = mb(47, 56) * 2;
+    d.rate_on = mb(35);
+    d.track_rate = d.rate_on ? float(mb(37, 45)) * (8.f / 256.f) - (mb(36) ? 16.f : 0.f) : 0.f;
+    if (!(d.roll >= -40.f && d.roll < 40.f) || !within(d.gs, 50, 700) || !within(d.tas, 50, 700)) return 0;
+    int score = 11 + 12 + 11 + 11;
+    if (d.rate_on) {
+        if (!(d.track_rate >= -10.f && d.track_rate <= 10.f)) return 0;
+        score += 11;
+        // the turn rate the bank angle implies at this airspeed against the reported one (comm_b.c:584-590); the reference's
+        // ground speed / airspeed consistency test two lines earlier compares the status bits and never fires
+        const double implied = __ddiv_rn(__dmul_rn(68625.0, tan(__ddiv_rn(__dmul_rn(double(d.roll), 3.14159265358979323846), 180.0))),
+                                         __dmul_rn(double(d.tas * 20), 3.14159265358979323846));
+        if (fabs(__dsub_rn(implied, double(d.track_rate))) > 2.0) score -= 6;
+    } else {
+        if (mb(36, 45) != 0) return 0;
+        score += 1;
+    }
+    return score;
+}
+
+struct Bds60 { float heading, mach; uint32_t ias; int baro_rate, ins_rate; bool baro_on, ins_on; };
+
+__device__ __forceinline__ int score_speed60(const MeBits &mb, Bds60 &d)        // BDS 6,0 (comm_b.c:626-775)
+{
+    d.baro_on = mb(35);
+    d.ins_on = mb(46);
+    if (!mb(1) || !mb(13) || !mb(24) || (!d.baro_on && !d.ins_on)) return 0;
+    d.heading = float(mb(3, 12)) * (90.f / 512.f) + (mb(2) ? 180.f : 0.f);
+    d.ias = mb(14, 23);
+    const uint32_t mach_raw = mb(25, 34);
+    d.mach = __double2float_rn(__ddiv_rn(__dmul_rn(double(mach_raw), 2.048), 512.0));      // float mach = mach_raw * 2.048 / 512
+    if (!within(d.ias, 50, 700) || mach_raw == 0 || !(double(d.mach) >= 0.1 && double(d.mach) <= 0.9)) return 0;
+    int score = 12 + 11 + 11;
+    d.baro_rate = d.ins_rate = 0;
+    if (d.baro_on) {
+        d.baro_rate = int(mb(37, 45)) * 32 - (mb(36) ? 16384 : 0);
+        if (d.baro_rate < -6000 || d.baro_rate > 6000) return 0;
+        score += 11;
+    } else {
+        if (mb(37, 45) != 0) return 0;
+        score += 1;
+    }
+    if (d.ins_on) {
+        d.ins_rate = int(mb(48, 56)) * 32 - (mb(47) ? 16384 : 0);
+        if (d.ins_rate < -6000 || d.ins_rate > 6000) return 0;
+        score += 11;
+    } else {
+        if (mb(48, 56) != 0) return 0;
+        score += 1;
+    }
+    if (d.baro_on && d.ins_on && abs(d.baro_rate - d.ins_rate) > 2000) score -= 12;
+    return score;
+}
+
+__device__ __forceinline__ int score_mrar44(const MeBits &mb)                    // BDS 4,4 (comm_b.c:778-937)
+{
+    const uint32_t source = mb(1, 4), wind = mb(6, 14), asp = mb(36, 46);
+    if (source == 0 || source >= 5 || !mb(5) || !mb(24)) return 0;             // wind and temperature are in every real report
+    if ((!mb(35) && asp) || (!mb(47) && mb(48, 49)) || (!mb(50) && mb(51, 56))) return 0;
+    const int quarter_deg = int(mb(26, 34)) - (mb(25) ? 512 : 0);              // static air temperature in units of 0.25 C
+    int score;
+    if (wind == 0) score = 2; else if (wind <= 250) score = 19; else return 0;
+    if (quarter_deg == 0) score += 2; else if (quarter_deg >= -320 && quarter_deg <= 240) score += 11; else return 0;
+    if (mb(35)) { if (!within(asp, 25, 1100)) return 0; score += 12; } else score += 1;
+    score += (mb(47) ? 3 : 1) + (mb(50) ? 7 : 1);
+    return source == 3 ? 1 : score;                                            // DME/DME look-alikes of a capability report: last resort
+}
+
+__device__ __forceinline__ int score_position05(const MeBits &mb, int df, uint32_t ac13)   // BDS 0,5 (comm_b.c:944-985)
+{
+    const uint32_t tc = mb(1, 5), ac12 = mb(9, 20);
+    if (df != 20 || tc < 9 || tc > 18 || mb(21) || !ac12) return 0;
+    if (ac13 != (((ac12 & 0x0FC0) << 1) | (ac12 & 0x003F))) return 0;          // must repeat the altitude of the reply around it
+    return (mb(23, 39) == 0 || mb(40, 56) == 0) ? 0 : 100;
+}
+
+__device__ void commb_decode_one(const uint8_t *m, int df, int corrected, adsbcu_fields_commb &o)
+{
+    memset(&o, 0, sizeof(o));
+    if (df != 20 && df != 21) return;
+    MeBits mb;
+    mb.v = 0;
+    for (int i = 0; i < 7; ++i) mb.v = (mb.v << 8) | m[4 + i];
+    // DR is bits 9-13 of the reply; the reference's UM test reads a field it has not filled in yet (mode_s.c:731-734 vs :757-760)
+    const uint32_t dr = (uint32_t(m[1]) >> 3) & 0x1Fu;
+    if (dr != 0 || corrected > 0) { o.commb_format = kCbNotDecoded; return; }
+    const uint32_t ac13 = df == 20 ? (((uint32_t(m[2]) << 8) | m[3]) & 0x1FFFu) : 0u;
+    const uint32_t bds = mb(1, 8);
+    bool callsign_usable = false;
+    Bds40 d40;
+    Bds50 d50;
+    Bds60 d60;
+    int score[10];                                                             // the reference's order: a later equal score is a tie
+    score[0] = ((bds == 0x00 || bds == 0x40 || bds == 0x50 || bds == 0x60) && mb.wide(9, 56) == 0) ? 56 : 0;      // empty response (comm_b.c:88-126)
+    score[1] = (bds == 0x10 && mb(10, 14) == 0) ? 56 : 0;                      // BDS 1,0 (comm_b.c:129-150)
+    score[2] = score_ident20(mb, &callsign_usable);
+    score[3] = bds == 0x30 ? 56 : 0;                                           // BDS 3,0 (comm_b.c:284-299)
+    score[4] = score_caps17(mb);
+    score[5] = score_intent40(mb, d40);
+    score[6] = score_track50(mb, d50);
+    score[7] = score_speed60(mb, d60);
+    score[8] = score_mrar44(mb);
+    score[9] = score_position05(mb, df, ac13);
+    int best = 0, winner = -1;
+    bool tie = false;
+#pragma unroll
+    for (int k = 0; k < 10; ++k) {
+        if (score[k] > best) { best = score[k]; winner = k; tie = false; }
+        else if (score[k] == best) tie = true;
+    }
+    if (winner < 0) { o.commb_format = kCbUnknown; return; }
+    if (tie) { o.commb_format = kCbAmbiguous; return; }
+    uint32_t valid = 0;
+    switch (winner) {
+    case 0: o.commb_format = kCbEmpty; break;
+    case 1: o.commb_format = kCbDatalinkCaps; break;
+    case 2:
+        o.commb_format = kCbIdent;
+        if (callsign_usable) {
+            valid |= ADSBCU_MB_CALLSIGN;
+            for (int k = 0; k < 8; ++k) { const uint32_t six = mb(9 + 6 * k, 14 + 6 * k); o.callsign[k] = char(six < 32 ? 0x40 + six : six); }
+        }
+        break;
+    case 3: o.commb_format = kCbAcasRa; break;
+    case 4: o.commb_format = kCbGicbCaps; break;
+    case 5: {
+        o.commb_format = kCbVerticalIntent;
+        if (mb(1)) { valid |= ADSBCU_MB_NAV_MCP_ALTITUDE; o.nav_mcp_altitude = int(d40.mcp_alt); }
+        if (mb(14)) { valid |= ADSBCU_MB_NAV_FMS_ALTITUDE; o.nav_fms_altitude = int(d40.fms_alt); }
+        if (mb(27)) { valid |= ADSBCU_MB_NAV_QNH; o.nav_qnh = d40.qnh; }
+        if (mb(48)) {
+            const uint32_t mode = mb(49, 51);
+            valid |= ADSBCU_MB_NAV_MODES;
+            o.nav_modes = uint8_t(((mode & 4) ? kNavVnav : 0) | ((mode & 2) ? kNavAltHold : 0) | ((mode & 1) ? kNavApproach : 0));
+        }
+        o.nav_altitude_source = mb(54) ? uint8_t(1 + mb(55, 56)) : 0;          // NAV_ALT_UNKNOWN / AIRCRAFT / MCP / FMS are 1..4
+        break;
+    }
+    case 6:
+        o.commb_format = kCbTrackTurn;
+        valid |= ADSBCU_MB_ROLL | ADSBCU_MB_HEADING | ADSBCU_MB_GS | ADSBCU_MB_TAS;
+        o.roll = d50.roll;
+        o.heading = d50.track;
+        o.heading_type = kHdgGroundTrack;
+        o.gs = float(d50.gs);
+        o.tas = uint16_t(d50.tas);
+        if (d50.rate_on) { valid |= ADSBCU_MB_TRACK_RATE; o.track_rate = d50.track_rate; }
+        break;
+    case 7:
+        o.commb_format = kCbHeadingSpeed;
+        valid |= ADSBCU_MB_HEADING | ADSBCU_MB_IAS | ADSBCU_MB_MACH;
+        o.heading = d60.heading;
+        o.heading_type = kHdgMagnetic;
+        o.ias = uint16_t(d60.ias);
+        o.mach = d60.mach;
+        if (d60.baro_on) { valid |= ADSBCU_MB_BARO_RATE; o.baro_rate = d60.baro_rate; }
+        if (d60.ins_on) { valid |= ADSBCU_MB_GEOM_RATE; o.geom_rate = d60.ins_rate; }       // inertial rate is filed as the geometric one
+        break;
+    case 8:
+        o.commb_format = kCbMrar;
+        valid |= ADSBCU_MB_MRAR_SOURCE | ADSBCU_MB_WIND | ADSBCU_MB_TEMPERATURE;
+        o.mrar_source = uint8_t(mb(1, 4));
+        o.wind_speed = float(mb(6, 14));
+        o.wind_dir = float(mb(15, 23)) * (180.f / 256.f);
+        o.temperature = float(int(mb(26, 34)) - (mb(25) ? 512 : 0)) * 0.25f;
+        if (mb(35)) { valid |= ADSBCU_MB_PRESSURE; o.pressure = float(mb(36, 46)); }
+        if (mb(47)) { valid |= ADSBCU_MB_TURBULENCE; o.turbulence = uint8_t(mb(48, 49)); }
+        if (mb(50)) { valid |= ADSBCU_MB_HUMIDITY; o.humidity = float(mb(51, 56)) * (100.f / 64.f); }
+        break;
+    default: o.commb_format = kCbAirbornePosition; break;                      // recognised only, never used as a position
+    }
+    o.valid = valid;
+}
+
+__global__ void __launch_bounds__(kEsThreads) fields_commb_kernel(const uint32_t *msgs, uint32_t n, uint32_t *out)
+{
+    constexpr uint32_t kInWords = sizeof(adsbcu_msg) / 4, kOutWords = sizeof(adsbcu_fields_commb) / 4;
+    __shared__ uint32_t s_in[kEsThreads * kInWords];
+    __shared__ uint32_t s_out[kEsThreads * kOutWords];
+    const uint32_t first = blockIdx.x * kEsThreads;
+    const uint32_t count = min(uint32_t(kEsThreads), n - first);
+    for (uint32_t w = threadIdx.x; w < count * kInWords; w += kEsThreads) s_in[w] = msgs[size_t(first) * kInWords + w];
+    __syncthreads();
+    if (threadIdx.x < count) {
+        const uint8_t *rec = reinterpret_cast<const uint8_t *>(s_in + threadIdx.x * kInWords);
+        adsbcu_fields_commb o;
+        commb_decode_one(rec + 8, rec[8 + 14 + 14 + 2], rec[8 + 14 + 14 + 1], o);
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(&o);
+        for (uint32_t w = 0; w < kOutWords; ++w) s_out[threadIdx.x * kOutWords + w] = src[w];
+    }
+    __syncthreads();
+    for (uint32_t w = threadIdx.x; w < count * kOutWords; w += kEsThreads) out[size_t(first) * kOutWords + w] = s_out[w];
+}
+
+}  // namespace
+
+int fields_commb_decode(Fields *&f, cudaStream_t s, const adsbcu_msg *msgs, size_t n, adsbcu_fields_commb *out, std::string &err)
+{
+    static_assert(sizeof(adsbcu_fields_commb) == 84 && sizeof(adsbcu_msg) == 56, "record layout");
+    if (!f) f = new Fields();
+    if (!n) return ADSBCU_OK;
+    cudaError_t e;
+    if (!grow(f->d_in, f->cap_in, n * sizeof(adsbcu_msg)) || !grow(f->d_out, f->cap_out, n * sizeof(adsbcu_fields_commb)))
+        return fail(err, "cudaMalloc(fields)", cudaGetLastError());
+    if ((e = cudaMemcpyAsync(f->d_in, msgs, n * sizeof(adsbcu_msg), cudaMemcpyHostToDevice, s)) != cudaSuccess) return fail(err, "H2D(commb)", e);
+    ADSBCU_LAUNCH(fields_commb_kernel, unsigned((n + kEsThreads - 1) / kEsThreads), kEsThreads, 0, s, static_cast<const uint32_t *>(f->d_in),
+                  uint32_t(n), static_cast<uint32_t *>(f->d_out));
+    if ((e = cudaGetLastError()) != cudaSuccess) return fail(err, "fields_commb_kernel", e);
+    if ((e = cudaMemcpyAsync(out, f->d_out, n * sizeof(adsbcu_fields_commb), cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(err, "D2H(commb)", e);
+    if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail(err, "commb sync", e);
     return ADSBCU_OK;
 }
 

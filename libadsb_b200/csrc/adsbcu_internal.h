@@ -300,6 +300,7 @@ struct adsbcu_cpr_in;
 struct adsbcu_cpr_out;
 struct adsbcu_fields_a;
 struct adsbcu_fields_es;
+struct adsbcu_fields_commb;
 namespace adsbcu {
 // Path B, next layer (adsbcu_fields.cu): bulk field decode and CPR
 struct Fields;
@@ -308,6 +309,7 @@ int  cpr_decode(Fields *&f, cudaStream_t s, const adsbcu_cpr_pair *pairs, size_t
 int  cpr_a_decode(Fields *&f, cudaStream_t s, const adsbcu_cpr_in *in, size_t n, adsbcu_cpr_out *out, std::string &err);
 int  fields_a_decode(Fields *&f, cudaStream_t s, const ::adsbcu_msg *msgs, size_t n, ::adsbcu_fields_a *out, std::string &err);
 int  fields_es_decode(Fields *&f, cudaStream_t s, const ::adsbcu_msg *msgs, size_t n, ::adsbcu_fields_es *out, std::string &err);
+int  fields_commb_decode(Fields *&f, cudaStream_t s, const ::adsbcu_msg *msgs, size_t n, ::adsbcu_fields_commb *out, std::string &err);
 void fields_free(Fields *f);
 
 // Path C (adsbcu_uat.cu): 978 MHz UAT

@@ -1141,3 +1141,291 @@ void oracle1090_decode_es_batch(const uint8_t *frames, size_t n, const uint8_t *
     size_t k;
     for (k = 0; k < n; ++k) oracle1090_decode_es(frames + 14 * k, frames[14 * k] >> 3, corrected ? corrected[k] : 0, out + k);
 }
+
+/* ---- Comm-B payload of DF20 / DF21 (decodeCommB and its register decoders, comm_b.c:50-985), for adsbcu_1090_decode_commb ----
+ * Pinned against the reference binary's own decodeModesMessage through the third tap of oracle/ref_harness.c
+ * (tests/golden/fields_mb.npz).  Layout == adsbcu_fields_commb. */
+typedef struct oracle_fields_mb {
+    uint32_t valid;
+    uint8_t  commb_format, heading_type, nav_modes, nav_altitude_source, mrar_source, turbulence, reserved[2];
+    char     callsign[8];
+    float    roll, heading, track_rate, gs, mach, nav_qnh, wind_speed, wind_dir, temperature, pressure, humidity;
+    int32_t  baro_rate, geom_rate, nav_mcp_altitude, nav_fms_altitude;
+    uint16_t ias, tas;
+} oracle_fields_mb;
+
+enum { B_CALLSIGN = 1u << 0, B_ROLL = 1u << 1, B_HEADING = 1u << 2, B_GS = 1u << 3, B_TRACK_RATE = 1u << 4, B_TAS = 1u << 5, B_IAS = 1u << 6,
+       B_MACH = 1u << 7, B_BARO_RATE = 1u << 8, B_GEOM_RATE = 1u << 9, B_NAV_MCP = 1u << 10, B_NAV_FMS = 1u << 11, B_NAV_QNH = 1u << 12,
+       B_NAV_MODES = 1u << 13, B_MRAR_SOURCE = 1u << 14, B_WIND = 1u << 15, B_TEMPERATURE = 1u << 16, B_PRESSURE = 1u << 17,
+       B_TURBULENCE = 1u << 18, B_HUMIDITY = 1u << 19 };
+/* commb_format_t, dump1090.h:203-217 */
+enum { CB_UNKNOWN, CB_AMBIGUOUS, CB_NOT_DECODED, CB_EMPTY_RESPONSE, CB_DATALINK_CAPS, CB_GICB_CAPS, CB_AIRCRAFT_IDENT, CB_ACAS_RA,
+       CB_VERTICAL_INTENT, CB_TRACK_TURN, CB_HEADING_SPEED, CB_MRAR, CB_AIRBORNE_POSITION };
+
+typedef struct mb_ctx { const uint8_t *mb; int df; unsigned ac; } mb_ctx;
+#define MB(a, b) f_getbits(c->mb, (a), (b))
+#define MB1(a) f_getbits(c->mb, (a), (a))
+
+static int mb_empty(const mb_ctx *c, oracle_fields_mb *o)                        /* decodeEmptyResponse, comm_b.c:88-126 */
+{
+    int i;
+    if (c->mb[0] != 0x00 && c->mb[0] != 0x40 && c->mb[0] != 0x50 && c->mb[0] != 0x60) return 0;
+    for (i = 1; i < 7; ++i) if (c->mb[i]) return 0;
+    if (o) o->commb_format = CB_EMPTY_RESPONSE;
+    return 56;
+}
+
+static int mb_bds10(const mb_ctx *c, oracle_fields_mb *o)                        /* comm_b.c:129-150 */
+{
+    if (c->mb[0] != 0x10 || MB(10, 14) != 0) return 0;
+    if (o) o->commb_format = CB_DATALINK_CAPS;
+    return 56;
+}
+
+static int mb_bds17(const mb_ctx *c, oracle_fields_mb *o)                        /* comm_b.c:153-234 */
+{
+    int score = 0;
+    const unsigned es = MB(1, 6);
+    if (MB(25, 56) != 0) return 0;
+    score += MB1(7) ? 1 : -2;
+    if (MB1(10)) score -= 2;
+    if (MB1(11)) score -= 2;
+    if (MB1(12)) score -= 2;
+    if (MB1(13)) score -= 1;
+    if (MB1(14)) score -= 1;
+    if (MB1(20)) score -= 2;
+    if (MB1(21)) score -= 2;
+    if (MB1(22)) score -= 2;
+    if ((es >> 1) == 0x1F) score += 5 + (es & 1 ? 1 : 0);
+    else if (es == 0) score += 1;
+    else if ((es >> 1) == 0x07) score += 3;
+    else score -= 12;
+    if (MB1(16) && MB1(24)) score += 2 + (MB1(9) ? 1 : 0);
+    else if (!MB1(16) && !MB1(24) && !MB1(9)) score += 1;
+    else score -= 6;
+    if (o) o->commb_format = CB_GICB_CAPS;
+    return score;
+}
+
+static int mb_bds20(const mb_ctx *c, oracle_fields_mb *o)                        /* comm_b.c:237-281 */
+{
+    static const char ais[65] = "@ABCDEFGHIJKLMNOPQRSTUVWXYZ[\\]^_ !\"#$%&'()*+,-./0123456789:;<=>?";
+    char cs[8];
+    int score = 8, valid = 1, k;
+    if (c->mb[0] != 0x20) return 0;
+    for (k = 0; k < 8; ++k) cs[k] = ais[MB(9 + 6 * k, 14 + 6 * k)];
+    for (k = 0; k < 8; ++k) {
+        if ((cs[k] >= 'A' && cs[k] <= 'Z') || (cs[k] >= '0' && cs[k] <= '9') || cs[k] == ' ') score += 6;
+        else if (cs[k] == '@') valid = 0;
+        else return 0;
+    }
+    if (o) {
+        o->commb_format = CB_AIRCRAFT_IDENT;
+        if (valid) { memcpy(o->callsign, cs, 8); o->valid |= B_CALLSIGN; }
+    }
+    return score;
+}
+
+static int mb_bds30(const mb_ctx *c, oracle_fields_mb *o)                        /* comm_b.c:284-299 */
+{
+    if (c->mb[0] != 0x30) return 0;
+    if (o) o->commb_format = CB_ACAS_RA;
+    return 56;
+}
+
+static int mb_bds40(const mb_ctx *c, oracle_fields_mb *o)                        /* comm_b.c:302-465 */
+{
+    const unsigned mcp_valid = MB1(1), mcp_raw = MB(2, 13), fms_valid = MB1(14), fms_raw = MB(15, 26), baro_valid = MB1(27), baro_raw = MB(28, 39);
+    const unsigned mode_valid = MB1(48), mode_raw = MB(49, 51), source_valid = MB1(54), source_raw = MB(55, 56);
+    unsigned mcp_alt = 0, fms_alt = 0;
+    float baro = 0;
+    int score = 0;
+    if (!mcp_valid && !fms_valid && !baro_valid && !mode_valid && !source_valid) return 0;
+    if (mcp_valid && mcp_raw != 0) { mcp_alt = mcp_raw * 16; if (mcp_alt >= 1000 && mcp_alt <= 50000) score += 13; else return 0; }
+    else if (!mcp_valid && mcp_raw == 0) score += 1;
+    else return 0;
+    if (fms_valid && fms_raw != 0) { fms_alt = fms_raw * 16; if (fms_alt >= 1000 && fms_alt <= 50000) score += 13; else return 0; }
+    else if (!fms_valid && fms_raw == 0) score += 1;
+    else return 0;
+    if (baro_valid && baro_raw != 0) { baro = 800 + baro_raw * 0.1; if (baro >= 900 && baro <= 1100) score += 13; else return 0; }
+    else if (!baro_valid && baro_raw == 0) score += 1;
+    else return 0;
+    if (MB(40, 47) != 0) return 0;
+    if (mode_valid) score += 4; else if (mode_raw == 0) score += 1; else return 0;
+    if (MB(52, 53) != 0) return 0;
+    if (source_valid) score += 3; else if (source_raw == 0) score += 1; else return 0;
+    if (mcp_valid && fms_valid && mcp_alt != fms_alt) score -= 4;
+    if (mcp_valid) { const unsigned r = mcp_alt % 500; if (!(r < 16 || r > 484)) score -= 4; }
+    if (fms_valid) { const unsigned r = fms_alt % 500; if (!(r < 16 || r > 484)) score -= 4; }
+    if (o) {
+        o->commb_format = CB_VERTICAL_INTENT;
+        if (mcp_valid) { o->valid |= B_NAV_MCP; o->nav_mcp_altitude = (int32_t)mcp_alt; }
+        if (fms_valid) { o->valid |= B_NAV_FMS; o->nav_fms_altitude = (int32_t)fms_alt; }
+        if (baro_valid) { o->valid |= B_NAV_QNH; o->nav_qnh = baro; }
+        if (mode_valid) { o->valid |= B_NAV_MODES; o->nav_modes = (uint8_t)(((mode_raw & 4) ? 2 : 0) | ((mode_raw & 2) ? 4 : 0) | ((mode_raw & 1) ? 8 : 0)); }
+        o->nav_altitude_source = source_valid ? (uint8_t)(source_raw + 1) : 0;    /* UNKNOWN, AIRCRAFT, MCP, FMS == 1..4 */
+    }
+    return score;
+}
+
+static int mb_bds50(const mb_ctx *c, oracle_fields_mb *o)                        /* comm_b.c:468-623 */
+{
+    const unsigned roll_valid = MB1(1), roll_sign = MB1(2), roll_raw = MB(3, 11), track_valid = MB1(12), track_sign = MB1(13), track_raw = MB(14, 23);
+    const unsigned gs_valid = MB1(24), gs_raw = MB(25, 34), rate_valid = MB1(35), rate_sign = MB1(36), rate_raw = MB(37, 45);
+    const unsigned tas_valid = MB1(46), tas_raw = MB(47, 56);
+    float roll, track, track_rate = 0;
+    unsigned gs, tas;
+    int score = 0;
+    if (!roll_valid || !track_valid || !gs_valid || !tas_valid) return 0;
+    roll = roll_raw * 45.0 / 256.0;
+    if (roll_sign) roll -= 90.0;
+    if (roll >= -40 && roll < 40) score += 11; else return 0;
+    score += 12;
+    track = track_raw * 90.0 / 512.0;
+    if (track_sign) track += 180.0;
+    if (gs_raw == 0) return 0;
+    gs = gs_raw * 2;
+    if (gs >= 50 && gs <= 700) score += 11; else return 0;
+    if (rate_valid) {
+        track_rate = rate_raw * 8.0 / 256.0;
+        if (rate_sign) track_rate -= 16;
+        if (track_rate >= -10.0 && track_rate <= 10.0) score += 11; else return 0;
+    } else if (rate_raw == 0 && !rate_sign) score += 1;
+    else return 0;
+    if (tas_raw == 0) return 0;
+    tas = tas_raw * 2;
+    if (tas >= 50 && tas <= 700) score += 11; else return 0;
+    /* comm_b.c:576-581 compares the two VALID bits (always 1 - 1), so its "inconsistent data" penalty never applies */
+    if (rate_valid) {                                                             /* comm_b.c:584-590 */
+        const double turn_rate = 68625 * tan(roll * M_PI / 180.0) / (tas * 20 * M_PI);
+        if (fabs(turn_rate - track_rate) > 2.0) score -= 6;
+    }
+    if (o) {
+        o->commb_format = CB_TRACK_TURN;
+        o->valid |= B_ROLL | B_HEADING | B_GS | B_TAS;
+        o->roll = roll;
+        o->heading = track;
+        o->heading_type = 1;
+        o->gs = gs;
+        if (rate_valid) { o->valid |= B_TRACK_RATE; o->track_rate = track_rate; }
+        o->tas = (uint16_t)tas;
+    }
+    return score;
+}
+
+static int mb_bds60(const mb_ctx *c, oracle_fields_mb *o)                        /* comm_b.c:626-775 */
+{
+    const unsigned hdg_valid = MB1(1), hdg_sign = MB1(2), hdg_raw = MB(3, 12), ias_valid = MB1(13), ias_raw = MB(14, 23);
+    const unsigned mach_valid = MB1(24), mach_raw = MB(25, 34), baro_valid = MB1(35), baro_sign = MB1(36), baro_raw = MB(37, 45);
+    const unsigned ins_valid = MB1(46), ins_sign = MB1(47), ins_raw = MB(48, 56);
+    float heading, mach;
+    int baro_rate = 0, ins_rate = 0, score = 0;
+    if (!hdg_valid || !ias_valid || !mach_valid || (!baro_valid && !ins_valid)) return 0;
+    heading = hdg_raw * 90.0 / 512.0;
+    if (hdg_sign) heading += 180.0;
+    score += 12;
+    if (ias_raw == 0) return 0;
+    if (ias_raw >= 50 && ias_raw <= 700) score += 11; else return 0;
+    if (mach_raw == 0) return 0;
+    mach = mach_raw * 2.048 / 512;
+    if (mach >= 0.1 && mach <= 0.9) score += 11; else return 0;
+    if (baro_valid) {
+        baro_rate = (int)baro_raw * 32 - (baro_sign ? 16384 : 0);
+        if (baro_rate >= -6000 && baro_rate <= 6000) score += 11; else return 0;
+    } else if (baro_raw == 0) score += 1;
+    else return 0;
+    if (ins_valid) {
+        ins_rate = (int)ins_raw * 32 - (ins_sign ? 16384 : 0);
+        if (ins_rate >= -6000 && ins_rate <= 6000) score += 11; else return 0;
+    } else if (ins_raw == 0) score += 1;
+    else return 0;
+    if (baro_valid && ins_valid && abs(baro_rate - ins_rate) > 2000) score -= 12;
+    if (o) {
+        o->commb_format = CB_HEADING_SPEED;
+        o->valid |= B_HEADING | B_IAS | B_MACH;
+        o->heading = heading;
+        o->heading_type = 3;
+        o->ias = (uint16_t)ias_raw;
+        o->mach = mach;
+        if (baro_valid) { o->valid |= B_BARO_RATE; o->baro_rate = baro_rate; }
+        if (ins_valid) { o->valid |= B_GEOM_RATE; o->geom_rate = ins_rate; }
+    }
+    return score;
+}
+
+static int mb_bds44(const mb_ctx *c, oracle_fields_mb *o)                        /* comm_b.c:778-937 */
+{
+    const unsigned source = MB(1, 4), wind_valid = MB1(5), windspeed_raw = MB(6, 14), winddir_raw = MB(15, 23);
+    const unsigned sat_valid = MB1(24), sat_sign = MB1(25), sat_raw = MB(26, 34), asp_valid = MB1(35), asp_raw = MB(36, 46);
+    const unsigned turb_valid = MB1(47), turb_raw = MB(48, 49), hum_valid = MB1(50), hum_raw = MB(51, 56);
+    float sat;
+    int score = 0;
+    if (source == 0 || source >= 5) return 0;
+    if (!wind_valid || !sat_valid) return 0;
+    if (!asp_valid && asp_raw != 0) return 0;
+    if (!turb_valid && turb_raw != 0) return 0;
+    if (!hum_valid && hum_raw != 0) return 0;
+    if (windspeed_raw == 0) score += 2; else if (windspeed_raw <= 250) score += 19; else return 0;
+    sat = sat_raw * 0.25;
+    if (sat_sign) sat -= 128;
+    if (sat == 0) score += 2; else if (sat >= -80 && sat <= 60) score += 11; else return 0;
+    if (asp_valid) { if (asp_raw >= 25 && asp_raw <= 1100) score += 12; else return 0; } else score += 1;
+    score += turb_valid ? 3 : 1;
+    score += hum_valid ? 7 : 1;
+    if (source == 3 && score > 0) score = 1;                                      /* GICB look-alike, comm_b.c:889-902 */
+    if (o) {
+        o->commb_format = CB_MRAR;
+        o->valid |= B_MRAR_SOURCE | B_WIND | B_TEMPERATURE;
+        o->mrar_source = (uint8_t)source;
+        o->wind_speed = windspeed_raw;
+        o->wind_dir = winddir_raw * (180.0 / 256.0);
+        o->temperature = sat;
+        if (asp_valid) { o->valid |= B_PRESSURE; o->pressure = asp_raw; }
+        if (turb_valid) { o->valid |= B_TURBULENCE; o->turbulence = (uint8_t)turb_raw; }
+        if (hum_valid) { o->valid |= B_HUMIDITY; o->humidity = hum_raw * (100.0 / 64.0); }
+    }
+    return score;
+}
+
+static int mb_bds05(const mb_ctx *c, oracle_fields_mb *o)                        /* comm_b.c:944-985 */
+{
+    const unsigned typecode = MB(1, 5), ac12 = MB(9, 20);
+    if (c->df != 20) return 0;
+    if (typecode < 9 || typecode > 18) return 0;
+    if (MB1(21)) return 0;
+    if (!ac12) return 0;
+    if (c->ac != (((ac12 & 0x0FC0) << 1) | (ac12 & 0x003F))) return 0;
+    if (MB(23, 39) == 0 || MB(40, 56) == 0) return 0;
+    if (o) o->commb_format = CB_AIRBORNE_POSITION;
+    return 100;
+}
+
+void oracle1090_decode_commb(const uint8_t *msg, int df, int corrected, oracle_fields_mb *o)   /* decodeCommB, comm_b.c:50-86 */
+{
+    typedef int (*fn)(const mb_ctx *, oracle_fields_mb *);
+    static const fn order[10] = {mb_empty, mb_bds10, mb_bds20, mb_bds30, mb_bds17, mb_bds40, mb_bds50, mb_bds60, mb_bds44, mb_bds05};
+    mb_ctx c;
+    int best = 0, ambiguous = 0, k;
+    fn winner = NULL;
+    memset(o, 0, sizeof(*o));
+    if (df != 20 && df != 21) return;
+    c.mb = msg + 4;
+    c.df = df;
+    c.ac = df == 20 ? f_getbits(msg, 20, 32) : 0;                                 /* mm->AC, mode_s.c:628-631 */
+    /* DR (bits 9-13, mode_s.c:668-670); UM is still zero when the reference gets here (mode_s.c:731-734 precedes :757-760) */
+    if (f_getbits(msg, 9, 13) != 0 || corrected > 0) { o->commb_format = CB_NOT_DECODED; return; }
+    for (k = 0; k < 10; ++k) {
+        const int score = order[k](&c, NULL);
+        if (score > best) { best = score; winner = order[k]; ambiguous = 0; }
+        else if (score == best) ambiguous = 1;
+    }
+    if (!winner) o->commb_format = CB_UNKNOWN;
+    else if (ambiguous) o->commb_format = CB_AMBIGUOUS;
+    else winner(&c, o);
+}
+
+void oracle1090_decode_commb_batch(const uint8_t *frames, size_t n, const uint8_t *corrected, oracle_fields_mb *out)
+{
+    size_t k;
+    for (k = 0; k < n; ++k) oracle1090_decode_commb(frames + 14 * k, frames[14 * k] >> 3, corrected ? corrected[k] : 0, out + k);
+}

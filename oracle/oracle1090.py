@@ -153,11 +153,30 @@ def decode_es(frames: np.ndarray, corrected=None) -> np.ndarray:
     return out
 
 
-def run_ref_decode(frames: np.ndarray):
-    """The reference's own decodeModesMessage on 14-byte frames as received (third tap of ref_harness.c): the ES
-    record of each frame and decodeModesMessage's return code."""
+FIELDS_MB_DTYPE = np.dtype([("valid", "<u4")] + [(k, "u1") for k in (
+    "commb_format", "heading_type", "nav_modes", "nav_altitude_source", "mrar_source", "turbulence")] + [("reserved", "u1", 2), ("callsign", "S8")] +
+    [(k, "<f4") for k in ("roll", "heading", "track_rate", "gs", "mach", "nav_qnh", "wind_speed", "wind_dir", "temperature", "pressure", "humidity")] +
+    [(k, "<i4") for k in ("baro_rate", "geom_rate", "nav_mcp_altitude", "nav_fms_altitude")] + [("ias", "<u2"), ("tas", "<u2")])
+assert FIELDS_MB_DTYPE.itemsize == 84
+
+
+def decode_commb(frames: np.ndarray, corrected=None) -> np.ndarray:
+    """oracle1090_decode_commb on n corrected 14-byte frames (uint8 [n, 14])."""
     frames = np.ascontiguousarray(frames, np.uint8).reshape(-1, 14)
-    rec = np.dtype([("es", FIELDS_ES_DTYPE), ("rc", "<i4")])
+    L = lib()
+    L.oracle1090_decode_commb_batch.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
+    L.oracle1090_decode_commb_batch.restype = None
+    out = np.zeros(len(frames), FIELDS_MB_DTYPE)
+    cor = None if corrected is None else np.ascontiguousarray(corrected, np.uint8)
+    L.oracle1090_decode_commb_batch(frames.ctypes.data, len(frames), None if cor is None else cor.ctypes.data, out.ctypes.data)
+    return out
+
+
+def run_ref_decode(frames: np.ndarray, commb=False):
+    """The reference's own decodeModesMessage on 14-byte frames as received (third tap of ref_harness.c): the ES
+    record of each frame (commb=True: the Comm-B record) and decodeModesMessage's return code."""
+    frames = np.ascontiguousarray(frames, np.uint8).reshape(-1, 14)
+    rec = np.dtype([("es", FIELDS_ES_DTYPE), ("mb", FIELDS_MB_DTYPE), ("rc", "<i4")])
     tmpdir = "/dev/shm" if os.path.isdir("/dev/shm") else None
     with tempfile.TemporaryDirectory(dir=tmpdir) as d:
         fin, fout = os.path.join(d, "frames.bin"), os.path.join(d, "es.bin")
@@ -166,7 +185,7 @@ def run_ref_decode(frames: np.ndarray):
                        stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
         r = np.fromfile(fout, dtype=rec)
     assert len(r) == len(frames)
-    return r["es"].copy(), r["rc"].copy()
+    return r["mb" if commb else "es"].copy(), r["rc"].copy()
 
 
 def run_ref_fields(iq: np.ndarray, nfix_crc=0, fix_df=1):

@@ -17,7 +17,8 @@
  *  3. a link-time wrap of main(): with REF1090_DECODE_IN / REF1090_DECODE_OUT set the binary does not demodulate
  *     anything; it reads 14-byte frames, hands each to the reference's decodeModesMessage() (mode_s.c:520) exactly
  *     as demodulate2400 does (zeroed struct, score from scoreModesMessage) and writes what the extended-squitter
- *     decoder left in struct modesMessage, in the layout of adsbcu_fields_es, for tests/make_golden_es.py.
+ *     and Comm-B decoders left in struct modesMessage, in the layouts of adsbcu_fields_es and adsbcu_fields_commb, for
+ *     tests/make_golden_es.py and tests/make_golden_mb.py.
  */
 #include "dump1090.h"
 #include "adsbcu.h"
@@ -191,6 +192,43 @@ static void es_record(const struct modesMessage *mm, adsbcu_fields_es *e)
     e->ops_flags = (uint16_t) o;
 }
 
+static void mb_record(const struct modesMessage *mm, adsbcu_fields_commb *b)
+{
+    unsigned v = 0;
+    memset(b, 0, sizeof(*b));
+    if (mm->msgtype != 20 && mm->msgtype != 21) return;
+    b->commb_format = (uint8_t) mm->commb_format; b->heading_type = (uint8_t) mm->heading_type;
+    b->nav_modes = (uint8_t) mm->nav.modes; b->nav_altitude_source = (uint8_t) mm->nav.altitude_source;
+    b->mrar_source = (uint8_t) mm->mrar_source; b->turbulence = (uint8_t) mm->turbulence;
+    memcpy(b->callsign, mm->callsign, 8);
+    b->roll = mm->roll; b->heading = mm->heading; b->track_rate = mm->track_rate; b->gs = mm->gs.selected; b->mach = (float) mm->mach;
+    b->nav_qnh = mm->nav.qnh; b->wind_speed = mm->wind_speed; b->wind_dir = mm->wind_dir; b->temperature = mm->temperature;
+    b->pressure = mm->pressure; b->humidity = mm->humidity;
+    b->baro_rate = mm->baro_rate; b->geom_rate = mm->geom_rate; b->nav_mcp_altitude = mm->nav.mcp_altitude; b->nav_fms_altitude = mm->nav.fms_altitude;
+    b->ias = (uint16_t) mm->ias; b->tas = (uint16_t) mm->tas;
+    if (mm->callsign_valid) v |= ADSBCU_MB_CALLSIGN;
+    if (mm->roll_valid) v |= ADSBCU_MB_ROLL;
+    if (mm->heading_valid) v |= ADSBCU_MB_HEADING;
+    if (mm->gs_valid) v |= ADSBCU_MB_GS;
+    if (mm->track_rate_valid) v |= ADSBCU_MB_TRACK_RATE;
+    if (mm->tas_valid) v |= ADSBCU_MB_TAS;
+    if (mm->ias_valid) v |= ADSBCU_MB_IAS;
+    if (mm->mach_valid) v |= ADSBCU_MB_MACH;
+    if (mm->baro_rate_valid) v |= ADSBCU_MB_BARO_RATE;
+    if (mm->geom_rate_valid) v |= ADSBCU_MB_GEOM_RATE;
+    if (mm->nav.mcp_altitude_valid) v |= ADSBCU_MB_NAV_MCP_ALTITUDE;
+    if (mm->nav.fms_altitude_valid) v |= ADSBCU_MB_NAV_FMS_ALTITUDE;
+    if (mm->nav.qnh_valid) v |= ADSBCU_MB_NAV_QNH;
+    if (mm->nav.modes_valid) v |= ADSBCU_MB_NAV_MODES;
+    if (mm->mrar_source_valid) v |= ADSBCU_MB_MRAR_SOURCE;
+    if (mm->wind_valid) v |= ADSBCU_MB_WIND;
+    if (mm->temperature_valid) v |= ADSBCU_MB_TEMPERATURE;
+    if (mm->pressure_valid) v |= ADSBCU_MB_PRESSURE;
+    if (mm->turbulence_valid) v |= ADSBCU_MB_TURBULENCE;
+    if (mm->humidity_valid) v |= ADSBCU_MB_HUMIDITY;
+    b->valid = v;
+}
+
 int __wrap_main(int argc, char **argv)
 {
     const char *in = getenv("REF1090_DECODE_IN"), *out = getenv("REF1090_DECODE_OUT");
@@ -205,11 +243,16 @@ int __wrap_main(int argc, char **argv)
         struct modesMessage mm;
         adsbcu_fields_es e;
         int32_t rc;
+        adsbcu_fields_commb b;
         memset(&mm, 0, sizeof(mm));  /* demod_2400.c:355 */
+        /* Address/Parity replies are only accepted from aircraft the filter knows: let it know this one, as an earlier
+         * DF11 / DF17 of the same aircraft would have (mode_s.c:781-788) */
+        if ((frame[0] >> 3) == 20 || (frame[0] >> 3) == 21) icaoFilterAdd(modesChecksum(frame, 112));
         mm.score = scoreModesMessage(frame);
         rc = decodeModesMessage(&mm, frame);
-        if (rc < 0) memset(&e, 0, sizeof(e)); else es_record(&mm, &e);
+        if (rc < 0) { memset(&e, 0, sizeof(e)); memset(&b, 0, sizeof(b)); } else { es_record(&mm, &e); mb_record(&mm, &b); }
         fwrite(&e, sizeof(e), 1, fo);
+        fwrite(&b, sizeof(b), 1, fo);
         fwrite(&rc, sizeof(rc), 1, fo);
     }
     fclose(fi); fclose(fo);

@@ -42,3 +42,9 @@ def test_emulated_es_payload_decode_matches_reference_fixture():
     """fields_es_kernel's source against what the reference binary's decodeModesMessage produced (tests/golden/fields_es.npz)."""
     out = run_selection(["tests/test_fields_es.py", "-k", "gpu_es_equals_reference_fixture"])
     assert " passed" in out
+
+
+def test_emulated_commb_payload_decode_matches_reference_fixture():
+    """fields_commb_kernel's source against what the reference binary's decodeCommB produced (tests/golden/fields_mb.npz)."""
+    out = run_selection(["tests/test_fields_mb.py", "-k", "gpu_commb_equals_reference_fixture"])
+    assert " passed" in out
