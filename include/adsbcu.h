@@ -386,6 +386,15 @@ typedef struct adsbcu_fields_commb {
 /* HOST arrays of n records; the decode runs on the handle's device (one thread per message). */
 int adsbcu_1090_decode_commb(adsbcu_handle *h, const adsbcu_msg *msgs, size_t n, adsbcu_fields_commb *out);
 
+/* The three decoders above in ONE launch for records that are already in device memory (the message set of a long
+ * replay kept on the GPU, or records a caller's own kernel produced): msgs_dev and the output arrays are DEVICE
+ * pointers of n records each, 4-byte aligned; any of the three outputs may be NULL (at least one is not).  Nothing is
+ * allocated, copied or waited for: the kernel is enqueued on cuda_stream (a cudaStream_t; NULL = the default stream)
+ * and the results are there when that stream reaches it.  Same records, bit for bit, as the host-array entry points
+ * (decodeModesMessage, mode_s.c:626-779 + :798-1551 + comm_b.c:50-985). */
+int adsbcu_1090_decode_device(adsbcu_handle *h, const adsbcu_msg *msgs_dev, size_t n, adsbcu_fields_a *fields_dev,
+                              adsbcu_fields_es *es_dev, adsbcu_fields_commb *commb_dev, void *cuda_stream);
+
 /* ---- Wire formats of the decoded set ---------------------------------------------
  * Host-side formatting of adsbcu_msg records exactly as dump1090's network outputs write them; no handle, no GPU.
  *   adsbcu_1090_encode_beast   writeBeastMessage (net_io.c:440-487) per message.  verbatim != 0: the bytes as sliced,

@@ -77,7 +77,7 @@ EXPORTS = ["adsbcu_abi_version", "adsbcu_last_error", "adsbcu_create", "adsbcu_d
            "adsbcu_1090_filter_test", "adsbcu_1090_filter_expire", "adsbcu_get_stats", "adsbcu_1090b_feed", "adsbcu_1090b_reset",
            "adsbcu_978_feed", "adsbcu_978_feed_device", "adsbcu_978_get_stats", "adsbcu_978_reset", "adsbcu_978_phase", "adsbcu_1090_seek", "adsbcu_1090_scan_candidates",
            "adsbcu_1090_known_export", "adsbcu_1090_known_import", "adsbcu_1090_revive", "adsbcu_1090_resolve", "adsbcu_1090_modeac_block", "adsbcu_1090_feed_sc16",
-           "adsbcu_1090_modeac_block_static", "adsbcu_1090_decode_fields", "adsbcu_1090_decode_es", "adsbcu_1090_decode_commb", "adsbcu_1090_encode_beast", "adsbcu_1090_encode_avr", "adsbcu_1090_state_export", "adsbcu_1090_state_import", "adsbcu_1090_replay_sharded", "adsbcu_1090_replay_sharded_tail",
+           "adsbcu_1090_modeac_block_static", "adsbcu_1090_decode_fields", "adsbcu_1090_decode_es", "adsbcu_1090_decode_commb", "adsbcu_1090_decode_device", "adsbcu_1090_encode_beast", "adsbcu_1090_encode_avr", "adsbcu_1090_state_export", "adsbcu_1090_state_import", "adsbcu_1090_replay_sharded", "adsbcu_1090_replay_sharded_tail",
            "adsbcu_1090b_decode_fields", "adsbcu_1090b_cpr_decode", "adsbcu_1090_cpr_decode"]
 
 
@@ -164,6 +164,7 @@ def load():
         L.adsbcu_1090_decode_fields.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         L.adsbcu_1090_decode_es.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         L.adsbcu_1090_decode_commb.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.adsbcu_1090_decode_device.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.adsbcu_1090_encode_beast.restype = C.c_size_t
         L.adsbcu_1090_encode_beast.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t]
         L.adsbcu_1090_encode_avr.restype = C.c_size_t
@@ -291,6 +292,11 @@ class Demod1090:
         out = np.zeros(len(msgs), dtype=FIELDS_MB_DTYPE)
         self._check(load().adsbcu_1090_decode_commb(self.h, msgs.ctypes.data, len(msgs), out.ctypes.data))
         return out
+
+    def decode_device(self, msgs_ptr: int, n: int, fields_ptr: int = 0, es_ptr: int = 0, commb_ptr: int = 0, stream: int = 0) -> None:
+        """All of decodeModesMessage for n device-resident records in one launch on `stream` (device pointers; outputs may be 0)."""
+        self._check(load().adsbcu_1090_decode_device(self.h, msgs_ptr or None, n, fields_ptr or None, es_ptr or None, commb_ptr or None,
+                                                     stream or None))
 
     def cpr_decode_a(self, rec: np.ndarray) -> np.ndarray:
         """dump1090's decodeCPRairborne / decodeCPRsurface / decodeCPRrelative on every CPR_IN_DTYPE record."""

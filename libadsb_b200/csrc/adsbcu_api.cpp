@@ -986,6 +986,19 @@ int adsbcu_1090_decode_commb(adsbcu_handle *h, const adsbcu_msg *msgs, size_t n,
     return fields_commb_decode(h->fields, h->stream, msgs, n, out, h->error);
 }
 
+int adsbcu_1090_decode_device(adsbcu_handle *h, const adsbcu_msg *msgs_dev, size_t n, adsbcu_fields_a *fields_dev, adsbcu_fields_es *es_dev,
+                              adsbcu_fields_commb *commb_dev, void *cuda_stream)
+{
+    if (!h) return ADSBCU_ERR_ARG;
+    NEED_DEVICE(h);
+    if (n && (!msgs_dev || (!fields_dev && !es_dev && !commb_dev))) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
+    if (n > (size_t(1) << 28)) { h->error = "bad argument (more than 2^28 records in one call)"; return ADSBCU_ERR_ARG; }
+    if ((reinterpret_cast<uintptr_t>(msgs_dev) | reinterpret_cast<uintptr_t>(fields_dev) | reinterpret_cast<uintptr_t>(es_dev) |
+         reinterpret_cast<uintptr_t>(commb_dev)) & 3u) { h->error = "bad argument (device arrays must be 4-byte aligned)"; return ADSBCU_ERR_ARG; }
+    CK(cudaSetDevice(h->device));
+    return fields_all_device(h->sm_count, static_cast<cudaStream_t>(cuda_stream), msgs_dev, n, fields_dev, es_dev, commb_dev, h->error);
+}
+
 int adsbcu_978_feed(adsbcu_handle *h, const uint8_t *iq, size_t nbytes, adsbcu_uat_frame *out, size_t cap, size_t *n_out)
 {
     if (!h) return ADSBCU_ERR_ARG;

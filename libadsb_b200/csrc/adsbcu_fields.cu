@@ -398,15 +398,8 @@ __device__ __forceinline__ int mode_a_to_c(uint32_t mode_a)
     return int(five * 5 + one) - 13;
 }
 
-__global__ void __launch_bounds__(256) fields_a_kernel(const adsbcu_msg *msgs, uint32_t n, adsbcu_fields_a *out)
+__device__ void fields_a_one(const uint8_t *m, int df, adsbcu_fields_a &f)
 {
-    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= n) return;
-    uint8_t m[14];
-    const uint8_t *src = reinterpret_cast<const uint8_t *>(&msgs[k]) + 8;        // adsbcu_msg::msg (packed record: byte loads)
-    for (int i = 0; i < 14; ++i) m[i] = src[i];
-    const int df = reinterpret_cast<const uint8_t *>(&msgs[k])[8 + 14 + 14 + 2];   // adsbcu_msg::msgtype
-    adsbcu_fields_a f;
     memset(&f, 0, sizeof(f));
     f.altitude_baro = 0;
     if (df == 0 || df == 4 || df == 16 || df == 20) {                             // AC (mode_s.c:628-637)
@@ -461,6 +454,18 @@ __global__ void __launch_bounds__(256) fields_a_kernel(const adsbcu_msg *msgs, u
         f.airground = f.VS ? 1 : 3;
     }
     f.es_pending = (df == 17 || df == 18) ? 1 : 0;
+}
+
+__global__ void __launch_bounds__(256) fields_a_kernel(const adsbcu_msg *msgs, uint32_t n, adsbcu_fields_a *out)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    uint8_t m[14];
+    const uint8_t *src = reinterpret_cast<const uint8_t *>(&msgs[k]) + 8;        // adsbcu_msg::msg (packed record: byte loads)
+    for (int i = 0; i < 14; ++i) m[i] = src[i];
+    const int df = reinterpret_cast<const uint8_t *>(&msgs[k])[8 + 14 + 14 + 2];   // adsbcu_msg::msgtype
+    adsbcu_fields_a f;
+    fields_a_one(m, df, f);
     out[k] = f;
 }
 
@@ -1119,6 +1124,70 @@ int fields_commb_decode(Fields *&f, cudaStream_t s, const adsbcu_msg *msgs, size
     if ((e = cudaGetLastError()) != cudaSuccess) return fail(err, "fields_commb_kernel", e);
     if ((e = cudaMemcpyAsync(out, f->d_out, n * sizeof(adsbcu_fields_commb), cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail(err, "D2H(commb)", e);
     if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail(err, "commb sync", e);
+    return ADSBCU_OK;
+}
+
+// ---- Path A: all of decodeModesMessage for records that are already on the device ---------------------------------------
+// One launch fills up to three output arrays (header fields, extended squitter, Comm-B) from device-resident adsbcu_msg
+// records: the input tile is staged once, every output goes through the same shared staging tile so that the global
+// writes are whole words in order.  No allocation, no copy, no wait: the caller's stream orders it.
+namespace {
+
+// tile <-> global copies: 16 bytes per thread and instruction when the global side is 16-byte aligned (every full tile of a
+// cudaMalloc'ed array is: 256 records of 56 / 32 / 120 / 84 bytes), words otherwise
+__device__ __forceinline__ void copy_words(uint32_t *dst, const uint32_t *src, uint32_t nwords)
+{
+    if (((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src)) & 15u) == 0) {
+        const uint32_t nvec = nwords / 4;
+        for (uint32_t v = threadIdx.x; v < nvec; v += kEsThreads) reinterpret_cast<uint4 *>(dst)[v] = reinterpret_cast<const uint4 *>(src)[v];
+        for (uint32_t w = nvec * 4 + threadIdx.x; w < nwords; w += kEsThreads) dst[w] = src[w];
+    } else {
+        for (uint32_t w = threadIdx.x; w < nwords; w += kEsThreads) dst[w] = src[w];
+    }
+}
+
+// decode into the thread's slot of the shared tile (the record never lives in registers), then write the tile out in order
+template <class Rec, class Decode>
+__device__ __forceinline__ void decode_tile(Decode decode, bool live, uint32_t *s_out, uint32_t *out, uint32_t first, uint32_t count)
+{
+    constexpr uint32_t kWords = sizeof(Rec) / 4;
+    __syncthreads();                                                           // the tile may still be read by the previous output's copy
+    if (live) decode(*reinterpret_cast<Rec *>(s_out + threadIdx.x * kWords));
+    __syncthreads();
+    copy_words(out + size_t(first) * kWords, s_out, count * kWords);
+}
+
+__global__ void __launch_bounds__(kEsThreads, 4) fields_all_kernel(const uint32_t *msgs, uint32_t n, uint32_t *out_a, uint32_t *out_es, uint32_t *out_mb)
+{
+    constexpr uint32_t kInWords = sizeof(adsbcu_msg) / 4;
+    __shared__ __align__(16) uint32_t s_in[kEsThreads * kInWords];
+    __shared__ __align__(16) uint32_t s_out[kEsThreads * sizeof(adsbcu_fields_es) / 4];      // the largest of the three records
+    for (uint32_t first = blockIdx.x * kEsThreads; first < n; first += gridDim.x * kEsThreads) {
+        const uint32_t count = min(uint32_t(kEsThreads), n - first);
+        __syncthreads();
+        copy_words(s_in, msgs + size_t(first) * kInWords, count * kInWords);
+        __syncthreads();
+        const bool live = threadIdx.x < count;
+        const uint8_t *rec = reinterpret_cast<const uint8_t *>(s_in + (live ? threadIdx.x : 0) * kInWords);
+        const int df = rec[8 + 14 + 14 + 2], corrected = rec[8 + 14 + 14 + 1];
+        if (out_a) decode_tile<adsbcu_fields_a>([&](adsbcu_fields_a &a) { fields_a_one(rec + 8, df, a); }, live, s_out, out_a, first, count);
+        if (out_es) decode_tile<adsbcu_fields_es>([&](adsbcu_fields_es &e) { es_decode_one(rec + 8, df, corrected, e); }, live, s_out, out_es, first, count);
+        if (out_mb) decode_tile<adsbcu_fields_commb>([&](adsbcu_fields_commb &b) { commb_decode_one(rec + 8, df, corrected, b); }, live, s_out, out_mb, first, count);
+    }
+}
+
+}  // namespace
+
+int fields_all_device(int sm_count, cudaStream_t s, const adsbcu_msg *msgs_dev, size_t n, adsbcu_fields_a *a_dev, adsbcu_fields_es *es_dev,
+                      adsbcu_fields_commb *mb_dev, std::string &err)
+{
+    if (!n) return ADSBCU_OK;
+    const unsigned tiles = unsigned((n + kEsThreads - 1) / kEsThreads);
+    const unsigned grid = std::min(tiles, unsigned(sm_count) * 4u);            // 4 resident CTAs per SM (44 KiB of shared memory each)
+    ADSBCU_LAUNCH(fields_all_kernel, grid, kEsThreads, 0, s, reinterpret_cast<const uint32_t *>(msgs_dev), uint32_t(n),
+                  reinterpret_cast<uint32_t *>(a_dev), reinterpret_cast<uint32_t *>(es_dev), reinterpret_cast<uint32_t *>(mb_dev));
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(err, "fields_all_kernel", e);
     return ADSBCU_OK;
 }
 

@@ -310,6 +310,8 @@ int  cpr_a_decode(Fields *&f, cudaStream_t s, const adsbcu_cpr_in *in, size_t n,
 int  fields_a_decode(Fields *&f, cudaStream_t s, const ::adsbcu_msg *msgs, size_t n, ::adsbcu_fields_a *out, std::string &err);
 int  fields_es_decode(Fields *&f, cudaStream_t s, const ::adsbcu_msg *msgs, size_t n, ::adsbcu_fields_es *out, std::string &err);
 int  fields_commb_decode(Fields *&f, cudaStream_t s, const ::adsbcu_msg *msgs, size_t n, ::adsbcu_fields_commb *out, std::string &err);
+int  fields_all_device(int sm_count, cudaStream_t s, const ::adsbcu_msg *msgs_dev, size_t n, ::adsbcu_fields_a *a_dev, ::adsbcu_fields_es *es_dev,
+                       ::adsbcu_fields_commb *mb_dev, std::string &err);
 void fields_free(Fields *f);
 
 // Path C (adsbcu_uat.cu): 978 MHz UAT

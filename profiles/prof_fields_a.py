@@ -56,3 +56,29 @@ if __name__ == "__main__":
             line["oracle_one_core_mrecords_s"] = len(sample) / tc / 1e6
         out.append(line)
         print(json.dumps(line), flush=True)
+    # the same three decoders in one launch over device-resident records (adsbcu_1090_decode_device), timed with CUDA events on
+    # the launching stream; algorithmic bytes per record = 56 in + 32 + 120 + 84 out
+    import torch
+    mixed = np.concatenate([es[: n // 2], mb[: n // 2]])[rng.permutation(n)]
+    m = msgs_of(mixed)
+    d_in = torch.from_numpy(np.frombuffer(m.tobytes(), np.uint8).copy()).cuda()
+    d_a = torch.empty(n * 32, dtype=torch.uint8, device="cuda")
+    d_es = torch.empty(n * 120, dtype=torch.uint8, device="cuda")
+    d_mb = torch.empty(n * 84, dtype=torch.uint8, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 0) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 0
+    for which, ptrs, nbytes in (("fields + es + commb", (d_a.data_ptr(), d_es.data_ptr(), d_mb.data_ptr()), 292), ("es only", (0, d_es.data_ptr(), 0), 176)):
+        for _ in range(3):
+            d.decode_device(d_in.data_ptr(), n, *ptrs, stream=stream)
+        torch.cuda.synchronize()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        reps = 20
+        ev[0].record()
+        for _ in range(reps):
+            d.decode_device(d_in.data_ptr(), n, *ptrs, stream=stream)
+        ev[1].record()
+        torch.cuda.synchronize()
+        ms = ev[0].elapsed_time(ev[1]) / reps
+        line = {"path": "A decode_device (" + which + ")", "records": n, "ms_per_launch": ms, "grecords_s": n / ms / 1e6,
+                "algorithmic_gb_s": n * nbytes / ms / 1e6, "hbm_peak_gb_s": peak, "frac": (n * nbytes / ms / 1e6 / peak) if peak else None}
+        print(json.dumps(line), flush=True)
