@@ -933,7 +933,9 @@ int adsbcu_1090b_decode_fields(adsbcu_handle *h, const adsbcu_msg_b *msgs, size_
     if (n && (!msgs || !out)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
     if (n > (size_t(1) << 28)) { h->error = "bad argument (more than 2^28 records in one call)"; return ADSBCU_ERR_ARG; }
     CK(cudaSetDevice(h->device));
+    ABI_GUARD_BEGIN
     return fields_decode(h->fields, h->stream, msgs, n, out, h->error);
+    ABI_GUARD_END(h)
 }
 
 int adsbcu_1090b_cpr_decode(adsbcu_handle *h, const adsbcu_cpr_pair *pairs, size_t n, adsbcu_cpr_fix *out)
@@ -943,7 +945,9 @@ int adsbcu_1090b_cpr_decode(adsbcu_handle *h, const adsbcu_cpr_pair *pairs, size
     if (n && (!pairs || !out)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
     if (n > (size_t(1) << 28)) { h->error = "bad argument (more than 2^28 records in one call)"; return ADSBCU_ERR_ARG; }
     CK(cudaSetDevice(h->device));
+    ABI_GUARD_BEGIN
     return cpr_decode(h->fields, h->stream, pairs, n, out, h->error);
+    ABI_GUARD_END(h)
 }
 
 int adsbcu_1090_cpr_decode(adsbcu_handle *h, const adsbcu_cpr_in *in, size_t n, adsbcu_cpr_out *out)
@@ -953,7 +957,9 @@ int adsbcu_1090_cpr_decode(adsbcu_handle *h, const adsbcu_cpr_in *in, size_t n, 
     if (n && (!in || !out)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
     if (n > (size_t(1) << 28)) { h->error = "bad argument (more than 2^28 records in one call)"; return ADSBCU_ERR_ARG; }
     CK(cudaSetDevice(h->device));
+    ABI_GUARD_BEGIN
     return cpr_a_decode(h->fields, h->stream, in, n, out, h->error);
+    ABI_GUARD_END(h)
 }
 
 int adsbcu_1090_decode_fields(adsbcu_handle *h, const adsbcu_msg *msgs, size_t n, adsbcu_fields_a *out)
@@ -963,7 +969,9 @@ int adsbcu_1090_decode_fields(adsbcu_handle *h, const adsbcu_msg *msgs, size_t n
     if (n && (!msgs || !out)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
     if (n > (size_t(1) << 28)) { h->error = "bad argument (more than 2^28 records in one call)"; return ADSBCU_ERR_ARG; }
     CK(cudaSetDevice(h->device));
+    ABI_GUARD_BEGIN
     return fields_a_decode(h->fields, h->stream, msgs, n, out, h->error);
+    ABI_GUARD_END(h)
 }
 
 int adsbcu_1090_decode_es(adsbcu_handle *h, const adsbcu_msg *msgs, size_t n, adsbcu_fields_es *out)
@@ -973,7 +981,9 @@ int adsbcu_1090_decode_es(adsbcu_handle *h, const adsbcu_msg *msgs, size_t n, ad
     if (n && (!msgs || !out)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
     if (n > (size_t(1) << 24)) { h->error = "bad argument (more than 2^24 records in one call)"; return ADSBCU_ERR_ARG; }
     CK(cudaSetDevice(h->device));
+    ABI_GUARD_BEGIN
     return fields_es_decode(h->fields, h->stream, msgs, n, out, h->error);
+    ABI_GUARD_END(h)
 }
 
 int adsbcu_1090_decode_commb(adsbcu_handle *h, const adsbcu_msg *msgs, size_t n, adsbcu_fields_commb *out)
@@ -983,7 +993,9 @@ int adsbcu_1090_decode_commb(adsbcu_handle *h, const adsbcu_msg *msgs, size_t n,
     if (n && (!msgs || !out)) { h->error = "bad argument (null pointer)"; return ADSBCU_ERR_ARG; }
     if (n > (size_t(1) << 24)) { h->error = "bad argument (more than 2^24 records in one call)"; return ADSBCU_ERR_ARG; }
     CK(cudaSetDevice(h->device));
+    ABI_GUARD_BEGIN
     return fields_commb_decode(h->fields, h->stream, msgs, n, out, h->error);
+    ABI_GUARD_END(h)
 }
 
 int adsbcu_1090_decode_device(adsbcu_handle *h, const adsbcu_msg *msgs_dev, size_t n, adsbcu_fields_a *fields_dev, adsbcu_fields_es *es_dev,
@@ -996,7 +1008,9 @@ int adsbcu_1090_decode_device(adsbcu_handle *h, const adsbcu_msg *msgs_dev, size
     if ((reinterpret_cast<uintptr_t>(msgs_dev) | reinterpret_cast<uintptr_t>(fields_dev) | reinterpret_cast<uintptr_t>(es_dev) |
          reinterpret_cast<uintptr_t>(commb_dev)) & 3u) { h->error = "bad argument (device arrays must be 4-byte aligned)"; return ADSBCU_ERR_ARG; }
     CK(cudaSetDevice(h->device));
+    ABI_GUARD_BEGIN
     return fields_all_device(h->sm_count, static_cast<cudaStream_t>(cuda_stream), msgs_dev, n, fields_dev, es_dev, commb_dev, h->error);
+    ABI_GUARD_END(h)
 }
 
 int adsbcu_978_feed(adsbcu_handle *h, const uint8_t *iq, size_t nbytes, adsbcu_uat_frame *out, size_t cap, size_t *n_out)
