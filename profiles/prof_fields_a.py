@@ -43,7 +43,8 @@ if __name__ == "__main__":
     mb = build(rng, n // 11 + 1)[:n]
     d = adsbcu.Demod1090()
     out = []
-    for name, frames, gpu, cpu, rec_bytes in (
+    device_only = "--device-only" in sys.argv            # for the ncu capture of fields_all_kernel
+    for name, frames, gpu, cpu, rec_bytes in () if device_only else (
             ("A fields (adsbcu_1090_decode_fields)", es, d.decode_fields_a, None, 56 + 32),
             ("A extended squitter (adsbcu_1090_decode_es)", es, d.decode_es, O.decode_es, 56 + 120),
             ("A Comm-B (adsbcu_1090_decode_commb)", mb, d.decode_commb, O.decode_commb, 56 + 84)):
