@@ -117,3 +117,36 @@ def test_gpu_es_velocity_every_component_pair(adsbcu_mod, oracle_mod):
         want = oracle_mod.decode_es(f).view(adsbcu_mod.FIELDS_ES_DTYPE)
         assert (want["valid"] & adsbcu_mod.ES_VALID["heading"]).sum() > 1000000
         assert not differences(got, want), (sub, signs)
+
+
+def check_capture_es(es, ref, msgs, valid_bits):
+    """fields_a.npz carries what the reference's struct modesMessage held for the accepted messages of a real (synthetic-air)
+    capture AFTER its ES decoder ran: for the DF17 / DF18 messages the ES record must give exactly those final values."""
+    sel = (msgs["msgtype"] == 17) | (msgs["msgtype"] == 18)
+    assert sel.sum() > 300 and (es["es"] == sel).all()
+    e, r = es[sel], ref[sel]
+    assert np.array_equal(e["airground"], r["airground"])
+    for name, bit in (("alert", "alert"), ("spi", "spi"), ("altitude_baro", "altitude_baro"), ("squawk", "squawk")):
+        have = (e["valid"] & valid_bits[bit]) != 0
+        assert np.array_equal(have, r[name + "_valid"] == 1), name
+        assert np.array_equal(e[name][have], r[name][have]), name
+    assert np.array_equal(e["altitude_baro_unit"], r["altitude_baro_unit"])
+    assert np.array_equal(e["CA_CF"], np.where(msgs["msgtype"][sel] == 17, r["CA"], r["CF"]))
+    assert np.array_equal(e["addr"], msgs["addr"][sel])                         # incl. the non-ICAO flag of the demodulator's record
+
+
+def test_oracle_es_gives_the_final_values_of_the_reference_capture(oracle_mod):
+    with np.load(os.path.join(os.path.dirname(GOLD), "fields_a.npz")) as z:
+        msgs, ref = z["msgs"], z["fields"]
+    bits = {"alert": 1 << 14, "spi": 1 << 13, "altitude_baro": 1 << 0, "squawk": 1 << 8}
+    check_capture_es(oracle_mod.decode_es(msgs["msg"], msgs["correctedbits"]), ref, msgs, bits)
+
+
+@pytest.mark.gpu
+def test_gpu_es_gives_the_final_values_of_the_reference_capture(adsbcu_mod):
+    with np.load(os.path.join(os.path.dirname(GOLD), "fields_a.npz")) as z:
+        msgs, ref = z["msgs"], z["fields"]
+    m = np.zeros(len(msgs), adsbcu_mod.MSG_DTYPE)
+    for f in adsbcu_mod.MSG_DTYPE.names:
+        m[f] = msgs[f]
+    check_capture_es(adsbcu_mod.Demod1090().decode_es(m), ref, msgs, adsbcu_mod.ES_VALID)
