@@ -106,7 +106,10 @@ int adsbcu_1090_reset(adsbcu_handle *h, int clear_filter);
  * iq is HOST memory; the copy to the device is part of the call.  Accepted
  * messages are appended to out[0..cap) in stream order, *n_out receives their
  * number.  Equivalent to the reference consuming the same bytes through
- * sdr_ifile.c:178-245 -> demodulate2400(). */
+ * sdr_ifile.c:178-245 -> demodulate2400().
+ * out[] may be ordinary host memory, pinned host memory (cudaHostAlloc / cudaHostRegister: the GPU writes the records
+ * there itself, no copy at the end) or DEVICE memory of the handle's GPU (8-byte aligned): the message set then stays on
+ * the device, complete when the call returns, ready for adsbcu_1090_decode_device.  The same holds for the two feeds below. */
 int adsbcu_1090_feed(adsbcu_handle *h, const uint8_t *iq, size_t nsamples,
                      adsbcu_msg *out, size_t cap, size_t *n_out);
 

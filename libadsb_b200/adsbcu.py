@@ -255,6 +255,12 @@ class Demod1090:
                                                    C.byref(got)))
         return out[:got.value]
 
+    def feed_device_resident(self, dev_ptr: int, nsamples: int, out_ptr: int, cap: int) -> int:
+        """adsbcu_1090_feed_device with out[] in DEVICE memory: the message set stays on the GPU; returns the message count."""
+        got = C.c_size_t(0)
+        self._check(load().adsbcu_1090_feed_device(self.h, C.c_void_p(dev_ptr), nsamples, C.c_void_p(out_ptr), cap, C.byref(got)))
+        return int(got.value)
+
     def magnitude(self, iq: np.ndarray) -> np.ndarray:
         iq = np.ascontiguousarray(iq, dtype=np.uint8)
         n = iq.size // 2

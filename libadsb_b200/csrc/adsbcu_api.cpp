@@ -569,9 +569,17 @@ int prepare_out(adsbcu_handle *h, adsbcu_msg *out, size_t cap, OutTarget &t)
     if (!cap) return ADSBCU_OK;
     // out[] in pinned (cudaHostAlloc / cudaHostRegister) memory: the GPU writes the messages there itself
     cudaPointerAttributes at{};
-    if (cudaPointerGetAttributes(&at, out) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer &&
-        (reinterpret_cast<uintptr_t>(at.devicePointer) & 7u) == 0) {
+    const bool known = cudaPointerGetAttributes(&at, out) == cudaSuccess;
+    if (known && at.type == cudaMemoryTypeHost && at.devicePointer && (reinterpret_cast<uintptr_t>(at.devicePointer) & 7u) == 0) {
         t.dev = static_cast<adsbcu_msg *>(at.devicePointer);
+        t.direct = true;
+        return ADSBCU_OK;
+    }
+    // out[] in device memory: the message set stays on the GPU (for adsbcu_1090_decode_device or the caller's own kernels)
+    if (known && (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged)) {
+        if (at.type == cudaMemoryTypeDevice && at.device != h->device) { h->error = "bad argument (out[] is memory of another device)"; return ADSBCU_ERR_ARG; }
+        if (reinterpret_cast<uintptr_t>(out) & 7u) { h->error = "bad argument (device out[] must be 8-byte aligned)"; return ADSBCU_ERR_ARG; }
+        t.dev = out;
         t.direct = true;
         return ADSBCU_OK;
     }

@@ -168,3 +168,25 @@ int sm_count()
 }
 
 }  // namespace emu
+
+// ---- "device memory" for cudaPointerGetAttributes: ranges a test marks (nbytes == 0 forgets them all) ----------------------
+#include <mutex>
+#include <utility>
+#include <vector>
+namespace {
+std::mutex g_dev_mu;
+std::vector<std::pair<const char *, size_t>> g_dev_ranges;
+}  // namespace
+extern "C" void adsbcu_emu_mark_device(const void *p, size_t nbytes)
+{
+    std::lock_guard<std::mutex> lock(g_dev_mu);
+    if (!nbytes) g_dev_ranges.clear();
+    else g_dev_ranges.emplace_back(static_cast<const char *>(p), nbytes);
+}
+extern "C" int adsbcu_emu_is_device(const void *p)
+{
+    std::lock_guard<std::mutex> lock(g_dev_mu);
+    for (const auto &r : g_dev_ranges)
+        if (static_cast<const char *>(p) >= r.first && static_cast<const char *>(p) < r.first + r.second) return 1;
+    return 0;
+}

@@ -314,9 +314,13 @@ static inline cudaError_t cudaFreeHost(void *p) { std::free(p); return cudaSucce
 template <class T> static inline cudaError_t cudaHostGetDevicePointer(T **d, void *h, unsigned) { *d = static_cast<T *>(h); return cudaSuccess; }
 static inline cudaError_t cudaHostRegister(void *, size_t, unsigned) { return cudaSuccess; }
 static inline cudaError_t cudaHostUnregister(void *) { return cudaSuccess; }
+// tests mark a host range as "device memory" with adsbcu_emu_mark_device (emu_runtime.cpp); everything else is unregistered
+extern "C" int adsbcu_emu_is_device(const void *p);
 static inline cudaError_t cudaPointerGetAttributes(cudaPointerAttributes *a, const void *p)
 {
-    a->type = cudaMemoryTypeUnregistered; a->device = 0; a->devicePointer = nullptr; a->hostPointer = const_cast<void *>(p);
+    const bool dev = adsbcu_emu_is_device(p) != 0;
+    a->type = dev ? cudaMemoryTypeDevice : cudaMemoryTypeUnregistered; a->device = 0;
+    a->devicePointer = dev ? const_cast<void *>(p) : nullptr; a->hostPointer = dev ? nullptr : const_cast<void *>(p);
     return cudaSuccess;
 }
 static inline cudaError_t cudaMemcpy(void *d, const void *s, size_t n, cudaMemcpyKind) { if (n) std::memmove(d, s, n); return cudaSuccess; }
