@@ -43,9 +43,30 @@ def one_case(A, seed):
             os.environ[k] = v
         else:
             os.environ.pop(k, None)
-    want = O.Oracle1090(nfix, fdf, block).feed(iq, cap=1 << 16)
+    o = O.Oracle1090(nfix, fdf, block)
     d = A.Demod1090(nfix, fdf, block_samples=block) if block else A.Demod1090(nfix, fdf)
-    got = np.concatenate([d.feed(iq[cuts[i]:cuts[i + 1]], cap=1 << 16) for i in range(len(cuts) - 1)]) if len(cuts) > 2 else d.feed(iq, cap=1 << 16)
+    mode = rng.choice(["uc8", "uc8", "uc8", "expire", "sc16", "sc16q11"])
+    params["mode"] = str(mode)
+    if mode == "expire":
+        # live mode: the filter's tables flip between some of the feeds (icao_filter.c:112-127), on both sides at the same places
+        want, got = [], []
+        for i in range(len(cuts) - 1):
+            part = iq[cuts[i]:cuts[i + 1]]
+            want.append(o.feed(part, cap=1 << 16))
+            got.append(d.feed(part, cap=1 << 16))
+            if rng.random() < 0.5:
+                o.filter_expire()
+                d.filter_expire()
+        want, got = np.concatenate(want), np.concatenate(got)
+    elif mode in ("sc16", "sc16q11"):
+        q11 = mode == "sc16q11"
+        s16 = synth.to_sc16(iq, q11)
+        o.set_input_format(2 if q11 else 1)
+        want = o.feed(s16, cap=1 << 16)
+        got = np.concatenate([d.feed_sc16(s16[cuts[i]:cuts[i + 1]], q11, cap=1 << 16) for i in range(len(cuts) - 1)])
+    else:
+        want = o.feed(iq, cap=1 << 16)
+        got = np.concatenate([d.feed(iq[cuts[i]:cuts[i + 1]], cap=1 << 16) for i in range(len(cuts) - 1)])
     diffs = O.same_messages(want, got)
     return params, len(want), diffs
 
