@@ -47,6 +47,11 @@ def one_case(A, seed):
     d = A.Demod1090(nfix, fdf, block_samples=block) if block else A.Demod1090(nfix, fdf)
     mode = rng.choice(["uc8", "uc8", "uc8", "expire", "sc16", "sc16q11"])
     params["mode"] = str(mode)
+    prefill = int(rng.choice([0, 0, 0, 0, 3900, 4090, 4096, 5000]))     # a filter that is (nearly) full: icao_filter.c:71-84 stops adding
+    params["prefill"] = prefill
+    for a in rng.integers(1, 1 << 24, prefill):
+        o.filter_add(int(a))
+        d.filter_add(int(a))
     if mode == "expire":
         # live mode: the filter's tables flip between some of the feeds (icao_filter.c:112-127), on both sides at the same places
         want, got = [], []
