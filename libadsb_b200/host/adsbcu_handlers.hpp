@@ -90,6 +90,12 @@ public:
         : eng_(make_config(device, nfix_crc, fix_df, max_feed_samples)), sink_(std::move(sink)), out_(1u << 16), mode_ac_(mode_ac), live_(live)
     {
     }
+    // The rest of decodeModesMessage for every accepted message (mode_s.c:626-796 with decodeExtendedSquitter and decodeCommB):
+    // when set, each buffer's messages go through the three batched decode calls and the sink gets message + fields, which is
+    // what useModesMessage(struct modesMessage*) sees in the reference.  Called after the plain sink, in the same order.
+    using DecodedSink = std::function<void(adsbcu_msg const &, adsbcu_fields_a const &, adsbcu_fields_es const &, adsbcu_fields_commb const &)>;
+    void SetDecodedSink(DecodedSink s) { decoded_sink_ = std::move(s); }
+
     void HandleData(std::span<uint8_t const> const &data) override
     {
         if (live_) {
@@ -110,7 +116,16 @@ public:
             n = cap;
         }
         eng_.check(rc, "adsbcu_1090_feed");
-        for (size_t k = 0; k < n; ++k) sink_(out_[k]);
+        if (decoded_sink_ && n) {
+            hdr_.resize(n); es_.resize(n); mb_.resize(n);
+            eng_.check(adsbcu_1090_decode_fields(eng_.get(), out_.data(), n, hdr_.data()), "adsbcu_1090_decode_fields");
+            eng_.check(adsbcu_1090_decode_es(eng_.get(), out_.data(), n, es_.data()), "adsbcu_1090_decode_es");
+            eng_.check(adsbcu_1090_decode_commb(eng_.get(), out_.data(), n, mb_.data()), "adsbcu_1090_decode_commb");
+        }
+        for (size_t k = 0; k < n; ++k) {
+            if (sink_) sink_(out_[k]);
+            if (decoded_sink_) decoded_sink_(out_[k], hdr_[k], es_[k], mb_[k]);
+        }
         if (mode_ac_) {
             const size_t ns = data.size() / 2;
             size_t na = 0;
@@ -118,7 +133,7 @@ public:
             const uint64_t ts = uint64_t(double(samples_seen_) * 12e6 / 2400000.0);
             eng_.check(adsbcu_1090_modeac_block(eng_.get(), data.data(), ns, tail_.data(), tail_.size() / 2, ts, out_.data(),
                                                 out_.size(), &na), "adsbcu_1090_modeac_block");
-            for (size_t k = 0; k < na; ++k) sink_(out_[k]);
+            for (size_t k = 0; k < na; ++k) if (sink_) sink_(out_[k]);
             // keep the last 326 samples as the next buffer's overlap (fifo.c:187-196)
             std::vector<uint8_t> t(tail_);
             t.insert(t.end(), data.begin(), data.begin() + 2 * ns);
@@ -140,6 +155,10 @@ private:
     Engine eng_;
     Sink sink_;
     std::vector<adsbcu_msg> out_;
+    DecodedSink decoded_sink_;
+    std::vector<adsbcu_fields_a> hdr_;
+    std::vector<adsbcu_fields_es> es_;
+    std::vector<adsbcu_fields_commb> mb_;
     bool mode_ac_ = false, live_ = false;
     std::chrono::steady_clock::time_point next_flip_{};
     std::vector<uint8_t> tail_;

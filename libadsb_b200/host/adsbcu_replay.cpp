@@ -3,11 +3,13 @@
 // tests/test_1090.cpp's TestEmbedded loop for libadsb's own handler, and of UAT978Handler fed from
 // a file.  Output formats:
 //   path a : "@<12 hex 12 MHz timestamp><hex msg>;"  one line per message (net_io.c:529-545), and with
-//            --beast FILE the Beast binary stream of writeBeastMessage (net_io.c:440-487) on the verbatim bytes
+//            --beast FILE the Beast binary stream of writeBeastMessage (net_io.c:440-487) on the verbatim bytes;
+//            --decode adds one "# ..." line per message with what decodeModesMessage would have filled in (header fields,
+//            extended squitter, Comm-B: the three batched decode calls of the handler)
 //   path b : "*<hex msg>;", or with --aircraft one "addr,altitude,speed,track,lat1E7,lon1E7,callsign" line per
 //            IListener::OnChanged callback of the reference (field decode + CPR on the device, aircraft table on the host)
 //   path uat: "<updown><hex payload>;rs=<n>;"  (dump978 raw line format)
-// usage: adsbcu_replay --path a|b|uat [--fix|--fix-2bit] [--no-fix-df] [--modeac] [--aircraft] [--block BYTES] [--beast FILE] capture.bin
+// usage: adsbcu_replay --path a|b|uat [--fix|--fix-2bit] [--no-fix-df] [--modeac] [--aircraft] [--decode] [--block BYTES] [--beast FILE] capture.bin
 // (--modeac: every block is one mag_buf of the reference; use --block 262144 to mirror dump1090 --ifile)
 #include "adsbcu_handlers.hpp"
 
@@ -22,7 +24,7 @@ int main(int argc, char **argv)
 {
     std::string path = "a", file, beast_file;
     int nfix = 0, fix_df = 1;
-    bool mode_ac = false, aircraft = false;
+    bool mode_ac = false, aircraft = false, decode = false;
     size_t block = 262144;   // RTLSDR::BufferLength (RTLSDR.hpp:55)
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
@@ -32,6 +34,7 @@ int main(int argc, char **argv)
         else if (a == "--no-fix-df") fix_df = 0;
         else if (a == "--modeac") mode_ac = true;
         else if (a == "--aircraft") aircraft = true;
+        else if (a == "--decode") decode = true;
         else if (a == "--block" && i + 1 < argc) block = std::strtoull(argv[++i], nullptr, 0);
         else if (a == "--beast" && i + 1 < argc) beast_file = argv[++i];
         else file = a;
@@ -55,6 +58,17 @@ int main(int argc, char **argv)
                 }
                 ++count;
             }, nfix, fix_df, 0, uint32_t(std::max<size_t>(block / 2, 1u << 20)), mode_ac);
+            if (decode)
+                static_cast<ModeS2400Handler *>(h.get())->SetDecodedSink(
+                    [](adsbcu_msg const &m, adsbcu_fields_a const &f, adsbcu_fields_es const &e, adsbcu_fields_commb const &b) {
+                        std::printf("# DF%u airground=%u alt=%d/%u squawk=%04x/%u es=%u metype=%u.%u addr=%07X addrtype=%u valid=%08X callsign=%.8s "
+                                    "cpr=%u,%u,%u alt_baro=%d alt_geom=%d gs=%.3f heading=%.3f commb=%u mbvalid=%05X mbcallsign=%.8s\n",
+                                    unsigned(m.msgtype), unsigned(e.es ? e.airground : f.airground), f.altitude_baro, unsigned(f.altitude_baro_valid),
+                                    unsigned(f.squawk), unsigned(f.squawk_valid), unsigned(e.es), unsigned(e.metype), unsigned(e.mesub), e.addr,
+                                    unsigned(e.addrtype), e.valid, std::string(e.callsign, 8).c_str(), unsigned(e.cpr_odd), e.cpr_lat, e.cpr_lon,
+                                    e.altitude_baro, e.altitude_geom, double(e.gs_selected), double(e.heading), unsigned(b.commb_format), b.valid,
+                                    std::string(b.callsign, 8).c_str());
+                    });
         } else if (path == "b") {
             auto raw = [&](adsbcu_msg_b const &m) {
                 std::printf("*");

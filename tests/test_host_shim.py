@@ -119,3 +119,34 @@ def test_replay_path_b_aircraft_callbacks_match_reference(tmp_path):
     assert len(got) == len(want)
     assert got == want
     assert sum(1 for c in calls if c["lat1e7"] != 0) > 10 and sum(1 for c in calls if c["speed"] != 0) > 10
+
+
+@pytest.mark.gpu
+def test_replay_decode_lines_equal_the_oracles_fields(golden, tmp_path, oracle_mod):
+    """`adsbcu_replay --path a --fix-2bit --decode`: the handler's decoded sink (three batched decode calls per buffer) prints what
+    decodeModesMessage fills in; the lines must be those the oracle's field / ES / Comm-B restatements (each pinned to the
+    reference binary) give for the reference's own messages of the capture."""
+    g = golden["c3_dense"]
+    cap = tmp_path / "cap.uc8"
+    g["iq"].tofile(cap)
+    p = subprocess.run([_replay(), "--path", "a", "--fix-2bit", "--decode", str(cap)], capture_output=True, text=True)
+    assert p.returncode == 0, p.stderr
+    got = [ln for ln in p.stdout.splitlines() if ln.startswith("# ")]
+    ref = g["ref_fix2_df1"]
+    f = oracle_mod.decode_fields(ref)
+    e = oracle_mod.decode_es(ref["msg"], ref["correctedbits"])
+    b = oracle_mod.decode_commb(ref["msg"], ref["correctedbits"])
+    assert len(got) == len(ref) > 200
+
+    def text(s):
+        return bytes(s).split(b"\0")[0].decode("latin-1")
+
+    for k in range(len(ref)):
+        want = ("# DF%u airground=%u alt=%d/%u squawk=%04x/%u es=%u metype=%u.%u addr=%07X addrtype=%u valid=%08X callsign=%s "
+                "cpr=%u,%u,%u alt_baro=%d alt_geom=%d gs=%.3f heading=%.3f commb=%u mbvalid=%05X mbcallsign=%s" % (
+                    ref["msgtype"][k], e["airground"][k] if e["es"][k] else f["airground"][k], f["altitude_baro"][k], f["altitude_baro_valid"][k],
+                    f["squawk"][k], f["squawk_valid"][k], e["es"][k], e["metype"][k], e["mesub"][k], e["addr"][k], e["addrtype"][k], e["valid"][k],
+                    text(e["callsign"][k]), e["cpr_odd"][k], e["cpr_lat"][k], e["cpr_lon"][k], e["altitude_baro"][k], e["altitude_geom"][k],
+                    float(e["gs_selected"][k]), float(e["heading"][k]), b["commb_format"][k], b["valid"][k], text(b["callsign"][k])))
+        assert got[k] == want, (k, got[k], want)
+    assert sum(" es=1 " in ln for ln in got) > 100 and sum(" commb=2 " in ln for ln in got) > 3
