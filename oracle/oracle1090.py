@@ -172,11 +172,12 @@ def decode_commb(frames: np.ndarray, corrected=None) -> np.ndarray:
     return out
 
 
-def run_ref_decode(frames: np.ndarray, commb=False):
+def run_ref_decode(frames: np.ndarray, commb=False, header=False):
     """The reference's own decodeModesMessage on 14-byte frames as received (third tap of ref_harness.c): the ES
-    record of each frame (commb=True: the Comm-B record) and decodeModesMessage's return code."""
+    record of each frame (commb=True: the Comm-B record; header=True: the surveillance-field record) and
+    decodeModesMessage's return code."""
     frames = np.ascontiguousarray(frames, np.uint8).reshape(-1, 14)
-    rec = np.dtype([("es", FIELDS_ES_DTYPE), ("mb", FIELDS_MB_DTYPE), ("rc", "<i4")])
+    rec = np.dtype([("es", FIELDS_ES_DTYPE), ("mb", FIELDS_MB_DTYPE), ("hdr", FIELDS_A_DTYPE), ("rc", "<i4")])
     tmpdir = "/dev/shm" if os.path.isdir("/dev/shm") else None
     with tempfile.TemporaryDirectory(dir=tmpdir) as d:
         fin, fout = os.path.join(d, "frames.bin"), os.path.join(d, "es.bin")
@@ -185,7 +186,7 @@ def run_ref_decode(frames: np.ndarray, commb=False):
                        stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
         r = np.fromfile(fout, dtype=rec)
     assert len(r) == len(frames)
-    return r["mb" if commb else "es"].copy(), r["rc"].copy()
+    return r["hdr" if header else "mb" if commb else "es"].copy(), r["rc"].copy()
 
 
 def run_ref_fields(iq: np.ndarray, nfix_crc=0, fix_df=1):

@@ -57,6 +57,23 @@ static void close_out(void)
     out_fp = NULL;
 }
 
+/* the surveillance fields decodeModesMessage filled in (mode_s.c:626-779), in the layout of adsbcu_fields_a */
+struct hdr_fields { uint16_t AC, ID; uint8_t CA, CC, CF, DR, FS, KE, ND, RI, SL, UM, VS, airground, alert_valid, alert, spi_valid, spi,
+                    altitude_baro_valid, altitude_baro_unit, squawk_valid, es_pending; uint16_t squawk; uint16_t pad; int32_t altitude_baro; };
+static void hdr_record(const struct modesMessage *mm, struct hdr_fields *out)
+{
+    struct hdr_fields f;
+    memset(&f, 0, sizeof(f));
+    f.AC = (uint16_t) mm->AC; f.ID = (uint16_t) mm->ID; f.CA = (uint8_t) mm->CA; f.CC = (uint8_t) mm->CC; f.CF = (uint8_t) mm->CF;
+    f.DR = (uint8_t) mm->DR; f.FS = (uint8_t) mm->FS; f.KE = (uint8_t) mm->KE; f.ND = (uint8_t) mm->ND; f.RI = (uint8_t) mm->RI;
+    f.SL = (uint8_t) mm->SL; f.UM = (uint8_t) mm->UM; f.VS = (uint8_t) mm->VS; f.airground = (uint8_t) mm->airground;
+    f.alert_valid = mm->alert_valid; f.alert = mm->alert; f.spi_valid = mm->spi_valid; f.spi = mm->spi;
+    f.altitude_baro_valid = mm->altitude_baro_valid; f.altitude_baro_unit = (uint8_t) mm->altitude_baro_unit;
+    f.squawk_valid = mm->squawk_valid; f.es_pending = (mm->msgtype == 17 || mm->msgtype == 18);
+    f.squawk = (uint16_t) mm->squawk; f.altitude_baro = mm->altitude_baro;
+    *out = f;
+}
+
 void __wrap_useModesMessage(struct modesMessage *mm)
 {
     if (!out_checked) {
@@ -96,16 +113,8 @@ void __wrap_useModesMessage(struct modesMessage *mm)
             if (p && *p) ffp = fopen(p, "wb");
         }
         if (ffp) {
-            struct { uint16_t AC, ID; uint8_t CA, CC, CF, DR, FS, KE, ND, RI, SL, UM, VS, airground, alert_valid, alert, spi_valid, spi,
-                     altitude_baro_valid, altitude_baro_unit, squawk_valid, es_pending; uint16_t squawk; uint16_t pad; int32_t altitude_baro; } f;
-            memset(&f, 0, sizeof(f));
-            f.AC = (uint16_t) mm->AC; f.ID = (uint16_t) mm->ID; f.CA = (uint8_t) mm->CA; f.CC = (uint8_t) mm->CC; f.CF = (uint8_t) mm->CF;
-            f.DR = (uint8_t) mm->DR; f.FS = (uint8_t) mm->FS; f.KE = (uint8_t) mm->KE; f.ND = (uint8_t) mm->ND; f.RI = (uint8_t) mm->RI;
-            f.SL = (uint8_t) mm->SL; f.UM = (uint8_t) mm->UM; f.VS = (uint8_t) mm->VS; f.airground = (uint8_t) mm->airground;
-            f.alert_valid = mm->alert_valid; f.alert = mm->alert; f.spi_valid = mm->spi_valid; f.spi = mm->spi;
-            f.altitude_baro_valid = mm->altitude_baro_valid; f.altitude_baro_unit = (uint8_t) mm->altitude_baro_unit;
-            f.squawk_valid = mm->squawk_valid; f.es_pending = (mm->msgtype == 17 || mm->msgtype == 18);
-            f.squawk = (uint16_t) mm->squawk; f.altitude_baro = mm->altitude_baro;
+            struct hdr_fields f;
+            hdr_record(mm, &f);
             fwrite(&f, sizeof(f), 1, ffp);
             fflush(ffp);
         }
@@ -247,12 +256,20 @@ int __wrap_main(int argc, char **argv)
         memset(&mm, 0, sizeof(mm));  /* demod_2400.c:355 */
         /* Address/Parity replies are only accepted from aircraft the filter knows: let it know this one, as an earlier
          * DF11 / DF17 of the same aircraft would have (mode_s.c:781-788) */
-        if ((frame[0] >> 3) == 20 || (frame[0] >> 3) == 21) icaoFilterAdd(modesChecksum(frame, 112));
+        struct hdr_fields hf;
+        {
+            const int df = frame[0] >> 3;
+            if (df == 20 || df == 21 || df == 16) icaoFilterAdd(modesChecksum(frame, 112));
+            if (df == 0 || df == 4 || df == 5) icaoFilterAdd(modesChecksum(frame, 56));
+            if (df == 11) icaoFilterAdd(((uint32_t) frame[1] << 16) | ((uint32_t) frame[2] << 8) | frame[3]);
+        }
         mm.score = scoreModesMessage(frame);
         rc = decodeModesMessage(&mm, frame);
-        if (rc < 0) { memset(&e, 0, sizeof(e)); memset(&b, 0, sizeof(b)); } else { es_record(&mm, &e); mb_record(&mm, &b); }
+        if (rc < 0) { memset(&e, 0, sizeof(e)); memset(&b, 0, sizeof(b)); memset(&hf, 0, sizeof(hf)); }
+        else { es_record(&mm, &e); mb_record(&mm, &b); hdr_record(&mm, &hf); }
         fwrite(&e, sizeof(e), 1, fo);
         fwrite(&b, sizeof(b), 1, fo);
+        fwrite(&hf, sizeof(hf), 1, fo);
         fwrite(&rc, sizeof(rc), 1, fo);
     }
     fclose(fi); fclose(fo);
